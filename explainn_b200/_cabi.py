@@ -1,0 +1,105 @@
+"""ctypes binding of libexplainn_b200.so (see include/explainn_b200.h).
+
+There is no fallback: if the shared object is missing this module raises at import, and every op
+raises if the CUDA call fails.
+"""
+import ctypes as C
+import os
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "csrc", "libexplainn_b200.so")
+
+if not os.path.exists(LIB_PATH):
+    raise ImportError(
+        "explainn_b200: %s not found. Build it with `python build_lib.py` "
+        "(nvcc, sm_100a); there is no CPU or PyTorch fallback." % LIB_PATH)
+
+lib = C.CDLL(LIB_PATH)
+
+DTYPE_F32, DTYPE_F16 = 0, 1
+LOSS_BCE, LOSS_MSE = 0, 1
+
+_P, _LL, _I, _F = C.c_void_p, C.c_longlong, C.c_int, C.c_float
+
+# name -> argtypes (restype int unless listed in _RESTYPES)
+SIGNATURES = {
+    "explainn_last_error": [],
+    "explainn_abi_version": [],
+    "explainn_num_sms": [],
+    "explainn_pack_onehot": [_P, _I, _LL, _I, _LL, _P, _P, _P, _P],
+    "explainn_conv_tables_floats": [_I, _I],
+    "explainn_conv_wq_floats": [_I, _I],
+    "explainn_conv_prepare": [_P, _P, _P, _P, _P, _P, _F, _I, _I, _P, _P, _P, _P, _P],
+    "explainn_conv_pool_fwd": [_P, _P, _LL, _I, _I, _I, _P, _P, _P, _P, _P],
+    "explainn_conv_pool_fwd_train": [_P, _P, _LL, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P],
+    "explainn_unit_activations": [_P, _P, _LL, _I, _I, _I, _P, _P, _P, _P, _I, _P],
+    "explainn_interp_unit_max_scratch_floats": [_I],
+    "explainn_interp_unit_max": [_P, _P, _LL, _I, _I, _I, _P, _P, _P, _P, _P, _I, _P],
+    "explainn_interp_thresholds": [_P, _I, _P, _P, _P, _P, _P],
+    "explainn_interp_pwm_count": [_P, _P, _LL, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P],
+    "explainn_fc_stack_fwd_eval": [_P, _LL, _I, _I] + [_P] * 12 + [_F, _P, _P],
+    "explainn_linear_fwd": [_P, _LL, _I, _I, _P, _P, _P, _P],
+}
+_RESTYPES = {
+    "explainn_last_error": C.c_char_p,
+    "explainn_conv_tables_floats": _LL,
+    "explainn_conv_wq_floats": _LL,
+    "explainn_interp_unit_max_scratch_floats": _LL,
+}
+
+
+def _bind():
+    for name, argtypes in SIGNATURES.items():
+        fn = getattr(lib, name)      # AttributeError if the library lacks a declared symbol
+        fn.argtypes = argtypes
+        fn.restype = _RESTYPES.get(name, C.c_int)
+
+
+def register(name, argtypes, restype=C.c_int):
+    """Bind one more symbol (used by modules that add entry points)."""
+    SIGNATURES[name] = argtypes
+    if restype is not C.c_int:
+        _RESTYPES[name] = restype
+    fn = getattr(lib, name)
+    fn.argtypes = argtypes
+    fn.restype = restype
+
+
+_bind()
+
+
+def last_error():
+    return lib.explainn_last_error().decode()
+
+
+def ptr(t):
+    """Device pointer of a contiguous CUDA tensor (None -> NULL)."""
+    if t is None:
+        return None
+    if not t.is_cuda:
+        raise ValueError("explainn_b200: expected a CUDA tensor, got device %s (no CPU path exists)" % t.device)
+    if not t.is_contiguous():
+        raise ValueError("explainn_b200: tensor must be contiguous")
+    return t.data_ptr()
+
+
+def stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+LAUNCHES = 0   # kernels launched through this binding (bench.py reports it)
+_LAUNCH_COST = {"explainn_interp_unit_max": 3}
+
+
+def call(name, *args):
+    global LAUNCHES
+    rc = getattr(lib, name)(*args)
+    if rc != 0:
+        msg = "%s failed (code %d): %s" % (name, rc, last_error())
+        if rc in (1, 3, 4):
+            raise ValueError(msg)
+        raise RuntimeError(msg)
+    LAUNCHES += _LAUNCH_COST.get(name, 1)
+    return rc

@@ -1,0 +1,703 @@
+// conv.cu -- the fused one-hot grouped-conv core and the kernels built on it.
+//
+// What it replaces in the reference (paths relative to /root/reference):
+//   x.repeat(1,U,1) + linears[0..3] = Conv1d(groups=U) -> BatchNorm1d -> exp -> MaxPool1d(7,7)
+//       explainn/models/networks.py:98-102,153
+//   linears[:3] activation scan cast to float16 ....... explainn/interpretation/interpretation.py:143-147
+//   per-unit max and threshold/count PWM extraction .... explainn/interpretation/interpretation.py:187-214
+//
+// Formulation.  On one-hot DNA the 4xF convolution is a gather-sum: y[s] = sum_k w[code(s+k), k].
+// Sequences arrive 2-bit packed, so four adjacent taps form an 8-bit k-mer index; the weights
+// (with BatchNorm folded in) are pre-summed into G = ceil(F/4) lookup tables of 256 entries per
+// unit (prep.cu).  One CTA owns a tile of 32 units (lane = unit): the G*256*32 floats of tables
+// (160 KB for F = 19) are brought into shared memory by TMA bulk copies, a warp walks one sequence
+// at a time, every lane adds G table entries per position (conflict-free: all lanes read the same
+// k-mer row, consecutive banks) and the pool / exp / threshold logic runs on registers.  Nothing
+// of size (B,U,S) is ever written unless the caller asks for the activation map itself.
+//
+// Canonical arithmetic order (shared with oracle/explainn_oracle.c, bit-exact):
+//   t_g = ((a_4g + a_4g+1) + a_4g+2) + a_4g+3 ;  z = (((t_0 + t_1) + ...) + t_{G-1}) + shift[u]
+// where a_k = 0 for N columns and for taps k >= F.  Windows that contain an N column take a
+// per-tap path that evaluates exactly the same expression.
+#include "common.cuh"
+#include "../../include/explainn_b200.h"
+
+namespace {
+
+constexpr int NW = 8;             // warps per CTA
+constexpr int ITER_WIN = 3;       // pool windows per unrolled iteration
+constexpr int ITER_POS = ITER_WIN * XB_POOL;   // 21 positions
+constexpr int TBL_GROUP_BYTES = 256 * XB_UT * 4;   // 32 KB per k-mer group
+
+struct ConvArgs {
+    const uint32_t *codes;     // (B, wc)
+    const uint32_t *nmask;     // (B, wm)
+    long long B;
+    int L, F, U, S;
+    int wc, wm;
+    int seq_stride;            // words of per-warp staging (codes + mask, padded)
+    int mask_off;              // word offset of the mask inside the staging buffer
+    const float *tables;       // (tiles, G, 256, 32)
+    const float *wq_t;         // (tiles, 4, F, 32) folded weights, lane-minor
+    const float *shift;        // (U)
+    int nwin;                  // windows to visit per sequence
+};
+
+__device__ __forceinline__ float lds_f32(const unsigned char *smem, uint32_t off)
+{
+    return *reinterpret_cast<const float *>(smem + off);
+}
+
+// ----------------------------------------------------------------------------------------------
+// Sinks: what happens with the 7 z-values of one pool window.  `acc` excludes shift[u].
+// ----------------------------------------------------------------------------------------------
+
+// (1) inference pooling: pooled[u][b][p] = exp(max_window z)   (unit-major, see fc.cu)
+struct PoolSink {
+    struct Params { float *pooled; int P; };
+    static constexpr int PCH = 36;
+    static __host__ __device__ int smem_bytes(int P) { int ps = (P < PCH ? P : PCH) | 1; return NW * XB_UT * ps * 4; }
+    Params p;
+    float *stage;
+    int ps, lane, nvalid;
+    float shift;
+    long long out_base, row_stride;   // element offset of pooled[u0][b][0]; distance between units
+    int win_base;
+    __device__ void init_cta(unsigned char *smem, const Params &pp, int warp, int lane_)
+    {
+        p = pp;
+        ps = (p.P < PCH ? p.P : PCH) | 1;
+        stage = reinterpret_cast<float *>(smem) + warp * XB_UT * ps;
+        lane = lane_;
+    }
+    __device__ void begin_tile(int u0, int nvalid_, float shift_, const ConvArgs &) { nvalid = nvalid_; shift = shift_; (void)u0; }
+    __device__ void begin_seq(long long b, int u0, const ConvArgs &a)
+    {
+        row_stride = a.B * p.P;
+        out_base = ((long long)u0 * a.B + b) * p.P;
+        win_base = 0;
+    }
+    __device__ void flush(int upto)
+    {
+        __syncwarp();
+        const int n = upto - win_base;
+        for (int r = 0; r < nvalid; ++r)
+            for (int c = lane; c < n; c += 32) p.pooled[out_base + r * row_stride + win_base + c] = stage[r * ps + c];
+        __syncwarp();
+        win_base = upto;
+    }
+    __device__ __forceinline__ void window(int win, int, const float *acc, const ConvArgs &)
+    {
+        if (win >= p.P) return;
+        if (win - win_base == PCH) flush(win);
+        float m = acc[0];
+#pragma unroll
+        for (int j = 1; j < XB_POOL; ++j) m = fmaxf(m, acc[j]);
+        stage[lane * ps + (win - win_base)] = det_expf(__fadd_rn(m, shift));
+    }
+    __device__ void end_seq(const ConvArgs &) { flush(p.P); }
+    __device__ void end_tile(int, const ConvArgs &) {}
+};
+
+// (2) training pooling: tables hold x_hat = (y - mu) / sigma; z = gamma * x_hat + beta.
+//     Emits pooled = exp(z*) , x_hat* and the first-max index inside the window.
+struct PoolTrainSink {
+    struct Params { float *pooled; float *xhat; unsigned char *idx; const float *gamma; const float *beta; int P; };
+    static constexpr int PCH = 12;
+    static __host__ __device__ int smem_bytes(int) { return NW * XB_UT * (PCH + 1) * 12; }
+    Params p;
+    float *st_a, *st_x;
+    int *st_i;
+    int lane, nvalid;
+    float shift, gam, bet;
+    long long out_base, row_stride;
+    int win_base;
+    __device__ void init_cta(unsigned char *smem, const Params &pp, int warp, int lane_)
+    {
+        p = pp;
+        lane = lane_;
+        float *base = reinterpret_cast<float *>(smem) + warp * XB_UT * (PCH + 1) * 3;
+        st_a = base;
+        st_x = base + XB_UT * (PCH + 1);
+        st_i = reinterpret_cast<int *>(base + 2 * XB_UT * (PCH + 1));
+    }
+    __device__ void begin_tile(int u0, int nvalid_, float shift_, const ConvArgs &a)
+    {
+        nvalid = nvalid_;
+        shift = shift_;
+        const int u = u0 + lane;
+        gam = u < a.U ? p.gamma[u] : 1.0f;
+        bet = u < a.U ? p.beta[u] : 0.0f;
+    }
+    __device__ void begin_seq(long long b, int u0, const ConvArgs &a)
+    {
+        row_stride = a.B * p.P;
+        out_base = ((long long)u0 * a.B + b) * p.P;
+        win_base = 0;
+    }
+    __device__ void flush(int upto)
+    {
+        __syncwarp();
+        const int n = upto - win_base;
+        for (int r = 0; r < nvalid; ++r)
+            for (int c = lane; c < n; c += 32) {
+                const long long o = out_base + r * row_stride + win_base + c;
+                p.pooled[o] = st_a[r * (PCH + 1) + c];
+                p.xhat[o] = st_x[r * (PCH + 1) + c];
+                p.idx[o] = (unsigned char)st_i[r * (PCH + 1) + c];
+            }
+        __syncwarp();
+        win_base = upto;
+    }
+    __device__ __forceinline__ void window(int win, int, const float *acc, const ConvArgs &)
+    {
+        if (win >= p.P) return;
+        if (win - win_base == PCH) flush(win);
+        // first maximum of z = gamma * x_hat + beta (networks.py:100-102; MaxPool1d backward routes the
+        // gradient to the first maximal element)
+        float xb = __fadd_rn(acc[0], shift);
+        float zb = __fmaf_rn(gam, xb, bet);
+        int ib = 0;
+#pragma unroll
+        for (int j = 1; j < XB_POOL; ++j) {
+            const float x = __fadd_rn(acc[j], shift);
+            const float z = __fmaf_rn(gam, x, bet);
+            if (z > zb) { zb = z; xb = x; ib = j; }
+        }
+        const int c = win - win_base;
+        st_a[lane * (PCH + 1) + c] = det_expf(zb);
+        st_x[lane * (PCH + 1) + c] = xb;
+        st_i[lane * (PCH + 1) + c] = ib;
+    }
+    __device__ void end_seq(const ConvArgs &) { flush(p.P); }
+    __device__ void end_tile(int, const ConvArgs &) {}
+};
+
+// (3) activation map: act[b,u,s] = exp(z) for every s < S, float16 or float32
+template <typename OutT>
+struct ActSink {
+    struct Params { OutT *act; };
+    static constexpr int PCH = 12;                       // windows per flush = 84 positions
+    static constexpr int ROW = PCH * XB_POOL + 1;
+    static __host__ __device__ int smem_bytes(int) { return NW * XB_UT * ROW * (int)sizeof(OutT); }
+    Params p;
+    OutT *stage;
+    int lane, nvalid;
+    float shift;
+    long long out_base;
+    int win_base;
+    __device__ void init_cta(unsigned char *smem, const Params &pp, int warp, int lane_)
+    {
+        p = pp;
+        lane = lane_;
+        stage = reinterpret_cast<OutT *>(smem) + warp * XB_UT * ROW;
+    }
+    __device__ void begin_tile(int, int nvalid_, float shift_, const ConvArgs &) { nvalid = nvalid_; shift = shift_; }
+    __device__ void begin_seq(long long b, int u0, const ConvArgs &a) { out_base = (b * a.U + u0) * (long long)a.S; win_base = 0; }
+    __device__ void flush(int upto_win, const ConvArgs &a)
+    {
+        __syncwarp();
+        const int s0 = win_base * XB_POOL;
+        int n = upto_win * XB_POOL - s0;
+        if (s0 + n > a.S) n = a.S - s0;
+        for (int r = 0; r < nvalid; ++r)
+            for (int c = lane; c < n; c += 32) p.act[out_base + (long long)r * a.S + s0 + c] = stage[r * ROW + c];
+        __syncwarp();
+        win_base = upto_win;
+    }
+    __device__ __forceinline__ void window(int win, int, const float *acc, const ConvArgs &a)
+    {
+        if (win >= a.nwin) return;
+        if (win - win_base == PCH) flush(win, a);
+        const int c0 = (win - win_base) * XB_POOL;
+#pragma unroll
+        for (int j = 0; j < XB_POOL; ++j) stage[lane * ROW + c0 + j] = (OutT)det_expf(__fadd_rn(acc[j], shift));
+    }
+    __device__ void end_seq(const ConvArgs &a) { flush(a.nwin, a); }
+    __device__ void end_tile(int, const ConvArgs &) {}
+};
+
+// (4) interpretation pass A: per-unit maximum of z over all sequences and positions s < S
+struct MaxSink {
+    struct Params { float *zmax_partial; int n_cta; };   // (n_cta, U) initialised to -inf by the host wrapper
+    static __host__ __device__ int smem_bytes(int) { return NW * XB_UT * 4; }
+    Params p;
+    float *red;
+    int lane, warp;
+    float shift, m;
+    __device__ void init_cta(unsigned char *smem, const Params &pp, int warp_, int lane_)
+    {
+        p = pp;
+        lane = lane_;
+        warp = warp_;
+        red = reinterpret_cast<float *>(smem);
+    }
+    __device__ void begin_tile(int, int, float shift_, const ConvArgs &) { shift = shift_; m = -INFINITY; }
+    __device__ void begin_seq(long long, int, const ConvArgs &) {}
+    __device__ __forceinline__ void window(int win, int t, const float *acc, const ConvArgs &a)
+    {
+        if (win >= a.nwin) return;
+#pragma unroll
+        for (int j = 0; j < XB_POOL; ++j)
+            if (t + j < a.S) m = fmaxf(m, acc[j]);
+    }
+    __device__ void end_seq(const ConvArgs &) {}
+    __device__ void end_tile(int u0, const ConvArgs &a)
+    {
+        // adding the same shift is monotone, so max(acc) + shift == max(acc + shift) exactly
+        red[warp * XB_UT + lane] = __fadd_rn(m, shift);
+        __syncthreads();
+        if (warp == 0) {
+            float v = red[lane];
+            for (int w = 1; w < NW; ++w) v = fmaxf(v, red[w * XB_UT + lane]);
+            const int u = u0 + lane;
+            if (u < a.U) {
+                float *dst = p.zmax_partial + (long long)blockIdx.x * a.U + u;
+                *dst = fmaxf(*dst, v);
+            }
+        }
+        __syncthreads();
+    }
+};
+
+// (5) interpretation pass B: count one-hot windows at positions whose float16 activation exceeds
+//     the float16 threshold (interpretation.py:187,209-214).
+//     hit  <=>  half(exp(z)) > thr  <=>  z > zhi, or z in (zlo, zhi] and the exact test holds;
+//     zlo/zhi bracket the cut-over by 64 ulps on each side (prep.cu: interp_thresholds).
+struct CountSink {
+    struct Params { const float *zlo; const float *zhi; const float *thr; unsigned long long *counts; unsigned long long *hits; };
+    static __host__ __device__ int smem_bytes(int F) { return (4 * F + 1) * XB_UT * 4; }
+    Params p;
+    unsigned int *cnt;   // [4*F + 1][32]; last row = number of hit positions
+    int lane, warp;
+    float shift, zlo, zhi, thr;
+    const uint32_t *cw, *mw;
+    __device__ void init_cta(unsigned char *smem, const Params &pp, int warp_, int lane_)
+    {
+        p = pp;
+        lane = lane_;
+        warp = warp_;
+        cnt = reinterpret_cast<unsigned int *>(smem);
+    }
+    __device__ void begin_tile(int u0, int, float shift_, const ConvArgs &a)
+    {
+        shift = shift_;
+        const int u = u0 + lane;
+        zlo = u < a.U ? p.zlo[u] : INFINITY;
+        zhi = u < a.U ? p.zhi[u] : INFINITY;
+        thr = u < a.U ? p.thr[u] : INFINITY;
+        for (int i = threadIdx.x; i < (4 * a.F + 1) * XB_UT; i += blockDim.x) cnt[i] = 0;
+        __syncthreads();
+    }
+    __device__ void set_seq(const uint32_t *cw_, const uint32_t *mw_) { cw = cw_; mw = mw_; }
+    __device__ void begin_seq(long long, int, const ConvArgs &) {}
+    __device__ __forceinline__ void window(int win, int t, const float *acc, const ConvArgs &a)
+    {
+        if (win >= a.nwin) return;
+        unsigned hitmask = 0;
+#pragma unroll
+        for (int j = 0; j < XB_POOL; ++j) {
+            const float z = __fadd_rn(acc[j], shift);
+            bool h = z > zhi;
+            if (!h && z > zlo) h = fp16_round(det_expf(z)) > thr;
+            if (h && t + j < a.S) hitmask |= 1u << j;
+        }
+        if (__any_sync(0xffffffffu, hitmask != 0)) record(t, hitmask, a);
+    }
+    __device__ __noinline__ void record(int t, unsigned hitmask, const ConvArgs &a)
+    {
+        for (int j = 0; j < XB_POOL; ++j) {
+            const bool h = (hitmask >> j) & 1;
+            if (!__any_sync(0xffffffffu, h)) continue;
+            if (h) atomicAdd(&cnt[4 * a.F * XB_UT + lane], 1u);
+            for (int k = 0; k < a.F; ++k) {
+                const int pos = t + j + k;
+                if ((mw[pos >> 5] >> (pos & 31)) & 1) continue;
+                const int c = (cw[pos >> 4] >> (2 * (pos & 15))) & 3;
+                if (h) atomicAdd(&cnt[(c * a.F + k) * XB_UT + lane], 1u);
+            }
+        }
+    }
+    __device__ void end_seq(const ConvArgs &) {}
+    __device__ void end_tile(int u0, const ConvArgs &a)
+    {
+        __syncthreads();
+        for (int i = threadIdx.x; i < (4 * a.F + 1) * XB_UT; i += blockDim.x) {
+            const unsigned v = cnt[i];
+            const int u = u0 + (i & 31);
+            if (v && u < a.U) {
+                const int row = i >> 5;
+                if (row < 4 * a.F) atomicAdd(&p.counts[(long long)u * 4 * a.F + row], (unsigned long long)v);
+                else atomicAdd(&p.hits[u], (unsigned long long)v);
+            }
+        }
+        __syncthreads();
+    }
+};
+
+template <class Sink> struct NeedsSeq { static constexpr bool value = false; };
+template <> struct NeedsSeq<CountSink> { static constexpr bool value = true; };
+
+// ----------------------------------------------------------------------------------------------
+// The scan kernel.  grid = one CTA per SM; the flattened (tile, sequence) space is split evenly.
+// ----------------------------------------------------------------------------------------------
+template <int G, class Sink>
+__global__ void __launch_bounds__(NW * 32, 1) conv_scan_kernel(const ConvArgs a, const typename Sink::Params sp)
+{
+    constexpr int SPAN = 4 * (G - 1);
+    constexpr int NA = ITER_POS + SPAN;
+    extern __shared__ __align__(128) unsigned char smem[];
+    __shared__ __align__(8) uint64_t bar;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    unsigned char *tbl = smem;                                         // G * 32 KB
+    float *wq = reinterpret_cast<float *>(smem + G * TBL_GROUP_BYTES); // 4*F*32 floats
+    uint32_t *seqbuf = reinterpret_cast<uint32_t *>(wq + 4 * a.F * XB_UT) + warp * a.seq_stride;
+    unsigned char *sink_smem = reinterpret_cast<unsigned char *>(reinterpret_cast<uint32_t *>(wq + 4 * a.F * XB_UT) + NW * a.seq_stride);
+
+    Sink sink;
+    sink.init_cta(sink_smem, sp, warp, lane);
+
+    if (threadIdx.x == 0) {
+        mbar_init(&bar, 1);
+        mbar_fence_init();
+    }
+    // zero the staging buffer once: words past the sequence stay zero for the over-read taps
+    for (int i = lane; i < a.seq_stride; i += 32) seqbuf[i] = 0;
+    __syncthreads();
+
+    const int n_tiles = (a.U + XB_UT - 1) / XB_UT;
+    const long long total = (long long)n_tiles * a.B;
+    long long it0 = total * blockIdx.x / gridDim.x;
+    const long long it1 = total * (blockIdx.x + 1) / gridDim.x;
+    uint32_t parity = 0;
+    const uint32_t lane_base = lane * 4;
+    const uint32_t *cw = seqbuf, *mw = seqbuf + a.mask_off;
+    const int nit = (a.nwin + ITER_WIN - 1) / ITER_WIN;
+
+    while (it0 < it1) {
+        const int tile = (int)(it0 / a.B);
+        const long long b_lo = it0 % a.B;
+        long long b_hi = b_lo + (it1 - it0);
+        if (b_hi > a.B) b_hi = a.B;
+        const int u0 = tile * XB_UT;
+        const int nvalid = min(XB_UT, a.U - u0);
+
+        // ---- bring this tile's tables in (TMA bulk copies, one per k-mer group) ----
+        if (threadIdx.x == 0) {
+            mbar_arrive_expect_tx(&bar, G * TBL_GROUP_BYTES);
+            const unsigned char *src = reinterpret_cast<const unsigned char *>(a.tables) + (size_t)tile * G * TBL_GROUP_BYTES;
+#pragma unroll
+            for (int g = 0; g < G; ++g) tma_bulk_g2s(tbl + g * TBL_GROUP_BYTES, src + (size_t)g * TBL_GROUP_BYTES, TBL_GROUP_BYTES, &bar);
+        }
+        for (int i = threadIdx.x; i < 4 * a.F * XB_UT; i += blockDim.x) wq[i] = a.wq_t[(size_t)tile * 4 * a.F * XB_UT + i];
+        const float shift = (u0 + lane < a.U) ? a.shift[u0 + lane] : 0.0f;
+        sink.begin_tile(u0, nvalid, shift, a);
+        mbar_wait(&bar, parity);
+        parity ^= 1;
+        __syncthreads();
+
+        // ---- sequences of this segment, one per warp ----
+        long long b = b_lo + warp;
+        uint32_t pre[6];
+        auto prefetch = [&](long long bb) {
+#pragma unroll
+            for (int i = 0; i < 6; ++i) {
+                const int w = lane + 32 * i;
+                pre[i] = 0;
+                if (bb < b_hi) {
+                    if (w < a.wc) pre[i] = a.codes[bb * a.wc + w];
+                    else if (w < a.wc + a.wm) pre[i] = a.nmask[bb * a.wm + (w - a.wc)];
+                }
+            }
+        };
+        prefetch(b);
+        for (; b < b_hi; b += NW) {
+            __syncwarp();
+#pragma unroll
+            for (int i = 0; i < 6; ++i) {
+                const int w = lane + 32 * i;
+                if (w < a.wc) seqbuf[w] = pre[i];
+                else if (w < a.wc + a.wm) seqbuf[a.mask_off + (w - a.wc)] = pre[i];
+            }
+            prefetch(b + NW);
+            __syncwarp();
+            if constexpr (NeedsSeq<Sink>::value) sink.set_seq(cw, mw);
+            sink.begin_seq(b, u0, a);
+
+            uint32_t addr[NA];
+            // prologue: k-mers at positions 0 .. SPAN-1
+            {
+                const uint32_t w0 = cw[0], w1 = cw[1];
+#pragma unroll
+                for (int j = 0; j < SPAN; ++j) {
+                    uint32_t km;
+                    if (2 * j + 8 <= 32) km = w0 >> (2 * j);
+                    else if (2 * j < 32) km = __funnelshift_r(w0, w1, 2 * j);
+                    else km = w1 >> (2 * j - 32);
+                    addr[j] = lane_base + ((km & 0xFFu) << 7);
+                }
+            }
+            for (int it = 0; it < nit; ++it) {
+                const int t0 = it * ITER_POS;
+                // new k-mers at positions t0+SPAN .. t0+SPAN+20
+                {
+                    const uint32_t o = 2u * (uint32_t)(t0 + SPAN);
+                    const uint32_t wi = o >> 5, sh = o & 31u;
+                    const uint32_t w0 = cw[wi], w1 = cw[wi + 1], w2 = cw[wi + 2];
+                    const uint32_t A0 = __funnelshift_r(w0, w1, sh), A1 = __funnelshift_r(w1, w2, sh);
+#pragma unroll
+                    for (int j = 0; j < ITER_POS; ++j) {
+                        uint32_t km;
+                        if (2 * j + 8 <= 32) km = A0 >> (2 * j);
+                        else if (2 * j < 32) km = __funnelshift_r(A0, A1, 2 * j);
+                        else km = A1 >> (2 * j - 32);
+                        addr[SPAN + j] = lane_base + ((km & 0xFFu) << 7);
+                    }
+                }
+                // any N column under this iteration's footprint?
+                bool has_n;
+                {
+                    constexpr int NB = ITER_POS - 1 + 4 * G;   // positions touched
+                    const uint32_t wi = (uint32_t)t0 >> 5, sh = (uint32_t)t0 & 31u;
+                    const uint32_t m0 = mw[wi], m1 = mw[wi + 1], m2 = mw[wi + 2];
+                    const uint32_t M0 = __funnelshift_r(m0, m1, sh), M1 = __funnelshift_r(m1, m2, sh);
+                    if (NB <= 32) has_n = (M0 & (NB == 32 ? 0xFFFFFFFFu : ((1u << (NB & 31)) - 1u))) != 0;
+                    else has_n = (M0 | (M1 & ((1u << ((NB - 32) & 31)) - 1u))) != 0;
+                }
+                float acc[ITER_POS];
+                if (!has_n) {
+#pragma unroll
+                    for (int j = 0; j < ITER_POS; ++j) {
+                        float v = lds_f32(tbl, addr[j]);
+#pragma unroll
+                        for (int g = 1; g < G; ++g) v = __fadd_rn(v, lds_f32(tbl, addr[j + 4 * g] + g * TBL_GROUP_BYTES));
+                        acc[j] = v;
+                    }
+                } else {
+#pragma unroll
+                    for (int j = 0; j < ITER_POS; ++j) {
+                        const int t = t0 + j;
+                        float v = 0.0f;
+#pragma unroll 1
+                        for (int g = 0; g < G; ++g) {
+                            float tg = 0.0f;
+#pragma unroll
+                            for (int jj = 0; jj < 4; ++jj) {
+                                const int k = 4 * g + jj, pos = t + k;
+                                float w = 0.0f;
+                                if (k < a.F && !((mw[pos >> 5] >> (pos & 31)) & 1)) {
+                                    const int c = (cw[pos >> 4] >> (2 * (pos & 15))) & 3;
+                                    w = wq[(c * a.F + k) * XB_UT + lane];
+                                }
+                                tg = jj == 0 ? w : __fadd_rn(tg, w);
+                            }
+                            v = g == 0 ? tg : __fadd_rn(v, tg);
+                        }
+                        acc[j] = v;
+                    }
+                }
+#pragma unroll
+                for (int w = 0; w < ITER_WIN; ++w) sink.window(it * ITER_WIN + w, t0 + w * XB_POOL, acc + w * XB_POOL, a);
+#pragma unroll
+                for (int j = 0; j < SPAN; ++j) addr[j] = addr[j + ITER_POS];
+            }
+            sink.end_seq(a);
+        }
+        __syncthreads();
+        sink.end_tile(u0, a);
+        it0 += (b_hi - b_lo);
+    }
+}
+
+// ----------------------------------------------------------------------------------------------
+// host side
+// ----------------------------------------------------------------------------------------------
+struct Geometry {
+    int G, wc, wm, seq_stride, mask_off, nwin_pool, nwin_all, S, P;
+};
+
+int make_geometry(int L, int F, Geometry *g)
+{
+    if (F < 1 || F > 4 * XB_MAX_G || L < F) return XB_ERR_UNSUPPORTED;
+    g->G = (F + 3) / 4;
+    g->wc = xb_words_codes(L);
+    g->wm = xb_words_mask(L);
+    g->S = L - F + 1;
+    g->P = g->S >= XB_POOL ? (g->S - XB_POOL) / XB_POOL + 1 : 0;
+    g->nwin_pool = g->P;
+    g->nwin_all = (g->S + XB_POOL - 1) / XB_POOL;
+    // positions touched by the unrolled loop: nit*21 + 4G + slack; +3 words for the funnel-shift look-ahead
+    const int nit = (g->nwin_all + ITER_WIN - 1) / ITER_WIN;
+    const int maxpos = nit * ITER_POS + 4 * g->G + 8;
+    const int cw_pad = (2 * maxpos + 31) / 32 + 3;
+    const int mw_pad = (maxpos + 31) / 32 + 3;
+    g->mask_off = cw_pad > g->wc ? cw_pad : g->wc;
+    g->seq_stride = g->mask_off + (mw_pad > g->wm ? mw_pad : g->wm);
+    if (g->wc + g->wm > 6 * 32) return XB_ERR_UNSUPPORTED;   // prefetch registers: L <= 2048
+    return XB_OK;
+}
+
+template <int G, class Sink>
+int launch_scan(const ConvArgs &a, const typename Sink::Params &sp, int sink_smem, cudaStream_t stream)
+{
+    const size_t smem = (size_t)G * TBL_GROUP_BYTES + (size_t)4 * a.F * XB_UT * 4 + (size_t)NW * a.seq_stride * 4 + sink_smem;
+    if (smem > 227 * 1024) {
+        xb_set_error("conv scan: %zu bytes of shared memory needed (filter_size=%d, L=%d) exceed 227 KB", smem, a.F, a.L);
+        return XB_ERR_UNSUPPORTED;
+    }
+    auto kern = conv_scan_kernel<G, Sink>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) {
+        xb_set_error("cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+        return XB_ERR_CUDA;
+    }
+    const int n_tiles = (a.U + XB_UT - 1) / XB_UT;
+    long long total = (long long)n_tiles * a.B;
+    int grid = xb_num_sms();
+    if (total < grid) grid = (int)total;
+    if (grid < 1) return XB_OK;
+    kern<<<grid, NW * 32, smem, stream>>>(a, sp);
+    return xb_check_launch("conv_scan_kernel");
+}
+
+template <class Sink>
+int dispatch_scan(int G, const ConvArgs &a, const typename Sink::Params &sp, int sink_smem, cudaStream_t stream)
+{
+    switch (G) {
+    case 1: return launch_scan<1, Sink>(a, sp, sink_smem, stream);
+    case 2: return launch_scan<2, Sink>(a, sp, sink_smem, stream);
+    case 3: return launch_scan<3, Sink>(a, sp, sink_smem, stream);
+    case 4: return launch_scan<4, Sink>(a, sp, sink_smem, stream);
+    case 5: return launch_scan<5, Sink>(a, sp, sink_smem, stream);
+    case 6: return launch_scan<6, Sink>(a, sp, sink_smem, stream);
+    }
+    xb_set_error("conv scan: filter_size %d not supported (max %d)", a.F, 4 * XB_MAX_G);
+    return XB_ERR_UNSUPPORTED;
+}
+
+int fill_args(ConvArgs *a, Geometry *g, const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F,
+              const float *tables, const float *wq_t, const float *shift)
+{
+    if (!codes || !nmask || !tables || !wq_t || !shift) {
+        xb_set_error("conv scan: null pointer");
+        return XB_ERR_ARG;
+    }
+    if (B < 0 || U < 1) {
+        xb_set_error("conv scan: bad sizes B=%lld U=%d", B, U);
+        return XB_ERR_ARG;
+    }
+    int rc = make_geometry(L, F, g);
+    if (rc != XB_OK) {
+        xb_set_error("conv scan: unsupported geometry L=%d filter_size=%d (need filter_size <= %d, L <= 2048)", L, F, 4 * XB_MAX_G);
+        return rc;
+    }
+    a->codes = codes; a->nmask = nmask; a->B = B; a->L = L; a->F = F; a->U = U; a->S = g->S;
+    a->wc = g->wc; a->wm = g->wm; a->seq_stride = g->seq_stride; a->mask_off = g->mask_off;
+    a->tables = tables; a->wq_t = wq_t; a->shift = shift; a->nwin = 0;
+    return XB_OK;
+}
+
+}  // namespace
+
+extern "C" int explainn_conv_pool_fwd(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F,
+                                      const float *tables, const float *wq_t, const float *shift, float *pooled,
+                                      cudaStream_t stream)
+{
+    ConvArgs a; Geometry g;
+    int rc = fill_args(&a, &g, codes, nmask, B, L, U, F, tables, wq_t, shift);
+    if (rc != XB_OK) return rc;
+    XB_REQUIRE(pooled, "conv_pool_fwd: null output");
+    if (B == 0 || g.P == 0) return XB_OK;
+    a.nwin = g.nwin_pool;
+    PoolSink::Params sp{pooled, g.P};
+    return dispatch_scan<PoolSink>(g.G, a, sp, PoolSink::smem_bytes(g.P), stream);
+}
+
+extern "C" int explainn_conv_pool_fwd_train(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F,
+                                            const float *tables, const float *wq_t, const float *shift,
+                                            const float *gamma, const float *beta, float *pooled, float *xhat,
+                                            unsigned char *idx, cudaStream_t stream)
+{
+    ConvArgs a; Geometry g;
+    int rc = fill_args(&a, &g, codes, nmask, B, L, U, F, tables, wq_t, shift);
+    if (rc != XB_OK) return rc;
+    XB_REQUIRE(pooled && xhat && idx && gamma && beta, "conv_pool_fwd_train: null pointer");
+    if (B == 0 || g.P == 0) return XB_OK;
+    a.nwin = g.nwin_pool;
+    PoolTrainSink::Params sp{pooled, xhat, idx, gamma, beta, g.P};
+    return dispatch_scan<PoolTrainSink>(g.G, a, sp, PoolTrainSink::smem_bytes(g.P), stream);
+}
+
+extern "C" int explainn_unit_activations(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F,
+                                         const float *tables, const float *wq_t, const float *shift, void *act,
+                                         int act_dtype, cudaStream_t stream)
+{
+    ConvArgs a; Geometry g;
+    int rc = fill_args(&a, &g, codes, nmask, B, L, U, F, tables, wq_t, shift);
+    if (rc != XB_OK) return rc;
+    XB_REQUIRE(act, "unit_activations: null output");
+    if (B == 0) return XB_OK;
+    a.nwin = g.nwin_all;
+    if (act_dtype == EXPLAINN_DTYPE_F16) {
+        ActSink<__half>::Params sp{(__half *)act};
+        return dispatch_scan<ActSink<__half>>(g.G, a, sp, ActSink<__half>::smem_bytes(0), stream);
+    } else if (act_dtype == EXPLAINN_DTYPE_F32) {
+        ActSink<float>::Params sp{(float *)act};
+        return dispatch_scan<ActSink<float>>(g.G, a, sp, ActSink<float>::smem_bytes(0), stream);
+    }
+    xb_set_error("unit_activations: unsupported dtype %d", act_dtype);
+    return XB_ERR_UNSUPPORTED;
+}
+
+extern "C" long long explainn_interp_unit_max_scratch_floats(int U) { return (long long)xb_num_sms() * U; }
+
+__global__ void fill_f32_kernel(float *p, long long n, float v)
+{
+    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) p[i] = v;
+}
+__global__ void reduce_zmax_kernel(const float *partial, int n_cta, int U, float *zmax, int accumulate)
+{
+    const int u = blockIdx.x * blockDim.x + threadIdx.x;
+    if (u >= U) return;
+    float m = accumulate ? zmax[u] : -INFINITY;
+    for (int c = 0; c < n_cta; ++c) m = fmaxf(m, partial[(long long)c * U + u]);
+    zmax[u] = m;
+}
+
+extern "C" int explainn_interp_unit_max(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F,
+                                        const float *tables, const float *wq_t, const float *shift, float *scratch,
+                                        float *zmax, int accumulate, cudaStream_t stream)
+{
+    ConvArgs a; Geometry g;
+    int rc = fill_args(&a, &g, codes, nmask, B, L, U, F, tables, wq_t, shift);
+    if (rc != XB_OK) return rc;
+    XB_REQUIRE(scratch && zmax, "interp_unit_max: null pointer");
+    const int n_cta = xb_num_sms();
+    const long long n = (long long)n_cta * U;
+    fill_f32_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(scratch, n, -INFINITY);
+    a.nwin = g.nwin_all;
+    if (B > 0) {
+        MaxSink::Params sp{scratch, n_cta};
+        rc = dispatch_scan<MaxSink>(g.G, a, sp, MaxSink::smem_bytes(0), stream);
+        if (rc != XB_OK) return rc;
+    }
+    reduce_zmax_kernel<<<(U + 127) / 128, 128, 0, stream>>>(scratch, n_cta, U, zmax, accumulate);
+    return xb_check_launch("interp_unit_max");
+}
+
+extern "C" int explainn_interp_pwm_count(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F,
+                                         const float *tables, const float *wq_t, const float *shift, const float *zlo,
+                                         const float *zhi, const float *thr, unsigned long long *counts,
+                                         unsigned long long *hits, cudaStream_t stream)
+{
+    ConvArgs a; Geometry g;
+    int rc = fill_args(&a, &g, codes, nmask, B, L, U, F, tables, wq_t, shift);
+    if (rc != XB_OK) return rc;
+    XB_REQUIRE(zlo && zhi && thr && counts && hits, "interp_pwm_count: null pointer");
+    if (B == 0) return XB_OK;
+    a.nwin = g.nwin_all;
+    CountSink::Params sp{zlo, zhi, thr, counts, hits};
+    return dispatch_scan<CountSink>(g.G, a, sp, CountSink::smem_bytes(F), stream);
+}

@@ -1,0 +1,136 @@
+"""Thin tensor-level wrappers over the C ABI (one function per kernel group).
+
+All tensors are CUDA tensors owned by PyTorch; the C layer never allocates.
+"""
+from collections import namedtuple
+
+import torch
+
+from . import _cabi
+from ._cabi import call, ptr, stream
+
+HIDDEN = 100          # networks.py:106
+POOL = 7
+
+Packed = namedtuple("Packed", "codes nmask B L invalid")
+ConvPrep = namedtuple("ConvPrep", "tables wq_t shift scale U F")
+
+
+def pooled_len(L, F, pool_size=7, pool_stride=7):
+    """networks.py:105 -- int(((L-(F-1)) - (pool_size-1) - 1)/pool_stride + 1)."""
+    return int(((L - (F - 1)) - (pool_size - 1) - 1) / pool_stride + 1)
+
+
+def pack_onehot(x, num_cnns=1, invalid=None):
+    """(B,4,L) or U-times tiled (B,4U,L) float one-hot on the GPU -> Packed (2-bit codes + N mask).
+
+    `invalid` is a 1-element int32 CUDA counter that accumulates the number of columns that are
+    neither one-hot nor all-zero; it is read lazily (see check_invalid) to avoid a sync per batch.
+    """
+    if x.dim() != 3:
+        raise ValueError("expected (B,4,L) input, got shape %s" % (tuple(x.shape),))
+    B, ch, L = x.shape
+    if ch != 4 and ch != 4 * num_cnns:
+        raise ValueError("expected 4 (or 4*num_cnns) input channels, got %d" % ch)
+    if x.dtype == torch.float32:
+        dt = _cabi.DTYPE_F32
+    elif x.dtype == torch.float16:
+        dt = _cabi.DTYPE_F16
+    else:
+        x = x.float()
+        dt = _cabi.DTYPE_F32
+    if not x.is_contiguous():
+        x = x.contiguous()
+    dev = x.device
+    codes = torch.empty((B, (L + 15) // 16), dtype=torch.int32, device=dev)
+    nmask = torch.empty((B, (L + 31) // 32), dtype=torch.int32, device=dev)
+    if invalid is None:
+        invalid = torch.zeros(1, dtype=torch.int32, device=dev)
+    if B:
+        call("explainn_pack_onehot", ptr(x), dt, B, L, ch * L, ptr(codes), ptr(nmask), ptr(invalid), stream())
+    return Packed(codes, nmask, B, L, invalid)
+
+
+def check_invalid(invalid):
+    n = int(invalid.item())
+    if n:
+        invalid.zero_()
+        raise ValueError("explainn_b200: %d input column(s) are neither one-hot nor all-zero; "
+                         "the fused kernels require one-hot DNA (there is no dense fallback)" % n)
+
+
+def conv_prepare(w, bias, gamma, beta, mean, var, eps=1e-5):
+    """Fold BatchNorm into the conv filter and build the k-mer tables."""
+    U, four, F = w.shape
+    dev = w.device
+    tables = torch.empty(_cabi.lib.explainn_conv_tables_floats(U, F), dtype=torch.float32, device=dev)
+    wq_t = torch.empty(_cabi.lib.explainn_conv_wq_floats(U, F), dtype=torch.float32, device=dev)
+    shift = torch.empty(U, dtype=torch.float32, device=dev)
+    scale = torch.empty(U, dtype=torch.float32, device=dev)
+    call("explainn_conv_prepare", ptr(w.contiguous()), ptr(bias), ptr(gamma), ptr(beta), ptr(mean), ptr(var),
+         float(eps), U, F, ptr(tables), ptr(wq_t), ptr(shift), ptr(scale), stream())
+    return ConvPrep(tables, wq_t, shift, scale, U, F)
+
+
+def conv_pool_fwd(pk, prep):
+    """-> pooled (U,B,P) unit-major."""
+    P = pooled_len(pk.L, prep.F)
+    pooled = torch.empty((prep.U, pk.B, P), dtype=torch.float32, device=pk.codes.device)
+    call("explainn_conv_pool_fwd", ptr(pk.codes), ptr(pk.nmask), pk.B, pk.L, prep.U, prep.F, ptr(prep.tables),
+         ptr(prep.wq_t), ptr(prep.shift), ptr(pooled), stream())
+    return pooled
+
+
+def unit_activations(pk, prep, dtype=torch.float16):
+    S = pk.L - prep.F + 1
+    act = torch.empty((pk.B, prep.U, S), dtype=dtype, device=pk.codes.device)
+    dt = _cabi.DTYPE_F16 if dtype == torch.float16 else _cabi.DTYPE_F32
+    call("explainn_unit_activations", ptr(pk.codes), ptr(pk.nmask), pk.B, pk.L, prep.U, prep.F, ptr(prep.tables),
+         ptr(prep.wq_t), ptr(prep.shift), ptr(act), dt, stream())
+    return act
+
+
+def interp_unit_max(pk, prep, zmax=None):
+    """Per-unit maximum pre-activation; pass `zmax` to fold another chunk into it."""
+    dev = pk.codes.device
+    scratch = torch.empty(_cabi.lib.explainn_interp_unit_max_scratch_floats(prep.U), dtype=torch.float32, device=dev)
+    acc = zmax is not None
+    if zmax is None:
+        zmax = torch.empty(prep.U, dtype=torch.float32, device=dev)
+    call("explainn_interp_unit_max", ptr(pk.codes), ptr(pk.nmask), pk.B, pk.L, prep.U, prep.F, ptr(prep.tables),
+         ptr(prep.wq_t), ptr(prep.shift), ptr(scratch), ptr(zmax), int(acc), stream())
+    return zmax
+
+
+def interp_thresholds(zmax):
+    U = zmax.numel()
+    thr, zlo, zhi, amax = (torch.empty(U, dtype=torch.float32, device=zmax.device) for _ in range(4))
+    call("explainn_interp_thresholds", ptr(zmax), U, ptr(thr), ptr(zlo), ptr(zhi), ptr(amax), stream())
+    return thr, zlo, zhi, amax
+
+
+def interp_pwm_count(pk, prep, thr, zlo, zhi, counts=None, hits=None):
+    dev = pk.codes.device
+    if counts is None:
+        counts = torch.zeros((prep.U, 4, prep.F), dtype=torch.int64, device=dev)
+        hits = torch.zeros(prep.U, dtype=torch.int64, device=dev)
+    call("explainn_interp_pwm_count", ptr(pk.codes), ptr(pk.nmask), pk.B, pk.L, prep.U, prep.F, ptr(prep.tables),
+         ptr(prep.wq_t), ptr(prep.shift), ptr(zlo), ptr(zhi), ptr(thr), ptr(counts), ptr(hits), stream())
+    return counts, hits
+
+
+def fc_stack_fwd_eval(pooled, W1, b1, bn2, W2, b2, bn3, eps=1e-5):
+    """pooled (U,B,P) -> unit outputs (B,U).  bn2/bn3 = (weight, bias, running_mean, running_var)."""
+    U, B, P = pooled.shape
+    out = torch.empty((B, U), dtype=torch.float32, device=pooled.device)
+    call("explainn_fc_stack_fwd_eval", ptr(pooled), B, U, P, ptr(W1), ptr(b1), ptr(bn2[0]), ptr(bn2[1]), ptr(bn2[2]),
+         ptr(bn2[3]), ptr(W2), ptr(b2), ptr(bn3[0]), ptr(bn3[1]), ptr(bn3[2]), ptr(bn3[3]), float(eps), ptr(out), stream())
+    return out
+
+
+def linear_fwd(x, W, bias):
+    B, U = x.shape
+    Cc = W.shape[0]
+    out = torch.empty((B, Cc), dtype=torch.float32, device=x.device)
+    call("explainn_linear_fwd", ptr(x), B, U, Cc, ptr(W), ptr(bias), ptr(out), stream())
+    return out

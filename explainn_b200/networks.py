@@ -1,0 +1,204 @@
+"""networks.ExplaiNN -- drop-in for explainn/models/networks.py:44-162 of the reference, running on the
+hand-written sm_100a kernels of libexplainn_b200.so.
+
+The module keeps the reference's attribute layout (`.linears` Sequential with the same module indices,
+`.final`, `._options`), so reference state_dicts load unchanged (same 23 keys, same order, same shapes)
+and callers that poke into the module (`model.linears[0].weight`, `model.final.weight.data.clamp_(0)`,
+`model.linears[:3](x.repeat(1, U, 1))`, `model.linears(x.repeat(1, U, 1))`) keep working.  The contained
+torch.nn modules are parameter containers: their own forward is never used on the fused paths.
+"""
+import torch
+import torch.nn as nn
+
+from . import functional as Fn
+
+HIDDEN = Fn.HIDDEN
+
+
+class ExpActivation(nn.Module):
+    """Exponential activation (networks.py:21-29 of the reference)."""
+
+    def forward(self, x):
+        return torch.exp(x)
+
+
+class Unsqueeze(nn.Module):
+    """Adds a trailing dimension (networks.py:32-37 of the reference)."""
+
+    def forward(self, x):
+        return x.unsqueeze(-1)
+
+
+def _require_cuda(x):
+    if not x.is_cuda:
+        raise RuntimeError("explainn_b200 runs only on CUDA devices (sm_100a kernels; there is no CPU fallback). "
+                           "Got input on %s." % x.device)
+
+
+class _UnitStack(nn.Sequential):
+    """`model.linears`: conv -> BN -> exp -> pool -> per-unit FC stack (networks.py:97-116).
+
+    Calling it (or a `[:3]` / `[:4]` prefix of it) on the U-times tiled input the reference passes
+    (`x.repeat(1, num_cnns, 1)`, interpretation.py:94-95,144-145) or on the plain (B,4,L) input runs
+    the fused kernels.
+    """
+
+    def __init__(self, *mods):
+        super().__init__(*mods)
+        self._owner = None     # set by ExplaiNN (plain attribute: not a submodule, not in state_dict)
+
+    def _bind(self, owner):
+        object.__setattr__(self, "_owner", owner)
+
+    def forward(self, x):
+        return self._owner._unit_outputs(x)
+
+    def __getitem__(self, idx):
+        if isinstance(idx, slice):
+            start, stop, step = idx.indices(len(self))
+            if start == 0 and step == 1 and stop in (3, 4) and self._owner is not None:
+                return _UnitStackPrefix(self._owner, stop)
+            return nn.Sequential(*list(self._modules.values())[idx])
+        return super().__getitem__(idx)
+
+
+class _UnitStackPrefix(nn.Module):
+    """`model.linears[:3]` (conv->BN->exp, (B,U,S)) and `model.linears[:4]` (+maxpool, (B,U,P))."""
+
+    def __init__(self, owner, stop):
+        super().__init__()
+        object.__setattr__(self, "_owner", owner)
+        self._stop = stop
+
+    def forward(self, x):
+        if self._stop == 3:
+            return self._owner._activations(x, torch.float32)
+        return self._owner._pooled(x).permute(1, 0, 2).contiguous()
+
+
+class ExplaiNN(nn.Module):
+    """The ExplaiNN model (reference: explainn/models/networks.py:44-162)."""
+
+    def __init__(self, num_cnns, input_length, num_classes, filter_size=19, num_fc=2, pool_size=7, pool_stride=7,
+                 weight_path=None):
+        """
+        :param num_cnns: int, number of independent cnn units
+        :param input_length: int, input sequence length
+        :param num_classes: int, number of outputs
+        :param filter_size: int, size of the unit's filter, default=19
+        :param num_fc: int, number of FC layers in the unit, default=2
+        :param pool_size: int, size of the unit's maxpooling layer, default=7
+        :param pool_stride: int, stride of the unit's maxpooling layer, default=7
+        :param weight_path: string, path to the file with model weights
+        """
+        super().__init__()
+        self._options = {
+            "num_cnns": num_cnns,
+            "input_length": input_length,
+            "num_classes": num_classes,
+            "filter_size": filter_size,
+            "num_fc": num_fc,
+            "pool_size": pool_size,
+            "pool_stride": pool_stride,
+            "weight_path": weight_path,
+        }
+        if num_fc != 2 or pool_size != Fn.POOL or pool_stride != Fn.POOL:
+            raise NotImplementedError(
+                "explainn_b200 implements the reference default unit (num_fc=2, pool 7/7; networks.py:96-116); "
+                "num_fc=%d pool=%d/%d is not built yet" % (num_fc, pool_size, pool_stride))
+        if filter_size > 24:
+            raise NotImplementedError("explainn_b200: filter_size <= 24 (k-mer tables of the fused conv kernel)")
+        U = num_cnns
+        P = Fn.pooled_len(input_length, filter_size, pool_size, pool_stride)
+        if P < 1:
+            raise ValueError("input_length %d too short for filter_size %d and pool 7" % (input_length, filter_size))
+        self.linears = _UnitStack(
+            nn.Conv1d(in_channels=4 * U, out_channels=U, kernel_size=filter_size, groups=U),   # 0
+            nn.BatchNorm1d(U),                                                                  # 1
+            ExpActivation(),                                                                    # 2
+            nn.MaxPool1d(pool_size, pool_stride),                                               # 3
+            nn.Flatten(),                                                                       # 4
+            Unsqueeze(),                                                                        # 5
+            nn.Conv1d(in_channels=P * U, out_channels=HIDDEN * U, kernel_size=1, groups=U),     # 6
+            nn.BatchNorm1d(HIDDEN * U, 1e-05, 0.1, True),                                       # 7
+            nn.ReLU(),                                                                          # 8
+            nn.Dropout(0.3),                                                                    # 9
+            nn.Conv1d(in_channels=HIDDEN * U, out_channels=U, kernel_size=1, groups=U),         # 10
+            nn.BatchNorm1d(U, 1e-05, 0.1, True),                                                # 11
+            nn.ReLU(),                                                                          # 12
+            nn.Flatten())                                                                       # 13
+        self.linears._bind(self)
+        self.final = nn.Linear(U, num_classes)
+        self._invalid = None      # lazily read counter of non-one-hot input columns
+        if weight_path:
+            self.load_state_dict(torch.load(weight_path))
+
+    # ------------------------------------------------------------------ helpers
+    @property
+    def pooled_length(self):
+        o = self._options
+        return Fn.pooled_len(o["input_length"], o["filter_size"], o["pool_size"], o["pool_stride"])
+
+    def _pack(self, x):
+        _require_cuda(x)
+        o = self._options
+        if x.dim() != 3 or x.shape[2] != o["input_length"]:
+            raise ValueError("expected input of shape (B, 4, %d), got %s" % (o["input_length"], tuple(x.shape)))
+        if self._invalid is None or self._invalid.device != x.device:
+            self._invalid = torch.zeros(1, dtype=torch.int32, device=x.device)
+        return Fn.pack_onehot(x, o["num_cnns"], self._invalid)
+
+    def check_inputs(self):
+        """Raise ValueError if any batch seen so far contained a column that is neither one-hot nor
+        all-zero (synchronises the device; the drivers call it once per loop, not per batch)."""
+        if self._invalid is not None:
+            Fn.check_invalid(self._invalid)
+
+    def _conv_prep_eval(self):
+        conv, bn = self.linears[0], self.linears[1]
+        return Fn.conv_prepare(conv.weight.detach(), conv.bias.detach(), bn.weight.detach(), bn.bias.detach(),
+                               bn.running_mean, bn.running_var, bn.eps)
+
+    def _bn_uses_batch_stats(self):
+        return self.linears[1].training
+
+    # ------------------------------------------------------------------ fused pieces (eval statistics)
+    def _activations(self, x, dtype=torch.float16):
+        """exp(BN(conv(x))) as (B,U,S) -- interpretation.py:143-145."""
+        if self._bn_uses_batch_stats():
+            raise RuntimeError("the activation scan uses BatchNorm running statistics; call model.eval() first "
+                               "(scripts/interpret.py:199 of the reference does)")
+        pk = self._pack(x)
+        return Fn.unit_activations(pk, self._conv_prep_eval(), dtype)
+
+    def _pooled(self, x):
+        """max-pooled activations, unit-major (U,B,P)."""
+        if self._bn_uses_batch_stats():
+            raise RuntimeError("model.linears[:4] on the fused path needs eval() mode")
+        pk = self._pack(x)
+        return Fn.conv_pool_fwd(pk, self._conv_prep_eval())
+
+    def _unit_outputs_eval(self, x):
+        L = self.linears
+        pooled = self._pooled(x)
+        bn2, bn3 = L[7], L[11]
+        return Fn.fc_stack_fwd_eval(
+            pooled, L[6].weight.detach(), L[6].bias.detach(),
+            (bn2.weight.detach(), bn2.bias.detach(), bn2.running_mean, bn2.running_var),
+            L[10].weight.detach(), L[10].bias.detach(),
+            (bn3.weight.detach(), bn3.bias.detach(), bn3.running_mean, bn3.running_var), bn2.eps)
+
+    def _unit_outputs(self, x):
+        if self.training:
+            from . import autograd_fn
+            return autograd_fn.unit_outputs_train(self, x)
+        return self._unit_outputs_eval(x)
+
+    # ------------------------------------------------------------------ forward
+    def forward(self, x):
+        """x: (B,4,L) one-hot float tensor on the GPU -> (B,C) logits (networks.py:152-162)."""
+        if self.training:
+            from . import autograd_fn
+            return autograd_fn.forward_train(self, x)
+        unit = self._unit_outputs_eval(x)
+        return Fn.linear_fwd(unit, self.final.weight.detach(), self.final.bias.detach())

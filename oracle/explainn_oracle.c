@@ -72,7 +72,7 @@ ORC_API int orc_words_codes(int L) { return (L + 15) / 16; }
 ORC_API int orc_words_mask(int L) { return (L + 31) / 32; }
 
 /* x: (B,4,L) fp32 with batch stride bstride (elements).  Returns number of invalid columns
- * (neither exactly one 1.0 with three 0.0, nor all 0.0). */
+ * (neither exactly one 1.0 with three 0.0, nor all 0.0).  Bits at positions >= L stay zero. */
 ORC_API long orc_pack_onehot(const float *x, long B, int L, long bstride,
                              uint32_t *codes, uint32_t *nmask)
 {
@@ -96,8 +96,6 @@ ORC_API long orc_pack_onehot(const float *x, long B, int L, long bstride,
                 if (!(ones == 0 && zeros == 4)) bad++;
             }
         }
-        /* positions >= L inside the last mask word are flagged N */
-        for (int i = L; i < wm * 32; ++i) nmask[b * wm + i / 32] |= 1u << (i % 32);
     }
     return bad;
 }
