@@ -21,7 +21,7 @@ lib = C.CDLL(LIB_PATH)
 DTYPE_F32, DTYPE_F16 = 0, 1
 LOSS_BCE, LOSS_MSE = 0, 1
 
-_P, _LL, _I, _F = C.c_void_p, C.c_longlong, C.c_int, C.c_float
+_P, _LL, _I, _F, _ULL = C.c_void_p, C.c_longlong, C.c_int, C.c_float, C.c_ulonglong
 
 # name -> argtypes (restype int unless listed in _RESTYPES)
 SIGNATURES = {
@@ -41,6 +41,16 @@ SIGNATURES = {
     "explainn_interp_pwm_count": [_P, _P, _LL, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P],
     "explainn_fc_stack_fwd_eval": [_P, _LL, _I, _I] + [_P] * 12 + [_F, _P, _P],
     "explainn_linear_fwd": [_P, _LL, _I, _I, _P, _P, _P, _P],
+    "explainn_input_cooc_stats": [_P, _P, _LL, _I, _I, _P, _P],
+    "explainn_bn1_batch_stats": [_P, _P, _P, _I, _I, _LL, _F, _P, _P, _P, _P, _P, _P, _P],
+    "explainn_fc_nchunk": [_LL],
+    "explainn_fc_stack_fwd_train": [_P, _LL, _I, _I, _I] + [_P] * 12 + [_F, _F, _F, _ULL] + [_P] * 12 + [_P],
+    "explainn_fc_stack_bwd": [_P, _LL, _I, _I, _I] + [_P] * 14 + [_F, _ULL] + [_P] * 14 + [_P],
+    "explainn_conv_bwd_nsplit": [_I],
+    "explainn_conv_pool_bwd": [_P, _P, _LL, _I, _I, _I] + [_P] * 10 + [_F, _P, _I] + [_P] * 4 + [_P],
+    "explainn_loss_fwd_bwd": [_P, _P, _LL, _I, _I, _F, _P, _P, _P],
+    "explainn_adam_step": [_P, _P, _P, _P, _LL, _P, _F, _F, _F, _F, _F, _P],
+    "explainn_reduce_partials": [_P, _P, _LL, _I, _P],
 }
 _RESTYPES = {
     "explainn_last_error": C.c_char_p,
@@ -90,7 +100,8 @@ def stream():
 
 
 LAUNCHES = 0   # kernels launched through this binding (bench.py reports it)
-_LAUNCH_COST = {"explainn_interp_unit_max": 3}
+_LAUNCH_COST = {"explainn_interp_unit_max": 3, "explainn_input_cooc_stats": 1, "explainn_fc_stack_fwd_train": 3,
+                "explainn_fc_stack_bwd": 5, "explainn_conv_pool_bwd": 2, "explainn_adam_step": 2}
 
 
 def call(name, *args):

@@ -1,0 +1,175 @@
+"""Training-mode forward/backward of ExplaiNN on the fused kernels, exposed to autograd.
+
+Reference semantics (explainn/models/networks.py:96-116,147,152-162 under `model.train()`;
+explainn/train/train.py:61-65): BatchNorm uses batch statistics (biased variance) and updates its
+running statistics with momentum 0.1 and the unbiased variance; dropout p=0.3 is active unless the
+Dropout module itself is in eval mode.  Parameters stay ordinary nn.Parameters: any criterion and any
+optimizer work on top of this function, gradient hooks on `model.linears[0].weight` fire as usual
+(explainn/utils/tools.py:248-264), `requires_grad=False` is honoured (scripts/finetune.py:216-221).
+"""
+import torch
+
+from . import functional as Fn
+from ._cabi import call, ptr, stream
+
+H = Fn.HIDDEN
+
+_SEED_STATE = {"counter": 0}
+
+
+def _next_dropout_seed():
+    """A fresh 64-bit seed per forward, derived from torch's CPU generator state so that
+    torch.manual_seed makes runs repeatable."""
+    _SEED_STATE["counter"] += 1
+    base = torch.initial_seed() & 0xFFFFFFFFFFFF
+    return (base * 0x9E3779B1 + _SEED_STATE["counter"] * 0x85EBCA77C2B2AE63) & 0xFFFFFFFFFFFFFFFF
+
+
+def _params(model):
+    L = model.linears
+    return (L[0].weight, L[0].bias, L[1].weight, L[1].bias, L[6].weight, L[6].bias, L[7].weight, L[7].bias,
+            L[10].weight, L[10].bias, L[11].weight, L[11].bias, model.final.weight, model.final.bias)
+
+
+def _check_modes(model):
+    L = model.linears
+    if not (L[1].training and L[7].training and L[11].training):
+        raise NotImplementedError("explainn_b200: in train() mode all three BatchNorm layers must be in training mode")
+    for bn in (L[1], L[7], L[11]):
+        if bn.momentum is None or not bn.track_running_stats or not bn.affine:
+            raise NotImplementedError("explainn_b200: BatchNorm layers must keep the reference configuration "
+                                      "(momentum=0.1, affine, track_running_stats)")
+
+
+class TrainWorkspace:
+    """Everything the backward needs, produced by one training forward."""
+    __slots__ = ("pk", "B", "U", "P", "C", "F", "M", "mean1", "var1", "Mw", "pooled", "xhat", "idx", "h1", "mean2",
+                 "invstd2", "h2", "mean3", "invstd3", "unit", "logits", "pdrop", "seed", "nchunk")
+
+
+def train_forward(model, x, params=None, seed=None):
+    """Runs the training-mode forward kernels.  Returns a TrainWorkspace (logits in ws.logits)."""
+    _check_modes(model)
+    L = model.linears
+    if params is None:
+        params = [p.detach() for p in _params(model)]
+    (cw, cb, g1, b1n, W1, b1, g2, be2, W2, b2, g3, be3, Wf, bf) = params
+    o = model._options
+    U, F, C = o["num_cnns"], o["filter_size"], o["num_classes"]
+    pk = model._pack(x)
+    B = pk.B
+    if B < 2:
+        # same failure BatchNorm raises in train mode (worked around at scripts/utils/__init__.py:121-132)
+        raise ValueError("Expected more than 1 value per channel when training, got input size %s" % (tuple(x.shape),))
+    dev = pk.codes.device
+    bn1, bn2, bn3, drop = L[1], L[7], L[11], L[9]
+    ws = TrainWorkspace()
+    ws.pk, ws.B, ws.U, ws.C, ws.F = pk, B, U, C, F
+    S = pk.L - F + 1
+    P = ws.P = model.pooled_length
+    ws.M = Fn.input_cooc_stats(pk, F)
+    ws.mean1, ws.var1, ws.Mw = Fn.bn1_batch_stats(ws.M, cw, cb, B * S, bn1.momentum, bn1.running_mean, bn1.running_var,
+                                                  bn1.num_batches_tracked)
+    ones, zeros = _const(dev, U)
+    prep = Fn.conv_prepare(cw, cb, ones, zeros, ws.mean1, ws.var1, bn1.eps)   # tables of x_hat = (y - mu) / sigma
+    ws.pooled, ws.xhat, ws.idx = Fn.conv_pool_fwd_train(pk, prep, g1, b1n)
+    nchunk = ws.nchunk = Fn.fc_nchunk(B)
+    f32 = dict(dtype=torch.float32, device=dev)
+    ws.h1 = torch.empty((U, B, H), **f32)
+    part2 = torch.empty((U, nchunk, 2, H), **f32)
+    ws.mean2 = torch.empty(U * H, **f32)
+    ws.invstd2 = torch.empty(U * H, **f32)
+    ws.h2 = torch.empty((U, B), **f32)
+    part3 = torch.empty((U, nchunk, 2), **f32)
+    ws.mean3 = torch.empty(U, **f32)
+    ws.invstd3 = torch.empty(U, **f32)
+    ws.unit = torch.empty((B, U), **f32)
+    ws.logits = torch.empty((B, C), **f32)
+    ws.pdrop = float(drop.p) if drop.training else 0.0
+    ws.seed = _next_dropout_seed() if seed is None else seed
+    call("explainn_fc_stack_fwd_train", ptr(ws.pooled), B, U, P, C, ptr(W1), ptr(b1), ptr(g2), ptr(be2),
+         ptr(bn2.running_mean), ptr(bn2.running_var), ptr(W2), ptr(b2), ptr(g3), ptr(be3), ptr(bn3.running_mean),
+         ptr(bn3.running_var), float(bn2.momentum), float(bn2.eps), ws.pdrop, ws.seed, ptr(Wf), ptr(bf), ptr(ws.h1),
+         ptr(part2), ptr(ws.mean2), ptr(ws.invstd2), ptr(ws.h2), ptr(part3), ptr(ws.mean3), ptr(ws.invstd3), ptr(ws.unit),
+         ptr(ws.logits), stream())
+    bn2.num_batches_tracked.add_(1)
+    bn3.num_batches_tracked.add_(1)
+    return ws
+
+
+_CONST = {}
+
+
+def _const(dev, U):
+    key = (str(dev), U)
+    if key not in _CONST:
+        _CONST[key] = (torch.ones(U, dtype=torch.float32, device=dev), torch.zeros(U, dtype=torch.float32, device=dev))
+    return _CONST[key]
+
+
+def train_backward(model, ws, gout, params=None, grads=None, wrt_unit=False):
+    """Backward kernels.  gout: (B,C) gradient w.r.t. the logits, or (B,U) w.r.t. the unit outputs when
+    `wrt_unit`.  `grads`: optional list of 14 preallocated gradient tensors (e.g. views into a flat buffer)."""
+    L = model.linears
+    if params is None:
+        params = [p.detach() for p in _params(model)]
+    (cw, cb, g1, b1n, W1, b1, g2, be2, W2, b2, g3, be3, Wf, bf) = params
+    B, U, P, C, F = ws.B, ws.U, ws.P, ws.C, ws.F
+    dev = gout.device
+    f32 = dict(dtype=torch.float32, device=dev)
+    if grads is None:
+        grads = [torch.empty_like(p) for p in params]
+    (dcw, dcb, dg1, db1n, dW1, db1, dg2, dbe2, dW2, db2, dg3, dbe3, dWf, dbf) = grads
+    gout = gout.contiguous()
+    gh2 = torch.empty((U, B), **f32)
+    pb2 = torch.empty((U, ws.nchunk, 3, H), **f32)
+    dW1p = torch.empty((ws.nchunk, U, H, P), **f32)
+    gpool = torch.empty((U, B, P), **f32)
+    call("explainn_fc_stack_bwd", ptr(gout), B, U, P, C, ptr(ws.pooled), ptr(ws.h1), ptr(ws.h2), ptr(ws.unit), ptr(W1),
+         ptr(g2), ptr(be2), ptr(ws.mean2), ptr(ws.invstd2), ptr(W2), ptr(g3), ptr(ws.mean3), ptr(ws.invstd3),
+         None if wrt_unit else ptr(Wf), ws.pdrop, ws.seed, ptr(gh2), ptr(pb2), ptr(dW1p), ptr(gpool), ptr(dW1), ptr(db1),
+         ptr(dg2), ptr(dbe2), ptr(dW2), ptr(db2), ptr(dg3), ptr(dbe3), None if wrt_unit else ptr(dWf),
+         None if wrt_unit else ptr(dbf), stream())
+    nsplit = Fn._cabi.lib.explainn_conv_bwd_nsplit(U)
+    partial = torch.empty((nsplit, U, 4 * F + 2), **f32)
+    call("explainn_conv_pool_bwd", ptr(ws.pk.codes), ptr(ws.pk.nmask), B, ws.pk.L, U, F, ptr(gpool), ptr(ws.pooled),
+         ptr(ws.xhat), ptr(ws.idx), ptr(ws.M), ptr(ws.Mw), ptr(cb), ptr(ws.mean1), ptr(ws.var1), ptr(g1),
+         float(L[1].eps), ptr(partial), nsplit, ptr(dcw), ptr(dcb), ptr(dg1), ptr(db1n), stream())
+    if wrt_unit:
+        dWf.zero_()
+        dbf.zero_()
+    return grads
+
+
+class _ExplaiNNTrainFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, model, x, wrt_unit, *params):
+        ps = [p.detach().contiguous() for p in params]
+        ws = train_forward(model, x, ps)
+        ctx.model, ctx.ws, ctx.ps, ctx.wrt_unit = model, ws, ps, wrt_unit
+        out = ws.unit if wrt_unit else ws.logits
+        return out
+
+    @staticmethod
+    def backward(ctx, gout):
+        grads = train_backward(ctx.model, ctx.ws, gout, ctx.ps, wrt_unit=ctx.wrt_unit)
+        need = ctx.needs_input_grad[3:]
+        out = [g if n else None for g, n in zip(grads, need)]
+        if ctx.wrt_unit:
+            out[12] = out[13] = None
+        ctx.ws = None
+        return (None, None, None) + tuple(out)
+
+
+def forward_train(model, x):
+    """model(x) in train() mode."""
+    if torch.is_grad_enabled() and any(p.requires_grad for p in _params(model)):
+        return _ExplaiNNTrainFn.apply(model, x, False, *_params(model))
+    return train_forward(model, x).logits
+
+
+def unit_outputs_train(model, x):
+    """model.linears(x) in train() mode."""
+    if torch.is_grad_enabled() and any(p.requires_grad for p in _params(model)):
+        return _ExplaiNNTrainFn.apply(model, x, True, *_params(model))
+    return train_forward(model, x).unit

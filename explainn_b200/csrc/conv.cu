@@ -21,6 +21,7 @@
 // per-tap path that evaluates exactly the same expression.
 #include "common.cuh"
 #include "../../include/explainn_b200.h"
+#include <string.h>
 
 namespace {
 
@@ -53,9 +54,10 @@ __device__ __forceinline__ float lds_f32(const unsigned char *smem, uint32_t off
 // ----------------------------------------------------------------------------------------------
 
 // (1) inference pooling: pooled[u][b][p] = exp(max_window z)   (unit-major, see fc.cu)
-struct PoolSink {
+template <int PCH_>
+struct PoolSinkT {
     struct Params { float *pooled; int P; };
-    static constexpr int PCH = 36;
+    static constexpr int PCH = PCH_;
     static __host__ __device__ int smem_bytes(int P) { int ps = (P < PCH ? P : PCH) | 1; return NW * XB_UT * ps * 4; }
     Params p;
     float *stage;
@@ -101,9 +103,10 @@ struct PoolSink {
 
 // (2) training pooling: tables hold x_hat = (y - mu) / sigma; z = gamma * x_hat + beta.
 //     Emits pooled = exp(z*) , x_hat* and the first-max index inside the window.
-struct PoolTrainSink {
+template <int PCH_>
+struct PoolTrainSinkT {
     struct Params { float *pooled; float *xhat; unsigned char *idx; const float *gamma; const float *beta; int P; };
-    static constexpr int PCH = 12;
+    static constexpr int PCH = PCH_;
     static __host__ __device__ int smem_bytes(int) { return NW * XB_UT * (PCH + 1) * 12; }
     Params p;
     float *st_a, *st_x;
@@ -174,10 +177,10 @@ struct PoolTrainSink {
 };
 
 // (3) activation map: act[b,u,s] = exp(z) for every s < S, float16 or float32
-template <typename OutT>
+template <typename OutT, int PCH_>
 struct ActSink {
     struct Params { OutT *act; };
-    static constexpr int PCH = 12;                       // windows per flush = 84 positions
+    static constexpr int PCH = PCH_;                     // windows per flush
     static constexpr int ROW = PCH * XB_POOL + 1;
     static __host__ __device__ int smem_bytes(int) { return NW * XB_UT * ROW * (int)sizeof(OutT); }
     Params p;
@@ -561,16 +564,24 @@ int launch_scan(const ConvArgs &a, const typename Sink::Params &sp, int sink_sme
     return xb_check_launch("conv_scan_kernel");
 }
 
-template <class Sink>
-int dispatch_scan(int G, const ConvArgs &a, const typename Sink::Params &sp, int sink_smem, cudaStream_t stream)
+// Sink: staging sized for G <= 5 (160 KB of tables); Small: the same sink with a short staging buffer
+// for G = 6 (192 KB of tables leave ~21 KB).
+template <class Sink, class Small>
+int dispatch_scan(int G, const ConvArgs &a, const typename Sink::Params &sp, int arg, cudaStream_t stream)
 {
+    static_assert(sizeof(typename Sink::Params) == sizeof(typename Small::Params), "sink params differ");
+    const int sink_smem = Sink::smem_bytes(arg);
     switch (G) {
     case 1: return launch_scan<1, Sink>(a, sp, sink_smem, stream);
     case 2: return launch_scan<2, Sink>(a, sp, sink_smem, stream);
     case 3: return launch_scan<3, Sink>(a, sp, sink_smem, stream);
     case 4: return launch_scan<4, Sink>(a, sp, sink_smem, stream);
     case 5: return launch_scan<5, Sink>(a, sp, sink_smem, stream);
-    case 6: return launch_scan<6, Sink>(a, sp, sink_smem, stream);
+    case 6: {
+        typename Small::Params sq;
+        memcpy(&sq, &sp, sizeof(sq));
+        return launch_scan<6, Small>(a, sq, Small::smem_bytes(arg), stream);
+    }
     }
     xb_set_error("conv scan: filter_size %d not supported (max %d)", a.F, 4 * XB_MAX_G);
     return XB_ERR_UNSUPPORTED;
@@ -610,8 +621,8 @@ extern "C" int explainn_conv_pool_fwd(const uint32_t *codes, const uint32_t *nma
     XB_REQUIRE(pooled, "conv_pool_fwd: null output");
     if (B == 0 || g.P == 0) return XB_OK;
     a.nwin = g.nwin_pool;
-    PoolSink::Params sp{pooled, g.P};
-    return dispatch_scan<PoolSink>(g.G, a, sp, PoolSink::smem_bytes(g.P), stream);
+    PoolSinkT<36>::Params sp{pooled, g.P};
+    return dispatch_scan<PoolSinkT<36>, PoolSinkT<12>>(g.G, a, sp, g.P, stream);
 }
 
 extern "C" int explainn_conv_pool_fwd_train(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F,
@@ -625,8 +636,8 @@ extern "C" int explainn_conv_pool_fwd_train(const uint32_t *codes, const uint32_
     XB_REQUIRE(pooled && xhat && idx && gamma && beta, "conv_pool_fwd_train: null pointer");
     if (B == 0 || g.P == 0) return XB_OK;
     a.nwin = g.nwin_pool;
-    PoolTrainSink::Params sp{pooled, xhat, idx, gamma, beta, g.P};
-    return dispatch_scan<PoolTrainSink>(g.G, a, sp, PoolTrainSink::smem_bytes(g.P), stream);
+    PoolTrainSinkT<12>::Params sp{pooled, xhat, idx, gamma, beta, g.P};
+    return dispatch_scan<PoolTrainSinkT<12>, PoolTrainSinkT<3>>(g.G, a, sp, g.P, stream);
 }
 
 extern "C" int explainn_unit_activations(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F,
@@ -640,11 +651,11 @@ extern "C" int explainn_unit_activations(const uint32_t *codes, const uint32_t *
     if (B == 0) return XB_OK;
     a.nwin = g.nwin_all;
     if (act_dtype == EXPLAINN_DTYPE_F16) {
-        ActSink<__half>::Params sp{(__half *)act};
-        return dispatch_scan<ActSink<__half>>(g.G, a, sp, ActSink<__half>::smem_bytes(0), stream);
+        ActSink<__half, 6>::Params sp{(__half *)act};
+        return dispatch_scan<ActSink<__half, 6>, ActSink<__half, 3>>(g.G, a, sp, 0, stream);
     } else if (act_dtype == EXPLAINN_DTYPE_F32) {
-        ActSink<float>::Params sp{(float *)act};
-        return dispatch_scan<ActSink<float>>(g.G, a, sp, ActSink<float>::smem_bytes(0), stream);
+        ActSink<float, 6>::Params sp{(float *)act};
+        return dispatch_scan<ActSink<float, 6>, ActSink<float, 1>>(g.G, a, sp, 0, stream);
     }
     xb_set_error("unit_activations: unsupported dtype %d", act_dtype);
     return XB_ERR_UNSUPPORTED;
@@ -680,7 +691,7 @@ extern "C" int explainn_interp_unit_max(const uint32_t *codes, const uint32_t *n
     a.nwin = g.nwin_all;
     if (B > 0) {
         MaxSink::Params sp{scratch, n_cta};
-        rc = dispatch_scan<MaxSink>(g.G, a, sp, MaxSink::smem_bytes(0), stream);
+        rc = dispatch_scan<MaxSink, MaxSink>(g.G, a, sp, 0, stream);
         if (rc != XB_OK) return rc;
     }
     reduce_zmax_kernel<<<(U + 127) / 128, 128, 0, stream>>>(scratch, n_cta, U, zmax, accumulate);
@@ -699,5 +710,5 @@ extern "C" int explainn_interp_pwm_count(const uint32_t *codes, const uint32_t *
     if (B == 0) return XB_OK;
     a.nwin = g.nwin_all;
     CountSink::Params sp{zlo, zhi, thr, counts, hits};
-    return dispatch_scan<CountSink>(g.G, a, sp, CountSink::smem_bytes(F), stream);
+    return dispatch_scan<CountSink, CountSink>(g.G, a, sp, F, stream);
 }

@@ -171,6 +171,485 @@ __global__ void __launch_bounds__(256) linear_fwd_kernel(const float *__restrict
     }
 }
 
+
+// ================================================================================================
+// Training-mode forward (BatchNorm batch statistics, dropout)
+// ================================================================================================
+constexpr int HS = H + 1;   // row stride of the hidden tile in shared memory (odd: conflict-free columns)
+
+// counter-based dropout mask: splitmix64 of (seed, element index); keep iff the top 32 bits >= p * 2^32
+__device__ __forceinline__ float drop_scale(unsigned long long seed, unsigned long long elem, unsigned thresh, float keep_scale)
+{
+    unsigned long long z = seed + elem * 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    z ^= z >> 31;
+    return (unsigned)(z >> 32) >= thresh ? keep_scale : 0.0f;
+}
+
+// h1[u][b][:] = W1[u] . pooled[u][b][:] + b1[u]  and per-tile column sums for BatchNorm-2
+__global__ void __launch_bounds__(FC_THREADS) fc1_train_kernel(const float *__restrict__ pooled, long long B, int U, int P,
+                                                               const float *__restrict__ W1, const float *__restrict__ b1,
+                                                               float *__restrict__ h1, float *__restrict__ part2)
+{
+    extern __shared__ __align__(16) unsigned char smem[];
+    FcSmem s(smem, P);
+    float *Hs = s.As + BM * s.Pp;
+    __shared__ float b1s[H];
+    const int u = blockIdx.x, chunk = blockIdx.y, nchunk = gridDim.y;
+    const long long b0 = (long long)chunk * BM;
+    const int rows = (int)min((long long)BM, B - b0);
+    load_w1(s, W1 + (size_t)u * H * P, P);
+    load_a(s, pooled + ((size_t)u * B + b0) * P, rows, P);
+    if (threadIdx.x < H) b1s[threadIdx.x] = b1[u * H + threadIdx.x];
+    __syncthreads();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int q = warp & 3, row0 = (warp >> 2) * 32 + lane;
+    float acc[2][JP];
+    fc1_tile(s, P, q, row0, acc);
+#pragma unroll
+    for (int j = 0; j < JW; ++j) {
+        Hs[row0 * HS + q * JW + j] = acc[0][j] + b1s[q * JW + j];
+        Hs[(row0 + 64) * HS + q * JW + j] = acc[1][j] + b1s[q * JW + j];
+    }
+    __syncthreads();
+    float *dst = h1 + ((size_t)u * B + b0) * H;
+    for (int i = threadIdx.x; i < rows * H; i += blockDim.x) {
+        const int r = i / H, j = i - r * H;
+        dst[i] = Hs[r * HS + j];
+    }
+    if (threadIdx.x < H) {
+        float sm = 0.f, sq = 0.f;
+        for (int r = 0; r < rows; ++r) {
+            const float v = Hs[r * HS + threadIdx.x];
+            sm += v;
+            sq = fmaf(v, v, sq);
+        }
+        float *pp = part2 + ((size_t)u * nchunk + chunk) * 2 * H;
+        pp[threadIdx.x] = sm;
+        pp[H + threadIdx.x] = sq;
+    }
+}
+
+// BatchNorm-2 (batch stats) -> ReLU -> dropout -> FC2 (+b2) ; per-tile sums for BatchNorm-3
+__global__ void __launch_bounds__(FC_THREADS) fc2_train_kernel(
+    const float *__restrict__ h1, long long B, int U, const float *__restrict__ part2, int nchunk,
+    const float *__restrict__ g2, const float *__restrict__ be2, float *__restrict__ rm2, float *__restrict__ rv2,
+    float momentum, float eps, const float *__restrict__ W2, const float *__restrict__ b2, float *__restrict__ mean2,
+    float *__restrict__ invstd2, float pdrop, unsigned long long seed, float *__restrict__ h2, float *__restrict__ part3)
+{
+    __shared__ float sc[128], sh[128], w2s[128];
+    __shared__ float red[8][2];
+    const int u = blockIdx.x, chunk = blockIdx.y;
+    const long long b0 = (long long)chunk * BM;
+    const int rows = (int)min((long long)BM, B - b0);
+    if (threadIdx.x < 128) {
+        const int j = threadIdx.x;
+        float a = 0.f, c = 0.f, w = 0.f;
+        if (j < H) {
+            double sm = 0.0, sq = 0.0;
+            for (int k = 0; k < nchunk; ++k) {
+                const float *pp = part2 + ((size_t)u * nchunk + k) * 2 * H;
+                sm += (double)pp[j];
+                sq += (double)pp[H + j];
+            }
+            const double mean = sm / (double)B;
+            double var = sq / (double)B - mean * mean;
+            if (var < 0.0) var = 0.0;
+            const float inv = (float)(1.0 / sqrt(var + (double)eps));
+            const int ch = u * H + j;
+            if (chunk == 0) {
+                mean2[ch] = (float)mean;
+                invstd2[ch] = inv;
+                if (rm2) {
+                    const double unb = B > 1 ? var * (double)B / (double)(B - 1) : var;
+                    rm2[ch] = (1.0f - momentum) * rm2[ch] + momentum * (float)mean;
+                    rv2[ch] = (1.0f - momentum) * rv2[ch] + momentum * (float)unb;
+                }
+            }
+            a = g2[ch] * inv;
+            c = be2[ch] - (float)mean * a;
+            w = W2[ch];
+        }
+        sc[j] = a; sh[j] = c; w2s[j] = w;
+    }
+    __syncthreads();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const unsigned thresh = pdrop > 0.f ? (unsigned)min(4294967295.0, (double)pdrop * 4294967296.0) : 0u;
+    const float keep_scale = pdrop > 0.f ? 1.0f / (1.0f - pdrop) : 1.0f;
+    float s3 = 0.f, q3 = 0.f;
+    for (int r = warp; r < rows; r += 8) {
+        const size_t rowi = (size_t)u * B + b0 + r;
+        const float *hr = h1 + rowi * H;
+        float dot = 0.f;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int j = lane + 32 * i;
+            if (j < H) {
+                float v = fmaxf(fmaf(hr[j], sc[j], sh[j]), 0.f);
+                if (pdrop > 0.f) v *= drop_scale(seed, rowi * H + j, thresh, keep_scale);
+                dot = fmaf(v, w2s[j], dot);
+            }
+        }
+        dot = warp_sum(dot);
+        const float o = dot + b2[u];
+        if (lane == 0) {
+            h2[rowi] = o;
+            s3 += o;
+            q3 = fmaf(o, o, q3);
+        }
+    }
+    if (lane == 0) { red[warp][0] = s3; red[warp][1] = q3; }
+    __syncthreads();
+    if (threadIdx.x < 2) {
+        float v = 0.f;
+        for (int w = 0; w < 8; ++w) v += red[w][threadIdx.x];
+        part3[((size_t)u * nchunk + chunk) * 2 + threadIdx.x] = v;
+    }
+}
+
+// BatchNorm-3 (batch stats) -> ReLU -> unit outputs (B,U) -> final Linear -> logits (B,C)
+__global__ void __launch_bounds__(256) out_train_kernel(const float *__restrict__ h2, long long B, int U, int C,
+                                                        const float *__restrict__ part3, int nchunk,
+                                                        const float *__restrict__ g3, const float *__restrict__ be3,
+                                                        float *__restrict__ rm3, float *__restrict__ rv3, float momentum,
+                                                        float eps, float *__restrict__ mean3, float *__restrict__ invstd3,
+                                                        const float *__restrict__ Wf, const float *__restrict__ bf,
+                                                        float *__restrict__ unit, float *__restrict__ logits)
+{
+    extern __shared__ float xs[];   // [32][U+1] then sc3[U], sh3[U]
+    const int Up = U + 1;
+    float *sc3 = xs + 32 * Up, *sh3 = sc3 + U;
+    const long long b0 = (long long)blockIdx.x * 32;
+    const int rows = (int)min(32LL, B - b0);
+    for (int u = threadIdx.x; u < U; u += blockDim.x) {
+        double sm = 0.0, sq = 0.0;
+        for (int k = 0; k < nchunk; ++k) {
+            sm += (double)part3[((size_t)u * nchunk + k) * 2];
+            sq += (double)part3[((size_t)u * nchunk + k) * 2 + 1];
+        }
+        const double mean = sm / (double)B;
+        double var = sq / (double)B - mean * mean;
+        if (var < 0.0) var = 0.0;
+        const float inv = (float)(1.0 / sqrt(var + (double)eps));
+        if (blockIdx.x == 0) {
+            mean3[u] = (float)mean;
+            invstd3[u] = inv;
+            if (rm3) {
+                const double unb = B > 1 ? var * (double)B / (double)(B - 1) : var;
+                rm3[u] = (1.0f - momentum) * rm3[u] + momentum * (float)mean;
+                rv3[u] = (1.0f - momentum) * rv3[u] + momentum * (float)unb;
+            }
+        }
+        const float a = g3[u] * inv;
+        sc3[u] = a;
+        sh3[u] = be3[u] - (float)mean * a;
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < 32 * U; i += blockDim.x) {
+        const int u = i >> 5, r = i & 31;
+        float v = 0.f;
+        if (r < rows) {
+            v = fmaxf(fmaf(h2[(size_t)u * B + b0 + r], sc3[u], sh3[u]), 0.f);
+            unit[(b0 + r) * U + u] = v;
+        }
+        xs[r * Up + u] = v;
+    }
+    __syncthreads();
+    const int r = threadIdx.x & 31;
+    for (int c = threadIdx.x >> 5; c < C; c += 8) {
+        const float *w = Wf + (size_t)c * U;
+        float a0 = 0.f, a1 = 0.f;
+        int k = 0;
+        for (; k + 1 < U; k += 2) {
+            a0 = fmaf(xs[r * Up + k], __ldg(w + k), a0);
+            a1 = fmaf(xs[r * Up + k + 1], __ldg(w + k + 1), a1);
+        }
+        if (k < U) a0 = fmaf(xs[r * Up + k], __ldg(w + k), a0);
+        if (r < rows) logits[(b0 + r) * C + c] = (a0 + a1) + bf[c];
+    }
+}
+
+// ================================================================================================
+// Backward
+// ================================================================================================
+
+// dWf[c][u] = sum_b gl[b][c] * unit[b][u] ; dbf[c] = sum_b gl[b][c].   grid (ceil(U/32), ceil(C/8))
+__global__ void __launch_bounds__(256) bwd_final_linear_kernel(const float *__restrict__ gl, const float *__restrict__ unit,
+                                                               long long B, int U, int C, float *__restrict__ dWf,
+                                                               float *__restrict__ dbf)
+{
+    const int lane = threadIdx.x & 31, cc = threadIdx.x >> 5;
+    const int u = blockIdx.x * 32 + lane, c = blockIdx.y * 8 + cc;
+    if (c >= C) return;
+    const bool uv = u < U;
+    float a0 = 0.f, a1 = 0.f, sg = 0.f;
+    long long b = 0;
+    for (; b + 1 < B; b += 2) {
+        const float g0 = __ldg(gl + b * C + c), g1 = __ldg(gl + (b + 1) * C + c);
+        sg += g0 + g1;
+        if (uv) {
+            a0 = fmaf(g0, unit[b * U + u], a0);
+            a1 = fmaf(g1, unit[(b + 1) * U + u], a1);
+        }
+    }
+    if (b < B) {
+        const float g0 = __ldg(gl + b * C + c);
+        sg += g0;
+        if (uv) a0 = fmaf(g0, unit[b * U + u], a0);
+    }
+    if (uv && dWf) dWf[(size_t)c * U + u] = a0 + a1;
+    if (dbf && blockIdx.x == 0 && lane == 0) dbf[c] = sg;
+}
+
+// gunit = gl . Wf -> ReLU-3 mask -> BatchNorm-3 backward -> gh2 (U,B), dgamma3, dbeta3.  8 units per block.
+__global__ void __launch_bounds__(256) bwd_bn3_kernel(const float *__restrict__ gl, const float *__restrict__ Wf,
+                                                      const float *__restrict__ unit, const float *__restrict__ h2,
+                                                      long long B, int U, int C, const float *__restrict__ g3,
+                                                      const float *__restrict__ mean3, const float *__restrict__ invstd3,
+                                                      float *__restrict__ gh2, float *__restrict__ dg3, float *__restrict__ db3)
+{
+    extern __shared__ float sm[];
+    const int Cp = C + 1;
+    float *Wfs = sm;                 // [8][C]
+    float *gls = Wfs + 8 * C;        // [64][C+1]
+    float *gz = gls + 64 * Cp;       // [8][B]
+    const int u0 = blockIdx.x * 8;
+    if (Wf == nullptr) {
+        // upstream gradient already refers to the unit outputs: gl is (B,U)
+        for (long long i = threadIdx.x; i < 8 * B; i += blockDim.x) {
+            const int uu = (int)(i / B);
+            const long long b = i - (long long)uu * B;
+            const int u = u0 + uu;
+            gz[i] = (u < U && unit[b * U + u] > 0.f) ? gl[b * U + u] : 0.f;
+        }
+    }
+    for (int i = threadIdx.x; Wf != nullptr && i < 8 * C; i += blockDim.x) {
+        const int uu = i / C, c = i - uu * C;
+        Wfs[i] = u0 + uu < U ? Wf[(size_t)c * U + u0 + uu] : 0.f;
+    }
+    for (long long r0 = 0; Wf != nullptr && r0 < B; r0 += 64) {
+        const int rows = (int)min(64LL, B - r0);
+        __syncthreads();
+        for (int i = threadIdx.x; i < rows * C; i += blockDim.x) {
+            const int r = i / C, c = i - r * C;
+            gls[r * Cp + c] = gl[(r0 + r) * C + c];
+        }
+        __syncthreads();
+        const int r = threadIdx.x & 63, uq = threadIdx.x >> 6;
+        if (r < rows) {
+            float a0 = 0.f, a1 = 0.f;
+            const float *w0 = Wfs + (2 * uq) * C, *w1 = w0 + C;
+            for (int c = 0; c < C; ++c) {
+                const float g = gls[r * Cp + c];
+                a0 = fmaf(g, w0[c], a0);
+                a1 = fmaf(g, w1[c], a1);
+            }
+            const int ua = u0 + 2 * uq, ub = ua + 1;
+            gz[(size_t)(2 * uq) * B + r0 + r] = (ua < U && unit[(r0 + r) * U + ua] > 0.f) ? a0 : 0.f;
+            gz[(size_t)(2 * uq + 1) * B + r0 + r] = (ub < U && unit[(r0 + r) * U + ub] > 0.f) ? a1 : 0.f;
+        }
+    }
+    __syncthreads();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int u = u0 + warp;
+    if (u >= U) return;
+    const float mean = mean3[u], inv = invstd3[u];
+    const float *gzu = gz + (size_t)warp * B;
+    const float *h2u = h2 + (size_t)u * B;
+    float s1 = 0.f, s2 = 0.f;
+    for (long long b = lane; b < B; b += 32) {
+        const float g = gzu[b], xh = (h2u[b] - mean) * inv;
+        s1 += g;
+        s2 = fmaf(g, xh, s2);
+    }
+    s1 = warp_sum(s1);
+    s2 = warp_sum(s2);
+    if (lane == 0) {
+        if (db3) db3[u] = s1;
+        if (dg3) dg3[u] = s2;
+    }
+    const float m1 = s1 / (float)B, m2 = s2 / (float)B, k = g3[u] * inv;
+    for (long long b = lane; b < B; b += 32) {
+        const float xh = (h2u[b] - mean) * inv;
+        gh2[(size_t)u * B + b] = k * (gzu[b] - m1 - xh * m2);
+    }
+}
+
+// FC2 backward + ReLU/dropout mask + BatchNorm-2 backward sums, per tile
+__global__ void __launch_bounds__(FC_THREADS) bwd_fc2_kernel(const float *__restrict__ h1, const float *__restrict__ gh2,
+                                                             long long B, int U, const float *__restrict__ g2,
+                                                             const float *__restrict__ be2, const float *__restrict__ mean2,
+                                                             const float *__restrict__ invstd2, const float *__restrict__ W2,
+                                                             float pdrop, unsigned long long seed, float *__restrict__ pb2)
+{
+    __shared__ float mu[128], inv[128], ga[128], be[128], w2s[128];
+    __shared__ float red[8][3][128];
+    const int u = blockIdx.x, chunk = blockIdx.y, nchunk = gridDim.y;
+    const long long b0 = (long long)chunk * BM;
+    const int rows = (int)min((long long)BM, B - b0);
+    if (threadIdx.x < 128) {
+        const int j = threadIdx.x, ch = u * H + j;
+        const bool v = j < H;
+        mu[j] = v ? mean2[ch] : 0.f; inv[j] = v ? invstd2[ch] : 0.f; ga[j] = v ? g2[ch] : 0.f;
+        be[j] = v ? be2[ch] : 0.f; w2s[j] = v ? W2[ch] : 0.f;
+    }
+    __syncthreads();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const unsigned thresh = pdrop > 0.f ? (unsigned)min(4294967295.0, (double)pdrop * 4294967296.0) : 0u;
+    const float keep_scale = pdrop > 0.f ? 1.0f / (1.0f - pdrop) : 1.0f;
+    float dW2[4] = {0, 0, 0, 0}, sg[4] = {0, 0, 0, 0}, sgx[4] = {0, 0, 0, 0};
+    for (int r = warp; r < rows; r += 8) {
+        const size_t rowi = (size_t)u * B + b0 + r;
+        const float *hr = h1 + rowi * H;
+        const float g = gh2[rowi];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int j = lane + 32 * i;
+            if (j < H) {
+                const float xh = (hr[j] - mu[j]) * inv[j];
+                const float zb = fmaf(ga[j], xh, be[j]);
+                const float ks = pdrop > 0.f ? drop_scale(seed, rowi * H + j, thresh, keep_scale) : 1.0f;
+                const float a2 = fmaxf(zb, 0.f) * ks;
+                dW2[i] = fmaf(g, a2, dW2[i]);
+                const float gz2 = zb > 0.f ? g * w2s[j] * ks : 0.f;
+                sg[i] += gz2;
+                sgx[i] = fmaf(gz2, xh, sgx[i]);
+            }
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        red[warp][0][lane + 32 * i] = dW2[i];
+        red[warp][1][lane + 32 * i] = sg[i];
+        red[warp][2][lane + 32 * i] = sgx[i];
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < 3 * H; i += blockDim.x) {
+        const int t = i / H, j = i - t * H;
+        float v = 0.f;
+        for (int w = 0; w < 8; ++w) v += red[w][t][j];
+        pb2[(((size_t)u * nchunk + chunk) * 3 + t) * H + j] = v;
+    }
+}
+
+// BatchNorm-2 backward -> gh1 tile -> d(pooled) = gh1 . W1 and dW1 partial = gh1^T . pooled
+template <int PH>
+__global__ void __launch_bounds__(FC_THREADS) bwd_fc1_kernel(
+    const float *__restrict__ h1, const float *__restrict__ gh2, const float *__restrict__ pooled, long long B, int U, int P,
+    const float *__restrict__ g2, const float *__restrict__ be2, const float *__restrict__ mean2, const float *__restrict__ invstd2,
+    const float *__restrict__ W1, const float *__restrict__ W2, float pdrop, unsigned long long seed,
+    const float *__restrict__ pb2, float *__restrict__ gpool, float *__restrict__ dW1p, float *__restrict__ dW2,
+    float *__restrict__ db1, float *__restrict__ db2, float *__restrict__ dg2, float *__restrict__ dbe2)
+{
+    constexpr int PQ = 2 * PH;
+    extern __shared__ __align__(16) unsigned char smem[];
+    float *Gs = reinterpret_cast<float *>(smem);   // [BM][HS]
+    float *As = Gs + BM * HS;                       // [BM][PQ]   (BM*HS = 12928 floats: 16-byte aligned)
+    float *Wr = As + BM * PQ;                       // [H][PQ]
+    __shared__ float mu[128], inv[128], ga[128], be[128], w2s[128], m1s[128], m2s[128];
+    const int u = blockIdx.x, chunk = blockIdx.y, nchunk = gridDim.y;
+    const long long b0 = (long long)chunk * BM;
+    const int rows = (int)min((long long)BM, B - b0);
+    if (threadIdx.x < 128) {
+        const int j = threadIdx.x, ch = u * H + j;
+        const bool v = j < H;
+        float a = 0.f, s1 = 0.f, s2 = 0.f;
+        if (v) {
+            for (int k = 0; k < nchunk; ++k) {
+                const float *pp = pb2 + ((size_t)u * nchunk + k) * 3 * H;
+                a += pp[j]; s1 += pp[H + j]; s2 += pp[2 * H + j];
+            }
+            if (chunk == 0) {
+                if (dW2) dW2[ch] = a;
+                if (dbe2) dbe2[ch] = s1;
+                if (dg2) dg2[ch] = s2;
+                if (db1) db1[ch] = 0.f;          // bias followed by train-mode BatchNorm: gradient is exactly zero
+                if (db2 && j == 0) db2[u] = 0.f;
+            }
+        }
+        mu[j] = v ? mean2[ch] : 0.f; inv[j] = v ? invstd2[ch] : 0.f; ga[j] = v ? g2[ch] : 0.f;
+        be[j] = v ? be2[ch] : 0.f; w2s[j] = v ? W2[ch] : 0.f;
+        m1s[j] = s1 / (float)B; m2s[j] = s2 / (float)B;
+    }
+    // pooled tile and W1[u], both zero-padded to PQ columns
+    for (int i = threadIdx.x; i < BM * PQ; i += blockDim.x) {
+        const int r = i / PQ, p = i - r * PQ;
+        As[i] = (r < rows && p < P) ? pooled[((size_t)u * B + b0 + r) * P + p] : 0.f;
+    }
+    for (int i = threadIdx.x; i < H * PQ; i += blockDim.x) {
+        const int j = i / PQ, p = i - j * PQ;
+        Wr[i] = p < P ? W1[((size_t)u * H + j) * P + p] : 0.f;
+    }
+    __syncthreads();
+    const unsigned thresh = pdrop > 0.f ? (unsigned)min(4294967295.0, (double)pdrop * 4294967296.0) : 0u;
+    const float keep_scale = pdrop > 0.f ? 1.0f / (1.0f - pdrop) : 1.0f;
+    for (int i = threadIdx.x; i < BM * H; i += blockDim.x) {
+        const int r = i / H, j = i - r * H;
+        float v = 0.f;
+        if (r < rows) {
+            const size_t rowi = (size_t)u * B + b0 + r;
+            const float xh = (h1[rowi * H + j] - mu[j]) * inv[j];
+            const float zb = fmaf(ga[j], xh, be[j]);
+            float gz2 = 0.f;
+            if (zb > 0.f) {
+                const float ks = pdrop > 0.f ? drop_scale(seed, rowi * H + j, thresh, keep_scale) : 1.0f;
+                gz2 = gh2[rowi] * w2s[j] * ks;
+            }
+            v = ga[j] * inv[j] * (gz2 - m1s[j] - xh * m2s[j]);
+        }
+        Gs[r * HS + j] = v;
+    }
+    __syncthreads();
+    const int t = threadIdx.x & 127, ph = threadIdx.x >> 7;
+    float acc[PH];
+    // (a) d(pooled)[b][p] = sum_j G[b][j] * W1[j][p]
+#pragma unroll
+    for (int i = 0; i < PH; ++i) acc[i] = 0.f;
+    for (int j = 0; j < H; ++j) {
+        const float g = Gs[t * HS + j];
+        const float4 *w = reinterpret_cast<const float4 *>(Wr + j * PQ + ph * PH);
+#pragma unroll
+        for (int v = 0; v < PH / 4; ++v) {
+            const float4 ww = w[v];
+            acc[4 * v + 0] = fmaf(g, ww.x, acc[4 * v + 0]);
+            acc[4 * v + 1] = fmaf(g, ww.y, acc[4 * v + 1]);
+            acc[4 * v + 2] = fmaf(g, ww.z, acc[4 * v + 2]);
+            acc[4 * v + 3] = fmaf(g, ww.w, acc[4 * v + 3]);
+        }
+    }
+    if (t < rows) {
+        float *dst = gpool + ((size_t)u * B + b0 + t) * P;
+#pragma unroll
+        for (int i = 0; i < PH; ++i)
+            if (ph * PH + i < P) dst[ph * PH + i] = acc[i];
+    }
+    // (b) dW1[j][p] partial = sum_b G[b][j] * pooled[b][p]
+#pragma unroll
+    for (int i = 0; i < PH; ++i) acc[i] = 0.f;
+    if (t < H) {
+        for (int b = 0; b < BM; ++b) {
+            const float g = Gs[b * HS + t];
+            const float4 *a = reinterpret_cast<const float4 *>(As + b * PQ + ph * PH);
+#pragma unroll
+            for (int v = 0; v < PH / 4; ++v) {
+                const float4 aa = a[v];
+                acc[4 * v + 0] = fmaf(g, aa.x, acc[4 * v + 0]);
+                acc[4 * v + 1] = fmaf(g, aa.y, acc[4 * v + 1]);
+                acc[4 * v + 2] = fmaf(g, aa.z, acc[4 * v + 2]);
+                acc[4 * v + 3] = fmaf(g, aa.w, acc[4 * v + 3]);
+            }
+        }
+        float *dst = dW1p + (((size_t)chunk * U + u) * H + t) * P;
+#pragma unroll
+        for (int i = 0; i < PH; ++i)
+            if (ph * PH + i < P) dst[ph * PH + i] = acc[i];
+    }
+}
+
+template <int PH>
+size_t bwd_fc1_smem() { return ((size_t)BM * HS + (size_t)BM * 2 * PH + (size_t)H * 2 * PH) * 4; }
+
 }  // namespace
 
 extern "C" int explainn_fc_stack_fwd_eval(const float *pooled, long long B, int U, int P, const float *W1, const float *b1,
@@ -208,4 +687,84 @@ extern "C" int explainn_linear_fwd(const float *x, long long B, int U, int C, co
     cudaFuncSetAttribute(linear_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     linear_fwd_kernel<<<(unsigned)((B + 31) / 32), 256, smem, stream>>>(x, B, U, C, W, bias, out);
     return xb_check_launch("linear_fwd");
+}
+
+// ---- training entry points --------------------------------------------------------------------------
+
+extern "C" int explainn_fc_nchunk(long long B) { return (int)((B + BM - 1) / BM); }
+
+extern "C" int explainn_fc_stack_fwd_train(const float *pooled, long long B, int U, int P, int C, const float *W1, const float *b1,
+                                           const float *bn2_w, const float *bn2_b, float *bn2_rm, float *bn2_rv, const float *W2,
+                                           const float *b2, const float *bn3_w, const float *bn3_b, float *bn3_rm, float *bn3_rv,
+                                           float momentum, float eps, float pdrop, unsigned long long seed, const float *Wf,
+                                           const float *bf, float *h1, float *part2, float *mean2, float *invstd2, float *h2,
+                                           float *part3, float *mean3, float *invstd3, float *unit, float *logits,
+                                           cudaStream_t stream)
+{
+    XB_REQUIRE(pooled && W1 && b1 && bn2_w && bn2_b && W2 && b2 && bn3_w && bn3_b && Wf && bf && h1 && part2 && mean2 && invstd2 &&
+                   h2 && part3 && mean3 && invstd3 && unit && logits,
+               "fc_stack_fwd_train: null pointer");
+    XB_REQUIRE(B >= 2 && U >= 1 && P >= 1 && C >= 1, "fc_stack_fwd_train: bad sizes (train-mode BatchNorm needs B >= 2)");
+    XB_REQUIRE(pdrop >= 0.f && pdrop < 1.f, "fc_stack_fwd_train: dropout probability %f", pdrop);
+    const int nchunk = (int)((B + BM - 1) / BM);
+    const size_t smem1 = FcSmem::bytes(P) + (size_t)BM * HS * 4;
+    const size_t smem3 = ((size_t)32 * (U + 1) + 2 * (size_t)U) * 4;
+    if (smem1 > 220 * 1024 || smem3 > 220 * 1024) {
+        xb_set_error("fc_stack_fwd_train: shared memory need (%zu / %zu bytes) exceeds the SM", smem1, smem3);
+        return XB_ERR_UNSUPPORTED;
+    }
+    cudaFuncSetAttribute(fc1_train_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1);
+    fc1_train_kernel<<<dim3(U, nchunk), FC_THREADS, smem1, stream>>>(pooled, B, U, P, W1, b1, h1, part2);
+    fc2_train_kernel<<<dim3(U, nchunk), FC_THREADS, 0, stream>>>(h1, B, U, part2, nchunk, bn2_w, bn2_b, bn2_rm, bn2_rv, momentum, eps,
+                                                                 W2, b2, mean2, invstd2, pdrop, seed, h2, part3);
+    cudaFuncSetAttribute(out_train_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem3);
+    out_train_kernel<<<(unsigned)((B + 31) / 32), 256, smem3, stream>>>(h2, B, U, C, part3, nchunk, bn3_w, bn3_b, bn3_rm, bn3_rv,
+                                                                        momentum, eps, mean3, invstd3, Wf, bf, unit, logits);
+    return xb_check_launch("fc_stack_fwd_train");
+}
+
+extern "C" int explainn_fc_stack_bwd(const float *glogits, long long B, int U, int P, int C, const float *pooled, const float *h1,
+                                     const float *h2, const float *unit, const float *W1, const float *bn2_w, const float *bn2_b,
+                                     const float *mean2, const float *invstd2, const float *W2, const float *bn3_w,
+                                     const float *mean3, const float *invstd3, const float *Wf, float pdrop,
+                                     unsigned long long seed, float *gh2, float *pb2, float *dW1_partials, float *gpool,
+                                     float *dW1, float *db1, float *dbn2_w, float *dbn2_b, float *dW2, float *db2, float *dbn3_w,
+                                     float *dbn3_b, float *dWf, float *dbf, cudaStream_t stream)
+{
+    XB_REQUIRE(glogits && pooled && h1 && h2 && unit && W1 && bn2_w && bn2_b && mean2 && invstd2 && W2 && bn3_w && mean3 && invstd3 &&
+                   gh2 && pb2 && dW1_partials && gpool && dW1,
+               "fc_stack_bwd: null pointer");
+    XB_REQUIRE(B >= 2 && U >= 1 && P >= 1 && C >= 1, "fc_stack_bwd: bad sizes");
+    const int nchunk = (int)((B + BM - 1) / BM);
+    // Wf == NULL: glogits is the gradient w.r.t. the unit outputs (B,U) and the final layer is skipped
+    if (Wf) bwd_final_linear_kernel<<<dim3((U + 31) / 32, (C + 7) / 8), 256, 0, stream>>>(glogits, unit, B, U, C, dWf, dbf);
+    const size_t smem_bn3 = ((size_t)8 * C + (size_t)64 * (C + 1) + (size_t)8 * B) * 4;
+    if (smem_bn3 > 220 * 1024) {
+        xb_set_error("fc_stack_bwd: batch %lld x classes %d needs %zu bytes of shared memory (limit 220 KB)", B, C, smem_bn3);
+        return XB_ERR_LIMIT;
+    }
+    cudaFuncSetAttribute(bwd_bn3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bn3);
+    bwd_bn3_kernel<<<(U + 7) / 8, 256, smem_bn3, stream>>>(glogits, Wf, unit, h2, B, U, C, bn3_w, mean3, invstd3, gh2, dbn3_w, dbn3_b);
+    bwd_fc2_kernel<<<dim3(U, nchunk), FC_THREADS, 0, stream>>>(h1, gh2, B, U, bn2_w, bn2_b, mean2, invstd2, W2, pdrop, seed, pb2);
+#define XB_LAUNCH_BWD_FC1(PHV)                                                                                                      \
+    do {                                                                                                                            \
+        const size_t sm = bwd_fc1_smem<PHV>();                                                                                      \
+        cudaFuncSetAttribute(bwd_fc1_kernel<PHV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);                            \
+        bwd_fc1_kernel<PHV><<<dim3(U, nchunk), FC_THREADS, sm, stream>>>(h1, gh2, pooled, B, U, P, bn2_w, bn2_b, mean2, invstd2, W1, \
+                                                                          W2, pdrop, seed, pb2, gpool, dW1_partials, dW2, db1, db2,  \
+                                                                          dbn2_w, dbn2_b);                                          \
+    } while (0)
+    if (P <= 32) XB_LAUNCH_BWD_FC1(16);
+    else if (P <= 40) XB_LAUNCH_BWD_FC1(20);
+    else if (P <= 72) XB_LAUNCH_BWD_FC1(36);
+    else if (P <= 144) XB_LAUNCH_BWD_FC1(72);
+    else {
+        xb_set_error("fc_stack_bwd: pooled length %d > 144 not supported", P);
+        return XB_ERR_UNSUPPORTED;
+    }
+#undef XB_LAUNCH_BWD_FC1
+    int rc = xb_check_launch("fc_stack_bwd");
+    if (rc != XB_OK) return rc;
+    // dW1 = sum over batch chunks of the per-tile partials
+    return explainn_reduce_partials(dW1, dW1_partials, (long long)U * H * P, nchunk, stream);
 }

@@ -111,14 +111,14 @@ __global__ void interp_thresholds_kernel(const float *__restrict__ zmax, int U, 
     if (t16 == t16 && t16 < INFINITY && zm > -INFINITY) {
         // smallest z with half(exp(z)) > t16, by bisection on the ordered-int representation.
         // pred(-104.5) is false (exp -> 0, and t16 >= 0), pred(89) is true (exp -> inf > finite t16).
-        int a = f2ord(-104.5f), b = f2ord(89.0f);
+        long long a = f2ord(-104.5f), b = f2ord(89.0f);
         while (b - a > 1) {
-            const int mid = a + ((b - a) >> 1);
+            const int mid = (int)(a + ((b - a) >> 1));
             const bool pr = fp16_round(det_expf(ord2f(mid))) > t16;
             if (pr) b = mid; else a = mid;
         }
-        lo = ord2f(b - 64);
-        hi = ord2f(b + 64);
+        lo = ord2f((int)b - 64);
+        hi = ord2f((int)b + 64);
     }
     zlo[u] = lo;
     zhi[u] = hi;

@@ -1,0 +1,379 @@
+// train.cu -- training-only kernels around the conv stage, the fused loss and the fused Adam step.
+//
+// Reference behaviour restated (paths relative to /root/reference):
+//   BatchNorm1d(U) in train mode (batch statistics over (B,S), running-stat update with momentum 0.1 and
+//   the unbiased variance) ........................................ explainn/models/networks.py:100
+//   autograd backward of Conv1d -> BatchNorm1d -> exp -> MaxPool1d .... explainn/train/train.py:65
+//   criterion (BCEWithLogitsLoss / MSELoss, mean reduction) ........... scripts/train.py:210-219, train.py:62
+//   torch.optim.Adam defaults ......................................... scripts/train.py:246-247, train.py:67
+//
+// Because the conv input is one-hot, the batch statistics of the conv output and the dense part of the
+// BatchNorm backward follow from input-only integer statistics (SURVEY.md 7.3 b):
+//   M[i][j] = sum_{b,s} x[b,c,s+k] * x[b,c',s+k'],   i = c*F+k, j = c'*F+k'    (co-occurrence counts)
+//   cnt[i]  = M[i][i]
+//   mean(y_u) = bias_u + w_u.cnt / N ;  E[(y_u-bias_u)^2] = w_u^T M w_u / N ;  N = B*S
+// so the (B,U,S) conv output is never needed twice, and the backward touches only the pool-argmax
+// positions plus these tables.
+#include "common.cuh"
+#include "../../include/explainn_b200.h"
+
+namespace {
+
+// ------------------------------------------------------------------------------------------------
+// co-occurrence counts.  One thread per tap pair (k <= k'), 16 private counters (c,c') in shared memory.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(320) cooc_kernel(const uint32_t *__restrict__ codes, const uint32_t *__restrict__ nmask,
+                                                   long long B, int L, int F, int wc, int wm, int *__restrict__ M)
+{
+    extern __shared__ __align__(16) unsigned char sm[];
+    const int NT = blockDim.x;
+    int *cnt = reinterpret_cast<int *>(sm);                        // [16][NT]
+    unsigned char *sb = sm + (size_t)16 * NT * 4;                   // [L + pad]
+    const int tid = threadIdx.x;
+    const int npairs = F * (F + 1) / 2;
+    // pair index -> (k, k2) with k <= k2
+    int k = 0, k2 = 0;
+    if (tid < npairs) {
+        int r = tid;
+        while (r >= F - k) { r -= F - k; ++k; }
+        k2 = k + r;
+    }
+    for (int j = 0; j < 16; ++j) cnt[j * NT + tid] = 0;
+    const int S = L - F + 1;
+    for (long long b = blockIdx.x; b < B; b += gridDim.x) {
+        __syncthreads();
+        for (int i = tid; i < L; i += NT) {
+            const unsigned c = (codes[b * wc + (i >> 4)] >> (2 * (i & 15))) & 3u;
+            const unsigned m = (nmask[b * wm + (i >> 5)] >> (i & 31)) & 1u;
+            sb[i] = (unsigned char)(m ? 4u : c);
+        }
+        __syncthreads();
+        if (tid < npairs) {
+            const unsigned char *p1 = sb + k, *p2 = sb + k2;
+#pragma unroll 4
+            for (int s = 0; s < S; ++s) {
+                const unsigned c = p1[s], c2 = p2[s];
+                if ((c | c2) < 4u) cnt[(c * 4 + c2) * NT + tid] += 1;
+            }
+        }
+    }
+    if (tid < npairs) {
+        const int W = 4 * F;
+        for (int c = 0; c < 4; ++c)
+            for (int c2 = 0; c2 < 4; ++c2) {
+                const int v = cnt[(c * 4 + c2) * NT + tid];
+                if (!v) continue;
+                atomicAdd(&M[(c * F + k) * W + (c2 * F + k2)], v);
+                if (k != k2) atomicAdd(&M[(c2 * F + k2) * W + (c * F + k)], v);
+            }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// BatchNorm-1 batch statistics from M (one block per unit, fp64 accumulation)
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) bn1_stats_kernel(const int *__restrict__ M, const float *__restrict__ w,
+                                                        const float *__restrict__ bias, int F, double N, float momentum,
+                                                        float *__restrict__ run_mean, float *__restrict__ run_var,
+                                                        long long *__restrict__ nbt, float *__restrict__ mean_out,
+                                                        float *__restrict__ var_out, float *__restrict__ Mw_out)
+{
+    __shared__ double wsm[4 * 4 * XB_MAX_G];
+    __shared__ double red_a[4], red_q[4];
+    const int u = blockIdx.x, W = 4 * F;
+    for (int i = threadIdx.x; i < W; i += blockDim.x) wsm[i] = (double)w[(size_t)u * W + i];
+    __syncthreads();
+    double a = 0.0, q = 0.0;
+    for (int i = threadIdx.x; i < W; i += blockDim.x) {
+        const int *row = M + (size_t)i * W;
+        double d = 0.0;
+        for (int j = 0; j < W; ++j) d += wsm[j] * (double)row[j];
+        Mw_out[(size_t)u * W + i] = (float)d;
+        q += wsm[i] * d;
+        a += wsm[i] * (double)row[i];
+    }
+    a = warp_sum_d(a);
+    q = warp_sum_d(q);
+    if ((threadIdx.x & 31) == 0) { red_a[threadIdx.x >> 5] = a; red_q[threadIdx.x >> 5] = q; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        a = (red_a[0] + red_a[1]) + (red_a[2] + red_a[3]);
+        q = (red_q[0] + red_q[1]) + (red_q[2] + red_q[3]);
+        const double mc = a / N;
+        double var = q / N - mc * mc;
+        if (var < 0.0) var = 0.0;
+        const float mean = (float)((double)bias[u] + mc);
+        mean_out[u] = mean;
+        var_out[u] = (float)var;
+        if (run_mean) {
+            const double unb = N > 1.0 ? var * N / (N - 1.0) : var;
+            run_mean[u] = (1.0f - momentum) * run_mean[u] + momentum * mean;
+            run_var[u] = (1.0f - momentum) * run_var[u] + momentum * (float)unb;
+        }
+        if (nbt && u == 0) *nbt += 1;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Sparse part of the conv backward: only pool-argmax positions carry gradient.
+// grid (U, nsplit); 4 warps; lanes walk the (b,p) entries of one unit, 32 at a time, with lane-private
+// accumulators acc[4F][lane] in shared memory.
+// ------------------------------------------------------------------------------------------------
+constexpr int BW_WARPS = 4;
+
+__global__ void __launch_bounds__(BW_WARPS * 32) conv_bwd_sparse_kernel(
+    const uint32_t *__restrict__ codes, const uint32_t *__restrict__ nmask, long long B, int L, int F, int P, int wc, int wm,
+    const float *__restrict__ gpool, const float *__restrict__ pooled, const float *__restrict__ xhat,
+    const unsigned char *__restrict__ idx, float *__restrict__ partial /* (nsplit, U, 4F+2) */, int U)
+{
+    extern __shared__ float acc[];   // [BW_WARPS][4F][32] then [BW_WARPS][4F+2] for the block reduce
+    const int u = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31, W = 4 * F;
+    float *my = acc + (size_t)warp * W * 32;
+    for (int i = lane; i < W * 32; i += 32) my[i] = 0.0f;
+    __syncwarp();
+    const long long n = B * P;
+    const long long per = (n + gridDim.y - 1) / gridDim.y;
+    const long long e0 = per * blockIdx.y, e1 = min(n, e0 + per);
+    const size_t ubase = (size_t)u * n;
+    float dbeta = 0.f, dgamma = 0.f;
+    for (long long e = e0 + warp * 32 + lane; e < e1; e += BW_WARPS * 32) {
+        const long long b = e / P;
+        const int p = (int)(e - b * P);
+        const float gz = gpool[ubase + e] * pooled[ubase + e];
+        const float xh = xhat[ubase + e];
+        const int s = p * XB_POOL + idx[ubase + e];
+        dbeta += gz;
+        dgamma = fmaf(gz, xh, dgamma);
+        const uint32_t *cw = codes + b * wc;
+        const uint32_t *mw = nmask + b * wm;
+        const int wi = s >> 4, sh = 2 * (s & 15);
+        const uint32_t w0 = cw[wi], w1 = wi + 1 < wc ? cw[wi + 1] : 0u, w2 = wi + 2 < wc ? cw[wi + 2] : 0u;
+        const uint32_t A0 = __funnelshift_r(w0, w1, sh), A1 = __funnelshift_r(w1, w2, sh);
+        const int mi = s >> 5;
+        const uint32_t m0 = mw[mi], m1 = mi + 1 < wm ? mw[mi + 1] : 0u;
+        const uint32_t MW = __funnelshift_r(m0, m1, s & 31);
+        for (int k = 0; k < F; ++k) {
+            const uint32_t c = ((k < 16 ? A0 : A1) >> ((2 * k) & 31)) & 3u;
+            if (!((MW >> k) & 1u)) my[(c * F + k) * 32 + lane] += gz;
+        }
+    }
+    __syncwarp();
+    // lane-transposed reduction: lane l sums rows l, l+32, ...
+    float *out = acc + (size_t)BW_WARPS * W * 32 + (size_t)warp * (W + 2);
+    for (int r = lane; r < W; r += 32) {
+        float v = 0.f;
+#pragma unroll 8
+        for (int j = 0; j < 32; ++j) v += my[r * 32 + ((j + lane) & 31)];
+        out[r] = v;
+    }
+    dbeta = warp_sum(dbeta);
+    dgamma = warp_sum(dgamma);
+    if (lane == 0) { out[W] = dgamma; out[W + 1] = dbeta; }
+    __syncthreads();
+    for (int r = threadIdx.x; r < W + 2; r += blockDim.x) {
+        float v = 0.f;
+        for (int w = 0; w < BW_WARPS; ++w) v += acc[(size_t)BW_WARPS * W * 32 + (size_t)w * (W + 2) + r];
+        partial[((size_t)blockIdx.y * U + u) * (W + 2) + r] = v;
+    }
+}
+
+// dense correction + assembly of the conv/BN-1 parameter gradients (one block per unit)
+__global__ void __launch_bounds__(128) conv_bwd_final_kernel(const float *__restrict__ partial, int nsplit, int U, int F,
+                                                             const int *__restrict__ M, const float *__restrict__ Mw,
+                                                             const float *__restrict__ bias, const float *__restrict__ mean,
+                                                             const float *__restrict__ var, const float *__restrict__ gamma,
+                                                             float eps, double N, float *__restrict__ dW,
+                                                             float *__restrict__ dbias, float *__restrict__ dgamma,
+                                                             float *__restrict__ dbeta)
+{
+    const int u = blockIdx.x, W = 4 * F;
+    __shared__ double s_dg, s_db;
+    if (threadIdx.x == 0) {
+        double dg = 0.0, db = 0.0;
+        for (int c = 0; c < nsplit; ++c) {
+            dg += (double)partial[((size_t)c * U + u) * (W + 2) + W];
+            db += (double)partial[((size_t)c * U + u) * (W + 2) + W + 1];
+        }
+        s_dg = dg; s_db = db;
+        if (dgamma) dgamma[u] = (float)dg;
+        if (dbeta) dbeta[u] = (float)db;
+        if (dbias) dbias[u] = 0.0f;      // exactly zero: the bias is followed by a train-mode BatchNorm
+    }
+    __syncthreads();
+    if (!dW) return;
+    const double inv = 1.0 / sqrt((double)var[u] + (double)eps);
+    const double mc = (double)mean[u] - (double)bias[u];
+    const double m1 = s_db / N, m2 = s_dg / N;
+    const double g = (double)gamma[u] * inv;
+    for (int i = threadIdx.x; i < W; i += blockDim.x) {
+        double A = 0.0;
+        for (int c = 0; c < nsplit; ++c) A += (double)partial[((size_t)c * U + u) * (W + 2) + i];
+        const double cnt = (double)M[(size_t)i * W + i];
+        const double R = inv * ((double)Mw[(size_t)u * W + i] - mc * cnt);
+        dW[(size_t)u * W + i] = (float)(g * (A - m1 * cnt - m2 * R));
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// fused loss (mean reduction) + d(loss)/d(logits).  Single block; n = B*C is small.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(1024) loss_kernel(const float *__restrict__ logits, const float *__restrict__ target,
+                                                    long long n, int kind, float grad_scale, float *__restrict__ loss,
+                                                    float *__restrict__ dlogits)
+{
+    __shared__ double red[32];
+    double acc = 0.0;
+    const float inv_n = 1.0f / (float)n;
+    for (long long i = threadIdx.x; i < n; i += blockDim.x) {
+        const float x = logits[i], y = target[i];
+        float l, g;
+        if (kind == EXPLAINN_LOSS_BCE_WITH_LOGITS) {
+            // max(x,0) - x*y + log(1 + exp(-|x|)) ; gradient sigmoid(x) - y
+            const float e = expf(-fabsf(x));
+            l = fmaxf(x, 0.f) - x * y + log1pf(e);
+            const float sg = x >= 0.f ? 1.f / (1.f + e) : e / (1.f + e);
+            g = sg - y;
+        } else {
+            const float d = x - y;
+            l = d * d;
+            g = 2.f * d;
+        }
+        acc += (double)l;
+        if (dlogits) dlogits[i] = g * inv_n * grad_scale;
+    }
+    acc = warp_sum_d(acc);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        double v = threadIdx.x < (blockDim.x >> 5) ? red[threadIdx.x] : 0.0;
+        v = warp_sum_d(v);
+        if (threadIdx.x == 0) *loss = (float)(v / (double)n);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// fused Adam over one flat buffer (torch.optim.Adam, amsgrad=False, weight_decay=0, maximize=False)
+//   m.lerp_(g, 1-b1); v = b2*v + (1-b2)*g*g; p -= step_size * m / (sqrt(v)/sqrt(bc2) + eps)
+// `step` is a device scalar that this kernel's launch wrapper does not read: bias corrections are
+// computed on the device from *step (float, already incremented by adam_tick_kernel).
+// ------------------------------------------------------------------------------------------------
+__global__ void adam_tick_kernel(float *step) { *step += 1.0f; }
+
+__global__ void __launch_bounds__(256) adam_kernel(float *__restrict__ p, const float *__restrict__ g, float *__restrict__ m,
+                                                   float *__restrict__ v, long long n, const float *__restrict__ step,
+                                                   float lr, float b1, float b2, float eps, float grad_scale)
+{
+    const double t = (double)*step;
+    const double bc1 = 1.0 - pow((double)b1, t), bc2 = 1.0 - pow((double)b2, t);
+    const float step_size = (float)((double)lr / bc1);
+    const float bc2s = (float)sqrt(bc2);
+    const float w1 = 1.0f - b1, w2 = 1.0f - b2;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const float gi = g[i] * grad_scale;
+        const float mi = fmaf(gi - m[i], w1, m[i]);
+        const float vi = fmaf(gi * gi, w2, v[i] * b2);
+        m[i] = mi;
+        v[i] = vi;
+        const float denom = sqrtf(vi) / bc2s + eps;
+        p[i] = p[i] - step_size * (mi / denom);
+    }
+}
+
+__global__ void reduce_partials_kernel(float *__restrict__ out, const float *__restrict__ part, long long n, int k)
+{
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float v = 0.f;
+    for (int c = 0; c < k; ++c) v += part[(size_t)c * n + i];
+    out[i] = v;
+}
+
+}  // namespace
+
+extern "C" int explainn_input_cooc_stats(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int F, int *M,
+                                         cudaStream_t stream)
+{
+    XB_REQUIRE(codes && nmask && M && B >= 0 && F >= 1 && F <= 4 * XB_MAX_G && L >= F, "input_cooc_stats: bad argument");
+    const int W = 4 * F;
+    cudaError_t e = cudaMemsetAsync(M, 0, (size_t)W * W * sizeof(int), stream);
+    if (e != cudaSuccess) { xb_set_error("cudaMemsetAsync: %s", cudaGetErrorString(e)); return XB_ERR_CUDA; }
+    if (B == 0) return XB_OK;
+    const int npairs = F * (F + 1) / 2;
+    const int NT = ((npairs + 31) / 32) * 32;
+    const size_t smem = (size_t)16 * NT * 4 + ((L + 15) / 16) * 16;
+    int grid = 2 * xb_num_sms();
+    if (grid > B) grid = (int)B;
+    cudaFuncSetAttribute(cooc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cooc_kernel<<<grid, NT, smem, stream>>>(codes, nmask, B, L, F, xb_words_codes(L), xb_words_mask(L), M);
+    return xb_check_launch("input_cooc_stats");
+}
+
+extern "C" int explainn_bn1_batch_stats(const int *M, const float *w, const float *bias, int U, int F, long long n_pos,
+                                        float momentum, float *run_mean, float *run_var, long long *num_batches_tracked,
+                                        float *mean, float *var, float *Mw, cudaStream_t stream)
+{
+    XB_REQUIRE(M && w && bias && mean && var && Mw && U >= 1 && F >= 1 && F <= 4 * XB_MAX_G && n_pos >= 1,
+               "bn1_batch_stats: bad argument");
+    bn1_stats_kernel<<<U, 128, 0, stream>>>(M, w, bias, F, (double)n_pos, momentum, run_mean, run_var, num_batches_tracked, mean,
+                                           var, Mw);
+    return xb_check_launch("bn1_batch_stats");
+}
+
+extern "C" int explainn_conv_bwd_nsplit(int U)
+{
+    const int target = 2 * xb_num_sms();
+    int ns = (target + U - 1) / U;
+    return ns < 1 ? 1 : ns;
+}
+
+extern "C" int explainn_conv_pool_bwd(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F,
+                                      const float *gpool, const float *pooled, const float *xhat, const unsigned char *idx,
+                                      const int *M, const float *Mw, const float *bias, const float *mean, const float *var,
+                                      const float *gamma, float eps, float *partial, int nsplit, float *dW, float *dbias,
+                                      float *dgamma, float *dbeta, cudaStream_t stream)
+{
+    XB_REQUIRE(codes && nmask && gpool && pooled && xhat && idx && M && Mw && bias && mean && var && gamma && partial,
+               "conv_pool_bwd: null pointer");
+    XB_REQUIRE(B >= 1 && U >= 1 && F >= 1 && F <= 4 * XB_MAX_G && L >= F + XB_POOL - 1 && nsplit >= 1, "conv_pool_bwd: bad sizes");
+    const int S = L - F + 1, P = (S - XB_POOL) / XB_POOL + 1, W = 4 * F;
+    const size_t smem = ((size_t)BW_WARPS * W * 32 + (size_t)BW_WARPS * (W + 2)) * sizeof(float);
+    cudaFuncSetAttribute(conv_bwd_sparse_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    conv_bwd_sparse_kernel<<<dim3(U, nsplit), BW_WARPS * 32, smem, stream>>>(codes, nmask, B, L, F, P, xb_words_codes(L),
+                                                                            xb_words_mask(L), gpool, pooled, xhat, idx, partial, U);
+    int rc = xb_check_launch("conv_bwd_sparse");
+    if (rc != XB_OK) return rc;
+    conv_bwd_final_kernel<<<U, 128, 0, stream>>>(partial, nsplit, U, F, M, Mw, bias, mean, var, gamma, eps, (double)B * S, dW, dbias,
+                                                dgamma, dbeta);
+    return xb_check_launch("conv_bwd_final");
+}
+
+extern "C" int explainn_loss_fwd_bwd(const float *logits, const float *target, long long B, int C, int kind, float grad_scale,
+                                     float *loss, float *dlogits, cudaStream_t stream)
+{
+    XB_REQUIRE(logits && target && loss && B >= 1 && C >= 1, "loss_fwd_bwd: bad argument");
+    XB_REQUIRE(kind == EXPLAINN_LOSS_BCE_WITH_LOGITS || kind == EXPLAINN_LOSS_MSE, "loss_fwd_bwd: unknown loss %d", kind);
+    loss_kernel<<<1, 1024, 0, stream>>>(logits, target, B * C, kind, grad_scale, loss, dlogits);
+    return xb_check_launch("loss_fwd_bwd");
+}
+
+extern "C" int explainn_adam_step(float *param, const float *grad, float *exp_avg, float *exp_avg_sq, long long n, float *step,
+                                  float lr, float beta1, float beta2, float eps, float grad_scale, cudaStream_t stream)
+{
+    XB_REQUIRE(param && grad && exp_avg && exp_avg_sq && step && n >= 0, "adam_step: bad argument");
+    adam_tick_kernel<<<1, 1, 0, stream>>>(step);
+    if (n > 0) {
+        long long blocks = (n + 255) / 256;
+        const long long cap = 8LL * xb_num_sms();
+        if (blocks > cap) blocks = cap;
+        adam_kernel<<<(unsigned)blocks, 256, 0, stream>>>(param, grad, exp_avg, exp_avg_sq, n, step, lr, beta1, beta2, eps, grad_scale);
+    }
+    return xb_check_launch("adam_step");
+}
+
+extern "C" int explainn_reduce_partials(float *out, const float *partials, long long n, int k, cudaStream_t stream)
+{
+    XB_REQUIRE(out && partials && n >= 0 && k >= 1, "reduce_partials: bad argument");
+    if (n == 0) return XB_OK;
+    reduce_partials_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(out, partials, n, k);
+    return xb_check_launch("reduce_partials");
+}

@@ -76,6 +76,8 @@ def conv_pool_fwd(pk, prep):
     """-> pooled (U,B,P) unit-major."""
     P = pooled_len(pk.L, prep.F)
     pooled = torch.empty((prep.U, pk.B, P), dtype=torch.float32, device=pk.codes.device)
+    if pk.B == 0:
+        return pooled
     call("explainn_conv_pool_fwd", ptr(pk.codes), ptr(pk.nmask), pk.B, pk.L, prep.U, prep.F, ptr(prep.tables),
          ptr(prep.wq_t), ptr(prep.shift), ptr(pooled), stream())
     return pooled
@@ -85,6 +87,8 @@ def unit_activations(pk, prep, dtype=torch.float16):
     S = pk.L - prep.F + 1
     act = torch.empty((pk.B, prep.U, S), dtype=dtype, device=pk.codes.device)
     dt = _cabi.DTYPE_F16 if dtype == torch.float16 else _cabi.DTYPE_F32
+    if pk.B == 0:
+        return act
     call("explainn_unit_activations", ptr(pk.codes), ptr(pk.nmask), pk.B, pk.L, prep.U, prep.F, ptr(prep.tables),
          ptr(prep.wq_t), ptr(prep.shift), ptr(act), dt, stream())
     return act
@@ -96,7 +100,10 @@ def interp_unit_max(pk, prep, zmax=None):
     scratch = torch.empty(_cabi.lib.explainn_interp_unit_max_scratch_floats(prep.U), dtype=torch.float32, device=dev)
     acc = zmax is not None
     if zmax is None:
-        zmax = torch.empty(prep.U, dtype=torch.float32, device=dev)
+        zmax = torch.full((prep.U,), float("-inf"), dtype=torch.float32, device=dev)
+        acc = True
+    if pk.B == 0:
+        return zmax
     call("explainn_interp_unit_max", ptr(pk.codes), ptr(pk.nmask), pk.B, pk.L, prep.U, prep.F, ptr(prep.tables),
          ptr(prep.wq_t), ptr(prep.shift), ptr(scratch), ptr(zmax), int(acc), stream())
     return zmax
@@ -114,6 +121,8 @@ def interp_pwm_count(pk, prep, thr, zlo, zhi, counts=None, hits=None):
     if counts is None:
         counts = torch.zeros((prep.U, 4, prep.F), dtype=torch.int64, device=dev)
         hits = torch.zeros(prep.U, dtype=torch.int64, device=dev)
+    if pk.B == 0:
+        return counts, hits
     call("explainn_interp_pwm_count", ptr(pk.codes), ptr(pk.nmask), pk.B, pk.L, prep.U, prep.F, ptr(prep.tables),
          ptr(prep.wq_t), ptr(prep.shift), ptr(zlo), ptr(zhi), ptr(thr), ptr(counts), ptr(hits), stream())
     return counts, hits
@@ -123,6 +132,8 @@ def fc_stack_fwd_eval(pooled, W1, b1, bn2, W2, b2, bn3, eps=1e-5):
     """pooled (U,B,P) -> unit outputs (B,U).  bn2/bn3 = (weight, bias, running_mean, running_var)."""
     U, B, P = pooled.shape
     out = torch.empty((B, U), dtype=torch.float32, device=pooled.device)
+    if B == 0:
+        return out
     call("explainn_fc_stack_fwd_eval", ptr(pooled), B, U, P, ptr(W1), ptr(b1), ptr(bn2[0]), ptr(bn2[1]), ptr(bn2[2]),
          ptr(bn2[3]), ptr(W2), ptr(b2), ptr(bn3[0]), ptr(bn3[1]), ptr(bn3[2]), ptr(bn3[3]), float(eps), ptr(out), stream())
     return out
@@ -132,5 +143,40 @@ def linear_fwd(x, W, bias):
     B, U = x.shape
     Cc = W.shape[0]
     out = torch.empty((B, Cc), dtype=torch.float32, device=x.device)
+    if B == 0:
+        return out
     call("explainn_linear_fwd", ptr(x), B, U, Cc, ptr(W), ptr(bias), ptr(out), stream())
     return out
+
+
+# ------------------------------------------------------------------------------------------ training
+def input_cooc_stats(pk, F):
+    M = torch.empty((4 * F, 4 * F), dtype=torch.int32, device=pk.codes.device)
+    call("explainn_input_cooc_stats", ptr(pk.codes), ptr(pk.nmask), pk.B, pk.L, F, ptr(M), stream())
+    return M
+
+
+def bn1_batch_stats(M, w, bias, n_pos, momentum, run_mean, run_var, nbt):
+    U, _, F = w.shape
+    dev = w.device
+    mean = torch.empty(U, dtype=torch.float32, device=dev)
+    var = torch.empty(U, dtype=torch.float32, device=dev)
+    Mw = torch.empty((U, 4 * F), dtype=torch.float32, device=dev)
+    call("explainn_bn1_batch_stats", ptr(M), ptr(w), ptr(bias), U, F, n_pos, float(momentum), ptr(run_mean), ptr(run_var),
+         ptr(nbt), ptr(mean), ptr(var), ptr(Mw), stream())
+    return mean, var, Mw
+
+
+def conv_pool_fwd_train(pk, prep, gamma, beta):
+    P = pooled_len(pk.L, prep.F)
+    dev = pk.codes.device
+    pooled = torch.empty((prep.U, pk.B, P), dtype=torch.float32, device=dev)
+    xhat = torch.empty((prep.U, pk.B, P), dtype=torch.float32, device=dev)
+    idx = torch.empty((prep.U, pk.B, P), dtype=torch.uint8, device=dev)
+    call("explainn_conv_pool_fwd_train", ptr(pk.codes), ptr(pk.nmask), pk.B, pk.L, prep.U, prep.F, ptr(prep.tables),
+         ptr(prep.wq_t), ptr(prep.shift), ptr(gamma), ptr(beta), ptr(pooled), ptr(xhat), ptr(idx), stream())
+    return pooled, xhat, idx
+
+
+def fc_nchunk(B):
+    return _cabi.lib.explainn_fc_nchunk(B)

@@ -1,0 +1,239 @@
+"""train.train_explainn -- drop-in for explainn/train/train.py:13-142 of the reference.
+
+Two execution paths, same results:
+  * generic: any criterion / optimizer; forward+backward run on the fused kernels through autograd
+    (autograd_fn.py), the optimizer is the caller's.
+  * fused (engaged automatically when the criterion is BCEWithLogitsLoss / MSELoss with mean reduction and
+    the optimizer is a plain torch.optim.Adam over exactly the model's parameters): parameters, gradients
+    and Adam moments live in flat buffers, the loss and its gradient come from one kernel, the whole
+    Adam update is one kernel, and under torch.distributed the step does ONE all-reduce of the flat
+    gradient buffer (data parallel, one process per GPU).
+The per-step `loss.item()` sync of the reference (train.py:73) is replaced by one device->host read of
+all step losses per epoch; the reported epoch means are the same numbers.
+"""
+import copy
+import os
+
+import torch
+import torch.nn as nn
+
+from . import _cabi, autograd_fn
+from ._cabi import call, ptr, stream
+
+
+def _dist():
+    import torch.distributed as dist
+    return dist if dist.is_available() and dist.is_initialized() else None
+
+
+class FusedTrainer:
+    """Flat-buffer training step: forward, fused loss, backward, (all-reduce), fused Adam."""
+
+    LOSSES = {nn.BCEWithLogitsLoss: _cabi.LOSS_BCE, nn.MSELoss: _cabi.LOSS_MSE}
+
+    @staticmethod
+    def supports(model, criterion, optimizer):
+        from .networks import ExplaiNN
+        if not isinstance(model, ExplaiNN) or type(criterion) not in FusedTrainer.LOSSES:
+            return False
+        if getattr(criterion, "reduction", "mean") != "mean":
+            return False
+        if getattr(criterion, "weight", None) is not None or getattr(criterion, "pos_weight", None) is not None:
+            return False
+        if type(optimizer) is not torch.optim.Adam or len(optimizer.param_groups) != 1:
+            return False
+        g = optimizer.param_groups[0]
+        if g.get("amsgrad") or g.get("weight_decay", 0) != 0 or g.get("maximize") or g.get("capturable") \
+                or g.get("differentiable"):
+            return False
+        mp = list(model.parameters())
+        if len(g["params"]) != len(mp) or any(a is not b for a, b in zip(g["params"], mp)):
+            return False
+        if not all(p.requires_grad and p.is_cuda and p.dtype == torch.float32 for p in mp):
+            return False
+        return True
+
+    def __init__(self, model, criterion, optimizer, dropout_seed=None):
+        self.model, self.criterion, self.optimizer = model, criterion, optimizer
+        self.kind = self.LOSSES[type(criterion)]
+        self.params = list(autograd_fn._params(model))
+        dev = self.params[0].device
+        sizes = [p.numel() for p in self.params]
+        # every slice starts on a 16-byte boundary
+        self.offsets, off = [], 0
+        for n in sizes:
+            self.offsets.append(off)
+            off += (n + 3) // 4 * 4
+        self.n = off
+        self.flat_p = torch.zeros(off, dtype=torch.float32, device=dev)
+        self.flat_g = torch.zeros(off, dtype=torch.float32, device=dev)
+        self.flat_m = torch.zeros(off, dtype=torch.float32, device=dev)
+        self.flat_v = torch.zeros(off, dtype=torch.float32, device=dev)
+        self.step_t = torch.zeros(1, dtype=torch.float32, device=dev)
+        self.views_p, self.views_g = [], []
+        state = optimizer.state
+        for p, o, n in zip(self.params, self.offsets, sizes):
+            v = self.flat_p[o:o + n].view_as(p)
+            v.copy_(p.data)
+            p.data = v                      # parameters now alias the flat buffer (same attribute paths)
+            self.views_p.append(v)
+            self.views_g.append(self.flat_g[o:o + n].view_as(p))
+            st = state.get(p)
+            if st:                          # continue from existing Adam state
+                self.flat_m[o:o + n].view_as(p).copy_(st["exp_avg"])
+                self.flat_v[o:o + n].view_as(p).copy_(st["exp_avg_sq"])
+                self.step_t.fill_(float(st["step"]))
+            # expose the moments through the optimizer so that optimizer.state_dict() stays meaningful
+            state[p] = {"step": torch.tensor(float(self.step_t.item())),
+                        "exp_avg": self.flat_m[o:o + n].view_as(p),
+                        "exp_avg_sq": self.flat_v[o:o + n].view_as(p)}
+        self.steps_done = int(self.step_t.item())
+        self.dropout_seed = dropout_seed
+        self.world = 1
+        d = _dist()
+        if d is not None:
+            self.world = d.get_world_size()
+
+    def _still_aliased(self):
+        return all(p.data_ptr() == v.data_ptr() for p, v in zip(self.params, self.views_p))
+
+    def step(self, x, y):
+        """One optimisation step (train.py:59-67).  Returns the loss as a 1-element device tensor."""
+        model = self.model
+        if not self._still_aliased():       # somebody re-assigned a parameter: re-adopt it
+            for p, v in zip(self.params, self.views_p):
+                if p.data_ptr() != v.data_ptr():
+                    v.copy_(p.data)
+                    p.data = v
+        ps = self.views_p
+        seed = None
+        if self.dropout_seed is not None:
+            seed = (self.dropout_seed + 0x9E3779B97F4A7C15 * (self.steps_done + 1)) & 0xFFFFFFFFFFFFFFFF
+        ws = autograd_fn.train_forward(model, x, ps, seed=seed)
+        B, C = ws.logits.shape
+        y = y.to(ws.logits.device, dtype=torch.float32).contiguous()
+        if tuple(y.shape) != (B, C):
+            raise ValueError("labels of shape %s do not match logits %s" % (tuple(y.shape), (B, C)))
+        loss = torch.empty(1, dtype=torch.float32, device=ws.logits.device)
+        dlogits = torch.empty_like(ws.logits)
+        call("explainn_loss_fwd_bwd", ptr(ws.logits), ptr(y), B, C, self.kind, 1.0, ptr(loss), ptr(dlogits), stream())
+        autograd_fn.train_backward(model, ws, dlogits, ps, self.views_g)
+        scale = 1.0
+        if self.world > 1:
+            _dist().all_reduce(self.flat_g)          # the one collective of the step (NCCL over NVLink)
+            scale = 1.0 / self.world
+        g = self.optimizer.param_groups[0]
+        b1, b2 = g["betas"]
+        call("explainn_adam_step", ptr(self.flat_p), ptr(self.flat_g), ptr(self.flat_m), ptr(self.flat_v), self.n,
+             ptr(self.step_t), float(g["lr"]), float(b1), float(b2), float(g["eps"]), scale, stream())
+        self.steps_done += 1
+        return loss
+
+    def sync_optimizer_state(self):
+        for p in self.params:
+            self.optimizer.state[p]["step"] = torch.tensor(float(self.steps_done))
+        for p, gview in zip(self.params, self.views_g):
+            p.grad = gview
+
+
+def _epoch_mean(losses):
+    """Mean of per-step losses exactly as train.py:73-76 accumulates them (python floats)."""
+    if not losses:
+        return float("nan")
+    vals = torch.cat([l.detach().reshape(1).float() for l in losses]).cpu().tolist()   # one sync per epoch
+    total = 0.0
+    for v in vals:
+        total += v
+    return total / len(vals)
+
+
+def train_explainn(train_loader, test_loader, model, device, criterion,
+                   optimizer, num_epochs=100, weights_folder="./",
+                   name_ind=None, verbose=False, trim_weights=False,
+                   checkpoint=1, patience=0):
+    """
+    Function to train the ExplaiNN model (reference: explainn/train/train.py:13-142)
+
+    :param train_loader: pytorch DataLoader, train data
+    :param test_loader: pytorch DataLoader, validation data
+    :param model: ExplaiNN model
+    :param device: current available device ("cuda:0")
+    :param criterion: objective (loss) function to use (e.g. MSELoss)
+    :param optimizer: pytorch Optimizer (e.g. SGD)
+    :param num_epochs: int, number of epochs to train the model
+    :param weights_folder: string, folder where to save checkpoints
+    :param name_ind: string, suffix name of the checkpoints
+    :param verbose: boolean, if False, does not print the progress
+    :param trim_weights: boolean, if True, makes output layer weights non-negative
+    :param checkpoint: int, how often to save checkpoints (e.g. 1 means that the model will be saved after each epoch;
+                       0 that only the best model will be saved)
+    :param patience: int, number of epochs to wait before stopping training if validation loss does not improve;
+                     if 0, this parameter is ignored
+    :return: tuple: trained ExplaiNN model, list of train losses, list of test losses
+    """
+    train_error, test_error = [], []
+    best_model_wts = copy.deepcopy(model.state_dict())
+    best_loss_valid = float('inf')
+    best_epoch = 1
+    fused = FusedTrainer(model, criterion, optimizer) if FusedTrainer.supports(model, criterion, optimizer) else None
+
+    for epoch in range(1, num_epochs + 1):
+        step_losses = []
+        model.train()
+        for seqs, labels in train_loader:
+            x = seqs.to(device, non_blocking=True)
+            labels = labels.to(device, non_blocking=True)
+            if fused is not None:
+                loss = fused.step(x, labels)
+            else:
+                optimizer.zero_grad()
+                outputs = model(x)
+                loss = criterion(outputs, labels)
+                loss.backward()
+                optimizer.step()
+            if trim_weights:        # constrain the output layer weights to be non-negative (train.py:70-71)
+                model.final.weight.data.clamp_(0)
+            step_losses.append(loss)
+        epoch_loss = _epoch_mean(step_losses)
+        train_error.append(epoch_loss)
+
+        val_losses = []
+        with torch.no_grad():
+            model.eval()
+            for seqs, labels in test_loader:
+                x = seqs.to(device, non_blocking=True)
+                y = labels.to(device, non_blocking=True)
+                val_losses.append(criterion(model(x), y))
+        test_loss = _epoch_mean(val_losses)
+        test_error.append(test_loss)
+        if hasattr(model, "check_inputs"):
+            model.check_inputs()
+
+        if verbose:
+            print('Epoch [{}], Current Train Loss: {:.5f}, Current Val Loss: {:.5f}'
+                  .format(epoch, epoch_loss, test_loss))
+
+        if test_loss < best_loss_valid:
+            best_loss_valid = test_loss
+            best_epoch = epoch
+            best_model_wts = copy.deepcopy(model.state_dict())
+
+        if checkpoint:
+            if epoch % checkpoint == 0:
+                model.load_state_dict(best_model_wts)
+                f = f"model_epoch_{epoch}_{name_ind}.pth" if name_ind else f"model_epoch_{epoch}.pth"
+                torch.save(best_model_wts, os.path.join(weights_folder, f))
+
+        if patience:
+            if epoch >= best_epoch + patience:
+                if verbose:
+                    print('Early stopping, Current Epoch {}, Best Epoch: {}, Patience: {}'
+                          .format(epoch, best_epoch, patience))
+                break
+
+    if fused is not None:
+        fused.sync_optimizer_state()
+    model.load_state_dict(best_model_wts)
+    f = f"model_epoch_best_{best_epoch}_{name_ind}.pth" if name_ind else f"model_epoch_best_{best_epoch}.pth"
+    torch.save(best_model_wts, os.path.join(weights_folder, f))
+    return model, train_error, test_error

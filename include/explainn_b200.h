@@ -124,6 +124,76 @@ int explainn_fc_stack_fwd_eval(const float *pooled, long long B, int U, int P, c
 int explainn_linear_fwd(const float *x, long long B, int U, int C, const float *W, const float *bias, float *out,
                         cudaStream_t stream);
 
+/* ==== training ================================================================================================ */
+
+/* ---- input co-occurrence statistics -------------------------------------------------------------------------
+ * M[i][j] = sum_{b,s} x[b,c,s+k] x[b,c',s+k'], i = c*F+k, j = c'*F+k' (int32, (4F,4F), zeroed by the call).
+ * Because the conv input is one-hot, the train-mode BatchNorm1d statistics of the conv output
+ * (explainn/models/networks.py:100) and the dense part of its backward follow from M alone. */
+int explainn_input_cooc_stats(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int F, int *M,
+                              cudaStream_t stream);
+/* Batch mean / biased variance of conv(x)+bias per unit from M; updates running stats like BatchNorm1d in
+ * train mode (momentum, unbiased variance; networks.py:100) when run_mean != NULL, and *num_batches_tracked += 1
+ * when non-NULL.  n_pos = B*S.  Mw (U,4F) = M w_u is kept for the backward. */
+int explainn_bn1_batch_stats(const int *M, const float *w, const float *bias, int U, int F, long long n_pos,
+                             float momentum, float *run_mean, float *run_var, long long *num_batches_tracked,
+                             float *mean, float *var, float *Mw, cudaStream_t stream);
+
+/* ---- FC stack + final linear, train mode --------------------------------------------------------------------
+ * Replaces linears[4..13] + final (networks.py:103-116,147) with BatchNorm batch statistics (running stats
+ * updated in place when the rm/rv pointers are non-NULL) and inverted dropout (p = pdrop, mask derived from
+ * `seed` and the element index, regenerated in the backward).  Saved for the backward: h1 (U,B,100),
+ * mean2/invstd2 (100U), h2 (U,B), mean3/invstd3 (U), unit (B,U).  part2: (U, nchunk, 2, 100) and part3:
+ * (U, nchunk, 2) floats of scratch, nchunk = explainn_fc_nchunk(B).  logits: (B,C). */
+int explainn_fc_nchunk(long long B);
+int explainn_fc_stack_fwd_train(const float *pooled, long long B, int U, int P, int C, const float *W1, const float *b1,
+                                const float *bn2_w, const float *bn2_b, float *bn2_rm, float *bn2_rv, const float *W2,
+                                const float *b2, const float *bn3_w, const float *bn3_b, float *bn3_rm, float *bn3_rv,
+                                float momentum, float eps, float pdrop, unsigned long long seed, const float *Wf,
+                                const float *bf, float *h1, float *part2, float *mean2, float *invstd2, float *h2,
+                                float *part3, float *mean3, float *invstd3, float *unit, float *logits,
+                                cudaStream_t stream);
+
+/* ---- backward of FC stack + final linear (autograd of networks.py:103-116,147; explainn/train/train.py:65) ---
+ * glogits (B,C).  Scratch: gh2 (U,B), pb2 (U,nchunk,3,100), dW1_partials (nchunk,U,100,P).  Outputs: gpool (U,B,P)
+ * = d loss / d pooled, and the parameter gradients (any of db1..dbf may be NULL to skip it).  The gradients of
+ * the biases that feed a train-mode BatchNorm (b1, b2) are written as exact zeros.  Wf == NULL: glogits is the
+ * gradient w.r.t. the unit outputs (B,U) (caller differentiates `model.linears(x)`), dWf/dbf are not written. */
+int explainn_fc_stack_bwd(const float *glogits, long long B, int U, int P, int C, const float *pooled, const float *h1,
+                          const float *h2, const float *unit, const float *W1, const float *bn2_w, const float *bn2_b,
+                          const float *mean2, const float *invstd2, const float *W2, const float *bn3_w,
+                          const float *mean3, const float *invstd3, const float *Wf, float pdrop,
+                          unsigned long long seed, float *gh2, float *pb2, float *dW1_partials, float *gpool,
+                          float *dW1, float *db1, float *dbn2_w, float *dbn2_b, float *dW2, float *db2, float *dbn3_w,
+                          float *dbn3_b, float *dWf, float *dbf, cudaStream_t stream);
+
+/* ---- backward of conv + BN + exp + maxpool (autograd of networks.py:98-102) ----------------------------------
+ * Only the pool-argmax positions carry gradient (sparse scatter); the dense BatchNorm correction comes from
+ * M / Mw.  partial: (nsplit, U, 4F+2) floats of scratch with nsplit = explainn_conv_bwd_nsplit(U).
+ * Outputs dW (U,4,F), dbias (U, exact zeros), dgamma (U), dbeta (U); each may be NULL. */
+int explainn_conv_bwd_nsplit(int U);
+int explainn_conv_pool_bwd(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F,
+                           const float *gpool, const float *pooled, const float *xhat, const unsigned char *idx,
+                           const int *M, const float *Mw, const float *bias, const float *mean, const float *var,
+                           const float *gamma, float eps, float *partial, int nsplit, float *dW, float *dbias,
+                           float *dgamma, float *dbeta, cudaStream_t stream);
+
+/* ---- fused criterion (mean reduction) and its gradient ---------------------------------------------------------
+ * BCEWithLogitsLoss / MSELoss as scripts/train.py:210-219 constructs them (explainn/train/train.py:62).
+ * loss: 1 float; dlogits (B,C) = grad_scale * d loss / d logits (may be NULL). */
+int explainn_loss_fwd_bwd(const float *logits, const float *target, long long B, int C, int kind, float grad_scale,
+                          float *loss, float *dlogits, cudaStream_t stream);
+
+/* ---- fused Adam over one flat buffer ------------------------------------------------------------------------------
+ * torch.optim.Adam with its defaults-compatible options (amsgrad=False, weight_decay=0, maximize=False), the
+ * optimizer scripts/train.py:246-247 builds (explainn/train/train.py:67).  *step (device float) is incremented
+ * first; grad is multiplied by grad_scale (1/world_size after a SUM all-reduce). */
+int explainn_adam_step(float *param, const float *grad, float *exp_avg, float *exp_avg_sq, long long n, float *step,
+                       float lr, float beta1, float beta2, float eps, float grad_scale, cudaStream_t stream);
+
+/* out[i] = sum_{c<k} partials[c*n + i] */
+int explainn_reduce_partials(float *out, const float *partials, long long n, int k, cudaStream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
