@@ -236,10 +236,12 @@ __global__ void __launch_bounds__(FC_THREADS) fc2_train_kernel(
     const float *__restrict__ h1, long long B, int U, const float *__restrict__ part2, int nchunk,
     const float *__restrict__ g2, const float *__restrict__ be2, float *__restrict__ rm2, float *__restrict__ rv2,
     float momentum, float eps, const float *__restrict__ W2, const float *__restrict__ b2, float *__restrict__ mean2,
-    float *__restrict__ invstd2, float pdrop, unsigned long long seed, float *__restrict__ h2, float *__restrict__ part3)
+    float *__restrict__ invstd2, float pdrop, unsigned long long seed0, const unsigned long long *__restrict__ seed_dev,
+    float *__restrict__ h2, float *__restrict__ part3)
 {
     __shared__ float sc[128], sh[128], w2s[128];
     __shared__ float red[8][2];
+    const unsigned long long seed = seed0 + (seed_dev ? *seed_dev * 0xD1B54A32D192ED03ull : 0ull);
     const int u = blockIdx.x, chunk = blockIdx.y;
     const long long b0 = (long long)chunk * BM;
     const int rows = (int)min((long long)BM, B - b0);
@@ -481,10 +483,12 @@ __global__ void __launch_bounds__(FC_THREADS) bwd_fc2_kernel(const float *__rest
                                                              long long B, int U, const float *__restrict__ g2,
                                                              const float *__restrict__ be2, const float *__restrict__ mean2,
                                                              const float *__restrict__ invstd2, const float *__restrict__ W2,
-                                                             float pdrop, unsigned long long seed, float *__restrict__ pb2)
+                                                             float pdrop, unsigned long long seed0,
+                                                             const unsigned long long *__restrict__ seed_dev, float *__restrict__ pb2)
 {
     __shared__ float mu[128], inv[128], ga[128], be[128], w2s[128];
     __shared__ float red[8][3][128];
+    const unsigned long long seed = seed0 + (seed_dev ? *seed_dev * 0xD1B54A32D192ED03ull : 0ull);
     const int u = blockIdx.x, chunk = blockIdx.y, nchunk = gridDim.y;
     const long long b0 = (long long)chunk * BM;
     const int rows = (int)min((long long)BM, B - b0);
@@ -538,8 +542,8 @@ template <int PH>
 __global__ void __launch_bounds__(FC_THREADS) bwd_fc1_kernel(
     const float *__restrict__ h1, const float *__restrict__ gh2, const float *__restrict__ pooled, long long B, int U, int P,
     const float *__restrict__ g2, const float *__restrict__ be2, const float *__restrict__ mean2, const float *__restrict__ invstd2,
-    const float *__restrict__ W1, const float *__restrict__ W2, float pdrop, unsigned long long seed,
-    const float *__restrict__ pb2, float *__restrict__ gpool, float *__restrict__ dW1p, float *__restrict__ dW2,
+    const float *__restrict__ W1, const float *__restrict__ W2, float pdrop, unsigned long long seed0,
+    const unsigned long long *__restrict__ seed_dev, const float *__restrict__ pb2, float *__restrict__ gpool, float *__restrict__ dW1p, float *__restrict__ dW2,
     float *__restrict__ db1, float *__restrict__ db2, float *__restrict__ dg2, float *__restrict__ dbe2)
 {
     constexpr int PQ = 2 * PH;
@@ -548,6 +552,7 @@ __global__ void __launch_bounds__(FC_THREADS) bwd_fc1_kernel(
     float *As = Gs + BM * HS;                       // [BM][PQ]   (BM*HS = 12928 floats: 16-byte aligned)
     float *Wr = As + BM * PQ;                       // [H][PQ]
     __shared__ float mu[128], inv[128], ga[128], be[128], w2s[128], m1s[128], m2s[128];
+    const unsigned long long seed = seed0 + (seed_dev ? *seed_dev * 0xD1B54A32D192ED03ull : 0ull);
     const int u = blockIdx.x, chunk = blockIdx.y, nchunk = gridDim.y;
     const long long b0 = (long long)chunk * BM;
     const int rows = (int)min((long long)BM, B - b0);
@@ -696,8 +701,8 @@ extern "C" int explainn_fc_nchunk(long long B) { return (int)((B + BM - 1) / BM)
 extern "C" int explainn_fc_stack_fwd_train(const float *pooled, long long B, int U, int P, int C, const float *W1, const float *b1,
                                            const float *bn2_w, const float *bn2_b, float *bn2_rm, float *bn2_rv, const float *W2,
                                            const float *b2, const float *bn3_w, const float *bn3_b, float *bn3_rm, float *bn3_rv,
-                                           float momentum, float eps, float pdrop, unsigned long long seed, const float *Wf,
-                                           const float *bf, float *h1, float *part2, float *mean2, float *invstd2, float *h2,
+                                           float momentum, float eps, float pdrop, unsigned long long seed,
+                                           const unsigned long long *seed_dev, const float *Wf, const float *bf, float *h1, float *part2, float *mean2, float *invstd2, float *h2,
                                            float *part3, float *mean3, float *invstd3, float *unit, float *logits,
                                            cudaStream_t stream)
 {
@@ -716,7 +721,7 @@ extern "C" int explainn_fc_stack_fwd_train(const float *pooled, long long B, int
     cudaFuncSetAttribute(fc1_train_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1);
     fc1_train_kernel<<<dim3(U, nchunk), FC_THREADS, smem1, stream>>>(pooled, B, U, P, W1, b1, h1, part2);
     fc2_train_kernel<<<dim3(U, nchunk), FC_THREADS, 0, stream>>>(h1, B, U, part2, nchunk, bn2_w, bn2_b, bn2_rm, bn2_rv, momentum, eps,
-                                                                 W2, b2, mean2, invstd2, pdrop, seed, h2, part3);
+                                                                 W2, b2, mean2, invstd2, pdrop, seed, seed_dev, h2, part3);
     cudaFuncSetAttribute(out_train_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem3);
     out_train_kernel<<<(unsigned)((B + 31) / 32), 256, smem3, stream>>>(h2, B, U, C, part3, nchunk, bn3_w, bn3_b, bn3_rm, bn3_rv,
                                                                         momentum, eps, mean3, invstd3, Wf, bf, unit, logits);
@@ -727,7 +732,7 @@ extern "C" int explainn_fc_stack_bwd(const float *glogits, long long B, int U, i
                                      const float *h2, const float *unit, const float *W1, const float *bn2_w, const float *bn2_b,
                                      const float *mean2, const float *invstd2, const float *W2, const float *bn3_w,
                                      const float *mean3, const float *invstd3, const float *Wf, float pdrop,
-                                     unsigned long long seed, float *gh2, float *pb2, float *dW1_partials, float *gpool,
+                                     unsigned long long seed, const unsigned long long *seed_dev, float *gh2, float *pb2, float *dW1_partials, float *gpool,
                                      float *dW1, float *db1, float *dbn2_w, float *dbn2_b, float *dW2, float *db2, float *dbn3_w,
                                      float *dbn3_b, float *dWf, float *dbf, cudaStream_t stream)
 {
@@ -745,13 +750,13 @@ extern "C" int explainn_fc_stack_bwd(const float *glogits, long long B, int U, i
     }
     cudaFuncSetAttribute(bwd_bn3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bn3);
     bwd_bn3_kernel<<<(U + 7) / 8, 256, smem_bn3, stream>>>(glogits, Wf, unit, h2, B, U, C, bn3_w, mean3, invstd3, gh2, dbn3_w, dbn3_b);
-    bwd_fc2_kernel<<<dim3(U, nchunk), FC_THREADS, 0, stream>>>(h1, gh2, B, U, bn2_w, bn2_b, mean2, invstd2, W2, pdrop, seed, pb2);
+    bwd_fc2_kernel<<<dim3(U, nchunk), FC_THREADS, 0, stream>>>(h1, gh2, B, U, bn2_w, bn2_b, mean2, invstd2, W2, pdrop, seed, seed_dev, pb2);
 #define XB_LAUNCH_BWD_FC1(PHV)                                                                                                      \
     do {                                                                                                                            \
         const size_t sm = bwd_fc1_smem<PHV>();                                                                                      \
         cudaFuncSetAttribute(bwd_fc1_kernel<PHV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);                            \
         bwd_fc1_kernel<PHV><<<dim3(U, nchunk), FC_THREADS, sm, stream>>>(h1, gh2, pooled, B, U, P, bn2_w, bn2_b, mean2, invstd2, W1, \
-                                                                          W2, pdrop, seed, pb2, gpool, dW1_partials, dW2, db1, db2,  \
+                                                                          W2, pdrop, seed, seed_dev, pb2, gpool, dW1_partials, dW2, db1, db2,  \
                                                                           dbn2_w, dbn2_b);                                          \
     } while (0)
     if (P <= 32) XB_LAUNCH_BWD_FC1(16);

@@ -53,7 +53,7 @@ class FusedTrainer:
             return False
         return True
 
-    def __init__(self, model, criterion, optimizer, dropout_seed=None):
+    def __init__(self, model, criterion, optimizer, dropout_seed=None, use_graph=True):
         self.model, self.criterion, self.optimizer = model, criterion, optimizer
         self.kind = self.LOSSES[type(criterion)]
         self.params = list(autograd_fn._params(model))
@@ -89,6 +89,13 @@ class FusedTrainer:
                         "exp_avg_sq": self.flat_v[o:o + n].view_as(p)}
         self.steps_done = int(self.step_t.item())
         self.dropout_seed = dropout_seed
+        # CUDA-graph replay of forward+loss+backward (the step is launch-bound at batch 512, SURVEY 7.3 g)
+        self.use_graph = use_graph
+        self._graph = None
+        self._graph_failed = False
+        self._gx = self._gy = self._gloss = None
+        self._graph_launches = 0
+        self._seed_ctr = torch.zeros(1, dtype=torch.int64, device=dev)
         self.world = 1
         d = _dist()
         if d is not None:
@@ -97,27 +104,65 @@ class FusedTrainer:
     def _still_aliased(self):
         return all(p.data_ptr() == v.data_ptr() for p, v in zip(self.params, self.views_p))
 
-    def step(self, x, y):
-        """One optimisation step (train.py:59-67).  Returns the loss as a 1-element device tensor."""
-        model = self.model
-        if not self._still_aliased():       # somebody re-assigned a parameter: re-adopt it
-            for p, v in zip(self.params, self.views_p):
-                if p.data_ptr() != v.data_ptr():
-                    v.copy_(p.data)
-                    p.data = v
+    def _fwd_bwd(self, x, y, seed, seed_dev=None):
+        """forward + fused loss + backward into the flat gradient buffer; returns the loss tensor."""
         ps = self.views_p
-        seed = None
-        if self.dropout_seed is not None:
-            seed = (self.dropout_seed + 0x9E3779B97F4A7C15 * (self.steps_done + 1)) & 0xFFFFFFFFFFFFFFFF
-        ws = autograd_fn.train_forward(model, x, ps, seed=seed)
+        ws = autograd_fn.train_forward(self.model, x, ps, seed=seed, seed_dev=seed_dev)
         B, C = ws.logits.shape
-        y = y.to(ws.logits.device, dtype=torch.float32).contiguous()
         if tuple(y.shape) != (B, C):
             raise ValueError("labels of shape %s do not match logits %s" % (tuple(y.shape), (B, C)))
         loss = torch.empty(1, dtype=torch.float32, device=ws.logits.device)
         dlogits = torch.empty_like(ws.logits)
         call("explainn_loss_fwd_bwd", ptr(ws.logits), ptr(y), B, C, self.kind, 1.0, ptr(loss), ptr(dlogits), stream())
-        autograd_fn.train_backward(model, ws, dlogits, ps, self.views_g)
+        autograd_fn.train_backward(self.model, ws, dlogits, ps, self.views_g)
+        return loss
+
+    def _capture(self, x, y, seed):
+        """Capture forward+loss+backward for this batch shape.  Capturing executes nothing, so the
+        BatchNorm running statistics are untouched until the first replay."""
+        self._gx = torch.empty_like(x)
+        self._gy = torch.empty_like(y)
+        g = torch.cuda.CUDAGraph()
+        l0 = _cabi.LAUNCHES
+        try:
+            with torch.cuda.graph(g):
+                self._seed_ctr.add_(1)
+                self._gloss = self._fwd_bwd(self._gx, self._gy, seed, self._seed_ctr)
+            self._graph_launches = _cabi.LAUNCHES - l0
+            _cabi.LAUNCHES = l0              # captured, not executed
+        except Exception as e:      # keep training eagerly rather than fail
+            import warnings
+            warnings.warn("explainn_b200: CUDA-graph capture failed (%s); continuing without graphs" % (e,))
+            self._graph_failed = True
+            self._graph = None
+            torch.cuda.synchronize()
+            return
+        self._graph = g
+
+    def step(self, x, y):
+        """One optimisation step (train.py:59-67).  Returns the loss as a 1-element device tensor."""
+        if not self._still_aliased():       # somebody re-assigned a parameter: re-adopt it
+            for p, v in zip(self.params, self.views_p):
+                if p.data_ptr() != v.data_ptr():
+                    v.copy_(p.data)
+                    p.data = v
+            self._graph = None
+        base = self.dropout_seed if self.dropout_seed is not None else (torch.initial_seed() & 0xFFFFFFFFFFFF)
+        seed = (base + 0x9E3779B97F4A7C15 * (self.steps_done + 1)) & 0xFFFFFFFFFFFFFFFF
+        y = y.to(x.device, dtype=torch.float32).contiguous()
+        x = x.contiguous()
+        # the first step runs eagerly (it is the warm-up); the graph is captured once, for the shape of the
+        # second step; batches of any other shape (a short last batch) run eagerly
+        if self.use_graph and not self._graph_failed and self._graph is None and self.steps_done >= 1:
+            self._capture(x, y, base)
+        if self._graph is not None and self._gx.shape == x.shape and self._gx.dtype == x.dtype:
+            self._gx.copy_(x, non_blocking=True)
+            self._gy.copy_(y, non_blocking=True)
+            self._graph.replay()
+            _cabi.LAUNCHES += self._graph_launches
+            loss = self._gloss.clone()
+        else:
+            loss = self._fwd_bwd(x, y, seed)
         scale = 1.0
         if self.world > 1:
             _dist().all_reduce(self.flat_g)          # the one collective of the step (NCCL over NVLink)
