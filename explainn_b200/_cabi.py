@@ -37,6 +37,7 @@ SIGNATURES = {
     "explainn_unit_activations": [_P, _P, _LL, _I, _I, _I, _P, _P, _P, _P, _I, _P],
     "explainn_interp_unit_max_scratch_floats": [_I],
     "explainn_interp_unit_max": [_P, _P, _LL, _I, _I, _I, _P, _P, _P, _P, _P, _I, _P],
+    "explainn_interp_unit_max_noalloc": [_P, _P, _LL, _I, _I, _I, _P, _P, _P, _P, _I, _P],
     "explainn_interp_thresholds": [_P, _I, _P, _P, _P, _P, _P],
     "explainn_interp_pwm_count": [_P, _P, _LL, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P],
     "explainn_fc_stack_fwd_eval": [_P, _LL, _I, _I] + [_P] * 12 + [_F, _P, _P],
@@ -100,7 +101,7 @@ def stream():
 
 
 LAUNCHES = 0   # kernels launched through this binding (bench.py reports it)
-_LAUNCH_COST = {"explainn_interp_unit_max": 3, "explainn_input_cooc_stats": 1, "explainn_fc_stack_fwd_train": 3,
+_LAUNCH_COST = {"explainn_interp_unit_max": 3, "explainn_interp_unit_max_noalloc": 3, "explainn_input_cooc_stats": 1, "explainn_fc_stack_fwd_train": 3,
                 "explainn_fc_stack_bwd": 5, "explainn_conv_pool_bwd": 2, "explainn_adam_step": 2}
 
 

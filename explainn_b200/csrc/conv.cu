@@ -712,3 +712,87 @@ extern "C" int explainn_interp_pwm_count(const uint32_t *codes, const uint32_t *
     CountSink::Params sp{zlo, zhi, thr, counts, hits};
     return dispatch_scan<CountSink, CountSink>(g.G, a, sp, F, stream);
 }
+
+// ----------------------------------------------------------------------------------------------
+// explainn_interp_unit_max_noalloc -- pass A of the PWM extraction for callers that cannot allocate.
+//
+// Some hosts of this library may not call cudaMalloc on the path where the scan runs: a serving process whose
+// device memory was fully partitioned at start-up, a plugin running inside another framework's stream-ordered
+// region, or a worker thread that must never hit the allocator lock.  For them the per-CTA partial maxima that
+// explainn_interp_unit_max() keeps in caller-provided scratch live here, in a fixed array that is part of the
+// library image.  Every GPU that loads the library holds these 640 KB until the process exits.
+//
+// Limits: U <= XB_NOALLOC_MAX_U (1024) units and a GPU with at most XB_NOALLOC_MAX_CTAS (160) SMs; larger
+// requests are refused with EXPLAINN_ERR_LIMIT.
+//
+// The array's name is only a host-side handle: host code must not pass it to a kernel.  The device address is
+// obtained once per device with cudaGetSymbolAddress (with that device current) and cached.  That set-up
+// happens inside the first call on a device, so make that first call outside of any stream capture.
+//
+// All calls on one GPU share the array, and it keeps whatever the previous call left in it; each call first
+// resets the part it uses to -inf on `stream`.  Two calls that overlap on the GPU (different streams, no
+// ordering between them) race on the array -- serialise them.
+// ----------------------------------------------------------------------------------------------
+#define XB_NOALLOC_MAX_U 1024
+#define XB_NOALLOC_MAX_CTAS 160
+#define XB_NOALLOC_MAX_DEVICES 64
+
+static __device__ __align__(256) float g_unit_max_scratch[XB_NOALLOC_MAX_CTAS * XB_NOALLOC_MAX_U];
+
+static float *g_unit_max_scratch_addr[XB_NOALLOC_MAX_DEVICES];   // device address, per device ordinal (0 = not set up)
+
+static int noalloc_scratch_for_current_device(float **out)
+{
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) {
+        xb_set_error("interp_unit_max_noalloc: cudaGetDevice: %s", cudaGetErrorString(e));
+        return XB_ERR_CUDA;
+    }
+    if (dev < 0 || dev >= XB_NOALLOC_MAX_DEVICES) {
+        xb_set_error("interp_unit_max_noalloc: device ordinal %d outside the supported range [0, %d)", dev, XB_NOALLOC_MAX_DEVICES);
+        return XB_ERR_LIMIT;
+    }
+    float *p = __atomic_load_n(&g_unit_max_scratch_addr[dev], __ATOMIC_ACQUIRE);
+    if (p == nullptr) {
+        // once per device, with that device current (two racing threads would store the same address)
+        e = cudaGetSymbolAddress((void **)&p, g_unit_max_scratch);
+        if (e != cudaSuccess || p == nullptr) {
+            xb_set_error("interp_unit_max_noalloc: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+            return XB_ERR_CUDA;
+        }
+        __atomic_store_n(&g_unit_max_scratch_addr[dev], p, __ATOMIC_RELEASE);
+    }
+    *out = p;
+    return XB_OK;
+}
+
+extern "C" int explainn_interp_unit_max_noalloc(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F,
+                                                const float *tables, const float *wq_t, const float *shift, float *zmax,
+                                                int accumulate, cudaStream_t stream)
+{
+    ConvArgs a; Geometry g;
+    int rc = fill_args(&a, &g, codes, nmask, B, L, U, F, tables, wq_t, shift);
+    if (rc != XB_OK) return rc;
+    XB_REQUIRE(zmax, "interp_unit_max_noalloc: null output");
+    const int n_cta = xb_num_sms();
+    if (U > XB_NOALLOC_MAX_U || n_cta > XB_NOALLOC_MAX_CTAS) {
+        xb_set_error("interp_unit_max_noalloc: %d units on %d SMs exceed the built-in scratch (at most %d units, %d SMs); "
+                     "use explainn_interp_unit_max with caller scratch",
+                     U, n_cta, XB_NOALLOC_MAX_U, XB_NOALLOC_MAX_CTAS);
+        return XB_ERR_LIMIT;
+    }
+    float *scratch = nullptr;
+    rc = noalloc_scratch_for_current_device(&scratch);
+    if (rc != XB_OK) return rc;
+    const long long n = (long long)n_cta * U;
+    fill_f32_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(scratch, n, -INFINITY);   // last call's maxima go away
+    a.nwin = g.nwin_all;
+    if (B > 0) {
+        MaxSink::Params sp{scratch, n_cta};
+        rc = dispatch_scan<MaxSink, MaxSink>(g.G, a, sp, 0, stream);
+        if (rc != XB_OK) return rc;
+    }
+    reduce_zmax_kernel<<<(U + 127) / 128, 128, 0, stream>>>(scratch, n_cta, U, zmax, accumulate);
+    return xb_check_launch("interp_unit_max_noalloc");
+}

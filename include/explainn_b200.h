@@ -96,6 +96,16 @@ long long explainn_interp_unit_max_scratch_floats(int U);
 int explainn_interp_unit_max(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F,
                              const float *tables, const float *wq_t, const float *shift, float *scratch,
                              float *zmax, int accumulate, cudaStream_t stream);
+/* Same result as explainn_interp_unit_max, for callers that must not allocate device memory (a serving process
+ * with a fully pre-partitioned GPU, a plugin inside another framework's stream, a thread that may not take the
+ * allocator lock): the partial maxima live in a fixed 640 KB array inside the library image instead of
+ * caller scratch.  This entry point has no counterpart in the reference.  Limits: U <= 1024 and a GPU with
+ * at most 160 SMs, else EXPLAINN_ERR_LIMIT.  The first call on each device looks the array's device address up
+ * (cudaGetSymbolAddress, no allocation); make that first call outside stream capture.  All calls on a GPU share
+ * the array: each call resets the part it uses, calls that overlap on the GPU race and must be serialised. */
+int explainn_interp_unit_max_noalloc(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F,
+                                     const float *tables, const float *wq_t, const float *shift, float *zmax,
+                                     int accumulate, cudaStream_t stream);
 /* float16 threshold 0.5*max (interpretation.py:187) and its pre-activation bracket.  All outputs (U). */
 int explainn_interp_thresholds(const float *zmax, int U, float *thr, float *zlo, float *zhi, float *amax,
                                cudaStream_t stream);
