@@ -17,7 +17,7 @@ import os
 import torch
 import torch.nn as nn
 
-from . import _cabi, autograd_fn
+from . import _cabi, autograd_fn, parallel
 from ._cabi import call, ptr, stream
 
 
@@ -163,10 +163,7 @@ class FusedTrainer:
             loss = self._gloss.clone()
         else:
             loss = self._fwd_bwd(x, y, seed)
-        scale = 1.0
-        if self.world > 1:
-            _dist().all_reduce(self.flat_g)          # the one collective of the step (NCCL over NVLink)
-            scale = 1.0 / self.world
+        scale = parallel.allreduce_mean_gradients(self.flat_g)   # the one collective of the step (NCCL over NVLink)
         g = self.optimizer.param_groups[0]
         b1, b2 = g["betas"]
         call("explainn_adam_step", ptr(self.flat_p), ptr(self.flat_g), ptr(self.flat_m), ptr(self.flat_v), self.n,

@@ -109,7 +109,9 @@ def test_two_adam_steps_vs_reference(name, fused):
             # 1e-9 gradient noise), ours stay put; the batch mean that feeds running_mean shifts accordingly
             _close(got, ref, 2e-3, k)
         elif "running_var" in k:
-            _close(got, ref, 1e-4, k)
+            # same cause: BN-1's beta (zero true gradient) random-walks by +-lr in the reference, which scales a
+            # unit's activations by exp(+-1e-3) and the downstream batch variance by ~(1 +- 2e-3)
+            _close(got, ref, 2e-3, k)
         else:
             upd_ref = ref - sd0[k].numpy()
             upd = got - sd0[k].numpy()
