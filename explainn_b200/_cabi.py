@@ -49,7 +49,8 @@ SIGNATURES = {
     "explainn_fc_stack_bwd": [_P, _LL, _I, _I, _I] + [_P] * 14 + [_F, _ULL, _P] + [_P] * 14 + [_P],
     "explainn_conv_bwd_nsplit": [_I],
     "explainn_conv_pool_bwd": [_P, _P, _LL, _I, _I, _I] + [_P] * 10 + [_F, _P, _I] + [_P] * 4 + [_P],
-    "explainn_loss_fwd_bwd": [_P, _P, _LL, _I, _I, _F, _P, _P, _P],
+    "explainn_loss_scratch_bytes": [],
+    "explainn_loss_fwd_bwd": [_P, _P, _LL, _I, _I, _F, _P, _P, _P, _P],
     "explainn_adam_step": [_P, _P, _P, _P, _LL, _P, _F, _F, _F, _F, _F, _P],
     "explainn_reduce_partials": [_P, _P, _LL, _I, _P],
 }
@@ -58,6 +59,7 @@ _RESTYPES = {
     "explainn_conv_tables_floats": _LL,
     "explainn_conv_wq_floats": _LL,
     "explainn_interp_unit_max_scratch_floats": _LL,
+    "explainn_loss_scratch_bytes": _LL,
 }
 
 
@@ -102,7 +104,7 @@ def stream():
 
 LAUNCHES = 0   # kernels launched through this binding (bench.py reports it)
 _LAUNCH_COST = {"explainn_interp_unit_max": 3, "explainn_interp_unit_max_noalloc": 3, "explainn_input_cooc_stats": 1, "explainn_fc_stack_fwd_train": 3,
-                "explainn_fc_stack_bwd": 5, "explainn_conv_pool_bwd": 2, "explainn_adam_step": 2}
+                "explainn_fc_stack_bwd": 6, "explainn_conv_pool_bwd": 2, "explainn_adam_step": 2}
 
 
 def call(name, *args):

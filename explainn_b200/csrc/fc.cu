@@ -12,6 +12,7 @@
 // and the pooled values by conflict-free scalar loads.
 #include "common.cuh"
 #include "../../include/explainn_b200.h"
+#include <algorithm>
 
 namespace {
 
@@ -311,6 +312,8 @@ __global__ void __launch_bounds__(FC_THREADS) fc2_train_kernel(
 }
 
 // BatchNorm-3 (batch stats) -> ReLU -> unit outputs (B,U) -> final Linear -> logits (B,C)
+// grid ceil(B/8): 8 sequences per CTA; warp w owns row w, lanes run over the classes.
+constexpr int OT_ROWS = 8;
 __global__ void __launch_bounds__(256) out_train_kernel(const float *__restrict__ h2, long long B, int U, int C,
                                                         const float *__restrict__ part3, int nchunk,
                                                         const float *__restrict__ g3, const float *__restrict__ be3,
@@ -319,11 +322,10 @@ __global__ void __launch_bounds__(256) out_train_kernel(const float *__restrict_
                                                         const float *__restrict__ Wf, const float *__restrict__ bf,
                                                         float *__restrict__ unit, float *__restrict__ logits)
 {
-    extern __shared__ float xs[];   // [32][U+1] then sc3[U], sh3[U]
-    const int Up = U + 1;
-    float *sc3 = xs + 32 * Up, *sh3 = sc3 + U;
-    const long long b0 = (long long)blockIdx.x * 32;
-    const int rows = (int)min(32LL, B - b0);
+    extern __shared__ float xs[];   // [8][U] then sc3[U], sh3[U]
+    float *sc3 = xs + OT_ROWS * U, *sh3 = sc3 + U;
+    const long long b0 = (long long)blockIdx.x * OT_ROWS;
+    const int rows = (int)min((long long)OT_ROWS, B - b0);
     for (int u = threadIdx.x; u < U; u += blockDim.x) {
         double sm = 0.0, sq = 0.0;
         for (int k = 0; k < nchunk; ++k) {
@@ -348,27 +350,30 @@ __global__ void __launch_bounds__(256) out_train_kernel(const float *__restrict_
         sh3[u] = be3[u] - (float)mean * a;
     }
     __syncthreads();
-    for (int i = threadIdx.x; i < 32 * U; i += blockDim.x) {
-        const int u = i >> 5, r = i & 31;
-        float v = 0.f;
-        if (r < rows) {
-            v = fmaxf(fmaf(h2[(size_t)u * B + b0 + r], sc3[u], sh3[u]), 0.f);
-            unit[(b0 + r) * U + u] = v;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (warp < rows) {
+        for (int u = lane; u < U; u += 32) {
+            const float v = fmaxf(fmaf(h2[(size_t)u * B + b0 + warp], sc3[u], sh3[u]), 0.f);
+            unit[(b0 + warp) * U + u] = v;
+            xs[warp * U + u] = v;
         }
-        xs[r * Up + u] = v;
     }
     __syncthreads();
-    const int r = threadIdx.x & 31;
-    for (int c = threadIdx.x >> 5; c < C; c += 8) {
-        const float *w = Wf + (size_t)c * U;
-        float a0 = 0.f, a1 = 0.f;
-        int k = 0;
-        for (; k + 1 < U; k += 2) {
-            a0 = fmaf(xs[r * Up + k], __ldg(w + k), a0);
-            a1 = fmaf(xs[r * Up + k + 1], __ldg(w + k + 1), a1);
+    if (warp < rows) {
+        const float *xr = xs + warp * U;
+        for (int c = lane; c < C; c += 32) {
+            const float *w = Wf + (size_t)c * U;
+            float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+            int k = 0;
+            for (; k + 3 < U; k += 4) {
+                a0 = fmaf(xr[k], __ldg(w + k), a0);
+                a1 = fmaf(xr[k + 1], __ldg(w + k + 1), a1);
+                a2 = fmaf(xr[k + 2], __ldg(w + k + 2), a2);
+                a3 = fmaf(xr[k + 3], __ldg(w + k + 3), a3);
+            }
+            for (; k < U; ++k) a0 = fmaf(xr[k], __ldg(w + k), a0);
+            logits[(b0 + warp) * C + c] = ((a0 + a1) + (a2 + a3)) + bf[c];
         }
-        if (k < U) a0 = fmaf(xs[r * Up + k], __ldg(w + k), a0);
-        if (r < rows) logits[(b0 + r) * C + c] = (a0 + a1) + bf[c];
     }
 }
 
@@ -376,7 +381,9 @@ __global__ void __launch_bounds__(256) out_train_kernel(const float *__restrict_
 // Backward
 // ================================================================================================
 
-// dWf[c][u] = sum_b gl[b][c] * unit[b][u] ; dbf[c] = sum_b gl[b][c].   grid (ceil(U/32), ceil(C/8))
+// dWf[c][u] += sum_{b in slice} gl[b][c] * unit[b][u] ; dbf[c] += sum_b gl[b][c].
+// grid (ceil(U/32), ceil(C/8), nsplit); outputs are zeroed by the host wrapper and accumulated with atomics
+// (nsplit partial sums per element).
 __global__ void __launch_bounds__(256) bwd_final_linear_kernel(const float *__restrict__ gl, const float *__restrict__ unit,
                                                                long long B, int U, int C, float *__restrict__ dWf,
                                                                float *__restrict__ dbf)
@@ -384,84 +391,80 @@ __global__ void __launch_bounds__(256) bwd_final_linear_kernel(const float *__re
     const int lane = threadIdx.x & 31, cc = threadIdx.x >> 5;
     const int u = blockIdx.x * 32 + lane, c = blockIdx.y * 8 + cc;
     if (c >= C) return;
+    const long long per = (B + gridDim.z - 1) / gridDim.z;
+    const long long bs = per * blockIdx.z, be = min(B, bs + per);
     const bool uv = u < U;
-    float a0 = 0.f, a1 = 0.f, sg = 0.f;
-    long long b = 0;
-    for (; b + 1 < B; b += 2) {
-        const float g0 = __ldg(gl + b * C + c), g1 = __ldg(gl + (b + 1) * C + c);
-        sg += g0 + g1;
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f, sg = 0.f;
+    long long b = bs;
+    for (; b + 3 < be; b += 4) {
+        const float g0 = __ldg(gl + b * C + c), g1 = __ldg(gl + (b + 1) * C + c), g2 = __ldg(gl + (b + 2) * C + c),
+                    g3 = __ldg(gl + (b + 3) * C + c);
+        sg += (g0 + g1) + (g2 + g3);
         if (uv) {
             a0 = fmaf(g0, unit[b * U + u], a0);
             a1 = fmaf(g1, unit[(b + 1) * U + u], a1);
+            a2 = fmaf(g2, unit[(b + 2) * U + u], a2);
+            a3 = fmaf(g3, unit[(b + 3) * U + u], a3);
         }
     }
-    if (b < B) {
+    for (; b < be; ++b) {
         const float g0 = __ldg(gl + b * C + c);
         sg += g0;
         if (uv) a0 = fmaf(g0, unit[b * U + u], a0);
     }
-    if (uv && dWf) dWf[(size_t)c * U + u] = a0 + a1;
-    if (dbf && blockIdx.x == 0 && lane == 0) dbf[c] = sg;
+    if (uv && dWf) atomicAdd(&dWf[(size_t)c * U + u], (a0 + a1) + (a2 + a3));
+    if (dbf && blockIdx.x == 0 && lane == 0) atomicAdd(&dbf[c], sg);
 }
 
-// gunit = gl . Wf -> ReLU-3 mask -> BatchNorm-3 backward -> gh2 (U,B), dgamma3, dbeta3.  8 units per block.
-__global__ void __launch_bounds__(256) bwd_bn3_kernel(const float *__restrict__ gl, const float *__restrict__ Wf,
-                                                      const float *__restrict__ unit, const float *__restrict__ h2,
-                                                      long long B, int U, int C, const float *__restrict__ g3,
-                                                      const float *__restrict__ mean3, const float *__restrict__ invstd3,
-                                                      float *__restrict__ gh2, float *__restrict__ dg3, float *__restrict__ db3)
+// gz3[b][u] = (unit[b][u] > 0) * sum_c gl[b][c] * Wf[c][u]     (ReLU-3 mask applied; (B,U) layout)
+// grid ceil(B/8); warp = one sequence, lanes run over the units.  Wf == NULL: gl already is d/d unit.
+__global__ void __launch_bounds__(256) bwd_gunit_kernel(const float *__restrict__ gl, const float *__restrict__ Wf,
+                                                        const float *__restrict__ unit, long long B, int U, int C,
+                                                        float *__restrict__ gz)
 {
-    extern __shared__ float sm[];
-    const int Cp = C + 1;
-    float *Wfs = sm;                 // [8][C]
-    float *gls = Wfs + 8 * C;        // [64][C+1]
-    float *gz = gls + 64 * Cp;       // [8][B]
-    const int u0 = blockIdx.x * 8;
-    if (Wf == nullptr) {
-        // upstream gradient already refers to the unit outputs: gl is (B,U)
-        for (long long i = threadIdx.x; i < 8 * B; i += blockDim.x) {
-            const int uu = (int)(i / B);
-            const long long b = i - (long long)uu * B;
-            const int u = u0 + uu;
-            gz[i] = (u < U && unit[b * U + u] > 0.f) ? gl[b * U + u] : 0.f;
-        }
-    }
-    for (int i = threadIdx.x; Wf != nullptr && i < 8 * C; i += blockDim.x) {
-        const int uu = i / C, c = i - uu * C;
-        Wfs[i] = u0 + uu < U ? Wf[(size_t)c * U + u0 + uu] : 0.f;
-    }
-    for (long long r0 = 0; Wf != nullptr && r0 < B; r0 += 64) {
-        const int rows = (int)min(64LL, B - r0);
-        __syncthreads();
-        for (int i = threadIdx.x; i < rows * C; i += blockDim.x) {
-            const int r = i / C, c = i - r * C;
-            gls[r * Cp + c] = gl[(r0 + r) * C + c];
-        }
-        __syncthreads();
-        const int r = threadIdx.x & 63, uq = threadIdx.x >> 6;
-        if (r < rows) {
-            float a0 = 0.f, a1 = 0.f;
-            const float *w0 = Wfs + (2 * uq) * C, *w1 = w0 + C;
-            for (int c = 0; c < C; ++c) {
-                const float g = gls[r * Cp + c];
-                a0 = fmaf(g, w0[c], a0);
-                a1 = fmaf(g, w1[c], a1);
-            }
-            const int ua = u0 + 2 * uq, ub = ua + 1;
-            gz[(size_t)(2 * uq) * B + r0 + r] = (ua < U && unit[(r0 + r) * U + ua] > 0.f) ? a0 : 0.f;
-            gz[(size_t)(2 * uq + 1) * B + r0 + r] = (ub < U && unit[(r0 + r) * U + ub] > 0.f) ? a1 : 0.f;
-        }
-    }
-    __syncthreads();
+    extern __shared__ float gls[];   // [8][C]
+    const long long b0 = (long long)blockIdx.x * 8;
+    const int rows = (int)min(8LL, B - b0);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int u = u0 + warp;
+    if (Wf != nullptr) {
+        for (int i = threadIdx.x; i < rows * C; i += blockDim.x) gls[i] = gl[b0 * C + i];
+        __syncthreads();
+    }
+    if (warp >= rows) return;
+    const long long b = b0 + warp;
+    for (int u = lane; u < U; u += 32) {
+        float g;
+        if (Wf != nullptr) {
+            const float *gr = gls + warp * C;
+            float a0 = 0.f, a1 = 0.f;
+            int c = 0;
+            for (; c + 1 < C; c += 2) {
+                a0 = fmaf(gr[c], __ldg(Wf + (size_t)c * U + u), a0);
+                a1 = fmaf(gr[c + 1], __ldg(Wf + (size_t)(c + 1) * U + u), a1);
+            }
+            if (c < C) a0 = fmaf(gr[c], __ldg(Wf + (size_t)c * U + u), a0);
+            g = a0 + a1;
+        } else {
+            g = gl[b * U + u];
+        }
+        gz[b * U + u] = unit[b * U + u] > 0.f ? g : 0.f;
+    }
+}
+
+// BatchNorm-3 backward per unit: sums over the batch, then gh2 (U,B), dgamma3, dbeta3.  One warp per unit.
+__global__ void __launch_bounds__(256) bwd_bn3_kernel(const float *__restrict__ gz, const float *__restrict__ h2, long long B,
+                                                      int U, const float *__restrict__ g3, const float *__restrict__ mean3,
+                                                      const float *__restrict__ invstd3, float *__restrict__ gh2,
+                                                      float *__restrict__ dg3, float *__restrict__ db3)
+{
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int u = blockIdx.x * 8 + warp;
     if (u >= U) return;
     const float mean = mean3[u], inv = invstd3[u];
-    const float *gzu = gz + (size_t)warp * B;
     const float *h2u = h2 + (size_t)u * B;
     float s1 = 0.f, s2 = 0.f;
     for (long long b = lane; b < B; b += 32) {
-        const float g = gzu[b], xh = (h2u[b] - mean) * inv;
+        const float g = gz[b * U + u], xh = (h2u[b] - mean) * inv;
         s1 += g;
         s2 = fmaf(g, xh, s2);
     }
@@ -474,7 +477,7 @@ __global__ void __launch_bounds__(256) bwd_bn3_kernel(const float *__restrict__ 
     const float m1 = s1 / (float)B, m2 = s2 / (float)B, k = g3[u] * inv;
     for (long long b = lane; b < B; b += 32) {
         const float xh = (h2u[b] - mean) * inv;
-        gh2[(size_t)u * B + b] = k * (gzu[b] - m1 - xh * m2);
+        gh2[(size_t)u * B + b] = k * (gz[b * U + u] - m1 - xh * m2);
     }
 }
 
@@ -713,7 +716,7 @@ extern "C" int explainn_fc_stack_fwd_train(const float *pooled, long long B, int
     XB_REQUIRE(pdrop >= 0.f && pdrop < 1.f, "fc_stack_fwd_train: dropout probability %f", pdrop);
     const int nchunk = (int)((B + BM - 1) / BM);
     const size_t smem1 = FcSmem::bytes(P) + (size_t)BM * HS * 4;
-    const size_t smem3 = ((size_t)32 * (U + 1) + 2 * (size_t)U) * 4;
+    const size_t smem3 = ((size_t)OT_ROWS * U + 2 * (size_t)U) * 4;
     if (smem1 > 220 * 1024 || smem3 > 220 * 1024) {
         xb_set_error("fc_stack_fwd_train: shared memory need (%zu / %zu bytes) exceeds the SM", smem1, smem3);
         return XB_ERR_UNSUPPORTED;
@@ -723,7 +726,7 @@ extern "C" int explainn_fc_stack_fwd_train(const float *pooled, long long B, int
     fc2_train_kernel<<<dim3(U, nchunk), FC_THREADS, 0, stream>>>(h1, B, U, part2, nchunk, bn2_w, bn2_b, bn2_rm, bn2_rv, momentum, eps,
                                                                  W2, b2, mean2, invstd2, pdrop, seed, seed_dev, h2, part3);
     cudaFuncSetAttribute(out_train_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem3);
-    out_train_kernel<<<(unsigned)((B + 31) / 32), 256, smem3, stream>>>(h2, B, U, C, part3, nchunk, bn3_w, bn3_b, bn3_rm, bn3_rv,
+    out_train_kernel<<<(unsigned)((B + OT_ROWS - 1) / OT_ROWS), 256, smem3, stream>>>(h2, B, U, C, part3, nchunk, bn3_w, bn3_b, bn3_rm, bn3_rv,
                                                                         momentum, eps, mean3, invstd3, Wf, bf, unit, logits);
     return xb_check_launch("fc_stack_fwd_train");
 }
@@ -742,14 +745,23 @@ extern "C" int explainn_fc_stack_bwd(const float *glogits, long long B, int U, i
     XB_REQUIRE(B >= 2 && U >= 1 && P >= 1 && C >= 1, "fc_stack_bwd: bad sizes");
     const int nchunk = (int)((B + BM - 1) / BM);
     // Wf == NULL: glogits is the gradient w.r.t. the unit outputs (B,U) and the final layer is skipped
-    if (Wf) bwd_final_linear_kernel<<<dim3((U + 31) / 32, (C + 7) / 8), 256, 0, stream>>>(glogits, unit, B, U, C, dWf, dbf);
-    const size_t smem_bn3 = ((size_t)8 * C + (size_t)64 * (C + 1) + (size_t)8 * B) * 4;
-    if (smem_bn3 > 220 * 1024) {
-        xb_set_error("fc_stack_bwd: batch %lld x classes %d needs %zu bytes of shared memory (limit 220 KB)", B, C, smem_bn3);
+    if (Wf) {
+        if (dWf) cudaMemsetAsync(dWf, 0, (size_t)C * U * sizeof(float), stream);
+        if (dbf) cudaMemsetAsync(dbf, 0, (size_t)C * sizeof(float), stream);
+        const int nsb = (int)std::min<long long>(8, (B + 63) / 64);
+        bwd_final_linear_kernel<<<dim3((U + 31) / 32, (C + 7) / 8, nsb), 256, 0, stream>>>(glogits, unit, B, U, C, dWf, dbf);
+    }
+    // gz3 (B,U) lives in the head of the gpool buffer (U*B*P floats >= B*U); it is consumed by bwd_bn3_kernel
+    // before bwd_fc1_kernel overwrites gpool
+    float *gz3 = gpool;
+    const size_t smem_gu = (size_t)8 * C * 4;
+    if (smem_gu > 200 * 1024) {
+        xb_set_error("fc_stack_bwd: %d classes need %zu bytes of shared memory", C, smem_gu);
         return XB_ERR_LIMIT;
     }
-    cudaFuncSetAttribute(bwd_bn3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bn3);
-    bwd_bn3_kernel<<<(U + 7) / 8, 256, smem_bn3, stream>>>(glogits, Wf, unit, h2, B, U, C, bn3_w, mean3, invstd3, gh2, dbn3_w, dbn3_b);
+    cudaFuncSetAttribute(bwd_gunit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_gu);
+    bwd_gunit_kernel<<<(unsigned)((B + 7) / 8), 256, smem_gu, stream>>>(glogits, Wf, unit, B, U, C, gz3);
+    bwd_bn3_kernel<<<(U + 7) / 8, 256, 0, stream>>>(gz3, h2, B, U, bn3_w, mean3, invstd3, gh2, dbn3_w, dbn3_b);
     bwd_fc2_kernel<<<dim3(U, nchunk), FC_THREADS, 0, stream>>>(h1, gh2, B, U, bn2_w, bn2_b, mean2, invstd2, W2, pdrop, seed, seed_dev, pb2);
 #define XB_LAUNCH_BWD_FC1(PHV)                                                                                                      \
     do {                                                                                                                            \

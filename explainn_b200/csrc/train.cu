@@ -16,6 +16,7 @@
 // positions plus these tables.
 #include "common.cuh"
 #include "../../include/explainn_b200.h"
+#include <algorithm>
 
 namespace {
 
@@ -117,16 +118,19 @@ __global__ void __launch_bounds__(128) bn1_stats_kernel(const int *__restrict__ 
 // ------------------------------------------------------------------------------------------------
 // Sparse part of the conv backward: only pool-argmax positions carry gradient.
 // grid (U, nsplit); 4 warps; lanes walk the (b,p) entries of one unit, 32 at a time, with lane-private
-// accumulators acc[4F][lane] in shared memory.
+// accumulators acc[k][c][lane] in shared memory (conflict-free, no atomics).  FT > 0: filter size known at
+// compile time (taps fully unrolled, all loads of an entry issued before its stores); FT == 0: any F.
 // ------------------------------------------------------------------------------------------------
 constexpr int BW_WARPS = 4;
 
+template <int FT>
 __global__ void __launch_bounds__(BW_WARPS * 32) conv_bwd_sparse_kernel(
-    const uint32_t *__restrict__ codes, const uint32_t *__restrict__ nmask, long long B, int L, int F, int P, int wc, int wm,
+    const uint32_t *__restrict__ codes, const uint32_t *__restrict__ nmask, long long B, int L, int Frt, int P, int wc, int wm,
     const float *__restrict__ gpool, const float *__restrict__ pooled, const float *__restrict__ xhat,
     const unsigned char *__restrict__ idx, float *__restrict__ partial /* (nsplit, U, 4F+2) */, int U)
 {
-    extern __shared__ float acc[];   // [BW_WARPS][4F][32] then [BW_WARPS][4F+2] for the block reduce
+    extern __shared__ float acc[];   // [BW_WARPS][F][4][32] then [BW_WARPS][4F+2] for the block reduce
+    const int F = FT > 0 ? FT : Frt;
     const int u = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31, W = 4 * F;
     float *my = acc + (size_t)warp * W * 32;
     for (int i = lane; i < W * 32; i += 32) my[i] = 0.0f;
@@ -136,35 +140,56 @@ __global__ void __launch_bounds__(BW_WARPS * 32) conv_bwd_sparse_kernel(
     const long long e0 = per * blockIdx.y, e1 = min(n, e0 + per);
     const size_t ubase = (size_t)u * n;
     float dbeta = 0.f, dgamma = 0.f;
+    float *mine = my + lane;
     for (long long e = e0 + warp * 32 + lane; e < e1; e += BW_WARPS * 32) {
-        const long long b = e / P;
-        const int p = (int)(e - b * P);
+        const int b = (int)e / P;                    // host wrapper guarantees B*P < 2^31
+        const int p = (int)e - b * P;
         const float gz = gpool[ubase + e] * pooled[ubase + e];
         const float xh = xhat[ubase + e];
         const int s = p * XB_POOL + idx[ubase + e];
         dbeta += gz;
         dgamma = fmaf(gz, xh, dgamma);
-        const uint32_t *cw = codes + b * wc;
-        const uint32_t *mw = nmask + b * wm;
+        const uint32_t *cw = codes + (size_t)b * wc;
+        const uint32_t *mw = nmask + (size_t)b * wm;
         const int wi = s >> 4, sh = 2 * (s & 15);
         const uint32_t w0 = cw[wi], w1 = wi + 1 < wc ? cw[wi + 1] : 0u, w2 = wi + 2 < wc ? cw[wi + 2] : 0u;
         const uint32_t A0 = __funnelshift_r(w0, w1, sh), A1 = __funnelshift_r(w1, w2, sh);
         const int mi = s >> 5;
         const uint32_t m0 = mw[mi], m1 = mi + 1 < wm ? mw[mi + 1] : 0u;
-        const uint32_t MW = __funnelshift_r(m0, m1, s & 31);
-        for (int k = 0; k < F; ++k) {
-            const uint32_t c = ((k < 16 ? A0 : A1) >> ((2 * k) & 31)) & 3u;
-            if (!((MW >> k) & 1u)) my[(c * F + k) * 32 + lane] += gz;
+        const uint32_t MW = __funnelshift_r(m0, m1, s & 31) & (F >= 32 ? 0xFFFFFFFFu : ((1u << F) - 1u));
+        if (FT > 0) {
+            // offsets of the 19 (k, code) cells; k*128 is a compile-time part of the address
+            float v[FT > 0 ? FT : 1];
+            uint32_t off[FT > 0 ? FT : 1];
+#pragma unroll
+            for (int k = 0; k < FT; ++k) {
+                const uint32_t c = ((k < 16 ? A0 : A1) >> ((2 * k) & 31)) & 3u;
+                off[k] = k * 128 + c * 32;
+            }
+#pragma unroll
+            for (int k = 0; k < FT; ++k) v[k] = mine[off[k]];
+            if (MW == 0u) {
+#pragma unroll
+                for (int k = 0; k < FT; ++k) mine[off[k]] = v[k] + gz;
+            } else {
+#pragma unroll
+                for (int k = 0; k < FT; ++k) mine[off[k]] = v[k] + (((MW >> k) & 1u) ? 0.0f : gz);
+            }
+        } else {
+            for (int k = 0; k < F; ++k) {
+                const uint32_t c = ((k < 16 ? A0 : A1) >> ((2 * k) & 31)) & 3u;
+                if (!((MW >> k) & 1u)) mine[k * 128 + c * 32] += gz;
+            }
         }
     }
     __syncwarp();
-    // lane-transposed reduction: lane l sums rows l, l+32, ...
+    // lane-transposed reduction: lane l sums cells l, l+32, ...  (cell r = k*4 + c  ->  output index c*F + k)
     float *out = acc + (size_t)BW_WARPS * W * 32 + (size_t)warp * (W + 2);
     for (int r = lane; r < W; r += 32) {
         float v = 0.f;
 #pragma unroll 8
         for (int j = 0; j < 32; ++j) v += my[r * 32 + ((j + lane) & 31)];
-        out[r] = v;
+        out[(r & 3) * F + (r >> 2)] = v;
     }
     dbeta = warp_sum(dbeta);
     dgamma = warp_sum(dgamma);
@@ -215,16 +240,22 @@ __global__ void __launch_bounds__(128) conv_bwd_final_kernel(const float *__rest
 }
 
 // ------------------------------------------------------------------------------------------------
-// fused loss (mean reduction) + d(loss)/d(logits).  Single block; n = B*C is small.
+// fused loss (mean reduction) + d(loss)/d(logits).  Up to 64 blocks write partial sums; the last block to
+// finish adds them in block order (deterministic) and resets the ticket counter for the next call.
+// scratch: LOSS_MAX_BLOCKS doubles + one unsigned ticket (zero-initialised once by the caller).
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(1024) loss_kernel(const float *__restrict__ logits, const float *__restrict__ target,
-                                                    long long n, int kind, float grad_scale, float *__restrict__ loss,
-                                                    float *__restrict__ dlogits)
+constexpr int LOSS_MAX_BLOCKS = 64;
+
+__global__ void __launch_bounds__(256) loss_kernel(const float *__restrict__ logits, const float *__restrict__ target,
+                                                   long long n, int kind, float grad_scale, float *__restrict__ loss,
+                                                   float *__restrict__ dlogits, double *__restrict__ partial,
+                                                   unsigned int *__restrict__ ticket)
 {
-    __shared__ double red[32];
+    __shared__ double red[8];
+    __shared__ bool last;
     double acc = 0.0;
     const float inv_n = 1.0f / (float)n;
-    for (long long i = threadIdx.x; i < n; i += blockDim.x) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
         const float x = logits[i], y = target[i];
         float l, g;
         if (kind == EXPLAINN_LOSS_BCE_WITH_LOGITS) {
@@ -244,10 +275,20 @@ __global__ void __launch_bounds__(1024) loss_kernel(const float *__restrict__ lo
     acc = warp_sum_d(acc);
     if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
     __syncthreads();
-    if (threadIdx.x < 32) {
-        double v = threadIdx.x < (blockDim.x >> 5) ? red[threadIdx.x] : 0.0;
-        v = warp_sum_d(v);
-        if (threadIdx.x == 0) *loss = (float)(v / (double)n);
+    if (threadIdx.x == 0) {
+        double v = 0.0;
+        for (int w = 0; w < 8; ++w) v += red[w];
+        partial[blockIdx.x] = v;
+        __threadfence();
+        last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (last && threadIdx.x == 0) {
+        __threadfence();
+        double v = 0.0;
+        for (unsigned k = 0; k < gridDim.x; ++k) v += ((volatile double *)partial)[k];
+        *loss = (float)(v / (double)n);
+        *ticket = 0u;
     }
 }
 
@@ -321,7 +362,7 @@ extern "C" int explainn_bn1_batch_stats(const int *M, const float *w, const floa
 
 extern "C" int explainn_conv_bwd_nsplit(int U)
 {
-    const int target = 2 * xb_num_sms();
+    const int target = 5 * xb_num_sms();     // 5 CTAs of 4 warps fit on an SM (39 KB of accumulators each)
     int ns = (target + U - 1) / U;
     return ns < 1 ? 1 : ns;
 }
@@ -336,10 +377,18 @@ extern "C" int explainn_conv_pool_bwd(const uint32_t *codes, const uint32_t *nma
                "conv_pool_bwd: null pointer");
     XB_REQUIRE(B >= 1 && U >= 1 && F >= 1 && F <= 4 * XB_MAX_G && L >= F + XB_POOL - 1 && nsplit >= 1, "conv_pool_bwd: bad sizes");
     const int S = L - F + 1, P = (S - XB_POOL) / XB_POOL + 1, W = 4 * F;
+    XB_REQUIRE(B * P < (1LL << 31), "conv_pool_bwd: B*P = %lld entries per unit exceed 2^31", B * P);
     const size_t smem = ((size_t)BW_WARPS * W * 32 + (size_t)BW_WARPS * (W + 2)) * sizeof(float);
-    cudaFuncSetAttribute(conv_bwd_sparse_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    conv_bwd_sparse_kernel<<<dim3(U, nsplit), BW_WARPS * 32, smem, stream>>>(codes, nmask, B, L, F, P, xb_words_codes(L),
-                                                                            xb_words_mask(L), gpool, pooled, xhat, idx, partial, U);
+#define XB_LAUNCH_SPARSE(FTV)                                                                                                  \
+    do {                                                                                                                      \
+        cudaFuncSetAttribute(conv_bwd_sparse_kernel<FTV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);            \
+        conv_bwd_sparse_kernel<FTV><<<dim3(U, nsplit), BW_WARPS * 32, smem, stream>>>(                                        \
+            codes, nmask, B, L, F, P, xb_words_codes(L), xb_words_mask(L), gpool, pooled, xhat, idx, partial, U);             \
+    } while (0)
+    if (F == 19) XB_LAUNCH_SPARSE(19);
+    else if (F == 20) XB_LAUNCH_SPARSE(20);
+    else XB_LAUNCH_SPARSE(0);
+#undef XB_LAUNCH_SPARSE
     int rc = xb_check_launch("conv_bwd_sparse");
     if (rc != XB_OK) return rc;
     conv_bwd_final_kernel<<<U, 128, 0, stream>>>(partial, nsplit, U, F, M, Mw, bias, mean, var, gamma, eps, (double)B * S, dW, dbias,
@@ -347,12 +396,19 @@ extern "C" int explainn_conv_pool_bwd(const uint32_t *codes, const uint32_t *nma
     return xb_check_launch("conv_bwd_final");
 }
 
+extern "C" long long explainn_loss_scratch_bytes(void) { return (long long)LOSS_MAX_BLOCKS * sizeof(double) + 16; }
+
 extern "C" int explainn_loss_fwd_bwd(const float *logits, const float *target, long long B, int C, int kind, float grad_scale,
-                                     float *loss, float *dlogits, cudaStream_t stream)
+                                     float *loss, float *dlogits, void *scratch, cudaStream_t stream)
 {
-    XB_REQUIRE(logits && target && loss && B >= 1 && C >= 1, "loss_fwd_bwd: bad argument");
+    XB_REQUIRE(logits && target && loss && scratch && B >= 1 && C >= 1, "loss_fwd_bwd: bad argument");
     XB_REQUIRE(kind == EXPLAINN_LOSS_BCE_WITH_LOGITS || kind == EXPLAINN_LOSS_MSE, "loss_fwd_bwd: unknown loss %d", kind);
-    loss_kernel<<<1, 1024, 0, stream>>>(logits, target, B * C, kind, grad_scale, loss, dlogits);
+    const long long n = B * C;
+    int blocks = (int)std::min<long long>(LOSS_MAX_BLOCKS, (n + 1023) / 1024);
+    if (blocks < 1) blocks = 1;
+    double *partial = reinterpret_cast<double *>(scratch);
+    unsigned int *ticket = reinterpret_cast<unsigned int *>(partial + LOSS_MAX_BLOCKS);
+    loss_kernel<<<blocks, 256, 0, stream>>>(logits, target, n, kind, grad_scale, loss, dlogits, partial, ticket);
     return xb_check_launch("loss_fwd_bwd");
 }
 

@@ -96,6 +96,7 @@ class FusedTrainer:
         self._gx = self._gy = self._gloss = None
         self._graph_launches = 0
         self._seed_ctr = torch.zeros(1, dtype=torch.int64, device=dev)
+        self._loss_scratch = torch.zeros(_cabi.lib.explainn_loss_scratch_bytes(), dtype=torch.uint8, device=dev)
         self.world = 1
         d = _dist()
         if d is not None:
@@ -113,7 +114,8 @@ class FusedTrainer:
             raise ValueError("labels of shape %s do not match logits %s" % (tuple(y.shape), (B, C)))
         loss = torch.empty(1, dtype=torch.float32, device=ws.logits.device)
         dlogits = torch.empty_like(ws.logits)
-        call("explainn_loss_fwd_bwd", ptr(ws.logits), ptr(y), B, C, self.kind, 1.0, ptr(loss), ptr(dlogits), stream())
+        call("explainn_loss_fwd_bwd", ptr(ws.logits), ptr(y), B, C, self.kind, 1.0, ptr(loss), ptr(dlogits),
+             ptr(self._loss_scratch), stream())
         autograd_fn.train_backward(self.model, ws, dlogits, ps, self.views_g)
         return loss
 

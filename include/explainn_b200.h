@@ -191,9 +191,11 @@ int explainn_conv_pool_bwd(const uint32_t *codes, const uint32_t *nmask, long lo
 
 /* ---- fused criterion (mean reduction) and its gradient ---------------------------------------------------------
  * BCEWithLogitsLoss / MSELoss as scripts/train.py:210-219 constructs them (explainn/train/train.py:62).
- * loss: 1 float; dlogits (B,C) = grad_scale * d loss / d logits (may be NULL). */
+ * loss: 1 float; dlogits (B,C) = grad_scale * d loss / d logits (may be NULL).  scratch: explainn_loss_scratch_bytes()
+ * bytes, zero-initialised ONCE by the caller (the kernel leaves it zeroed again). */
+long long explainn_loss_scratch_bytes(void);
 int explainn_loss_fwd_bwd(const float *logits, const float *target, long long B, int C, int kind, float grad_scale,
-                          float *loss, float *dlogits, cudaStream_t stream);
+                          float *loss, float *dlogits, void *scratch, cudaStream_t stream);
 
 /* ---- fused Adam over one flat buffer ------------------------------------------------------------------------------
  * torch.optim.Adam with its defaults-compatible options (amsgrad=False, weight_decay=0, maximize=False), the
