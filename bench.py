@@ -215,17 +215,17 @@ def main():
     sync_all()
     launches = _cabi.LAUNCHES - l0
     ms = e0.elapsed_time(e1)
-    # keep the GPU busy a little longer so that nvidia-smi (100 ms period) gets samples under load
-    # (a fixed number of steps: every rank must issue the same number of all-reduces)
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    # keep the GPU busy a little longer so that nvidia-smi (100 ms period) gets samples under load; the count is
+    # derived from the all-reduced time, so every rank issues the same number of collectives
     extra_steps = max(20, int(0.6 / max(ms / K * 1e-3, 1e-5)))
     for i in range(extra_steps):
         trainer.step(*batch(i))
     torch.cuda.synchronize()
     clocks = sampler.stop() if rank == 0 else None
-    t = torch.tensor([ms], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms = float(t.item())
     value = n_gpus * B * K / (ms * 1e-3)
     final_loss = float(loss.item())
 

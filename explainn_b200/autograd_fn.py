@@ -125,7 +125,7 @@ def train_backward(model, ws, gout, params=None, grads=None, wrt_unit=False):
     gh2 = torch.empty((U, B), **f32)
     pb2 = torch.empty((U, ws.nchunk, 3, H), **f32)
     dW1p = torch.empty((ws.nchunk, U, H, P), **f32)
-    gpool = torch.empty((U, B, P), **f32)
+    gpool = torch.empty((B, U, P), **f32)
     call("explainn_fc_stack_bwd", ptr(gout), B, U, P, C, ptr(ws.pooled), ptr(ws.h1), ptr(ws.h2), ptr(ws.unit), ptr(W1),
          ptr(g2), ptr(be2), ptr(ws.mean2), ptr(ws.invstd2), ptr(W2), ptr(g3), ptr(ws.mean3), ptr(ws.invstd3),
          None if wrt_unit else ptr(Wf), ws.pdrop, ws.seed, ptr(ws.seed_dev), ptr(gh2), ptr(pb2), ptr(dW1p), ptr(gpool), ptr(dW1), ptr(db1),

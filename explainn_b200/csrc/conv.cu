@@ -53,7 +53,7 @@ __device__ __forceinline__ float lds_f32(const unsigned char *smem, uint32_t off
 // Sinks: what happens with the 7 z-values of one pool window.  `acc` excludes shift[u].
 // ----------------------------------------------------------------------------------------------
 
-// (1) inference pooling: pooled[u][b][p] = exp(max_window z)   (unit-major, see fc.cu)
+// (1) inference pooling: pooled[b][u][p] = exp(max_window z)
 template <int PCH_>
 struct PoolSinkT {
     struct Params { float *pooled; int P; };
@@ -63,7 +63,7 @@ struct PoolSinkT {
     float *stage;
     int ps, lane, nvalid;
     float shift;
-    long long out_base, row_stride;   // element offset of pooled[u0][b][0]; distance between units
+    long long out_base, row_stride;   // element offset of pooled[b][u0][0]; distance between units
     int win_base;
     __device__ void init_cta(unsigned char *smem, const Params &pp, int warp, int lane_)
     {
@@ -75,8 +75,8 @@ struct PoolSinkT {
     __device__ void begin_tile(int u0, int nvalid_, float shift_, const ConvArgs &) { nvalid = nvalid_; shift = shift_; (void)u0; }
     __device__ void begin_seq(long long b, int u0, const ConvArgs &a)
     {
-        row_stride = a.B * p.P;
-        out_base = ((long long)u0 * a.B + b) * p.P;
+        row_stride = p.P;
+        out_base = (b * a.U + u0) * (long long)p.P;
         win_base = 0;
     }
     __device__ void flush(int upto)
@@ -134,8 +134,8 @@ struct PoolTrainSinkT {
     }
     __device__ void begin_seq(long long b, int u0, const ConvArgs &a)
     {
-        row_stride = a.B * p.P;
-        out_base = ((long long)u0 * a.B + b) * p.P;
+        row_stride = p.P;
+        out_base = (b * a.U + u0) * (long long)p.P;
         win_base = 0;
     }
     __device__ void flush(int upto)

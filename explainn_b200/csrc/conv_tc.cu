@@ -1,0 +1,457 @@
+// conv_tc.cu -- tensor-core (tcgen05 / TMEM) variant of the fused conv + BN + exp + maxpool forward.
+//
+// Replaces the same reference lines as conv.cu (explainn/models/networks.py:98-102,153) for the two paths
+// that tolerate fp32 rounding differences (inference and the training forward); the interpretation pass keeps
+// the bit-exact table kernel of conv.cu.
+//
+// Formulation.  The conv on one-hot DNA is the GEMM  D[u][n] = sum_k A[u][k] * X[n][k]  with
+//   A[u][k = 4*tap + c] = w'[u][c][tap]  (BatchNorm folded in),  A[u][4F] = shift[u],
+//   X[n][4*tap + c]     = 1 if base(n + tap) == c,               X[n][4F] = 1.
+// X is exactly representable in fp16; the fp32 weights are split A = A_hi + A_lo (two fp16 pieces, ~22
+// significant bits), so  D = A_hi X^T + A_lo X^T  with every product exact and fp32 accumulation in TMEM.
+// Units are the M dimension (one TMEM lane per unit), positions the N dimension (columns), so each epilogue
+// thread owns one unit and pools 7 consecutive columns in registers.
+//
+// One CTA per SM, persistent.  A (one 128-unit tile, hi+lo, 40 KB) stays in shared memory; for every
+// (sequence, 34-window chunk) the producer warps expand the 2-bit codes into the X tile (240 rows x K fp16,
+// canonical no-swizzle K-major core-matrix layout), one thread issues 2*K/16 tcgen05.mma into one of two
+// TMEM accumulators (240 columns each) and the epilogue warps drain the other one.
+#include "common.cuh"
+#include "../../include/explainn_b200.h"
+
+namespace {
+
+constexpr int TC_M = 128;          // units per tile (TMEM lanes)
+constexpr int TC_N = 240;          // positions per tile (TMEM columns), 34 windows of 7 = 238 used
+constexpr int TC_WIN = 34;         // pool windows per tile
+constexpr int TC_THREADS = 256;    // warps 0-3: epilogue (lane quarter = warp), warps 4-7: producers
+
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes)
+{
+    // SM100 shared-memory matrix descriptor, SWIZZLE_NONE, K-major
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_addr & 0x3FFFFu) >> 4);
+    d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFFu) << 16;
+    d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFFu) << 32;
+    d |= (uint64_t)1 << 46;     // descriptor version (Blackwell)
+    return d;
+}
+
+__device__ __forceinline__ void tc_mma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate)
+{
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+
+__device__ __forceinline__ void tc_commit(uint64_t *bar)
+{
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+__device__ __forceinline__ void tc_ld32(uint32_t taddr, float (&v)[32])
+{
+    uint32_t r[32];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),
+          "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]),
+          "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]),
+          "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr)
+        : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+__device__ __forceinline__ void tc_ld16(uint32_t taddr, float (&v)[32])
+{
+    uint32_t r[16];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),
+          "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr)
+        : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+// ------------------------------------------------------------------------------------------------
+// A-operand images: per 128-unit tile, [hi | lo] x canonical K-major layout
+//   byte offset of element (row r, k) inside one image = (r/8)*KC*128 + (k/8)*128 + (r%8)*16 + (k%8)*2
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) tc_prepare_kernel(const float *__restrict__ w, const float *__restrict__ bias,
+                                                         const float *__restrict__ gamma, const float *__restrict__ beta,
+                                                         const float *__restrict__ mean, const float *__restrict__ var, float eps,
+                                                         int U, int F, int K, __half *__restrict__ images)
+{
+    const int mt = blockIdx.x, KC = K / 8;
+    __half *hi = images + (size_t)mt * 2 * TC_M * K, *lo = hi + (size_t)TC_M * K;
+    for (int i = threadIdx.x; i < TC_M * K; i += blockDim.x) {
+        const int r = i / K, k = i - r * K;
+        const int u = mt * TC_M + r;
+        float v = 0.0f;
+        if (u < U) {
+            const float sc = __fdiv_rn(gamma[u], __fsqrt_rn(__fadd_rn(var[u], eps)));
+            if (k < 4 * F) {
+                const int tap = k >> 2, c = k & 3;
+                v = __fmul_rn(w[((size_t)u * 4 + c) * F + tap], sc);
+            } else if (k == 4 * F) {
+                v = __fadd_rn(__fmul_rn(__fsub_rn(bias[u], mean[u]), sc), beta[u]);
+            }
+        }
+        const __half h = __float2half_rn(v);
+        const __half l = __float2half_rn(v - __half2float(h));
+        const size_t off = (size_t)(r >> 3) * KC * 64 + (size_t)(k >> 3) * 64 + (r & 7) * 8 + (k & 7);
+        hi[off] = h;
+        lo[off] = l;
+    }
+}
+
+struct TcArgs {
+    const uint32_t *codes, *nmask;
+    long long B;
+    int L, F, U, K, P, wc, wm;
+    const __half *images;
+    float *pooled;          // (B,U,P)
+    float *xhat;            // train only
+    unsigned char *idx;     // train only
+    const float *gamma, *beta;
+};
+
+template <bool TRAIN>
+__global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const TcArgs a)
+{
+    extern __shared__ __align__(128) unsigned char smem[];
+    __shared__ __align__(8) uint64_t bar_a, bar_full[2];
+    __shared__ uint32_t tmem_base_s;
+
+    const int K = a.K, KC = K / 8, KS = K / 16;
+    const uint32_t a_bytes = (uint32_t)TC_M * K * 2;        // one image (hi or lo)
+    const uint32_t b_bytes = (uint32_t)TC_N * K * 2;
+    unsigned char *sA = smem;                               // hi, lo
+    unsigned char *sB = sA + 2 * a_bytes;                   // 2 buffers
+    // staging: [128][sst] floats per plane (pooled; + x_hat, argmax when TRAIN).  With a single chunk per sequence
+    // the row stride is P itself, so a plane is the exact image of pooled[b][u0..u0+127][:] and leaves with ONE
+    // TMA bulk store.
+    const int sst = a.P <= TC_WIN ? a.P : TC_WIN + 1;
+    float *stage = reinterpret_cast<float *>(sB + 2 * b_bytes);
+    const int plane = TC_M * (TC_WIN + 1);
+    unsigned char *sseq = reinterpret_cast<unsigned char *>(stage + (TRAIN ? 3 : 1) * plane);   // 2 x seq bytes
+    const int seq_pad = ((a.L + 64 + 15) / 16) * 16;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int n_mt = (a.U + TC_M - 1) / TC_M;
+    const int nchunk = (a.P + TC_WIN - 1) / TC_WIN;
+
+    // work split: CTA -> (m-tile, contiguous range of (sequence, chunk) items)
+    const long long items_per_mt = a.B * nchunk;
+    const long long total = items_per_mt * n_mt;
+    const long long it0 = total * blockIdx.x / gridDim.x, it1 = total * (blockIdx.x + 1) / gridDim.x;
+
+    if (threadIdx.x == 0) {
+        mbar_init(&bar_a, 1);
+        mbar_init(&bar_full[0], 1);
+        mbar_init(&bar_full[1], 1);
+        mbar_fence_init();
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"(512u) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_base_s;
+
+    // instruction descriptor: f16 x f16 -> f32, M=128, N=240, both operands K-major
+    const uint32_t idesc = (1u << 4) | ((uint32_t)(TC_N >> 3) << 17) | ((uint32_t)(TC_M >> 4) << 24);
+    const uint32_t lbo = 128, sbo = (uint32_t)KC * 128;
+
+    uint32_t a_parity = 0;
+    uint32_t full_parity[2] = {0, 0};
+    int cur_mt = -1;
+    long long it = it0;
+    int issued = 0;                      // number of tiles issued so far by this CTA (buffer = issued & 1)
+    // descriptor of the previous tile (for the deferred epilogue)
+    long long prev_b = -1;
+    int prev_chunk = 0, prev_buf = 0, prev_u0 = 0;
+    bool have_prev = false;
+
+    auto epilogue = [&](long long b, int chunk, int buf, int u0) {
+        // warps 0-3: drain TMEM buffer `buf` (unit = u0 + 32*warp + lane), pool, exp, stage
+        const int w0 = chunk * TC_WIN;
+        const int nwin = min(TC_WIN, a.P - w0);
+        if (warp < 4) {
+            mbar_wait(&bar_full[buf], full_parity[buf]);
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + ((uint32_t)(32 * warp) << 16) + (uint32_t)buf * 256u;
+            const int row = 32 * warp + lane;
+            float gam = 1.f, bet = 0.f;
+            if (TRAIN) {
+                const int u = u0 + row;
+                gam = u < a.U ? a.gamma[u] : 1.f;
+                bet = u < a.U ? a.beta[u] : 0.f;
+            }
+            float m = 0.f, xb = 0.f;
+            int ib = 0;
+#pragma unroll
+            for (int cb = 0; cb < 8; ++cb) {
+                float v[32];
+                if (cb < 7) tc_ld32(taddr + cb * 32, v);
+                else tc_ld16(taddr + cb * 32, v);
+#pragma unroll
+                for (int j = 0; j < (cb < 7 ? 32 : 16); ++j) {
+                    const int col = cb * 32 + j;
+                    if (col >= TC_WIN * XB_POOL) break;
+                    const int ph = col % XB_POOL, win = col / XB_POOL;
+                    if (TRAIN) {
+                        const float z = fmaf(gam, v[j], bet);
+                        if (ph == 0 || z > m) { m = z; xb = v[j]; ib = ph; }
+                    } else {
+                        m = ph == 0 ? v[j] : fmaxf(m, v[j]);
+                    }
+                    if (ph == XB_POOL - 1) {
+                        if (win < nwin) {
+                            stage[row * sst + win] = __expf(m);
+                            if (TRAIN) {
+                                stage[plane + row * sst + win] = xb;
+                                reinterpret_cast<unsigned char *>(stage + 2 * plane)[row * sst + win] = (unsigned char)ib;
+                            }
+                        }
+                    }
+                }
+            }
+            tc_fence_before();
+        }
+        full_parity[buf] ^= 1;
+        (void)b; (void)u0;
+    };
+
+    auto store_stage = [&](long long b, int chunk, int u0) {
+        const int w0 = chunk * TC_WIN;
+        const int nwin = min(TC_WIN, a.P - w0);
+        const int nvalid = min(TC_M, a.U - u0);
+        const size_t o = ((size_t)b * a.U + u0) * a.P;
+        const uint32_t bytes = (uint32_t)nvalid * a.P * 4;
+        // when the staged planes are exact images of the global tiles they leave as TMA bulk stores
+        const bool bulk_f = sst == a.P && (bytes & 15u) == 0 && ((o * 4) & 15u) == 0;
+        const bool bulk_i = TRAIN && sst == a.P && ((bytes / 4) & 15u) == 0 && (o & 15u) == 0;
+        if (bulk_f || bulk_i) {
+            fence_proxy_async();
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                if (bulk_f) {
+                    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(a.pooled + o), "r"(smem_u32(stage)), "r"(bytes) : "memory");
+                    if (TRAIN)
+                        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(a.xhat + o), "r"(smem_u32(stage + plane)), "r"(bytes) : "memory");
+                }
+                if (bulk_i)
+                    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(a.idx + o), "r"(smem_u32(stage + 2 * plane)), "r"(bytes / 4) : "memory");
+                asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            }
+        }
+        if (!bulk_f || (TRAIN && !bulk_i)) {
+            for (int r = warp; r < nvalid; r += TC_THREADS / 32) {
+                const size_t orow = o + (size_t)r * a.P + w0;
+                for (int c = lane; c < nwin; c += 32) {
+                    if (!bulk_f) {
+                        a.pooled[orow + c] = stage[r * sst + c];
+                        if (TRAIN) a.xhat[orow + c] = stage[plane + r * sst + c];
+                    }
+                    if (TRAIN && !bulk_i) a.idx[orow + c] = reinterpret_cast<unsigned char *>(stage + 2 * plane)[r * sst + c];
+                }
+            }
+        }
+        if ((bulk_f || bulk_i) && threadIdx.x == 0)
+            asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // staging may be rewritten after this
+    };
+
+    while (it < it1 || have_prev) {
+        const bool have_cur = it < it1;
+        int mt = 0, chunk = 0, buf = issued & 1, u0 = 0;
+        long long b = 0;
+        if (have_cur) {
+            mt = (int)(it / items_per_mt);
+            const long long rem = it - (long long)mt * items_per_mt;
+            b = rem / nchunk;
+            chunk = (int)(rem - b * nchunk);
+            u0 = mt * TC_M;
+            if (mt != cur_mt) {
+                // a new unit tile: the previous tile's MMAs must be done with sA before it is overwritten
+                if (have_prev) {
+                    epilogue(prev_b, prev_chunk, prev_buf, prev_u0);
+                    __syncthreads();
+                    store_stage(prev_b, prev_chunk, prev_u0);
+                    have_prev = false;
+                }
+                __syncthreads();
+                if (threadIdx.x == 0) {
+                    mbar_arrive_expect_tx(&bar_a, 2 * a_bytes);
+                    tma_bulk_g2s(sA, reinterpret_cast<const unsigned char *>(a.images) + (size_t)mt * 2 * a_bytes, 2 * a_bytes, &bar_a);
+                }
+                mbar_wait(&bar_a, a_parity);
+                a_parity ^= 1;
+                cur_mt = mt;
+            }
+            // ---- expand the sequence into bytes (code 0..3, 4 = N) and build the X tile ----
+            unsigned char *sb = sseq + (size_t)buf * seq_pad;
+            for (int i = threadIdx.x; i < seq_pad; i += TC_THREADS) {
+                unsigned v = 4;
+                if (i < a.L) {
+                    const unsigned c = (a.codes[b * a.wc + (i >> 4)] >> (2 * (i & 15))) & 3u;
+                    const unsigned mk = (a.nmask[b * a.wm + (i >> 5)] >> (i & 31)) & 1u;
+                    v = mk ? 4u : c;
+                }
+                sb[i] = (unsigned char)v;
+            }
+            __syncthreads();
+            {
+                unsigned char *Bt = sB + (size_t)buf * b_bytes;
+                const int n0 = chunk * TC_WIN * XB_POOL;
+                const int F = a.F;
+                for (int q = threadIdx.x; q < TC_N * KC; q += TC_THREADS) {
+                    const int kc = q / TC_N, n = q - kc * TC_N;        // consecutive threads -> consecutive rows
+                    const int t0 = 2 * kc, t1 = t0 + 1;
+                    unsigned long long lo64 = 0ull, hi64 = 0ull;
+                    const int p0 = n0 + n + t0;
+                    if (t0 < F) {
+                        const unsigned c = p0 < seq_pad ? sb[p0] : 4u;
+                        if (c < 4u) lo64 = 0x3C00ull << (16 * c);
+                    } else if (t0 == F) lo64 = 0x3C00ull;
+                    if (t1 < F) {
+                        const unsigned c = p0 + 1 < seq_pad ? sb[p0 + 1] : 4u;
+                        if (c < 4u) hi64 = 0x3C00ull << (16 * c);
+                    } else if (t1 == F) hi64 = 0x3C00ull;
+                    uint4 val;
+                    val.x = (uint32_t)lo64; val.y = (uint32_t)(lo64 >> 32); val.z = (uint32_t)hi64; val.w = (uint32_t)(hi64 >> 32);
+                    *reinterpret_cast<uint4 *>(Bt + (size_t)(n >> 3) * sbo + (size_t)kc * 128 + (n & 7) * 16) = val;
+                }
+            }
+            fence_proxy_async();
+            tc_fence_before();
+            __syncthreads();
+            // ---- issue the MMAs of this tile ----
+            if (threadIdx.x == 0) {
+                tc_fence_after();
+                const uint32_t d = tmem_base + (uint32_t)buf * 256u;
+                const uint32_t a_hi = smem_u32(sA), a_lo = a_hi + a_bytes, bt = smem_u32(sB + (size_t)buf * b_bytes);
+                for (int ks = 0; ks < KS; ++ks) {
+                    const uint64_t bd = make_smem_desc(bt + ks * 256, lbo, sbo);
+                    tc_mma_f16(d, make_smem_desc(a_hi + ks * 256, lbo, sbo), bd, idesc, ks > 0 ? 1u : 0u);
+                    tc_mma_f16(d, make_smem_desc(a_lo + ks * 256, lbo, sbo), bd, idesc, 1u);
+                }
+                tc_commit(&bar_full[buf]);
+            }
+        }
+        // ---- epilogue of the previous tile overlaps the MMAs just issued ----
+        if (have_prev) {
+            epilogue(prev_b, prev_chunk, prev_buf, prev_u0);
+            __syncthreads();
+            store_stage(prev_b, prev_chunk, prev_u0);
+            have_prev = false;
+        }
+        if (have_cur) {
+            prev_b = b; prev_chunk = chunk; prev_buf = buf; prev_u0 = u0;
+            have_prev = true;
+            ++issued;
+            ++it;
+        }
+        __syncthreads();
+    }
+
+    if (threadIdx.x == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
+    }
+}
+
+int tc_K(int F) { return ((4 * F + 1 + 15) / 16) * 16; }
+
+}  // namespace
+
+extern "C" long long explainn_conv_tc_image_halfs(int U, int F)
+{
+    const long long n_mt = (U + TC_M - 1) / TC_M;
+    return n_mt * 2 * TC_M * tc_K(F);
+}
+
+extern "C" int explainn_conv_tc_prepare(const float *w, const float *bias, const float *gamma, const float *beta,
+                                        const float *mean, const float *var, float eps, int U, int F, void *images,
+                                        cudaStream_t stream)
+{
+    XB_REQUIRE(w && bias && gamma && beta && mean && var && images && U >= 1 && F >= 1, "conv_tc_prepare: bad argument");
+    if (F > 4 * XB_MAX_G) {
+        xb_set_error("conv_tc_prepare: filter_size %d not supported (max %d)", F, 4 * XB_MAX_G);
+        return XB_ERR_UNSUPPORTED;
+    }
+    const int n_mt = (U + TC_M - 1) / TC_M;
+    tc_prepare_kernel<<<n_mt, 256, 0, stream>>>(w, bias, gamma, beta, mean, var, eps, U, F, tc_K(F), (__half *)images);
+    return xb_check_launch("conv_tc_prepare");
+}
+
+static int launch_tc(bool train, const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F, const void *images,
+                     const float *gamma, const float *beta, float *pooled, float *xhat, unsigned char *idx, cudaStream_t stream)
+{
+    XB_REQUIRE(codes && nmask && images && pooled && B >= 0 && U >= 1, "conv_pool_fwd_tc: bad argument");
+    if (F < 1 || F > 4 * XB_MAX_G || L < F + XB_POOL - 1) {
+        xb_set_error("conv_pool_fwd_tc: unsupported geometry L=%d filter_size=%d", L, F);
+        return XB_ERR_UNSUPPORTED;
+    }
+    if (B == 0) return XB_OK;
+    TcArgs a;
+    a.codes = codes; a.nmask = nmask; a.B = B; a.L = L; a.F = F; a.U = U; a.K = tc_K(F);
+    a.P = ((L - F + 1) - XB_POOL) / XB_POOL + 1;
+    a.wc = xb_words_codes(L); a.wm = xb_words_mask(L);
+    a.images = (const __half *)images; a.pooled = pooled; a.xhat = xhat; a.idx = idx; a.gamma = gamma; a.beta = beta;
+    const int seq_pad = ((L + 64 + 15) / 16) * 16;
+    const size_t smem = (size_t)2 * TC_M * a.K * 2 + (size_t)2 * TC_N * a.K * 2 + (size_t)(train ? 3 : 1) * TC_M * (TC_WIN + 1) * 4 + 2 * (size_t)seq_pad;
+    if (smem > 227 * 1024) {
+        xb_set_error("conv_pool_fwd_tc: %zu bytes of shared memory needed (L=%d, filter_size=%d)", smem, L, F);
+        return XB_ERR_UNSUPPORTED;
+    }
+    const int n_mt = (U + TC_M - 1) / TC_M, nchunk = (a.P + TC_WIN - 1) / TC_WIN;
+    long long total = (long long)n_mt * B * nchunk;
+    int grid = xb_num_sms();
+    if (total < grid) grid = (int)total;
+    cudaError_t e;
+    if (train) {
+        e = cudaFuncSetAttribute(conv_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e == cudaSuccess) conv_tc_kernel<true><<<grid, TC_THREADS, smem, stream>>>(a);
+    } else {
+        e = cudaFuncSetAttribute(conv_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e == cudaSuccess) conv_tc_kernel<false><<<grid, TC_THREADS, smem, stream>>>(a);
+    }
+    if (e != cudaSuccess) {
+        xb_set_error("conv_pool_fwd_tc: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+        return XB_ERR_CUDA;
+    }
+    return xb_check_launch("conv_pool_fwd_tc");
+}
+
+extern "C" int explainn_conv_pool_fwd_tc(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F,
+                                         const void *images, float *pooled, cudaStream_t stream)
+{
+    return launch_tc(false, codes, nmask, B, L, U, F, images, nullptr, nullptr, pooled, nullptr, nullptr, stream);
+}
+
+extern "C" int explainn_conv_pool_fwd_train_tc(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F,
+                                               const void *images, const float *gamma, const float *beta, float *pooled,
+                                               float *xhat, unsigned char *idx, cudaStream_t stream)
+{
+    XB_REQUIRE(gamma && beta && xhat && idx, "conv_pool_fwd_train_tc: null pointer");
+    return launch_tc(true, codes, nmask, B, L, U, F, images, gamma, beta, pooled, xhat, idx, stream);
+}

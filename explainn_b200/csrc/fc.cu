@@ -5,9 +5,9 @@
 //                   Dropout(0.3), grouped 1x1 Conv1d(100U -> U), BatchNorm1d(U), ReLU, Flatten   (:103-116)
 //   final = Linear(U, C)                                                                        (:147,161)
 //
-// Layout.  The pooled activations arrive unit-major, pooled[u][b][p], so that the tile a CTA works on
-// (one unit x 128 sequences) is one contiguous block.  The hidden activations h1[u][b][100] use the
-// same convention.  A CTA keeps W1[u] (100 x P) transposed in shared memory; each thread owns two
+// Layout.  The pooled activations arrive as pooled[b][u][p] (the reference's (B,U,P)); a CTA works on the tile
+// (one unit x 128 sequences), i.e. 128 rows of P floats U*P apart.  The hidden activations are unit-major,
+// h1[u][b][100], so that their tile is one contiguous block.  A CTA keeps W1[u] (100 x P) transposed in shared memory; each thread owns two
 // sequences x 25 hidden channels, so every W1 value is fetched by a warp-uniform (broadcast) LDS.128
 // and the pooled values by conflict-free scalar loads.
 #include "common.cuh"
@@ -50,12 +50,12 @@ __device__ __forceinline__ void load_w1(const FcSmem &s, const float *__restrict
     }
 }
 
-__device__ __forceinline__ void load_a(const FcSmem &s, const float *__restrict__ tile, int rows, int P)
+__device__ __forceinline__ void load_a(const FcSmem &s, const float *__restrict__ tile, size_t row_stride, int rows, int P)
 {
-    // tile: rows x P contiguous
+    // tile: `rows` rows of P floats, row_stride elements apart (pooled is (B,U,P): stride U*P)
     for (int i = threadIdx.x; i < BM * P; i += blockDim.x) {
         const int r = i / P, p = i - r * P;
-        s.As[r * s.Pp + p] = r < rows ? tile[i] : 0.0f;
+        s.As[r * s.Pp + p] = r < rows ? tile[(size_t)r * row_stride + p] : 0.0f;
     }
 }
 
@@ -105,7 +105,7 @@ __global__ void __launch_bounds__(FC_THREADS) fc_stack_eval_kernel(
     const long long b0 = (long long)blockIdx.y * BM;
     const int rows = (int)min((long long)BM, B - b0);
     load_w1(s, W1 + (size_t)u * H * P, P);
-    load_a(s, pooled + ((size_t)u * B + b0) * P, rows, P);
+    load_a(s, pooled + ((size_t)b0 * U + u) * P, (size_t)U * P, rows, P);
     if (threadIdx.x < JQ * JP) {
         const int q = threadIdx.x / JP, jj = threadIdx.x % JP;
         float sc = 0.f, sh = 0.f, w2 = 0.f;
@@ -201,7 +201,7 @@ __global__ void __launch_bounds__(FC_THREADS) fc1_train_kernel(const float *__re
     const long long b0 = (long long)chunk * BM;
     const int rows = (int)min((long long)BM, B - b0);
     load_w1(s, W1 + (size_t)u * H * P, P);
-    load_a(s, pooled + ((size_t)u * B + b0) * P, rows, P);
+    load_a(s, pooled + ((size_t)b0 * U + u) * P, (size_t)U * P, rows, P);
     if (threadIdx.x < H) b1s[threadIdx.x] = b1[u * H + threadIdx.x];
     __syncthreads();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -583,7 +583,7 @@ __global__ void __launch_bounds__(FC_THREADS) bwd_fc1_kernel(
     // pooled tile and W1[u], both zero-padded to PQ columns
     for (int i = threadIdx.x; i < BM * PQ; i += blockDim.x) {
         const int r = i / PQ, p = i - r * PQ;
-        As[i] = (r < rows && p < P) ? pooled[((size_t)u * B + b0 + r) * P + p] : 0.f;
+        As[i] = (r < rows && p < P) ? pooled[((size_t)(b0 + r) * U + u) * P + p] : 0.f;
     }
     for (int i = threadIdx.x; i < H * PQ; i += blockDim.x) {
         const int j = i / PQ, p = i - j * PQ;
@@ -627,7 +627,7 @@ __global__ void __launch_bounds__(FC_THREADS) bwd_fc1_kernel(
         }
     }
     if (t < rows) {
-        float *dst = gpool + ((size_t)u * B + b0 + t) * P;
+        float *dst = gpool + ((size_t)(b0 + t) * U + u) * P;
 #pragma unroll
         for (int i = 0; i < PH; ++i)
             if (ph * PH + i < P) dst[ph * PH + i] = acc[i];

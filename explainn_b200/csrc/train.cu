@@ -138,15 +138,15 @@ __global__ void __launch_bounds__(BW_WARPS * 32) conv_bwd_sparse_kernel(
     const long long n = B * P;
     const long long per = (n + gridDim.y - 1) / gridDim.y;
     const long long e0 = per * blockIdx.y, e1 = min(n, e0 + per);
-    const size_t ubase = (size_t)u * n;
     float dbeta = 0.f, dgamma = 0.f;
     float *mine = my + lane;
     for (long long e = e0 + warp * 32 + lane; e < e1; e += BW_WARPS * 32) {
         const int b = (int)e / P;                    // host wrapper guarantees B*P < 2^31
         const int p = (int)e - b * P;
-        const float gz = gpool[ubase + e] * pooled[ubase + e];
-        const float xh = xhat[ubase + e];
-        const int s = p * XB_POOL + idx[ubase + e];
+        const size_t o = ((size_t)b * U + u) * P + p;   // (B,U,P) layout
+        const float gz = gpool[o] * pooled[o];
+        const float xh = xhat[o];
+        const int s = p * XB_POOL + idx[o];
         dbeta += gz;
         dgamma = fmaf(gz, xh, dgamma);
         const uint32_t *cw = codes + (size_t)b * wc;

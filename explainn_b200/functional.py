@@ -73,9 +73,9 @@ def conv_prepare(w, bias, gamma, beta, mean, var, eps=1e-5):
 
 
 def conv_pool_fwd(pk, prep):
-    """-> pooled (U,B,P) unit-major."""
+    """-> pooled (B,U,P)."""
     P = pooled_len(pk.L, prep.F)
-    pooled = torch.empty((prep.U, pk.B, P), dtype=torch.float32, device=pk.codes.device)
+    pooled = torch.empty((pk.B, prep.U, P), dtype=torch.float32, device=pk.codes.device)
     if pk.B == 0:
         return pooled
     call("explainn_conv_pool_fwd", ptr(pk.codes), ptr(pk.nmask), pk.B, pk.L, prep.U, prep.F, ptr(prep.tables),
@@ -129,8 +129,8 @@ def interp_pwm_count(pk, prep, thr, zlo, zhi, counts=None, hits=None):
 
 
 def fc_stack_fwd_eval(pooled, W1, b1, bn2, W2, b2, bn3, eps=1e-5):
-    """pooled (U,B,P) -> unit outputs (B,U).  bn2/bn3 = (weight, bias, running_mean, running_var)."""
-    U, B, P = pooled.shape
+    """pooled (B,U,P) -> unit outputs (B,U).  bn2/bn3 = (weight, bias, running_mean, running_var)."""
+    B, U, P = pooled.shape
     out = torch.empty((B, U), dtype=torch.float32, device=pooled.device)
     if B == 0:
         return out
@@ -170,9 +170,9 @@ def bn1_batch_stats(M, w, bias, n_pos, momentum, run_mean, run_var, nbt):
 def conv_pool_fwd_train(pk, prep, gamma, beta):
     P = pooled_len(pk.L, prep.F)
     dev = pk.codes.device
-    pooled = torch.empty((prep.U, pk.B, P), dtype=torch.float32, device=dev)
-    xhat = torch.empty((prep.U, pk.B, P), dtype=torch.float32, device=dev)
-    idx = torch.empty((prep.U, pk.B, P), dtype=torch.uint8, device=dev)
+    pooled = torch.empty((pk.B, prep.U, P), dtype=torch.float32, device=dev)
+    xhat = torch.empty((pk.B, prep.U, P), dtype=torch.float32, device=dev)
+    idx = torch.empty((pk.B, prep.U, P), dtype=torch.uint8, device=dev)
     call("explainn_conv_pool_fwd_train", ptr(pk.codes), ptr(pk.nmask), pk.B, pk.L, prep.U, prep.F, ptr(prep.tables),
          ptr(prep.wq_t), ptr(prep.shift), ptr(gamma), ptr(beta), ptr(pooled), ptr(xhat), ptr(idx), stream())
     return pooled, xhat, idx
@@ -180,3 +180,33 @@ def conv_pool_fwd_train(pk, prep, gamma, beta):
 
 def fc_nchunk(B):
     return _cabi.lib.explainn_fc_nchunk(B)
+
+
+# ------------------------------------------------------------------------------------------ tensor-core conv
+def conv_tc_prepare(w, bias, gamma, beta, mean, var, eps=1e-5):
+    U, four, F = w.shape
+    images = torch.empty(_cabi.lib.explainn_conv_tc_image_halfs(U, F), dtype=torch.float16, device=w.device)
+    call("explainn_conv_tc_prepare", ptr(w.contiguous()), ptr(bias), ptr(gamma), ptr(beta), ptr(mean), ptr(var), float(eps),
+         U, F, ptr(images), stream())
+    return images, U, F
+
+
+def conv_pool_fwd_tc(pk, tcprep):
+    images, U, F = tcprep
+    P = pooled_len(pk.L, F)
+    pooled = torch.empty((pk.B, U, P), dtype=torch.float32, device=pk.codes.device)
+    if pk.B:
+        call("explainn_conv_pool_fwd_tc", ptr(pk.codes), ptr(pk.nmask), pk.B, pk.L, U, F, ptr(images), ptr(pooled), stream())
+    return pooled
+
+
+def conv_pool_fwd_train_tc(pk, tcprep, gamma, beta):
+    images, U, F = tcprep
+    P = pooled_len(pk.L, F)
+    dev = pk.codes.device
+    pooled = torch.empty((pk.B, U, P), dtype=torch.float32, device=dev)
+    xhat = torch.empty((pk.B, U, P), dtype=torch.float32, device=dev)
+    idx = torch.empty((pk.B, U, P), dtype=torch.uint8, device=dev)
+    call("explainn_conv_pool_fwd_train_tc", ptr(pk.codes), ptr(pk.nmask), pk.B, pk.L, U, F, ptr(images), ptr(gamma), ptr(beta),
+         ptr(pooled), ptr(xhat), ptr(idx), stream())
+    return pooled, xhat, idx

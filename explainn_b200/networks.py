@@ -73,7 +73,7 @@ class _UnitStackPrefix(nn.Module):
     def forward(self, x):
         if self._stop == 3:
             return self._owner._activations(x, torch.float32)
-        return self._owner._pooled(x).permute(1, 0, 2).contiguous()
+        return self._owner._pooled(x)
 
 
 class ExplaiNN(nn.Module):
@@ -172,7 +172,7 @@ class ExplaiNN(nn.Module):
         return Fn.unit_activations(pk, self._conv_prep_eval(), dtype)
 
     def _pooled(self, x):
-        """max-pooled activations, unit-major (U,B,P)."""
+        """max-pooled activations (B,U,P)."""
         if self._bn_uses_batch_stats():
             raise RuntimeError("model.linears[:4] on the fused path needs eval() mode")
         pk = self._pack(x)

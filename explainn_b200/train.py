@@ -127,7 +127,7 @@ class FusedTrainer:
         g = torch.cuda.CUDAGraph()
         l0 = _cabi.LAUNCHES
         try:
-            with torch.cuda.graph(g):
+            with torch.cuda.graph(g, capture_error_mode="thread_local"):
                 self._seed_ctr.add_(1)
                 self._gloss = self._fwd_bwd(self._gx, self._gy, seed, self._seed_ctr)
             self._graph_launches = _cabi.LAUNCHES - l0

@@ -67,19 +67,34 @@ int explainn_conv_prepare(const float *w, const float *bias, const float *gamma,
                           float *wq_t, float *shift, float *scale, cudaStream_t stream);
 
 /* ---- fused conv + BN + exp + maxpool(7,7) forward -----------------------------------------------------
- * Replaces linears[0..3] (explainn/models/networks.py:98-102).  pooled: (U,B,P) -- UNIT-MAJOR, so that the
- * (unit, 128-sequence) tile the FC kernels work on is one contiguous block. */
+ * Replaces linears[0..3] (explainn/models/networks.py:98-102).  pooled: (B,U,P), the reference's layout. */
 int explainn_conv_pool_fwd(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F,
                            const float *tables, const float *wq_t, const float *shift, float *pooled,
                            cudaStream_t stream);
 
 /* Training variant: tables built with gamma=1, beta=0 and the batch statistics, so the scan yields
  * x_hat = (y-mu)/sigma; z = gamma*x_hat+beta.  Also returns x_hat at the window maximum and the
- * first-max index inside the window (MaxPool1d backward routing).  pooled/xhat (U,B,P) fp32, idx (U,B,P) u8. */
+ * first-max index inside the window (MaxPool1d backward routing).  pooled/xhat (B,U,P) fp32, idx (B,U,P) u8. */
 int explainn_conv_pool_fwd_train(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F,
                                  const float *tables, const float *wq_t, const float *shift,
                                  const float *gamma, const float *beta, float *pooled, float *xhat,
                                  unsigned char *idx, cudaStream_t stream);
+
+/* ---- tensor-core variant of the fused conv forward (tcgen05 / TMEM) ----------------------------------------------
+ * Same reference lines as explainn_conv_pool_fwd[_train] (explainn/models/networks.py:98-102,153).  The conv is
+ * evaluated as an fp16 GEMM (one-hot operand exact; fp32 weights split into two fp16 pieces, fp32 accumulation in
+ * tensor memory), so results agree with the table kernel to fp32 rounding, not bit for bit; the interpretation
+ * entry points keep the table kernel.  images: explainn_conv_tc_image_halfs(U,F) fp16 values written by
+ * explainn_conv_tc_prepare (arguments as explainn_conv_prepare).  Outputs as in the table variants (B,U,P). */
+long long explainn_conv_tc_image_halfs(int U, int F);
+int explainn_conv_tc_prepare(const float *w, const float *bias, const float *gamma, const float *beta,
+                             const float *mean, const float *var, float eps, int U, int F, void *images,
+                             cudaStream_t stream);
+int explainn_conv_pool_fwd_tc(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F,
+                              const void *images, float *pooled, cudaStream_t stream);
+int explainn_conv_pool_fwd_train_tc(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F,
+                                    const void *images, const float *gamma, const float *beta, float *pooled,
+                                    float *xhat, unsigned char *idx, cudaStream_t stream);
 
 /* ---- activation scan ------------------------------------------------------------------------------------
  * Replaces `model.linears[:3](seq.repeat(...))` + `.astype(np.half)`
@@ -120,7 +135,7 @@ int explainn_interp_pwm_count(const uint32_t *codes, const uint32_t *nmask, long
 /* ---- per-unit FC stack, eval mode -----------------------------------------------------------------------
  * Replaces linears[4..13] with BatchNorm in eval mode (explainn/models/networks.py:103-116): grouped 1x1
  * Conv1d(U*P->100U) -> BN -> ReLU -> (Dropout = identity) -> grouped 1x1 Conv1d(100U->U) -> BN -> ReLU.
- * pooled (U,B,P); W1 = linears.6.weight (100U,P); b1 (100U); bn2_* (100U); W2 = linears.10.weight (U,100);
+ * pooled (B,U,P); W1 = linears.6.weight (100U,P); b1 (100U); bn2_* (100U); W2 = linears.10.weight (U,100);
  * b2 (U); bn3_* (U).  unit_out: (B,U), the tensor get_explainn_unit_outputs returns
  * (explainn/interpretation/interpretation.py:82-99). */
 int explainn_fc_stack_fwd_eval(const float *pooled, long long B, int U, int P, const float *W1, const float *b1,
@@ -166,7 +181,7 @@ int explainn_fc_stack_fwd_train(const float *pooled, long long B, int U, int P, 
                                 cudaStream_t stream);
 
 /* ---- backward of FC stack + final linear (autograd of networks.py:103-116,147; explainn/train/train.py:65) ---
- * glogits (B,C).  Scratch: gh2 (U,B), pb2 (U,nchunk,3,100), dW1_partials (nchunk,U,100,P).  Outputs: gpool (U,B,P)
+ * glogits (B,C).  Scratch: gh2 (U,B), pb2 (U,nchunk,3,100), dW1_partials (nchunk,U,100,P).  Outputs: gpool (B,U,P)
  * = d loss / d pooled, and the parameter gradients (any of db1..dbf may be NULL to skip it).  The gradients of
  * the biases that feed a train-mode BatchNorm (b1, b2) are written as exact zeros.  Wf == NULL: glogits is the
  * gradient w.r.t. the unit outputs (B,U) (caller differentiates `model.linears(x)`), dWf/dbf are not written. */
