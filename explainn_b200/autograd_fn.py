@@ -71,8 +71,13 @@ def train_forward(model, x, params=None, seed=None, seed_dev=None):
     ws.mean1, ws.var1, ws.Mw = Fn.bn1_batch_stats(ws.M, cw, cb, B * S, bn1.momentum, bn1.running_mean, bn1.running_var,
                                                   bn1.num_batches_tracked)
     ones, zeros = _const(dev, U)
-    prep = Fn.conv_prepare(cw, cb, ones, zeros, ws.mean1, ws.var1, bn1.eps)   # tables of x_hat = (y - mu) / sigma
-    ws.pooled, ws.xhat, ws.idx = Fn.conv_pool_fwd_train(pk, prep, g1, b1n)
+    # the conv is prepared with gamma=1, beta=0 and the batch statistics, so the scan yields x_hat = (y - mu) / sigma
+    if getattr(model, "conv_backend", "tc") == "tc":
+        tcp = Fn.conv_tc_prepare(cw, cb, ones, zeros, ws.mean1, ws.var1, bn1.eps)
+        ws.pooled, ws.xhat, ws.idx = Fn.conv_pool_fwd_train_tc(pk, tcp, g1, b1n)
+    else:
+        prep = Fn.conv_prepare(cw, cb, ones, zeros, ws.mean1, ws.var1, bn1.eps)
+        ws.pooled, ws.xhat, ws.idx = Fn.conv_pool_fwd_train(pk, prep, g1, b1n)
     nchunk = ws.nchunk = Fn.fc_nchunk(B)
     f32 = dict(dtype=torch.float32, device=dev)
     ws.h1 = torch.empty((U, B, H), **f32)

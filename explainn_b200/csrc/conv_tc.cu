@@ -24,7 +24,7 @@ namespace {
 constexpr int TC_M = 128;          // units per tile (TMEM lanes)
 constexpr int TC_N = 240;          // positions per tile (TMEM columns), 34 windows of 7 = 238 used
 constexpr int TC_WIN = 34;         // pool windows per tile
-constexpr int TC_THREADS = 256;    // warps 0-3: epilogue (lane quarter = warp), warps 4-7: producers
+constexpr int TC_THREADS = 512;    // 16 warps: lane quarter = warp & 3, column range = warp >> 2
 
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -89,15 +89,17 @@ __device__ __forceinline__ void tc_ld16(uint32_t taddr, float (&v)[32])
 // ------------------------------------------------------------------------------------------------
 // A-operand images: per 128-unit tile, [hi | lo] x canonical K-major layout
 //   byte offset of element (row r, k) inside one image = (r/8)*KC*128 + (k/8)*128 + (r%8)*16 + (k%8)*2
+// shift[u] (fp32) is added in the epilogue.
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) tc_prepare_kernel(const float *__restrict__ w, const float *__restrict__ bias,
                                                          const float *__restrict__ gamma, const float *__restrict__ beta,
                                                          const float *__restrict__ mean, const float *__restrict__ var, float eps,
-                                                         int U, int F, int K, __half *__restrict__ images)
+                                                         int U, int F, int K, __half *__restrict__ images, float *__restrict__ shift)
 {
     const int mt = blockIdx.x, KC = K / 8;
     __half *hi = images + (size_t)mt * 2 * TC_M * K, *lo = hi + (size_t)TC_M * K;
-    for (int i = threadIdx.x; i < TC_M * K; i += blockDim.x) {
+    // grid (n_mt, 8): block y handles 16 rows of the tile
+    for (int i = blockIdx.y * 16 * K + threadIdx.x; i < (blockIdx.y + 1) * 16 * K; i += blockDim.x) {
         const int r = i / K, k = i - r * K;
         const int u = mt * TC_M + r;
         float v = 0.0f;
@@ -106,9 +108,8 @@ __global__ void __launch_bounds__(256) tc_prepare_kernel(const float *__restrict
             if (k < 4 * F) {
                 const int tap = k >> 2, c = k & 3;
                 v = __fmul_rn(w[((size_t)u * 4 + c) * F + tap], sc);
-            } else if (k == 4 * F) {
-                v = __fadd_rn(__fmul_rn(__fsub_rn(bias[u], mean[u]), sc), beta[u]);
             }
+            if (k == 0) shift[u] = __fadd_rn(__fmul_rn(__fsub_rn(bias[u], mean[u]), sc), beta[u]);
         }
         const __half h = __float2half_rn(v);
         const __half l = __float2half_rn(v - __half2float(h));
@@ -123,11 +124,50 @@ struct TcArgs {
     long long B;
     int L, F, U, K, P, wc, wm;
     const __half *images;
+    const float *shift;     // (U)
     float *pooled;          // (B,U,P)
     float *xhat;            // train only
     unsigned char *idx;     // train only
     const float *gamma, *beta;
 };
+
+constexpr int TC_VROWS = TC_N + 64;     // dinucleotide entries per tile: positions n0 .. n0 + 240 + 2*KC
+
+// Epilogue of one accumulator for the columns [C0, C1) (whole pool windows), one unit per thread.
+template <bool TRAIN, int C0, int C1>
+__device__ __forceinline__ void tc_drain(uint32_t taddr, int row, int nwin, int sst, int plane, float *stage, float shift, float gam,
+                                         float bet)
+{
+    constexpr int CB0 = C0 / 32, CB1 = (C1 + 31) / 32;
+    float m = 0.f, xb = 0.f;
+    int ib = 0;
+#pragma unroll
+    for (int cb = CB0; cb < CB1; ++cb) {
+        float v[32];
+        if (cb * 32 + 32 <= TC_N) tc_ld32(taddr + cb * 32, v);
+        else tc_ld16(taddr + cb * 32, v);
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+            const int col = cb * 32 + j;
+            if (col < C0 || col >= C1) continue;
+            const int ph = col % XB_POOL, win = col / XB_POOL;
+            if (TRAIN) {
+                const float x = v[j] + shift;
+                const float z = fmaf(gam, x, bet);
+                if (ph == 0 || z > m) { m = z; xb = x; ib = ph; }
+            } else {
+                m = ph == 0 ? v[j] : fmaxf(m, v[j]);
+            }
+            if (ph == XB_POOL - 1 && win < nwin) {
+                stage[row * sst + win] = __expf(TRAIN ? m : m + shift);
+                if (TRAIN) {
+                    stage[plane + row * sst + win] = xb;
+                    reinterpret_cast<unsigned char *>(stage + 2 * plane)[row * sst + win] = (unsigned char)ib;
+                }
+            }
+        }
+    }
+}
 
 template <bool TRAIN>
 __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const TcArgs a)
@@ -138,23 +178,23 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const TcArgs a)
 
     const int K = a.K, KC = K / 8, KS = K / 16;
     const uint32_t a_bytes = (uint32_t)TC_M * K * 2;        // one image (hi or lo)
-    const uint32_t b_bytes = (uint32_t)TC_N * K * 2;
     unsigned char *sA = smem;                               // hi, lo
-    unsigned char *sB = sA + 2 * a_bytes;                   // 2 buffers
+    // X operand: V[pos] = 16 bytes = one-hot fp16 of (base(pos), base(pos+1)), 16-byte pitch.  Row n of the im2col
+    // matrix is V[n], V[n+2], V[n+4], ... so the K-major core-matrix layout is the V array itself with
+    // LBO = 32 B (next K chunk = two positions on) and SBO = 128 B (next 8 rows): no expansion is ever written.
+    uint4 *sV = reinterpret_cast<uint4 *>(sA + 2 * a_bytes);            // 2 buffers x TC_VROWS
     // staging: [128][sst] floats per plane (pooled; + x_hat, argmax when TRAIN).  With a single chunk per sequence
     // the row stride is P itself, so a plane is the exact image of pooled[b][u0..u0+127][:] and leaves with ONE
     // TMA bulk store.
     const int sst = a.P <= TC_WIN ? a.P : TC_WIN + 1;
-    float *stage = reinterpret_cast<float *>(sB + 2 * b_bytes);
+    float *stage = reinterpret_cast<float *>(sV + 2 * TC_VROWS);
     const int plane = TC_M * (TC_WIN + 1);
-    unsigned char *sseq = reinterpret_cast<unsigned char *>(stage + (TRAIN ? 3 : 1) * plane);   // 2 x seq bytes
-    const int seq_pad = ((a.L + 64 + 15) / 16) * 16;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n_mt = (a.U + TC_M - 1) / TC_M;
     const int nchunk = (a.P + TC_WIN - 1) / TC_WIN;
 
-    // work split: CTA -> (m-tile, contiguous range of (sequence, chunk) items)
+    // work split: CTA -> contiguous range of (m-tile, sequence, chunk) items
     const long long items_per_mt = a.B * nchunk;
     const long long total = items_per_mt * n_mt;
     const long long it0 = total * blockIdx.x / gridDim.x, it1 = total * (blockIdx.x + 1) / gridDim.x;
@@ -176,73 +216,44 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const TcArgs a)
 
     // instruction descriptor: f16 x f16 -> f32, M=128, N=240, both operands K-major
     const uint32_t idesc = (1u << 4) | ((uint32_t)(TC_N >> 3) << 17) | ((uint32_t)(TC_M >> 4) << 24);
-    const uint32_t lbo = 128, sbo = (uint32_t)KC * 128;
 
     uint32_t a_parity = 0;
     uint32_t full_parity[2] = {0, 0};
+    // current item, advanced incrementally (no 64-bit divisions in the loop)
+    int mt = (int)(it0 / items_per_mt);
+    long long b = (it0 - (long long)mt * items_per_mt) / nchunk;
+    int chunk = (int)((it0 - (long long)mt * items_per_mt) - b * nchunk);
     int cur_mt = -1;
     long long it = it0;
-    int issued = 0;                      // number of tiles issued so far by this CTA (buffer = issued & 1)
-    // descriptor of the previous tile (for the deferred epilogue)
+    int issued = 0;
     long long prev_b = -1;
     int prev_chunk = 0, prev_buf = 0, prev_u0 = 0;
     bool have_prev = false;
+    const int row = 32 * (warp & 3) + lane;       // TMEM lane = unit inside the tile
+    float shift = 0.f, gam = 1.f, bet = 0.f;
 
-    auto epilogue = [&](long long b, int chunk, int buf, int u0) {
-        // warps 0-3: drain TMEM buffer `buf` (unit = u0 + 32*warp + lane), pool, exp, stage
-        const int w0 = chunk * TC_WIN;
-        const int nwin = min(TC_WIN, a.P - w0);
-        if (warp < 4) {
-            mbar_wait(&bar_full[buf], full_parity[buf]);
-            tc_fence_after();
-            const uint32_t taddr = tmem_base + ((uint32_t)(32 * warp) << 16) + (uint32_t)buf * 256u;
-            const int row = 32 * warp + lane;
-            float gam = 1.f, bet = 0.f;
-            if (TRAIN) {
-                const int u = u0 + row;
-                gam = u < a.U ? a.gamma[u] : 1.f;
-                bet = u < a.U ? a.beta[u] : 0.f;
-            }
-            float m = 0.f, xb = 0.f;
-            int ib = 0;
-#pragma unroll
-            for (int cb = 0; cb < 8; ++cb) {
-                float v[32];
-                if (cb < 7) tc_ld32(taddr + cb * 32, v);
-                else tc_ld16(taddr + cb * 32, v);
-#pragma unroll
-                for (int j = 0; j < (cb < 7 ? 32 : 16); ++j) {
-                    const int col = cb * 32 + j;
-                    if (col >= TC_WIN * XB_POOL) break;
-                    const int ph = col % XB_POOL, win = col / XB_POOL;
-                    if (TRAIN) {
-                        const float z = fmaf(gam, v[j], bet);
-                        if (ph == 0 || z > m) { m = z; xb = v[j]; ib = ph; }
-                    } else {
-                        m = ph == 0 ? v[j] : fmaxf(m, v[j]);
-                    }
-                    if (ph == XB_POOL - 1) {
-                        if (win < nwin) {
-                            stage[row * sst + win] = __expf(m);
-                            if (TRAIN) {
-                                stage[plane + row * sst + win] = xb;
-                                reinterpret_cast<unsigned char *>(stage + 2 * plane)[row * sst + win] = (unsigned char)ib;
-                            }
-                        }
-                    }
-                }
-            }
-            tc_fence_before();
-        }
+    auto epilogue = [&](int pchunk, int buf) {
+        const int nwin = min(TC_WIN, a.P - pchunk * TC_WIN);
+        mbar_wait(&bar_full[buf], full_parity[buf]);
         full_parity[buf] ^= 1;
-        (void)b; (void)u0;
+        tc_fence_after();
+        const uint32_t taddr = tmem_base + ((uint32_t)(32 * (warp & 3)) << 16) + (uint32_t)buf * 256u;
+        // four warps share a lane quarter; each drains a range of whole windows: 9 + 9 + 8 + 8 = 34
+        constexpr int S1 = 9 * XB_POOL, S2 = 18 * XB_POOL, S3 = 26 * XB_POOL, S4 = TC_WIN * XB_POOL;
+        switch (warp >> 2) {
+        case 0: tc_drain<TRAIN, 0, S1>(taddr, row, nwin, sst, plane, stage, shift, gam, bet); break;
+        case 1: tc_drain<TRAIN, S1, S2>(taddr, row, nwin, sst, plane, stage, shift, gam, bet); break;
+        case 2: tc_drain<TRAIN, S2, S3>(taddr, row, nwin, sst, plane, stage, shift, gam, bet); break;
+        default: tc_drain<TRAIN, S3, S4>(taddr, row, nwin, sst, plane, stage, shift, gam, bet); break;
+        }
+        tc_fence_before();
     };
 
-    auto store_stage = [&](long long b, int chunk, int u0) {
-        const int w0 = chunk * TC_WIN;
+    auto store_stage = [&](long long sb_, int pchunk, int u0) {
+        const int w0 = pchunk * TC_WIN;
         const int nwin = min(TC_WIN, a.P - w0);
         const int nvalid = min(TC_M, a.U - u0);
-        const size_t o = ((size_t)b * a.U + u0) * a.P;
+        const size_t o = ((size_t)sb_ * a.U + u0) * a.P;
         const uint32_t bytes = (uint32_t)nvalid * a.P * 4;
         // when the staged planes are exact images of the global tiles they leave as TMA bulk stores
         const bool bulk_f = sst == a.P && (bytes & 15u) == 0 && ((o * 4) & 15u) == 0;
@@ -261,7 +272,17 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const TcArgs a)
                 asm volatile("cp.async.bulk.commit_group;" ::: "memory");
             }
         }
-        if (!bulk_f || (TRAIN && !bulk_i)) {
+        if (sst == a.P) {
+            // single chunk per sequence: the planes are contiguous images, copy them flat
+            const int nel = nvalid * a.P;
+            if (!bulk_f)
+                for (int i = threadIdx.x; i < nel; i += TC_THREADS) {
+                    a.pooled[o + i] = stage[i];
+                    if (TRAIN) a.xhat[o + i] = stage[plane + i];
+                }
+            if (TRAIN && !bulk_i)
+                for (int i = threadIdx.x; i < nel; i += TC_THREADS) a.idx[o + i] = reinterpret_cast<unsigned char *>(stage + 2 * plane)[i];
+        } else if (!bulk_f || (TRAIN && !bulk_i)) {
             for (int r = warp; r < nvalid; r += TC_THREADS / 32) {
                 const size_t orow = o + (size_t)r * a.P + w0;
                 for (int c = lane; c < nwin; c += 32) {
@@ -279,18 +300,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const TcArgs a)
 
     while (it < it1 || have_prev) {
         const bool have_cur = it < it1;
-        int mt = 0, chunk = 0, buf = issued & 1, u0 = 0;
-        long long b = 0;
+        const int buf = issued & 1;
+        const int u0 = mt * TC_M;
         if (have_cur) {
-            mt = (int)(it / items_per_mt);
-            const long long rem = it - (long long)mt * items_per_mt;
-            b = rem / nchunk;
-            chunk = (int)(rem - b * nchunk);
-            u0 = mt * TC_M;
             if (mt != cur_mt) {
-                // a new unit tile: the previous tile's MMAs must be done with sA before it is overwritten
+                // a new unit tile: every MMA that reads sA must be finished before it is overwritten
                 if (have_prev) {
-                    epilogue(prev_b, prev_chunk, prev_buf, prev_u0);
+                    epilogue(prev_chunk, prev_buf);
                     __syncthreads();
                     store_stage(prev_b, prev_chunk, prev_u0);
                     have_prev = false;
@@ -300,42 +316,40 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const TcArgs a)
                     mbar_arrive_expect_tx(&bar_a, 2 * a_bytes);
                     tma_bulk_g2s(sA, reinterpret_cast<const unsigned char *>(a.images) + (size_t)mt * 2 * a_bytes, 2 * a_bytes, &bar_a);
                 }
+                const int u = u0 + row;
+                shift = u < a.U ? a.shift[u] : 0.f;
+                if (TRAIN) {
+                    gam = u < a.U ? a.gamma[u] : 1.f;
+                    bet = u < a.U ? a.beta[u] : 0.f;
+                }
                 mbar_wait(&bar_a, a_parity);
                 a_parity ^= 1;
                 cur_mt = mt;
             }
-            // ---- expand the sequence into bytes (code 0..3, 4 = N) and build the X tile ----
-            unsigned char *sb = sseq + (size_t)buf * seq_pad;
-            for (int i = threadIdx.x; i < seq_pad; i += TC_THREADS) {
-                unsigned v = 4;
-                if (i < a.L) {
-                    const unsigned c = (a.codes[b * a.wc + (i >> 4)] >> (2 * (i & 15))) & 3u;
-                    const unsigned mk = (a.nmask[b * a.wm + (i >> 5)] >> (i & 31)) & 1u;
-                    v = mk ? 4u : c;
-                }
-                sb[i] = (unsigned char)v;
-            }
-            __syncthreads();
+            // ---- V entries of this tile: positions n0 .. n0 + TC_VROWS ----
             {
-                unsigned char *Bt = sB + (size_t)buf * b_bytes;
+                uint4 *V = sV + buf * TC_VROWS;
                 const int n0 = chunk * TC_WIN * XB_POOL;
-                const int F = a.F;
-                for (int q = threadIdx.x; q < TC_N * KC; q += TC_THREADS) {
-                    const int kc = q / TC_N, n = q - kc * TC_N;        // consecutive threads -> consecutive rows
-                    const int t0 = 2 * kc, t1 = t0 + 1;
-                    unsigned long long lo64 = 0ull, hi64 = 0ull;
-                    const int p0 = n0 + n + t0;
-                    if (t0 < F) {
-                        const unsigned c = p0 < seq_pad ? sb[p0] : 4u;
-                        if (c < 4u) lo64 = 0x3C00ull << (16 * c);
-                    } else if (t0 == F) lo64 = 0x3C00ull;
-                    if (t1 < F) {
-                        const unsigned c = p0 + 1 < seq_pad ? sb[p0 + 1] : 4u;
-                        if (c < 4u) hi64 = 0x3C00ull << (16 * c);
-                    } else if (t1 == F) hi64 = 0x3C00ull;
+                const uint32_t *cw = a.codes + b * a.wc;
+                const uint32_t *mw = a.nmask + b * a.wm;
+                for (int i = threadIdx.x; i < TC_VROWS; i += TC_THREADS) {
+                    const int p0 = n0 + i;
+                    uint32_t c0 = 4, c1 = 4;
+                    if (p0 < a.L) {
+                        c0 = (cw[p0 >> 4] >> (2 * (p0 & 15))) & 3u;
+                        if ((mw[p0 >> 5] >> (p0 & 31)) & 1u) c0 = 4;
+                    }
+                    if (p0 + 1 < a.L) {
+                        c1 = (cw[(p0 + 1) >> 4] >> (2 * ((p0 + 1) & 15))) & 3u;
+                        if ((mw[(p0 + 1) >> 5] >> ((p0 + 1) & 31)) & 1u) c1 = 4;
+                    }
+                    // one-hot fp16 quadruple of a base: 1.0 (0x3C00) in half c, N -> all zero
                     uint4 val;
-                    val.x = (uint32_t)lo64; val.y = (uint32_t)(lo64 >> 32); val.z = (uint32_t)hi64; val.w = (uint32_t)(hi64 >> 32);
-                    *reinterpret_cast<uint4 *>(Bt + (size_t)(n >> 3) * sbo + (size_t)kc * 128 + (n & 7) * 16) = val;
+                    val.x = c0 == 0 ? 0x00003C00u : (c0 == 1 ? 0x3C000000u : 0u);
+                    val.y = c0 == 2 ? 0x00003C00u : (c0 == 3 ? 0x3C000000u : 0u);
+                    val.z = c1 == 0 ? 0x00003C00u : (c1 == 1 ? 0x3C000000u : 0u);
+                    val.w = c1 == 2 ? 0x00003C00u : (c1 == 3 ? 0x3C000000u : 0u);
+                    V[i] = val;
                 }
             }
             fence_proxy_async();
@@ -345,18 +359,19 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const TcArgs a)
             if (threadIdx.x == 0) {
                 tc_fence_after();
                 const uint32_t d = tmem_base + (uint32_t)buf * 256u;
-                const uint32_t a_hi = smem_u32(sA), a_lo = a_hi + a_bytes, bt = smem_u32(sB + (size_t)buf * b_bytes);
+                const uint32_t a_hi = smem_u32(sA), a_lo = a_hi + a_bytes, bt = smem_u32(sV + buf * TC_VROWS);
+                const uint32_t a_lbo = 128, a_sbo = (uint32_t)KC * 128;
                 for (int ks = 0; ks < KS; ++ks) {
-                    const uint64_t bd = make_smem_desc(bt + ks * 256, lbo, sbo);
-                    tc_mma_f16(d, make_smem_desc(a_hi + ks * 256, lbo, sbo), bd, idesc, ks > 0 ? 1u : 0u);
-                    tc_mma_f16(d, make_smem_desc(a_lo + ks * 256, lbo, sbo), bd, idesc, 1u);
+                    const uint64_t bd = make_smem_desc(bt + ks * 64, 32, 128);
+                    tc_mma_f16(d, make_smem_desc(a_hi + ks * 256, a_lbo, a_sbo), bd, idesc, ks > 0 ? 1u : 0u);
+                    tc_mma_f16(d, make_smem_desc(a_lo + ks * 256, a_lbo, a_sbo), bd, idesc, 1u);
                 }
                 tc_commit(&bar_full[buf]);
             }
         }
         // ---- epilogue of the previous tile overlaps the MMAs just issued ----
         if (have_prev) {
-            epilogue(prev_b, prev_chunk, prev_buf, prev_u0);
+            epilogue(prev_chunk, prev_buf);
             __syncthreads();
             store_stage(prev_b, prev_chunk, prev_u0);
             have_prev = false;
@@ -366,6 +381,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const TcArgs a)
             have_prev = true;
             ++issued;
             ++it;
+            if (++chunk == nchunk) {
+                chunk = 0;
+                if (++b == a.B) { b = 0; ++mt; }
+            }
         }
         __syncthreads();
     }
@@ -379,7 +398,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const TcArgs a)
     }
 }
 
-int tc_K(int F) { return ((4 * F + 1 + 15) / 16) * 16; }
+int tc_K(int F) { return ((4 * F + 15) / 16) * 16; }
 
 }  // namespace
 
@@ -391,22 +410,23 @@ extern "C" long long explainn_conv_tc_image_halfs(int U, int F)
 
 extern "C" int explainn_conv_tc_prepare(const float *w, const float *bias, const float *gamma, const float *beta,
                                         const float *mean, const float *var, float eps, int U, int F, void *images,
-                                        cudaStream_t stream)
+                                        float *shift, cudaStream_t stream)
 {
-    XB_REQUIRE(w && bias && gamma && beta && mean && var && images && U >= 1 && F >= 1, "conv_tc_prepare: bad argument");
+    XB_REQUIRE(w && bias && gamma && beta && mean && var && images && shift && U >= 1 && F >= 1, "conv_tc_prepare: bad argument");
     if (F > 4 * XB_MAX_G) {
         xb_set_error("conv_tc_prepare: filter_size %d not supported (max %d)", F, 4 * XB_MAX_G);
         return XB_ERR_UNSUPPORTED;
     }
     const int n_mt = (U + TC_M - 1) / TC_M;
-    tc_prepare_kernel<<<n_mt, 256, 0, stream>>>(w, bias, gamma, beta, mean, var, eps, U, F, tc_K(F), (__half *)images);
+    tc_prepare_kernel<<<dim3(n_mt, 8), 256, 0, stream>>>(w, bias, gamma, beta, mean, var, eps, U, F, tc_K(F), (__half *)images, shift);
     return xb_check_launch("conv_tc_prepare");
 }
 
 static int launch_tc(bool train, const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F, const void *images,
-                     const float *gamma, const float *beta, float *pooled, float *xhat, unsigned char *idx, cudaStream_t stream)
+                     const float *shift, const float *gamma, const float *beta, float *pooled, float *xhat, unsigned char *idx,
+                     cudaStream_t stream)
 {
-    XB_REQUIRE(codes && nmask && images && pooled && B >= 0 && U >= 1, "conv_pool_fwd_tc: bad argument");
+    XB_REQUIRE(codes && nmask && images && shift && pooled && B >= 0 && U >= 1, "conv_pool_fwd_tc: bad argument");
     if (F < 1 || F > 4 * XB_MAX_G || L < F + XB_POOL - 1) {
         xb_set_error("conv_pool_fwd_tc: unsupported geometry L=%d filter_size=%d", L, F);
         return XB_ERR_UNSUPPORTED;
@@ -416,9 +436,8 @@ static int launch_tc(bool train, const uint32_t *codes, const uint32_t *nmask, l
     a.codes = codes; a.nmask = nmask; a.B = B; a.L = L; a.F = F; a.U = U; a.K = tc_K(F);
     a.P = ((L - F + 1) - XB_POOL) / XB_POOL + 1;
     a.wc = xb_words_codes(L); a.wm = xb_words_mask(L);
-    a.images = (const __half *)images; a.pooled = pooled; a.xhat = xhat; a.idx = idx; a.gamma = gamma; a.beta = beta;
-    const int seq_pad = ((L + 64 + 15) / 16) * 16;
-    const size_t smem = (size_t)2 * TC_M * a.K * 2 + (size_t)2 * TC_N * a.K * 2 + (size_t)(train ? 3 : 1) * TC_M * (TC_WIN + 1) * 4 + 2 * (size_t)seq_pad;
+    a.images = (const __half *)images; a.shift = shift; a.pooled = pooled; a.xhat = xhat; a.idx = idx; a.gamma = gamma; a.beta = beta;
+    const size_t smem = (size_t)2 * TC_M * a.K * 2 + (size_t)2 * TC_VROWS * 16 + (size_t)(train ? 3 : 1) * TC_M * (TC_WIN + 1) * 4;
     if (smem > 227 * 1024) {
         xb_set_error("conv_pool_fwd_tc: %zu bytes of shared memory needed (L=%d, filter_size=%d)", smem, L, F);
         return XB_ERR_UNSUPPORTED;
@@ -443,15 +462,15 @@ static int launch_tc(bool train, const uint32_t *codes, const uint32_t *nmask, l
 }
 
 extern "C" int explainn_conv_pool_fwd_tc(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F,
-                                         const void *images, float *pooled, cudaStream_t stream)
+                                         const void *images, const float *shift, float *pooled, cudaStream_t stream)
 {
-    return launch_tc(false, codes, nmask, B, L, U, F, images, nullptr, nullptr, pooled, nullptr, nullptr, stream);
+    return launch_tc(false, codes, nmask, B, L, U, F, images, shift, nullptr, nullptr, pooled, nullptr, nullptr, stream);
 }
 
 extern "C" int explainn_conv_pool_fwd_train_tc(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F,
-                                               const void *images, const float *gamma, const float *beta, float *pooled,
-                                               float *xhat, unsigned char *idx, cudaStream_t stream)
+                                               const void *images, const float *shift, const float *gamma, const float *beta,
+                                               float *pooled, float *xhat, unsigned char *idx, cudaStream_t stream)
 {
     XB_REQUIRE(gamma && beta && xhat && idx, "conv_pool_fwd_train_tc: null pointer");
-    return launch_tc(true, codes, nmask, B, L, U, F, images, gamma, beta, pooled, xhat, idx, stream);
+    return launch_tc(true, codes, nmask, B, L, U, F, images, shift, gamma, beta, pooled, xhat, idx, stream);
 }

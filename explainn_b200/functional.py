@@ -186,27 +186,29 @@ def fc_nchunk(B):
 def conv_tc_prepare(w, bias, gamma, beta, mean, var, eps=1e-5):
     U, four, F = w.shape
     images = torch.empty(_cabi.lib.explainn_conv_tc_image_halfs(U, F), dtype=torch.float16, device=w.device)
+    shift = torch.empty(U, dtype=torch.float32, device=w.device)
     call("explainn_conv_tc_prepare", ptr(w.contiguous()), ptr(bias), ptr(gamma), ptr(beta), ptr(mean), ptr(var), float(eps),
-         U, F, ptr(images), stream())
-    return images, U, F
+         U, F, ptr(images), ptr(shift), stream())
+    return images, shift, U, F
 
 
 def conv_pool_fwd_tc(pk, tcprep):
-    images, U, F = tcprep
+    images, shift, U, F = tcprep
     P = pooled_len(pk.L, F)
     pooled = torch.empty((pk.B, U, P), dtype=torch.float32, device=pk.codes.device)
     if pk.B:
-        call("explainn_conv_pool_fwd_tc", ptr(pk.codes), ptr(pk.nmask), pk.B, pk.L, U, F, ptr(images), ptr(pooled), stream())
+        call("explainn_conv_pool_fwd_tc", ptr(pk.codes), ptr(pk.nmask), pk.B, pk.L, U, F, ptr(images), ptr(shift), ptr(pooled),
+             stream())
     return pooled
 
 
 def conv_pool_fwd_train_tc(pk, tcprep, gamma, beta):
-    images, U, F = tcprep
+    images, shift, U, F = tcprep
     P = pooled_len(pk.L, F)
     dev = pk.codes.device
     pooled = torch.empty((pk.B, U, P), dtype=torch.float32, device=dev)
     xhat = torch.empty((pk.B, U, P), dtype=torch.float32, device=dev)
     idx = torch.empty((pk.B, U, P), dtype=torch.uint8, device=dev)
-    call("explainn_conv_pool_fwd_train_tc", ptr(pk.codes), ptr(pk.nmask), pk.B, pk.L, U, F, ptr(images), ptr(gamma), ptr(beta),
+    call("explainn_conv_pool_fwd_train_tc", ptr(pk.codes), ptr(pk.nmask), pk.B, pk.L, U, F, ptr(images), ptr(shift), ptr(gamma), ptr(beta),
          ptr(pooled), ptr(xhat), ptr(idx), stream())
     return pooled, xhat, idx

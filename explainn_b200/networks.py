@@ -130,6 +130,9 @@ class ExplaiNN(nn.Module):
         self.linears._bind(self)
         self.final = nn.Linear(U, num_classes)
         self._invalid = None      # lazily read counter of non-one-hot input columns
+        # "tc": tcgen05/TMEM implicit-GEMM conv for inference and the training forward (fp32-rounding accurate);
+        # "lut": the k-mer table kernel (bit-identical to the CPU oracle).  The interpretation pass always uses "lut".
+        self.conv_backend = "tc"
         if weight_path:
             self.load_state_dict(torch.load(weight_path))
 
@@ -176,6 +179,11 @@ class ExplaiNN(nn.Module):
         if self._bn_uses_batch_stats():
             raise RuntimeError("model.linears[:4] on the fused path needs eval() mode")
         pk = self._pack(x)
+        if self.conv_backend == "tc":
+            conv, bn = self.linears[0], self.linears[1]
+            tcp = Fn.conv_tc_prepare(conv.weight.detach(), conv.bias.detach(), bn.weight.detach(), bn.bias.detach(),
+                                     bn.running_mean, bn.running_var, bn.eps)
+            return Fn.conv_pool_fwd_tc(pk, tcp)
         return Fn.conv_pool_fwd(pk, self._conv_prep_eval())
 
     def _unit_outputs_eval(self, x):

@@ -85,16 +85,16 @@ int explainn_conv_pool_fwd_train(const uint32_t *codes, const uint32_t *nmask, l
  * evaluated as an fp16 GEMM (one-hot operand exact; fp32 weights split into two fp16 pieces, fp32 accumulation in
  * tensor memory), so results agree with the table kernel to fp32 rounding, not bit for bit; the interpretation
  * entry points keep the table kernel.  images: explainn_conv_tc_image_halfs(U,F) fp16 values written by
- * explainn_conv_tc_prepare (arguments as explainn_conv_prepare).  Outputs as in the table variants (B,U,P). */
+ * explainn_conv_tc_prepare (arguments as explainn_conv_prepare; shift (U) fp32 is added in the epilogue).  Outputs as in the table variants (B,U,P). */
 long long explainn_conv_tc_image_halfs(int U, int F);
 int explainn_conv_tc_prepare(const float *w, const float *bias, const float *gamma, const float *beta,
                              const float *mean, const float *var, float eps, int U, int F, void *images,
-                             cudaStream_t stream);
+                             float *shift, cudaStream_t stream);
 int explainn_conv_pool_fwd_tc(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F,
-                              const void *images, float *pooled, cudaStream_t stream);
+                              const void *images, const float *shift, float *pooled, cudaStream_t stream);
 int explainn_conv_pool_fwd_train_tc(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F,
-                                    const void *images, const float *gamma, const float *beta, float *pooled,
-                                    float *xhat, unsigned char *idx, cudaStream_t stream);
+                                    const void *images, const float *shift, const float *gamma, const float *beta,
+                                    float *pooled, float *xhat, unsigned char *idx, cudaStream_t stream);
 
 /* ---- activation scan ------------------------------------------------------------------------------------
  * Replaces `model.linears[:3](seq.repeat(...))` + `.astype(np.half)`

@@ -40,10 +40,12 @@ def _close(a, b, rtol, name=""):
     assert err <= rtol, "%s: max err %.3e of scale (tol %.1e)" % (name, err, rtol)
 
 
+@pytest.mark.parametrize("backend", ["tc", "lut"])
 @pytest.mark.parametrize("name", TRAIN_GOLDENS)
-def test_train_forward_backward_vs_reference(name):
+def test_train_forward_backward_vs_reference(name, backend):
     g = load_golden(name)
     m = _model(g, "sd0.")
+    m.conv_backend = backend
     x = torch.from_numpy(onehot_from_codes(g["codes"])).to(DEV)
     y = torch.from_numpy(g["labels"]).to(DEV)
     out = m(x)
@@ -128,8 +130,22 @@ def test_two_adam_steps_vs_reference(name, fused):
                 assert np.mean(d > 2e-2 * 2e-3 + 1e-7) <= 2e-3, k
 
 
+def _close_per_unit(got, ref, rtol, name, max_outlier_frac=0.02, outlier_rtol=0.1):
+    """Conv-stage gradients, unit by unit.  MaxPool routes a window's gradient to ONE position; when two
+    positions of a window tie to within fp32 rounding, two correct implementations can pick different ones and
+    that unit's filter gradient changes by ~1/sqrt(B*P) of its norm (the reference's own CPU and cuDNN paths
+    differ the same way).  So: every unit within `outlier_rtol`, and all but a few within `rtol`."""
+    got = np.asarray(got, np.float64).reshape(got.shape[0], -1)
+    ref = np.asarray(ref, np.float64).reshape(ref.shape[0], -1)
+    scale = np.maximum(np.abs(ref).max(axis=1), 1e-30)
+    err = np.abs(got - ref).max(axis=1) / scale
+    assert err.max() <= outlier_rtol, "%s: worst unit err %.3e" % (name, err.max())
+    assert np.mean(err > rtol) <= max_outlier_frac, "%s: %d of %d units above %.1e" % (name, (err > rtol).sum(), err.size, rtol)
+
+
+@pytest.mark.parametrize("backend", ["tc", "lut"])
 @pytest.mark.parametrize("U,L,C,F,B", [(300, 251, 81, 19, 160), (20, 1000, 3, 19, 130), (33, 96, 2, 7, 70)])
-def test_train_step_vs_torch_port(U, L, C, F, B):
+def test_train_step_vs_torch_port(U, L, C, F, B, backend):
     """cfg-2 / cfg-5 shapes (reduced batch): logits, loss and all gradients against the fp32 CPU port."""
     from explainn_b200 import networks
     from oracle import torch_port as tp
@@ -143,6 +159,7 @@ def test_train_step_vs_torch_port(U, L, C, F, B):
     m = networks.ExplaiNN(U, L, C, F)
     m.load_state_dict(port.state_dict())
     m = m.to(DEV).train()
+    m.conv_backend = backend
     m.linears[9].eval()
     port.train()
     port.linears[9].eval()
@@ -160,6 +177,8 @@ def test_train_step_vs_torch_port(U, L, C, F, B):
             assert float(q.grad.abs().max()) == 0.0
         elif k in NOISE_GRAD:
             assert float(q.grad.abs().max()) < 1e-4 * float(port.linears[1].weight.grad.abs().max())
+        elif k in ("linears.0.weight", "linears.1.weight"):
+            _close_per_unit(q.grad.cpu().numpy(), p.grad.numpy(), 2e-4, "grad " + k)
         else:
             _close(q.grad.cpu().numpy(), p.grad.numpy(), 2e-4, "grad " + k)
     for (k, a), (_, b) in zip(port.state_dict().items(), m.state_dict().items()):
