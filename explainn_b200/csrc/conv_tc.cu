@@ -169,11 +169,45 @@ __device__ __forceinline__ void tc_drain(uint32_t taddr, int row, int nwin, int 
     }
 }
 
+// item iterator shared by both roles: (m-tile, sequence, chunk), advanced without divisions
+struct TcIter {
+    int mt, chunk, nchunk;
+    long long b, B, it, it1;
+    __device__ TcIter(long long it0, long long it1_, long long B_, int nchunk_) : nchunk(nchunk_), B(B_), it(it0), it1(it1_)
+    {
+        const long long per_mt = B_ * nchunk_;
+        mt = (int)(it0 / per_mt);
+        const long long rem = it0 - (long long)mt * per_mt;
+        b = rem / nchunk_;
+        chunk = (int)(rem - b * nchunk_);
+    }
+    __device__ bool valid() const { return it < it1; }
+    __device__ void next()
+    {
+        ++it;
+        if (++chunk == nchunk) {
+            chunk = 0;
+            if (++b == B) { b = 0; ++mt; }
+        }
+    }
+};
+
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+// Warp-specialised persistent kernel.
+//   warp 16      producer: builds the V operand of a tile from the packed codes, issues its tcgen05.mma, commits
+//   warps 0..15  epilogue: drain the accumulator (lane quarter = warp & 3, window range = warp >> 2), pool, exp,
+//                stage, TMA bulk store
+// Two TMEM accumulators (tmem_full / tmem_empty mbarriers) and two staging buffers keep the tensor pipe, the
+// epilogue and the stores of three consecutive tiles in flight.
 template <bool TRAIN>
-__global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const TcArgs a)
+__global__ void __launch_bounds__(TC_THREADS + 32, 1) conv_tc_kernel(const TcArgs a)
 {
     extern __shared__ __align__(128) unsigned char smem[];
-    __shared__ __align__(8) uint64_t bar_a, bar_full[2];
+    __shared__ __align__(8) uint64_t bar_a, tmem_full[2], tmem_empty[2];
     __shared__ uint32_t tmem_base_s;
 
     const int K = a.K, KC = K / 8, KS = K / 16;
@@ -183,26 +217,26 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const TcArgs a)
     // matrix is V[n], V[n+2], V[n+4], ... so the K-major core-matrix layout is the V array itself with
     // LBO = 32 B (next K chunk = two positions on) and SBO = 128 B (next 8 rows): no expansion is ever written.
     uint4 *sV = reinterpret_cast<uint4 *>(sA + 2 * a_bytes);            // 2 buffers x TC_VROWS
-    // staging: [128][sst] floats per plane (pooled; + x_hat, argmax when TRAIN).  With a single chunk per sequence
-    // the row stride is P itself, so a plane is the exact image of pooled[b][u0..u0+127][:] and leaves with ONE
-    // TMA bulk store.
+    // staging, two buffers of [128][sst] floats per plane (pooled; + x_hat, argmax when TRAIN).  With a single
+    // chunk per sequence the row stride is P itself: a plane is the exact image of pooled[b][u0..u0+127][:] and
+    // leaves with ONE TMA bulk store.
     const int sst = a.P <= TC_WIN ? a.P : TC_WIN + 1;
-    float *stage = reinterpret_cast<float *>(sV + 2 * TC_VROWS);
     const int plane = TC_M * (TC_WIN + 1);
+    const int nplanes = TRAIN ? 3 : 1;
+    float *stage0 = reinterpret_cast<float *>(sV + 2 * TC_VROWS);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n_mt = (a.U + TC_M - 1) / TC_M;
     const int nchunk = (a.P + TC_WIN - 1) / TC_WIN;
-
-    // work split: CTA -> contiguous range of (m-tile, sequence, chunk) items
-    const long long items_per_mt = a.B * nchunk;
-    const long long total = items_per_mt * n_mt;
+    const long long total = a.B * nchunk * n_mt;
     const long long it0 = total * blockIdx.x / gridDim.x, it1 = total * (blockIdx.x + 1) / gridDim.x;
 
     if (threadIdx.x == 0) {
         mbar_init(&bar_a, 1);
-        mbar_init(&bar_full[0], 1);
-        mbar_init(&bar_full[1], 1);
+        mbar_init(&tmem_full[0], 1);
+        mbar_init(&tmem_full[1], 1);
+        mbar_init(&tmem_empty[0], TC_THREADS / 32);
+        mbar_init(&tmem_empty[1], TC_THREADS / 32);
         mbar_fence_init();
     }
     if (warp == 0) {
@@ -214,149 +248,75 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const TcArgs a)
     tc_fence_after();
     const uint32_t tmem_base = tmem_base_s;
 
-    // instruction descriptor: f16 x f16 -> f32, M=128, N=240, both operands K-major
-    const uint32_t idesc = (1u << 4) | ((uint32_t)(TC_N >> 3) << 17) | ((uint32_t)(TC_M >> 4) << 24);
-
-    uint32_t a_parity = 0;
-    uint32_t full_parity[2] = {0, 0};
-    // current item, advanced incrementally (no 64-bit divisions in the loop)
-    int mt = (int)(it0 / items_per_mt);
-    long long b = (it0 - (long long)mt * items_per_mt) / nchunk;
-    int chunk = (int)((it0 - (long long)mt * items_per_mt) - b * nchunk);
-    int cur_mt = -1;
-    long long it = it0;
-    int issued = 0;
-    long long prev_b = -1;
-    int prev_chunk = 0, prev_buf = 0, prev_u0 = 0;
-    bool have_prev = false;
-    const int row = 32 * (warp & 3) + lane;       // TMEM lane = unit inside the tile
-    float shift = 0.f, gam = 1.f, bet = 0.f;
-
-    auto epilogue = [&](int pchunk, int buf) {
-        const int nwin = min(TC_WIN, a.P - pchunk * TC_WIN);
-        mbar_wait(&bar_full[buf], full_parity[buf]);
-        full_parity[buf] ^= 1;
-        tc_fence_after();
-        const uint32_t taddr = tmem_base + ((uint32_t)(32 * (warp & 3)) << 16) + (uint32_t)buf * 256u;
-        // four warps share a lane quarter; each drains a range of whole windows: 9 + 9 + 8 + 8 = 34
-        constexpr int S1 = 9 * XB_POOL, S2 = 18 * XB_POOL, S3 = 26 * XB_POOL, S4 = TC_WIN * XB_POOL;
-        switch (warp >> 2) {
-        case 0: tc_drain<TRAIN, 0, S1>(taddr, row, nwin, sst, plane, stage, shift, gam, bet); break;
-        case 1: tc_drain<TRAIN, S1, S2>(taddr, row, nwin, sst, plane, stage, shift, gam, bet); break;
-        case 2: tc_drain<TRAIN, S2, S3>(taddr, row, nwin, sst, plane, stage, shift, gam, bet); break;
-        default: tc_drain<TRAIN, S3, S4>(taddr, row, nwin, sst, plane, stage, shift, gam, bet); break;
+    if (warp == TC_THREADS / 32) {
+        // =========================== producer warp ===========================
+        const uint32_t idesc = (1u << 4) | ((uint32_t)(TC_N >> 3) << 17) | ((uint32_t)(TC_M >> 4) << 24);   // f16xf16->f32, M128 N240
+        uint32_t a_parity = 0;
+        int cur_mt = -1, last_buf = -1;
+        long long n = 0;                                   // tiles issued by this CTA
+        // a tile touches positions n0 .. n0 + TC_VROWS: at most 20 code words and 11 mask words, one per lane
+        auto load_words = [&](const TcIter &t, uint32_t &cwv, uint32_t &mwv) {
+            const int n0 = t.chunk * TC_WIN * XB_POOL;
+            const int ci = (n0 >> 4) + lane, mi = (n0 >> 5) + lane;
+            cwv = ci < a.wc ? a.codes[t.b * a.wc + ci] : 0u;
+            mwv = mi < a.wm ? a.nmask[t.b * a.wm + mi] : 0u;
+        };
+        uint32_t cwr_next = 0, mwr_next = 0;
+        {
+            TcIter t0(it0, it1, a.B, nchunk);
+            if (t0.valid()) load_words(t0, cwr_next, mwr_next);
         }
-        tc_fence_before();
-    };
-
-    auto store_stage = [&](long long sb_, int pchunk, int u0) {
-        const int w0 = pchunk * TC_WIN;
-        const int nwin = min(TC_WIN, a.P - w0);
-        const int nvalid = min(TC_M, a.U - u0);
-        const size_t o = ((size_t)sb_ * a.U + u0) * a.P;
-        const uint32_t bytes = (uint32_t)nvalid * a.P * 4;
-        // when the staged planes are exact images of the global tiles they leave as TMA bulk stores
-        const bool bulk_f = sst == a.P && (bytes & 15u) == 0 && ((o * 4) & 15u) == 0;
-        const bool bulk_i = TRAIN && sst == a.P && ((bytes / 4) & 15u) == 0 && (o & 15u) == 0;
-        if (bulk_f || bulk_i) {
-            fence_proxy_async();
-            __syncthreads();
-            if (threadIdx.x == 0) {
-                if (bulk_f) {
-                    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(a.pooled + o), "r"(smem_u32(stage)), "r"(bytes) : "memory");
-                    if (TRAIN)
-                        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(a.xhat + o), "r"(smem_u32(stage + plane)), "r"(bytes) : "memory");
-                }
-                if (bulk_i)
-                    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(a.idx + o), "r"(smem_u32(stage + 2 * plane)), "r"(bytes / 4) : "memory");
-                asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-            }
-        }
-        if (sst == a.P) {
-            // single chunk per sequence: the planes are contiguous images, copy them flat
-            const int nel = nvalid * a.P;
-            if (!bulk_f)
-                for (int i = threadIdx.x; i < nel; i += TC_THREADS) {
-                    a.pooled[o + i] = stage[i];
-                    if (TRAIN) a.xhat[o + i] = stage[plane + i];
-                }
-            if (TRAIN && !bulk_i)
-                for (int i = threadIdx.x; i < nel; i += TC_THREADS) a.idx[o + i] = reinterpret_cast<unsigned char *>(stage + 2 * plane)[i];
-        } else if (!bulk_f || (TRAIN && !bulk_i)) {
-            for (int r = warp; r < nvalid; r += TC_THREADS / 32) {
-                const size_t orow = o + (size_t)r * a.P + w0;
-                for (int c = lane; c < nwin; c += 32) {
-                    if (!bulk_f) {
-                        a.pooled[orow + c] = stage[r * sst + c];
-                        if (TRAIN) a.xhat[orow + c] = stage[plane + r * sst + c];
-                    }
-                    if (TRAIN && !bulk_i) a.idx[orow + c] = reinterpret_cast<unsigned char *>(stage + 2 * plane)[r * sst + c];
-                }
-            }
-        }
-        if ((bulk_f || bulk_i) && threadIdx.x == 0)
-            asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // staging may be rewritten after this
-    };
-
-    while (it < it1 || have_prev) {
-        const bool have_cur = it < it1;
-        const int buf = issued & 1;
-        const int u0 = mt * TC_M;
-        if (have_cur) {
-            if (mt != cur_mt) {
-                // a new unit tile: every MMA that reads sA must be finished before it is overwritten
-                if (have_prev) {
-                    epilogue(prev_chunk, prev_buf);
-                    __syncthreads();
-                    store_stage(prev_b, prev_chunk, prev_u0);
-                    have_prev = false;
-                }
-                __syncthreads();
-                if (threadIdx.x == 0) {
+        for (TcIter t(it0, it1, a.B, nchunk); t.valid(); t.next(), ++n) {
+            const int buf = (int)(n & 1);
+            const uint32_t use = (uint32_t)(n >> 1);       // how often this buffer has been used before
+            if (t.mt != cur_mt) {
+                // a new unit tile: every MMA that reads sA must have completed before TMA overwrites it
+                if (last_buf >= 0) mbar_wait(&tmem_full[last_buf], (uint32_t)(((n - 1) >> 1) & 1));
+                if (lane == 0) {
                     mbar_arrive_expect_tx(&bar_a, 2 * a_bytes);
-                    tma_bulk_g2s(sA, reinterpret_cast<const unsigned char *>(a.images) + (size_t)mt * 2 * a_bytes, 2 * a_bytes, &bar_a);
-                }
-                const int u = u0 + row;
-                shift = u < a.U ? a.shift[u] : 0.f;
-                if (TRAIN) {
-                    gam = u < a.U ? a.gamma[u] : 1.f;
-                    bet = u < a.U ? a.beta[u] : 0.f;
+                    tma_bulk_g2s(sA, reinterpret_cast<const unsigned char *>(a.images) + (size_t)t.mt * 2 * a_bytes, 2 * a_bytes, &bar_a);
                 }
                 mbar_wait(&bar_a, a_parity);
                 a_parity ^= 1;
-                cur_mt = mt;
+                cur_mt = t.mt;
             }
-            // ---- V entries of this tile: positions n0 .. n0 + TC_VROWS ----
+            // the words of this tile were prefetched into registers during the previous tile; fetch the next ones now
+            const uint32_t cwr = cwr_next, mwr = mwr_next;
+            const int n0 = t.chunk * TC_WIN * XB_POOL;
+            {
+                TcIter tn = t;
+                tn.next();
+                if (tn.valid()) load_words(tn, cwr_next, mwr_next);
+            }
+            // accumulator `buf` drained (which also means the MMAs that read V[buf] are done)
+            mbar_wait(&tmem_empty[buf], (use & 1) ^ 1);
             {
                 uint4 *V = sV + buf * TC_VROWS;
-                const int n0 = chunk * TC_WIN * XB_POOL;
-                const uint32_t *cw = a.codes + b * a.wc;
-                const uint32_t *mw = a.nmask + b * a.wm;
-                for (int i = threadIdx.x; i < TC_VROWS; i += TC_THREADS) {
-                    const int p0 = n0 + i;
-                    uint32_t c0 = 4, c1 = 4;
-                    if (p0 < a.L) {
-                        c0 = (cw[p0 >> 4] >> (2 * (p0 & 15))) & 3u;
-                        if ((mw[p0 >> 5] >> (p0 & 31)) & 1u) c0 = 4;
-                    }
-                    if (p0 + 1 < a.L) {
-                        c1 = (cw[(p0 + 1) >> 4] >> (2 * ((p0 + 1) & 15))) & 3u;
-                        if ((mw[(p0 + 1) >> 5] >> ((p0 + 1) & 31)) & 1u) c1 = 4;
-                    }
-                    // one-hot fp16 quadruple of a base: 1.0 (0x3C00) in half c, N -> all zero
-                    uint4 val;
+                const int cbase = n0 >> 4, mbase = n0 >> 5;
+                // warp-uniform trip count: the shuffles below need all 32 lanes (source lane indices are
+                // clamped by the hardware modulo 32; out-of-tile entries are simply not stored)
+#pragma unroll 5
+                for (int i0 = 0; i0 < TC_VROWS; i0 += 32) {
+                    const int i = i0 + lane;
+                    const int p0 = n0 + i, p1 = p0 + 1;
+                    const uint32_t wa = __shfl_sync(0xffffffffu, cwr, (p0 >> 4) - cbase);
+                    const uint32_t wb = __shfl_sync(0xffffffffu, cwr, (p1 >> 4) - cbase);
+                    const uint32_t ma = __shfl_sync(0xffffffffu, mwr, (p0 >> 5) - mbase);
+                    const uint32_t mb = __shfl_sync(0xffffffffu, mwr, (p1 >> 5) - mbase);
+                    uint32_t c0 = (wa >> (2 * (p0 & 15))) & 3u, c1 = (wb >> (2 * (p1 & 15))) & 3u;
+                    if (p0 >= a.L || ((ma >> (p0 & 31)) & 1u)) c0 = 4;
+                    if (p1 >= a.L || ((mb >> (p1 & 31)) & 1u)) c1 = 4;
+                    uint4 val;      // one-hot fp16 quadruple per base: 1.0 (0x3C00) in half c, N -> zeros
                     val.x = c0 == 0 ? 0x00003C00u : (c0 == 1 ? 0x3C000000u : 0u);
                     val.y = c0 == 2 ? 0x00003C00u : (c0 == 3 ? 0x3C000000u : 0u);
                     val.z = c1 == 0 ? 0x00003C00u : (c1 == 1 ? 0x3C000000u : 0u);
                     val.w = c1 == 2 ? 0x00003C00u : (c1 == 3 ? 0x3C000000u : 0u);
-                    V[i] = val;
+                    if (i < TC_VROWS) V[i] = val;
                 }
             }
             fence_proxy_async();
-            tc_fence_before();
-            __syncthreads();
-            // ---- issue the MMAs of this tile ----
-            if (threadIdx.x == 0) {
+            __syncwarp();
+            if (lane == 0) {
                 tc_fence_after();
                 const uint32_t d = tmem_base + (uint32_t)buf * 256u;
                 const uint32_t a_hi = smem_u32(sA), a_lo = a_hi + a_bytes, bt = smem_u32(sV + buf * TC_VROWS);
@@ -366,30 +326,96 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const TcArgs a)
                     tc_mma_f16(d, make_smem_desc(a_hi + ks * 256, a_lbo, a_sbo), bd, idesc, ks > 0 ? 1u : 0u);
                     tc_mma_f16(d, make_smem_desc(a_lo + ks * 256, a_lbo, a_sbo), bd, idesc, 1u);
                 }
-                tc_commit(&bar_full[buf]);
+                tc_commit(&tmem_full[buf]);
+            }
+            __syncwarp();
+            last_buf = buf;
+        }
+    } else {
+        // =========================== epilogue warps ===========================
+        const int row = 32 * (warp & 3) + lane;            // TMEM lane = unit inside the tile
+        int cur_mt = -1;
+        float shift = 0.f, gam = 1.f, bet = 0.f;
+        long long n = 0;
+        for (TcIter t(it0, it1, a.B, nchunk); t.valid(); t.next(), ++n) {
+            const int buf = (int)(n & 1);
+            const uint32_t use = (uint32_t)(n >> 1);
+            const int u0 = t.mt * TC_M;
+            if (t.mt != cur_mt) {
+                const int u = u0 + row;
+                shift = u < a.U ? a.shift[u] : 0.f;
+                if (TRAIN) {
+                    gam = u < a.U ? a.gamma[u] : 1.f;
+                    bet = u < a.U ? a.beta[u] : 0.f;
+                }
+                cur_mt = t.mt;
+            }
+            float *stage = stage0 + (size_t)buf * nplanes * plane;
+            const int w0 = t.chunk * TC_WIN;
+            const int nwin = min(TC_WIN, a.P - w0);
+            mbar_wait(&tmem_full[buf], use & 1);
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + ((uint32_t)(32 * (warp & 3)) << 16) + (uint32_t)buf * 256u;
+            // four warps share a lane quarter; each drains a range of whole windows: 9 + 9 + 8 + 8 = 34
+            constexpr int S1 = 9 * XB_POOL, S2 = 18 * XB_POOL, S3 = 26 * XB_POOL, S4 = TC_WIN * XB_POOL;
+            switch (warp >> 2) {
+            case 0: tc_drain<TRAIN, 0, S1>(taddr, row, nwin, sst, plane, stage, shift, gam, bet); break;
+            case 1: tc_drain<TRAIN, S1, S2>(taddr, row, nwin, sst, plane, stage, shift, gam, bet); break;
+            case 2: tc_drain<TRAIN, S2, S3>(taddr, row, nwin, sst, plane, stage, shift, gam, bet); break;
+            default: tc_drain<TRAIN, S3, S4>(taddr, row, nwin, sst, plane, stage, shift, gam, bet); break;
+            }
+            // accumulator free again for the producer
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tmem_empty[buf]);
+
+            // ---- store the staged tile ----
+            const int nvalid = min(TC_M, a.U - u0);
+            const size_t o = ((size_t)t.b * a.U + u0) * a.P;
+            const uint32_t bytes = (uint32_t)nvalid * a.P * 4;
+            const bool bulk_f = sst == a.P && (bytes & 15u) == 0 && ((o * 4) & 15u) == 0;
+            const bool bulk_i = TRAIN && sst == a.P && ((bytes / 4) & 15u) == 0 && (o & 15u) == 0;
+            fence_proxy_async();
+            // the bulk stores of the previous tile read the OTHER staging buffer; they must be done reading before
+            // anybody writes it again (next tile), which this barrier then publishes
+            if (threadIdx.x == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+            asm volatile("bar.sync 1, %0;" ::"n"(TC_THREADS) : "memory");
+            if (threadIdx.x == 0 && (bulk_f || bulk_i)) {
+                if (bulk_f) {
+                    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(a.pooled + o), "r"(smem_u32(stage)), "r"(bytes) : "memory");
+                    if (TRAIN)
+                        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(a.xhat + o), "r"(smem_u32(stage + plane)), "r"(bytes) : "memory");
+                }
+                if (bulk_i)
+                    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(a.idx + o), "r"(smem_u32(stage + 2 * plane)), "r"(bytes / 4) : "memory");
+                asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            }
+            if (sst == a.P) {
+                // single chunk per sequence: whatever cannot leave as a bulk store is copied flat
+                const int nel = nvalid * a.P;
+                if (!bulk_f)
+                    for (int i = threadIdx.x; i < nel; i += TC_THREADS) {
+                        a.pooled[o + i] = stage[i];
+                        if (TRAIN) a.xhat[o + i] = stage[plane + i];
+                    }
+                if (TRAIN && !bulk_i)
+                    for (int i = threadIdx.x; i < nel; i += TC_THREADS) a.idx[o + i] = reinterpret_cast<unsigned char *>(stage + 2 * plane)[i];
+            } else {
+                for (int r = warp; r < nvalid; r += TC_THREADS / 32) {
+                    const size_t orow = o + (size_t)r * a.P + w0;
+                    for (int c = lane; c < nwin; c += 32) {
+                        a.pooled[orow + c] = stage[r * sst + c];
+                        if (TRAIN) {
+                            a.xhat[orow + c] = stage[plane + r * sst + c];
+                            a.idx[orow + c] = reinterpret_cast<unsigned char *>(stage + 2 * plane)[r * sst + c];
+                        }
+                    }
+                }
             }
         }
-        // ---- epilogue of the previous tile overlaps the MMAs just issued ----
-        if (have_prev) {
-            epilogue(prev_chunk, prev_buf);
-            __syncthreads();
-            store_stage(prev_b, prev_chunk, prev_u0);
-            have_prev = false;
-        }
-        if (have_cur) {
-            prev_b = b; prev_chunk = chunk; prev_buf = buf; prev_u0 = u0;
-            have_prev = true;
-            ++issued;
-            ++it;
-            if (++chunk == nchunk) {
-                chunk = 0;
-                if (++b == a.B) { b = 0; ++mt; }
-            }
-        }
-        __syncthreads();
+        if (threadIdx.x == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
     }
 
-    if (threadIdx.x == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
     tc_fence_before();
     __syncthreads();
     if (warp == 0) {
@@ -437,7 +463,7 @@ static int launch_tc(bool train, const uint32_t *codes, const uint32_t *nmask, l
     a.P = ((L - F + 1) - XB_POOL) / XB_POOL + 1;
     a.wc = xb_words_codes(L); a.wm = xb_words_mask(L);
     a.images = (const __half *)images; a.shift = shift; a.pooled = pooled; a.xhat = xhat; a.idx = idx; a.gamma = gamma; a.beta = beta;
-    const size_t smem = (size_t)2 * TC_M * a.K * 2 + (size_t)2 * TC_VROWS * 16 + (size_t)(train ? 3 : 1) * TC_M * (TC_WIN + 1) * 4;
+    const size_t smem = (size_t)2 * TC_M * a.K * 2 + (size_t)2 * TC_VROWS * 16 + (size_t)2 * (train ? 3 : 1) * TC_M * (TC_WIN + 1) * 4;
     if (smem > 227 * 1024) {
         xb_set_error("conv_pool_fwd_tc: %zu bytes of shared memory needed (L=%d, filter_size=%d)", smem, L, F);
         return XB_ERR_UNSUPPORTED;
@@ -449,10 +475,10 @@ static int launch_tc(bool train, const uint32_t *codes, const uint32_t *nmask, l
     cudaError_t e;
     if (train) {
         e = cudaFuncSetAttribute(conv_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e == cudaSuccess) conv_tc_kernel<true><<<grid, TC_THREADS, smem, stream>>>(a);
+        if (e == cudaSuccess) conv_tc_kernel<true><<<grid, TC_THREADS + 32, smem, stream>>>(a);
     } else {
         e = cudaFuncSetAttribute(conv_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e == cudaSuccess) conv_tc_kernel<false><<<grid, TC_THREADS, smem, stream>>>(a);
+        if (e == cudaSuccess) conv_tc_kernel<false><<<grid, TC_THREADS + 32, smem, stream>>>(a);
     }
     if (e != cudaSuccess) {
         xb_set_error("conv_pool_fwd_tc: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
