@@ -18,6 +18,7 @@
 // TMEM accumulators (240 columns each) and the epilogue warps drain the other one.
 #include "common.cuh"
 #include "../../include/explainn_b200.h"
+#include <stdlib.h>
 
 namespace {
 
@@ -129,41 +130,56 @@ struct TcArgs {
     float *xhat;            // train only
     unsigned char *idx;     // train only
     const float *gamma, *beta;
+    int dbg;                // XB_TC_DBG bitmask (profiling experiments only): 1 no stores, 2 no V build, 4 no drain, 8 no MMA
 };
 
 constexpr int TC_VROWS = TC_N + 64;     // dinucleotide entries per tile: positions n0 .. n0 + 240 + 2*KC
+constexpr int TC_VBUFS = 4;             // V tiles in flight: tile n may be built while the MMAs of n-1, n-2 run
+
+// 16 accumulator columns of this thread's TMEM lane -> 16 registers (no wait: the caller batches loads)
+__device__ __forceinline__ void tc_ld16_nowait(uint32_t taddr, uint32_t *r)
+{
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),
+          "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr)
+        : "memory");
+}
 
 // Epilogue of one accumulator for the columns [C0, C1) (whole pool windows), one unit per thread.
+// TMEM reads are the scarce resource of this kernel (~64 B/clk/SM), so only the 16-column pieces that
+// intersect the range are loaded, all of them are issued before a single wait, and warps whose lane
+// quarter holds no valid unit skip the drain altogether (caller).
 template <bool TRAIN, int C0, int C1>
 __device__ __forceinline__ void tc_drain(uint32_t taddr, int row, int nwin, int sst, int plane, float *stage, float shift, float gam,
                                          float bet)
 {
-    constexpr int CB0 = C0 / 32, CB1 = (C1 + 31) / 32;
+    constexpr int P0 = C0 / 16, P1 = (C1 + 15) / 16, NP = P1 - P0;
+    uint32_t r[NP * 16];
+#pragma unroll
+    for (int p = 0; p < NP; ++p) tc_ld16_nowait(taddr + (P0 + p) * 16, r + p * 16);
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
     float m = 0.f, xb = 0.f;
     int ib = 0;
 #pragma unroll
-    for (int cb = CB0; cb < CB1; ++cb) {
-        float v[32];
-        if (cb * 32 + 32 <= TC_N) tc_ld32(taddr + cb * 32, v);
-        else tc_ld16(taddr + cb * 32, v);
-#pragma unroll
-        for (int j = 0; j < 32; ++j) {
-            const int col = cb * 32 + j;
-            if (col < C0 || col >= C1) continue;
-            const int ph = col % XB_POOL, win = col / XB_POOL;
+    for (int i = 0; i < NP * 16; ++i) {
+        const int col = P0 * 16 + i;
+        if (col < C0 || col >= C1) continue;
+        const float v = __uint_as_float(r[i]);
+        const int ph = col % XB_POOL, win = col / XB_POOL;
+        if (TRAIN) {
+            const float x = v + shift;
+            const float z = fmaf(gam, x, bet);
+            if (ph == 0 || z > m) { m = z; xb = x; ib = ph; }
+        } else {
+            m = ph == 0 ? v : fmaxf(m, v);
+        }
+        if (ph == XB_POOL - 1 && win < nwin) {
+            stage[row * sst + win] = __expf(TRAIN ? m : m + shift);
             if (TRAIN) {
-                const float x = v[j] + shift;
-                const float z = fmaf(gam, x, bet);
-                if (ph == 0 || z > m) { m = z; xb = x; ib = ph; }
-            } else {
-                m = ph == 0 ? v[j] : fmaxf(m, v[j]);
-            }
-            if (ph == XB_POOL - 1 && win < nwin) {
-                stage[row * sst + win] = __expf(TRAIN ? m : m + shift);
-                if (TRAIN) {
-                    stage[plane + row * sst + win] = xb;
-                    reinterpret_cast<unsigned char *>(stage + 2 * plane)[row * sst + win] = (unsigned char)ib;
-                }
+                stage[plane + row * sst + win] = xb;
+                reinterpret_cast<unsigned char *>(stage + 2 * plane)[row * sst + win] = (unsigned char)ib;
             }
         }
     }
@@ -216,14 +232,14 @@ __global__ void __launch_bounds__(TC_THREADS + 32, 1) conv_tc_kernel(const TcArg
     // X operand: V[pos] = 16 bytes = one-hot fp16 of (base(pos), base(pos+1)), 16-byte pitch.  Row n of the im2col
     // matrix is V[n], V[n+2], V[n+4], ... so the K-major core-matrix layout is the V array itself with
     // LBO = 32 B (next K chunk = two positions on) and SBO = 128 B (next 8 rows): no expansion is ever written.
-    uint4 *sV = reinterpret_cast<uint4 *>(sA + 2 * a_bytes);            // 2 buffers x TC_VROWS
+    uint4 *sV = reinterpret_cast<uint4 *>(sA + 2 * a_bytes);            // TC_VBUFS buffers x TC_VROWS
     // staging, two buffers of [128][sst] floats per plane (pooled; + x_hat, argmax when TRAIN).  With a single
     // chunk per sequence the row stride is P itself: a plane is the exact image of pooled[b][u0..u0+127][:] and
     // leaves with ONE TMA bulk store.
     const int sst = a.P <= TC_WIN ? a.P : TC_WIN + 1;
     const int plane = TC_M * (TC_WIN + 1);
     const int nplanes = TRAIN ? 3 : 1;
-    float *stage0 = reinterpret_cast<float *>(sV + 2 * TC_VROWS);
+    float *stage0 = reinterpret_cast<float *>(sV + TC_VBUFS * TC_VROWS);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n_mt = (a.U + TC_M - 1) / TC_M;
@@ -288,40 +304,48 @@ __global__ void __launch_bounds__(TC_THREADS + 32, 1) conv_tc_kernel(const TcArg
                 tn.next();
                 if (tn.valid()) load_words(tn, cwr_next, mwr_next);
             }
-            // accumulator `buf` drained (which also means the MMAs that read V[buf] are done)
-            mbar_wait(&tmem_empty[buf], (use & 1) ^ 1);
+            // ---- build V(n) into buffer n % 4.  Its previous user was tile n-4, whose MMAs are known to be complete
+            //      (tile n-2 has been seen drained), so no wait is needed here and the build overlaps the MMAs of the
+            //      two tiles in flight.  Lane l expands the 16 positions n0+16l .. n0+16l+15 of its own code word.
             {
-                uint4 *V = sV + buf * TC_VROWS;
-                const int cbase = n0 >> 4, mbase = n0 >> 5;
-                // warp-uniform trip count: the shuffles below need all 32 lanes (source lane indices are
-                // clamped by the hardware modulo 32; out-of-tile entries are simply not stored)
-#pragma unroll 5
-                for (int i0 = 0; i0 < TC_VROWS; i0 += 32) {
-                    const int i = i0 + lane;
-                    const int p0 = n0 + i, p1 = p0 + 1;
-                    const uint32_t wa = __shfl_sync(0xffffffffu, cwr, (p0 >> 4) - cbase);
-                    const uint32_t wb = __shfl_sync(0xffffffffu, cwr, (p1 >> 4) - cbase);
-                    const uint32_t ma = __shfl_sync(0xffffffffu, mwr, (p0 >> 5) - mbase);
-                    const uint32_t mb = __shfl_sync(0xffffffffu, mwr, (p1 >> 5) - mbase);
-                    uint32_t c0 = (wa >> (2 * (p0 & 15))) & 3u, c1 = (wb >> (2 * (p1 & 15))) & 3u;
-                    if (p0 >= a.L || ((ma >> (p0 & 31)) & 1u)) c0 = 4;
-                    if (p1 >= a.L || ((mb >> (p1 & 31)) & 1u)) c1 = 4;
-                    uint4 val;      // one-hot fp16 quadruple per base: 1.0 (0x3C00) in half c, N -> zeros
-                    val.x = c0 == 0 ? 0x00003C00u : (c0 == 1 ? 0x3C000000u : 0u);
-                    val.y = c0 == 2 ? 0x00003C00u : (c0 == 3 ? 0x3C000000u : 0u);
-                    val.z = c1 == 0 ? 0x00003C00u : (c1 == 1 ? 0x3C000000u : 0u);
-                    val.w = c1 == 2 ? 0x00003C00u : (c1 == 3 ? 0x3C000000u : 0u);
-                    if (i < TC_VROWS) V[i] = val;
+                uint4 *V = sV + (int)(n & (TC_VBUFS - 1)) * TC_VROWS;
+                const uint32_t w_hi = __shfl_down_sync(0xffffffffu, cwr, 1);
+                const uint32_t c16 = __funnelshift_r(cwr, w_hi, 2 * (n0 & 15));          // codes of my 16 positions
+                const uint32_t c_nx = __shfl_down_sync(0xffffffffu, c16, 1) & 3u;         // code of position n0+16(l+1)
+                const int mpos = (n0 & 31) + 16 * lane;
+                const uint32_t mw_a = __shfl_sync(0xffffffffu, mwr, mpos >> 5);
+                const uint32_t mw_b = __shfl_sync(0xffffffffu, mwr, (mpos >> 5) + 1);
+                uint32_t m16 = __funnelshift_r(mw_a, mw_b, mpos & 31) & 0xFFFFu;          // N flags of my 16 positions
+                const int nvalid_pos = a.L - (n0 + 16 * lane);                            // positions >= L count as N
+                if (nvalid_pos < 16) m16 |= nvalid_pos <= 0 ? 0xFFFFu : (0xFFFFu << nvalid_pos) & 0xFFFFu;
+                const uint32_t m_nx = __shfl_down_sync(0xffffffffu, m16, 1) & 1u;
+                // one-hot fp16 quadruple of each of the 17 bases: (x,y) = halves (A,C) and (G,T)
+                uint32_t ox[17], oy[17];
+#pragma unroll
+                for (int j = 0; j < 17; ++j) {
+                    const uint32_t c = j < 16 ? (c16 >> (2 * j)) & 3u : c_nx;
+                    const uint32_t isn = j < 16 ? (m16 >> j) & 1u : m_nx;
+                    const uint32_t one = isn ? 0u : (0x3C00u << ((c & 1u) * 16));
+                    ox[j] = (c & 2u) ? 0u : one;
+                    oy[j] = (c & 2u) ? one : 0u;
+                }
+                if (lane < TC_VROWS / 16 && !((a.dbg & 2) && n >= TC_VBUFS)) {
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) V[16 * lane + j] = make_uint4(ox[j], oy[j], ox[j + 1], oy[j + 1]);
                 }
             }
+            fence_proxy_async();
+            __syncwarp();
+            // accumulator `buf` drained by the epilogue warps
+            mbar_wait(&tmem_empty[buf], (use & 1) ^ 1);
             fence_proxy_async();
             __syncwarp();
             if (lane == 0) {
                 tc_fence_after();
                 const uint32_t d = tmem_base + (uint32_t)buf * 256u;
-                const uint32_t a_hi = smem_u32(sA), a_lo = a_hi + a_bytes, bt = smem_u32(sV + buf * TC_VROWS);
+                const uint32_t a_hi = smem_u32(sA), a_lo = a_hi + a_bytes, bt = smem_u32(sV + (int)(n & (TC_VBUFS - 1)) * TC_VROWS);
                 const uint32_t a_lbo = 128, a_sbo = (uint32_t)KC * 128;
-                for (int ks = 0; ks < KS; ++ks) {
+                for (int ks = 0; ks < ((a.dbg & 8) ? 0 : KS); ++ks) {
                     const uint64_t bd = make_smem_desc(bt + ks * 64, 32, 128);
                     tc_mma_f16(d, make_smem_desc(a_hi + ks * 256, a_lbo, a_sbo), bd, idesc, ks > 0 ? 1u : 0u);
                     tc_mma_f16(d, make_smem_desc(a_lo + ks * 256, a_lbo, a_sbo), bd, idesc, 1u);
@@ -358,11 +382,13 @@ __global__ void __launch_bounds__(TC_THREADS + 32, 1) conv_tc_kernel(const TcArg
             const uint32_t taddr = tmem_base + ((uint32_t)(32 * (warp & 3)) << 16) + (uint32_t)buf * 256u;
             // four warps share a lane quarter; each drains a range of whole windows: 9 + 9 + 8 + 8 = 34
             constexpr int S1 = 9 * XB_POOL, S2 = 18 * XB_POOL, S3 = 26 * XB_POOL, S4 = TC_WIN * XB_POOL;
-            switch (warp >> 2) {
-            case 0: tc_drain<TRAIN, 0, S1>(taddr, row, nwin, sst, plane, stage, shift, gam, bet); break;
-            case 1: tc_drain<TRAIN, S1, S2>(taddr, row, nwin, sst, plane, stage, shift, gam, bet); break;
-            case 2: tc_drain<TRAIN, S2, S3>(taddr, row, nwin, sst, plane, stage, shift, gam, bet); break;
-            default: tc_drain<TRAIN, S3, S4>(taddr, row, nwin, sst, plane, stage, shift, gam, bet); break;
+            if (u0 + 32 * (warp & 3) < a.U && !(a.dbg & 4)) {   // lane quarters without a valid unit are not read at all
+                switch (warp >> 2) {
+                case 0: tc_drain<TRAIN, 0, S1>(taddr, row, nwin, sst, plane, stage, shift, gam, bet); break;
+                case 1: tc_drain<TRAIN, S1, S2>(taddr, row, nwin, sst, plane, stage, shift, gam, bet); break;
+                case 2: tc_drain<TRAIN, S2, S3>(taddr, row, nwin, sst, plane, stage, shift, gam, bet); break;
+                default: tc_drain<TRAIN, S3, S4>(taddr, row, nwin, sst, plane, stage, shift, gam, bet); break;
+                }
             }
             // accumulator free again for the producer
             tc_fence_before();
@@ -375,6 +401,7 @@ __global__ void __launch_bounds__(TC_THREADS + 32, 1) conv_tc_kernel(const TcArg
             const uint32_t bytes = (uint32_t)nvalid * a.P * 4;
             const bool bulk_f = sst == a.P && (bytes & 15u) == 0 && ((o * 4) & 15u) == 0;
             const bool bulk_i = TRAIN && sst == a.P && ((bytes / 4) & 15u) == 0 && (o & 15u) == 0;
+            if (a.dbg & 1) continue;
             fence_proxy_async();
             // the bulk stores of the previous tile read the OTHER staging buffer; they must be done reading before
             // anybody writes it again (next tile), which this barrier then publishes
@@ -462,8 +489,9 @@ static int launch_tc(bool train, const uint32_t *codes, const uint32_t *nmask, l
     a.codes = codes; a.nmask = nmask; a.B = B; a.L = L; a.F = F; a.U = U; a.K = tc_K(F);
     a.P = ((L - F + 1) - XB_POOL) / XB_POOL + 1;
     a.wc = xb_words_codes(L); a.wm = xb_words_mask(L);
+    { const char *e = getenv("XB_TC_DBG"); a.dbg = e ? atoi(e) : 0; }
     a.images = (const __half *)images; a.shift = shift; a.pooled = pooled; a.xhat = xhat; a.idx = idx; a.gamma = gamma; a.beta = beta;
-    const size_t smem = (size_t)2 * TC_M * a.K * 2 + (size_t)2 * TC_VROWS * 16 + (size_t)2 * (train ? 3 : 1) * TC_M * (TC_WIN + 1) * 4;
+    const size_t smem = (size_t)2 * TC_M * a.K * 2 + (size_t)TC_VBUFS * TC_VROWS * 16 + (size_t)2 * (train ? 3 : 1) * TC_M * (TC_WIN + 1) * 4;
     if (smem > 227 * 1024) {
         xb_set_error("conv_pool_fwd_tc: %zu bytes of shared memory needed (L=%d, filter_size=%d)", smem, L, F);
         return XB_ERR_UNSUPPORTED;
