@@ -19,6 +19,7 @@
 #include "common.cuh"
 #include "../../include/explainn_b200.h"
 #include <stdlib.h>
+#include <algorithm>
 
 namespace {
 
@@ -130,6 +131,7 @@ struct TcArgs {
     float *xhat;            // train only
     unsigned char *idx;     // train only
     const float *gamma, *beta;
+    int gsz;                // unit tiles (of 128) whose weights stay resident in shared memory together
     int dbg;                // XB_TC_DBG bitmask (profiling experiments only): 1 no stores, 2 no V build, 4 no drain, 8 no MMA
 };
 
@@ -152,9 +154,10 @@ __device__ __forceinline__ void tc_ld16_nowait(uint32_t taddr, uint32_t *r)
 // intersect the range are loaded, all of them are issued before a single wait, and warps whose lane
 // quarter holds no valid unit skip the drain altogether (caller).
 template <bool TRAIN, int C0, int C1>
-__device__ __forceinline__ void tc_drain(uint32_t taddr, int row, int nwin, int sst, int plane, float *stage, float shift, float gam,
-                                         float bet)
+__device__ __forceinline__ void tc_drain(uint32_t taddr, int row, int nwin, int sst, float *stage, unsigned char *stage_i, float shift,
+                                         float gam, float bet)
 {
+    constexpr int plane = TC_M * (TC_WIN + 1);
     constexpr int P0 = C0 / 16, P1 = (C1 + 15) / 16, NP = P1 - P0;
     uint32_t r[NP * 16];
 #pragma unroll
@@ -179,21 +182,21 @@ __device__ __forceinline__ void tc_drain(uint32_t taddr, int row, int nwin, int 
             stage[row * sst + win] = __expf(TRAIN ? m : m + shift);
             if (TRAIN) {
                 stage[plane + row * sst + win] = xb;
-                reinterpret_cast<unsigned char *>(stage + 2 * plane)[row * sst + win] = (unsigned char)ib;
+                stage_i[row * sst + win] = (unsigned char)ib;
             }
         }
     }
 }
 
-// item iterator shared by both roles: (m-tile, sequence, chunk), advanced without divisions
+// item iterator shared by both roles: (tile group, sequence, chunk), advanced without divisions
 struct TcIter {
-    int mt, chunk, nchunk;
+    int grp, chunk, nchunk;
     long long b, B, it, it1;
     __device__ TcIter(long long it0, long long it1_, long long B_, int nchunk_) : nchunk(nchunk_), B(B_), it(it0), it1(it1_)
     {
-        const long long per_mt = B_ * nchunk_;
-        mt = (int)(it0 / per_mt);
-        const long long rem = it0 - (long long)mt * per_mt;
+        const long long per_grp = B_ * nchunk_;
+        grp = (int)(it0 / per_grp);
+        const long long rem = it0 - (long long)grp * per_grp;
         b = rem / nchunk_;
         chunk = (int)(rem - b * nchunk_);
     }
@@ -203,7 +206,7 @@ struct TcIter {
         ++it;
         if (++chunk == nchunk) {
             chunk = 0;
-            if (++b == B) { b = 0; ++mt; }
+            if (++b == B) { b = 0; ++grp; }
         }
     }
 };
@@ -214,11 +217,13 @@ __device__ __forceinline__ void mbar_arrive(uint64_t *bar)
 }
 
 // Warp-specialised persistent kernel.
-//   warp 16      producer: builds the V operand of a tile from the packed codes, issues its tcgen05.mma, commits
+//   warp 16      producer: expands the packed codes of one (sequence, chunk) into the V operand ONCE, then issues
+//                the tcgen05.mma of every resident unit tile against it (the weights of up to `gsz` 128-unit
+//                tiles stay in shared memory), committing each accumulator to an mbarrier
 //   warps 0..15  epilogue: drain the accumulator (lane quarter = warp & 3, window range = warp >> 2), pool, exp,
 //                stage, TMA bulk store
-// Two TMEM accumulators (tmem_full / tmem_empty mbarriers) and two staging buffers keep the tensor pipe, the
-// epilogue and the stores of three consecutive tiles in flight.
+// Two TMEM accumulators (tmem_full / tmem_empty mbarriers), four V buffers and two staging buffers keep the
+// tensor pipe, the epilogue and the stores of consecutive tiles in flight.
 template <bool TRAIN>
 __global__ void __launch_bounds__(TC_THREADS + 32, 1) conv_tc_kernel(const TcArgs a)
 {
@@ -228,23 +233,24 @@ __global__ void __launch_bounds__(TC_THREADS + 32, 1) conv_tc_kernel(const TcArg
 
     const int K = a.K, KC = K / 8, KS = K / 16;
     const uint32_t a_bytes = (uint32_t)TC_M * K * 2;        // one image (hi or lo)
-    unsigned char *sA = smem;                               // hi, lo
+    unsigned char *sA = smem;                               // gsz tiles x (hi, lo)
     // X operand: V[pos] = 16 bytes = one-hot fp16 of (base(pos), base(pos+1)), 16-byte pitch.  Row n of the im2col
     // matrix is V[n], V[n+2], V[n+4], ... so the K-major core-matrix layout is the V array itself with
     // LBO = 32 B (next K chunk = two positions on) and SBO = 128 B (next 8 rows): no expansion is ever written.
-    uint4 *sV = reinterpret_cast<uint4 *>(sA + 2 * a_bytes);            // TC_VBUFS buffers x TC_VROWS
-    // staging, two buffers of [128][sst] floats per plane (pooled; + x_hat, argmax when TRAIN).  With a single
+    uint4 *sV = reinterpret_cast<uint4 *>(sA + (size_t)a.gsz * 2 * a_bytes);   // TC_VBUFS buffers x TC_VROWS
+    // staging, two buffers: [128][sst] floats (pooled) (+ x_hat floats and argmax bytes when TRAIN).  With a single
     // chunk per sequence the row stride is P itself: a plane is the exact image of pooled[b][u0..u0+127][:] and
     // leaves with ONE TMA bulk store.
     const int sst = a.P <= TC_WIN ? a.P : TC_WIN + 1;
-    const int plane = TC_M * (TC_WIN + 1);
-    const int nplanes = TRAIN ? 3 : 1;
-    float *stage0 = reinterpret_cast<float *>(sV + TC_VBUFS * TC_VROWS);
+    constexpr int plane = TC_M * (TC_WIN + 1);
+    constexpr int stage_bytes = (TRAIN ? 9 : 4) * plane;
+    unsigned char *stage_base = reinterpret_cast<unsigned char *>(sV + TC_VBUFS * TC_VROWS);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n_mt = (a.U + TC_M - 1) / TC_M;
+    const int n_grp = (n_mt + a.gsz - 1) / a.gsz;
     const int nchunk = (a.P + TC_WIN - 1) / TC_WIN;
-    const long long total = a.B * nchunk * n_mt;
+    const long long total = a.B * nchunk * n_grp;
     const long long it0 = total * blockIdx.x / gridDim.x, it1 = total * (blockIdx.x + 1) / gridDim.x;
 
     if (threadIdx.x == 0) {
@@ -268,47 +274,47 @@ __global__ void __launch_bounds__(TC_THREADS + 32, 1) conv_tc_kernel(const TcArg
         // =========================== producer warp ===========================
         const uint32_t idesc = (1u << 4) | ((uint32_t)(TC_N >> 3) << 17) | ((uint32_t)(TC_M >> 4) << 24);   // f16xf16->f32, M128 N240
         uint32_t a_parity = 0;
-        int cur_mt = -1, last_buf = -1;
+        int cur_grp = -1;
         long long n = 0;                                   // tiles issued by this CTA
-        // a tile touches positions n0 .. n0 + TC_VROWS: at most 20 code words and 11 mask words, one per lane
+        long long vi = 0;                                  // items (V tiles) built by this CTA
+        // an item touches positions n0 .. n0 + TC_VROWS: at most 20 code words and 11 mask words, one per lane;
+        // they are prefetched two items ahead (global latency ~ one item of work when there is a single unit tile)
         auto load_words = [&](const TcIter &t, uint32_t &cwv, uint32_t &mwv) {
+            cwv = 0u; mwv = 0u;
+            if (!t.valid()) return;
             const int n0 = t.chunk * TC_WIN * XB_POOL;
             const int ci = (n0 >> 4) + lane, mi = (n0 >> 5) + lane;
-            cwv = ci < a.wc ? a.codes[t.b * a.wc + ci] : 0u;
-            mwv = mi < a.wm ? a.nmask[t.b * a.wm + mi] : 0u;
+            if (ci < a.wc) cwv = a.codes[t.b * a.wc + ci];
+            if (mi < a.wm) mwv = a.nmask[t.b * a.wm + mi];
         };
-        uint32_t cwr_next = 0, mwr_next = 0;
-        {
-            TcIter t0(it0, it1, a.B, nchunk);
-            if (t0.valid()) load_words(t0, cwr_next, mwr_next);
-        }
-        for (TcIter t(it0, it1, a.B, nchunk); t.valid(); t.next(), ++n) {
-            const int buf = (int)(n & 1);
-            const uint32_t use = (uint32_t)(n >> 1);       // how often this buffer has been used before
-            if (t.mt != cur_mt) {
-                // a new unit tile: every MMA that reads sA must have completed before TMA overwrites it
-                if (last_buf >= 0) mbar_wait(&tmem_full[last_buf], (uint32_t)(((n - 1) >> 1) & 1));
+        uint32_t cw0, mw0, cw1, mw1;
+        TcIter tp(it0, it1, a.B, nchunk);                  // prefetch cursor
+        load_words(tp, cw0, mw0); tp.next();
+        load_words(tp, cw1, mw1); tp.next();
+        for (TcIter t(it0, it1, a.B, nchunk); t.valid(); t.next(), ++vi) {
+            const uint32_t cwr = cw0, mwr = mw0;
+            cw0 = cw1; mw0 = mw1;
+            load_words(tp, cw1, mw1); tp.next();
+            const int n0 = t.chunk * TC_WIN * XB_POOL;
+            const int mt0 = t.grp * a.gsz, mtn = min(a.gsz, n_mt - mt0);
+            if (t.grp != cur_grp) {
+                // new group of unit tiles: every MMA that reads sA must have completed before TMA overwrites it
+                if (n > 0) mbar_wait(&tmem_full[(n - 1) & 1], (uint32_t)(((n - 1) >> 1) & 1));
                 if (lane == 0) {
-                    mbar_arrive_expect_tx(&bar_a, 2 * a_bytes);
-                    tma_bulk_g2s(sA, reinterpret_cast<const unsigned char *>(a.images) + (size_t)t.mt * 2 * a_bytes, 2 * a_bytes, &bar_a);
+                    mbar_arrive_expect_tx(&bar_a, (uint32_t)mtn * 2 * a_bytes);
+                    for (int m = 0; m < mtn; ++m)
+                        tma_bulk_g2s(sA + (size_t)m * 2 * a_bytes, reinterpret_cast<const unsigned char *>(a.images) + (size_t)(mt0 + m) * 2 * a_bytes,
+                                     2 * a_bytes, &bar_a);
                 }
                 mbar_wait(&bar_a, a_parity);
                 a_parity ^= 1;
-                cur_mt = t.mt;
+                cur_grp = t.grp;
             }
-            // the words of this tile were prefetched into registers during the previous tile; fetch the next ones now
-            const uint32_t cwr = cwr_next, mwr = mwr_next;
-            const int n0 = t.chunk * TC_WIN * XB_POOL;
+            // ---- build V into buffer vi % 4.  Its previous user was item vi-4, whose MMAs are known to be complete
+            //      (the accumulators of later tiles have been seen drained), so no wait is needed and the build
+            //      overlaps the MMAs in flight.  Lane l expands the 16 positions n0+16l .. n0+16l+15 of its code word.
+            uint4 *V = sV + (int)(vi & (TC_VBUFS - 1)) * TC_VROWS;
             {
-                TcIter tn = t;
-                tn.next();
-                if (tn.valid()) load_words(tn, cwr_next, mwr_next);
-            }
-            // ---- build V(n) into buffer n % 4.  Its previous user was tile n-4, whose MMAs are known to be complete
-            //      (tile n-2 has been seen drained), so no wait is needed here and the build overlaps the MMAs of the
-            //      two tiles in flight.  Lane l expands the 16 positions n0+16l .. n0+16l+15 of its own code word.
-            {
-                uint4 *V = sV + (int)(n & (TC_VBUFS - 1)) * TC_VROWS;
                 const uint32_t w_hi = __shfl_down_sync(0xffffffffu, cwr, 1);
                 const uint32_t c16 = __funnelshift_r(cwr, w_hi, 2 * (n0 & 15));          // codes of my 16 positions
                 const uint32_t c_nx = __shfl_down_sync(0xffffffffu, c16, 1) & 3u;         // code of position n0+16(l+1)
@@ -329,112 +335,109 @@ __global__ void __launch_bounds__(TC_THREADS + 32, 1) conv_tc_kernel(const TcArg
                     ox[j] = (c & 2u) ? 0u : one;
                     oy[j] = (c & 2u) ? one : 0u;
                 }
-                if (lane < TC_VROWS / 16 && !((a.dbg & 2) && n >= TC_VBUFS)) {
+                if (lane < TC_VROWS / 16 && !((a.dbg & 2) && vi >= TC_VBUFS)) {
 #pragma unroll
                     for (int j = 0; j < 16; ++j) V[16 * lane + j] = make_uint4(ox[j], oy[j], ox[j + 1], oy[j + 1]);
                 }
             }
             fence_proxy_async();
             __syncwarp();
-            // accumulator `buf` drained by the epilogue warps
-            mbar_wait(&tmem_empty[buf], (use & 1) ^ 1);
-            fence_proxy_async();
-            __syncwarp();
-            if (lane == 0) {
-                tc_fence_after();
-                const uint32_t d = tmem_base + (uint32_t)buf * 256u;
-                const uint32_t a_hi = smem_u32(sA), a_lo = a_hi + a_bytes, bt = smem_u32(sV + (int)(n & (TC_VBUFS - 1)) * TC_VROWS);
-                const uint32_t a_lbo = 128, a_sbo = (uint32_t)KC * 128;
-                for (int ks = 0; ks < ((a.dbg & 8) ? 0 : KS); ++ks) {
-                    const uint64_t bd = make_smem_desc(bt + ks * 64, 32, 128);
-                    tc_mma_f16(d, make_smem_desc(a_hi + ks * 256, a_lbo, a_sbo), bd, idesc, ks > 0 ? 1u : 0u);
-                    tc_mma_f16(d, make_smem_desc(a_lo + ks * 256, a_lbo, a_sbo), bd, idesc, 1u);
+            for (int m = 0; m < mtn; ++m, ++n) {
+                const int buf = (int)(n & 1);
+                const uint32_t use = (uint32_t)(n >> 1);   // how often this accumulator has been used before
+                mbar_wait(&tmem_empty[buf], (use & 1) ^ 1);          // drained by the epilogue warps
+                if (lane == 0) {
+                    tc_fence_after();
+                    const uint32_t d = tmem_base + (uint32_t)buf * 256u;
+                    const uint32_t a_hi = smem_u32(sA) + (uint32_t)m * 2 * a_bytes, a_lo = a_hi + a_bytes, bt = smem_u32(V);
+                    const uint32_t a_lbo = 128, a_sbo = (uint32_t)KC * 128;
+                    for (int ks = 0; ks < ((a.dbg & 8) ? 0 : KS); ++ks) {
+                        const uint64_t bd = make_smem_desc(bt + ks * 64, 32, 128);
+                        tc_mma_f16(d, make_smem_desc(a_hi + ks * 256, a_lbo, a_sbo), bd, idesc, ks > 0 ? 1u : 0u);
+                        tc_mma_f16(d, make_smem_desc(a_lo + ks * 256, a_lbo, a_sbo), bd, idesc, 1u);
+                    }
+                    tc_commit(&tmem_full[buf]);
                 }
-                tc_commit(&tmem_full[buf]);
+                __syncwarp();
             }
-            __syncwarp();
-            last_buf = buf;
         }
     } else {
         // =========================== epilogue warps ===========================
         const int row = 32 * (warp & 3) + lane;            // TMEM lane = unit inside the tile
-        int cur_mt = -1;
-        float shift = 0.f, gam = 1.f, bet = 0.f;
         long long n = 0;
-        for (TcIter t(it0, it1, a.B, nchunk); t.valid(); t.next(), ++n) {
-            const int buf = (int)(n & 1);
-            const uint32_t use = (uint32_t)(n >> 1);
-            const int u0 = t.mt * TC_M;
-            if (t.mt != cur_mt) {
-                const int u = u0 + row;
-                shift = u < a.U ? a.shift[u] : 0.f;
-                if (TRAIN) {
-                    gam = u < a.U ? a.gamma[u] : 1.f;
-                    bet = u < a.U ? a.beta[u] : 0.f;
-                }
-                cur_mt = t.mt;
-            }
-            float *stage = stage0 + (size_t)buf * nplanes * plane;
+        for (TcIter t(it0, it1, a.B, nchunk); t.valid(); t.next()) {
+            const int mt0 = t.grp * a.gsz, mtn = min(a.gsz, n_mt - mt0);
             const int w0 = t.chunk * TC_WIN;
             const int nwin = min(TC_WIN, a.P - w0);
-            mbar_wait(&tmem_full[buf], use & 1);
-            tc_fence_after();
-            const uint32_t taddr = tmem_base + ((uint32_t)(32 * (warp & 3)) << 16) + (uint32_t)buf * 256u;
-            // four warps share a lane quarter; each drains a range of whole windows: 9 + 9 + 8 + 8 = 34
-            constexpr int S1 = 9 * XB_POOL, S2 = 18 * XB_POOL, S3 = 26 * XB_POOL, S4 = TC_WIN * XB_POOL;
-            if (u0 + 32 * (warp & 3) < a.U && !(a.dbg & 4)) {   // lane quarters without a valid unit are not read at all
-                switch (warp >> 2) {
-                case 0: tc_drain<TRAIN, 0, S1>(taddr, row, nwin, sst, plane, stage, shift, gam, bet); break;
-                case 1: tc_drain<TRAIN, S1, S2>(taddr, row, nwin, sst, plane, stage, shift, gam, bet); break;
-                case 2: tc_drain<TRAIN, S2, S3>(taddr, row, nwin, sst, plane, stage, shift, gam, bet); break;
-                default: tc_drain<TRAIN, S3, S4>(taddr, row, nwin, sst, plane, stage, shift, gam, bet); break;
-                }
-            }
-            // accumulator free again for the producer
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&tmem_empty[buf]);
-
-            // ---- store the staged tile ----
-            const int nvalid = min(TC_M, a.U - u0);
-            const size_t o = ((size_t)t.b * a.U + u0) * a.P;
-            const uint32_t bytes = (uint32_t)nvalid * a.P * 4;
-            const bool bulk_f = sst == a.P && (bytes & 15u) == 0 && ((o * 4) & 15u) == 0;
-            const bool bulk_i = TRAIN && sst == a.P && ((bytes / 4) & 15u) == 0 && (o & 15u) == 0;
-            if (a.dbg & 1) continue;
-            fence_proxy_async();
-            // the bulk stores of the previous tile read the OTHER staging buffer; they must be done reading before
-            // anybody writes it again (next tile), which this barrier then publishes
-            if (threadIdx.x == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
-            asm volatile("bar.sync 1, %0;" ::"n"(TC_THREADS) : "memory");
-            if (threadIdx.x == 0 && (bulk_f || bulk_i)) {
-                if (bulk_f) {
-                    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(a.pooled + o), "r"(smem_u32(stage)), "r"(bytes) : "memory");
-                    if (TRAIN)
-                        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(a.xhat + o), "r"(smem_u32(stage + plane)), "r"(bytes) : "memory");
-                }
-                if (bulk_i)
-                    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(a.idx + o), "r"(smem_u32(stage + 2 * plane)), "r"(bytes / 4) : "memory");
-                asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-            }
-            if (sst == a.P) {
-                // single chunk per sequence: whatever cannot leave as a bulk store is copied flat
-                const int nel = nvalid * a.P;
-                if (!bulk_f)
-                    for (int i = threadIdx.x; i < nel; i += TC_THREADS) {
-                        a.pooled[o + i] = stage[i];
-                        if (TRAIN) a.xhat[o + i] = stage[plane + i];
+            for (int m = 0; m < mtn; ++m, ++n) {
+                const int buf = (int)(n & 1);
+                const uint32_t use = (uint32_t)(n >> 1);
+                const int u0 = (mt0 + m) * TC_M;
+                const int u = u0 + row;
+                const float shift = u < a.U ? __ldg(a.shift + u) : 0.f;
+                float gam = 1.f, bet = 0.f;
+                if (TRAIN && u < a.U) { gam = __ldg(a.gamma + u); bet = __ldg(a.beta + u); }
+                float *stage = reinterpret_cast<float *>(stage_base + (size_t)buf * stage_bytes);
+                unsigned char *stage_i = reinterpret_cast<unsigned char *>(stage) + 8 * plane;
+                mbar_wait(&tmem_full[buf], use & 1);
+                tc_fence_after();
+                const uint32_t taddr = tmem_base + ((uint32_t)(32 * (warp & 3)) << 16) + (uint32_t)buf * 256u;
+                // four warps share a lane quarter; each drains a range of whole windows: 9 + 9 + 8 + 8 = 34
+                constexpr int S1 = 9 * XB_POOL, S2 = 18 * XB_POOL, S3 = 26 * XB_POOL, S4 = TC_WIN * XB_POOL;
+                if (u0 + 32 * (warp & 3) < a.U && !(a.dbg & 4)) {   // lane quarters without a valid unit are not read at all
+                    switch (warp >> 2) {
+                    case 0: tc_drain<TRAIN, 0, S1>(taddr, row, nwin, sst, stage, stage_i, shift, gam, bet); break;
+                    case 1: tc_drain<TRAIN, S1, S2>(taddr, row, nwin, sst, stage, stage_i, shift, gam, bet); break;
+                    case 2: tc_drain<TRAIN, S2, S3>(taddr, row, nwin, sst, stage, stage_i, shift, gam, bet); break;
+                    default: tc_drain<TRAIN, S3, S4>(taddr, row, nwin, sst, stage, stage_i, shift, gam, bet); break;
                     }
-                if (TRAIN && !bulk_i)
-                    for (int i = threadIdx.x; i < nel; i += TC_THREADS) a.idx[o + i] = reinterpret_cast<unsigned char *>(stage + 2 * plane)[i];
-            } else {
-                for (int r = warp; r < nvalid; r += TC_THREADS / 32) {
-                    const size_t orow = o + (size_t)r * a.P + w0;
-                    for (int c = lane; c < nwin; c += 32) {
-                        a.pooled[orow + c] = stage[r * sst + c];
-                        if (TRAIN) {
-                            a.xhat[orow + c] = stage[plane + r * sst + c];
-                            a.idx[orow + c] = reinterpret_cast<unsigned char *>(stage + 2 * plane)[r * sst + c];
+                }
+                // accumulator free again for the producer
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&tmem_empty[buf]);
+
+                // ---- store the staged tile ----
+                const int nvalid = min(TC_M, a.U - u0);
+                const size_t o = ((size_t)t.b * a.U + u0) * a.P;
+                const uint32_t bytes = (uint32_t)nvalid * a.P * 4;
+                const bool bulk_f = sst == a.P && (bytes & 15u) == 0 && ((o * 4) & 15u) == 0;
+                const bool bulk_i = TRAIN && sst == a.P && ((bytes / 4) & 15u) == 0 && (o & 15u) == 0;
+                if (a.dbg & 1) continue;
+                fence_proxy_async();
+                // the bulk stores of the previous tile read the OTHER staging buffer; they must be done reading before
+                // anybody writes it again (next tile), which this barrier then publishes
+                if (threadIdx.x == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+                asm volatile("bar.sync 1, %0;" ::"n"(TC_THREADS) : "memory");
+                if (threadIdx.x == 0 && (bulk_f || bulk_i)) {
+                    if (bulk_f) {
+                        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(a.pooled + o), "r"(smem_u32(stage)), "r"(bytes) : "memory");
+                        if (TRAIN)
+                            asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(a.xhat + o), "r"(smem_u32(stage + plane)), "r"(bytes) : "memory");
+                    }
+                    if (bulk_i)
+                        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(a.idx + o), "r"(smem_u32(stage_i)), "r"(bytes / 4) : "memory");
+                    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                }
+                if (sst == a.P) {
+                    // single chunk per sequence: whatever cannot leave as a bulk store is copied flat
+                    const int nel = nvalid * a.P;
+                    if (!bulk_f)
+                        for (int i = threadIdx.x; i < nel; i += TC_THREADS) {
+                            a.pooled[o + i] = stage[i];
+                            if (TRAIN) a.xhat[o + i] = stage[plane + i];
+                        }
+                    if (TRAIN && !bulk_i)
+                        for (int i = threadIdx.x; i < nel; i += TC_THREADS) a.idx[o + i] = stage_i[i];
+                } else {
+                    for (int r = warp; r < nvalid; r += TC_THREADS / 32) {
+                        const size_t orow = o + (size_t)r * a.P + w0;
+                        for (int c = lane; c < nwin; c += 32) {
+                            a.pooled[orow + c] = stage[r * sst + c];
+                            if (TRAIN) {
+                                a.xhat[orow + c] = stage[plane + r * sst + c];
+                                a.idx[orow + c] = stage_i[r * sst + c];
+                            }
                         }
                     }
                 }
@@ -491,13 +494,18 @@ static int launch_tc(bool train, const uint32_t *codes, const uint32_t *nmask, l
     a.wc = xb_words_codes(L); a.wm = xb_words_mask(L);
     { const char *e = getenv("XB_TC_DBG"); a.dbg = e ? atoi(e) : 0; }
     a.images = (const __half *)images; a.shift = shift; a.pooled = pooled; a.xhat = xhat; a.idx = idx; a.gamma = gamma; a.beta = beta;
-    const size_t smem = (size_t)2 * TC_M * a.K * 2 + (size_t)TC_VBUFS * TC_VROWS * 16 + (size_t)2 * (train ? 3 : 1) * TC_M * (TC_WIN + 1) * 4;
-    if (smem > 227 * 1024) {
-        xb_set_error("conv_pool_fwd_tc: %zu bytes of shared memory needed (L=%d, filter_size=%d)", smem, L, F);
+    const int n_mt = (U + TC_M - 1) / TC_M, nchunk = (a.P + TC_WIN - 1) / TC_WIN;
+    const size_t tile_bytes = (size_t)2 * TC_M * a.K * 2;
+    const size_t fixed = (size_t)TC_VBUFS * TC_VROWS * 16 + (size_t)2 * (train ? 9 : 4) * TC_M * (TC_WIN + 1);
+    const size_t budget = 227 * 1024 - 512;
+    if (fixed + tile_bytes > budget) {
+        xb_set_error("conv_pool_fwd_tc: %zu bytes of shared memory needed (L=%d, filter_size=%d)", fixed + tile_bytes, L, F);
         return XB_ERR_UNSUPPORTED;
     }
-    const int n_mt = (U + TC_M - 1) / TC_M, nchunk = (a.P + TC_WIN - 1) / TC_WIN;
-    long long total = (long long)n_mt * B * nchunk;
+    a.gsz = (int)std::min<size_t>((budget - fixed) / tile_bytes, (size_t)n_mt);
+    const size_t smem = fixed + (size_t)a.gsz * tile_bytes;
+    const int n_grp = (n_mt + a.gsz - 1) / a.gsz;
+    long long total = (long long)n_grp * B * nchunk;
     int grid = xb_num_sms();
     if (total < grid) grid = (int)total;
     cudaError_t e;
