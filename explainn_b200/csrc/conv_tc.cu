@@ -158,31 +158,36 @@ __device__ __forceinline__ void tc_drain(uint32_t taddr, int row, int nwin, int 
                                          float gam, float bet)
 {
     constexpr int plane = TC_M * (TC_WIN + 1);
-    constexpr int P0 = C0 / 16, P1 = (C1 + 15) / 16, NP = P1 - P0;
-    uint32_t r[NP * 16];
-#pragma unroll
-    for (int p = 0; p < NP; ++p) tc_ld16_nowait(taddr + (P0 + p) * 16, r + p * 16);
-    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+    constexpr int P0 = C0 / 16, P1 = (C1 + 15) / 16;
+    constexpr int BATCH = 4;                      // 64 columns in registers at a time
     float m = 0.f, xb = 0.f;
     int ib = 0;
 #pragma unroll
-    for (int i = 0; i < NP * 16; ++i) {
-        const int col = P0 * 16 + i;
-        if (col < C0 || col >= C1) continue;
-        const float v = __uint_as_float(r[i]);
-        const int ph = col % XB_POOL, win = col / XB_POOL;
-        if (TRAIN) {
-            const float x = v + shift;
-            const float z = fmaf(gam, x, bet);
-            if (ph == 0 || z > m) { m = z; xb = x; ib = ph; }
-        } else {
-            m = ph == 0 ? v : fmaxf(m, v);
-        }
-        if (ph == XB_POOL - 1 && win < nwin) {
-            stage[row * sst + win] = __expf(TRAIN ? m : m + shift);
+    for (int pb = P0; pb < P1; pb += BATCH) {
+        uint32_t r[BATCH * 16];
+#pragma unroll
+        for (int p = 0; p < BATCH; ++p)
+            if (pb + p < P1) tc_ld16_nowait(taddr + (pb + p) * 16, r + p * 16);
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+        for (int i = 0; i < BATCH * 16; ++i) {
+            const int col = pb * 16 + i;
+            if (col < C0 || col >= C1) continue;
+            const float v = __uint_as_float(r[i]);
+            const int ph = col % XB_POOL, win = col / XB_POOL;
             if (TRAIN) {
-                stage[plane + row * sst + win] = xb;
-                stage_i[row * sst + win] = (unsigned char)ib;
+                const float x = v + shift;
+                const float z = fmaf(gam, x, bet);
+                if (ph == 0 || z > m) { m = z; xb = x; ib = ph; }
+            } else {
+                m = ph == 0 ? v : fmaxf(m, v);
+            }
+            if (ph == XB_POOL - 1 && win < nwin) {
+                stage[row * sst + win] = __expf(TRAIN ? m : m + shift);
+                if (TRAIN) {
+                    stage[plane + row * sst + win] = xb;
+                    stage_i[row * sst + win] = (unsigned char)ib;
+                }
             }
         }
     }
@@ -257,8 +262,8 @@ __global__ void __launch_bounds__(TC_THREADS + 32, 1) conv_tc_kernel(const TcArg
         mbar_init(&bar_a, 1);
         mbar_init(&tmem_full[0], 1);
         mbar_init(&tmem_full[1], 1);
-        mbar_init(&tmem_empty[0], TC_THREADS / 32);
-        mbar_init(&tmem_empty[1], TC_THREADS / 32);
+        mbar_init(&tmem_empty[0], TC_THREADS / 64);      // the 8 warps of the epilogue group that owns the buffer
+        mbar_init(&tmem_empty[1], TC_THREADS / 64);
         mbar_fence_init();
     }
     if (warp == 0) {
@@ -363,53 +368,54 @@ __global__ void __launch_bounds__(TC_THREADS + 32, 1) conv_tc_kernel(const TcArg
         }
     } else {
         // =========================== epilogue warps ===========================
+        // Two groups of 8 warps; group g owns accumulator g and staging buffer g, i.e. every other tile, so the
+        // drain / stage / store chain of one tile overlaps the next tile's.  Inside a group: lane quarter =
+        // warp & 3, column half = (warp >> 2) & 1 (17 whole windows each).
+        const int grp = warp >> 3;
+        const int gtid = threadIdx.x & 255;                // thread index inside the group
         const int row = 32 * (warp & 3) + lane;            // TMEM lane = unit inside the tile
+        float *stage = reinterpret_cast<float *>(stage_base + (size_t)grp * stage_bytes);
+        unsigned char *stage_i = reinterpret_cast<unsigned char *>(stage) + 8 * plane;
+        const uint32_t taddr = tmem_base + ((uint32_t)(32 * (warp & 3)) << 16) + (uint32_t)grp * 256u;
+        constexpr int SPLIT = 17 * XB_POOL;
         long long n = 0;
         for (TcIter t(it0, it1, a.B, nchunk); t.valid(); t.next()) {
             const int mt0 = t.grp * a.gsz, mtn = min(a.gsz, n_mt - mt0);
             const int w0 = t.chunk * TC_WIN;
             const int nwin = min(TC_WIN, a.P - w0);
             for (int m = 0; m < mtn; ++m, ++n) {
-                const int buf = (int)(n & 1);
+                if ((int)(n & 1) != grp) continue;
                 const uint32_t use = (uint32_t)(n >> 1);
                 const int u0 = (mt0 + m) * TC_M;
                 const int u = u0 + row;
                 const float shift = u < a.U ? __ldg(a.shift + u) : 0.f;
                 float gam = 1.f, bet = 0.f;
                 if (TRAIN && u < a.U) { gam = __ldg(a.gamma + u); bet = __ldg(a.beta + u); }
-                float *stage = reinterpret_cast<float *>(stage_base + (size_t)buf * stage_bytes);
-                unsigned char *stage_i = reinterpret_cast<unsigned char *>(stage) + 8 * plane;
-                mbar_wait(&tmem_full[buf], use & 1);
+                // the previous tile of this group was staged in the same buffer: its bulk stores must be done
+                // reading before anybody overwrites it
+                if (gtid == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+                asm volatile("bar.sync %0, 256;" ::"r"(1 + grp) : "memory");
+                mbar_wait(&tmem_full[grp], use & 1);
                 tc_fence_after();
-                const uint32_t taddr = tmem_base + ((uint32_t)(32 * (warp & 3)) << 16) + (uint32_t)buf * 256u;
-                // four warps share a lane quarter; each drains a range of whole windows: 9 + 9 + 8 + 8 = 34
-                constexpr int S1 = 9 * XB_POOL, S2 = 18 * XB_POOL, S3 = 26 * XB_POOL, S4 = TC_WIN * XB_POOL;
                 if (u0 + 32 * (warp & 3) < a.U && !(a.dbg & 4)) {   // lane quarters without a valid unit are not read at all
-                    switch (warp >> 2) {
-                    case 0: tc_drain<TRAIN, 0, S1>(taddr, row, nwin, sst, stage, stage_i, shift, gam, bet); break;
-                    case 1: tc_drain<TRAIN, S1, S2>(taddr, row, nwin, sst, stage, stage_i, shift, gam, bet); break;
-                    case 2: tc_drain<TRAIN, S2, S3>(taddr, row, nwin, sst, stage, stage_i, shift, gam, bet); break;
-                    default: tc_drain<TRAIN, S3, S4>(taddr, row, nwin, sst, stage, stage_i, shift, gam, bet); break;
-                    }
+                    if (((warp >> 2) & 1) == 0) tc_drain<TRAIN, 0, SPLIT>(taddr, row, nwin, sst, stage, stage_i, shift, gam, bet);
+                    else tc_drain<TRAIN, SPLIT, TC_WIN * XB_POOL>(taddr, row, nwin, sst, stage, stage_i, shift, gam, bet);
                 }
                 // accumulator free again for the producer
                 tc_fence_before();
                 __syncwarp();
-                if (lane == 0) mbar_arrive(&tmem_empty[buf]);
+                if (lane == 0) mbar_arrive(&tmem_empty[grp]);
+                if (a.dbg & 1) continue;
 
                 // ---- store the staged tile ----
+                fence_proxy_async();
+                asm volatile("bar.sync %0, 256;" ::"r"(1 + grp) : "memory");
                 const int nvalid = min(TC_M, a.U - u0);
                 const size_t o = ((size_t)t.b * a.U + u0) * a.P;
                 const uint32_t bytes = (uint32_t)nvalid * a.P * 4;
                 const bool bulk_f = sst == a.P && (bytes & 15u) == 0 && ((o * 4) & 15u) == 0;
                 const bool bulk_i = TRAIN && sst == a.P && ((bytes / 4) & 15u) == 0 && (o & 15u) == 0;
-                if (a.dbg & 1) continue;
-                fence_proxy_async();
-                // the bulk stores of the previous tile read the OTHER staging buffer; they must be done reading before
-                // anybody writes it again (next tile), which this barrier then publishes
-                if (threadIdx.x == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
-                asm volatile("bar.sync 1, %0;" ::"n"(TC_THREADS) : "memory");
-                if (threadIdx.x == 0 && (bulk_f || bulk_i)) {
+                if (gtid == 0 && (bulk_f || bulk_i)) {
                     if (bulk_f) {
                         asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(a.pooled + o), "r"(smem_u32(stage)), "r"(bytes) : "memory");
                         if (TRAIN)
@@ -423,14 +429,14 @@ __global__ void __launch_bounds__(TC_THREADS + 32, 1) conv_tc_kernel(const TcArg
                     // single chunk per sequence: whatever cannot leave as a bulk store is copied flat
                     const int nel = nvalid * a.P;
                     if (!bulk_f)
-                        for (int i = threadIdx.x; i < nel; i += TC_THREADS) {
+                        for (int i = gtid; i < nel; i += 256) {
                             a.pooled[o + i] = stage[i];
                             if (TRAIN) a.xhat[o + i] = stage[plane + i];
                         }
                     if (TRAIN && !bulk_i)
-                        for (int i = threadIdx.x; i < nel; i += TC_THREADS) a.idx[o + i] = stage_i[i];
+                        for (int i = gtid; i < nel; i += 256) a.idx[o + i] = stage_i[i];
                 } else {
-                    for (int r = warp; r < nvalid; r += TC_THREADS / 32) {
+                    for (int r = warp & 7; r < nvalid; r += 8) {
                         const size_t orow = o + (size_t)r * a.P + w0;
                         for (int c = lane; c < nwin; c += 32) {
                             a.pooled[orow + c] = stage[r * sst + c];
@@ -443,7 +449,7 @@ __global__ void __launch_bounds__(TC_THREADS + 32, 1) conv_tc_kernel(const TcArg
                 }
             }
         }
-        if (threadIdx.x == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+        if (gtid == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
     }
 
     tc_fence_before();
