@@ -183,7 +183,9 @@ __device__ __forceinline__ void tc_drain(uint32_t taddr, int row, int nwin, int 
                 m = ph == 0 ? v : fmaxf(m, v);
             }
             if (ph == XB_POOL - 1 && win < nwin) {
-                stage[row * sst + win] = __expf(TRAIN ? m : m + shift);
+                // training keeps the 1-ulp deterministic exp of the table kernel: ReLU / max-pool kinks downstream turn
+                // a 1e-6 relative error into visibly different gradients; inference uses the 2-instruction MUFU exp
+                stage[row * sst + win] = TRAIN ? det_expf(m) : __expf(m + shift);
                 if (TRAIN) {
                     stage[plane + row * sst + win] = xb;
                     stage_i[row * sst + win] = (unsigned char)ib;
