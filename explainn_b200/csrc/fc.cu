@@ -14,6 +14,14 @@
 #include "../../include/explainn_b200.h"
 #include <algorithm>
 
+// tensor-core variants (fc_tc.cu)
+int xb_fc1_fwd_train_tc(const float *pooled, long long B, int U, int P, const float *W1, const float *b1, float *h1, float *part2,
+                        cudaStream_t stream);
+int xb_fc_stack_fwd_eval_tc(const float *pooled, long long B, int U, int P, const float *W1, const float *b1, const float *g2,
+                            const float *be2, const float *rm2, const float *rv2, const float *W2, const float *b2, const float *g3,
+                            const float *be3, const float *rm3, const float *rv3, float eps, float *unit_out, cudaStream_t stream);
+bool xb_fc_tc_enabled();
+
 namespace {
 
 constexpr int H = XB_HIDDEN;      // 100
@@ -670,6 +678,9 @@ extern "C" int explainn_fc_stack_fwd_eval(const float *pooled, long long B, int 
                "fc_stack_fwd_eval: null pointer");
     XB_REQUIRE(B >= 0 && U >= 1 && P >= 1, "fc_stack_fwd_eval: bad sizes");
     if (B == 0) return XB_OK;
+    if (xb_fc_tc_enabled())      // tcgen05 path (XB_FC_TC=0 selects the CUDA-core kernel below)
+        return xb_fc_stack_fwd_eval_tc(pooled, B, U, P, W1, b1, bn2_w, bn2_b, bn2_rm, bn2_rv, W2, b2, bn3_w, bn3_b, bn3_rm, bn3_rv, eps,
+                                       unit_out, stream);
     const size_t smem = FcSmem::bytes(P);
     if (smem > 200 * 1024) {
         xb_set_error("fc_stack_fwd_eval: pooled length %d needs %zu bytes of shared memory", P, smem);
@@ -721,8 +732,13 @@ extern "C" int explainn_fc_stack_fwd_train(const float *pooled, long long B, int
         xb_set_error("fc_stack_fwd_train: shared memory need (%zu / %zu bytes) exceeds the SM", smem1, smem3);
         return XB_ERR_UNSUPPORTED;
     }
-    cudaFuncSetAttribute(fc1_train_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1);
-    fc1_train_kernel<<<dim3(U, nchunk), FC_THREADS, smem1, stream>>>(pooled, B, U, P, W1, b1, h1, part2);
+    if (xb_fc_tc_enabled()) {    // tcgen05 path (XB_FC_TC=0 selects the CUDA-core kernel)
+        int rc = xb_fc1_fwd_train_tc(pooled, B, U, P, W1, b1, h1, part2, stream);
+        if (rc != XB_OK) return rc;
+    } else {
+        cudaFuncSetAttribute(fc1_train_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1);
+        fc1_train_kernel<<<dim3(U, nchunk), FC_THREADS, smem1, stream>>>(pooled, B, U, P, W1, b1, h1, part2);
+    }
     fc2_train_kernel<<<dim3(U, nchunk), FC_THREADS, 0, stream>>>(h1, B, U, part2, nchunk, bn2_w, bn2_b, bn2_rm, bn2_rv, momentum, eps,
                                                                  W2, b2, mean2, invstd2, pdrop, seed, seed_dev, h2, part3);
     cudaFuncSetAttribute(out_train_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem3);

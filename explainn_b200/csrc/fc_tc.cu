@@ -1,0 +1,265 @@
+// fc_tc.cu -- per-unit FC1 (grouped 1x1 Conv1d(U*P -> 100U), explainn/models/networks.py:105-107) on the tensor
+// cores (tcgen05.mma.kind::tf32, fp32 accumulate in TMEM), with fp32-level accuracy through the 3-term split
+//   x = x_hi + x_lo (x_hi = x truncated to tf32),   A.B ~= A_hi.B_hi + A_lo.B_hi + A_hi.B_lo      (error ~2^-21)
+//
+// MODE_TRAIN:  D[j][b] = sum_p W1[u][j][p] * pooled[b][u][p]     M = 128 (hidden channel j, 100 valid), N = 128 (b)
+//              epilogue thread = one hidden channel: + bias, per-channel sum / sum of squares over its columns
+//              (BatchNorm-2 batch statistics), h1[u][b][j] stored with lanes along j (coalesced)
+// MODE_EVAL:   D[b][j] = same product transposed                  M = 128 (b), N = 112 (j)
+//              epilogue thread = one sequence: BN-2 (running) -> ReLU -> dot with W2 -> BN-3 -> ReLU -> unit_out[b][u]
+//              (replaces networks.py:105-116 in eval mode; the hidden activations never leave the SM)
+// Both modes use the same two shared-memory tiles (W1[u] and the pooled tile, K-major, no-swizzle core-matrix
+// layout); only which one is the A operand changes.
+#include "tc_common.cuh"
+#include "../../include/explainn_b200.h"
+#include <stdlib.h>
+
+namespace {
+
+constexpr int H = XB_HIDDEN;          // 100
+constexpr int FT_ROWS = 128;          // rows of both operand tiles
+constexpr int FT_KCH = 40;            // K (= pooled positions) per chunk, multiple of 8
+constexpr int FT_KC = FT_KCH / 4;     // 16-byte core columns per chunk
+constexpr int FT_TILE_BYTES = FT_ROWS * FT_KCH * 4;   // 20 KB
+constexpr int FT_THREADS = 256;
+constexpr int FT_NEVAL = 112;         // hidden channels padded to a multiple of 16
+
+// Fill one operand tile pair (hi, lo) from `rows` x `kvalid` fp32 values (row stride in elements), zero padded.
+// Warp-level mapping: one warp store = one 8x4 core matrix (128 contiguous bytes, conflict-free).
+__device__ __forceinline__ void fill_tile(unsigned char *hi, unsigned char *lo, const float *__restrict__ src, size_t row_stride,
+                                          int rows, int k0, int kend)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int rl = lane >> 2, kl = lane & 3;
+    for (int cm = warp; cm < (FT_ROWS / 8) * FT_KC; cm += FT_THREADS / 32) {
+        const int rg = cm / FT_KC, kc = cm - rg * FT_KC;
+        const int r = rg * 8 + rl, k = k0 + kc * 4 + kl;
+        float x = 0.f;
+        if (r < rows && k < kend) x = src[(size_t)r * row_stride + k];
+        const float xh = __uint_as_float(__float_as_uint(x) & 0xFFFFE000u);
+        const uint32_t off = (uint32_t)cm * 128 + lane * 4;
+        *reinterpret_cast<float *>(hi + off) = xh;
+        *reinterpret_cast<float *>(lo + off) = x - xh;
+    }
+}
+
+struct FcTcArgs {
+    const float *pooled;     // (B,U,P)
+    long long B;
+    int U, P, nchunk;        // nchunk = ceil(B/128)
+    const float *W1, *b1;    // (100U,P), (100U)
+    // train outputs
+    float *h1;               // (U,B,100)
+    float *part2;            // (U,nchunk,2,100)
+    // eval
+    const float *g2, *be2, *rm2, *rv2, *W2, *b2, *g3, *be3, *rm3, *rv3;
+    float eps;
+    float *unit_out;         // (B,U)
+};
+
+template <bool EVAL>
+__global__ void __launch_bounds__(FT_THREADS, 2) fc1_tc_kernel(const FcTcArgs a)
+{
+    extern __shared__ __align__(128) unsigned char smem[];
+    __shared__ __align__(8) uint64_t bar;
+    __shared__ uint32_t tmem_base_s;
+    __shared__ float cf[4][128];      // train: [0] = b1 ; eval: sc2, sh2, w2
+    __shared__ float red[2][128];
+
+    unsigned char *sWh = smem, *sWl = sWh + FT_TILE_BYTES, *sAh = sWl + FT_TILE_BYTES, *sAl = sAh + FT_TILE_BYTES;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int nkch = (a.P + FT_KCH - 1) / FT_KCH;
+
+    if (threadIdx.x == 0) {
+        mbar_init(&bar, 1);
+        mbar_fence_init();
+    }
+    if (warp == 0) tc_alloc(&tmem_base_s, 128u);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_base_s;
+    const uint32_t idesc = tc_idesc(2u, 128, EVAL ? FT_NEVAL : 128);
+    uint32_t parity = 0;
+
+    const long long total = (long long)a.U * a.nchunk;
+    int cur_u = -1;
+    // contiguous tile ranges: consecutive tiles of a CTA mostly share the unit, so W1[u] is converted once
+    const long long t_begin = total * blockIdx.x / gridDim.x, t_end = total * (blockIdx.x + 1) / gridDim.x;
+    for (long long tile = t_begin; tile < t_end; ++tile) {
+        const int u = (int)(tile / a.nchunk), chunk = (int)(tile - (long long)u * a.nchunk);
+        const long long b0 = (long long)chunk * FT_ROWS;
+        const int rows = (int)min((long long)FT_ROWS, a.B - b0);
+        if (u != cur_u) {
+            if (threadIdx.x < 128) {
+                const int j = threadIdx.x, ch = u * H + j;
+                const bool v = j < H;
+                if (EVAL) {
+                    const float sc = v ? a.g2[ch] / sqrtf(a.rv2[ch] + a.eps) : 0.f;
+                    cf[0][j] = sc;
+                    cf[1][j] = v ? (a.b1[ch] - a.rm2[ch]) * sc + a.be2[ch] : 0.f;
+                    cf[2][j] = v ? a.W2[ch] : 0.f;
+                } else {
+                    cf[0][j] = v ? a.b1[ch] : 0.f;
+                }
+            }
+        }
+        for (int kc = 0; kc < nkch; ++kc) {
+            const int k0 = kc * FT_KCH;
+            // W1[u] chunk (reloaded per tile only when K is chunked or the unit changed)
+            if (u != cur_u || nkch > 1) fill_tile(sWh, sWl, a.W1 + (size_t)u * H * a.P, (size_t)a.P, H, k0, a.P);
+            fill_tile(sAh, sAl, a.pooled + ((size_t)b0 * a.U + u) * a.P, (size_t)a.U * a.P, rows, k0, a.P);
+            fence_proxy_async();
+            tc_fence_before();
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                tc_fence_after();
+                const uint32_t wh = smem_u32(sWh), wl = smem_u32(sWl), ah = smem_u32(sAh), al = smem_u32(sAl);
+                const uint32_t lbo = 128, sbo = FT_KC * 128;
+                for (int ks = 0; ks < FT_KCH / 8; ++ks) {
+                    const uint32_t o = ks * 256;      // two 16-byte core columns per K = 8 step
+                    const uint64_t dWh = make_smem_desc(wh + o, lbo, sbo), dWl = make_smem_desc(wl + o, lbo, sbo);
+                    const uint64_t dAh = make_smem_desc(ah + o, lbo, sbo), dAl = make_smem_desc(al + o, lbo, sbo);
+                    const uint32_t acc0 = (kc > 0 || ks > 0) ? 1u : 0u;
+                    if (EVAL) {      // M = sequences (pooled tile is the A operand), N = hidden channels
+                        tc_mma_tf32(tmem_base, dAh, dWh, idesc, acc0);
+                        tc_mma_tf32(tmem_base, dAl, dWh, idesc, 1u);
+                        tc_mma_tf32(tmem_base, dAh, dWl, idesc, 1u);
+                    } else {         // M = hidden channels (W1 is the A operand), N = sequences
+                        tc_mma_tf32(tmem_base, dWh, dAh, idesc, acc0);
+                        tc_mma_tf32(tmem_base, dWl, dAh, idesc, 1u);
+                        tc_mma_tf32(tmem_base, dWh, dAl, idesc, 1u);
+                    }
+                }
+                tc_commit(&bar);
+            }
+            mbar_wait(&bar, parity);
+            parity ^= 1;
+            tc_fence_after();
+        }
+        cur_u = u;
+
+        // ---------------- epilogue ----------------
+        const int q = warp & 3, half = warp >> 2;
+        const int row = 32 * q + lane;                                   // TMEM lane
+        const uint32_t taddr = tmem_base + ((uint32_t)(32 * q) << 16);
+        if (!EVAL) {
+            // row = hidden channel j; this warp handles sequences [64*half, 64*half+64)
+            const int j = row;
+            const float bias = cf[0][j];
+            float s = 0.f, sq = 0.f;
+            float *dst = a.h1 + ((size_t)u * a.B + b0) * H + j;
+#pragma unroll
+            for (int pb = 0; pb < 4; pb += 2) {
+                uint32_t r[32];
+                tc_ld16_nowait(taddr + 64 * half + pb * 16, r);
+                tc_ld16_nowait(taddr + 64 * half + pb * 16 + 16, r + 16);
+                tc_wait_ld();
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                    const int b = 64 * half + pb * 16 + i;
+                    const float h = __uint_as_float(r[i]) + bias;
+                    if (b < rows) {
+                        s += h;
+                        sq = fmaf(h, h, sq);
+                        if (j < H) dst[(size_t)b * H] = h;
+                    }
+                }
+            }
+            red[half][j] = s;
+            __syncthreads();
+            float s_all = 0.f;
+            if (threadIdx.x < 128) s_all = red[0][threadIdx.x] + red[1][threadIdx.x];
+            __syncthreads();
+            red[half][j] = sq;
+            __syncthreads();
+            if (threadIdx.x < H) {
+                float *pp = a.part2 + ((size_t)u * a.nchunk + chunk) * 2 * H;
+                pp[threadIdx.x] = s_all;
+                pp[H + threadIdx.x] = red[0][threadIdx.x] + red[1][threadIdx.x];
+            }
+        } else {
+            // row = sequence b; warps 0-3 handle hidden channels 0..63, warps 4-7 channels 64..111
+            float dot = 0.f;
+#pragma unroll
+            for (int pb = 0; pb < 4; ++pb) {
+                if (half == 1 && pb == 3) break;
+                uint32_t r[16];
+                const int c0 = 64 * half + pb * 16;
+                tc_ld16_nowait(taddr + c0, r);
+                tc_wait_ld();
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                    const int jj = c0 + i;
+                    const float v = fmaxf(fmaf(__uint_as_float(r[i]), cf[0][jj], cf[1][jj]), 0.f);
+                    dot = fmaf(v, cf[2][jj], dot);
+                }
+            }
+            red[half][row] = dot;
+            __syncthreads();
+            if (threadIdx.x < rows) {
+                const int b = threadIdx.x;
+                const float h2 = (red[0][b] + red[1][b]) + a.b2[u];
+                const float sc = a.g3[u] / sqrtf(a.rv3[u] + a.eps);
+                a.unit_out[(b0 + b) * a.U + u] = fmaxf((h2 - a.rm3[u]) * sc + a.be3[u], 0.f);
+            }
+        }
+        // the accumulator and the operand tiles are reused by the next tile
+        tc_fence_before();
+        __syncthreads();
+    }
+    if (warp == 0) {
+        tc_fence_after();
+        tc_dealloc(tmem_base, 128u);
+    }
+}
+
+int launch_fc1_tc(bool eval, const FcTcArgs &a, cudaStream_t stream)
+{
+    const size_t smem = 4 * (size_t)FT_TILE_BYTES;
+    const long long total = (long long)a.U * a.nchunk;
+    int grid = 2 * xb_num_sms();
+    if (total < grid) grid = (int)total;
+    cudaError_t e;
+    if (eval) {
+        e = cudaFuncSetAttribute(fc1_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e == cudaSuccess) fc1_tc_kernel<true><<<grid, FT_THREADS, smem, stream>>>(a);
+    } else {
+        e = cudaFuncSetAttribute(fc1_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e == cudaSuccess) fc1_tc_kernel<false><<<grid, FT_THREADS, smem, stream>>>(a);
+    }
+    if (e != cudaSuccess) {
+        xb_set_error("fc1_tc: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+        return XB_ERR_CUDA;
+    }
+    return xb_check_launch("fc1_tc");
+}
+
+}  // namespace
+
+// used by fc.cu
+int xb_fc1_fwd_train_tc(const float *pooled, long long B, int U, int P, const float *W1, const float *b1, float *h1, float *part2,
+                        cudaStream_t stream)
+{
+    FcTcArgs a{};
+    a.pooled = pooled; a.B = B; a.U = U; a.P = P; a.nchunk = (int)((B + FT_ROWS - 1) / FT_ROWS);
+    a.W1 = W1; a.b1 = b1; a.h1 = h1; a.part2 = part2;
+    return launch_fc1_tc(false, a, stream);
+}
+
+int xb_fc_stack_fwd_eval_tc(const float *pooled, long long B, int U, int P, const float *W1, const float *b1, const float *g2,
+                            const float *be2, const float *rm2, const float *rv2, const float *W2, const float *b2, const float *g3,
+                            const float *be3, const float *rm3, const float *rv3, float eps, float *unit_out, cudaStream_t stream)
+{
+    FcTcArgs a{};
+    a.pooled = pooled; a.B = B; a.U = U; a.P = P; a.nchunk = (int)((B + FT_ROWS - 1) / FT_ROWS);
+    a.W1 = W1; a.b1 = b1; a.g2 = g2; a.be2 = be2; a.rm2 = rm2; a.rv2 = rv2; a.W2 = W2; a.b2 = b2;
+    a.g3 = g3; a.be3 = be3; a.rm3 = rm3; a.rv3 = rv3; a.eps = eps; a.unit_out = unit_out;
+    return launch_fc1_tc(true, a, stream);
+}
+
+bool xb_fc_tc_enabled()
+{
+    const char *e = getenv("XB_FC_TC");
+    return !(e && e[0] == '0');
+}
