@@ -69,6 +69,17 @@ __device__ __forceinline__ float det_expf(float x)
 
 __device__ __forceinline__ float fp16_round(float x) { return __half2float(__float2half_rn(x)); }
 
+// ---- dropout ---------------------------------------------------------------------------------------
+// counter-based dropout mask: splitmix64 of (seed, element index); keep iff the top 32 bits >= p * 2^32
+__device__ __forceinline__ float drop_scale(unsigned long long seed, unsigned long long elem, unsigned thresh, float keep_scale)
+{
+    unsigned long long z = seed + elem * 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    z ^= z >> 31;
+    return (unsigned)(z >> 32) >= thresh ? keep_scale : 0.0f;
+}
+
 // ---- small warp helpers ------------------------------------------------------------------------
 __device__ __forceinline__ float warp_sum(float v)
 {

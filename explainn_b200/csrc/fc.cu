@@ -21,6 +21,10 @@ int xb_fc_stack_fwd_eval_tc(const float *pooled, long long B, int U, int P, cons
                             const float *be2, const float *rm2, const float *rv2, const float *W2, const float *b2, const float *g3,
                             const float *be3, const float *rm3, const float *rv3, float eps, float *unit_out, cudaStream_t stream);
 bool xb_fc_tc_enabled();
+int xb_bwd_fc1_tc(const float *h1, const float *gh2, const float *pooled, long long B, int U, int P, const float *g2, const float *be2,
+                  const float *mean2, const float *invstd2, const float *W1, const float *W2, float pdrop, unsigned long long seed,
+                  const unsigned long long *seed_dev, const float *pb2, float *gpool, float *dW1p, float *dW2, float *db1, float *db2,
+                  float *dg2, float *dbe2, cudaStream_t stream);
 
 namespace {
 
@@ -185,16 +189,6 @@ __global__ void __launch_bounds__(256) linear_fwd_kernel(const float *__restrict
 // Training-mode forward (BatchNorm batch statistics, dropout)
 // ================================================================================================
 constexpr int HS = H + 1;   // row stride of the hidden tile in shared memory (odd: conflict-free columns)
-
-// counter-based dropout mask: splitmix64 of (seed, element index); keep iff the top 32 bits >= p * 2^32
-__device__ __forceinline__ float drop_scale(unsigned long long seed, unsigned long long elem, unsigned thresh, float keep_scale)
-{
-    unsigned long long z = seed + elem * 0x9E3779B97F4A7C15ull;
-    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
-    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
-    z ^= z >> 31;
-    return (unsigned)(z >> 32) >= thresh ? keep_scale : 0.0f;
-}
 
 // h1[u][b][:] = W1[u] . pooled[u][b][:] + b1[u]  and per-tile column sums for BatchNorm-2
 __global__ void __launch_bounds__(FC_THREADS) fc1_train_kernel(const float *__restrict__ pooled, long long B, int U, int P,
@@ -787,7 +781,13 @@ extern "C" int explainn_fc_stack_bwd(const float *glogits, long long B, int U, i
                                                                           W2, pdrop, seed, seed_dev, pb2, gpool, dW1_partials, dW2, db1, db2,  \
                                                                           dbn2_w, dbn2_b);                                          \
     } while (0)
-    if (P <= 32) XB_LAUNCH_BWD_FC1(16);
+    int rc_tc = XB_ERR_UNSUPPORTED;
+    if (xb_fc_tc_enabled())
+        rc_tc = xb_bwd_fc1_tc(h1, gh2, pooled, B, U, P, bn2_w, bn2_b, mean2, invstd2, W1, W2, pdrop, seed, seed_dev, pb2, gpool, dW1_partials,
+                              dW2, db1, db2, dbn2_w, dbn2_b, stream);
+    if (rc_tc == XB_OK) {
+    } else if (rc_tc != XB_ERR_UNSUPPORTED) return rc_tc;
+    else if (P <= 32) XB_LAUNCH_BWD_FC1(16);
     else if (P <= 40) XB_LAUNCH_BWD_FC1(20);
     else if (P <= 72) XB_LAUNCH_BWD_FC1(36);
     else if (P <= 144) XB_LAUNCH_BWD_FC1(72);

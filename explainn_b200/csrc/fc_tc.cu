@@ -214,6 +214,266 @@ __global__ void __launch_bounds__(FT_THREADS, 2) fc1_tc_kernel(const FcTcArgs a)
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// Backward of FC1 on the tensor cores.  Per tile (unit u, 128 sequences):
+//   G[b][j]  = d loss / d h1 (BatchNorm-2 backward of the ReLU/dropout-masked upstream gradient), built on the CUDA cores
+//   D1[b][p] = sum_j G[b][j] * W1[j][p]       -> d(pooled)        M = b,  N = p (48), K = j (104)
+//   D2[j][p] = sum_b G[b][j] * pooled[b][p]   -> dW1 partial      M = j,  N = p (48), K = b (128)
+// kind::tf32 takes K-major operands only (MN-major descriptors produce no result on this part), so the two
+// products need G with different contiguous indices.  Each thread keeps its 52 G values in registers: phase 1
+// stores them j-contiguous and runs D1; once those MMAs have retired, phase 2 stores them b-contiguous into the
+// SAME shared-memory region and runs D2.  W1 and the pooled tile are stored transposed once.  3-term tf32 split.
+// ------------------------------------------------------------------------------------------------
+constexpr int BT_J = 104;                 // hidden channels padded to a multiple of 8
+constexpr int BT_P = 48;                  // pooled positions padded to a multiple of 16
+constexpr int BT_G_SBO = (BT_J / 4) * 128;          // 8-row group stride of a tile with K = j  (3328)
+constexpr int BT_B_SBO = (FT_ROWS / 4) * 128;       // 8-row group stride of a tile with K = b  (4096)
+constexpr int BT_G_BYTES = FT_ROWS * BT_J * 4;      // G  [128 b][104 j]   53,248
+constexpr int BT_GT_BYTES = FT_ROWS * FT_ROWS * 4;  // Gt [128 j][128 b]   65,536
+constexpr int BT_W_BYTES = BT_P * BT_J * 4;         // W1t [48 p][104 j]   19,968
+constexpr int BT_A_BYTES = BT_P * FT_ROWS * 4;      // At  [48 p][128 b]   24,576
+constexpr int BT_NG = (FT_ROWS / 8) * (BT_J / 4) / (FT_THREADS / 32);   // core matrices of G per warp = 52
+
+struct FcBwdArgs {
+    const float *h1, *gh2, *pooled;
+    long long B;
+    int U, P, nchunk;
+    const float *g2, *be2, *mean2, *invstd2, *W1, *W2;
+    float pdrop;
+    unsigned long long seed0;
+    const unsigned long long *seed_dev;
+    const float *pb2;
+    float *gpool, *dW1p, *dW2, *db1, *db2, *dg2, *dbe2;
+};
+
+__device__ __forceinline__ uint32_t core_off(int r, int k, int sbo) { return (uint32_t)(r >> 3) * sbo + (uint32_t)(k >> 2) * 128 + (r & 7) * 16 + (k & 3) * 4; }
+
+__device__ __forceinline__ void st_split(unsigned char *hi, unsigned char *lo, uint32_t off, float x)
+{
+    const float xh = __uint_as_float(__float_as_uint(x) & 0xFFFFE000u);
+    *reinterpret_cast<float *>(hi + off) = xh;
+    *reinterpret_cast<float *>(lo + off) = x - xh;
+}
+
+__global__ void __launch_bounds__(FT_THREADS, 1) bwd_fc1_tc_kernel(const FcBwdArgs a)
+{
+    extern __shared__ __align__(128) unsigned char smem[];
+    __shared__ __align__(8) uint64_t bar;
+    __shared__ uint32_t tmem_base_s;
+    __shared__ float mu[128], inv[128], ga[128], be[128], w2s[128], m1s[128], m2s[128];
+
+    unsigned char *sR = smem;                                   // phase 1: G hi | G lo ; phase 2: Gt hi | Gt lo
+    unsigned char *sAh = sR + 2 * BT_GT_BYTES, *sAl = sAh + BT_A_BYTES;
+    unsigned char *sWh = sAl + BT_A_BYTES, *sWl = sWh + BT_W_BYTES;
+    // the h1 tile (128 x 100 floats, contiguous in global memory) is staged by ONE TMA bulk copy into the bytes that
+    // phase 1 does not use yet: the tail of the Gt region plus the pooled-tile buffers (filled after the G build)
+    float *sH = reinterpret_cast<float *>(sR + 2 * BT_G_BYTES);
+    static_assert(2 * BT_GT_BYTES + 2 * BT_A_BYTES - 2 * BT_G_BYTES >= FT_ROWS * H * 4, "h1 staging does not fit");
+    __shared__ __align__(8) uint64_t bar_h;
+    __shared__ float gh2s[FT_ROWS];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const unsigned long long seed = a.seed0 + (a.seed_dev ? *a.seed_dev * 0xD1B54A32D192ED03ull : 0ull);
+    const unsigned thresh = a.pdrop > 0.f ? (unsigned)min(4294967295.0, (double)a.pdrop * 4294967296.0) : 0u;
+    const float keep_scale = a.pdrop > 0.f ? 1.0f / (1.0f - a.pdrop) : 1.0f;
+
+    if (threadIdx.x == 0) {
+        mbar_init(&bar, 1);
+        mbar_init(&bar_h, 1);
+        mbar_fence_init();
+    }
+    if (warp == 0) tc_alloc(&tmem_base_s, 128u);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_base_s;
+    const uint32_t idesc = tc_idesc(2u, 128, BT_P);
+    uint32_t parity = 0, h_parity = 0;
+
+    const long long total = (long long)a.U * a.nchunk;
+    const long long t_begin = total * blockIdx.x / gridDim.x, t_end = total * (blockIdx.x + 1) / gridDim.x;
+    int cur_u = -1;
+    for (long long tile = t_begin; tile < t_end; ++tile) {
+        const int u = (int)(tile / a.nchunk), chunk = (int)(tile - (long long)u * a.nchunk);
+        const long long b0 = (long long)chunk * FT_ROWS;
+        const int rows = (int)min((long long)FT_ROWS, a.B - b0);
+        if (threadIdx.x == 0) {
+            // previous tile's tensor-core reads of this region are complete (its second commit was waited on)
+            mbar_arrive_expect_tx(&bar_h, (uint32_t)rows * H * 4);
+            tma_bulk_g2s(sH, a.h1 + ((size_t)u * a.B + b0) * H, (uint32_t)rows * H * 4, &bar_h);
+        }
+        if (threadIdx.x < FT_ROWS) gh2s[threadIdx.x] = threadIdx.x < rows ? a.gh2[(size_t)u * a.B + b0 + threadIdx.x] : 0.f;
+        if (u != cur_u) {
+            if (threadIdx.x < 128) {
+                const int j = threadIdx.x, ch = u * H + j;
+                const bool v = j < H;
+                float acc = 0.f, s1 = 0.f, s2 = 0.f;
+                if (v) {
+                    for (int k = 0; k < a.nchunk; ++k) {
+                        const float *pp = a.pb2 + ((size_t)u * a.nchunk + k) * 3 * H;
+                        acc += pp[j]; s1 += pp[H + j]; s2 += pp[2 * H + j];
+                    }
+                    if (chunk == 0) {
+                        if (a.dW2) a.dW2[ch] = acc;
+                        if (a.dbe2) a.dbe2[ch] = s1;
+                        if (a.dg2) a.dg2[ch] = s2;
+                        if (a.db1) a.db1[ch] = 0.f;          // bias followed by train-mode BatchNorm: gradient is exactly zero
+                        if (a.db2 && j == 0) a.db2[u] = 0.f;
+                    }
+                }
+                mu[j] = v ? a.mean2[ch] : 0.f; inv[j] = v ? a.invstd2[ch] : 0.f; ga[j] = v ? a.g2[ch] : 0.f;
+                be[j] = v ? a.be2[ch] : 0.f; w2s[j] = v ? a.W2[ch] : 0.f;
+                m1s[j] = s1 / (float)a.B; m2s[j] = s2 / (float)a.B;
+            }
+            // W1[u] transposed: rows p, K = j contiguous (B operand of D1); one warp store = one core matrix.
+            // All loads are issued before the first store so that only one global latency is exposed.
+            {
+                constexpr int NCM = (BT_P / 8) * (BT_J / 4), NIT = (NCM + FT_THREADS / 32 - 1) / (FT_THREADS / 32);
+                float xv[NIT];
+                const float *wsrc = a.W1 + (size_t)u * H * a.P;
+#pragma unroll
+                for (int i = 0; i < NIT; ++i) {
+                    const int cm = warp + (FT_THREADS / 32) * i;
+                    const int pg = cm / (BT_J / 4), kc = cm - pg * (BT_J / 4);
+                    const int p = pg * 8 + (lane >> 2), j = kc * 4 + (lane & 3);
+                    xv[i] = (cm < NCM && j < H && p < a.P) ? __ldg(wsrc + j * a.P + p) : 0.f;
+                }
+#pragma unroll
+                for (int i = 0; i < NIT; ++i) {
+                    const int cm = warp + (FT_THREADS / 32) * i;
+                    if (cm < NCM) st_split(sWh, sWl, (uint32_t)cm * 128 + lane * 4, xv[i]);
+                }
+            }
+            cur_u = u;
+        }
+        __syncthreads();          // coefficient arrays and gh2 tile ready for the G build
+        mbar_wait(&bar_h, h_parity);
+        h_parity ^= 1;
+        // G values of this thread: core matrix cm = warp + 8*i  ->  (row r = 8*rg + lane/4, channel j = 4*kc + lane%4)
+        float gv[BT_NG];
+#pragma unroll
+        for (int i = 0; i < BT_NG; ++i) {
+            const int cm = warp + (FT_THREADS / 32) * i;
+            const int rg = cm / (BT_J / 4), kc = cm - rg * (BT_J / 4);
+            const int r = rg * 8 + (lane >> 2), j = kc * 4 + (lane & 3);
+            float v = 0.f;
+            if (r < rows && j < H) {
+                const size_t rowi = (size_t)u * a.B + b0 + r;
+                const float xh = (sH[r * H + j] - mu[j]) * inv[j];
+                const float zb = fmaf(ga[j], xh, be[j]);
+                float gz2 = 0.f;
+                if (zb > 0.f) {
+                    const float ks = a.pdrop > 0.f ? drop_scale(seed, rowi * H + j, thresh, keep_scale) : 1.0f;
+                    gz2 = gh2s[r] * w2s[j] * ks;
+                }
+                v = ga[j] * inv[j] * (gz2 - m1s[j] - xh * m2s[j]);
+            }
+            gv[i] = v;
+            st_split(sR, sR + BT_G_BYTES, (uint32_t)cm * 128 + lane * 4, v);      // G, j-contiguous
+        }
+        fence_proxy_async();
+        tc_fence_before();
+        __syncthreads();
+        // ---- D1 = G . W1   (TMEM columns 0..47) ----
+        if (threadIdx.x == 0) {
+            tc_fence_after();
+            const uint32_t gh = smem_u32(sR), gl = gh + BT_G_BYTES, wh = smem_u32(sWh), wl = smem_u32(sWl);
+            for (int ks = 0; ks < BT_J / 8; ++ks) {
+                const uint64_t dGh = make_smem_desc(gh + ks * 256, 128, BT_G_SBO), dGl = make_smem_desc(gl + ks * 256, 128, BT_G_SBO);
+                const uint64_t dWh = make_smem_desc(wh + ks * 256, 128, BT_G_SBO), dWl = make_smem_desc(wl + ks * 256, 128, BT_G_SBO);
+                tc_mma_tf32(tmem_base, dGh, dWh, idesc, ks > 0 ? 1u : 0u);
+                tc_mma_tf32(tmem_base, dGl, dWh, idesc, 1u);
+                tc_mma_tf32(tmem_base, dGh, dWl, idesc, 1u);
+            }
+            tc_commit(&bar);
+        }
+        // while D1 runs: pooled tile transposed, rows p, K = b contiguous (B operand of D2).  It overwrites the h1
+        // staging, which every thread has finished reading (barrier above).
+        {
+            constexpr int NIT = (BT_P / 8) * (FT_ROWS / 4) / (FT_THREADS / 32);     // 24 core matrices per warp
+            float xv[NIT];
+            const float *psrc = a.pooled + ((size_t)b0 * a.U + u) * a.P;
+            const int rstride = a.U * a.P;
+#pragma unroll
+            for (int i = 0; i < NIT; ++i) {
+                const int cm = warp + (FT_THREADS / 32) * i;
+                const int pg = cm / (FT_ROWS / 4), bc = cm - pg * (FT_ROWS / 4);
+                const int p = pg * 8 + (lane >> 2), r = bc * 4 + (lane & 3);
+                xv[i] = (r < rows && p < a.P) ? __ldg(psrc + (size_t)r * rstride + p) : 0.f;
+            }
+#pragma unroll
+            for (int i = 0; i < NIT; ++i) st_split(sAh, sAl, (uint32_t)(warp + (FT_THREADS / 32) * i) * 128 + lane * 4, xv[i]);
+        }
+        mbar_wait(&bar, parity);
+        parity ^= 1;
+        tc_fence_after();
+        // ---- phase 2: the same values b-contiguous (Gt[j][b]) over the region the finished MMAs no longer read ----
+#pragma unroll
+        for (int i = 0; i < BT_NG; ++i) {
+            const int cm = warp + (FT_THREADS / 32) * i;
+            const int rg = cm / (BT_J / 4), kc = cm - rg * (BT_J / 4);
+            const int r = rg * 8 + (lane >> 2), j = kc * 4 + (lane & 3);
+            st_split(sR, sR + BT_GT_BYTES, core_off(j, r, BT_B_SBO), gv[i]);
+        }
+        // rows 104..127 of Gt are never written: they only feed accumulator rows that are not read back
+        fence_proxy_async();
+        tc_fence_before();
+        __syncthreads();
+        // ---- D2 = G^T . pooled   (TMEM columns 64..111) ----
+        if (threadIdx.x == 0) {
+            tc_fence_after();
+            const uint32_t th = smem_u32(sR), tl = th + BT_GT_BYTES, ah = smem_u32(sAh), al = smem_u32(sAl);
+            for (int ks = 0; ks < FT_ROWS / 8; ++ks) {
+                const uint64_t dTh = make_smem_desc(th + ks * 256, 128, BT_B_SBO), dTl = make_smem_desc(tl + ks * 256, 128, BT_B_SBO);
+                const uint64_t dAh = make_smem_desc(ah + ks * 256, 128, BT_B_SBO), dAl = make_smem_desc(al + ks * 256, 128, BT_B_SBO);
+                tc_mma_tf32(tmem_base + 64, dTh, dAh, idesc, ks > 0 ? 1u : 0u);
+                tc_mma_tf32(tmem_base + 64, dTl, dAh, idesc, 1u);
+                tc_mma_tf32(tmem_base + 64, dTh, dAl, idesc, 1u);
+            }
+            tc_commit(&bar);
+        }
+        // ---- while D2 runs, warps 0-3 drain D1 (row = sequence) ----
+        const int q = warp & 3, which = warp >> 2;
+        const int row = 32 * q + lane;
+        if (which == 0) {
+            const uint32_t taddr = tmem_base + ((uint32_t)(32 * q) << 16);
+            uint32_t r[48];
+            tc_ld16_nowait(taddr, r);
+            tc_ld16_nowait(taddr + 16, r + 16);
+            tc_ld16_nowait(taddr + 32, r + 32);
+            tc_wait_ld();
+            if (row < rows) {
+                float *dst = a.gpool + ((size_t)(b0 + row) * a.U + u) * a.P;
+#pragma unroll
+                for (int p = 0; p < BT_P; ++p)
+                    if (p < a.P) dst[p] = __uint_as_float(r[p]);
+            }
+        }
+        mbar_wait(&bar, parity);
+        parity ^= 1;
+        tc_fence_after();
+        if (which == 1) {      // warps 4-7 drain D2 (row = hidden channel)
+            const uint32_t taddr = tmem_base + ((uint32_t)(32 * q) << 16) + 64;
+            uint32_t r[48];
+            tc_ld16_nowait(taddr, r);
+            tc_ld16_nowait(taddr + 16, r + 16);
+            tc_ld16_nowait(taddr + 32, r + 32);
+            tc_wait_ld();
+            if (row < H) {
+                float *dst = a.dW1p + (((size_t)chunk * a.U + u) * H + row) * a.P;
+#pragma unroll
+                for (int p = 0; p < BT_P; ++p)
+                    if (p < a.P) dst[p] = __uint_as_float(r[p]);
+            }
+        }
+        tc_fence_before();
+        __syncthreads();
+    }
+    if (warp == 0) {
+        tc_fence_after();
+        tc_dealloc(tmem_base, 128u);
+    }
+}
+
 int launch_fc1_tc(bool eval, const FcTcArgs &a, cudaStream_t stream)
 {
     const size_t smem = 4 * (size_t)FT_TILE_BYTES;
@@ -262,4 +522,28 @@ bool xb_fc_tc_enabled()
 {
     const char *e = getenv("XB_FC_TC");
     return !(e && e[0] == '0');
+}
+
+// returns XB_ERR_UNSUPPORTED (without setting an error) when the shape does not fit the tensor-core tiles
+int xb_bwd_fc1_tc(const float *h1, const float *gh2, const float *pooled, long long B, int U, int P, const float *g2, const float *be2,
+                  const float *mean2, const float *invstd2, const float *W1, const float *W2, float pdrop, unsigned long long seed,
+                  const unsigned long long *seed_dev, const float *pb2, float *gpool, float *dW1p, float *dW2, float *db1, float *db2,
+                  float *dg2, float *dbe2, cudaStream_t stream)
+{
+    if (P > BT_P) return XB_ERR_UNSUPPORTED;
+    FcBwdArgs a{};
+    a.h1 = h1; a.gh2 = gh2; a.pooled = pooled; a.B = B; a.U = U; a.P = P; a.nchunk = (int)((B + FT_ROWS - 1) / FT_ROWS);
+    a.g2 = g2; a.be2 = be2; a.mean2 = mean2; a.invstd2 = invstd2; a.W1 = W1; a.W2 = W2; a.pdrop = pdrop; a.seed0 = seed; a.seed_dev = seed_dev;
+    a.pb2 = pb2; a.gpool = gpool; a.dW1p = dW1p; a.dW2 = dW2; a.db1 = db1; a.db2 = db2; a.dg2 = dg2; a.dbe2 = dbe2;
+    const size_t smem = 2 * (size_t)(BT_GT_BYTES + BT_A_BYTES + BT_W_BYTES);
+    const long long total = (long long)U * a.nchunk;
+    int grid = xb_num_sms();
+    if (total < grid) grid = (int)total;
+    cudaError_t e = cudaFuncSetAttribute(bwd_fc1_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) {
+        xb_set_error("bwd_fc1_tc: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+        return XB_ERR_CUDA;
+    }
+    bwd_fc1_tc_kernel<<<grid, FT_THREADS, smem, stream>>>(a);
+    return xb_check_launch("bwd_fc1_tc");
 }
