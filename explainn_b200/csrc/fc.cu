@@ -322,10 +322,16 @@ __global__ void __launch_bounds__(256) out_train_kernel(const float *__restrict_
                                                         float *__restrict__ rm3, float *__restrict__ rv3, float momentum,
                                                         float eps, float *__restrict__ mean3, float *__restrict__ invstd3,
                                                         const float *__restrict__ Wf, const float *__restrict__ bf,
-                                                        float *__restrict__ unit, float *__restrict__ logits)
+                                                        float *__restrict__ unit, float *__restrict__ logits, int wf_in_smem)
 {
-    extern __shared__ float xs[];   // [8][U] then sc3[U], sh3[U]
+    extern __shared__ float xs[];   // [8][U] then sc3[U], sh3[U], then (when it fits) Wf as [C][U+1]
     float *sc3 = xs + OT_ROWS * U, *sh3 = sc3 + U;
+    float *wfs = sh3 + U;
+    if (wf_in_smem)
+        for (int i = threadIdx.x; i < C * U; i += blockDim.x) {
+            const int c = i / U, k = i - c * U;
+            wfs[c * (U + 1) + k] = Wf[i];
+        }
     const long long b0 = (long long)blockIdx.x * OT_ROWS;
     const int rows = (int)min((long long)OT_ROWS, B - b0);
     for (int u = threadIdx.x; u < U; u += blockDim.x) {
@@ -364,16 +370,17 @@ __global__ void __launch_bounds__(256) out_train_kernel(const float *__restrict_
     if (warp < rows) {
         const float *xr = xs + warp * U;
         for (int c = lane; c < C; c += 32) {
-            const float *w = Wf + (size_t)c * U;
+            // lanes run over the classes: in shared memory the row stride U+1 keeps them on different banks
+            const float *w = wf_in_smem ? wfs + (size_t)c * (U + 1) : Wf + (size_t)c * U;
             float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
             int k = 0;
             for (; k + 3 < U; k += 4) {
-                a0 = fmaf(xr[k], __ldg(w + k), a0);
-                a1 = fmaf(xr[k + 1], __ldg(w + k + 1), a1);
-                a2 = fmaf(xr[k + 2], __ldg(w + k + 2), a2);
-                a3 = fmaf(xr[k + 3], __ldg(w + k + 3), a3);
+                a0 = fmaf(xr[k], w[k], a0);
+                a1 = fmaf(xr[k + 1], w[k + 1], a1);
+                a2 = fmaf(xr[k + 2], w[k + 2], a2);
+                a3 = fmaf(xr[k + 3], w[k + 3], a3);
             }
-            for (; k < U; ++k) a0 = fmaf(xr[k], __ldg(w + k), a0);
+            for (; k < U; ++k) a0 = fmaf(xr[k], w[k], a0);
             logits[(b0 + warp) * C + c] = ((a0 + a1) + (a2 + a3)) + bf[c];
         }
     }
@@ -419,38 +426,54 @@ __global__ void __launch_bounds__(256) bwd_final_linear_kernel(const float *__re
 }
 
 // gz3[b][u] = (unit[b][u] > 0) * sum_c gl[b][c] * Wf[c][u]     (ReLU-3 mask applied; (B,U) layout)
-// grid ceil(B/8); warp = one sequence, lanes run over the units.  Wf == NULL: gl already is d/d unit.
+// grid (ceil(B/8), ceil(U/64)); warp = one sequence, each lane two units of the 64-unit slice whose Wf columns
+// sit in shared memory.  Wf == NULL: gl already is d/d unit.
+constexpr int GU_UT = 64;
 __global__ void __launch_bounds__(256) bwd_gunit_kernel(const float *__restrict__ gl, const float *__restrict__ Wf,
                                                         const float *__restrict__ unit, long long B, int U, int C,
                                                         float *__restrict__ gz)
 {
-    extern __shared__ float gls[];   // [8][C]
+    extern __shared__ float gsm[];   // gls [8][C], then wfs [C][64]
+    float *gls = gsm, *wfs = gsm + 8 * C;
     const long long b0 = (long long)blockIdx.x * 8;
+    const int u0 = blockIdx.y * GU_UT;
     const int rows = (int)min(8LL, B - b0);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (Wf != nullptr) {
         for (int i = threadIdx.x; i < rows * C; i += blockDim.x) gls[i] = gl[b0 * C + i];
+        for (int i = threadIdx.x; i < C * GU_UT; i += blockDim.x) {
+            const int c = i / GU_UT, uu = i - c * GU_UT;
+            wfs[i] = u0 + uu < U ? Wf[(size_t)c * U + u0 + uu] : 0.f;
+        }
         __syncthreads();
     }
     if (warp >= rows) return;
     const long long b = b0 + warp;
-    for (int u = lane; u < U; u += 32) {
-        float g;
-        if (Wf != nullptr) {
-            const float *gr = gls + warp * C;
-            float a0 = 0.f, a1 = 0.f;
-            int c = 0;
-            for (; c + 1 < C; c += 2) {
-                a0 = fmaf(gr[c], __ldg(Wf + (size_t)c * U + u), a0);
-                a1 = fmaf(gr[c + 1], __ldg(Wf + (size_t)(c + 1) * U + u), a1);
-            }
-            if (c < C) a0 = fmaf(gr[c], __ldg(Wf + (size_t)c * U + u), a0);
-            g = a0 + a1;
-        } else {
-            g = gl[b * U + u];
+    const int ua = u0 + lane, ub = ua + 32;
+    float ga = 0.f, gb = 0.f;
+    if (Wf != nullptr) {
+        const float *gr = gls + warp * C;
+        float a0 = 0.f, a1 = 0.f, c0 = 0.f, c1 = 0.f;
+        int c = 0;
+        for (; c + 1 < C; c += 2) {
+            const float g0 = gr[c], g1 = gr[c + 1];
+            a0 = fmaf(g0, wfs[c * GU_UT + lane], a0);
+            c0 = fmaf(g0, wfs[c * GU_UT + lane + 32], c0);
+            a1 = fmaf(g1, wfs[(c + 1) * GU_UT + lane], a1);
+            c1 = fmaf(g1, wfs[(c + 1) * GU_UT + lane + 32], c1);
         }
-        gz[b * U + u] = unit[b * U + u] > 0.f ? g : 0.f;
+        if (c < C) {
+            a0 = fmaf(gr[c], wfs[c * GU_UT + lane], a0);
+            c0 = fmaf(gr[c], wfs[c * GU_UT + lane + 32], c0);
+        }
+        ga = a0 + a1;
+        gb = c0 + c1;
+    } else {
+        if (ua < U) ga = gl[b * U + ua];
+        if (ub < U) gb = gl[b * U + ub];
     }
+    if (ua < U) gz[b * U + ua] = unit[b * U + ua] > 0.f ? ga : 0.f;
+    if (ub < U) gz[b * U + ub] = unit[b * U + ub] > 0.f ? gb : 0.f;
 }
 
 // BatchNorm-3 backward per unit: sums over the batch, then gh2 (U,B), dgamma3, dbeta3.  One warp per unit.
@@ -721,7 +744,10 @@ extern "C" int explainn_fc_stack_fwd_train(const float *pooled, long long B, int
     XB_REQUIRE(pdrop >= 0.f && pdrop < 1.f, "fc_stack_fwd_train: dropout probability %f", pdrop);
     const int nchunk = (int)((B + BM - 1) / BM);
     const size_t smem1 = FcSmem::bytes(P) + (size_t)BM * HS * 4;
-    const size_t smem3 = ((size_t)OT_ROWS * U + 2 * (size_t)U) * 4;
+    size_t smem3 = ((size_t)OT_ROWS * U + 2 * (size_t)U) * 4;
+    const size_t smem3_wf = smem3 + (size_t)C * (U + 1) * 4;
+    const int wf_in_smem = smem3_wf <= 200 * 1024;
+    if (wf_in_smem) smem3 = smem3_wf;
     if (smem1 > 220 * 1024 || smem3 > 220 * 1024) {
         xb_set_error("fc_stack_fwd_train: shared memory need (%zu / %zu bytes) exceeds the SM", smem1, smem3);
         return XB_ERR_UNSUPPORTED;
@@ -737,7 +763,7 @@ extern "C" int explainn_fc_stack_fwd_train(const float *pooled, long long B, int
                                                                  W2, b2, mean2, invstd2, pdrop, seed, seed_dev, h2, part3);
     cudaFuncSetAttribute(out_train_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem3);
     out_train_kernel<<<(unsigned)((B + OT_ROWS - 1) / OT_ROWS), 256, smem3, stream>>>(h2, B, U, C, part3, nchunk, bn3_w, bn3_b, bn3_rm, bn3_rv,
-                                                                        momentum, eps, mean3, invstd3, Wf, bf, unit, logits);
+                                                                        momentum, eps, mean3, invstd3, Wf, bf, unit, logits, wf_in_smem);
     return xb_check_launch("fc_stack_fwd_train");
 }
 
@@ -764,13 +790,13 @@ extern "C" int explainn_fc_stack_bwd(const float *glogits, long long B, int U, i
     // gz3 (B,U) lives in the head of the gpool buffer (U*B*P floats >= B*U); it is consumed by bwd_bn3_kernel
     // before bwd_fc1_kernel overwrites gpool
     float *gz3 = gpool;
-    const size_t smem_gu = (size_t)8 * C * 4;
+    const size_t smem_gu = ((size_t)8 * C + (size_t)C * GU_UT) * 4;
     if (smem_gu > 200 * 1024) {
         xb_set_error("fc_stack_bwd: %d classes need %zu bytes of shared memory", C, smem_gu);
         return XB_ERR_LIMIT;
     }
     cudaFuncSetAttribute(bwd_gunit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_gu);
-    bwd_gunit_kernel<<<(unsigned)((B + 7) / 8), 256, smem_gu, stream>>>(glogits, Wf, unit, B, U, C, gz3);
+    bwd_gunit_kernel<<<dim3((unsigned)((B + 7) / 8), (U + GU_UT - 1) / GU_UT), 256, smem_gu, stream>>>(glogits, Wf, unit, B, U, C, gz3);
     bwd_bn3_kernel<<<(U + 7) / 8, 256, 0, stream>>>(gz3, h2, B, U, bn3_w, mean3, invstd3, gh2, dbn3_w, dbn3_b);
     bwd_fc2_kernel<<<dim3(U, nchunk), FC_THREADS, 0, stream>>>(h1, gh2, B, U, bn2_w, bn2_b, mean2, invstd2, W2, pdrop, seed, seed_dev, pb2);
 #define XB_LAUNCH_BWD_FC1(PHV)                                                                                                      \

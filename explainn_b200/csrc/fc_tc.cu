@@ -31,11 +31,20 @@ __device__ __forceinline__ void fill_tile(unsigned char *hi, unsigned char *lo, 
 {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int rl = lane >> 2, kl = lane & 3;
-    for (int cm = warp; cm < (FT_ROWS / 8) * FT_KC; cm += FT_THREADS / 32) {
+    constexpr int NIT = (FT_ROWS / 8) * FT_KC / (FT_THREADS / 32);      // 20 core matrices per warp
+    float xv[NIT];
+    // all loads first (one exposed global latency), then the conversions and stores
+#pragma unroll
+    for (int i = 0; i < NIT; ++i) {
+        const int cm = warp + (FT_THREADS / 32) * i;
         const int rg = cm / FT_KC, kc = cm - rg * FT_KC;
         const int r = rg * 8 + rl, k = k0 + kc * 4 + kl;
-        float x = 0.f;
-        if (r < rows && k < kend) x = src[(size_t)r * row_stride + k];
+        xv[i] = (r < rows && k < kend) ? __ldg(src + (size_t)r * row_stride + k) : 0.f;
+    }
+#pragma unroll
+    for (int i = 0; i < NIT; ++i) {
+        const int cm = warp + (FT_THREADS / 32) * i;
+        const float x = xv[i];
         const float xh = __uint_as_float(__float_as_uint(x) & 0xFFFFE000u);
         const uint32_t off = (uint32_t)cm * 128 + lane * 4;
         *reinterpret_cast<float *>(hi + off) = xh;

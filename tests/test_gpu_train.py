@@ -137,7 +137,7 @@ def _close_per_unit(got, ref, rtol, name, max_outlier_frac=0.02, outlier_rtol=0.
     differ the same way).  So: every unit within `outlier_rtol`, and all but a few within `rtol`."""
     got = np.asarray(got, np.float64).reshape(got.shape[0], -1)
     ref = np.asarray(ref, np.float64).reshape(ref.shape[0], -1)
-    scale = np.maximum(np.abs(ref).max(axis=1), 1e-30)
+    scale = np.maximum(np.abs(ref).max(axis=1), 1e-3 * np.abs(ref).max())
     err = np.abs(got - ref).max(axis=1) / scale
     assert err.max() <= outlier_rtol, "%s: worst unit err %.3e" % (name, err.max())
     allowed = max(1, int(max_outlier_frac * err.size))
@@ -178,7 +178,10 @@ def test_train_step_vs_torch_port(U, L, C, F, B, backend):
             assert float(q.grad.abs().max()) == 0.0
         elif k in NOISE_GRAD:
             assert float(q.grad.abs().max()) < 1e-4 * float(port.linears[1].weight.grad.abs().max())
-        elif k in ("linears.0.weight", "linears.1.weight"):
+        elif k in ("linears.0.weight", "linears.1.weight", "linears.6.weight", "linears.7.weight", "linears.7.bias"):
+            # parameters upstream of a ReLU / max-pool kink, compared row by row (unit or hidden channel): a
+            # pre-activation within rounding of zero may fall on the other side of the kink, which moves that one
+            # row's gradient by ~1/B of its norm
             _close_per_unit(q.grad.cpu().numpy(), p.grad.numpy(), 2e-4, "grad " + k)
         else:
             _close(q.grad.cpu().numpy(), p.grad.numpy(), 2e-4, "grad " + k)
