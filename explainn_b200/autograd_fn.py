@@ -44,7 +44,7 @@ def _check_modes(model):
 class TrainWorkspace:
     """Everything the backward needs, produced by one training forward."""
     __slots__ = ("pk", "B", "U", "P", "C", "F", "M", "mean1", "var1", "Mw", "pooled", "xhat", "idx", "h1", "mean2",
-                 "invstd2", "h2", "mean3", "invstd3", "unit", "logits", "pdrop", "seed", "seed_dev", "nchunk")
+                 "invstd2", "h2", "mean3", "invstd3", "unit", "logits", "pdrop", "seed", "seed_dev", "nchunk", "dropmask")
 
 
 def train_forward(model, x, params=None, seed=None, seed_dev=None):
@@ -93,9 +93,10 @@ def train_forward(model, x, params=None, seed=None, seed_dev=None):
     ws.pdrop = float(drop.p) if drop.training else 0.0
     ws.seed = _next_dropout_seed() if seed is None else seed
     ws.seed_dev = seed_dev
+    ws.dropmask = torch.empty((U, B, 4), dtype=torch.int32, device=dev) if ws.pdrop > 0 else None
     call("explainn_fc_stack_fwd_train", ptr(ws.pooled), B, U, P, C, ptr(W1), ptr(b1), ptr(g2), ptr(be2),
          ptr(bn2.running_mean), ptr(bn2.running_var), ptr(W2), ptr(b2), ptr(g3), ptr(be3), ptr(bn3.running_mean),
-         ptr(bn3.running_var), float(bn2.momentum), float(bn2.eps), ws.pdrop, ws.seed, ptr(seed_dev), ptr(Wf), ptr(bf), ptr(ws.h1),
+         ptr(bn3.running_var), float(bn2.momentum), float(bn2.eps), ws.pdrop, ws.seed, ptr(seed_dev), ptr(ws.dropmask), ptr(Wf), ptr(bf), ptr(ws.h1),
          ptr(part2), ptr(ws.mean2), ptr(ws.invstd2), ptr(ws.h2), ptr(part3), ptr(ws.mean3), ptr(ws.invstd3), ptr(ws.unit),
          ptr(ws.logits), stream())
     bn2.num_batches_tracked.add_(1)
@@ -133,7 +134,7 @@ def train_backward(model, ws, gout, params=None, grads=None, wrt_unit=False):
     gpool = torch.empty((B, U, P), **f32)
     call("explainn_fc_stack_bwd", ptr(gout), B, U, P, C, ptr(ws.pooled), ptr(ws.h1), ptr(ws.h2), ptr(ws.unit), ptr(W1),
          ptr(g2), ptr(be2), ptr(ws.mean2), ptr(ws.invstd2), ptr(W2), ptr(g3), ptr(ws.mean3), ptr(ws.invstd3),
-         None if wrt_unit else ptr(Wf), ws.pdrop, ws.seed, ptr(ws.seed_dev), ptr(gh2), ptr(pb2), ptr(dW1p), ptr(gpool), ptr(dW1), ptr(db1),
+         None if wrt_unit else ptr(Wf), ws.pdrop, ws.seed, ptr(ws.seed_dev), ptr(ws.dropmask), ptr(gh2), ptr(pb2), ptr(dW1p), ptr(gpool), ptr(dW1), ptr(db1),
          ptr(dg2), ptr(dbe2), ptr(dW2), ptr(db2), ptr(dg3), ptr(dbe3), None if wrt_unit else ptr(dWf),
          None if wrt_unit else ptr(dbf), stream())
     nsplit = Fn._cabi.lib.explainn_conv_bwd_nsplit(U)

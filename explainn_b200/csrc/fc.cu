@@ -23,8 +23,8 @@ int xb_fc_stack_fwd_eval_tc(const float *pooled, long long B, int U, int P, cons
 bool xb_fc_tc_enabled();
 int xb_bwd_fc1_tc(const float *h1, const float *gh2, const float *pooled, long long B, int U, int P, const float *g2, const float *be2,
                   const float *mean2, const float *invstd2, const float *W1, const float *W2, float pdrop, unsigned long long seed,
-                  const unsigned long long *seed_dev, const float *pb2, float *gpool, float *dW1p, float *dW2, float *db1, float *db2,
-                  float *dg2, float *dbe2, cudaStream_t stream);
+                  const unsigned long long *seed_dev, const uint32_t *dropmask, const float *pb2, float *gpool, float *dW1p, float *dW2,
+                  float *db1, float *db2, float *dg2, float *dbe2, cudaStream_t stream);
 
 namespace {
 
@@ -240,7 +240,7 @@ __global__ void __launch_bounds__(FC_THREADS) fc2_train_kernel(
     const float *__restrict__ g2, const float *__restrict__ be2, float *__restrict__ rm2, float *__restrict__ rv2,
     float momentum, float eps, const float *__restrict__ W2, const float *__restrict__ b2, float *__restrict__ mean2,
     float *__restrict__ invstd2, float pdrop, unsigned long long seed0, const unsigned long long *__restrict__ seed_dev,
-    float *__restrict__ h2, float *__restrict__ part3)
+    uint32_t *__restrict__ dropmask, float *__restrict__ h2, float *__restrict__ part3)
 {
     __shared__ float sc[128], sh[128], w2s[128];
     __shared__ float red[8][2];
@@ -287,15 +287,25 @@ __global__ void __launch_bounds__(FC_THREADS) fc2_train_kernel(
         const size_t rowi = (size_t)u * B + b0 + r;
         const float *hr = h1 + rowi * H;
         float dot = 0.f;
+        uint32_t mword = 0;
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             const int j = lane + 32 * i;
+            bool keep = false;
             if (j < H) {
                 float v = fmaxf(fmaf(hr[j], sc[j], sh[j]), 0.f);
-                if (pdrop > 0.f) v *= drop_scale(seed, rowi * H + j, thresh, keep_scale);
+                if (pdrop > 0.f) {
+                    const float ks = drop_scale(seed, rowi * H + j, thresh, keep_scale);
+                    keep = ks != 0.f;
+                    v *= ks;
+                }
                 dot = fmaf(v, w2s[j], dot);
             }
+            // the keep bits are saved for the backward: word i of the row holds channels 32i .. 32i+31
+            const uint32_t w = __ballot_sync(0xffffffffu, keep);
+            if (lane == i) mword = w;
         }
+        if (pdrop > 0.f && dropmask && lane < 4) dropmask[rowi * 4 + lane] = mword;
         dot = warp_sum(dot);
         const float o = dot + b2[u];
         if (lane == 0) {
@@ -512,7 +522,8 @@ __global__ void __launch_bounds__(FC_THREADS) bwd_fc2_kernel(const float *__rest
                                                              const float *__restrict__ be2, const float *__restrict__ mean2,
                                                              const float *__restrict__ invstd2, const float *__restrict__ W2,
                                                              float pdrop, unsigned long long seed0,
-                                                             const unsigned long long *__restrict__ seed_dev, float *__restrict__ pb2)
+                                                             const unsigned long long *__restrict__ seed_dev,
+                                                             const uint32_t *__restrict__ dropmask, float *__restrict__ pb2)
 {
     __shared__ float mu[128], inv[128], ga[128], be[128], w2s[128];
     __shared__ float red[8][3][128];
@@ -535,13 +546,17 @@ __global__ void __launch_bounds__(FC_THREADS) bwd_fc2_kernel(const float *__rest
         const size_t rowi = (size_t)u * B + b0 + r;
         const float *hr = h1 + rowi * H;
         const float g = gh2[rowi];
+        const uint32_t myw = (pdrop > 0.f && dropmask && lane < 4) ? dropmask[rowi * 4 + lane] : 0u;
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             const int j = lane + 32 * i;
+            const uint32_t wi = __shfl_sync(0xffffffffu, myw, i);
             if (j < H) {
                 const float xh = (hr[j] - mu[j]) * inv[j];
                 const float zb = fmaf(ga[j], xh, be[j]);
-                const float ks = pdrop > 0.f ? drop_scale(seed, rowi * H + j, thresh, keep_scale) : 1.0f;
+                const float ks = pdrop > 0.f ? (dropmask ? (((wi >> lane) & 1u) ? keep_scale : 0.f)
+                                                         : drop_scale(seed, rowi * H + j, thresh, keep_scale))
+                                             : 1.0f;
                 const float a2 = fmaxf(zb, 0.f) * ks;
                 dW2[i] = fmaf(g, a2, dW2[i]);
                 const float gz2 = zb > 0.f ? g * w2s[j] * ks : 0.f;
@@ -733,7 +748,7 @@ extern "C" int explainn_fc_stack_fwd_train(const float *pooled, long long B, int
                                            const float *bn2_w, const float *bn2_b, float *bn2_rm, float *bn2_rv, const float *W2,
                                            const float *b2, const float *bn3_w, const float *bn3_b, float *bn3_rm, float *bn3_rv,
                                            float momentum, float eps, float pdrop, unsigned long long seed,
-                                           const unsigned long long *seed_dev, const float *Wf, const float *bf, float *h1, float *part2, float *mean2, float *invstd2, float *h2,
+                                           const unsigned long long *seed_dev, uint32_t *dropmask, const float *Wf, const float *bf, float *h1, float *part2, float *mean2, float *invstd2, float *h2,
                                            float *part3, float *mean3, float *invstd3, float *unit, float *logits,
                                            cudaStream_t stream)
 {
@@ -760,7 +775,7 @@ extern "C" int explainn_fc_stack_fwd_train(const float *pooled, long long B, int
         fc1_train_kernel<<<dim3(U, nchunk), FC_THREADS, smem1, stream>>>(pooled, B, U, P, W1, b1, h1, part2);
     }
     fc2_train_kernel<<<dim3(U, nchunk), FC_THREADS, 0, stream>>>(h1, B, U, part2, nchunk, bn2_w, bn2_b, bn2_rm, bn2_rv, momentum, eps,
-                                                                 W2, b2, mean2, invstd2, pdrop, seed, seed_dev, h2, part3);
+                                                                 W2, b2, mean2, invstd2, pdrop, seed, seed_dev, dropmask, h2, part3);
     cudaFuncSetAttribute(out_train_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem3);
     out_train_kernel<<<(unsigned)((B + OT_ROWS - 1) / OT_ROWS), 256, smem3, stream>>>(h2, B, U, C, part3, nchunk, bn3_w, bn3_b, bn3_rm, bn3_rv,
                                                                         momentum, eps, mean3, invstd3, Wf, bf, unit, logits, wf_in_smem);
@@ -771,7 +786,7 @@ extern "C" int explainn_fc_stack_bwd(const float *glogits, long long B, int U, i
                                      const float *h2, const float *unit, const float *W1, const float *bn2_w, const float *bn2_b,
                                      const float *mean2, const float *invstd2, const float *W2, const float *bn3_w,
                                      const float *mean3, const float *invstd3, const float *Wf, float pdrop,
-                                     unsigned long long seed, const unsigned long long *seed_dev, float *gh2, float *pb2, float *dW1_partials, float *gpool,
+                                     unsigned long long seed, const unsigned long long *seed_dev, const uint32_t *dropmask, float *gh2, float *pb2, float *dW1_partials, float *gpool,
                                      float *dW1, float *db1, float *dbn2_w, float *dbn2_b, float *dW2, float *db2, float *dbn3_w,
                                      float *dbn3_b, float *dWf, float *dbf, cudaStream_t stream)
 {
@@ -798,7 +813,7 @@ extern "C" int explainn_fc_stack_bwd(const float *glogits, long long B, int U, i
     cudaFuncSetAttribute(bwd_gunit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_gu);
     bwd_gunit_kernel<<<dim3((unsigned)((B + 7) / 8), (U + GU_UT - 1) / GU_UT), 256, smem_gu, stream>>>(glogits, Wf, unit, B, U, C, gz3);
     bwd_bn3_kernel<<<(U + 7) / 8, 256, 0, stream>>>(gz3, h2, B, U, bn3_w, mean3, invstd3, gh2, dbn3_w, dbn3_b);
-    bwd_fc2_kernel<<<dim3(U, nchunk), FC_THREADS, 0, stream>>>(h1, gh2, B, U, bn2_w, bn2_b, mean2, invstd2, W2, pdrop, seed, seed_dev, pb2);
+    bwd_fc2_kernel<<<dim3(U, nchunk), FC_THREADS, 0, stream>>>(h1, gh2, B, U, bn2_w, bn2_b, mean2, invstd2, W2, pdrop, seed, seed_dev, dropmask, pb2);
 #define XB_LAUNCH_BWD_FC1(PHV)                                                                                                      \
     do {                                                                                                                            \
         const size_t sm = bwd_fc1_smem<PHV>();                                                                                      \
@@ -809,7 +824,7 @@ extern "C" int explainn_fc_stack_bwd(const float *glogits, long long B, int U, i
     } while (0)
     int rc_tc = XB_ERR_UNSUPPORTED;
     if (xb_fc_tc_enabled())
-        rc_tc = xb_bwd_fc1_tc(h1, gh2, pooled, B, U, P, bn2_w, bn2_b, mean2, invstd2, W1, W2, pdrop, seed, seed_dev, pb2, gpool, dW1_partials,
+        rc_tc = xb_bwd_fc1_tc(h1, gh2, pooled, B, U, P, bn2_w, bn2_b, mean2, invstd2, W1, W2, pdrop, seed, seed_dev, dropmask, pb2, gpool, dW1_partials,
                               dW2, db1, db2, dbn2_w, dbn2_b, stream);
     if (rc_tc == XB_OK) {
     } else if (rc_tc != XB_ERR_UNSUPPORTED) return rc_tc;

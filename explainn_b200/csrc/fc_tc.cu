@@ -251,6 +251,7 @@ struct FcBwdArgs {
     float pdrop;
     unsigned long long seed0;
     const unsigned long long *seed_dev;
+    const uint32_t *dropmask;   // (U,B,4) keep bits written by the forward, or NULL (hash is recomputed)
     const float *pb2;
     float *gpool, *dW1p, *dW2, *db1, *db2, *dg2, *dbe2;
 };
@@ -269,7 +270,9 @@ __global__ void __launch_bounds__(FT_THREADS, 1) bwd_fc1_tc_kernel(const FcBwdAr
     extern __shared__ __align__(128) unsigned char smem[];
     __shared__ __align__(8) uint64_t bar;
     __shared__ uint32_t tmem_base_s;
-    __shared__ float mu[128], inv[128], ga[128], be[128], w2s[128], m1s[128], m2s[128];
+    // per hidden channel: zb = h*c1 + c0 ;  G = h*cB + cC + (zb > 0 && kept ? gh2[row] * cA : 0)
+    __shared__ float c1s[128], c0s[128], cAs[128], cBs[128], cCs[128];
+    __shared__ __align__(16) uint32_t msk[FT_ROWS][4];
 
     unsigned char *sR = smem;                                   // phase 1: G hi | G lo ; phase 2: Gt hi | Gt lo
     unsigned char *sAh = sR + 2 * BT_GT_BYTES, *sAl = sAh + BT_A_BYTES;
@@ -310,7 +313,13 @@ __global__ void __launch_bounds__(FT_THREADS, 1) bwd_fc1_tc_kernel(const FcBwdAr
             mbar_arrive_expect_tx(&bar_h, (uint32_t)rows * H * 4);
             tma_bulk_g2s(sH, a.h1 + ((size_t)u * a.B + b0) * H, (uint32_t)rows * H * 4, &bar_h);
         }
-        if (threadIdx.x < FT_ROWS) gh2s[threadIdx.x] = threadIdx.x < rows ? a.gh2[(size_t)u * a.B + b0 + threadIdx.x] : 0.f;
+        if (threadIdx.x < FT_ROWS) {
+            const int r = threadIdx.x;
+            gh2s[r] = r < rows ? a.gh2[(size_t)u * a.B + b0 + r] : 0.f;
+            uint4 mw = make_uint4(~0u, ~0u, ~0u, ~0u);
+            if (a.pdrop > 0.f && a.dropmask && r < rows) mw = *reinterpret_cast<const uint4 *>(a.dropmask + ((size_t)u * a.B + b0 + r) * 4);
+            *reinterpret_cast<uint4 *>(&msk[r][0]) = mw;
+        }
         if (u != cur_u) {
             if (threadIdx.x < 128) {
                 const int j = threadIdx.x, ch = u * H + j;
@@ -329,9 +338,15 @@ __global__ void __launch_bounds__(FT_THREADS, 1) bwd_fc1_tc_kernel(const FcBwdAr
                         if (a.db2 && j == 0) a.db2[u] = 0.f;
                     }
                 }
-                mu[j] = v ? a.mean2[ch] : 0.f; inv[j] = v ? a.invstd2[ch] : 0.f; ga[j] = v ? a.g2[ch] : 0.f;
-                be[j] = v ? a.be2[ch] : 0.f; w2s[j] = v ? a.W2[ch] : 0.f;
-                m1s[j] = s1 / (float)a.B; m2s[j] = s2 / (float)a.B;
+                const float mu = v ? a.mean2[ch] : 0.f, inv = v ? a.invstd2[ch] : 0.f, gam = v ? a.g2[ch] : 0.f;
+                const float bet = v ? a.be2[ch] : 0.f, w2 = v ? a.W2[ch] : 0.f;
+                const float m1 = s1 / (float)a.B, m2 = s2 / (float)a.B;
+                const float c1 = gam * inv;
+                c1s[j] = c1;
+                c0s[j] = bet - mu * c1;
+                cAs[j] = w2 * c1 * keep_scale;
+                cBs[j] = -c1 * m2 * inv;
+                cCs[j] = c1 * (m2 * inv * mu - m1);
             }
             // W1[u] transposed: rows p, K = j contiguous (B operand of D1); one warp store = one core matrix.
             // All loads are issued before the first store so that only one global latency is exposed.
@@ -366,15 +381,12 @@ __global__ void __launch_bounds__(FT_THREADS, 1) bwd_fc1_tc_kernel(const FcBwdAr
             const int r = rg * 8 + (lane >> 2), j = kc * 4 + (lane & 3);
             float v = 0.f;
             if (r < rows && j < H) {
-                const size_t rowi = (size_t)u * a.B + b0 + r;
-                const float xh = (sH[r * H + j] - mu[j]) * inv[j];
-                const float zb = fmaf(ga[j], xh, be[j]);
-                float gz2 = 0.f;
-                if (zb > 0.f) {
-                    const float ks = a.pdrop > 0.f ? drop_scale(seed, rowi * H + j, thresh, keep_scale) : 1.0f;
-                    gz2 = gh2s[r] * w2s[j] * ks;
-                }
-                v = ga[j] * inv[j] * (gz2 - m1s[j] - xh * m2s[j]);
+                const float h = sH[r * H + j];
+                const float zb = fmaf(h, c1s[j], c0s[j]);
+                bool kept = (msk[r][j >> 5] >> (j & 31)) & 1u;
+                if (a.pdrop > 0.f && !a.dropmask) kept = drop_scale(seed, ((size_t)u * a.B + b0 + r) * H + j, thresh, keep_scale) != 0.f;
+                v = fmaf(h, cBs[j], cCs[j]);
+                if (zb > 0.f && kept) v = fmaf(gh2s[r], cAs[j], v);
             }
             gv[i] = v;
             st_split(sR, sR + BT_G_BYTES, (uint32_t)cm * 128 + lane * 4, v);      // G, j-contiguous
@@ -536,13 +548,13 @@ bool xb_fc_tc_enabled()
 // returns XB_ERR_UNSUPPORTED (without setting an error) when the shape does not fit the tensor-core tiles
 int xb_bwd_fc1_tc(const float *h1, const float *gh2, const float *pooled, long long B, int U, int P, const float *g2, const float *be2,
                   const float *mean2, const float *invstd2, const float *W1, const float *W2, float pdrop, unsigned long long seed,
-                  const unsigned long long *seed_dev, const float *pb2, float *gpool, float *dW1p, float *dW2, float *db1, float *db2,
-                  float *dg2, float *dbe2, cudaStream_t stream)
+                  const unsigned long long *seed_dev, const uint32_t *dropmask, const float *pb2, float *gpool, float *dW1p, float *dW2,
+                  float *db1, float *db2, float *dg2, float *dbe2, cudaStream_t stream)
 {
     if (P > BT_P) return XB_ERR_UNSUPPORTED;
     FcBwdArgs a{};
     a.h1 = h1; a.gh2 = gh2; a.pooled = pooled; a.B = B; a.U = U; a.P = P; a.nchunk = (int)((B + FT_ROWS - 1) / FT_ROWS);
-    a.g2 = g2; a.be2 = be2; a.mean2 = mean2; a.invstd2 = invstd2; a.W1 = W1; a.W2 = W2; a.pdrop = pdrop; a.seed0 = seed; a.seed_dev = seed_dev;
+    a.g2 = g2; a.be2 = be2; a.mean2 = mean2; a.invstd2 = invstd2; a.W1 = W1; a.W2 = W2; a.pdrop = pdrop; a.seed0 = seed; a.seed_dev = seed_dev; a.dropmask = dropmask;
     a.pb2 = pb2; a.gpool = gpool; a.dW1p = dW1p; a.dW2 = dW2; a.db1 = db1; a.db2 = db2; a.dg2 = dg2; a.dbe2 = dbe2;
     const size_t smem = 2 * (size_t)(BT_GT_BYTES + BT_A_BYTES + BT_W_BYTES);
     const long long total = (long long)U * a.nchunk;

@@ -168,7 +168,8 @@ int explainn_bn1_batch_stats(const int *M, const float *w, const float *bias, in
  * Replaces linears[4..13] + final (networks.py:103-116,147) with BatchNorm batch statistics (running stats
  * updated in place when the rm/rv pointers are non-NULL) and inverted dropout (p = pdrop, mask derived from
  * `seed` (+ the device counter *seed_dev when non-NULL, so a captured CUDA graph draws a new mask on every
- * replay) and the element index, regenerated in the backward).  Saved for the backward: h1 (U,B,100),
+ * replay) and the element index; the keep bits are also written to dropmask (U,B,4) u32 (may be NULL, then the
+ * backward regenerates them from the seed).  Saved for the backward: h1 (U,B,100),
  * mean2/invstd2 (100U), h2 (U,B), mean3/invstd3 (U), unit (B,U).  part2: (U, nchunk, 2, 100) and part3:
  * (U, nchunk, 2) floats of scratch, nchunk = explainn_fc_nchunk(B).  logits: (B,C). */
 int explainn_fc_nchunk(long long B);
@@ -176,7 +177,7 @@ int explainn_fc_stack_fwd_train(const float *pooled, long long B, int U, int P, 
                                 const float *bn2_w, const float *bn2_b, float *bn2_rm, float *bn2_rv, const float *W2,
                                 const float *b2, const float *bn3_w, const float *bn3_b, float *bn3_rm, float *bn3_rv,
                                 float momentum, float eps, float pdrop, unsigned long long seed,
-                                const unsigned long long *seed_dev, const float *Wf, const float *bf, float *h1, float *part2, float *mean2, float *invstd2, float *h2,
+                                const unsigned long long *seed_dev, uint32_t *dropmask, const float *Wf, const float *bf, float *h1, float *part2, float *mean2, float *invstd2, float *h2,
                                 float *part3, float *mean3, float *invstd3, float *unit, float *logits,
                                 cudaStream_t stream);
 
@@ -189,7 +190,7 @@ int explainn_fc_stack_bwd(const float *glogits, long long B, int U, int P, int C
                           const float *h2, const float *unit, const float *W1, const float *bn2_w, const float *bn2_b,
                           const float *mean2, const float *invstd2, const float *W2, const float *bn3_w,
                           const float *mean3, const float *invstd3, const float *Wf, float pdrop,
-                          unsigned long long seed, const unsigned long long *seed_dev, float *gh2, float *pb2, float *dW1_partials, float *gpool,
+                          unsigned long long seed, const unsigned long long *seed_dev, const uint32_t *dropmask, float *gh2, float *pb2, float *dW1_partials, float *gpool,
                           float *dW1, float *db1, float *dbn2_w, float *dbn2_b, float *dW2, float *db2, float *dbn3_w,
                           float *dbn3_b, float *dWf, float *dbf, cudaStream_t stream);
 
