@@ -268,7 +268,7 @@ struct MaxSink {
 //     hit  <=>  half(exp(z)) > thr  <=>  z > zhi, or z in (zlo, zhi] and the exact test holds;
 //     zlo/zhi bracket the cut-over by 64 ulps on each side (prep.cu: interp_thresholds).
 struct CountSink {
-    struct Params { const float *zlo; const float *zhi; const float *thr; unsigned long long *counts; unsigned long long *hits; };
+    struct Params { const float *zlo; const float *zhi; const float *thr; unsigned long long *counts; unsigned long long *hits; unsigned char *seq_hit; };
     static __host__ __device__ int smem_bytes(int F) { return (4 * F + 1) * XB_UT * 4; }
     Params p;
     unsigned int *cnt;   // [4*F + 1][32]; last row = number of hit positions
@@ -292,8 +292,11 @@ struct CountSink {
         for (int i = threadIdx.x; i < (4 * a.F + 1) * XB_UT; i += blockDim.x) cnt[i] = 0;
         __syncthreads();
     }
+    long long seq_b;
+    int seq_u0;
+    bool seq_any;
     __device__ void set_seq(const uint32_t *cw_, const uint32_t *mw_) { cw = cw_; mw = mw_; }
-    __device__ void begin_seq(long long, int, const ConvArgs &) {}
+    __device__ void begin_seq(long long b, int u0, const ConvArgs &) { seq_b = b; seq_u0 = u0; seq_any = false; }
     __device__ __forceinline__ void window(int win, int t, const float *acc, const ConvArgs &a)
     {
         if (win >= a.nwin) return;
@@ -305,6 +308,7 @@ struct CountSink {
             if (!h && z > zlo) h = fp16_round(det_expf(z)) > thr;
             if (h && t + j < a.S) hitmask |= 1u << j;
         }
+        seq_any |= hitmask != 0;
         if (__any_sync(0xffffffffu, hitmask != 0)) record(t, hitmask, a);
     }
     __device__ __noinline__ void record(int t, unsigned hitmask, const ConvArgs &a)
@@ -321,7 +325,11 @@ struct CountSink {
             }
         }
     }
-    __device__ void end_seq(const ConvArgs &) {}
+    __device__ void end_seq(const ConvArgs &a)
+    {
+        // "does sequence b have any position above threshold for unit u" -- the set interpretation.py:311-317 builds
+        if (p.seq_hit && seq_u0 + lane < a.U) p.seq_hit[seq_b * a.U + seq_u0 + lane] = seq_any ? 1 : 0;
+    }
     __device__ void end_tile(int u0, const ConvArgs &a)
     {
         __syncthreads();
@@ -701,7 +709,7 @@ extern "C" int explainn_interp_unit_max(const uint32_t *codes, const uint32_t *n
 extern "C" int explainn_interp_pwm_count(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F,
                                          const float *tables, const float *wq_t, const float *shift, const float *zlo,
                                          const float *zhi, const float *thr, unsigned long long *counts,
-                                         unsigned long long *hits, cudaStream_t stream)
+                                         unsigned long long *hits, unsigned char *seq_hit, cudaStream_t stream)
 {
     ConvArgs a; Geometry g;
     int rc = fill_args(&a, &g, codes, nmask, B, L, U, F, tables, wq_t, shift);
@@ -709,7 +717,7 @@ extern "C" int explainn_interp_pwm_count(const uint32_t *codes, const uint32_t *
     XB_REQUIRE(zlo && zhi && thr && counts && hits, "interp_pwm_count: null pointer");
     if (B == 0) return XB_OK;
     a.nwin = g.nwin_all;
-    CountSink::Params sp{zlo, zhi, thr, counts, hits};
+    CountSink::Params sp{zlo, zhi, thr, counts, hits, seq_hit};
     return dispatch_scan<CountSink, CountSink>(g.G, a, sp, F, stream);
 }
 

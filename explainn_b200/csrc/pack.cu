@@ -65,3 +65,47 @@ extern "C" int explainn_pack_onehot(const void *x, int x_dtype, long long B, int
     }
     return xb_check_launch("pack_onehot");
 }
+
+
+// Reverse complement of packed sequences: position i of the output is the complement (A<->T, C<->G, i.e. 3 - code)
+// of position L-1-i of the input; N stays N.  This is `s[::-1, ::-1]` on the one-hot matrix
+// (scripts/fasta2predictions.py:160).  One thread per output code word.
+__global__ void __launch_bounds__(256) revcomp_packed_kernel(const uint32_t *__restrict__ codes, const uint32_t *__restrict__ nmask,
+                                                             long long B, int L, uint32_t *__restrict__ codes_rc,
+                                                             uint32_t *__restrict__ nmask_rc)
+{
+    const int wc = xb_words_codes(L), wm = xb_words_mask(L);
+    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= B * wc) return;
+    const long long b = t / wc;
+    const int w = (int)(t - b * wc);
+    const uint32_t *cb = codes + b * wc, *mb = nmask + b * wm;
+    uint32_t cw = 0, mbits = 0;
+#pragma unroll 4
+    for (int k = 0; k < 16; ++k) {
+        const int i = w * 16 + k;
+        if (i >= L) break;
+        const int src = L - 1 - i;
+        const uint32_t isn = (mb[src >> 5] >> (src & 31)) & 1u;
+        const uint32_t c = (cb[src >> 4] >> (2 * (src & 15))) & 3u;
+        if (isn) mbits |= 1u << k;
+        else cw |= (3u - c) << (2 * k);
+    }
+    codes_rc[b * wc + w] = cw;
+    // two code words make one mask word
+    // mask halves are written with a 16-bit store each (word w covers bits 16*(w&1) .. +15 of mask word w/2)
+    reinterpret_cast<unsigned short *>(nmask_rc + b * wm)[w] = (unsigned short)mbits;
+}
+
+extern "C" int explainn_revcomp_packed(const uint32_t *codes, const uint32_t *nmask, long long B, int L, uint32_t *codes_rc,
+                                       uint32_t *nmask_rc, cudaStream_t stream)
+{
+    XB_REQUIRE(codes && nmask && codes_rc && nmask_rc && B >= 0 && L > 0, "revcomp_packed: bad argument");
+    if (B == 0) return XB_OK;
+    // odd number of code words: the upper half of the last mask word is never written by the kernel
+    cudaError_t e = cudaMemsetAsync(nmask_rc, 0, (size_t)B * xb_words_mask(L) * 4, stream);
+    if (e != cudaSuccess) { xb_set_error("cudaMemsetAsync: %s", cudaGetErrorString(e)); return XB_ERR_CUDA; }
+    const long long n = B * xb_words_codes(L);
+    revcomp_packed_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(codes, nmask, B, L, codes_rc, nmask_rc);
+    return xb_check_launch("revcomp_packed");
+}

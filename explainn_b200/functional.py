@@ -116,7 +116,16 @@ def interp_thresholds(zmax):
     return thr, zlo, zhi, amax
 
 
-def interp_pwm_count(pk, prep, thr, zlo, zhi, counts=None, hits=None):
+def revcomp_packed(pk):
+    """Reverse complement of packed sequences (the other strand)."""
+    codes = torch.empty_like(pk.codes)
+    nmask = torch.empty_like(pk.nmask)
+    if pk.B:
+        call("explainn_revcomp_packed", ptr(pk.codes), ptr(pk.nmask), pk.B, pk.L, ptr(codes), ptr(nmask), stream())
+    return Packed(codes, nmask, pk.B, pk.L, pk.invalid)
+
+
+def interp_pwm_count(pk, prep, thr, zlo, zhi, counts=None, hits=None, seq_hit=None):
     dev = pk.codes.device
     if counts is None:
         counts = torch.zeros((prep.U, 4, prep.F), dtype=torch.int64, device=dev)
@@ -124,7 +133,7 @@ def interp_pwm_count(pk, prep, thr, zlo, zhi, counts=None, hits=None):
     if pk.B == 0:
         return counts, hits
     call("explainn_interp_pwm_count", ptr(pk.codes), ptr(pk.nmask), pk.B, pk.L, prep.U, prep.F, ptr(prep.tables),
-         ptr(prep.wq_t), ptr(prep.shift), ptr(zlo), ptr(zhi), ptr(thr), ptr(counts), ptr(hits), stream())
+         ptr(prep.wq_t), ptr(prep.shift), ptr(zlo), ptr(zhi), ptr(thr), ptr(counts), ptr(hits), ptr(seq_hit), stream())
     return counts, hits
 
 

@@ -86,6 +86,8 @@ class PwmAccumulator:
         self.zmax = None
         self.thr = self.zlo = self.zhi = self.amax = None
         self.counts = self.hits = None
+        self.keep_seq_hits = False      # set True to also collect, per batch, which sequences pass each unit's threshold
+        self.seq_hits = []
 
     def scan_max(self, x):
         pk = self.model._pack(x)
@@ -98,7 +100,12 @@ class PwmAccumulator:
 
     def scan_count(self, x):
         pk = self.model._pack(x)
-        self.counts, self.hits = Fn.interp_pwm_count(pk, self.prep, self.thr, self.zlo, self.zhi, self.counts, self.hits)
+        seq_hit = None
+        if self.keep_seq_hits:
+            seq_hit = torch.zeros((pk.B, self.prep.U), dtype=torch.uint8, device=pk.codes.device)
+            self.seq_hits.append(seq_hit)
+        self.counts, self.hits = Fn.interp_pwm_count(pk, self.prep, self.thr, self.zlo, self.zhi, self.counts, self.hits,
+                                                     seq_hit)
 
     def result(self):
         self.model.check_inputs()
@@ -153,3 +160,65 @@ def pwm_to_meme(pwm, output_file_path, names=None, verbose=True):
                     meme_file.write("\t".join(str(pwm[i][c, j]) for c in range(4)) + "\n")
     if verbose:
         print('Saved PWM File as : {}'.format(output_file_path))
+
+
+# ------------------------------------------------------------------------------------------ unit importance
+def get_specific_unit_importance(activations, model, unit_outputs, filt, target_labels):
+    """Importance (unit output x class weight) of unit `filt` over the sequences that activate it above its
+    threshold -- drop-in for interpretation.py:303-340 (host arrays in, pandas.Series out)."""
+    import pandas as pd
+    thr = 0.5 * np.amax(activations, axis=(0, 2))
+    hit = (activations[:, filt, :] > thr[filt]).any(axis=1)
+    weights = model.final.weight.detach().cpu().numpy()
+    res = {}
+    for cl in range(len(target_labels)):
+        res[target_labels[cl]] = np.multiply(unit_outputs, weights[cl])[:, filt][hit]
+    return pd.Series(res)
+
+
+def unit_importance_fused(data_loader, model, device, target_labels=None):
+    """Unit importances for ALL units without the activation tensor.
+
+    The per-unit sequence sets ("has a position above 0.5 x max", interpretation.py:311-317) come out of the PWM
+    count pass as a by-product; unit outputs come from the fused forward.  Returns
+      importance: dict unit -> pandas.Series(label -> 1-D array over the sequences that activate the unit)
+                  (the object get_specific_unit_importance returns, for every unit)
+      median:     (U, C) array of medians (get_median_unit_importance, interpretation.py:261-300, without its
+                  hard-coded 100 units / 50 classes); NaN where no sequence activates the unit
+    """
+    import pandas as pd
+
+    def batches():
+        if isinstance(data_loader, torch.Tensor):
+            for i in range(0, data_loader.shape[0], 8192):
+                yield data_loader[i:i + 8192]
+        else:
+            for item in data_loader:
+                yield item[0] if isinstance(item, (tuple, list)) else item
+
+    acc = PwmAccumulator(model)
+    acc.keep_seq_hits = True
+    units = []
+    with torch.no_grad():
+        for seq in batches():
+            acc.scan_max(seq.to(device, non_blocking=True))
+        acc.finish_max()
+        for seq in batches():
+            x = seq.to(device, non_blocking=True)
+            acc.scan_count(x)
+            units.append(model.linears(x))
+    model.check_inputs()
+    hit = torch.cat(acc.seq_hits, 0).bool().cpu().numpy()          # (N,U)
+    unit_outputs = torch.cat(units, 0).cpu().numpy()               # (N,U)
+    weights = model.final.weight.detach().cpu().numpy()            # (C,U)
+    C, U = weights.shape
+    if target_labels is None:
+        target_labels = list(range(C))
+    importance, median = {}, np.full((U, C), np.nan)
+    for u in range(U):
+        rows = hit[:, u]
+        vals = unit_outputs[rows, u][:, None] * weights[None, :, u]      # (n_hit, C)
+        importance[u] = pd.Series({target_labels[c]: vals[:, c] for c in range(C)})
+        if vals.shape[0]:
+            median[u] = np.median(vals, axis=0)
+    return importance, median

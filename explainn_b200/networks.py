@@ -176,9 +176,11 @@ class ExplaiNN(nn.Module):
 
     def _pooled(self, x):
         """max-pooled activations (B,U,P)."""
+        return self._pooled_packed(self._pack(x))
+
+    def _pooled_packed(self, pk):
         if self._bn_uses_batch_stats():
             raise RuntimeError("model.linears[:4] on the fused path needs eval() mode")
-        pk = self._pack(x)
         if self.conv_backend == "tc":
             conv, bn = self.linears[0], self.linears[1]
             tcp = Fn.conv_tc_prepare(conv.weight.detach(), conv.bias.detach(), bn.weight.detach(), bn.bias.detach(),
@@ -187,8 +189,16 @@ class ExplaiNN(nn.Module):
         return Fn.conv_pool_fwd(pk, self._conv_prep_eval())
 
     def _unit_outputs_eval(self, x):
+        return self._unit_outputs_eval_packed(self._pack(x))
+
+    def forward_packed(self, pk):
+        """Eval-mode logits from already packed sequences (functional.Packed), e.g. the reverse strand."""
+        unit = self._unit_outputs_eval_packed(pk)
+        return Fn.linear_fwd(unit, self.final.weight.detach(), self.final.bias.detach())
+
+    def _unit_outputs_eval_packed(self, pk):
         L = self.linears
-        pooled = self._pooled(x)
+        pooled = self._pooled_packed(pk)
         bn2, bn3 = L[7], L[11]
         return Fn.fc_stack_fwd_eval(
             pooled, L[6].weight.detach(), L[6].bias.detach(),

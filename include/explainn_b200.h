@@ -55,6 +55,11 @@ int explainn_num_sms(void);
 int explainn_pack_onehot(const void *x, int x_dtype, long long B, int L, long long batch_stride,
                          uint32_t *codes, uint32_t *nmask, int *n_invalid, cudaStream_t stream);
 
+/* Reverse complement on the packed form (A<->T, C<->G, order reversed, N stays N): the `s[::-1, ::-1]` of the
+ * strand-aware prediction loop (scripts/fasta2predictions.py:160, scripts/tsv2predictions.py). */
+int explainn_revcomp_packed(const uint32_t *codes, const uint32_t *nmask, long long B, int L, uint32_t *codes_rc,
+                            uint32_t *nmask_rc, cudaStream_t stream);
+
 /* ---- weight preparation -------------------------------------------------------------------------------
  * Folds BatchNorm1d (explainn/models/networks.py:100; eval: running stats, train: batch stats) into the
  * grouped Conv1d filter (networks.py:98-99) and builds the k-mer lookup tables the scan kernels read.
@@ -126,11 +131,13 @@ int explainn_interp_thresholds(const float *zmax, int U, float *thr, float *zlo,
                                cudaStream_t stream);
 /* Pass B: counts[u,c,k] += #positions with half(act) > thr[u] whose window has base c at offset k
  * (interpretation.py:203-214); hits[u] += number of such positions.  counts (U,4,F) u64, hits (U) u64,
- * both accumulated into (zero them first). */
+ * both accumulated into (zero them first).  seq_hit (B,U) u8, optional (NULL to skip): 1 if the sequence has any
+ * position above threshold for the unit -- the per-unit sequence sets of get_specific_unit_importance
+ * (interpretation.py:311-317). */
 int explainn_interp_pwm_count(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F,
                               const float *tables, const float *wq_t, const float *shift, const float *zlo,
                               const float *zhi, const float *thr, unsigned long long *counts,
-                              unsigned long long *hits, cudaStream_t stream);
+                              unsigned long long *hits, unsigned char *seq_hit, cudaStream_t stream);
 
 /* ---- per-unit FC stack, eval mode -----------------------------------------------------------------------
  * Replaces linears[4..13] with BatchNorm in eval mode (explainn/models/networks.py:103-116): grouped 1x1
