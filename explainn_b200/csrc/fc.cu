@@ -171,16 +171,27 @@ __global__ void __launch_bounds__(256) linear_fwd_kernel(const float *__restrict
     }
     __syncthreads();
     const int r = threadIdx.x & 31;
-    for (int c = threadIdx.x >> 5; c < C; c += 8) {
-        const float *w = W + (size_t)c * U;
-        float a0 = 0.f, a1 = 0.f;
-        int k = 0;
-        for (; k + 1 < U; k += 2) {
-            a0 = fmaf(xs[r * Up + k], __ldg(w + k), a0);
-            a1 = fmaf(xs[r * Up + k + 1], __ldg(w + k + 1), a1);
+    // four classes at a time per thread: four independent FMA chains share every x value
+    for (int c = threadIdx.x >> 5; c < C; c += 32) {
+        const float *w0 = W + (size_t)c * U;
+        const bool v1 = c + 8 < C, v2 = c + 16 < C, v3 = c + 24 < C;
+        const float *w1 = v1 ? w0 + (size_t)8 * U : w0, *w2 = v2 ? w0 + (size_t)16 * U : w0, *w3 = v3 ? w0 + (size_t)24 * U : w0;
+        float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+#pragma unroll 4
+        for (int k = 0; k < U; ++k) {
+            const float xv = xs[r * Up + k];
+            a0 = fmaf(xv, __ldg(w0 + k), a0);
+            a1 = fmaf(xv, __ldg(w1 + k), a1);
+            a2 = fmaf(xv, __ldg(w2 + k), a2);
+            a3 = fmaf(xv, __ldg(w3 + k), a3);
         }
-        if (k < U) a0 = fmaf(xs[r * Up + k], __ldg(w + k), a0);
-        if (r < rows) out[(b0 + r) * C + c] = (a0 + a1) + bias[c];
+        if (r < rows) {
+            float *o = out + (b0 + r) * C;
+            o[c] = a0 + bias[c];
+            if (v1) o[c + 8] = a1 + bias[c + 8];
+            if (v2) o[c + 16] = a2 + bias[c + 16];
+            if (v3) o[c + 24] = a3 + bias[c + 24];
+        }
     }
 }
 
@@ -283,9 +294,25 @@ __global__ void __launch_bounds__(FC_THREADS) fc2_train_kernel(
     const unsigned thresh = pdrop > 0.f ? (unsigned)min(4294967295.0, (double)pdrop * 4294967296.0) : 0u;
     const float keep_scale = pdrop > 0.f ? 1.0f / (1.0f - pdrop) : 1.0f;
     float s3 = 0.f, q3 = 0.f;
+    // software pipeline: the four values of the next row are in flight while this row is reduced
+    float hn[4] = {0.f, 0.f, 0.f, 0.f};
+    if (warp < rows) {
+        const float *hr = h1 + ((size_t)u * B + b0 + warp) * H;
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+            if (lane + 32 * i < H) hn[i] = hr[lane + 32 * i];
+    }
     for (int r = warp; r < rows; r += 8) {
         const size_t rowi = (size_t)u * B + b0 + r;
-        const float *hr = h1 + rowi * H;
+        float hc[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) hc[i] = hn[i];
+        if (r + 8 < rows) {
+            const float *hr = h1 + (rowi + 8) * H;
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+                if (lane + 32 * i < H) hn[i] = hr[lane + 32 * i];
+        }
         float dot = 0.f;
         uint32_t mword = 0;
 #pragma unroll
@@ -293,7 +320,7 @@ __global__ void __launch_bounds__(FC_THREADS) fc2_train_kernel(
             const int j = lane + 32 * i;
             bool keep = false;
             if (j < H) {
-                float v = fmaxf(fmaf(hr[j], sc[j], sh[j]), 0.f);
+                float v = fmaxf(fmaf(hc[i], sc[j], sh[j]), 0.f);
                 if (pdrop > 0.f) {
                     const float ks = drop_scale(seed, rowi * H + j, thresh, keep_scale);
                     keep = ks != 0.f;
@@ -337,11 +364,12 @@ __global__ void __launch_bounds__(256) out_train_kernel(const float *__restrict_
     extern __shared__ float xs[];   // [8][U] then sc3[U], sh3[U], then (when it fits) Wf as [C][U+1]
     float *sc3 = xs + OT_ROWS * U, *sh3 = sc3 + U;
     float *wfs = sh3 + U;
+    // blockIdx.y selects a slice of the classes, so that more SMs share the work and each CTA stages less of Wf
+    const int cper = (C + gridDim.y - 1) / gridDim.y;
+    const int c_lo = blockIdx.y * cper, c_hi = min(C, c_lo + cper);
     if (wf_in_smem)
-        for (int i = threadIdx.x; i < C * U; i += blockDim.x) {
-            const int c = i / U, k = i - c * U;
-            wfs[c * (U + 1) + k] = Wf[i];
-        }
+        for (int c = c_lo + (threadIdx.x >> 5); c < c_hi; c += blockDim.x >> 5)
+            for (int k = threadIdx.x & 31; k < U; k += 32) wfs[(c - c_lo) * (U + 1) + k] = Wf[(size_t)c * U + k];
     const long long b0 = (long long)blockIdx.x * OT_ROWS;
     const int rows = (int)min((long long)OT_ROWS, B - b0);
     for (int u = threadIdx.x; u < U; u += blockDim.x) {
@@ -354,7 +382,7 @@ __global__ void __launch_bounds__(256) out_train_kernel(const float *__restrict_
         double var = sq / (double)B - mean * mean;
         if (var < 0.0) var = 0.0;
         const float inv = (float)(1.0 / sqrt(var + (double)eps));
-        if (blockIdx.x == 0) {
+        if (blockIdx.x == 0 && blockIdx.y == 0) {
             mean3[u] = (float)mean;
             invstd3[u] = inv;
             if (rm3) {
@@ -372,16 +400,16 @@ __global__ void __launch_bounds__(256) out_train_kernel(const float *__restrict_
     if (warp < rows) {
         for (int u = lane; u < U; u += 32) {
             const float v = fmaxf(fmaf(h2[(size_t)u * B + b0 + warp], sc3[u], sh3[u]), 0.f);
-            unit[(b0 + warp) * U + u] = v;
+            if (blockIdx.y == 0) unit[(b0 + warp) * U + u] = v;
             xs[warp * U + u] = v;
         }
     }
     __syncthreads();
     if (warp < rows) {
         const float *xr = xs + warp * U;
-        for (int c = lane; c < C; c += 32) {
+        for (int c = c_lo + lane; c < c_hi; c += 32) {
             // lanes run over the classes: in shared memory the row stride U+1 keeps them on different banks
-            const float *w = wf_in_smem ? wfs + (size_t)c * (U + 1) : Wf + (size_t)c * U;
+            const float *w = wf_in_smem ? wfs + (size_t)(c - c_lo) * (U + 1) : Wf + (size_t)c * U;
             float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
             int k = 0;
             for (; k + 3 < U; k += 4) {
@@ -542,17 +570,31 @@ __global__ void __launch_bounds__(FC_THREADS) bwd_fc2_kernel(const float *__rest
     const unsigned thresh = pdrop > 0.f ? (unsigned)min(4294967295.0, (double)pdrop * 4294967296.0) : 0u;
     const float keep_scale = pdrop > 0.f ? 1.0f / (1.0f - pdrop) : 1.0f;
     float dW2[4] = {0, 0, 0, 0}, sg[4] = {0, 0, 0, 0}, sgx[4] = {0, 0, 0, 0};
+    float hn[4] = {0.f, 0.f, 0.f, 0.f}, gn = 0.f;
+    uint32_t wn = 0u;
+    auto fetch = [&](size_t rowi) {
+        const float *hr = h1 + rowi * H;
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+            if (lane + 32 * i < H) hn[i] = hr[lane + 32 * i];
+        gn = gh2[rowi];
+        wn = (pdrop > 0.f && dropmask && lane < 4) ? dropmask[rowi * 4 + lane] : 0u;
+    };
+    if (warp < rows) fetch((size_t)u * B + b0 + warp);
     for (int r = warp; r < rows; r += 8) {
         const size_t rowi = (size_t)u * B + b0 + r;
-        const float *hr = h1 + rowi * H;
-        const float g = gh2[rowi];
-        const uint32_t myw = (pdrop > 0.f && dropmask && lane < 4) ? dropmask[rowi * 4 + lane] : 0u;
+        float hc[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) hc[i] = hn[i];
+        const float g = gn;
+        const uint32_t myw = wn;
+        if (r + 8 < rows) fetch(rowi + 8);       // next row in flight while this one is processed
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             const int j = lane + 32 * i;
             const uint32_t wi = __shfl_sync(0xffffffffu, myw, i);
             if (j < H) {
-                const float xh = (hr[j] - mu[j]) * inv[j];
+                const float xh = (hc[i] - mu[j]) * inv[j];
                 const float zb = fmaf(ga[j], xh, be[j]);
                 const float ks = pdrop > 0.f ? (dropmask ? (((wi >> lane) & 1u) ? keep_scale : 0.f)
                                                          : drop_scale(seed, rowi * H + j, thresh, keep_scale))
@@ -760,7 +802,8 @@ extern "C" int explainn_fc_stack_fwd_train(const float *pooled, long long B, int
     const int nchunk = (int)((B + BM - 1) / BM);
     const size_t smem1 = FcSmem::bytes(P) + (size_t)BM * HS * 4;
     size_t smem3 = ((size_t)OT_ROWS * U + 2 * (size_t)U) * 4;
-    const size_t smem3_wf = smem3 + (size_t)C * (U + 1) * 4;
+    const int ot_ny = C >= 48 ? 3 : 1;           // class slices per row group
+    const size_t smem3_wf = smem3 + (size_t)((C + ot_ny - 1) / ot_ny) * (U + 1) * 4;
     const int wf_in_smem = smem3_wf <= 200 * 1024;
     if (wf_in_smem) smem3 = smem3_wf;
     if (smem1 > 220 * 1024 || smem3 > 220 * 1024) {
@@ -777,7 +820,7 @@ extern "C" int explainn_fc_stack_fwd_train(const float *pooled, long long B, int
     fc2_train_kernel<<<dim3(U, nchunk), FC_THREADS, 0, stream>>>(h1, B, U, part2, nchunk, bn2_w, bn2_b, bn2_rm, bn2_rv, momentum, eps,
                                                                  W2, b2, mean2, invstd2, pdrop, seed, seed_dev, dropmask, h2, part3);
     cudaFuncSetAttribute(out_train_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem3);
-    out_train_kernel<<<(unsigned)((B + OT_ROWS - 1) / OT_ROWS), 256, smem3, stream>>>(h2, B, U, C, part3, nchunk, bn3_w, bn3_b, bn3_rm, bn3_rv,
+    out_train_kernel<<<dim3((unsigned)((B + OT_ROWS - 1) / OT_ROWS), ot_ny), 256, smem3, stream>>>(h2, B, U, C, part3, nchunk, bn3_w, bn3_b, bn3_rm, bn3_rv,
                                                                         momentum, eps, mean3, invstd3, Wf, bf, unit, logits, wf_in_smem);
     return xb_check_launch("fc_stack_fwd_train");
 }

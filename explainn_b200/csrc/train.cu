@@ -21,48 +21,76 @@
 namespace {
 
 // ------------------------------------------------------------------------------------------------
-// co-occurrence counts.  One thread per tap pair (k <= k'), 16 private counters (c,c') in shared memory.
+// co-occurrence counts, bit-parallel.  Per sequence four indicator bitmasks I_c (bit s set iff base s is c; N sets
+// none) are built in shared memory; the thread that owns the tap pair (k <= k') then gets, for all 16 base pairs,
+//   M[(c,k),(c',k')] += popcount( (I_c >> k) & (I_c' >> k') & [s < S] )
+// 32 positions per AND+POPC, counters in registers, one atomicAdd per counter and CTA at the end.
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(320) cooc_kernel(const uint32_t *__restrict__ codes, const uint32_t *__restrict__ nmask,
                                                    long long B, int L, int F, int wc, int wm, int *__restrict__ M)
 {
-    extern __shared__ __align__(16) unsigned char sm[];
-    const int NT = blockDim.x;
-    int *cnt = reinterpret_cast<int *>(sm);                        // [16][NT]
-    unsigned char *sb = sm + (size_t)16 * NT * 4;                   // [L + pad]
-    const int tid = threadIdx.x;
+    extern __shared__ uint32_t ind[];          // [4][wm + 1] indicator words, one zero word of padding per base
+    const int NT = blockDim.x, tid = threadIdx.x;
+    const int IW = wm + 1;
     const int npairs = F * (F + 1) / 2;
-    // pair index -> (k, k2) with k <= k2
-    int k = 0, k2 = 0;
+    int k = 0, k2 = 0;                         // pair index -> (k, k2) with k <= k2
     if (tid < npairs) {
         int r = tid;
         while (r >= F - k) { r -= F - k; ++k; }
         k2 = k + r;
     }
-    for (int j = 0; j < 16; ++j) cnt[j * NT + tid] = 0;
+    int cnt[4][4];
+#pragma unroll
+    for (int c = 0; c < 4; ++c)
+#pragma unroll
+        for (int c2 = 0; c2 < 4; ++c2) cnt[c][c2] = 0;
     const int S = L - F + 1;
     for (long long b = blockIdx.x; b < B; b += gridDim.x) {
         __syncthreads();
-        for (int i = tid; i < L; i += NT) {
-            const unsigned c = (codes[b * wc + (i >> 4)] >> (2 * (i & 15))) & 3u;
-            const unsigned m = (nmask[b * wm + (i >> 5)] >> (i & 31)) & 1u;
-            sb[i] = (unsigned char)(m ? 4u : c);
+        // indicator words: word w covers positions 32w .. 32w+31 = code words 2w, 2w+1
+        for (int i = tid; i < 4 * IW; i += NT) {
+            const int c = i / IW, w = i - c * IW;
+            uint32_t bits = 0;
+            if (w < wm) {
+                const uint32_t c0 = codes[b * wc + 2 * w], c1 = 2 * w + 1 < wc ? codes[b * wc + 2 * w + 1] : 0u;
+                // a position matches base c iff its 2-bit code equals c: xor with the replicated pattern, then test both bits
+                const uint32_t pat = 0x55555555u * (uint32_t)c;
+                const uint32_t x0 = c0 ^ pat, x1 = c1 ^ pat;
+                const uint32_t z0 = ~(x0 | (x0 >> 1)) & 0x55555555u, z1 = ~(x1 | (x1 >> 1)) & 0x55555555u;   // bit 2j set iff code j == c
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    bits |= ((z0 >> (2 * j)) & 1u) << j;
+                    bits |= ((z1 >> (2 * j)) & 1u) << (16 + j);
+                }
+                bits &= ~nmask[b * wm + w];
+                if (32 * w + 32 > L) bits &= (L - 32 * w >= 32) ? 0xFFFFFFFFu : ((1u << (L - 32 * w)) - 1u);
+            }
+            ind[i] = bits;
         }
         __syncthreads();
         if (tid < npairs) {
-            const unsigned char *p1 = sb + k, *p2 = sb + k2;
-#pragma unroll 4
-            for (int s = 0; s < S; ++s) {
-                const unsigned c = p1[s], c2 = p2[s];
-                if ((c | c2) < 4u) cnt[(c * 4 + c2) * NT + tid] += 1;
+            for (int w = 0; 32 * w < S; ++w) {
+                const uint32_t valid = S - 32 * w >= 32 ? 0xFFFFFFFFu : ((1u << (S - 32 * w)) - 1u);
+                uint32_t a[4], bb[4];
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    a[c] = __funnelshift_r(ind[c * IW + w], ind[c * IW + w + 1], k) & valid;
+                    bb[c] = __funnelshift_r(ind[c * IW + w], ind[c * IW + w + 1], k2);
+                }
+#pragma unroll
+                for (int c = 0; c < 4; ++c)
+#pragma unroll
+                    for (int c2 = 0; c2 < 4; ++c2) cnt[c][c2] += __popc(a[c] & bb[c2]);
             }
         }
     }
     if (tid < npairs) {
         const int W = 4 * F;
+#pragma unroll
         for (int c = 0; c < 4; ++c)
+#pragma unroll
             for (int c2 = 0; c2 < 4; ++c2) {
-                const int v = cnt[(c * 4 + c2) * NT + tid];
+                const int v = cnt[c][c2];
                 if (!v) continue;
                 atomicAdd(&M[(c * F + k) * W + (c2 * F + k2)], v);
                 if (k != k2) atomicAdd(&M[(c2 * F + k2) * W + (c * F + k)], v);
@@ -341,8 +369,8 @@ extern "C" int explainn_input_cooc_stats(const uint32_t *codes, const uint32_t *
     if (B == 0) return XB_OK;
     const int npairs = F * (F + 1) / 2;
     const int NT = ((npairs + 31) / 32) * 32;
-    const size_t smem = (size_t)16 * NT * 4 + ((L + 15) / 16) * 16;
-    int grid = 2 * xb_num_sms();
+    const size_t smem = (size_t)4 * (xb_words_mask(L) + 1) * 4;
+    int grid = xb_num_sms();
     if (grid > B) grid = (int)B;
     cudaFuncSetAttribute(cooc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     cooc_kernel<<<grid, NT, smem, stream>>>(codes, nmask, B, L, F, xb_words_codes(L), xb_words_mask(L), M);
