@@ -70,14 +70,34 @@ __device__ __forceinline__ float det_expf(float x)
 __device__ __forceinline__ float fp16_round(float x) { return __half2float(__float2half_rn(x)); }
 
 // ---- dropout ---------------------------------------------------------------------------------------
-// counter-based dropout mask: splitmix64 of (seed, element index); keep iff the top 32 bits >= p * 2^32
+// counter-based dropout mask.  One 32-bit multiply-xorshift hash per QUAD of consecutive elements (keyed with both
+// halves of the seed) plus one cheap multiply-xorshift step per further element; element e is kept iff its 32-bit
+// value >= p * 2^32.  32-bit arithmetic and the quad sharing are on purpose: the mask generation sits in the inner
+// loop of the FC2 training kernel.  Returns the keep bits of elements 4*quad .. 4*quad+3 in bits 0..3.
+__device__ __forceinline__ uint32_t drop_keep4(unsigned long long seed, unsigned long long quad, unsigned thresh)
+{
+    uint32_t x = (uint32_t)quad ^ (uint32_t)seed ^ ((uint32_t)(quad >> 32) * 0x9E3779B9u);
+    x ^= x >> 16;
+    x *= 0x7FEB352Du;
+    x ^= x >> 15;
+    x *= 0x846CA68Bu;
+    x ^= x >> 16;
+    x += (uint32_t)(seed >> 32);
+    x *= 0x9E3779B1u;
+    x ^= x >> 15;
+    uint32_t bits = x >= thresh ? 1u : 0u;
+#pragma unroll
+    for (int i = 1; i < 4; ++i) {
+        x = x * 0x2C1B3C6Du + 0x7F4A7C15u;
+        x ^= x >> 15;
+        bits |= (x >= thresh ? 1u : 0u) << i;
+    }
+    return bits;
+}
+
 __device__ __forceinline__ float drop_scale(unsigned long long seed, unsigned long long elem, unsigned thresh, float keep_scale)
 {
-    unsigned long long z = seed + elem * 0x9E3779B97F4A7C15ull;
-    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
-    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
-    z ^= z >> 31;
-    return (unsigned)(z >> 32) >= thresh ? keep_scale : 0.0f;
+    return ((drop_keep4(seed, elem >> 2, thresh) >> (elem & 3ull)) & 1u) ? keep_scale : 0.0f;
 }
 
 // ---- small warp helpers ------------------------------------------------------------------------

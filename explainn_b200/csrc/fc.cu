@@ -21,6 +21,7 @@ int xb_fc_stack_fwd_eval_tc(const float *pooled, long long B, int U, int P, cons
                             const float *be2, const float *rm2, const float *rv2, const float *W2, const float *b2, const float *g3,
                             const float *be3, const float *rm3, const float *rv3, float eps, float *unit_out, cudaStream_t stream);
 bool xb_fc_tc_enabled();
+int xb_linear_tc(const float *x, long long B, int U, int C, const float *W, const float *bias, float *out, cudaStream_t stream);
 int xb_bwd_fc1_tc(const float *h1, const float *gh2, const float *pooled, long long B, int U, int P, const float *g2, const float *be2,
                   const float *mean2, const float *invstd2, const float *W1, const float *W2, float pdrop, unsigned long long seed,
                   const unsigned long long *seed_dev, const uint32_t *dropmask, const float *pb2, float *gpool, float *dW1p, float *dW2,
@@ -294,47 +295,38 @@ __global__ void __launch_bounds__(FC_THREADS) fc2_train_kernel(
     const unsigned thresh = pdrop > 0.f ? (unsigned)min(4294967295.0, (double)pdrop * 4294967296.0) : 0u;
     const float keep_scale = pdrop > 0.f ? 1.0f / (1.0f - pdrop) : 1.0f;
     float s3 = 0.f, q3 = 0.f;
-    // software pipeline: the four values of the next row are in flight while this row is reduced
-    float hn[4] = {0.f, 0.f, 0.f, 0.f};
-    if (warp < rows) {
-        const float *hr = h1 + ((size_t)u * B + b0 + warp) * H;
-#pragma unroll
-        for (int i = 0; i < 4; ++i)
-            if (lane + 32 * i < H) hn[i] = hr[lane + 32 * i];
-    }
+    // lane l < 25 owns hidden channels 4l .. 4l+3 (one 16-byte load per row); its BN-2 / FC2 coefficients stay in registers
+    static_assert(H % 4 == 0 && H / 4 <= 32, "quad layout");
+    const bool act = lane < H / 4;
+    const int j0 = act ? 4 * lane : 0;
+    const float4 scv = act ? make_float4(sc[j0], sc[j0 + 1], sc[j0 + 2], sc[j0 + 3]) : make_float4(0.f, 0.f, 0.f, 0.f);
+    const float4 shv = act ? make_float4(sh[j0], sh[j0 + 1], sh[j0 + 2], sh[j0 + 3]) : make_float4(0.f, 0.f, 0.f, 0.f);
+    const float4 w2v = act ? make_float4(w2s[j0], w2s[j0 + 1], w2s[j0 + 2], w2s[j0 + 3]) : make_float4(0.f, 0.f, 0.f, 0.f);
+    const float bias2 = b2[u];
+    // software pipeline: the next row is in flight while this row is reduced
+    float4 hn = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (warp < rows && act) hn = *reinterpret_cast<const float4 *>(h1 + ((size_t)u * B + b0 + warp) * H + j0);
     for (int r = warp; r < rows; r += 8) {
         const size_t rowi = (size_t)u * B + b0 + r;
-        float hc[4];
-#pragma unroll
-        for (int i = 0; i < 4; ++i) hc[i] = hn[i];
-        if (r + 8 < rows) {
-            const float *hr = h1 + (rowi + 8) * H;
-#pragma unroll
-            for (int i = 0; i < 4; ++i)
-                if (lane + 32 * i < H) hn[i] = hr[lane + 32 * i];
+        const float4 hc = hn;
+        if (r + 8 < rows && act) hn = *reinterpret_cast<const float4 *>(h1 + (rowi + 8) * H + j0);
+        uint32_t nib = 15u;
+        if (pdrop > 0.f) nib = drop_keep4(seed, rowi * (H / 4) + lane, thresh);
+        const float v0 = (nib & 1u) ? fmaxf(fmaf(hc.x, scv.x, shv.x), 0.f) * keep_scale : 0.f;
+        const float v1 = (nib & 2u) ? fmaxf(fmaf(hc.y, scv.y, shv.y), 0.f) * keep_scale : 0.f;
+        const float v2 = (nib & 4u) ? fmaxf(fmaf(hc.z, scv.z, shv.z), 0.f) * keep_scale : 0.f;
+        const float v3 = (nib & 8u) ? fmaxf(fmaf(hc.w, scv.w, shv.w), 0.f) * keep_scale : 0.f;
+        float dot = fmaf(v3, w2v.w, fmaf(v2, w2v.z, fmaf(v1, w2v.y, v0 * w2v.x)));
+        if (pdrop > 0.f && dropmask) {
+            // the keep bits are saved for the backward: word w of the row holds channels 32w .. 32w+31 (8 lanes' nibbles)
+            uint32_t m = act ? nib << (4 * (lane & 7)) : 0u;
+            m |= __shfl_xor_sync(0xffffffffu, m, 1);
+            m |= __shfl_xor_sync(0xffffffffu, m, 2);
+            m |= __shfl_xor_sync(0xffffffffu, m, 4);
+            if ((lane & 7) == 0) dropmask[rowi * 4 + (lane >> 3)] = m;
         }
-        float dot = 0.f;
-        uint32_t mword = 0;
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            const int j = lane + 32 * i;
-            bool keep = false;
-            if (j < H) {
-                float v = fmaxf(fmaf(hc[i], sc[j], sh[j]), 0.f);
-                if (pdrop > 0.f) {
-                    const float ks = drop_scale(seed, rowi * H + j, thresh, keep_scale);
-                    keep = ks != 0.f;
-                    v *= ks;
-                }
-                dot = fmaf(v, w2s[j], dot);
-            }
-            // the keep bits are saved for the backward: word i of the row holds channels 32i .. 32i+31
-            const uint32_t w = __ballot_sync(0xffffffffu, keep);
-            if (lane == i) mword = w;
-        }
-        if (pdrop > 0.f && dropmask && lane < 4) dropmask[rowi * 4 + lane] = mword;
         dot = warp_sum(dot);
-        const float o = dot + b2[u];
+        const float o = dot + bias2;
         if (lane == 0) {
             h2[rowi] = o;
             s3 += o;
@@ -569,49 +561,52 @@ __global__ void __launch_bounds__(FC_THREADS) bwd_fc2_kernel(const float *__rest
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const unsigned thresh = pdrop > 0.f ? (unsigned)min(4294967295.0, (double)pdrop * 4294967296.0) : 0u;
     const float keep_scale = pdrop > 0.f ? 1.0f / (1.0f - pdrop) : 1.0f;
-    float dW2[4] = {0, 0, 0, 0}, sg[4] = {0, 0, 0, 0}, sgx[4] = {0, 0, 0, 0};
-    float hn[4] = {0.f, 0.f, 0.f, 0.f}, gn = 0.f;
-    uint32_t wn = 0u;
-    auto fetch = [&](size_t rowi) {
-        const float *hr = h1 + rowi * H;
+    // lane l < 25 owns hidden channels 4l .. 4l+3 (one 16-byte load per row); coefficients stay in registers
+    const bool act = lane < H / 4;
+    const int j0 = act ? 4 * lane : 0;
+    float muv[4], inv4[4], gav[4], bev[4], w2v[4];
 #pragma unroll
-        for (int i = 0; i < 4; ++i)
-            if (lane + 32 * i < H) hn[i] = hr[lane + 32 * i];
+    for (int i = 0; i < 4; ++i) {
+        muv[i] = act ? mu[j0 + i] : 0.f; inv4[i] = act ? inv[j0 + i] : 0.f; gav[i] = act ? ga[j0 + i] : 0.f;
+        bev[i] = act ? be[j0 + i] : 0.f; w2v[i] = act ? w2s[j0 + i] : 0.f;
+    }
+    float dW2[4] = {0, 0, 0, 0}, sg[4] = {0, 0, 0, 0}, sgx[4] = {0, 0, 0, 0};
+    float4 hn = make_float4(0.f, 0.f, 0.f, 0.f);
+    float gn = 0.f;
+    uint32_t wn = 0u;
+    const bool use_mask = pdrop > 0.f && dropmask;
+    auto fetch = [&](size_t rowi) {
+        if (act) hn = *reinterpret_cast<const float4 *>(h1 + rowi * H + j0);
         gn = gh2[rowi];
-        wn = (pdrop > 0.f && dropmask && lane < 4) ? dropmask[rowi * 4 + lane] : 0u;
+        wn = use_mask ? dropmask[rowi * 4 + (lane >> 3)] : 0u;
     };
     if (warp < rows) fetch((size_t)u * B + b0 + warp);
     for (int r = warp; r < rows; r += 8) {
         const size_t rowi = (size_t)u * B + b0 + r;
-        float hc[4];
-#pragma unroll
-        for (int i = 0; i < 4; ++i) hc[i] = hn[i];
+        const float hc[4] = {hn.x, hn.y, hn.z, hn.w};
         const float g = gn;
-        const uint32_t myw = wn;
+        uint32_t nib = 15u;
+        if (pdrop > 0.f) nib = use_mask ? (wn >> (4 * (lane & 7))) & 15u : drop_keep4(seed, rowi * (H / 4) + lane, thresh);
         if (r + 8 < rows) fetch(rowi + 8);       // next row in flight while this one is processed
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-            const int j = lane + 32 * i;
-            const uint32_t wi = __shfl_sync(0xffffffffu, myw, i);
-            if (j < H) {
-                const float xh = (hc[i] - mu[j]) * inv[j];
-                const float zb = fmaf(ga[j], xh, be[j]);
-                const float ks = pdrop > 0.f ? (dropmask ? (((wi >> lane) & 1u) ? keep_scale : 0.f)
-                                                         : drop_scale(seed, rowi * H + j, thresh, keep_scale))
-                                             : 1.0f;
-                const float a2 = fmaxf(zb, 0.f) * ks;
-                dW2[i] = fmaf(g, a2, dW2[i]);
-                const float gz2 = zb > 0.f ? g * w2s[j] * ks : 0.f;
-                sg[i] += gz2;
-                sgx[i] = fmaf(gz2, xh, sgx[i]);
-            }
+            const float xh = (hc[i] - muv[i]) * inv4[i];
+            const float zb = fmaf(gav[i], xh, bev[i]);
+            const float ks = ((nib >> i) & 1u) ? keep_scale : 0.f;
+            const float a2 = fmaxf(zb, 0.f) * ks;
+            dW2[i] = fmaf(g, a2, dW2[i]);
+            const float gz2 = zb > 0.f ? g * w2v[i] * ks : 0.f;
+            sg[i] += gz2;
+            sgx[i] = fmaf(gz2, xh, sgx[i]);
         }
     }
+    if (act) {
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        red[warp][0][lane + 32 * i] = dW2[i];
-        red[warp][1][lane + 32 * i] = sg[i];
-        red[warp][2][lane + 32 * i] = sgx[i];
+        for (int i = 0; i < 4; ++i) {
+            red[warp][0][j0 + i] = dW2[i];
+            red[warp][1][j0 + i] = sg[i];
+            red[warp][2][j0 + i] = sgx[i];
+        }
     }
     __syncthreads();
     for (int i = threadIdx.x; i < 3 * H; i += blockDim.x) {
@@ -772,6 +767,10 @@ extern "C" int explainn_linear_fwd(const float *x, long long B, int U, int C, co
 {
     XB_REQUIRE(x && W && bias && out && B >= 0 && U >= 1 && C >= 1, "linear_fwd: bad argument");
     if (B == 0) return XB_OK;
+    if (xb_fc_tc_enabled()) {    // tcgen05 path (XB_FC_TC=0 selects the CUDA-core kernel below)
+        const int rc = xb_linear_tc(x, B, U, C, W, bias, out, stream);
+        if (rc != XB_ERR_UNSUPPORTED) return rc;
+    }
     const size_t smem = (size_t)32 * (U + 1) * 4;
     if (smem > 200 * 1024) {
         xb_set_error("linear_fwd: %d input features need %zu bytes of shared memory", U, smem);
@@ -799,6 +798,7 @@ extern "C" int explainn_fc_stack_fwd_train(const float *pooled, long long B, int
                "fc_stack_fwd_train: null pointer");
     XB_REQUIRE(B >= 2 && U >= 1 && P >= 1 && C >= 1, "fc_stack_fwd_train: bad sizes (train-mode BatchNorm needs B >= 2)");
     XB_REQUIRE(pdrop >= 0.f && pdrop < 1.f, "fc_stack_fwd_train: dropout probability %f", pdrop);
+    XB_REQUIRE(((uintptr_t)h1 & 15) == 0, "fc_stack_fwd_train: h1 must be 16-byte aligned");
     const int nchunk = (int)((B + BM - 1) / BM);
     const size_t smem1 = FcSmem::bytes(P) + (size_t)BM * HS * 4;
     size_t smem3 = ((size_t)OT_ROWS * U + 2 * (size_t)U) * 4;
@@ -837,6 +837,7 @@ extern "C" int explainn_fc_stack_bwd(const float *glogits, long long B, int U, i
                    gh2 && pb2 && dW1_partials && gpool && dW1,
                "fc_stack_bwd: null pointer");
     XB_REQUIRE(B >= 2 && U >= 1 && P >= 1 && C >= 1, "fc_stack_bwd: bad sizes");
+    XB_REQUIRE(((uintptr_t)h1 & 15) == 0, "fc_stack_bwd: h1 must be 16-byte aligned");
     const int nchunk = (int)((B + BM - 1) / BM);
     // Wf == NULL: glogits is the gradient w.r.t. the unit outputs (B,U) and the final layer is skipped
     if (Wf) {

@@ -238,7 +238,9 @@ constexpr int BT_P = 48;                  // pooled positions padded to a multip
 constexpr int BT_G_SBO = (BT_J / 4) * 128;          // 8-row group stride of a tile with K = j  (3328)
 constexpr int BT_B_SBO = (FT_ROWS / 4) * 128;       // 8-row group stride of a tile with K = b  (4096)
 constexpr int BT_G_BYTES = FT_ROWS * BT_J * 4;      // G  [128 b][104 j]   53,248
-constexpr int BT_GT_BYTES = FT_ROWS * FT_ROWS * 4;  // Gt [128 j][128 b]   65,536
+constexpr int BT_GT_BYTES = BT_J * FT_ROWS * 4;     // Gt [104 j][128 b]   53,248 (accumulator rows 104..127 are never read back)
+constexpr int BT_H_BYTES = FT_ROWS * H * 4;         // staged h1 tile       51,200
+constexpr int BT_S_BYTES = FT_ROWS * BT_P * 4;      // output staging       24,576
 constexpr int BT_W_BYTES = BT_P * BT_J * 4;         // W1t [48 p][104 j]   19,968
 constexpr int BT_A_BYTES = BT_P * FT_ROWS * 4;      // At  [48 p][128 b]   24,576
 constexpr int BT_NG = (FT_ROWS / 8) * (BT_J / 4) / (FT_THREADS / 32);   // core matrices of G per warp = 52
@@ -276,11 +278,13 @@ __global__ void __launch_bounds__(FT_THREADS, 1) bwd_fc1_tc_kernel(const FcBwdAr
 
     unsigned char *sR = smem;                                   // phase 1: G hi | G lo ; phase 2: Gt hi | Gt lo
     unsigned char *sAh = sR + 2 * BT_GT_BYTES, *sAl = sAh + BT_A_BYTES;
-    unsigned char *sWh = sAl + BT_A_BYTES, *sWl = sWh + BT_W_BYTES;
-    // the h1 tile (128 x 100 floats, contiguous in global memory) is staged by ONE TMA bulk copy into the bytes that
-    // phase 1 does not use yet: the tail of the Gt region plus the pooled-tile buffers (filled after the G build)
-    float *sH = reinterpret_cast<float *>(sR + 2 * BT_G_BYTES);
-    static_assert(2 * BT_GT_BYTES + 2 * BT_A_BYTES - 2 * BT_G_BYTES >= FT_ROWS * H * 4, "h1 staging does not fit");
+    // the h1 tile (128 x 100 floats, contiguous in global memory) is staged by ONE TMA bulk copy into the pooled-tile
+    // buffers (filled only after the G build) plus a 2 KB pad; it is issued as soon as the previous tile's D2 MMAs
+    // have retired, so it flies during that tile's output drain
+    float *sH = reinterpret_cast<float *>(sAh);
+    float *sS = reinterpret_cast<float *>(sAh + BT_H_BYTES);           // staging of D1 / D2 for coalesced stores
+    unsigned char *sWh = sAh + BT_H_BYTES + BT_S_BYTES, *sWl = sWh + BT_W_BYTES;
+    static_assert(BT_H_BYTES >= 2 * BT_A_BYTES && BT_GT_BYTES == BT_G_BYTES, "shared-memory plan");
     __shared__ __align__(8) uint64_t bar_h;
     __shared__ float gh2s[FT_ROWS];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -308,8 +312,7 @@ __global__ void __launch_bounds__(FT_THREADS, 1) bwd_fc1_tc_kernel(const FcBwdAr
         const int u = (int)(tile / a.nchunk), chunk = (int)(tile - (long long)u * a.nchunk);
         const long long b0 = (long long)chunk * FT_ROWS;
         const int rows = (int)min((long long)FT_ROWS, a.B - b0);
-        if (threadIdx.x == 0) {
-            // previous tile's tensor-core reads of this region are complete (its second commit was waited on)
+        if (threadIdx.x == 0 && tile == t_begin) {      // later tiles: issued by the previous iteration (see below)
             mbar_arrive_expect_tx(&bar_h, (uint32_t)rows * H * 4);
             tma_bulk_g2s(sH, a.h1 + ((size_t)u * a.B + b0) * H, (uint32_t)rows * H * 4, &bar_h);
         }
@@ -462,16 +465,33 @@ __global__ void __launch_bounds__(FT_THREADS, 1) bwd_fc1_tc_kernel(const FcBwdAr
             tc_ld16_nowait(taddr + 16, r + 16);
             tc_ld16_nowait(taddr + 32, r + 32);
             tc_wait_ld();
-            if (row < rows) {
-                float *dst = a.gpool + ((size_t)(b0 + row) * a.U + u) * a.P;
+            float *st = sS + row * a.P;
 #pragma unroll
-                for (int p = 0; p < BT_P; ++p)
-                    if (p < a.P) dst[p] = __uint_as_float(r[p]);
+            for (int p = 0; p < BT_P; ++p)
+                if (p < a.P) st[p] = __uint_as_float(r[p]);
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            // rows of P floats, P*4 bytes contiguous each: consecutive threads write consecutive addresses
+            float *dst = a.gpool + ((size_t)b0 * a.U + u) * a.P;
+            const size_t rstride = (size_t)a.U * a.P;
+            const int n = rows * a.P;
+            for (int i = threadIdx.x; i < n; i += 128) {
+                const int rr = i / a.P;
+                dst[rr * rstride + (i - rr * a.P)] = sS[i];
             }
         }
         mbar_wait(&bar, parity);
         parity ^= 1;
         tc_fence_after();
+        if (threadIdx.x == 0 && tile + 1 < t_end) {
+            // D2 has retired: the pooled-tile buffers are free, prefetch the next tile's h1 rows into them
+            const long long tn = tile + 1;
+            const int un = (int)(tn / a.nchunk);
+            const long long bn = (tn - (long long)un * a.nchunk) * FT_ROWS;
+            const uint32_t bytes = (uint32_t)min((long long)FT_ROWS, a.B - bn) * H * 4;
+            mbar_arrive_expect_tx(&bar_h, bytes);
+            tma_bulk_g2s(sH, a.h1 + ((size_t)un * a.B + bn) * H, bytes, &bar_h);
+        }
+        __syncthreads();      // the D1 copy-out has finished reading the staging buffer
         if (which == 1) {      // warps 4-7 drain D2 (row = hidden channel)
             const uint32_t taddr = tmem_base + ((uint32_t)(32 * q) << 16) + 64;
             uint32_t r[48];
@@ -480,14 +500,299 @@ __global__ void __launch_bounds__(FT_THREADS, 1) bwd_fc1_tc_kernel(const FcBwdAr
             tc_ld16_nowait(taddr + 32, r + 32);
             tc_wait_ld();
             if (row < H) {
-                float *dst = a.dW1p + (((size_t)chunk * a.U + u) * H + row) * a.P;
+                float *st = sS + row * a.P;
 #pragma unroll
                 for (int p = 0; p < BT_P; ++p)
-                    if (p < a.P) dst[p] = __uint_as_float(r[p]);
+                    if (p < a.P) st[p] = __uint_as_float(r[p]);
             }
+            asm volatile("bar.sync 2, 128;" ::: "memory");
+            float *dst = a.dW1p + ((size_t)chunk * a.U + u) * H * a.P;      // 100 x P floats, contiguous
+            const int n = H * a.P;
+            for (int i = threadIdx.x - 128; i < n; i += 128) dst[i] = sS[i];
         }
         tc_fence_before();
         __syncthreads();
+    }
+    if (warp == 0) {
+        tc_fence_after();
+        tc_dealloc(tmem_base, 128u);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Software-pipelined eval-mode FC stack (P <= 40: one K chunk).  Same arithmetic, operand order and reduction
+// order as fc1_tc_kernel<true>; only the schedule differs.  Two TMEM accumulators: while the tensor core works on
+// tile t, the CUDA cores issue the global loads of tile t+1 and run the epilogue of tile t-1.
+// ------------------------------------------------------------------------------------------------
+constexpr int FT_NIT = (FT_ROWS / 8) * FT_KC / (FT_THREADS / 32);      // 20 core matrices per warp
+
+__device__ __forceinline__ void tile_load(float (&xv)[FT_NIT], const float *__restrict__ src, size_t row_stride, int rows, int kend)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int rl = lane >> 2, kl = lane & 3;
+#pragma unroll
+    for (int i = 0; i < FT_NIT; ++i) {
+        const int cm = warp + (FT_THREADS / 32) * i;
+        const int rg = cm / FT_KC, kc = cm - rg * FT_KC;
+        const int r = rg * 8 + rl, k = kc * 4 + kl;
+        xv[i] = (r < rows && k < kend) ? __ldg(src + (size_t)r * row_stride + k) : 0.f;
+    }
+}
+
+__device__ __forceinline__ void tile_store(const float (&xv)[FT_NIT], unsigned char *hi, unsigned char *lo)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int i = 0; i < FT_NIT; ++i) {
+        const int cm = warp + (FT_THREADS / 32) * i;
+        const float x = xv[i];
+        const float xh = __uint_as_float(__float_as_uint(x) & 0xFFFFE000u);
+        const uint32_t off = (uint32_t)cm * 128 + lane * 4;
+        *reinterpret_cast<float *>(hi + off) = xh;
+        *reinterpret_cast<float *>(lo + off) = x - xh;
+    }
+}
+
+__global__ void __launch_bounds__(FT_THREADS, 2) fc1_tc_eval_pipe_kernel(const FcTcArgs a)
+{
+    extern __shared__ __align__(128) unsigned char smem[];
+    __shared__ __align__(8) uint64_t bar;
+    __shared__ uint32_t tmem_base_s;
+    __shared__ __align__(16) float4 cf[2][128];     // per unit parity: {BN-2 scale, BN-2 shift (+bias), W2, -}
+    __shared__ float post[2][4];                    // per unit parity: b2, rm3, BN-3 scale, be3
+    __shared__ float red[2][128];
+
+    unsigned char *sWh = smem, *sWl = sWh + FT_TILE_BYTES, *sAh = sWl + FT_TILE_BYTES, *sAl = sAh + FT_TILE_BYTES;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    if (threadIdx.x == 0) {
+        mbar_init(&bar, 1);
+        mbar_fence_init();
+    }
+    if (warp == 0) tc_alloc(&tmem_base_s, 256u);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_base_s;
+    const uint32_t idesc = tc_idesc(2u, 128, FT_NEVAL);
+    uint32_t parity = 0;
+
+    const long long total = (long long)a.U * a.nchunk;
+    const long long t_begin = total * blockIdx.x / gridDim.x, t_end = total * (blockIdx.x + 1) / gridDim.x;
+    const size_t row_stride = (size_t)a.U * a.P;
+    float xv[FT_NIT];
+    int cur_u = -1, sel = 0;
+    int p_u = 0, p_rows = 0, p_sel = 0;
+    long long p_b0 = 0;
+    if (t_begin < t_end) {
+        const int u = (int)(t_begin / a.nchunk), chunk = (int)(t_begin - (long long)u * a.nchunk);
+        const long long b0 = (long long)chunk * FT_ROWS;
+        tile_load(xv, a.pooled + ((size_t)b0 * a.U + u) * a.P, row_stride, (int)min((long long)FT_ROWS, a.B - b0), a.P);
+    }
+    int it = 0;
+    for (long long tile = t_begin; tile <= t_end && t_begin < t_end; ++tile, ++it) {
+        const bool have = tile < t_end;
+        if (it > 0) {        // the MMAs of the previous tile have retired: its accumulator is ready, the operand tiles are free
+            mbar_wait(&bar, parity);
+            parity ^= 1;
+            tc_fence_after();
+        }
+        int u = 0, rows = 0;
+        long long b0 = 0;
+        if (have) {
+            u = (int)(tile / a.nchunk);
+            const int chunk = (int)(tile - (long long)u * a.nchunk);
+            b0 = (long long)chunk * FT_ROWS;
+            rows = (int)min((long long)FT_ROWS, a.B - b0);
+            if (u != cur_u) {
+                sel ^= 1;
+                if (threadIdx.x < 128) {
+                    const int j = threadIdx.x, ch = u * H + j;
+                    const bool v = j < H;
+                    const float sc = v ? a.g2[ch] / sqrtf(a.rv2[ch] + a.eps) : 0.f;
+                    cf[sel][j] = make_float4(sc, v ? (a.b1[ch] - a.rm2[ch]) * sc + a.be2[ch] : 0.f, v ? a.W2[ch] : 0.f, 0.f);
+                }
+                if (threadIdx.x == 128) {
+                    post[sel][0] = a.b2[u];
+                    post[sel][1] = a.rm3[u];
+                    post[sel][2] = a.g3[u] / sqrtf(a.rv3[u] + a.eps);
+                    post[sel][3] = a.be3[u];
+                }
+                fill_tile(sWh, sWl, a.W1 + (size_t)u * H * a.P, (size_t)a.P, H, 0, a.P);
+                cur_u = u;
+            }
+            tile_store(xv, sAh, sAl);
+            fence_proxy_async();
+        }
+        tc_fence_before();
+        __syncthreads();
+        if (have && threadIdx.x == 0) {
+            tc_fence_after();
+            const uint32_t acc = tmem_base + (uint32_t)(it & 1) * 128u;
+            const uint32_t wh = smem_u32(sWh), wl = smem_u32(sWl), ah = smem_u32(sAh), al = smem_u32(sAl);
+            const uint32_t lbo = 128, sbo = FT_KC * 128;
+#pragma unroll
+            for (int ks = 0; ks < FT_KCH / 8; ++ks) {
+                const uint32_t o = ks * 256;
+                const uint64_t dWh = make_smem_desc(wh + o, lbo, sbo), dWl = make_smem_desc(wl + o, lbo, sbo);
+                const uint64_t dAh = make_smem_desc(ah + o, lbo, sbo), dAl = make_smem_desc(al + o, lbo, sbo);
+                tc_mma_tf32(acc, dAh, dWh, idesc, ks > 0 ? 1u : 0u);
+                tc_mma_tf32(acc, dAl, dWh, idesc, 1u);
+                tc_mma_tf32(acc, dAh, dWl, idesc, 1u);
+            }
+            tc_commit(&bar);
+        }
+        if (tile + 1 < t_end) {      // global loads of the next tile fly during this tile's MMAs and the epilogue below
+            const int un = (int)((tile + 1) / a.nchunk), chunk = (int)((tile + 1) - (long long)un * a.nchunk);
+            const long long bn = (long long)chunk * FT_ROWS;
+            tile_load(xv, a.pooled + ((size_t)bn * a.U + un) * a.P, row_stride, (int)min((long long)FT_ROWS, a.B - bn), a.P);
+        }
+        if (it > 0) {
+            // ---------------- epilogue of the previous tile ----------------
+            const int q = warp & 3, half = warp >> 2;
+            const int row = 32 * q + lane;
+            const uint32_t taddr = tmem_base + (uint32_t)((it - 1) & 1) * 128u + ((uint32_t)(32 * q) << 16);
+            const float4 *c = cf[p_sel];
+            float dot = 0.f;
+            if (half == 0) {
+                uint32_t r[64];
+                tc_ld16_nowait(taddr, r);
+                tc_ld16_nowait(taddr + 16, r + 16);
+                tc_ld16_nowait(taddr + 32, r + 32);
+                tc_ld16_nowait(taddr + 48, r + 48);
+                tc_wait_ld();
+#pragma unroll
+                for (int i = 0; i < 64; ++i) {
+                    const float4 k = c[i];
+                    dot = fmaf(fmaxf(fmaf(__uint_as_float(r[i]), k.x, k.y), 0.f), k.z, dot);
+                }
+            } else {
+                uint32_t r[48];
+                tc_ld16_nowait(taddr + 64, r);
+                tc_ld16_nowait(taddr + 80, r + 16);
+                tc_ld16_nowait(taddr + 96, r + 32);
+                tc_wait_ld();
+#pragma unroll
+                for (int i = 0; i < 48; ++i) {
+                    const float4 k = c[64 + i];
+                    dot = fmaf(fmaxf(fmaf(__uint_as_float(r[i]), k.x, k.y), 0.f), k.z, dot);
+                }
+            }
+            red[half][row] = dot;
+            tc_fence_before();
+            __syncthreads();
+            if (threadIdx.x < p_rows) {
+                const int b = threadIdx.x;
+                const float h2 = (red[0][b] + red[1][b]) + post[p_sel][0];
+                a.unit_out[(p_b0 + b) * a.U + p_u] = fmaxf((h2 - post[p_sel][1]) * post[p_sel][2] + post[p_sel][3], 0.f);
+            }
+        }
+        p_u = u; p_rows = rows; p_sel = sel; p_b0 = b0;
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) {
+        tc_fence_after();
+        tc_dealloc(tmem_base, 256u);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Final linear layer (networks.py:118,160-162: out = unit_out @ Wf^T + bias) on the tensor cores, 3-term tf32 split.
+//   D[b][c] = sum_u x[b][u] * Wf[c][u]      M = 128 sequences, N = classes padded to 16 (<= 128), K = U in chunks of 40
+// Both operands are K-major as they lie in memory.  One tile of 128 sequences per CTA; the global loads of K chunk
+// k+1 are in flight while the MMAs of chunk k run.  The output tile is staged in shared memory and written coalesced.
+// ------------------------------------------------------------------------------------------------
+struct LinTcArgs {
+    const float *x, *W, *bias;
+    float *out;
+    long long B;
+    int U, C, npad;
+};
+
+__global__ void __launch_bounds__(FT_THREADS, 1) linear_tc_kernel(const LinTcArgs a)
+{
+    extern __shared__ __align__(128) unsigned char smem[];
+    __shared__ __align__(8) uint64_t bar;
+    __shared__ uint32_t tmem_base_s;
+    unsigned char *sWh = smem, *sWl = sWh + FT_TILE_BYTES, *sAh = sWl + FT_TILE_BYTES, *sAl = sAh + FT_TILE_BYTES;
+    float *sOut = reinterpret_cast<float *>(smem);       // reused after the last MMA: [128][C+1] floats (<= 66 KB)
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int nkch = (a.U + FT_KCH - 1) / FT_KCH;
+
+    if (threadIdx.x == 0) {
+        mbar_init(&bar, 1);
+        mbar_fence_init();
+    }
+    if (warp == 0) tc_alloc(&tmem_base_s, 128u);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_base_s;
+    const uint32_t idesc = tc_idesc(2u, 128, a.npad);
+    uint32_t parity = 0;
+
+    const long long b0 = (long long)blockIdx.x * FT_ROWS;
+    const int rows = (int)min((long long)FT_ROWS, a.B - b0);
+    const float *xsrc = a.x + (size_t)b0 * a.U;
+    float xv[FT_NIT], wv[FT_NIT];
+    tile_load(xv, xsrc, (size_t)a.U, rows, a.U);
+    tile_load(wv, a.W, (size_t)a.U, a.C, a.U);
+    for (int kc = 0; kc < nkch; ++kc) {
+        if (kc > 0) {        // MMAs of the previous chunk have retired: operand tiles are free again
+            mbar_wait(&bar, parity);
+            parity ^= 1;
+            tc_fence_after();
+        }
+        tile_store(xv, sAh, sAl);
+        tile_store(wv, sWh, sWl);
+        fence_proxy_async();
+        tc_fence_before();
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            tc_fence_after();
+            const uint32_t wh = smem_u32(sWh), wl = smem_u32(sWl), ah = smem_u32(sAh), al = smem_u32(sAl);
+            const uint32_t lbo = 128, sbo = FT_KC * 128;
+#pragma unroll
+            for (int ks = 0; ks < FT_KCH / 8; ++ks) {
+                const uint32_t o = ks * 256;
+                const uint64_t dWh = make_smem_desc(wh + o, lbo, sbo), dWl = make_smem_desc(wl + o, lbo, sbo);
+                const uint64_t dAh = make_smem_desc(ah + o, lbo, sbo), dAl = make_smem_desc(al + o, lbo, sbo);
+                tc_mma_tf32(tmem_base, dAh, dWh, idesc, (kc > 0 || ks > 0) ? 1u : 0u);
+                tc_mma_tf32(tmem_base, dAl, dWh, idesc, 1u);
+                tc_mma_tf32(tmem_base, dAh, dWl, idesc, 1u);
+            }
+            tc_commit(&bar);
+        }
+        if (kc + 1 < nkch) {
+            const int k0 = (kc + 1) * FT_KCH;
+            tile_load(xv, xsrc + k0, (size_t)a.U, rows, a.U - k0);
+            tile_load(wv, a.W + k0, (size_t)a.U, a.C, a.U - k0);
+        }
+    }
+    mbar_wait(&bar, parity);
+    tc_fence_after();
+
+    // ---------------- epilogue: TMEM -> shared memory (+bias) -> coalesced global stores ----------------
+    const int q = warp & 3, half = warp >> 2;
+    const int row = 32 * q + lane;
+    const uint32_t taddr = tmem_base + ((uint32_t)(32 * q) << 16);
+    const int ld = a.C + 1;
+    for (int c0 = 64 * half; c0 < min(a.npad, 64 * half + 64); c0 += 16) {
+        uint32_t r[16];
+        tc_ld16_nowait(taddr + c0, r);
+        tc_wait_ld();
+#pragma unroll
+        for (int i = 0; i < 16; ++i)
+            if (c0 + i < a.C) sOut[row * ld + c0 + i] = __uint_as_float(r[i]) + __ldg(a.bias + c0 + i);
+    }
+    tc_fence_before();
+    __syncthreads();
+    float *dst = a.out + (size_t)b0 * a.C;
+    const int n = rows * a.C;
+    for (int i = threadIdx.x; i < n; i += FT_THREADS) {
+        const int r = i / a.C, c = i - r * a.C;
+        dst[i] = sOut[r * ld + c];
     }
     if (warp == 0) {
         tc_fence_after();
@@ -502,7 +807,11 @@ int launch_fc1_tc(bool eval, const FcTcArgs &a, cudaStream_t stream)
     int grid = 2 * xb_num_sms();
     if (total < grid) grid = (int)total;
     cudaError_t e;
-    if (eval) {
+    static const bool no_pipe = [] { const char *v = getenv("XB_FC_PIPE"); return v && v[0] == '0'; }();
+    if (eval && a.P <= FT_KCH && !no_pipe) {
+        e = cudaFuncSetAttribute(fc1_tc_eval_pipe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e == cudaSuccess) fc1_tc_eval_pipe_kernel<<<grid, FT_THREADS, smem, stream>>>(a);
+    } else if (eval) {
         e = cudaFuncSetAttribute(fc1_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e == cudaSuccess) fc1_tc_kernel<true><<<grid, FT_THREADS, smem, stream>>>(a);
     } else {
@@ -539,6 +848,22 @@ int xb_fc_stack_fwd_eval_tc(const float *pooled, long long B, int U, int P, cons
     return launch_fc1_tc(true, a, stream);
 }
 
+// returns XB_ERR_UNSUPPORTED (without setting an error) when the class count does not fit one N tile
+int xb_linear_tc(const float *x, long long B, int U, int C, const float *W, const float *bias, float *out, cudaStream_t stream)
+{
+    if (C > 128) return XB_ERR_UNSUPPORTED;
+    LinTcArgs a{};
+    a.x = x; a.W = W; a.bias = bias; a.out = out; a.B = B; a.U = U; a.C = C; a.npad = (C + 15) / 16 * 16;
+    const size_t smem = 4 * (size_t)FT_TILE_BYTES;
+    cudaError_t e = cudaFuncSetAttribute(linear_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) {
+        xb_set_error("linear_tc: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+        return XB_ERR_CUDA;
+    }
+    linear_tc_kernel<<<(unsigned)((B + FT_ROWS - 1) / FT_ROWS), FT_THREADS, smem, stream>>>(a);
+    return xb_check_launch("linear_tc");
+}
+
 bool xb_fc_tc_enabled()
 {
     const char *e = getenv("XB_FC_TC");
@@ -556,7 +881,7 @@ int xb_bwd_fc1_tc(const float *h1, const float *gh2, const float *pooled, long l
     a.h1 = h1; a.gh2 = gh2; a.pooled = pooled; a.B = B; a.U = U; a.P = P; a.nchunk = (int)((B + FT_ROWS - 1) / FT_ROWS);
     a.g2 = g2; a.be2 = be2; a.mean2 = mean2; a.invstd2 = invstd2; a.W1 = W1; a.W2 = W2; a.pdrop = pdrop; a.seed0 = seed; a.seed_dev = seed_dev; a.dropmask = dropmask;
     a.pb2 = pb2; a.gpool = gpool; a.dW1p = dW1p; a.dW2 = dW2; a.db1 = db1; a.db2 = db2; a.dg2 = dg2; a.dbe2 = dbe2;
-    const size_t smem = 2 * (size_t)(BT_GT_BYTES + BT_A_BYTES + BT_W_BYTES);
+    const size_t smem = 2 * (size_t)BT_GT_BYTES + BT_H_BYTES + BT_S_BYTES + 2 * (size_t)BT_W_BYTES;
     const long long total = (long long)U * a.nchunk;
     int grid = xb_num_sms();
     if (total < grid) grid = (int)total;

@@ -168,45 +168,96 @@ __global__ void __launch_bounds__(BW_WARPS * 32) conv_bwd_sparse_kernel(
     const long long e0 = per * blockIdx.y, e1 = min(n, e0 + per);
     float dbeta = 0.f, dgamma = 0.f;
     float *mine = my + lane;
-    for (long long e = e0 + warp * 32 + lane; e < e1; e += BW_WARPS * 32) {
-        const int b = (int)e / P;                    // host wrapper guarantees B*P < 2^31
-        const int p = (int)e - b * P;
-        const size_t o = ((size_t)b * U + u) * P + p;   // (B,U,P) layout
-        const float gz = gpool[o] * pooled[o];
-        const float xh = xhat[o];
-        const int s = p * XB_POOL + idx[o];
+    // Two-stage software pipeline over this lane's entries e = first, first + 128, ...:
+    //   stage A (entry i+2): gradient, pooled value, xhat, argmax offset      stage B (entry i+1): the code / N-mask words
+    //   at the argmax position (their address depends on stage A)             stage C (entry i): shared-memory updates
+    // Entries past the end are clamped to the last one and weighted with zero, so every lane runs the same trip count.
+    constexpr int STRIDE = BW_WARPS * 32;
+    const int db = STRIDE / P, dp = STRIDE - db * P;
+    const long long first = e0 + warp * 32 + lane, last = e1 - 1;
+    const int niter = e1 > e0 ? (int)((e1 - e0 + STRIDE - 1) / STRIDE) : 0;
+    struct StA { float gp, po, xh; int s, b; };
+    struct StB { float gz, xh; uint32_t w0, w1, w2, m0, m1; int s; };
+    long long ea = first;                      // entry index of the next stage-A fetch
+    int ab, ap;                                // its (b, p), kept incrementally (host wrapper guarantees B*P < 2^31)
+    {
+        const long long ec = min(ea, last);
+        ab = (int)(ec / P);
+        ap = (int)(ec - (long long)ab * P);
+    }
+    auto fetchA = [&]() {
+        StA r;
+        const bool valid = ea <= last;
+        if (!valid) { ab = (int)(last / P); ap = (int)(last - (long long)ab * P); }
+        const size_t o = ((size_t)ab * U + u) * P + ap;   // (B,U,P) layout
+        r.gp = valid ? gpool[o] : 0.f;
+        r.po = valid ? pooled[o] : 0.f;
+        r.xh = xhat[o];
+        r.s = ap * XB_POOL + idx[o];
+        r.b = ab;
+        ea += STRIDE;
+        ab += db; ap += dp;
+        if (ap >= P) { ap -= P; ++ab; }
+        return r;
+    };
+    auto fetchB = [&](const StA &x) {
+        StB r;
+        r.gz = x.gp * x.po;
+        r.xh = x.xh;
+        r.s = x.s;
+        const uint32_t *cw = codes + (size_t)x.b * wc;
+        const uint32_t *mw = nmask + (size_t)x.b * wm;
+        const int wi = x.s >> 4, mi = x.s >> 5;
+        r.w0 = cw[wi];
+        r.w1 = wi + 1 < wc ? cw[wi + 1] : 0u;
+        r.w2 = wi + 2 < wc ? cw[wi + 2] : 0u;
+        r.m0 = mw[mi];
+        r.m1 = mi + 1 < wm ? mw[mi + 1] : 0u;
+        return r;
+    };
+    StA sa{};
+    StB sb{};
+    if (niter > 0) {
+        sa = fetchA();
+        sb = fetchB(sa);
+        sa = fetchA();
+    }
+    for (int it = 0; it < niter; ++it) {
+        const StB c = sb;
+        if (it + 1 < niter) {
+            sb = fetchB(sa);
+            sa = fetchA();
+        }
+        const float gz = c.gz;
         dbeta += gz;
-        dgamma = fmaf(gz, xh, dgamma);
-        const uint32_t *cw = codes + (size_t)b * wc;
-        const uint32_t *mw = nmask + (size_t)b * wm;
-        const int wi = s >> 4, sh = 2 * (s & 15);
-        const uint32_t w0 = cw[wi], w1 = wi + 1 < wc ? cw[wi + 1] : 0u, w2 = wi + 2 < wc ? cw[wi + 2] : 0u;
-        const uint32_t A0 = __funnelshift_r(w0, w1, sh), A1 = __funnelshift_r(w1, w2, sh);
-        const int mi = s >> 5;
-        const uint32_t m0 = mw[mi], m1 = mi + 1 < wm ? mw[mi + 1] : 0u;
-        const uint32_t MW = __funnelshift_r(m0, m1, s & 31) & (F >= 32 ? 0xFFFFFFFFu : ((1u << F) - 1u));
+        dgamma = fmaf(gz, c.xh, dgamma);
+        const int sh = 2 * (c.s & 15);
+        const uint32_t A0 = __funnelshift_r(c.w0, c.w1, sh), A1 = __funnelshift_r(c.w1, c.w2, sh);
+        const uint32_t MW = __funnelshift_r(c.m0, c.m1, c.s & 31) & (F >= 32 ? 0xFFFFFFFFu : ((1u << F) - 1u));
         if (FT > 0) {
-            // offsets of the 19 (k, code) cells; k*128 is a compile-time part of the address
+            // byte offsets of the F (k, code) cells; k*512 is a compile-time part of the address
             float v[FT > 0 ? FT : 1];
             uint32_t off[FT > 0 ? FT : 1];
+            char *base = reinterpret_cast<char *>(mine);
 #pragma unroll
             for (int k = 0; k < FT; ++k) {
-                const uint32_t c = ((k < 16 ? A0 : A1) >> ((2 * k) & 31)) & 3u;
-                off[k] = k * 128 + c * 32;
+                const uint32_t A = k < 16 ? A0 : A1;
+                const int shr = ((2 * k) & 31) - 7;             // code << 7  =  code * 32 floats * 4 bytes
+                off[k] = (shr >= 0 ? (A >> shr) : (A << -shr)) & 0x180u;
             }
 #pragma unroll
-            for (int k = 0; k < FT; ++k) v[k] = mine[off[k]];
+            for (int k = 0; k < FT; ++k) v[k] = *reinterpret_cast<float *>(base + k * 512 + off[k]);
             if (MW == 0u) {
 #pragma unroll
-                for (int k = 0; k < FT; ++k) mine[off[k]] = v[k] + gz;
+                for (int k = 0; k < FT; ++k) *reinterpret_cast<float *>(base + k * 512 + off[k]) = v[k] + gz;
             } else {
 #pragma unroll
-                for (int k = 0; k < FT; ++k) mine[off[k]] = v[k] + (((MW >> k) & 1u) ? 0.0f : gz);
+                for (int k = 0; k < FT; ++k) *reinterpret_cast<float *>(base + k * 512 + off[k]) = v[k] + (((MW >> k) & 1u) ? 0.0f : gz);
             }
         } else {
             for (int k = 0; k < F; ++k) {
-                const uint32_t c = ((k < 16 ? A0 : A1) >> ((2 * k) & 31)) & 3u;
-                if (!((MW >> k) & 1u)) mine[k * 128 + c * 32] += gz;
+                const uint32_t cc = ((k < 16 ? A0 : A1) >> ((2 * k) & 31)) & 3u;
+                if (!((MW >> k) & 1u)) mine[k * 128 + cc * 32] += gz;
             }
         }
     }
