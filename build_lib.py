@@ -44,7 +44,8 @@ def build(force=False, verbose=False):
     for src in sources():
         obj = src[:-3] + ".o"
         objs.append(obj)
-        cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-I", INCLUDE, "-c", src, "-o", obj]
+        extra = os.environ.get("XB_NVCC_EXTRA", "").split()      # e.g. -DXB_PHASE_CLOCKS for the phase-clock experiments
+        cmd = [nvcc] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-I", INCLUDE, "-c", src, "-o", obj]
         procs.append((cmd, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
     failed = False
     for cmd, p in procs:

@@ -201,7 +201,7 @@ __global__ void __launch_bounds__(TC_THREADS + 32, 1) conv_tc_kernel(const TcArg
     tc_fence_after();
     const uint32_t tmem_base = tmem_base_s;
 
-    if (warp == TC_THREADS / 32) {
+    if (tc_warp_uniform() == TC_THREADS / 32) {      // warp-uniform role branch: MMA operands stay in uniform registers
         // =========================== producer warp ===========================
         const uint32_t idesc = (1u << 4) | ((uint32_t)(TC_N >> 3) << 17) | ((uint32_t)(TC_M >> 4) << 24);   // f16xf16->f32, M128 N240
         uint32_t a_parity = 0;
@@ -277,15 +277,16 @@ __global__ void __launch_bounds__(TC_THREADS + 32, 1) conv_tc_kernel(const TcArg
                 const int buf = (int)(n & 1);
                 const uint32_t use = (uint32_t)(n >> 1);   // how often this accumulator has been used before
                 mbar_wait(&tmem_empty[buf], (use & 1) ^ 1);          // drained by the epilogue warps
-                if (lane == 0) {
+                // descriptors of K step 0, computed by the whole warp; a K step advances A by 256 bytes and V by 64
+                const uint32_t d = tmem_base + (uint32_t)buf * 256u;
+                const uint32_t a_hi = smem_u32(sA) + (uint32_t)m * 2 * a_bytes;
+                const uint64_t dA_hi = make_smem_desc(a_hi, 128, (uint32_t)KC * 128), dA_lo = make_smem_desc(a_hi + a_bytes, 128, (uint32_t)KC * 128);
+                const uint64_t dV = make_smem_desc(smem_u32(V), 32, 128);
+                if (tc_elect_one()) {
                     tc_fence_after();
-                    const uint32_t d = tmem_base + (uint32_t)buf * 256u;
-                    const uint32_t a_hi = smem_u32(sA) + (uint32_t)m * 2 * a_bytes, a_lo = a_hi + a_bytes, bt = smem_u32(V);
-                    const uint32_t a_lbo = 128, a_sbo = (uint32_t)KC * 128;
                     for (int ks = 0; ks < ((a.dbg & 8) ? 0 : KS); ++ks) {
-                        const uint64_t bd = make_smem_desc(bt + ks * 64, 32, 128);
-                        tc_mma_f16(d, make_smem_desc(a_hi + ks * 256, a_lbo, a_sbo), bd, idesc, ks > 0 ? 1u : 0u);
-                        tc_mma_f16(d, make_smem_desc(a_lo + ks * 256, a_lbo, a_sbo), bd, idesc, 1u);
+                        tc_mma_f16(d, dA_hi + ks * 16, dV + ks * 4, idesc, ks > 0 ? 1u : 0u);
+                        tc_mma_f16(d, dA_lo + ks * 16, dV + ks * 4, idesc, 1u);
                     }
                     tc_commit(&tmem_full[buf]);
                 }

@@ -90,6 +90,10 @@ __global__ void __launch_bounds__(FT_THREADS, 2) fc1_tc_kernel(const FcTcArgs a)
     const uint32_t tmem_base = tmem_base_s;
     const uint32_t idesc = tc_idesc(2u, 128, EVAL ? FT_NEVAL : 128);
     uint32_t parity = 0;
+    // operand descriptors of K step 0, computed once in warp-uniform code (see tc_elect_one)
+    const int warp_u = tc_warp_uniform();
+    const uint64_t dW_hi = make_smem_desc(smem_u32(sWh), 128, FT_KC * 128), dW_lo = make_smem_desc(smem_u32(sWl), 128, FT_KC * 128);
+    const uint64_t dA_hi = make_smem_desc(smem_u32(sAh), 128, FT_KC * 128), dA_lo = make_smem_desc(smem_u32(sAl), 128, FT_KC * 128);
 
     const long long total = (long long)a.U * a.nchunk;
     int cur_u = -1;
@@ -121,14 +125,12 @@ __global__ void __launch_bounds__(FT_THREADS, 2) fc1_tc_kernel(const FcTcArgs a)
             fence_proxy_async();
             tc_fence_before();
             __syncthreads();
-            if (threadIdx.x == 0) {
+            if (warp_u == 0 && tc_elect_one()) {
                 tc_fence_after();
-                const uint32_t wh = smem_u32(sWh), wl = smem_u32(sWl), ah = smem_u32(sAh), al = smem_u32(sAl);
-                const uint32_t lbo = 128, sbo = FT_KC * 128;
+#pragma unroll
                 for (int ks = 0; ks < FT_KCH / 8; ++ks) {
-                    const uint32_t o = ks * 256;      // two 16-byte core columns per K = 8 step
-                    const uint64_t dWh = make_smem_desc(wh + o, lbo, sbo), dWl = make_smem_desc(wl + o, lbo, sbo);
-                    const uint64_t dAh = make_smem_desc(ah + o, lbo, sbo), dAl = make_smem_desc(al + o, lbo, sbo);
+                    // two 16-byte core columns (256 bytes = 16 in the descriptor's address field) per K = 8 step
+                    const uint64_t dWh = dW_hi + ks * 16, dWl = dW_lo + ks * 16, dAh = dA_hi + ks * 16, dAl = dA_lo + ks * 16;
                     const uint32_t acc0 = (kc > 0 || ks > 0) ? 1u : 0u;
                     if (EVAL) {      // M = sequences (pooled tile is the A operand), N = hidden channels
                         tc_mma_tf32(tmem_base, dAh, dWh, idesc, acc0);
@@ -243,7 +245,8 @@ constexpr int BT_H_BYTES = FT_ROWS * H * 4;         // staged h1 tile       51,2
 constexpr int BT_S_BYTES = FT_ROWS * BT_P * 4;      // output staging       24,576
 constexpr int BT_W_BYTES = BT_P * BT_J * 4;         // W1t [48 p][104 j]   19,968
 constexpr int BT_A_BYTES = BT_P * FT_ROWS * 4;      // At  [48 p][128 b]   24,576
-constexpr int BT_NG = (FT_ROWS / 8) * (BT_J / 4) / (FT_THREADS / 32);   // core matrices of G per warp = 52
+constexpr int BT_KT = 7;                  // column groups (of 26) per warp in the G build: kc = warp%4 + 4t
+constexpr int BT_RG = 8;                  // row groups (of 16) per warp in the G build: rg = 8*(warp/4) + g
 
 struct FcBwdArgs {
     const float *h1, *gh2, *pooled;
@@ -267,7 +270,20 @@ __device__ __forceinline__ void st_split(unsigned char *hi, unsigned char *lo, u
     *reinterpret_cast<float *>(lo + off) = x - xh;
 }
 
-__global__ void __launch_bounds__(FT_THREADS, 1) bwd_fc1_tc_kernel(const FcBwdArgs a)
+// Phase clocks (experiments only, compiled in with -DXB_PHASE_CLOCKS): thread 0 of CTA 0 records clock64() at the
+// phase boundaries of its first tiles; tools/phase_clocks.py prints the per-phase cycle counts.
+#ifdef XB_PHASE_CLOCKS
+__device__ long long g_phase_clk[32 * 16];
+#define XB_PHASE(i) do { if (blockIdx.x == 0 && threadIdx.x == 0 && tile - t_begin < 32) g_phase_clk[(tile - t_begin) * 16 + (i)] = clock64(); } while (0)
+#else
+#define XB_PHASE(i) do { } while (0)
+#endif
+
+// 8 worker warps (builds, fills, drains) + 1 issue warp: the tcgen05.mma issue of one product takes about as long as the
+// product itself (the issuing thread blocks on the MMA queue), so it runs beside the workers' next fill / drain.
+constexpr int BT_THREADS = FT_THREADS + 32;
+
+__global__ void __launch_bounds__(BT_THREADS, 1) bwd_fc1_tc_kernel(const FcBwdArgs a)
 {
     extern __shared__ __align__(128) unsigned char smem[];
     __shared__ __align__(8) uint64_t bar;
@@ -288,6 +304,7 @@ __global__ void __launch_bounds__(FT_THREADS, 1) bwd_fc1_tc_kernel(const FcBwdAr
     __shared__ __align__(8) uint64_t bar_h;
     __shared__ float gh2s[FT_ROWS];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const bool worker = warp < FT_THREADS / 32;
     const unsigned long long seed = a.seed0 + (a.seed_dev ? *a.seed_dev * 0xD1B54A32D192ED03ull : 0ull);
     const unsigned thresh = a.pdrop > 0.f ? (unsigned)min(4294967295.0, (double)a.pdrop * 4294967296.0) : 0u;
     const float keep_scale = a.pdrop > 0.f ? 1.0f / (1.0f - a.pdrop) : 1.0f;
@@ -304,6 +321,12 @@ __global__ void __launch_bounds__(FT_THREADS, 1) bwd_fc1_tc_kernel(const FcBwdAr
     const uint32_t tmem_base = tmem_base_s;
     const uint32_t idesc = tc_idesc(2u, 128, BT_P);
     uint32_t parity = 0, h_parity = 0;
+    // operand descriptors of K step 0, computed once in warp-uniform code (see tc_elect_one)
+    const int warp_u = tc_warp_uniform();
+    const uint64_t dG_hi = make_smem_desc(smem_u32(sR), 128, BT_G_SBO), dG_lo = make_smem_desc(smem_u32(sR) + BT_G_BYTES, 128, BT_G_SBO);
+    const uint64_t dW_hi = make_smem_desc(smem_u32(sWh), 128, BT_G_SBO), dW_lo = make_smem_desc(smem_u32(sWl), 128, BT_G_SBO);
+    const uint64_t dT_hi = make_smem_desc(smem_u32(sR), 128, BT_B_SBO), dT_lo = make_smem_desc(smem_u32(sR) + BT_GT_BYTES, 128, BT_B_SBO);
+    const uint64_t dA_hi = make_smem_desc(smem_u32(sAh), 128, BT_B_SBO), dA_lo = make_smem_desc(smem_u32(sAl), 128, BT_B_SBO);
 
     const long long total = (long long)a.U * a.nchunk;
     const long long t_begin = total * blockIdx.x / gridDim.x, t_end = total * (blockIdx.x + 1) / gridDim.x;
@@ -312,6 +335,7 @@ __global__ void __launch_bounds__(FT_THREADS, 1) bwd_fc1_tc_kernel(const FcBwdAr
         const int u = (int)(tile / a.nchunk), chunk = (int)(tile - (long long)u * a.nchunk);
         const long long b0 = (long long)chunk * FT_ROWS;
         const int rows = (int)min((long long)FT_ROWS, a.B - b0);
+        XB_PHASE(0);
         if (threadIdx.x == 0 && tile == t_begin) {      // later tiles: issued by the previous iteration (see below)
             mbar_arrive_expect_tx(&bar_h, (uint32_t)rows * H * 4);
             tma_bulk_g2s(sH, a.h1 + ((size_t)u * a.B + b0) * H, (uint32_t)rows * H * 4, &bar_h);
@@ -320,7 +344,16 @@ __global__ void __launch_bounds__(FT_THREADS, 1) bwd_fc1_tc_kernel(const FcBwdAr
             const int r = threadIdx.x;
             gh2s[r] = r < rows ? a.gh2[(size_t)u * a.B + b0 + r] : 0.f;
             uint4 mw = make_uint4(~0u, ~0u, ~0u, ~0u);
-            if (a.pdrop > 0.f && a.dropmask && r < rows) mw = *reinterpret_cast<const uint4 *>(a.dropmask + ((size_t)u * a.B + b0 + r) * 4);
+            if (a.pdrop > 0.f && r < rows) {
+                if (a.dropmask) {
+                    mw = *reinterpret_cast<const uint4 *>(a.dropmask + ((size_t)u * a.B + b0 + r) * 4);
+                } else {          // no saved keep bits: regenerate them from the counter hash (slow path)
+                    uint32_t w[4] = {0u, 0u, 0u, 0u};
+                    for (int qd = 0; qd < H / 4; ++qd)
+                        w[qd >> 3] |= drop_keep4(seed, ((size_t)u * a.B + b0 + r) * (H / 4) + qd, thresh) << (4 * (qd & 7));
+                    mw = make_uint4(w[0], w[1], w[2], w[3]);
+                }
+            }
             *reinterpret_cast<uint4 *>(&msk[r][0]) = mw;
         }
         if (u != cur_u) {
@@ -353,7 +386,7 @@ __global__ void __launch_bounds__(FT_THREADS, 1) bwd_fc1_tc_kernel(const FcBwdAr
             }
             // W1[u] transposed: rows p, K = j contiguous (B operand of D1); one warp store = one core matrix.
             // All loads are issued before the first store so that only one global latency is exposed.
-            {
+            if (worker) {
                 constexpr int NCM = (BT_P / 8) * (BT_J / 4), NIT = (NCM + FT_THREADS / 32 - 1) / (FT_THREADS / 32);
                 float xv[NIT];
                 const float *wsrc = a.W1 + (size_t)u * H * a.P;
@@ -373,46 +406,74 @@ __global__ void __launch_bounds__(FT_THREADS, 1) bwd_fc1_tc_kernel(const FcBwdAr
             cur_u = u;
         }
         __syncthreads();          // coefficient arrays and gh2 tile ready for the G build
+        XB_PHASE(1);
         mbar_wait(&bar_h, h_parity);
         h_parity ^= 1;
-        // G values of this thread: core matrix cm = warp + 8*i  ->  (row r = 8*rg + lane/4, channel j = 4*kc + lane%4)
-        float gv[BT_NG];
+        XB_PHASE(2);
+        // G values of this thread.  Warp w owns the core matrices (row group rg = 8*(w/4) + g, column group kc = w%4 + 4t),
+        // g < 8, t < 7: thread (rl = lane/4, jl = lane%4) sees rows r = 8*rg + rl and only seven channels j = 4*kc + jl,
+        // whose BatchNorm coefficients are read once.  Pass 1 issues every shared-memory read of the h1 tile back to
+        // back; pass 2 does the arithmetic and the operand-tile stores.
+        float gv[BT_KT * BT_RG];
+        const int kq = warp & 3, rg0 = BT_RG * (warp >> 2), rl = lane >> 2, jl = lane & 3;
+        if (worker) {
 #pragma unroll
-        for (int i = 0; i < BT_NG; ++i) {
-            const int cm = warp + (FT_THREADS / 32) * i;
-            const int rg = cm / (BT_J / 4), kc = cm - rg * (BT_J / 4);
-            const int r = rg * 8 + (lane >> 2), j = kc * 4 + (lane & 3);
-            float v = 0.f;
-            if (r < rows && j < H) {
-                const float h = sH[r * H + j];
-                const float zb = fmaf(h, c1s[j], c0s[j]);
-                bool kept = (msk[r][j >> 5] >> (j & 31)) & 1u;
-                if (a.pdrop > 0.f && !a.dropmask) kept = drop_scale(seed, ((size_t)u * a.B + b0 + r) * H + j, thresh, keep_scale) != 0.f;
-                v = fmaf(h, cBs[j], cCs[j]);
-                if (zb > 0.f && kept) v = fmaf(gh2s[r], cAs[j], v);
+            for (int t = 0; t < BT_KT; ++t) {
+                const int kc = kq + 4 * t, j = 4 * kc + jl;
+#pragma unroll
+                for (int g = 0; g < BT_RG; ++g) {
+                    const int r = (rg0 + g) * 8 + rl;
+                    gv[t * BT_RG + g] = (j < H && r < rows) ? sH[r * H + j] : 0.f;
+                }
             }
-            gv[i] = v;
-            st_split(sR, sR + BT_G_BYTES, (uint32_t)cm * 128 + lane * 4, v);      // G, j-contiguous
+            float k1[BT_KT], k0[BT_KT], kA[BT_KT], kB[BT_KT], kC[BT_KT];
+#pragma unroll
+            for (int t = 0; t < BT_KT; ++t) {
+                const int j = 4 * (kq + 4 * t) + jl;      // <= 111: inside the 128-entry arrays, zero beyond channel 99
+                k1[t] = c1s[j]; k0[t] = c0s[j]; kA[t] = cAs[j]; kB[t] = cBs[j]; kC[t] = cCs[j];
+            }
+#pragma unroll
+            for (int g = 0; g < BT_RG; ++g) {
+                const int rg = rg0 + g, r = rg * 8 + rl;
+                const float gh = gh2s[r];
+                const uint4 mw = *reinterpret_cast<const uint4 *>(&msk[r][0]);
+                const uint32_t mws[4] = {mw.x, mw.y, mw.z, mw.w};
+#pragma unroll
+                for (int t = 0; t < BT_KT; ++t) {
+                    const int kc = kq + 4 * t;
+                    if (kc < BT_J / 4) {                       // warp-uniform (t = 6 exists only for w%4 < 2)
+                        const int j = 4 * kc + jl;
+                        const float h = gv[t * BT_RG + g];
+                        const float zb = fmaf(h, k1[t], k0[t]);
+                        const bool kept = (mws[t >> 1] >> (j & 31)) & 1u;    // word j/32 == t/2
+                        float v = fmaf(h, kB[t], kC[t]);
+                        if (zb > 0.f && kept) v = fmaf(gh, kA[t], v);
+                        if (r >= rows) v = 0.f;
+                        gv[t * BT_RG + g] = v;
+                        st_split(sR, sR + BT_G_BYTES, (uint32_t)(rg * (BT_J / 4) + kc) * 128 + lane * 4, v);      // G, j-contiguous
+                    }
+                }
+            }
         }
         fence_proxy_async();
         tc_fence_before();
         __syncthreads();
+        XB_PHASE(3);
         // ---- D1 = G . W1   (TMEM columns 0..47) ----
-        if (threadIdx.x == 0) {
+        if (warp_u == FT_THREADS / 32 && tc_elect_one()) {
             tc_fence_after();
-            const uint32_t gh = smem_u32(sR), gl = gh + BT_G_BYTES, wh = smem_u32(sWh), wl = smem_u32(sWl);
-            for (int ks = 0; ks < BT_J / 8; ++ks) {
-                const uint64_t dGh = make_smem_desc(gh + ks * 256, 128, BT_G_SBO), dGl = make_smem_desc(gl + ks * 256, 128, BT_G_SBO);
-                const uint64_t dWh = make_smem_desc(wh + ks * 256, 128, BT_G_SBO), dWl = make_smem_desc(wl + ks * 256, 128, BT_G_SBO);
-                tc_mma_tf32(tmem_base, dGh, dWh, idesc, ks > 0 ? 1u : 0u);
-                tc_mma_tf32(tmem_base, dGl, dWh, idesc, 1u);
-                tc_mma_tf32(tmem_base, dGh, dWl, idesc, 1u);
+#pragma unroll
+            for (int ks = 0; ks < BT_J / 8; ++ks) {      // + 16 per K step: 256 bytes in the descriptor's address field
+                tc_mma_tf32(tmem_base, dG_hi + ks * 16, dW_hi + ks * 16, idesc, ks > 0 ? 1u : 0u);
+                tc_mma_tf32(tmem_base, dG_lo + ks * 16, dW_hi + ks * 16, idesc, 1u);
+                tc_mma_tf32(tmem_base, dG_hi + ks * 16, dW_lo + ks * 16, idesc, 1u);
             }
             tc_commit(&bar);
         }
+        XB_PHASE(4);
         // while D1 runs: pooled tile transposed, rows p, K = b contiguous (B operand of D2).  It overwrites the h1
         // staging, which every thread has finished reading (barrier above).
-        {
+        if (worker) {
             constexpr int NIT = (BT_P / 8) * (FT_ROWS / 4) / (FT_THREADS / 32);     // 24 core matrices per warp
             float xv[NIT];
             const float *psrc = a.pooled + ((size_t)b0 * a.U + u) * a.P;
@@ -427,58 +488,82 @@ __global__ void __launch_bounds__(FT_THREADS, 1) bwd_fc1_tc_kernel(const FcBwdAr
 #pragma unroll
             for (int i = 0; i < NIT; ++i) st_split(sAh, sAl, (uint32_t)(warp + (FT_THREADS / 32) * i) * 128 + lane * 4, xv[i]);
         }
+        XB_PHASE(5);
         mbar_wait(&bar, parity);
         parity ^= 1;
         tc_fence_after();
+        XB_PHASE(6);
         // ---- phase 2: the same values b-contiguous (Gt[j][b]) over the region the finished MMAs no longer read ----
 #pragma unroll
-        for (int i = 0; i < BT_NG; ++i) {
-            const int cm = warp + (FT_THREADS / 32) * i;
-            const int rg = cm / (BT_J / 4), kc = cm - rg * (BT_J / 4);
-            const int r = rg * 8 + (lane >> 2), j = kc * 4 + (lane & 3);
-            st_split(sR, sR + BT_GT_BYTES, core_off(j, r, BT_B_SBO), gv[i]);
+        for (int t = 0; t < BT_KT; ++t) {
+            const int kc = kq + 4 * t;
+            if (worker && kc < BT_J / 4) {
+#pragma unroll
+                for (int g = 0; g < BT_RG; ++g)
+                    st_split(sR, sR + BT_GT_BYTES, core_off(4 * kc + jl, (rg0 + g) * 8 + rl, BT_B_SBO), gv[t * BT_RG + g]);
+            }
         }
         // rows 104..127 of Gt are never written: they only feed accumulator rows that are not read back
         fence_proxy_async();
         tc_fence_before();
         __syncthreads();
+        XB_PHASE(7);
         // ---- D2 = G^T . pooled   (TMEM columns 64..111) ----
-        if (threadIdx.x == 0) {
+        if (warp_u == FT_THREADS / 32 && tc_elect_one()) {
             tc_fence_after();
-            const uint32_t th = smem_u32(sR), tl = th + BT_GT_BYTES, ah = smem_u32(sAh), al = smem_u32(sAl);
+#pragma unroll
             for (int ks = 0; ks < FT_ROWS / 8; ++ks) {
-                const uint64_t dTh = make_smem_desc(th + ks * 256, 128, BT_B_SBO), dTl = make_smem_desc(tl + ks * 256, 128, BT_B_SBO);
-                const uint64_t dAh = make_smem_desc(ah + ks * 256, 128, BT_B_SBO), dAl = make_smem_desc(al + ks * 256, 128, BT_B_SBO);
-                tc_mma_tf32(tmem_base + 64, dTh, dAh, idesc, ks > 0 ? 1u : 0u);
-                tc_mma_tf32(tmem_base + 64, dTl, dAh, idesc, 1u);
-                tc_mma_tf32(tmem_base + 64, dTh, dAl, idesc, 1u);
+                tc_mma_tf32(tmem_base + 64, dT_hi + ks * 16, dA_hi + ks * 16, idesc, ks > 0 ? 1u : 0u);
+                tc_mma_tf32(tmem_base + 64, dT_lo + ks * 16, dA_hi + ks * 16, idesc, 1u);
+                tc_mma_tf32(tmem_base + 64, dT_hi + ks * 16, dA_lo + ks * 16, idesc, 1u);
             }
             tc_commit(&bar);
         }
-        // ---- while D2 runs, warps 0-3 drain D1 (row = sequence) ----
+        XB_PHASE(8);
+        // ---- while D2 runs, all warps drain D1 (row = sequence): warps 0-3 take columns 0-15 and 32-47, warps 4-7
+        //      columns 16-31; the tile is staged in shared memory and written with consecutive threads on consecutive
+        //      addresses (rows of P floats) ----
         const int q = warp & 3, which = warp >> 2;
         const int row = 32 * q + lane;
-        if (which == 0) {
-            const uint32_t taddr = tmem_base + ((uint32_t)(32 * q) << 16);
-            uint32_t r[48];
-            tc_ld16_nowait(taddr, r);
-            tc_ld16_nowait(taddr + 16, r + 16);
-            tc_ld16_nowait(taddr + 32, r + 32);
-            tc_wait_ld();
+        auto tmem_to_staging = [&](uint32_t taddr, bool row_ok) {
             float *st = sS + row * a.P;
+            if (which == 0) {
+                uint32_t r[32];
+                tc_ld16_nowait(taddr, r);
+                tc_ld16_nowait(taddr + 32, r + 16);
+                tc_wait_ld();
+                if (row_ok) {
 #pragma unroll
-            for (int p = 0; p < BT_P; ++p)
-                if (p < a.P) st[p] = __uint_as_float(r[p]);
-            asm volatile("bar.sync 1, 128;" ::: "memory");
-            // rows of P floats, P*4 bytes contiguous each: consecutive threads write consecutive addresses
+                    for (int p = 0; p < 16; ++p) {
+                        if (p < a.P) st[p] = __uint_as_float(r[p]);
+                        if (32 + p < a.P) st[32 + p] = __uint_as_float(r[16 + p]);
+                    }
+                }
+            } else {
+                uint32_t r[16];
+                tc_ld16_nowait(taddr + 16, r);
+                tc_wait_ld();
+                if (row_ok) {
+#pragma unroll
+                    for (int p = 0; p < 16; ++p)
+                        if (16 + p < a.P) st[16 + p] = __uint_as_float(r[p]);
+                }
+            }
+        };
+        if (worker) tmem_to_staging(tmem_base + ((uint32_t)(32 * q) << 16), true);
+        __syncthreads();
+        if (worker) {
             float *dst = a.gpool + ((size_t)b0 * a.U + u) * a.P;
             const size_t rstride = (size_t)a.U * a.P;
-            const int n = rows * a.P;
-            for (int i = threadIdx.x; i < n; i += 128) {
-                const int rr = i / a.P;
-                dst[rr * rstride + (i - rr * a.P)] = sS[i];
+            const int n = rows * a.P, dr = FT_THREADS / a.P, dp = FT_THREADS - dr * a.P;
+            int rr = threadIdx.x / a.P, pp = threadIdx.x - rr * a.P;
+            for (int i = threadIdx.x; i < n; i += FT_THREADS) {
+                dst[rr * rstride + pp] = sS[i];
+                rr += dr; pp += dp;
+                if (pp >= a.P) { pp -= a.P; ++rr; }
             }
         }
+        XB_PHASE(9);
         mbar_wait(&bar, parity);
         parity ^= 1;
         tc_fence_after();
@@ -492,26 +577,19 @@ __global__ void __launch_bounds__(FT_THREADS, 1) bwd_fc1_tc_kernel(const FcBwdAr
             tma_bulk_g2s(sH, a.h1 + ((size_t)un * a.B + bn) * H, bytes, &bar_h);
         }
         __syncthreads();      // the D1 copy-out has finished reading the staging buffer
-        if (which == 1) {      // warps 4-7 drain D2 (row = hidden channel)
-            const uint32_t taddr = tmem_base + ((uint32_t)(32 * q) << 16) + 64;
-            uint32_t r[48];
-            tc_ld16_nowait(taddr, r);
-            tc_ld16_nowait(taddr + 16, r + 16);
-            tc_ld16_nowait(taddr + 32, r + 32);
-            tc_wait_ld();
-            if (row < H) {
-                float *st = sS + row * a.P;
-#pragma unroll
-                for (int p = 0; p < BT_P; ++p)
-                    if (p < a.P) st[p] = __uint_as_float(r[p]);
-            }
-            asm volatile("bar.sync 2, 128;" ::: "memory");
-            float *dst = a.dW1p + ((size_t)chunk * a.U + u) * H * a.P;      // 100 x P floats, contiguous
+        XB_PHASE(10);
+        // ---- D2 drain (row = hidden channel): the 100 x P tile is contiguous in global memory ----
+        if (worker) tmem_to_staging(tmem_base + ((uint32_t)(32 * q) << 16) + 64, row < H);
+        __syncthreads();
+        if (worker) {
+            float *dst = a.dW1p + ((size_t)chunk * a.U + u) * H * a.P;
             const int n = H * a.P;
-            for (int i = threadIdx.x - 128; i < n; i += 128) dst[i] = sS[i];
+            for (int i = threadIdx.x; i < n; i += FT_THREADS) dst[i] = sS[i];
         }
+        XB_PHASE(11);
         tc_fence_before();
         __syncthreads();
+        XB_PHASE(12);
     }
     if (warp == 0) {
         tc_fence_after();
@@ -576,6 +654,10 @@ __global__ void __launch_bounds__(FT_THREADS, 2) fc1_tc_eval_pipe_kernel(const F
     const uint32_t tmem_base = tmem_base_s;
     const uint32_t idesc = tc_idesc(2u, 128, FT_NEVAL);
     uint32_t parity = 0;
+    // operand descriptors of K step 0, computed once in warp-uniform code (see tc_elect_one)
+    const int warp_u = tc_warp_uniform();
+    const uint64_t dW_hi = make_smem_desc(smem_u32(sWh), 128, FT_KC * 128), dW_lo = make_smem_desc(smem_u32(sWl), 128, FT_KC * 128);
+    const uint64_t dA_hi = make_smem_desc(smem_u32(sAh), 128, FT_KC * 128), dA_lo = make_smem_desc(smem_u32(sAl), 128, FT_KC * 128);
 
     const long long total = (long long)a.U * a.nchunk;
     const long long t_begin = total * blockIdx.x / gridDim.x, t_end = total * (blockIdx.x + 1) / gridDim.x;
@@ -626,16 +708,12 @@ __global__ void __launch_bounds__(FT_THREADS, 2) fc1_tc_eval_pipe_kernel(const F
         }
         tc_fence_before();
         __syncthreads();
-        if (have && threadIdx.x == 0) {
+        if (have && warp_u == 0 && tc_elect_one()) {
             tc_fence_after();
             const uint32_t acc = tmem_base + (uint32_t)(it & 1) * 128u;
-            const uint32_t wh = smem_u32(sWh), wl = smem_u32(sWl), ah = smem_u32(sAh), al = smem_u32(sAl);
-            const uint32_t lbo = 128, sbo = FT_KC * 128;
 #pragma unroll
             for (int ks = 0; ks < FT_KCH / 8; ++ks) {
-                const uint32_t o = ks * 256;
-                const uint64_t dWh = make_smem_desc(wh + o, lbo, sbo), dWl = make_smem_desc(wl + o, lbo, sbo);
-                const uint64_t dAh = make_smem_desc(ah + o, lbo, sbo), dAl = make_smem_desc(al + o, lbo, sbo);
+                const uint64_t dWh = dW_hi + ks * 16, dWl = dW_lo + ks * 16, dAh = dA_hi + ks * 16, dAl = dA_lo + ks * 16;
                 tc_mma_tf32(acc, dAh, dWh, idesc, ks > 0 ? 1u : 0u);
                 tc_mma_tf32(acc, dAl, dWh, idesc, 1u);
                 tc_mma_tf32(acc, dAh, dWl, idesc, 1u);
@@ -731,6 +809,10 @@ __global__ void __launch_bounds__(FT_THREADS, 1) linear_tc_kernel(const LinTcArg
     const uint32_t tmem_base = tmem_base_s;
     const uint32_t idesc = tc_idesc(2u, 128, a.npad);
     uint32_t parity = 0;
+    // operand descriptors of K step 0, computed once in warp-uniform code (see tc_elect_one)
+    const int warp_u = tc_warp_uniform();
+    const uint64_t dW_hi = make_smem_desc(smem_u32(sWh), 128, FT_KC * 128), dW_lo = make_smem_desc(smem_u32(sWl), 128, FT_KC * 128);
+    const uint64_t dA_hi = make_smem_desc(smem_u32(sAh), 128, FT_KC * 128), dA_lo = make_smem_desc(smem_u32(sAl), 128, FT_KC * 128);
 
     const long long b0 = (long long)blockIdx.x * FT_ROWS;
     const int rows = (int)min((long long)FT_ROWS, a.B - b0);
@@ -749,15 +831,11 @@ __global__ void __launch_bounds__(FT_THREADS, 1) linear_tc_kernel(const LinTcArg
         fence_proxy_async();
         tc_fence_before();
         __syncthreads();
-        if (threadIdx.x == 0) {
+        if (warp_u == 0 && tc_elect_one()) {
             tc_fence_after();
-            const uint32_t wh = smem_u32(sWh), wl = smem_u32(sWl), ah = smem_u32(sAh), al = smem_u32(sAl);
-            const uint32_t lbo = 128, sbo = FT_KC * 128;
 #pragma unroll
             for (int ks = 0; ks < FT_KCH / 8; ++ks) {
-                const uint32_t o = ks * 256;
-                const uint64_t dWh = make_smem_desc(wh + o, lbo, sbo), dWl = make_smem_desc(wl + o, lbo, sbo);
-                const uint64_t dAh = make_smem_desc(ah + o, lbo, sbo), dAl = make_smem_desc(al + o, lbo, sbo);
+                const uint64_t dWh = dW_hi + ks * 16, dWl = dW_lo + ks * 16, dAh = dA_hi + ks * 16, dAl = dA_lo + ks * 16;
                 tc_mma_tf32(tmem_base, dAh, dWh, idesc, (kc > 0 || ks > 0) ? 1u : 0u);
                 tc_mma_tf32(tmem_base, dAl, dWh, idesc, 1u);
                 tc_mma_tf32(tmem_base, dAh, dWl, idesc, 1u);
@@ -848,6 +926,10 @@ int xb_fc_stack_fwd_eval_tc(const float *pooled, long long B, int U, int P, cons
     return launch_fc1_tc(true, a, stream);
 }
 
+#ifdef XB_PHASE_CLOCKS
+extern "C" int xb_dbg_phase_clocks(long long *host) { return (int)cudaMemcpyFromSymbol(host, g_phase_clk, sizeof(g_phase_clk)); }
+#endif
+
 // returns XB_ERR_UNSUPPORTED (without setting an error) when the class count does not fit one N tile
 int xb_linear_tc(const float *x, long long B, int U, int C, const float *W, const float *bias, float *out, cudaStream_t stream)
 {
@@ -890,6 +972,6 @@ int xb_bwd_fc1_tc(const float *h1, const float *gh2, const float *pooled, long l
         xb_set_error("bwd_fc1_tc: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
         return XB_ERR_CUDA;
     }
-    bwd_fc1_tc_kernel<<<grid, FT_THREADS, smem, stream>>>(a);
+    bwd_fc1_tc_kernel<<<grid, BT_THREADS, smem, stream>>>(a);
     return xb_check_launch("bwd_fc1_tc");
 }

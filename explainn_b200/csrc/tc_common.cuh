@@ -94,6 +94,17 @@ __device__ __forceinline__ void tc_mma_tf32(uint32_t tmem_d, uint64_t adesc, uin
         : "memory");
 }
 
+// One lane of the (fully active) warp.  Use inside a branch on tc_warp_uniform(): with the branch warp-uniform and
+// the descriptors computed outside of it, ptxas keeps the tcgen05.mma operands in uniform registers; a plain
+// `if (threadIdx.x == 0)` makes it wrap every MMA in an elect / R2UR / branch loop (about 15 instructions per MMA).
+__device__ __forceinline__ bool tc_elect_one()
+{
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred != 0;
+}
+__device__ __forceinline__ int tc_warp_uniform() { return __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0); }
+
 __device__ __forceinline__ void tc_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 __device__ __forceinline__ uint32_t tc_alloc(uint32_t *slot_in_smem, uint32_t ncols)
