@@ -303,13 +303,15 @@ __global__ void __launch_bounds__(FC_THREADS) fc2_train_kernel(
     const float4 shv = act ? make_float4(sh[j0], sh[j0 + 1], sh[j0 + 2], sh[j0 + 3]) : make_float4(0.f, 0.f, 0.f, 0.f);
     const float4 w2v = act ? make_float4(w2s[j0], w2s[j0 + 1], w2s[j0 + 2], w2s[j0 + 3]) : make_float4(0.f, 0.f, 0.f, 0.f);
     const float bias2 = b2[u];
-    // software pipeline: the next row is in flight while this row is reduced
-    float4 hn = make_float4(0.f, 0.f, 0.f, 0.f);
+    // software pipeline: the next two rows of this warp are in flight while this row is reduced
+    float4 hn = make_float4(0.f, 0.f, 0.f, 0.f), hn2 = hn;
     if (warp < rows && act) hn = *reinterpret_cast<const float4 *>(h1 + ((size_t)u * B + b0 + warp) * H + j0);
+    if (warp + 8 < rows && act) hn2 = *reinterpret_cast<const float4 *>(h1 + ((size_t)u * B + b0 + warp + 8) * H + j0);
     for (int r = warp; r < rows; r += 8) {
         const size_t rowi = (size_t)u * B + b0 + r;
         const float4 hc = hn;
-        if (r + 8 < rows && act) hn = *reinterpret_cast<const float4 *>(h1 + (rowi + 8) * H + j0);
+        hn = hn2;
+        if (r + 16 < rows && act) hn2 = *reinterpret_cast<const float4 *>(h1 + (rowi + 16) * H + j0);
         uint32_t nib = 15u;
         if (pdrop > 0.f) nib = drop_keep4(seed, rowi * (H / 4) + lane, thresh);
         const float v0 = (nib & 1u) ? fmaxf(fmaf(hc.x, scv.x, shv.x), 0.f) * keep_scale : 0.f;
@@ -571,23 +573,25 @@ __global__ void __launch_bounds__(FC_THREADS) bwd_fc2_kernel(const float *__rest
         bev[i] = act ? be[j0 + i] : 0.f; w2v[i] = act ? w2s[j0 + i] : 0.f;
     }
     float dW2[4] = {0, 0, 0, 0}, sg[4] = {0, 0, 0, 0}, sgx[4] = {0, 0, 0, 0};
-    float4 hn = make_float4(0.f, 0.f, 0.f, 0.f);
-    float gn = 0.f;
-    uint32_t wn = 0u;
+    float4 hn = make_float4(0.f, 0.f, 0.f, 0.f), hn2 = hn;
+    float gn = 0.f, gn2 = 0.f;
+    uint32_t wn = 0u, wn2 = 0u;
     const bool use_mask = pdrop > 0.f && dropmask;
-    auto fetch = [&](size_t rowi) {
-        if (act) hn = *reinterpret_cast<const float4 *>(h1 + rowi * H + j0);
-        gn = gh2[rowi];
-        wn = use_mask ? dropmask[rowi * 4 + (lane >> 3)] : 0u;
+    auto fetch = [&](size_t rowi, float4 &hh, float &gg, uint32_t &ww) {
+        if (act) hh = *reinterpret_cast<const float4 *>(h1 + rowi * H + j0);
+        gg = gh2[rowi];
+        ww = use_mask ? dropmask[rowi * 4 + (lane >> 3)] : 0u;
     };
-    if (warp < rows) fetch((size_t)u * B + b0 + warp);
+    if (warp < rows) fetch((size_t)u * B + b0 + warp, hn, gn, wn);
+    if (warp + 8 < rows) fetch((size_t)u * B + b0 + warp + 8, hn2, gn2, wn2);
     for (int r = warp; r < rows; r += 8) {
         const size_t rowi = (size_t)u * B + b0 + r;
         const float hc[4] = {hn.x, hn.y, hn.z, hn.w};
         const float g = gn;
         uint32_t nib = 15u;
         if (pdrop > 0.f) nib = use_mask ? (wn >> (4 * (lane & 7))) & 15u : drop_keep4(seed, rowi * (H / 4) + lane, thresh);
-        if (r + 8 < rows) fetch(rowi + 8);       // next row in flight while this one is processed
+        hn = hn2; gn = gn2; wn = wn2;
+        if (r + 16 < rows) fetch(rowi + 16, hn2, gn2, wn2);       // two rows in flight while this one is processed
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             const float xh = (hc[i] - muv[i]) * inv4[i];

@@ -314,12 +314,17 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bwd_fc1_tc_kernel(const FcBwdAr
         mbar_init(&bar_h, 1);
         mbar_fence_init();
     }
-    if (warp == 0) tc_alloc(&tmem_base_s, 128u);
+    if (warp == 0) tc_alloc(&tmem_base_s, 256u);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = tmem_base_s;
-    const uint32_t idesc = tc_idesc(2u, 128, BT_P);
+    // The hi and lo tiles of W1t (and of the pooled tile) are adjacent in shared memory, so one MMA with N = 2*BT_P
+    // multiplies by [hi ; lo] at once: per K step  X_hi.[Y_hi ; Y_lo] -> columns 0..95  and  X_lo.Y_hi -> columns 0..47.
+    // The drain adds column p and column BT_P + p.  (Two MMAs instead of three: a third less operand traffic from
+    // shared memory, which is what bounds these products.)
+    const uint32_t idesc = tc_idesc(2u, 128, BT_P), idesc2 = tc_idesc(2u, 128, 2 * BT_P);
+    static_assert(BT_W_BYTES == (BT_P / 8) * BT_G_SBO && BT_A_BYTES == (BT_P / 8) * BT_B_SBO, "hi/lo tiles must be adjacent row groups");
     uint32_t parity = 0, h_parity = 0;
     // operand descriptors of K step 0, computed once in warp-uniform code (see tc_elect_one)
     const int warp_u = tc_warp_uniform();
@@ -459,14 +464,13 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bwd_fc1_tc_kernel(const FcBwdAr
         tc_fence_before();
         __syncthreads();
         XB_PHASE(3);
-        // ---- D1 = G . W1   (TMEM columns 0..47) ----
+        // ---- D1 = G . W1   (TMEM columns 0..95) ----
         if (warp_u == FT_THREADS / 32 && tc_elect_one()) {
             tc_fence_after();
 #pragma unroll
             for (int ks = 0; ks < BT_J / 8; ++ks) {      // + 16 per K step: 256 bytes in the descriptor's address field
-                tc_mma_tf32(tmem_base, dG_hi + ks * 16, dW_hi + ks * 16, idesc, ks > 0 ? 1u : 0u);
+                tc_mma_tf32(tmem_base, dG_hi + ks * 16, dW_hi + ks * 16, idesc2, ks > 0 ? 1u : 0u);
                 tc_mma_tf32(tmem_base, dG_lo + ks * 16, dW_hi + ks * 16, idesc, 1u);
-                tc_mma_tf32(tmem_base, dG_hi + ks * 16, dW_lo + ks * 16, idesc, 1u);
             }
             tc_commit(&bar);
         }
@@ -508,14 +512,13 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bwd_fc1_tc_kernel(const FcBwdAr
         tc_fence_before();
         __syncthreads();
         XB_PHASE(7);
-        // ---- D2 = G^T . pooled   (TMEM columns 64..111) ----
+        // ---- D2 = G^T . pooled   (TMEM columns 128..223) ----
         if (warp_u == FT_THREADS / 32 && tc_elect_one()) {
             tc_fence_after();
 #pragma unroll
             for (int ks = 0; ks < FT_ROWS / 8; ++ks) {
-                tc_mma_tf32(tmem_base + 64, dT_hi + ks * 16, dA_hi + ks * 16, idesc, ks > 0 ? 1u : 0u);
-                tc_mma_tf32(tmem_base + 64, dT_lo + ks * 16, dA_hi + ks * 16, idesc, 1u);
-                tc_mma_tf32(tmem_base + 64, dT_hi + ks * 16, dA_lo + ks * 16, idesc, 1u);
+                tc_mma_tf32(tmem_base + 128, dT_hi + ks * 16, dA_hi + ks * 16, idesc2, ks > 0 ? 1u : 0u);
+                tc_mma_tf32(tmem_base + 128, dT_lo + ks * 16, dA_hi + ks * 16, idesc, 1u);
             }
             tc_commit(&bar);
         }
@@ -528,25 +531,28 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bwd_fc1_tc_kernel(const FcBwdAr
         auto tmem_to_staging = [&](uint32_t taddr, bool row_ok) {
             float *st = sS + row * a.P;
             if (which == 0) {
-                uint32_t r[32];
+                uint32_t r[32], r2[32];
                 tc_ld16_nowait(taddr, r);
                 tc_ld16_nowait(taddr + 32, r + 16);
+                tc_ld16_nowait(taddr + BT_P, r2);
+                tc_ld16_nowait(taddr + BT_P + 32, r2 + 16);
                 tc_wait_ld();
                 if (row_ok) {
 #pragma unroll
                     for (int p = 0; p < 16; ++p) {
-                        if (p < a.P) st[p] = __uint_as_float(r[p]);
-                        if (32 + p < a.P) st[32 + p] = __uint_as_float(r[16 + p]);
+                        if (p < a.P) st[p] = __uint_as_float(r[p]) + __uint_as_float(r2[p]);
+                        if (32 + p < a.P) st[32 + p] = __uint_as_float(r[16 + p]) + __uint_as_float(r2[16 + p]);
                     }
                 }
             } else {
-                uint32_t r[16];
+                uint32_t r[16], r2[16];
                 tc_ld16_nowait(taddr + 16, r);
+                tc_ld16_nowait(taddr + BT_P + 16, r2);
                 tc_wait_ld();
                 if (row_ok) {
 #pragma unroll
                     for (int p = 0; p < 16; ++p)
-                        if (16 + p < a.P) st[16 + p] = __uint_as_float(r[p]);
+                        if (16 + p < a.P) st[16 + p] = __uint_as_float(r[p]) + __uint_as_float(r2[p]);
                 }
             }
         };
@@ -579,7 +585,7 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bwd_fc1_tc_kernel(const FcBwdAr
         __syncthreads();      // the D1 copy-out has finished reading the staging buffer
         XB_PHASE(10);
         // ---- D2 drain (row = hidden channel): the 100 x P tile is contiguous in global memory ----
-        if (worker) tmem_to_staging(tmem_base + ((uint32_t)(32 * q) << 16) + 64, row < H);
+        if (worker) tmem_to_staging(tmem_base + ((uint32_t)(32 * q) << 16) + 128, row < H);
         __syncthreads();
         if (worker) {
             float *dst = a.dW1p + ((size_t)chunk * a.U + u) * H * a.P;
@@ -593,7 +599,7 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bwd_fc1_tc_kernel(const FcBwdAr
     }
     if (warp == 0) {
         tc_fence_after();
-        tc_dealloc(tmem_base, 128u);
+        tc_dealloc(tmem_base, 256u);
     }
 }
 

@@ -176,7 +176,7 @@ __global__ void __launch_bounds__(BW_WARPS * 32) conv_bwd_sparse_kernel(
     const int db = STRIDE / P, dp = STRIDE - db * P;
     const long long first = e0 + warp * 32 + lane, last = e1 - 1;
     const int niter = e1 > e0 ? (int)((e1 - e0 + STRIDE - 1) / STRIDE) : 0;
-    struct StA { float gp, po, xh; int s, b; };
+    struct StA { float gp, po, xh; int ix, p7, b; bool valid; };     // raw loaded values: nothing here may wait for a load
     struct StB { float gz, xh; uint32_t w0, w1, w2, m0, m1; int s; };
     long long ea = first;                      // entry index of the next stage-A fetch
     int ab, ap;                                // its (b, p), kept incrementally (host wrapper guarantees B*P < 2^31)
@@ -185,15 +185,17 @@ __global__ void __launch_bounds__(BW_WARPS * 32) conv_bwd_sparse_kernel(
         ab = (int)(ec / P);
         ap = (int)(ec - (long long)ab * P);
     }
+    const int lastb = (int)(last / P), lastp = (int)(last - (long long)lastb * P);
     auto fetchA = [&]() {
         StA r;
-        const bool valid = ea <= last;
-        if (!valid) { ab = (int)(last / P); ap = (int)(last - (long long)ab * P); }
+        r.valid = ea <= last;
+        if (!r.valid) { ab = lastb; ap = lastp; }
         const size_t o = ((size_t)ab * U + u) * P + ap;   // (B,U,P) layout
-        r.gp = valid ? gpool[o] : 0.f;
-        r.po = valid ? pooled[o] : 0.f;
+        r.gp = gpool[o];
+        r.po = pooled[o];
         r.xh = xhat[o];
-        r.s = ap * XB_POOL + idx[o];
+        r.ix = idx[o];
+        r.p7 = ap * XB_POOL;
         r.b = ab;
         ea += STRIDE;
         ab += db; ap += dp;
@@ -202,12 +204,12 @@ __global__ void __launch_bounds__(BW_WARPS * 32) conv_bwd_sparse_kernel(
     };
     auto fetchB = [&](const StA &x) {
         StB r;
-        r.gz = x.gp * x.po;
+        r.gz = x.valid ? x.gp * x.po : 0.f;
         r.xh = x.xh;
-        r.s = x.s;
+        r.s = x.p7 + x.ix;
         const uint32_t *cw = codes + (size_t)x.b * wc;
         const uint32_t *mw = nmask + (size_t)x.b * wm;
-        const int wi = x.s >> 4, mi = x.s >> 5;
+        const int wi = r.s >> 4, mi = r.s >> 5;
         r.w0 = cw[wi];
         r.w1 = wi + 1 < wc ? cw[wi + 1] : 0u;
         r.w2 = wi + 2 < wc ? cw[wi + 2] : 0u;
