@@ -45,6 +45,9 @@ SIGNATURES = {
     "explainn_interp_thresholds": [_P, _I, _P, _P, _P, _P, _P],
     "explainn_interp_pwm_count": [_P, _P, _LL, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P],
     "explainn_revcomp_packed": [_P, _P, _LL, _I, _P, _P, _P],
+    "explainn_encode_dna": [_P, _P, _LL, _I, _P, _P, _P],
+    "explainn_unpack_onehot": [_P, _P, _LL, _I, _P, _I, _P],
+    "explainn_pwm_score": [_P, _P, _LL, _I, _I, _I, _P, _P, _P, _I, _I, _P, _P],
     "explainn_fc_stack_fwd_eval": [_P, _LL, _I, _I] + [_P] * 12 + [_F, _P, _P],
     "explainn_linear_fwd": [_P, _LL, _I, _I, _P, _P, _P, _P],
     "explainn_input_cooc_stats": [_P, _P, _LL, _I, _I, _P, _P],

@@ -346,6 +346,45 @@ struct CountSink {
     }
 };
 
+// (6) PWM scoring (explainn/models/networks.py:393-441): per sequence and unit, the maximum or the sum of the conv
+//     output over the S valid positions.  `accumulate` folds the call for the reverse strand into the same output
+//     (max of both strands / sum of both strands), which is torch.cat((o, o_rev), 2) followed by max / sum.
+struct ScoreSink {
+    struct Params { float *out; int use_max; int accumulate; };
+    static __host__ __device__ int smem_bytes(int) { return 0; }
+    Params p;
+    int lane;
+    float shift, m, sum;
+    long long out_idx;
+    __device__ void init_cta(unsigned char *, const Params &pp, int, int lane_) { p = pp; lane = lane_; }
+    __device__ void begin_tile(int, int, float shift_, const ConvArgs &) { shift = shift_; }
+    __device__ void begin_seq(long long b, int u0, const ConvArgs &a)
+    {
+        m = -INFINITY;
+        sum = 0.f;
+        out_idx = u0 + lane < a.U ? b * a.U + u0 + lane : -1;
+    }
+    __device__ __forceinline__ void window(int win, int t, const float *acc, const ConvArgs &a)
+    {
+        if (win >= a.nwin) return;
+#pragma unroll
+        for (int j = 0; j < XB_POOL; ++j)
+            if (t + j < a.S) {
+                const float z = __fadd_rn(acc[j], shift);
+                m = fmaxf(m, z);
+                sum = __fadd_rn(sum, z);       // positions in increasing order
+            }
+    }
+    __device__ void end_seq(const ConvArgs &)
+    {
+        if (out_idx < 0) return;
+        const float v = p.use_max ? m : sum;
+        if (p.accumulate) p.out[out_idx] = p.use_max ? fmaxf(p.out[out_idx], v) : __fadd_rn(p.out[out_idx], v);
+        else p.out[out_idx] = v;
+    }
+    __device__ void end_tile(int, const ConvArgs &) {}
+};
+
 template <class Sink> struct NeedsSeq { static constexpr bool value = false; };
 template <> struct NeedsSeq<CountSink> { static constexpr bool value = true; };
 
@@ -704,6 +743,20 @@ extern "C" int explainn_interp_unit_max(const uint32_t *codes, const uint32_t *n
     }
     reduce_zmax_kernel<<<(U + 127) / 128, 128, 0, stream>>>(scratch, n_cta, U, zmax, accumulate);
     return xb_check_launch("interp_unit_max");
+}
+
+extern "C" int explainn_pwm_score(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F,
+                                  const float *tables, const float *wq_t, const float *shift, int use_max, int accumulate,
+                                  float *out, cudaStream_t stream)
+{
+    ConvArgs a; Geometry g;
+    int rc = fill_args(&a, &g, codes, nmask, B, L, U, F, tables, wq_t, shift);
+    if (rc != XB_OK) return rc;
+    XB_REQUIRE(out, "pwm_score: null output");
+    if (B == 0) return XB_OK;
+    a.nwin = g.nwin_all;
+    ScoreSink::Params sp{out, use_max, accumulate};
+    return dispatch_scan<ScoreSink, ScoreSink>(g.G, a, sp, 0, stream);
 }
 
 extern "C" int explainn_interp_pwm_count(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F,

@@ -109,3 +109,91 @@ extern "C" int explainn_revcomp_packed(const uint32_t *codes, const uint32_t *nm
     revcomp_packed_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(codes, nmask, B, L, codes_rc, nmask_rc);
     return xb_check_launch("revcomp_packed");
 }
+
+
+// ------------------------------------------------------------------------------------------------
+// DNA text -> packed codes, on the device (replaces the per-character Python loop of
+// explainn/utils/tools.py:136-181, `dna_one_hot`, and the 16-bytes-per-base fp32 host-to-device copy).
+// Same semantics as the reference: case-insensitive A/C/G/T -> 0..3; because the reference substitutes the letters
+// by the digits '0'..'3' before indexing, those digits in the input mean A..T as well; every other character is an
+// all-zero column (N).  A sequence longer than L is centre-cropped (start (len-L)//2), a shorter one is placed at
+// column (L-len)//2 and the rest is N.  One warp per 32 consecutive positions of one sequence.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) encode_dna_kernel(const unsigned char *__restrict__ text, const long long *__restrict__ offsets,
+                                                         long long B, int L, uint32_t *__restrict__ codes, uint32_t *__restrict__ nmask)
+{
+    const int wc = xb_words_codes(L), wm = xb_words_mask(L);
+    const int lane = threadIdx.x & 31;
+    const long long warp = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const long long b = warp / wm;
+    const int chunk = (int)(warp % wm);
+    if (b >= B) return;
+    const long long beg = offsets[b], len = offsets[b + 1] - beg;
+    const long long shift = len >= L ? (len - L) / 2 : -(((long long)L - len) / 2);      // source index = i + shift
+    const int i = chunk * 32 + lane;
+    int code = 0, isn = 0;
+    if (i < L) {
+        const long long src = i + shift;
+        isn = 1;
+        if (src >= 0 && src < len) {
+            unsigned c = text[beg + src];
+            if (c >= 'a' && c <= 'z') c -= 32;
+            if (c == 'A' || c == '0') { code = 0; isn = 0; }
+            else if (c == 'C' || c == '1') { code = 1; isn = 0; }
+            else if (c == 'G' || c == '2') { code = 2; isn = 0; }
+            else if (c == 'T' || c == '3') { code = 3; isn = 0; }
+        }
+    }
+    const unsigned m = __ballot_sync(0xffffffffu, isn);
+    const unsigned v = (unsigned)code << (2 * (lane & 15));
+    const unsigned lo = __reduce_or_sync(0xffffffffu, lane < 16 ? v : 0u);
+    const unsigned hi = __reduce_or_sync(0xffffffffu, lane >= 16 ? v : 0u);
+    if (lane == 0) {
+        nmask[b * wm + chunk] = m;
+        codes[b * wc + 2 * chunk] = lo;
+        if (2 * chunk + 1 < wc) codes[b * wc + 2 * chunk + 1] = hi;
+    }
+}
+
+extern "C" int explainn_encode_dna(const unsigned char *text, const long long *offsets, long long B, int L, uint32_t *codes,
+                                   uint32_t *nmask, cudaStream_t stream)
+{
+    XB_REQUIRE(text && offsets && codes && nmask && B >= 0 && L > 0, "encode_dna: bad argument");
+    if (B == 0) return XB_OK;
+    const long long warps = B * xb_words_mask(L);
+    encode_dna_kernel<<<(unsigned)((warps + 7) / 8), 256, 0, stream>>>(text, offsets, B, L, codes, nmask);
+    return xb_check_launch("encode_dna");
+}
+
+// Packed codes -> one-hot (B,4,L), fp32 or fp16 (the dtype `dna_one_hot` returns); N columns are all zero.
+template <typename T>
+__global__ void __launch_bounds__(256) unpack_onehot_kernel(const uint32_t *__restrict__ codes, const uint32_t *__restrict__ nmask,
+                                                            long long B, int L, T *__restrict__ x)
+{
+    const int wc = xb_words_codes(L), wm = xb_words_mask(L);
+    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= B * 4 * L) return;
+    const long long b = t / (4LL * L);
+    const int rem = (int)(t - b * 4LL * L), c = rem / L, i = rem - c * L;
+    const uint32_t isn = (nmask[b * wm + (i >> 5)] >> (i & 31)) & 1u;
+    const uint32_t code = (codes[b * wc + (i >> 4)] >> (2 * (i & 15))) & 3u;
+    x[t] = (T)((!isn && code == (uint32_t)c) ? 1.0f : 0.0f);
+}
+
+extern "C" int explainn_unpack_onehot(const uint32_t *codes, const uint32_t *nmask, long long B, int L, void *x, int x_dtype,
+                                      cudaStream_t stream)
+{
+    XB_REQUIRE(codes && nmask && x && B >= 0 && L > 0, "unpack_onehot: bad argument");
+    if (B == 0) return XB_OK;
+    const long long n = B * 4 * L;
+    const unsigned grid = (unsigned)((n + 255) / 256);
+    if (x_dtype == EXPLAINN_DTYPE_F32)
+        unpack_onehot_kernel<float><<<grid, 256, 0, stream>>>(codes, nmask, B, L, (float *)x);
+    else if (x_dtype == EXPLAINN_DTYPE_F16)
+        unpack_onehot_kernel<__half><<<grid, 256, 0, stream>>>(codes, nmask, B, L, (__half *)x);
+    else {
+        xb_set_error("unpack_onehot: unsupported dtype %d", x_dtype);
+        return XB_ERR_UNSUPPORTED;
+    }
+    return xb_check_launch("unpack_onehot");
+}

@@ -51,6 +51,52 @@ def pack_onehot(x, num_cnns=1, invalid=None):
     return Packed(codes, nmask, B, L, invalid)
 
 
+def encode_dna(seqs, seq_len, device="cuda"):
+    """List of DNA strings -> Packed, encoded on the GPU (semantics of `dna_one_hot`, tools.py:136-181).
+
+    The host only concatenates the bytes (1 byte per base crosses PCIe instead of 16 for an fp32 one-hot)."""
+    import numpy as np
+    B = len(seqs)
+    L = int(seq_len)
+    dev = torch.device(device)
+    if dev.type != "cuda":
+        raise RuntimeError("explainn_b200 runs only on CUDA devices (there is no CPU fallback)")
+    raw = [s if isinstance(s, bytes) else str(s).encode("latin-1", "replace") for s in seqs]
+    offs = np.zeros(B + 1, dtype=np.int64)
+    if B:
+        np.cumsum([len(r) for r in raw], out=offs[1:])
+    text = np.frombuffer(b"".join(raw) + b"\0", dtype=np.uint8)       # never empty
+    text_d = torch.from_numpy(text.copy()).to(dev, non_blocking=True)
+    offs_d = torch.from_numpy(offs).to(dev, non_blocking=True)
+    codes = torch.empty((B, (L + 15) // 16), dtype=torch.int32, device=dev)
+    nmask = torch.empty((B, (L + 31) // 32), dtype=torch.int32, device=dev)
+    if B:
+        call("explainn_encode_dna", ptr(text_d), ptr(offs_d), B, L, ptr(codes), ptr(nmask), stream())
+    return Packed(codes, nmask, B, L, torch.zeros(1, dtype=torch.int32, device=dev))
+
+
+def unpack_onehot(pk, dtype=torch.float32):
+    """Packed -> (B,4,L) one-hot tensor (N columns all zero)."""
+    x = torch.empty((pk.B, 4, pk.L), dtype=dtype, device=pk.codes.device)
+    dt = _cabi.DTYPE_F32 if dtype == torch.float32 else _cabi.DTYPE_F16
+    if dtype not in (torch.float32, torch.float16):
+        raise ValueError("unpack_onehot: float32 or float16")
+    if pk.B:
+        call("explainn_unpack_onehot", ptr(pk.codes), ptr(pk.nmask), pk.B, pk.L, ptr(x), dt, stream())
+    return x
+
+
+def pwm_score(pk, prep, use_max, out=None):
+    """Max or sum over positions of the grouped conv output; with `out` given the result is folded into it."""
+    acc = out is not None
+    if out is None:
+        out = torch.empty((pk.B, prep.U), dtype=torch.float32, device=pk.codes.device)
+    if pk.B:
+        call("explainn_pwm_score", ptr(pk.codes), ptr(pk.nmask), pk.B, pk.L, prep.U, prep.F, ptr(prep.tables),
+             ptr(prep.wq_t), ptr(prep.shift), int(bool(use_max)), int(acc), ptr(out), stream())
+    return out
+
+
 def check_invalid(invalid):
     n = int(invalid.item())
     if n:

@@ -220,3 +220,58 @@ class ExplaiNN(nn.Module):
             return autograd_fn.forward_train(self, x)
         unit = self._unit_outputs_eval(x)
         return Fn.linear_fwd(unit, self.final.weight.detach(), self.final.bias.detach())
+
+
+class PWM(nn.Module):
+    """PWM (Position Weight Matrix) scoring -- drop-in for explainn/models/networks.py:393-437.
+
+    Same constructor, `._options` and frozen `.conv1d` (weight (G,4,F) = the PWMs, bias 0) as the reference.  The
+    forward scores both strands with the fused one-hot conv kernel (the reverse strand is the packed reverse
+    complement, `_flip(_flip(x, 1), 2)` in the reference) and reduces over positions inside the kernel; neither the
+    G-times tiled input nor the (B,G,2S) score tensor is built.
+    """
+
+    def __init__(self, pwms, input_length, scoring="sum"):
+        super().__init__()
+        pwms = torch.as_tensor(pwms, dtype=torch.float32)
+        groups, _, kernel_size = pwms.shape
+        self._options = {
+            "groups": groups,
+            "kernel_size": kernel_size,
+            "sequence_length": input_length,
+            "scoring": scoring,
+        }
+        if kernel_size > 24:
+            raise NotImplementedError("explainn_b200: kernel_size <= 24 (k-mer tables of the fused conv kernel)")
+        self.conv1d = nn.Conv1d(in_channels=4 * groups, out_channels=1 * groups, kernel_size=kernel_size, groups=groups)
+        self.conv1d.bias.data = torch.zeros(groups)
+        self.conv1d.weight.data = pwms.clone()
+        for p in self.conv1d.parameters():
+            p.requires_grad = False
+        self._invalid = None
+
+    def _prep(self):
+        w = self.conv1d.weight.detach()
+        G = w.shape[0]
+        one = torch.ones(G, dtype=torch.float32, device=w.device)
+        zero = torch.zeros(G, dtype=torch.float32, device=w.device)
+        # identity BatchNorm (gamma 1, beta 0, mean 0, var 1, eps 0): the tables hold the PWM weights unchanged
+        return Fn.conv_prepare(w, self.conv1d.bias.detach(), one, zero, zero, one, 0.0)
+
+    def forward_packed(self, pk):
+        prep = self._prep()
+        use_max = self._options["scoring"] == "max"
+        out = Fn.pwm_score(pk, prep, use_max)
+        return Fn.pwm_score(Fn.revcomp_packed(pk), prep, use_max, out=out)
+
+    def forward(self, x):
+        """x: (B,4,L) one-hot float tensor on the GPU -> (B,G) scores."""
+        _require_cuda(x)
+        if x.dim() != 3 or x.shape[1] != 4:
+            raise ValueError("expected input of shape (B, 4, L), got %s" % (tuple(x.shape),))
+        if x.shape[2] < self._options["kernel_size"]:
+            raise RuntimeError("Calculated padded input size per channel: (%d). Kernel size: (%d). Kernel size can't be "
+                               "greater than actual input size" % (x.shape[2], self._options["kernel_size"]))
+        if self._invalid is None or self._invalid.device != x.device:
+            self._invalid = torch.zeros(1, dtype=torch.int32, device=x.device)
+        return self.forward_packed(Fn.pack_onehot(x, 1, self._invalid))

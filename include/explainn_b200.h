@@ -60,6 +60,17 @@ int explainn_pack_onehot(const void *x, int x_dtype, long long B, int L, long lo
 int explainn_revcomp_packed(const uint32_t *codes, const uint32_t *nmask, long long B, int L, uint32_t *codes_rc,
                             uint32_t *nmask_rc, cudaStream_t stream);
 
+/* DNA text -> packed codes on the device: the batched counterpart of `dna_one_hot` (explainn/utils/tools.py:136-181).
+ * text: concatenated ASCII bytes on the device, sequence b = text[offsets[b] .. offsets[b+1]) (offsets: B+1 int64 on the
+ * device).  Case-insensitive A,C,G,T (and, as in the reference, the digits '0'..'3') -> codes 0..3, anything else -> N.
+ * Longer than L: centre crop starting at (len-L)/2; shorter: placed at column (L-len)/2, N elsewhere (tools.py:150-173). */
+int explainn_encode_dna(const unsigned char *text, const long long *offsets, long long B, int L, uint32_t *codes,
+                        uint32_t *nmask, cudaStream_t stream);
+
+/* Packed codes -> one-hot (B,4,L) of dtype EXPLAINN_DTYPE_F32/F16 (what `dna_one_hot` returns, tools.py:163); N columns are zero. */
+int explainn_unpack_onehot(const uint32_t *codes, const uint32_t *nmask, long long B, int L, void *x, int x_dtype,
+                           cudaStream_t stream);
+
 /* ---- weight preparation -------------------------------------------------------------------------------
  * Folds BatchNorm1d (explainn/models/networks.py:100; eval: running stats, train: batch stats) into the
  * grouped Conv1d filter (networks.py:98-99) and builds the k-mer lookup tables the scan kernels read.
@@ -129,6 +140,14 @@ int explainn_interp_unit_max_noalloc(const uint32_t *codes, const uint32_t *nmas
 /* float16 threshold 0.5*max (interpretation.py:187) and its pre-activation bracket.  All outputs (U). */
 int explainn_interp_thresholds(const float *zmax, int U, float *thr, float *zlo, float *zhi, float *amax,
                                cudaStream_t stream);
+/* PWM scoring, `networks.PWM.forward` (explainn/models/networks.py:428-437): out[b][u] = max (use_max=1) or sum
+ * (use_max=0) over the S valid positions of the grouped conv output z[b][u][s] (tables/wq_t/shift from
+ * explainn_conv_prepare with identity BatchNorm).  accumulate=1 folds the result into `out` (max / +), which is how
+ * the reverse strand (explainn_revcomp_packed) joins: torch.cat((o, o_rev), 2) then max / sum.  out: (B,U) fp32. */
+int explainn_pwm_score(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F,
+                       const float *tables, const float *wq_t, const float *shift, int use_max, int accumulate,
+                       float *out, cudaStream_t stream);
+
 /* Pass B: counts[u,c,k] += #positions with half(act) > thr[u] whose window has base c at offset k
  * (interpretation.py:203-214); hits[u] += number of such positions.  counts (U,4,F) u64, hits (U) u64,
  * both accumulated into (zero them first).  seq_hit (B,U) u8, optional (NULL to skip): 1 if the sequence has any

@@ -169,3 +169,59 @@ def pwm_to_meme_text(pwm, names=None):
             if np.sum(pwm[i][:, j]) > 0:
                 out.append("\t".join(str(pwm[i][c, j]) for c in range(4)) + "\n")
     return "".join(out)
+
+
+_DNA_CODE = {"A": 0, "C": 1, "G": 2, "T": 3, "0": 0, "1": 1, "2": 2, "3": 3}
+
+
+def dna_one_hot(seq, seq_len=None):
+    """explainn/utils/tools.py:136-181 restated without the per-character try/except: (4,L) float16.
+
+    The reference upper-cases, replaces A,C,G,T by the digits '0'..'3' and indexes with int(char), so the digits
+    '0'..'3' in the input also select a row; every other character (and every position outside the placed
+    sequence) is an all-zero column.  Longer than seq_len: centre crop from (len-seq_len)//2 (tools.py:153-155);
+    shorter: placed at column (seq_len-len)//2 (tools.py:158)."""
+    if seq_len is None:
+        seq_len = len(seq)
+        start = 0
+    elif seq_len <= len(seq):
+        trim = (len(seq) - seq_len) // 2
+        seq = seq[trim:trim + seq_len]
+        start = 0
+    else:
+        start = (seq_len - len(seq)) // 2
+    seq = seq.upper()
+    x = np.zeros((4, seq_len), np.float16)
+    for i, ch in enumerate(seq):
+        c = _DNA_CODE.get(ch)
+        if c is not None:
+            x[c, start + i] = 1.0
+    return x
+
+
+def revcomp_onehot(x):
+    """`_flip(_flip(x, 1), 2)` of networks.py:430 / `s[::-1, ::-1]` of fasta2predictions.py:160 on (B,4,L)."""
+    return np.ascontiguousarray(x[:, ::-1, ::-1])
+
+
+def pwm_scores(onehot, pwms, scoring="sum"):
+    """networks.PWM.forward (networks.py:428-437) in the canonical arithmetic: grouped conv (bias 0) on both strands,
+    then max or a float32 sum over positions in increasing order (forward strand first, then the reverse strand).
+    onehot (B,4,L) float, pwms (G,4,F) float32 -> (B,G) float32."""
+    G, four, F = pwms.shape
+    ident = (np.zeros(G, np.float32), np.ones(G, np.float32), np.zeros(G, np.float32), np.zeros(G, np.float32),
+             np.ones(G, np.float32))
+    wq, shift, _ = fold_bn(np.ascontiguousarray(pwms, np.float32), ident[0], ident[1], ident[2], ident[3], ident[4], eps=0.0)
+    outs = []
+    for x in (onehot, revcomp_onehot(onehot)):
+        codes, nmask, _ = pack_onehot(np.ascontiguousarray(x, np.float32))
+        outs.append(conv_z(codes, nmask, x.shape[2], wq, shift))            # (B,G,S)
+    if scoring == "max":
+        return np.maximum(outs[0].max(axis=2), outs[1].max(axis=2)).astype(np.float32)
+    acc = []
+    for z in outs:
+        s = np.zeros(z.shape[:2], np.float32)
+        for t in range(z.shape[2]):
+            s = (s + z[:, :, t]).astype(np.float32)
+        acc.append(s)
+    return (acc[0] + acc[1]).astype(np.float32)
