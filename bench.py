@@ -320,7 +320,12 @@ def extras(torch, dev, model, trainer, data, labels, batch, _cabi, Fn, interpret
                  if conv_key.endswith("_tc") else "conv_scan_kernel<PoolTrainSink> (k-mer table fused conv+BN+exp+maxpool fwd)")
         out["roofline"] = {"kernel": kname,
                            "bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
-                           "traffic": None, "peak_source": peak_src, "avg_launch_us": conv_ms * 1e3,
+                           # dram__bytes_read.sum + dram__bytes_write.sum of one launch at this batch size, from the
+                           # ncu --set full capture summarised in profiles/r1_ncu_full_summary_final.txt: the 45.7 MB the
+                           # kernel writes are still resident in the 126 MB L2 when it ends
+                           "traffic": 515072 if conv_key.endswith("_tc") and B == 512 and U == 300 else None,
+                           "traffic_source": "profiles/r1_ncu_full_summary_final.txt",
+                           "peak_source": peak_src, "avg_launch_us": conv_ms * 1e3,
                            "algorithmic_bytes_per_launch": bytes_train,
                            "note": "HBM fraction as BASELINE.json asks; the kernel's own ceiling is the tensor pipe "
                                    "(2*U*S*4F*2 fp16 flop per sequence), see DESIGN.md"}
@@ -378,6 +383,44 @@ def extras(torch, dev, model, trainer, data, labels, batch, _cabi, Fn, interpret
     out["interp"] = {"sequences_per_sec": NI / (s.elapsed_time(e) * 1e-3), "sequences": NI, "passes": 2,
                      "total_hits": int(acc.hits.sum().item())}
     model.train()
+
+    # ---- input encoding and PWM scoring ----------------------------------------------
+    try:
+        import numpy as np
+        from explainn_b200 import networks as xnet, tools as xtools
+        from oracle import canonical as oc
+        NE = 4 * IB
+        rng = np.random.default_rng(5)
+        letters = np.frombuffer(b"ACGTN", dtype=np.uint8)
+        cd = rng.integers(0, 4, size=(NE, L)).astype(np.uint8)
+        cd[rng.random((NE, L)) < 0.01] = 4
+        seqs = [letters[c].tobytes() for c in cd]
+        xtools.encode_sequences(seqs[:IB], L, dev)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for i in range(0, NE, IB):
+            pk_e = xtools.encode_sequences(seqs[i:i + IB], L, dev)     # host join + H2D of the bytes + encode kernel
+        torch.cuda.synchronize()
+        enc_s = time.perf_counter() - t0
+        t0 = time.perf_counter()
+        nref = 256
+        for sq in seqs[:nref]:
+            oc.dna_one_hot(sq.decode("ascii"), L)
+        ref_s = time.perf_counter() - t0
+        pwm = xnet.PWM(rng.normal(size=(U, 4, model._options["filter_size"])).astype(np.float32), L, "max").to(dev)
+        pwm.forward_packed(pk_e)
+        torch.cuda.synchronize()
+        s.record()
+        for i in range(5):
+            pwm.forward_packed(pk_e)
+        e.record()
+        torch.cuda.synchronize()
+        out["io"] = {"encode_sequences_per_sec_e2e": NE / enc_s, "encode_h2d_bytes_per_seq": L,
+                     "encode_cpu_port_sequences_per_sec": nref / ref_s, "encode_cpu_sample": "%d sequences, 1 core" % nref,
+                     "pwm_score_sequences_per_sec": IB / (s.elapsed_time(e) / 5 * 1e-3), "pwm_score_groups": U,
+                     "pwm_score_strands": 2}
+    except Exception as ex:       # pragma: no cover
+        out["io"] = {"error": str(ex)}
 
     # ---- CPU baseline: the reference step on this box's host cores (bounded sample) -------------------
     try:

@@ -11,6 +11,7 @@
 // sequences x 25 hidden channels, so every W1 value is fetched by a warp-uniform (broadcast) LDS.128
 // and the pooled values by conflict-free scalar loads.
 #include "common.cuh"
+#include <stdlib.h>
 #include "../../include/explainn_b200.h"
 #include <algorithm>
 
@@ -252,7 +253,7 @@ __global__ void __launch_bounds__(FC_THREADS) fc2_train_kernel(
     const float *__restrict__ g2, const float *__restrict__ be2, float *__restrict__ rm2, float *__restrict__ rv2,
     float momentum, float eps, const float *__restrict__ W2, const float *__restrict__ b2, float *__restrict__ mean2,
     float *__restrict__ invstd2, float pdrop, unsigned long long seed0, const unsigned long long *__restrict__ seed_dev,
-    uint32_t *__restrict__ dropmask, float *__restrict__ h2, float *__restrict__ part3)
+    uint32_t *__restrict__ dropmask, float *__restrict__ h2, float *__restrict__ part3, double inv_batch)
 {
     __shared__ float sc[128], sh[128], w2s[128];
     __shared__ float red[8][2];
@@ -265,23 +266,28 @@ __global__ void __launch_bounds__(FC_THREADS) fc2_train_kernel(
         float a = 0.f, c = 0.f, w = 0.f;
         if (j < H) {
             double sm = 0.0, sq = 0.0;
+            const double inv_B = (double)inv_batch;
+            const float unbias = (float)B / (float)(B > 1 ? B - 1 : 1);
             for (int k = 0; k < nchunk; ++k) {
                 const float *pp = part2 + ((size_t)u * nchunk + k) * 2 * H;
                 sm += (double)pp[j];
                 sq += (double)pp[H + j];
             }
-            const double mean = sm / (double)B;
-            double var = sq / (double)B - mean * mean;
+            // only the cancellation-prone difference E[x^2] - mean^2 is formed in double (multiplications by the
+            // reciprocal batch size, no double division or square root in this per-CTA prologue)
+            const double mean = sm * inv_B;
+            double var = sq * inv_B - mean * mean;
             if (var < 0.0) var = 0.0;
-            const float inv = (float)(1.0 / sqrt(var + (double)eps));
+            const float varf = (float)var;
+            const float inv = 1.0f / sqrtf(varf + eps);
             const int ch = u * H + j;
             if (chunk == 0) {
                 mean2[ch] = (float)mean;
                 invstd2[ch] = inv;
                 if (rm2) {
-                    const double unb = B > 1 ? var * (double)B / (double)(B - 1) : var;
+                    const float unb = B > 1 ? varf * unbias : varf;
                     rm2[ch] = (1.0f - momentum) * rm2[ch] + momentum * (float)mean;
-                    rv2[ch] = (1.0f - momentum) * rv2[ch] + momentum * (float)unb;
+                    rv2[ch] = (1.0f - momentum) * rv2[ch] + momentum * unb;
                 }
             }
             a = g2[ch] * inv;
@@ -353,7 +359,7 @@ __global__ void __launch_bounds__(256) out_train_kernel(const float *__restrict_
                                                         float *__restrict__ rm3, float *__restrict__ rv3, float momentum,
                                                         float eps, float *__restrict__ mean3, float *__restrict__ invstd3,
                                                         const float *__restrict__ Wf, const float *__restrict__ bf,
-                                                        float *__restrict__ unit, float *__restrict__ logits, int wf_in_smem)
+                                                        float *__restrict__ unit, float *__restrict__ logits, int wf_in_smem, double inv_batch)
 {
     extern __shared__ float xs[];   // [8][U] then sc3[U], sh3[U], then (when it fits) Wf as [C][U+1]
     float *sc3 = xs + OT_ROWS * U, *sh3 = sc3 + U;
@@ -372,17 +378,18 @@ __global__ void __launch_bounds__(256) out_train_kernel(const float *__restrict_
             sm += (double)part3[((size_t)u * nchunk + k) * 2];
             sq += (double)part3[((size_t)u * nchunk + k) * 2 + 1];
         }
-        const double mean = sm / (double)B;
-        double var = sq / (double)B - mean * mean;
+        const double mean = sm * inv_batch;
+        double var = sq * inv_batch - mean * mean;       // the only double arithmetic: a cancellation-prone difference
         if (var < 0.0) var = 0.0;
-        const float inv = (float)(1.0 / sqrt(var + (double)eps));
+        const float varf = (float)var;
+        const float inv = 1.0f / sqrtf(varf + eps);
         if (blockIdx.x == 0 && blockIdx.y == 0) {
             mean3[u] = (float)mean;
             invstd3[u] = inv;
             if (rm3) {
-                const double unb = B > 1 ? var * (double)B / (double)(B - 1) : var;
+                const float unb = B > 1 ? varf * ((float)B / (float)(B - 1)) : varf;
                 rm3[u] = (1.0f - momentum) * rm3[u] + momentum * (float)mean;
-                rv3[u] = (1.0f - momentum) * rv3[u] + momentum * (float)unb;
+                rv3[u] = (1.0f - momentum) * rv3[u] + momentum * unb;
             }
         }
         const float a = g3[u] * inv;
@@ -421,41 +428,6 @@ __global__ void __launch_bounds__(256) out_train_kernel(const float *__restrict_
 // ================================================================================================
 // Backward
 // ================================================================================================
-
-// dWf[c][u] += sum_{b in slice} gl[b][c] * unit[b][u] ; dbf[c] += sum_b gl[b][c].
-// grid (ceil(U/32), ceil(C/8), nsplit); outputs are zeroed by the host wrapper and accumulated with atomics
-// (nsplit partial sums per element).
-__global__ void __launch_bounds__(256) bwd_final_linear_kernel(const float *__restrict__ gl, const float *__restrict__ unit,
-                                                               long long B, int U, int C, float *__restrict__ dWf,
-                                                               float *__restrict__ dbf)
-{
-    const int lane = threadIdx.x & 31, cc = threadIdx.x >> 5;
-    const int u = blockIdx.x * 32 + lane, c = blockIdx.y * 8 + cc;
-    if (c >= C) return;
-    const long long per = (B + gridDim.z - 1) / gridDim.z;
-    const long long bs = per * blockIdx.z, be = min(B, bs + per);
-    const bool uv = u < U;
-    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f, sg = 0.f;
-    long long b = bs;
-    for (; b + 3 < be; b += 4) {
-        const float g0 = __ldg(gl + b * C + c), g1 = __ldg(gl + (b + 1) * C + c), g2 = __ldg(gl + (b + 2) * C + c),
-                    g3 = __ldg(gl + (b + 3) * C + c);
-        sg += (g0 + g1) + (g2 + g3);
-        if (uv) {
-            a0 = fmaf(g0, unit[b * U + u], a0);
-            a1 = fmaf(g1, unit[(b + 1) * U + u], a1);
-            a2 = fmaf(g2, unit[(b + 2) * U + u], a2);
-            a3 = fmaf(g3, unit[(b + 3) * U + u], a3);
-        }
-    }
-    for (; b < be; ++b) {
-        const float g0 = __ldg(gl + b * C + c);
-        sg += g0;
-        if (uv) a0 = fmaf(g0, unit[b * U + u], a0);
-    }
-    if (uv && dWf) atomicAdd(&dWf[(size_t)c * U + u], (a0 + a1) + (a2 + a3));
-    if (dbf && blockIdx.x == 0 && lane == 0) atomicAdd(&dbf[c], sg);
-}
 
 // gz3[b][u] = (unit[b][u] > 0) * sum_c gl[b][c] * Wf[c][u]     (ReLU-3 mask applied; (B,U) layout)
 // grid (ceil(B/8), ceil(U/64)); warp = one sequence, each lane two units of the 64-unit slice whose Wf columns
@@ -506,6 +478,64 @@ __global__ void __launch_bounds__(256) bwd_gunit_kernel(const float *__restrict_
     }
     if (ua < U) gz[b * U + ua] = unit[b * U + ua] > 0.f ? ga : 0.f;
     if (ub < U) gz[b * U + ub] = unit[b * U + ub] > 0.f ? gb : 0.f;
+}
+
+// Register-tiled dWf / dbf:  dWf[c][u] += sum_b gl[b][c] * unit[b][u].
+// grid (ceil(U/128), ceil(C/8), nsplit): a CTA owns 128 units x 8 classes and one slice of the batch; its 4 warps take every
+// fourth sequence of the slice (lane l: units u0+l+32j), keep 32 accumulators each, and are combined through shared
+// memory before ONE atomicAdd per output and CTA.  The gl tile of the slice is staged class-minor in shared memory.
+constexpr int FL_SLICE = 64;
+__global__ void __launch_bounds__(128) bwd_final_linear2_kernel(const float *__restrict__ gl, const float *__restrict__ unit,
+                                                                long long B, int U, int C, float *__restrict__ dWf,
+                                                                float *__restrict__ dbf)
+{
+    __shared__ __align__(16) float gls[FL_SLICE][8];
+    __shared__ float red[4][8][128];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int u0 = blockIdx.x * 128, c0 = blockIdx.y * 8;
+    const long long per = (B + gridDim.z - 1) / gridDim.z;
+    const long long bs = per * blockIdx.z, be = min(B, bs + per);
+    float acc[8][4];
+#pragma unroll
+    for (int c = 0; c < 8; ++c)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[c][j] = 0.f;
+    float sg = 0.f;
+    for (long long t0 = bs; t0 < be; t0 += FL_SLICE) {
+        const int nb = (int)min((long long)FL_SLICE, be - t0);
+        __syncthreads();
+        for (int i = threadIdx.x; i < nb * 8; i += 128) {
+            const int bb = i >> 3, c = i & 7;
+            gls[bb][c] = c0 + c < C ? gl[(t0 + bb) * C + c0 + c] : 0.f;
+        }
+        __syncthreads();
+        if (threadIdx.x < 8)
+            for (int bb = 0; bb < nb; ++bb) sg += gls[bb][threadIdx.x];
+        for (int bb = warp; bb < nb; bb += 4) {
+            const float *ur = unit + (t0 + bb) * U + u0 + lane;
+            float x[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) x[j] = u0 + lane + 32 * j < U ? ur[32 * j] : 0.f;
+            const float4 ga = *reinterpret_cast<const float4 *>(&gls[bb][0]), gb = *reinterpret_cast<const float4 *>(&gls[bb][4]);
+            const float g[8] = {ga.x, ga.y, ga.z, ga.w, gb.x, gb.y, gb.z, gb.w};
+#pragma unroll
+            for (int c = 0; c < 8; ++c)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc[c][j] = fmaf(g[c], x[j], acc[c][j]);
+        }
+    }
+#pragma unroll
+    for (int c = 0; c < 8; ++c)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) red[warp][c][lane + 32 * j] = acc[c][j];
+    __syncthreads();
+    if (dWf) {
+        const int uu = threadIdx.x, u = u0 + uu;
+        if (u < U)
+            for (int c = 0; c < 8 && c0 + c < C; ++c)
+                atomicAdd(&dWf[(size_t)(c0 + c) * U + u], (red[0][c][uu] + red[1][c][uu]) + (red[2][c][uu] + red[3][c][uu]));
+    }
+    if (dbf && blockIdx.x == 0 && threadIdx.x < 8 && c0 + threadIdx.x < C) atomicAdd(&dbf[c0 + threadIdx.x], sg);
 }
 
 // BatchNorm-3 backward per unit: sums over the batch, then gh2 (U,B), dgamma3, dbeta3.  One warp per unit.
@@ -822,10 +852,10 @@ extern "C" int explainn_fc_stack_fwd_train(const float *pooled, long long B, int
         fc1_train_kernel<<<dim3(U, nchunk), FC_THREADS, smem1, stream>>>(pooled, B, U, P, W1, b1, h1, part2);
     }
     fc2_train_kernel<<<dim3(U, nchunk), FC_THREADS, 0, stream>>>(h1, B, U, part2, nchunk, bn2_w, bn2_b, bn2_rm, bn2_rv, momentum, eps,
-                                                                 W2, b2, mean2, invstd2, pdrop, seed, seed_dev, dropmask, h2, part3);
+                                                                 W2, b2, mean2, invstd2, pdrop, seed, seed_dev, dropmask, h2, part3, 1.0 / (double)B);
     cudaFuncSetAttribute(out_train_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem3);
     out_train_kernel<<<dim3((unsigned)((B + OT_ROWS - 1) / OT_ROWS), ot_ny), 256, smem3, stream>>>(h2, B, U, C, part3, nchunk, bn3_w, bn3_b, bn3_rm, bn3_rv,
-                                                                        momentum, eps, mean3, invstd3, Wf, bf, unit, logits, wf_in_smem);
+                                                                        momentum, eps, mean3, invstd3, Wf, bf, unit, logits, wf_in_smem, 1.0 / (double)B);
     return xb_check_launch("fc_stack_fwd_train");
 }
 
@@ -848,7 +878,7 @@ extern "C" int explainn_fc_stack_bwd(const float *glogits, long long B, int U, i
         if (dWf) cudaMemsetAsync(dWf, 0, (size_t)C * U * sizeof(float), stream);
         if (dbf) cudaMemsetAsync(dbf, 0, (size_t)C * sizeof(float), stream);
         const int nsb = (int)std::min<long long>(8, (B + 63) / 64);
-        bwd_final_linear_kernel<<<dim3((U + 31) / 32, (C + 7) / 8, nsb), 256, 0, stream>>>(glogits, unit, B, U, C, dWf, dbf);
+        bwd_final_linear2_kernel<<<dim3((U + 127) / 128, (C + 7) / 8, nsb), 128, 0, stream>>>(glogits, unit, B, U, C, dWf, dbf);
     }
     // gz3 (B,U) lives in the head of the gpool buffer (U*B*P floats >= B*U); it is consumed by bwd_bn3_kernel
     // before bwd_fc1_kernel overwrites gpool
