@@ -257,8 +257,10 @@ def main():
             "dtype": "f32", "data": "synthetic", "config": config_dict(n_gpus), "clocks": clocks, "e2e": e2e,
             "gpu_launches": launches, "final_loss": final_loss, "cuda_graph": trainer._graph is not None}
 
-    if rank == 0 and not args.no_extras:
-        line.update(extras(torch, dev, model, trainer, data, labels, batch, _cabi, Fn, interpretation))
+    if not args.no_extras:
+        # every rank takes part in the per-kernel breakdown (its eager steps contain the gradient all-reduce);
+        # the remaining legs use no collective and run on rank 0 only
+        line.update(extras(torch, dev, model, trainer, data, labels, batch, _cabi, Fn, interpretation, rank, world))
     if rank == 0:
         print(json.dumps(line), flush=True)
     if world > 1:
@@ -266,7 +268,7 @@ def main():
         dist.destroy_process_group()
 
 
-def extras(torch, dev, model, trainer, data, labels, batch, _cabi, Fn, interpretation):
+def extras(torch, dev, model, trainer, data, labels, batch, _cabi, Fn, interpretation, rank=0, world=1):
     """Roofline of the fused conv kernel, per-kernel breakdown of the step, inference / interpretation
     throughput, CPU baseline.  Rank 0 only, outside the headline timed region."""
     out = {}
@@ -304,6 +306,8 @@ def extras(torch, dev, model, trainer, data, labels, batch, _cabi, Fn, interpret
     for mod in (_cabi, autograd_fn, functional, xtrain):
         mod.call = real_call
     trainer._graph, trainer.use_graph = g_saved, True
+    if rank != 0:
+        return out
     agg = {}
     for name, s, e in records:
         agg[name] = agg.get(name, 0.0) + s.elapsed_time(e)
@@ -422,7 +426,9 @@ def extras(torch, dev, model, trainer, data, labels, batch, _cabi, Fn, interpret
     except Exception as ex:       # pragma: no cover
         out["io"] = {"error": str(ex)}
 
-    # ---- CPU baseline: the reference step on this box's host cores (bounded sample) -------------------
+    # ---- CPU baseline: the reference step on this box's host cores (bounded sample; N = 1 only) -------
+    if world > 1:
+        return out
     try:
         v, sec, threads = cpu_port_step_throughput(B, steps=2, warmup=1)
         out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",

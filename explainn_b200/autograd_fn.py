@@ -114,9 +114,12 @@ def _const(dev, U):
     return _CONST[key]
 
 
-def train_backward(model, ws, gout, params=None, grads=None, wrt_unit=False):
+def train_backward(model, ws, gout, params=None, grads=None, wrt_unit=False, between=None):
     """Backward kernels.  gout: (B,C) gradient w.r.t. the logits, or (B,U) w.r.t. the unit outputs when
-    `wrt_unit`.  `grads`: optional list of 14 preallocated gradient tensors (e.g. views into a flat buffer)."""
+    `wrt_unit`.  `grads`: optional list of 14 preallocated gradient tensors (e.g. views into a flat buffer).
+    `between`: optional callable run after the FC-stack backward (grads[4:] final) and before the conv backward
+    (grads[:4]); the data-parallel trainer uses it to start the all-reduce of the FC-stack gradients early, or to
+    split the step into two CUDA graphs (it may return False to stop after the first half)."""
     L = model.linears
     if params is None:
         params = [p.detach() for p in _params(model)]
@@ -137,6 +140,19 @@ def train_backward(model, ws, gout, params=None, grads=None, wrt_unit=False):
          None if wrt_unit else ptr(Wf), ws.pdrop, ws.seed, ptr(ws.seed_dev), ptr(ws.dropmask), ptr(gh2), ptr(pb2), ptr(dW1p), ptr(gpool), ptr(dW1), ptr(db1),
          ptr(dg2), ptr(dbe2), ptr(dW2), ptr(db2), ptr(dg3), ptr(dbe3), None if wrt_unit else ptr(dWf),
          None if wrt_unit else ptr(dbf), stream())
+    if between is not None and between(ws, gpool, params, grads, wrt_unit) is False:
+        return grads
+    return train_backward_conv(model, ws, gpool, params, grads, wrt_unit)
+
+
+def train_backward_conv(model, ws, gpool, params, grads, wrt_unit=False):
+    """Second half of the backward: sparse conv / BatchNorm-1 gradients from d(pooled)."""
+    L = model.linears
+    (cw, cb, g1, b1n) = params[:4]
+    (dcw, dcb, dg1, db1n) = grads[:4]
+    dWf, dbf = grads[12], grads[13]
+    B, U, F = ws.B, ws.U, ws.F
+    f32 = dict(dtype=torch.float32, device=gpool.device)
     nsplit = Fn._cabi.lib.explainn_conv_bwd_nsplit(U)
     partial = torch.empty((nsplit, U, 4 * F + 2), **f32)
     call("explainn_conv_pool_bwd", ptr(ws.pk.codes), ptr(ws.pk.nmask), B, ws.pk.L, U, F, ptr(gpool), ptr(ws.pooled),

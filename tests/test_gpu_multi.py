@@ -1,0 +1,84 @@
+"""Two-GPU data-parallel step over NCCL (skipped on a one-GPU box): after one FusedTrainer step with the gradient
+all-reduce overlapped with the conv backward, both ranks hold identical parameters, and the reduced gradient equals
+the mean of the two ranks' gradients computed by one process."""
+import os
+import subprocess
+import sys
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+WORKER = r'''
+import os, sys
+import torch, torch.distributed as dist
+sys.path.insert(0, sys.argv[1]); sys.path.insert(0, os.path.join(sys.argv[1], "tests"))
+from util import onehot_from_codes, random_codes
+from explainn_b200 import networks, train as xtrain, autograd_fn
+rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+torch.cuda.set_device(rank)
+dev = "cuda:%d" % rank
+dist.init_process_group("nccl", device_id=torch.device(dev))
+U, L, C, F, B = 20, 80, 3, 19, 32
+use_graph = sys.argv[3] == "graph"
+torch.manual_seed(0)
+m = networks.ExplaiNN(U, L, C, F).to(dev).train()
+m.linears[9].eval()                                   # dropout off: the gradients are then a deterministic function of the batch
+ref = networks.ExplaiNN(U, L, C, F).to(dev).train()
+ref.load_state_dict(m.state_dict()); ref.linears[9].eval()
+xs = [torch.from_numpy(onehot_from_codes(random_codes(B, L, 100 + r, n_frac=0.02))).to(dev) for r in range(world)]
+ys = [(torch.rand(B, C, generator=torch.Generator().manual_seed(200 + r)) < 0.5).float().to(dev) for r in range(world)]
+opt = torch.optim.Adam(m.parameters(), lr=1e-2)
+tr = xtrain.FusedTrainer(m, torch.nn.BCEWithLogitsLoss(), opt, dropout_seed=1, use_graph=use_graph)
+for s in range(2):                                   # step 2 captures the graphs (when enabled), step 3 replays them
+    tr.step(xs[rank], ys[rank])
+# single-process restatement of step 3: both ranks' gradients through the autograd path of the same kernels, then the mean
+ref.load_state_dict(m.state_dict())
+crit = torch.nn.BCEWithLogitsLoss()
+mean_g = None
+for r in range(world):
+    ref.zero_grad()
+    crit(ref(xs[r]), ys[r]).backward()
+    g = [p.grad.clone() for p in autograd_fn._params(ref)]
+    mean_g = g if mean_g is None else [a + b for a, b in zip(mean_g, g)]
+mean_g = [g / world for g in mean_g]
+tr.step(xs[rank], ys[rank])
+torch.cuda.synchronize()
+got = [v / world for v in tr.views_g]                # the flat buffer holds the SUM over ranks; Adam applies 1/world
+err = 0.0
+for i, (a, b) in enumerate(zip(got, mean_g)):
+    # index 3 = BatchNorm-1 beta: its gradient is mathematically zero, both sides hold rounding noise (test_gpu_train.py)
+    scale = float(mean_g[2].abs().max()) * 1e4 if i == 3 else float(b.abs().max())
+    if scale > 0:
+        err = max(err, float((a - b).abs().max()) / scale)
+    else:
+        err = max(err, float(a.abs().max()))
+flat = tr.flat_p.clone()
+others = [torch.empty_like(flat) for _ in range(world)]
+dist.all_gather(others, flat)
+same = all(torch.equal(o, others[0]) for o in others)
+if rank == 0:
+    open(sys.argv[2], "w").write("%d %g %d\n" % (int(same), err, int(tr._graph2 is not None)))
+dist.barrier()
+dist.destroy_process_group()
+'''
+
+
+@pytest.mark.parametrize("overlap", ["0", "1"])
+@pytest.mark.parametrize("mode", ["eager", "graph"])
+def test_two_gpu_step_allreduce(tmp_path, mode, overlap):
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    script = tmp_path / "worker.py"
+    script.write_text(WORKER)
+    out = tmp_path / "out.txt"
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+           "--master-port", "29533", str(script), ROOT, str(out), mode]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300, env=dict(os.environ, XB_DP_OVERLAP=overlap))
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    same, err, split = out.read_text().split()
+    assert int(same) == 1, "ranks diverged"
+    assert float(err) < 1e-4, (same, err, split)                    # same kernels on both paths; only summation order differs
+    assert int(split) == (1 if mode == "graph" and overlap == "1" else 0)
