@@ -412,11 +412,12 @@ def extras(torch, dev, model, trainer, data, labels, batch, _cabi, Fn, interpret
             oc.dna_one_hot(sq.decode("ascii"), L)
         ref_s = time.perf_counter() - t0
         pwm = xnet.PWM(rng.normal(size=(U, 4, model._options["filter_size"])).astype(np.float32), L, "max").to(dev)
-        pwm.forward_packed(pk_e)
+        pk_s = model._pack(data[:IB])          # the same N-free sequences the other legs use
+        pwm.forward_packed(pk_s)
         torch.cuda.synchronize()
         s.record()
         for i in range(5):
-            pwm.forward_packed(pk_e)
+            pwm.forward_packed(pk_s)
         e.record()
         torch.cuda.synchronize()
         out["io"] = {"encode_sequences_per_sec_e2e": NE / enc_s, "encode_h2d_bytes_per_seq": L,
