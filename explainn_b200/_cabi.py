@@ -50,6 +50,9 @@ SIGNATURES = {
     "explainn_pwm_score": [_P, _P, _LL, _I, _I, _I, _P, _P, _P, _I, _I, _P, _P],
     "explainn_fc_stack_fwd_eval": [_P, _LL, _I, _I] + [_P] * 12 + [_F, _P, _P],
     "explainn_linear_fwd": [_P, _LL, _I, _I, _P, _P, _P, _P],
+    "explainn_fc1_stack_fwd_eval": [_P, _LL, _I, _I] + [_P] * 6 + [_F, _P, _P],
+    "explainn_fc1_stack_fwd_train": [_P, _LL, _I, _I, _I] + [_P] * 6 + [_F, _F] + [_P] * 8 + [_P],
+    "explainn_fc1_stack_bwd": [_P, _LL, _I, _I, _I] + [_P] * 8 + [_P] * 9 + [_P],
     "explainn_input_cooc_stats": [_P, _P, _LL, _I, _I, _P, _P],
     "explainn_bn1_batch_stats": [_P, _P, _P, _I, _I, _LL, _F, _P, _P, _P, _P, _P, _P, _P],
     "explainn_fc_nchunk": [_LL],

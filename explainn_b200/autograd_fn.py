@@ -25,17 +25,31 @@ def _next_dropout_seed():
     return (base * 0x9E3779B1 + _SEED_STATE["counter"] * 0x85EBCA77C2B2AE63) & 0xFFFFFFFFFFFFFFFF
 
 
+def _num_fc(model):
+    return model._options.get("num_fc", 2)
+
+
 def _params(model):
+    """Parameters in state_dict order; the conv / BatchNorm-1 tensors always come first."""
     L = model.linears
+    if _num_fc(model) == 0:        # networks.py:73-80 (eval only here: _check_modes refuses to train it)
+        return (L[0].weight, L[0].bias, L[1].weight, L[1].bias, model.final.weight, model.final.bias)
+    if _num_fc(model) == 1:        # networks.py:82-95
+        return (L[0].weight, L[0].bias, L[1].weight, L[1].bias, L[6].weight, L[6].bias, L[7].weight, L[7].bias,
+                model.final.weight, model.final.bias)
     return (L[0].weight, L[0].bias, L[1].weight, L[1].bias, L[6].weight, L[6].bias, L[7].weight, L[7].bias,
             L[10].weight, L[10].bias, L[11].weight, L[11].bias, model.final.weight, model.final.bias)
 
 
 def _check_modes(model):
     L = model.linears
-    if not (L[1].training and L[7].training and L[11].training):
-        raise NotImplementedError("explainn_b200: in train() mode all three BatchNorm layers must be in training mode")
-    for bn in (L[1], L[7], L[11]):
+    nfc = _num_fc(model)
+    if nfc not in (1, 2):
+        raise NotImplementedError("explainn_b200: training is built for num_fc = 1 and 2; num_fc = %d runs in eval() mode only" % nfc)
+    bns = (L[1], L[7]) if nfc == 1 else (L[1], L[7], L[11])
+    if not all(bn.training for bn in bns):
+        raise NotImplementedError("explainn_b200: in train() mode all BatchNorm layers must be in training mode")
+    for bn in bns:
         if bn.momentum is None or not bn.track_running_stats or not bn.affine:
             raise NotImplementedError("explainn_b200: BatchNorm layers must keep the reference configuration "
                                       "(momentum=0.1, affine, track_running_stats)")
@@ -53,6 +67,8 @@ def train_forward(model, x, params=None, seed=None, seed_dev=None):
     L = model.linears
     if params is None:
         params = [p.detach() for p in _params(model)]
+    if _num_fc(model) == 1:
+        return _train_forward_fc1(model, x, params)
     (cw, cb, g1, b1n, W1, b1, g2, be2, W2, b2, g3, be3, Wf, bf) = params
     o = model._options
     U, F, C = o["num_cnns"], o["filter_size"], o["num_classes"]
@@ -104,6 +120,74 @@ def train_forward(model, x, params=None, seed=None, seed_dev=None):
     return ws
 
 
+def _train_forward_conv(model, x, cw, cb, g1, b1n):
+    """Packing, BatchNorm-1 batch statistics and the fused conv -> BN -> exp -> pool forward (shared by the variants)."""
+    o = model._options
+    U, F, C = o["num_cnns"], o["filter_size"], o["num_classes"]
+    pk = model._pack(x)
+    B = pk.B
+    if B < 2:
+        raise ValueError("Expected more than 1 value per channel when training, got input size %s" % (tuple(x.shape),))
+    dev = pk.codes.device
+    bn1 = model.linears[1]
+    ws = TrainWorkspace()
+    ws.pk, ws.B, ws.U, ws.C, ws.F = pk, B, U, C, F
+    S = pk.L - F + 1
+    ws.P = model.pooled_length
+    ws.M = Fn.input_cooc_stats(pk, F)
+    ws.mean1, ws.var1, ws.Mw = Fn.bn1_batch_stats(ws.M, cw, cb, B * S, bn1.momentum, bn1.running_mean, bn1.running_var,
+                                                  bn1.num_batches_tracked)
+    ones, zeros = _const(dev, U)
+    if getattr(model, "conv_backend", "tc") == "tc":
+        tcp = Fn.conv_tc_prepare(cw, cb, ones, zeros, ws.mean1, ws.var1, bn1.eps)
+        ws.pooled, ws.xhat, ws.idx = Fn.conv_pool_fwd_train_tc(pk, tcp, g1, b1n)
+    else:
+        prep = Fn.conv_prepare(cw, cb, ones, zeros, ws.mean1, ws.var1, bn1.eps)
+        ws.pooled, ws.xhat, ws.idx = Fn.conv_pool_fwd_train(pk, prep, g1, b1n)
+    ws.nchunk = Fn.fc_nchunk(B)
+    ws.pdrop, ws.seed, ws.seed_dev, ws.dropmask = 0.0, 0, None, None
+    return ws
+
+
+def _train_forward_fc1(model, x, params):
+    """num_fc = 1 (networks.py:82-95): pooled -> FC (P -> 1) -> BatchNorm -> ReLU -> final Linear."""
+    (cw, cb, g1, b1n, W1, b1, g3, be3, Wf, bf) = params
+    ws = _train_forward_conv(model, x, cw, cb, g1, b1n)
+    bn3 = model.linears[7]
+    B, U, P, C = ws.B, ws.U, ws.P, ws.C
+    f32 = dict(dtype=torch.float32, device=ws.pooled.device)
+    ws.h2 = torch.empty((U, B), **f32)
+    part3 = torch.empty((U, ws.nchunk, 2), **f32)
+    ws.mean3 = torch.empty(U, **f32)
+    ws.invstd3 = torch.empty(U, **f32)
+    ws.unit = torch.empty((B, U), **f32)
+    ws.logits = torch.empty((B, C), **f32)
+    call("explainn_fc1_stack_fwd_train", ptr(ws.pooled), B, U, P, C, ptr(W1), ptr(b1), ptr(g3), ptr(be3), ptr(bn3.running_mean),
+         ptr(bn3.running_var), float(bn3.momentum), float(bn3.eps), ptr(Wf), ptr(bf), ptr(ws.h2), ptr(part3), ptr(ws.mean3),
+         ptr(ws.invstd3), ptr(ws.unit), ptr(ws.logits), stream())
+    bn3.num_batches_tracked.add_(1)
+    return ws
+
+
+def _train_backward_fc1(model, ws, gout, params, grads, wrt_unit, between):
+    (cw, cb, g1, b1n, W1, b1, g3, be3, Wf, bf) = params
+    if grads is None:
+        grads = [torch.empty_like(p) for p in params]
+    (dcw, dcb, dg1, db1n, dW1, db1, dg3, dbe3, dWf, dbf) = grads
+    B, U, P, C = ws.B, ws.U, ws.P, ws.C
+    f32 = dict(dtype=torch.float32, device=gout.device)
+    gout = gout.contiguous()
+    gh2 = torch.empty((U, B), **f32)
+    dWp = torch.empty((ws.nchunk, U, P), **f32)
+    gpool = torch.empty((B, U, P), **f32)
+    call("explainn_fc1_stack_bwd", ptr(gout), B, U, P, C, ptr(ws.pooled), ptr(ws.h2), ptr(ws.unit), ptr(W1), ptr(g3), ptr(ws.mean3),
+         ptr(ws.invstd3), None if wrt_unit else ptr(Wf), ptr(gh2), ptr(dWp), ptr(gpool), ptr(dW1), ptr(db1), ptr(dg3), ptr(dbe3),
+         None if wrt_unit else ptr(dWf), None if wrt_unit else ptr(dbf), stream())
+    if between is not None and between(ws, gpool, params, grads, wrt_unit) is False:
+        return grads
+    return train_backward_conv(model, ws, gpool, params, grads, wrt_unit)
+
+
 _CONST = {}
 
 
@@ -123,6 +207,8 @@ def train_backward(model, ws, gout, params=None, grads=None, wrt_unit=False, bet
     L = model.linears
     if params is None:
         params = [p.detach() for p in _params(model)]
+    if _num_fc(model) == 1:
+        return _train_backward_fc1(model, ws, gout, params, grads, wrt_unit, between)
     (cw, cb, g1, b1n, W1, b1, g2, be2, W2, b2, g3, be3, Wf, bf) = params
     B, U, P, C, F = ws.B, ws.U, ws.P, ws.C, ws.F
     dev = gout.device
@@ -150,7 +236,7 @@ def train_backward_conv(model, ws, gpool, params, grads, wrt_unit=False):
     L = model.linears
     (cw, cb, g1, b1n) = params[:4]
     (dcw, dcb, dg1, db1n) = grads[:4]
-    dWf, dbf = grads[12], grads[13]
+    dWf, dbf = grads[-2], grads[-1]
     B, U, F = ws.B, ws.U, ws.F
     f32 = dict(dtype=torch.float32, device=gpool.device)
     nsplit = Fn._cabi.lib.explainn_conv_bwd_nsplit(U)
@@ -179,7 +265,7 @@ class _ExplaiNNTrainFn(torch.autograd.Function):
         need = ctx.needs_input_grad[3:]
         out = [g if n else None for g, n in zip(grads, need)]
         if ctx.wrt_unit:
-            out[12] = out[13] = None
+            out[-2] = out[-1] = None
         ctx.ws = None
         return (None, None, None) + tuple(out)
 

@@ -378,7 +378,7 @@ struct ScoreSink {
     __device__ void end_seq(const ConvArgs &)
     {
         if (out_idx < 0) return;
-        const float v = p.use_max ? m : sum;
+        const float v = p.use_max == 2 ? det_expf(m) : (p.use_max ? m : sum);      // 2: exp(max z), the num_fc = 0 unit output
         if (p.accumulate) p.out[out_idx] = p.use_max ? fmaxf(p.out[out_idx], v) : __fadd_rn(p.out[out_idx], v);
         else p.out[out_idx] = v;
     }

@@ -769,6 +769,87 @@ __global__ void __launch_bounds__(FC_THREADS) bwd_fc1_kernel(
 template <int PH>
 size_t bwd_fc1_smem() { return ((size_t)BM * HS + (size_t)BM * 2 * PH + (size_t)H * 2 * PH) * 4; }
 
+// ================================================================================================
+// num_fc = 1 variant of the unit (explainn/models/networks.py:82-95): conv -> BN -> exp -> pool -> per-unit
+// FC (P -> 1) -> BatchNorm -> ReLU.  h2[u][b] = b1[u] + sum_p W[u][p] * pooled[b][u][p]; everything after it
+// (BatchNorm over the batch, ReLU, final Linear and their backward) reuses the kernels of the default stack.
+// grid (U, nchunk), 128 threads: thread = one sequence of the 128-row tile.
+// ================================================================================================
+template <bool EVAL>
+__global__ void __launch_bounds__(BM) fc1x1_fwd_kernel(const float *__restrict__ pooled, long long B, int U, int P,
+                                                       const float *__restrict__ W, const float *__restrict__ b1,
+                                                       const float *__restrict__ g, const float *__restrict__ be,
+                                                       const float *__restrict__ rm, const float *__restrict__ rv, float eps,
+                                                       float *__restrict__ h2, float *__restrict__ part3, float *__restrict__ unit_out)
+{
+    extern __shared__ float ws1[];      // W[u][0..P)
+    __shared__ float red[2][4];
+    const int u = blockIdx.x, chunk = blockIdx.y, nchunk = gridDim.y;
+    for (int p = threadIdx.x; p < P; p += blockDim.x) ws1[p] = W[(size_t)u * P + p];
+    __syncthreads();
+    const long long b = (long long)chunk * BM + threadIdx.x;
+    float h = 0.f;
+    if (b < B) {
+        const float *pr = pooled + ((size_t)b * U + u) * P;
+        float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+        int p = 0;
+        for (; p + 3 < P; p += 4) {
+            a0 = fmaf(ws1[p], pr[p], a0);
+            a1 = fmaf(ws1[p + 1], pr[p + 1], a1);
+            a2 = fmaf(ws1[p + 2], pr[p + 2], a2);
+            a3 = fmaf(ws1[p + 3], pr[p + 3], a3);
+        }
+        for (; p < P; ++p) a0 = fmaf(ws1[p], pr[p], a0);
+        h = ((a0 + a1) + (a2 + a3)) + b1[u];
+        if (EVAL) {
+            const float sc = g[u] / sqrtf(rv[u] + eps);
+            unit_out[b * U + u] = fmaxf((h - rm[u]) * sc + be[u], 0.f);
+        } else {
+            h2[(size_t)u * B + b] = h;
+        }
+    }
+    if (!EVAL) {
+        const float hv = b < B ? h : 0.f;
+        const float s = warp_sum(hv), q = warp_sum(hv * hv);
+        const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+        if (lane == 0) { red[0][warp] = s; red[1][warp] = q; }
+        __syncthreads();
+        if (threadIdx.x < 2) {
+            const float *r = red[threadIdx.x];
+            part3[((size_t)u * nchunk + chunk) * 2 + threadIdx.x] = (r[0] + r[1]) + (r[2] + r[3]);
+        }
+    }
+}
+
+// backward of the P -> 1 FC: gpool[b][u][p] = gh2[u][b] * W[u][p]; dW partial[chunk][u][p] = sum_b gh2[u][b] * pooled[b][u][p]
+__global__ void __launch_bounds__(BM) fc1x1_bwd_kernel(const float *__restrict__ pooled, const float *__restrict__ gh2, long long B,
+                                                       int U, int P, const float *__restrict__ W, float *__restrict__ gpool,
+                                                       float *__restrict__ dWp)
+{
+    extern __shared__ float sm1[];      // W[u][0..P), then gh[128], then the pooled tile [128][P+1]
+    float *ws1 = sm1, *ghs = sm1 + P, *tile = ghs + BM;
+    const int u = blockIdx.x, chunk = blockIdx.y;
+    const long long b0 = (long long)chunk * BM;
+    const int rows = (int)min((long long)BM, B - b0);
+    for (int p = threadIdx.x; p < P; p += blockDim.x) ws1[p] = W[(size_t)u * P + p];
+    ghs[threadIdx.x] = threadIdx.x < rows ? gh2[(size_t)u * B + b0 + threadIdx.x] : 0.f;
+    __syncthreads();
+    // rows of P floats: consecutive threads on consecutive addresses
+    const int n = rows * P;
+    for (int i = threadIdx.x; i < n; i += BM) {
+        const int r = i / P, p = i - r * P;
+        const size_t o = ((size_t)(b0 + r) * U + u) * P + p;
+        tile[r * (P + 1) + p] = pooled[o];
+        gpool[o] = ghs[r] * ws1[p];
+    }
+    __syncthreads();
+    for (int p = threadIdx.x; p < P; p += BM) {
+        float a = 0.f;
+        for (int r = 0; r < rows; ++r) a = fmaf(ghs[r], tile[r * (P + 1) + p], a);
+        dWp[((size_t)chunk * U + u) * P + p] = a;
+    }
+}
+
 }  // namespace
 
 extern "C" int explainn_fc_stack_fwd_eval(const float *pooled, long long B, int U, int P, const float *W1, const float *b1,
@@ -919,4 +1000,82 @@ extern "C" int explainn_fc_stack_bwd(const float *glogits, long long B, int U, i
     if (rc != XB_OK) return rc;
     // dW1 = sum over batch chunks of the per-tile partials
     return explainn_reduce_partials(dW1, dW1_partials, (long long)U * H * P, nchunk, stream);
+}
+
+
+// ---- num_fc = 1 entry points (explainn/models/networks.py:82-95) ---------------------------------------
+extern "C" int explainn_fc1_stack_fwd_eval(const float *pooled, long long B, int U, int P, const float *W, const float *b1,
+                                           const float *bn_w, const float *bn_b, const float *bn_rm, const float *bn_rv, float eps,
+                                           float *unit_out, cudaStream_t stream)
+{
+    XB_REQUIRE(pooled && W && b1 && bn_w && bn_b && bn_rm && bn_rv && unit_out, "fc1_stack_fwd_eval: null pointer");
+    XB_REQUIRE(B >= 0 && U >= 1 && P >= 1 && P <= 8192, "fc1_stack_fwd_eval: bad sizes");
+    if (B == 0) return XB_OK;
+    fc1x1_fwd_kernel<true><<<dim3(U, (unsigned)((B + BM - 1) / BM)), BM, (size_t)P * 4, stream>>>(pooled, B, U, P, W, b1, bn_w, bn_b, bn_rm, bn_rv,
+                                                                                               eps, nullptr, nullptr, unit_out);
+    return xb_check_launch("fc1_stack_fwd_eval");
+}
+
+extern "C" int explainn_fc1_stack_fwd_train(const float *pooled, long long B, int U, int P, int C, const float *W, const float *b1,
+                                            const float *bn_w, const float *bn_b, float *bn_rm, float *bn_rv, float momentum,
+                                            float eps, const float *Wf, const float *bf, float *h2, float *part3, float *mean3,
+                                            float *invstd3, float *unit, float *logits, cudaStream_t stream)
+{
+    XB_REQUIRE(pooled && W && b1 && bn_w && bn_b && Wf && bf && h2 && part3 && mean3 && invstd3 && unit && logits,
+               "fc1_stack_fwd_train: null pointer");
+    XB_REQUIRE(B >= 2 && U >= 1 && P >= 1 && P <= 8192 && C >= 1, "fc1_stack_fwd_train: bad sizes (train-mode BatchNorm needs B >= 2)");
+    const int nchunk = (int)((B + BM - 1) / BM);
+    fc1x1_fwd_kernel<false><<<dim3(U, nchunk), BM, (size_t)P * 4, stream>>>(pooled, B, U, P, W, b1, nullptr, nullptr, nullptr, nullptr, eps, h2,
+                                                                        part3, nullptr);
+    size_t smem3 = ((size_t)OT_ROWS * U + 2 * (size_t)U) * 4;
+    const int ot_ny = C >= 48 ? 3 : 1;
+    const size_t smem3_wf = smem3 + (size_t)((C + ot_ny - 1) / ot_ny) * (U + 1) * 4;
+    const int wf_in_smem = smem3_wf <= 200 * 1024;
+    if (wf_in_smem) smem3 = smem3_wf;
+    if (smem3 > 220 * 1024) {
+        xb_set_error("fc1_stack_fwd_train: %d units need %zu bytes of shared memory", U, smem3);
+        return XB_ERR_UNSUPPORTED;
+    }
+    cudaFuncSetAttribute(out_train_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem3);
+    out_train_kernel<<<dim3((unsigned)((B + OT_ROWS - 1) / OT_ROWS), ot_ny), 256, smem3, stream>>>(h2, B, U, C, part3, nchunk, bn_w, bn_b, bn_rm, bn_rv,
+                                                                                                 momentum, eps, mean3, invstd3, Wf, bf, unit, logits,
+                                                                                                 wf_in_smem, 1.0 / (double)B);
+    return xb_check_launch("fc1_stack_fwd_train");
+}
+
+extern "C" int explainn_fc1_stack_bwd(const float *glogits, long long B, int U, int P, int C, const float *pooled, const float *h2,
+                                      const float *unit, const float *W, const float *bn_w, const float *mean3, const float *invstd3,
+                                      const float *Wf, float *gh2, float *dW_partials, float *gpool, float *dW, float *db1,
+                                      float *dbn_w, float *dbn_b, float *dWf, float *dbf, cudaStream_t stream)
+{
+    XB_REQUIRE(glogits && pooled && h2 && unit && W && bn_w && mean3 && invstd3 && gh2 && dW_partials && gpool && dW,
+               "fc1_stack_bwd: null pointer");
+    XB_REQUIRE(B >= 2 && U >= 1 && P >= 1 && C >= 1, "fc1_stack_bwd: bad sizes");
+    const int nchunk = (int)((B + BM - 1) / BM);
+    if (Wf) {
+        if (dWf) cudaMemsetAsync(dWf, 0, (size_t)C * U * sizeof(float), stream);
+        if (dbf) cudaMemsetAsync(dbf, 0, (size_t)C * sizeof(float), stream);
+        const int nsb = (int)std::min<long long>(8, (B + 63) / 64);
+        bwd_final_linear2_kernel<<<dim3((U + 127) / 128, (C + 7) / 8, nsb), 128, 0, stream>>>(glogits, unit, B, U, C, dWf, dbf);
+    }
+    float *gz3 = gpool;      // (B,U) in the head of the (B,U,P) buffer, consumed before fc1x1_bwd_kernel overwrites it
+    const size_t smem_gu = ((size_t)8 * C + (size_t)C * GU_UT) * 4;
+    if (smem_gu > 200 * 1024) {
+        xb_set_error("fc1_stack_bwd: %d classes need %zu bytes of shared memory", C, smem_gu);
+        return XB_ERR_LIMIT;
+    }
+    cudaFuncSetAttribute(bwd_gunit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_gu);
+    bwd_gunit_kernel<<<dim3((unsigned)((B + 7) / 8), (U + GU_UT - 1) / GU_UT), 256, smem_gu, stream>>>(glogits, Wf, unit, B, U, C, gz3);
+    bwd_bn3_kernel<<<(U + 7) / 8, 256, 0, stream>>>(gz3, h2, B, U, bn_w, mean3, invstd3, gh2, dbn_w, dbn_b);
+    const size_t smem = ((size_t)P + BM + (size_t)BM * (P + 1)) * 4;
+    if (smem > 200 * 1024) {
+        xb_set_error("fc1_stack_bwd: pooled length %d needs %zu bytes of shared memory", P, smem);
+        return XB_ERR_UNSUPPORTED;
+    }
+    cudaFuncSetAttribute(fc1x1_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    fc1x1_bwd_kernel<<<dim3(U, nchunk), BM, smem, stream>>>(pooled, gh2, B, U, P, W, gpool, dW_partials);
+    if (db1) cudaMemsetAsync(db1, 0, (size_t)U * sizeof(float), stream);      // bias in front of a train-mode BatchNorm: exactly zero
+    int rc = xb_check_launch("fc1_stack_bwd");
+    if (rc != XB_OK) return rc;
+    return explainn_reduce_partials(dW, dW_partials, (long long)U * P, nchunk, stream);
 }

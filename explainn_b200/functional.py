@@ -93,7 +93,18 @@ def pwm_score(pk, prep, use_max, out=None):
         out = torch.empty((pk.B, prep.U), dtype=torch.float32, device=pk.codes.device)
     if pk.B:
         call("explainn_pwm_score", ptr(pk.codes), ptr(pk.nmask), pk.B, pk.L, prep.U, prep.F, ptr(prep.tables),
-             ptr(prep.wq_t), ptr(prep.shift), int(bool(use_max)), int(acc), ptr(out), stream())
+             ptr(prep.wq_t), ptr(prep.shift), int(use_max), int(acc), ptr(out), stream())      # 0 sum, 1 max, 2 exp(max)
+    return out
+
+
+def fc1_stack_fwd_eval(pooled, W, b1, bn, eps):
+    """num_fc = 1 unit in eval mode: pooled (B,U,P) -> relu(bn(W . pooled + b1)) as (B,U)."""
+    B, U, P = pooled.shape
+    g, be, rm, rv = bn
+    out = torch.empty((B, U), dtype=torch.float32, device=pooled.device)
+    if B:
+        call("explainn_fc1_stack_fwd_eval", ptr(pooled), B, U, P, ptr(W.contiguous()), ptr(b1), ptr(g), ptr(be), ptr(rm), ptr(rv),
+             float(eps), ptr(out), stream())
     return out
 
 

@@ -102,31 +102,55 @@ class ExplaiNN(nn.Module):
             "pool_stride": pool_stride,
             "weight_path": weight_path,
         }
-        if num_fc != 2 or pool_size != Fn.POOL or pool_stride != Fn.POOL:
+        if num_fc not in (0, 1, 2):
             raise NotImplementedError(
-                "explainn_b200 implements the reference default unit (num_fc=2, pool 7/7; networks.py:96-116); "
-                "num_fc=%d pool=%d/%d is not built yet" % (num_fc, pool_size, pool_stride))
+                "explainn_b200 implements num_fc = 0, 1 (networks.py:73-95) and the default 2 (networks.py:96-116); "
+                "num_fc=%d (extra 100 -> 100 layers, networks.py:117-145) is not built yet" % num_fc)
+        if num_fc != 0 and (pool_size != Fn.POOL or pool_stride != Fn.POOL):
+            raise NotImplementedError("explainn_b200: pool 7/7 only (the reference default); pool=%d/%d is not built yet"
+                                      % (pool_size, pool_stride))
         if filter_size > 24:
             raise NotImplementedError("explainn_b200: filter_size <= 24 (k-mer tables of the fused conv kernel)")
         U = num_cnns
-        P = Fn.pooled_len(input_length, filter_size, pool_size, pool_stride)
-        if P < 1:
+        S = input_length - (filter_size - 1)
+        P = 1 if num_fc == 0 else Fn.pooled_len(input_length, filter_size, pool_size, pool_stride)
+        if S < 1 or P < 1:
             raise ValueError("input_length %d too short for filter_size %d and pool 7" % (input_length, filter_size))
-        self.linears = _UnitStack(
-            nn.Conv1d(in_channels=4 * U, out_channels=U, kernel_size=filter_size, groups=U),   # 0
-            nn.BatchNorm1d(U),                                                                  # 1
-            ExpActivation(),                                                                    # 2
-            nn.MaxPool1d(pool_size, pool_stride),                                               # 3
-            nn.Flatten(),                                                                       # 4
-            Unsqueeze(),                                                                        # 5
-            nn.Conv1d(in_channels=P * U, out_channels=HIDDEN * U, kernel_size=1, groups=U),     # 6
-            nn.BatchNorm1d(HIDDEN * U, 1e-05, 0.1, True),                                       # 7
-            nn.ReLU(),                                                                          # 8
-            nn.Dropout(0.3),                                                                    # 9
-            nn.Conv1d(in_channels=HIDDEN * U, out_channels=U, kernel_size=1, groups=U),         # 10
-            nn.BatchNorm1d(U, 1e-05, 0.1, True),                                                # 11
-            nn.ReLU(),                                                                          # 12
-            nn.Flatten())                                                                       # 13
+        if num_fc == 0:          # networks.py:73-80: global max-pool, no FC
+            self.linears = _UnitStack(
+                nn.Conv1d(in_channels=4 * U, out_channels=U, kernel_size=filter_size, groups=U),   # 0
+                nn.BatchNorm1d(U),                                                                  # 1
+                ExpActivation(),                                                                    # 2
+                nn.MaxPool1d(S),                                                                    # 3
+                nn.Flatten())                                                                       # 4
+        elif num_fc == 1:        # networks.py:82-95
+            self.linears = _UnitStack(
+                nn.Conv1d(in_channels=4 * U, out_channels=U, kernel_size=filter_size, groups=U),   # 0
+                nn.BatchNorm1d(U),                                                                  # 1
+                ExpActivation(),                                                                    # 2
+                nn.MaxPool1d(pool_size, pool_stride),                                               # 3
+                nn.Flatten(),                                                                       # 4
+                Unsqueeze(),                                                                        # 5
+                nn.Conv1d(in_channels=P * U, out_channels=U, kernel_size=1, groups=U),              # 6
+                nn.BatchNorm1d(U, 1e-05, 0.1, True),                                                # 7
+                nn.ReLU(),                                                                          # 8
+                nn.Flatten())                                                                       # 9
+        else:
+            self.linears = _UnitStack(
+                nn.Conv1d(in_channels=4 * U, out_channels=U, kernel_size=filter_size, groups=U),   # 0
+                nn.BatchNorm1d(U),                                                                  # 1
+                ExpActivation(),                                                                    # 2
+                nn.MaxPool1d(pool_size, pool_stride),                                               # 3
+                nn.Flatten(),                                                                       # 4
+                Unsqueeze(),                                                                        # 5
+                nn.Conv1d(in_channels=P * U, out_channels=HIDDEN * U, kernel_size=1, groups=U),     # 6
+                nn.BatchNorm1d(HIDDEN * U, 1e-05, 0.1, True),                                       # 7
+                nn.ReLU(),                                                                          # 8
+                nn.Dropout(0.3),                                                                    # 9
+                nn.Conv1d(in_channels=HIDDEN * U, out_channels=U, kernel_size=1, groups=U),         # 10
+                nn.BatchNorm1d(U, 1e-05, 0.1, True),                                                # 11
+                nn.ReLU(),                                                                          # 12
+                nn.Flatten())                                                                       # 13
         self.linears._bind(self)
         self.final = nn.Linear(U, num_classes)
         self._invalid = None      # lazily read counter of non-one-hot input columns
@@ -140,6 +164,8 @@ class ExplaiNN(nn.Module):
     @property
     def pooled_length(self):
         o = self._options
+        if o["num_fc"] == 0:
+            return 1
         return Fn.pooled_len(o["input_length"], o["filter_size"], o["pool_size"], o["pool_stride"])
 
     def _pack(self, x):
@@ -181,6 +207,8 @@ class ExplaiNN(nn.Module):
     def _pooled_packed(self, pk):
         if self._bn_uses_batch_stats():
             raise RuntimeError("model.linears[:4] on the fused path needs eval() mode")
+        if self._options["num_fc"] == 0:       # MaxPool1d(S): exp of the maximum over all positions, (B,U,1)
+            return Fn.pwm_score(pk, self._conv_prep_eval(), 2).unsqueeze(-1)
         if self.conv_backend == "tc":
             conv, bn = self.linears[0], self.linears[1]
             tcp = Fn.conv_tc_prepare(conv.weight.detach(), conv.bias.detach(), bn.weight.detach(), bn.bias.detach(),
@@ -198,7 +226,14 @@ class ExplaiNN(nn.Module):
 
     def _unit_outputs_eval_packed(self, pk):
         L = self.linears
+        nfc = self._options["num_fc"]
+        if nfc == 0:
+            return self._pooled_packed(pk).squeeze(-1)
         pooled = self._pooled_packed(pk)
+        if nfc == 1:
+            bn = L[7]
+            return Fn.fc1_stack_fwd_eval(pooled, L[6].weight.detach(), L[6].bias.detach(),
+                                         (bn.weight.detach(), bn.bias.detach(), bn.running_mean, bn.running_var), bn.eps)
         bn2, bn3 = L[7], L[11]
         return Fn.fc_stack_fwd_eval(
             pooled, L[6].weight.detach(), L[6].bias.detach(),

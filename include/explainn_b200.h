@@ -143,7 +143,9 @@ int explainn_interp_thresholds(const float *zmax, int U, float *thr, float *zlo,
 /* PWM scoring, `networks.PWM.forward` (explainn/models/networks.py:428-437): out[b][u] = max (use_max=1) or sum
  * (use_max=0) over the S valid positions of the grouped conv output z[b][u][s] (tables/wq_t/shift from
  * explainn_conv_prepare with identity BatchNorm).  accumulate=1 folds the result into `out` (max / +), which is how
- * the reverse strand (explainn_revcomp_packed) joins: torch.cat((o, o_rev), 2) then max / sum.  out: (B,U) fp32. */
+ * the reverse strand (explainn_revcomp_packed) joins: torch.cat((o, o_rev), 2) then max / sum.  out: (B,U) fp32.
+ * use_max=2 writes exp(max z): the unit output of the num_fc = 0 model, conv -> BN -> exp -> MaxPool1d(S)
+ * (networks.py:73-80), with tables built from the model's BatchNorm. */
 int explainn_pwm_score(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F,
                        const float *tables, const float *wq_t, const float *shift, int use_max, int accumulate,
                        float *out, cudaStream_t stream);
@@ -169,6 +171,25 @@ int explainn_fc_stack_fwd_eval(const float *pooled, long long B, int U, int P, c
                                const float *W2, const float *b2, const float *bn3_w, const float *bn3_b,
                                const float *bn3_rm, const float *bn3_rv, float eps, float *unit_out,
                                cudaStream_t stream);
+
+/* ---- num_fc = 1 unit (explainn/models/networks.py:82-95): pooled -> grouped Conv1d(U*P -> U, k=1) -> BatchNorm1d(U) ->
+ * ReLU.  W (U,P) = linears.6.weight, b1 (U); bn_* = linears.7.  Eval: running statistics, unit_out (B,U).
+ * Train: batch statistics (running buffers updated, may be NULL), h2 (U,B) pre-BatchNorm values, part3 (U, fc_nchunk, 2)
+ * scratch, mean3/invstd3 (U), unit (B,U), logits (B,C) = unit @ Wf^T + bf (networks.py:147,161).
+ * Backward: glogits (B,C) -> all parameter gradients and gpool (B,U,P) = d loss / d pooled for explainn_conv_pool_bwd;
+ * gh2 (U,B) and dW_partials (fc_nchunk, U, P) are scratch; db1 is written as exact zeros (bias in front of a
+ * train-mode BatchNorm).  Wf == NULL: glogits is (B,U), the gradient w.r.t. the unit outputs. */
+int explainn_fc1_stack_fwd_eval(const float *pooled, long long B, int U, int P, const float *W, const float *b1,
+                                const float *bn_w, const float *bn_b, const float *bn_rm, const float *bn_rv, float eps,
+                                float *unit_out, cudaStream_t stream);
+int explainn_fc1_stack_fwd_train(const float *pooled, long long B, int U, int P, int C, const float *W, const float *b1,
+                                 const float *bn_w, const float *bn_b, float *bn_rm, float *bn_rv, float momentum,
+                                 float eps, const float *Wf, const float *bf, float *h2, float *part3, float *mean3,
+                                 float *invstd3, float *unit, float *logits, cudaStream_t stream);
+int explainn_fc1_stack_bwd(const float *glogits, long long B, int U, int P, int C, const float *pooled, const float *h2,
+                           const float *unit, const float *W, const float *bn_w, const float *mean3, const float *invstd3,
+                           const float *Wf, float *gh2, float *dW_partials, float *gpool, float *dW, float *db1,
+                           float *dbn_w, float *dbn_b, float *dWf, float *dbf, cudaStream_t stream);
 
 /* ---- final linear ------------------------------------------------------------------------------------------
  * out (B,C) = x (B,U) @ W(C,U)^T + bias (explainn/models/networks.py:147,161). */

@@ -5,7 +5,7 @@ for the floating-point kernels and the timed CPU baseline of bench.py (`cpu_base
 
 The reference is pure Python on top of torch.nn, so the arithmetic below is executed by the very
 same ATen CPU kernels the reference triggers; what is restated is the module graph:
-  explainn/models/networks.py:96-116   unit stack for num_fc == 2 (module indices kept identical,
+  explainn/models/networks.py:73-116   unit stack for num_fc == 0, 1, 2 (module indices kept identical,
                                        so reference state_dicts load unchanged)
   explainn/models/networks.py:147      final Linear(U, C)
   explainn/models/networks.py:152-162  forward: tile the 4 input rows U times, stack, final
@@ -35,25 +35,35 @@ def pooled_len(L, F, pool_size=7, pool_stride=7):
 
 
 class PortExplaiNN(nn.Module):
-    def __init__(self, num_cnns, input_length, num_classes, filter_size=19, pool_size=7, pool_stride=7):
+    def __init__(self, num_cnns, input_length, num_classes, filter_size=19, pool_size=7, pool_stride=7, num_fc=2):
         super().__init__()
         U, P = num_cnns, pooled_len(input_length, filter_size, pool_size, pool_stride)
         self.U = U
-        self.linears = nn.Sequential(
-            nn.Conv1d(4 * U, U, filter_size, groups=U),      # 0
-            nn.BatchNorm1d(U),                                # 1
-            _Exp(),                                           # 2
-            nn.MaxPool1d(pool_size, pool_stride),             # 3
-            nn.Flatten(),                                     # 4
-            _AddTrailingDim(),                                # 5
-            nn.Conv1d(P * U, HIDDEN * U, 1, groups=U),        # 6
-            nn.BatchNorm1d(HIDDEN * U, 1e-05, 0.1, True),     # 7
-            nn.ReLU(),                                        # 8
-            nn.Dropout(0.3),                                  # 9
-            nn.Conv1d(HIDDEN * U, U, 1, groups=U),            # 10
-            nn.BatchNorm1d(U, 1e-05, 0.1, True),              # 11
-            nn.ReLU(),                                        # 12
-            nn.Flatten())                                     # 13
+        head = [nn.Conv1d(4 * U, U, filter_size, groups=U),  # 0
+                nn.BatchNorm1d(U),                            # 1
+                _Exp()]                                       # 2
+        if num_fc == 0:          # networks.py:73-80
+            tail = [nn.MaxPool1d(input_length - (filter_size - 1)), nn.Flatten()]
+        elif num_fc == 1:        # networks.py:82-95
+            tail = [nn.MaxPool1d(pool_size, pool_stride), nn.Flatten(), _AddTrailingDim(),
+                    nn.Conv1d(P * U, U, 1, groups=U),                 # 6
+                    nn.BatchNorm1d(U, 1e-05, 0.1, True),              # 7
+                    nn.ReLU(), nn.Flatten()]
+        elif num_fc == 2:        # networks.py:96-116
+            tail = [nn.MaxPool1d(pool_size, pool_stride),             # 3
+                    nn.Flatten(),                                     # 4
+                    _AddTrailingDim(),                                # 5
+                    nn.Conv1d(P * U, HIDDEN * U, 1, groups=U),        # 6
+                    nn.BatchNorm1d(HIDDEN * U, 1e-05, 0.1, True),     # 7
+                    nn.ReLU(),                                        # 8
+                    nn.Dropout(0.3),                                  # 9
+                    nn.Conv1d(HIDDEN * U, U, 1, groups=U),            # 10
+                    nn.BatchNorm1d(U, 1e-05, 0.1, True),              # 11
+                    nn.ReLU(),                                        # 12
+                    nn.Flatten()]                                     # 13
+        else:
+            raise NotImplementedError("port: num_fc in (0, 1, 2)")
+        self.linears = nn.Sequential(*(head + tail))
         self.final = nn.Linear(U, num_classes)
 
     def tile(self, x):

@@ -220,4 +220,6 @@ def test_empty_batch_and_errors():
     with pytest.raises(ValueError):
         m(torch.zeros(2, 4, 61, device=DEV))
     with pytest.raises(NotImplementedError):
-        networks.ExplaiNN(8, 60, 2, 19, num_fc=1)
+        networks.ExplaiNN(8, 60, 2, 19, num_fc=3)
+    with pytest.raises(NotImplementedError):
+        networks.ExplaiNN(8, 60, 2, 19, pool_size=5, pool_stride=5)
