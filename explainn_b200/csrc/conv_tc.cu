@@ -28,6 +28,19 @@ constexpr int TC_N = 240;          // positions per tile (TMEM columns), 34 wind
 constexpr int TC_WIN = 34;         // pool windows per tile
 constexpr int TC_THREADS = 512;    // 16 warps: lane quarter = warp & 3, column range = warp >> 2
 
+// Phase clocks (experiments only, -DXB_PHASE_CLOCKS): CTA 0 accumulates clock64() differences per phase; slots 0-7 by
+// the producer lane, 8-15 by thread 0 (epilogue group 0).  tools/phase_clocks_conv.py prints them per tile.
+#ifdef XB_PHASE_CLOCKS
+__device__ long long g_conv_clk[16];
+#define XB_CLK_DECL long long clk_t = clock64(), clk_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0}
+#define XB_CLK(i) do { const long long clk_n = clock64(); clk_acc[i] += clk_n - clk_t; clk_t = clk_n; } while (0)
+#define XB_CLK_FLUSH(base, cond, ntiles) do { clk_acc[7] = (ntiles); if (blockIdx.x == 0 && (cond)) for (int ci = 0; ci < 8; ++ci) g_conv_clk[(base) + ci] = clk_acc[ci]; } while (0)
+#else
+#define XB_CLK_DECL do { } while (0)
+#define XB_CLK(i) do { } while (0)
+#define XB_CLK_FLUSH(base, cond, ntiles) do { } while (0)
+#endif
+
 // ------------------------------------------------------------------------------------------------
 // A-operand images: per 128-unit tile, [hi | lo] x canonical K-major layout
 //   byte offset of element (row r, k) inside one image = (r/8)*KC*128 + (k/8)*128 + (r%8)*16 + (k%8)*2
@@ -156,10 +169,10 @@ struct TcIter {
 // Two TMEM accumulators (tmem_full / tmem_empty mbarriers), four V buffers and two staging buffers keep the
 // tensor pipe, the epilogue and the stores of consecutive tiles in flight.
 template <bool TRAIN>
-__global__ void __launch_bounds__(TC_THREADS + 32, 1) conv_tc_kernel(const TcArgs a)
+__global__ void __launch_bounds__(TC_THREADS + 64, 1) conv_tc_kernel(const TcArgs a)
 {
     extern __shared__ __align__(128) unsigned char smem[];
-    __shared__ __align__(8) uint64_t bar_a, tmem_full[2], tmem_empty[2];
+    __shared__ __align__(8) uint64_t bar_a, tmem_full[2], tmem_empty[2], v_full[TC_VBUFS], v_empty[TC_VBUFS];
     __shared__ uint32_t tmem_base_s;
 
     const int K = a.K, KC = K / 8, KS = K / 16;
@@ -190,6 +203,7 @@ __global__ void __launch_bounds__(TC_THREADS + 32, 1) conv_tc_kernel(const TcArg
         mbar_init(&tmem_full[1], 1);
         mbar_init(&tmem_empty[0], TC_THREADS / 64);      // the 8 warps of the epilogue group that owns the buffer
         mbar_init(&tmem_empty[1], TC_THREADS / 64);
+        for (int i = 0; i < TC_VBUFS; ++i) { mbar_init(&v_full[i], 1); mbar_init(&v_empty[i], 1); }
         mbar_fence_init();
     }
     if (warp == 0) {
@@ -201,15 +215,67 @@ __global__ void __launch_bounds__(TC_THREADS + 32, 1) conv_tc_kernel(const TcArg
     tc_fence_after();
     const uint32_t tmem_base = tmem_base_s;
 
-    if (tc_warp_uniform() == TC_THREADS / 32) {      // warp-uniform role branch: MMA operands stay in uniform registers
-        // =========================== producer warp ===========================
+    const int role = tc_warp_uniform();              // warp-uniform role branch: MMA operands stay in uniform registers
+    if (role == TC_THREADS / 32) {
+        // =========================== issue warp ===========================
+        // waits for an operand buffer (built by the builder warp) and a free accumulator, issues the MMAs of every
+        // resident unit tile and commits; the last commit of an item also hands its operand buffer back
         const uint32_t idesc = (1u << 4) | ((uint32_t)(TC_N >> 3) << 17) | ((uint32_t)(TC_M >> 4) << 24);   // f16xf16->f32, M128 N240
         uint32_t a_parity = 0;
         int cur_grp = -1;
         long long n = 0;                                   // tiles issued by this CTA
-        long long vi = 0;                                  // items (V tiles) built by this CTA
+        long long vi = 0;                                  // items (V tiles) consumed by this CTA
+        XB_CLK_DECL;
+        for (TcIter t(it0, it1, a.B, nchunk); t.valid(); t.next(), ++vi) {
+            XB_CLK(0);                                     // loop overhead
+            const int mt0 = t.grp * a.gsz, mtn = min(a.gsz, n_mt - mt0);
+            if (t.grp != cur_grp) {
+                // new group of unit tiles: every MMA that reads sA must have completed before TMA overwrites it
+                if (n > 0) mbar_wait(&tmem_full[(n - 1) & 1], (uint32_t)(((n - 1) >> 1) & 1));
+                if (lane == 0) {
+                    mbar_arrive_expect_tx(&bar_a, (uint32_t)mtn * 2 * a_bytes);
+                    for (int m = 0; m < mtn; ++m)
+                        tma_bulk_g2s(sA + (size_t)m * 2 * a_bytes, reinterpret_cast<const unsigned char *>(a.images) + (size_t)(mt0 + m) * 2 * a_bytes,
+                                     2 * a_bytes, &bar_a);
+                }
+                mbar_wait(&bar_a, a_parity);
+                a_parity ^= 1;
+                cur_grp = t.grp;
+            }
+            const int slot = (int)(vi & (TC_VBUFS - 1));
+            const uint4 *V = sV + slot * TC_VROWS;
+            mbar_wait(&v_full[slot], (uint32_t)((vi / TC_VBUFS) & 1));
+            XB_CLK(1);                                     // wait for the operand buffer
+            for (int m = 0; m < mtn; ++m, ++n) {
+                const int buf = (int)(n & 1);
+                const uint32_t use = (uint32_t)(n >> 1);   // how often this accumulator has been used before
+                mbar_wait(&tmem_empty[buf], (use & 1) ^ 1);          // drained by the epilogue warps
+                XB_CLK(2);                                 // wait for a free accumulator
+                // descriptors of K step 0, computed by the whole warp; a K step advances A by 256 bytes and V by 64
+                const uint32_t d = tmem_base + (uint32_t)buf * 256u;
+                const uint32_t a_hi = smem_u32(sA) + (uint32_t)m * 2 * a_bytes;
+                const uint64_t dA_hi = make_smem_desc(a_hi, 128, (uint32_t)KC * 128), dA_lo = make_smem_desc(a_hi + a_bytes, 128, (uint32_t)KC * 128);
+                const uint64_t dV = make_smem_desc(smem_u32(V), 32, 128);
+                if (tc_elect_one()) {
+                    tc_fence_after();
+                    for (int ks = 0; ks < ((a.dbg & 8) ? 0 : KS); ++ks) {
+                        tc_mma_f16(d, dA_hi + ks * 16, dV + ks * 4, idesc, ks > 0 ? 1u : 0u);
+                        tc_mma_f16(d, dA_lo + ks * 16, dV + ks * 4, idesc, 1u);
+                    }
+                    tc_commit(&tmem_full[buf]);
+                    if (m == mtn - 1) tc_commit(&v_empty[slot]);     // all MMAs reading this operand buffer have retired
+                }
+                __syncwarp();
+                XB_CLK(3);                                 // MMA issue
+            }
+        }
+        XB_CLK_FLUSH(0, lane == 0, n);
+    } else if (role == TC_THREADS / 32 + 1) {
+        // =========================== builder warp ===========================
+        // expands the packed codes of one (sequence, chunk) into the V operand, TC_VBUFS buffers ahead of the issue warp
+        long long vi = 0;
         // an item touches positions n0 .. n0 + TC_VROWS: at most 20 code words and 11 mask words, one per lane;
-        // they are prefetched two items ahead (global latency ~ one item of work when there is a single unit tile)
+        // they are prefetched two items ahead
         auto load_words = [&](const TcIter &t, uint32_t &cwv, uint32_t &mwv) {
             cwv = 0u; mwv = 0u;
             if (!t.valid()) return;
@@ -227,24 +293,9 @@ __global__ void __launch_bounds__(TC_THREADS + 32, 1) conv_tc_kernel(const TcArg
             cw0 = cw1; mw0 = mw1;
             load_words(tp, cw1, mw1); tp.next();
             const int n0 = t.chunk * TC_WIN * XB_POOL;
-            const int mt0 = t.grp * a.gsz, mtn = min(a.gsz, n_mt - mt0);
-            if (t.grp != cur_grp) {
-                // new group of unit tiles: every MMA that reads sA must have completed before TMA overwrites it
-                if (n > 0) mbar_wait(&tmem_full[(n - 1) & 1], (uint32_t)(((n - 1) >> 1) & 1));
-                if (lane == 0) {
-                    mbar_arrive_expect_tx(&bar_a, (uint32_t)mtn * 2 * a_bytes);
-                    for (int m = 0; m < mtn; ++m)
-                        tma_bulk_g2s(sA + (size_t)m * 2 * a_bytes, reinterpret_cast<const unsigned char *>(a.images) + (size_t)(mt0 + m) * 2 * a_bytes,
-                                     2 * a_bytes, &bar_a);
-                }
-                mbar_wait(&bar_a, a_parity);
-                a_parity ^= 1;
-                cur_grp = t.grp;
-            }
-            // ---- build V into buffer vi % 4.  Its previous user was item vi-4, whose MMAs are known to be complete
-            //      (the accumulators of later tiles have been seen drained), so no wait is needed and the build
-            //      overlaps the MMAs in flight.  Lane l expands the 16 positions n0+16l .. n0+16l+15 of its code word.
-            uint4 *V = sV + (int)(vi & (TC_VBUFS - 1)) * TC_VROWS;
+            const int slot = (int)(vi & (TC_VBUFS - 1));
+            mbar_wait(&v_empty[slot], (uint32_t)(((vi / TC_VBUFS) & 1) ^ 1));    // its previous user's MMAs have retired
+            uint4 *V = sV + slot * TC_VROWS;
             {
                 const uint32_t w_hi = __shfl_down_sync(0xffffffffu, cwr, 1);
                 const uint32_t c16 = __funnelshift_r(cwr, w_hi, 2 * (n0 & 15));          // codes of my 16 positions
@@ -273,25 +324,7 @@ __global__ void __launch_bounds__(TC_THREADS + 32, 1) conv_tc_kernel(const TcArg
             }
             fence_proxy_async();
             __syncwarp();
-            for (int m = 0; m < mtn; ++m, ++n) {
-                const int buf = (int)(n & 1);
-                const uint32_t use = (uint32_t)(n >> 1);   // how often this accumulator has been used before
-                mbar_wait(&tmem_empty[buf], (use & 1) ^ 1);          // drained by the epilogue warps
-                // descriptors of K step 0, computed by the whole warp; a K step advances A by 256 bytes and V by 64
-                const uint32_t d = tmem_base + (uint32_t)buf * 256u;
-                const uint32_t a_hi = smem_u32(sA) + (uint32_t)m * 2 * a_bytes;
-                const uint64_t dA_hi = make_smem_desc(a_hi, 128, (uint32_t)KC * 128), dA_lo = make_smem_desc(a_hi + a_bytes, 128, (uint32_t)KC * 128);
-                const uint64_t dV = make_smem_desc(smem_u32(V), 32, 128);
-                if (tc_elect_one()) {
-                    tc_fence_after();
-                    for (int ks = 0; ks < ((a.dbg & 8) ? 0 : KS); ++ks) {
-                        tc_mma_f16(d, dA_hi + ks * 16, dV + ks * 4, idesc, ks > 0 ? 1u : 0u);
-                        tc_mma_f16(d, dA_lo + ks * 16, dV + ks * 4, idesc, 1u);
-                    }
-                    tc_commit(&tmem_full[buf]);
-                }
-                __syncwarp();
-            }
+            if (lane == 0) mbar_arrive(&v_full[slot]);
         }
     } else {
         // =========================== epilogue warps ===========================
@@ -306,6 +339,7 @@ __global__ void __launch_bounds__(TC_THREADS + 32, 1) conv_tc_kernel(const TcArg
         const uint32_t taddr = tmem_base + ((uint32_t)(32 * (warp & 3)) << 16) + (uint32_t)grp * 256u;
         constexpr int SPLIT = 17 * XB_POOL;
         long long n = 0;
+        XB_CLK_DECL;
         for (TcIter t(it0, it1, a.B, nchunk); t.valid(); t.next()) {
             const int mt0 = t.grp * a.gsz, mtn = min(a.gsz, n_mt - mt0);
             const int w0 = t.chunk * TC_WIN;
@@ -320,10 +354,14 @@ __global__ void __launch_bounds__(TC_THREADS + 32, 1) conv_tc_kernel(const TcArg
                 if (TRAIN && u < a.U) { gam = __ldg(a.gamma + u); bet = __ldg(a.beta + u); }
                 // the previous tile of this group was staged in the same buffer: its bulk stores must be done
                 // reading before anybody overwrites it
+                XB_CLK(0);                                 // loop overhead, coefficient loads
                 if (gtid == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+                XB_CLK(1);                                 // previous bulk store finished reading the staging buffer
                 asm volatile("bar.sync %0, 256;" ::"r"(1 + grp) : "memory");
+                XB_CLK(2);                                 // group barrier 1
                 mbar_wait(&tmem_full[grp], use & 1);
                 tc_fence_after();
+                XB_CLK(3);                                 // wait for the accumulator
                 if (u0 + 32 * (warp & 3) < a.U && !(a.dbg & 4)) {   // lane quarters without a valid unit are not read at all
                     if (((warp >> 2) & 1) == 0) tc_drain<TRAIN, 0, SPLIT>(taddr, row, nwin, sst, stage, stage_i, shift, gam, bet);
                     else tc_drain<TRAIN, SPLIT, TC_WIN * XB_POOL>(taddr, row, nwin, sst, stage, stage_i, shift, gam, bet);
@@ -332,11 +370,13 @@ __global__ void __launch_bounds__(TC_THREADS + 32, 1) conv_tc_kernel(const TcArg
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&tmem_empty[grp]);
+                XB_CLK(4);                                 // drain
                 if (a.dbg & 1) continue;
 
                 // ---- store the staged tile ----
                 fence_proxy_async();
                 asm volatile("bar.sync %0, 256;" ::"r"(1 + grp) : "memory");
+                XB_CLK(5);                                 // group barrier 2
                 const int nvalid = min(TC_M, a.U - u0);
                 const size_t o = ((size_t)t.b * a.U + u0) * a.P;
                 const uint32_t bytes = (uint32_t)nvalid * a.P * 4;
@@ -374,8 +414,10 @@ __global__ void __launch_bounds__(TC_THREADS + 32, 1) conv_tc_kernel(const TcArg
                         }
                     }
                 }
+                XB_CLK(6);                                 // store issue
             }
         }
+        XB_CLK_FLUSH(8, threadIdx.x == 0, n);
         if (gtid == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
     }
 
@@ -388,6 +430,12 @@ __global__ void __launch_bounds__(TC_THREADS + 32, 1) conv_tc_kernel(const TcArg
 }
 
 int tc_K(int F) { return ((4 * F + 15) / 16) * 16; }
+
+}  // namespace
+#ifdef XB_PHASE_CLOCKS
+extern "C" int xb_dbg_conv_clocks(long long *host) { return (int)cudaMemcpyFromSymbol(host, g_conv_clk, sizeof(g_conv_clk)); }
+#endif
+namespace {
 
 }  // namespace
 
@@ -444,10 +492,10 @@ static int launch_tc(bool train, const uint32_t *codes, const uint32_t *nmask, l
     cudaError_t e;
     if (train) {
         e = cudaFuncSetAttribute(conv_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e == cudaSuccess) conv_tc_kernel<true><<<grid, TC_THREADS + 32, smem, stream>>>(a);
+        if (e == cudaSuccess) conv_tc_kernel<true><<<grid, TC_THREADS + 64, smem, stream>>>(a);
     } else {
         e = cudaFuncSetAttribute(conv_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e == cudaSuccess) conv_tc_kernel<false><<<grid, TC_THREADS + 32, smem, stream>>>(a);
+        if (e == cudaSuccess) conv_tc_kernel<false><<<grid, TC_THREADS + 64, smem, stream>>>(a);
     }
     if (e != cudaSuccess) {
         xb_set_error("conv_pool_fwd_tc: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
