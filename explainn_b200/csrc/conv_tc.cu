@@ -101,37 +101,67 @@ __device__ __forceinline__ void tc_drain(uint32_t taddr, int row, int nwin, int 
 {
     constexpr int plane = TC_M * (TC_WIN + 1);
     constexpr int P0 = C0 / 16, P1 = (C1 + 15) / 16;
-    constexpr int BATCH = 4;                      // 64 columns in registers at a time
     float m = 0.f, xb = 0.f;
     int ib = 0;
+    // one pooled column: running max of the window, emit at its last position
+    auto column = [&](int col, uint32_t bits) {
+        const float v = __uint_as_float(bits);
+        const int ph = col % XB_POOL, win = col / XB_POOL;
+        if (TRAIN) {
+            const float x = v + shift;
+            const float z = fmaf(gam, x, bet);
+            if (ph == 0 || z > m) { m = z; xb = x; ib = ph; }
+        } else {
+            m = ph == 0 ? v : fmaxf(m, v);
+        }
+        if (ph == XB_POOL - 1 && win < nwin) {
+            // training keeps the 1-ulp deterministic exp of the table kernel: ReLU / max-pool kinks downstream turn
+            // a 1e-6 relative error into visibly different gradients; inference uses the 2-instruction MUFU exp
+            stage[row * sst + win] = TRAIN ? det_expf(m) : __expf(m + shift);
+            if (TRAIN) {
+                stage[plane + row * sst + win] = xb;
+                stage_i[row * sst + win] = (unsigned char)ib;
+            }
+        }
+    };
+    if constexpr (TRAIN) {
+        // 64 columns in registers at a time (the training epilogue needs its registers for the three outputs)
+        constexpr int BATCH = 4;
 #pragma unroll
-    for (int pb = P0; pb < P1; pb += BATCH) {
-        uint32_t r[BATCH * 16];
+        for (int pb = P0; pb < P1; pb += BATCH) {
+            uint32_t r[BATCH * 16];
+#pragma unroll
+            for (int p = 0; p < BATCH; ++p)
+                if (pb + p < P1) tc_ld16_nowait(taddr + (pb + p) * 16, r + p * 16);
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+            for (int i = 0; i < BATCH * 16; ++i) {
+                const int col = pb * 16 + i;
+                if (col >= C0 && col < C1) column(col, r[i]);
+            }
+        }
+    } else {
+        // double-buffered batches of 32 columns: the TMEM loads of batch k+1 are in flight while batch k is pooled
+        constexpr int BATCH = 2;
+        constexpr int NB = (P1 - P0 + BATCH - 1) / BATCH;
+        uint32_t rr[2][BATCH * 16] = {};
 #pragma unroll
         for (int p = 0; p < BATCH; ++p)
-            if (pb + p < P1) tc_ld16_nowait(taddr + (pb + p) * 16, r + p * 16);
-        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            if (P0 + p < P1) tc_ld16_nowait(taddr + (P0 + p) * 16, rr[0] + p * 16);
 #pragma unroll
-        for (int i = 0; i < BATCH * 16; ++i) {
-            const int col = pb * 16 + i;
-            if (col < C0 || col >= C1) continue;
-            const float v = __uint_as_float(r[i]);
-            const int ph = col % XB_POOL, win = col / XB_POOL;
-            if (TRAIN) {
-                const float x = v + shift;
-                const float z = fmaf(gam, x, bet);
-                if (ph == 0 || z > m) { m = z; xb = x; ib = ph; }
-            } else {
-                m = ph == 0 ? v : fmaxf(m, v);
+        for (int bi = 0; bi < NB; ++bi) {
+            const int pb = P0 + bi * BATCH;
+            uint32_t *r = rr[bi & 1];
+            tc_wait_ld32(r);
+            if (bi + 1 < NB) {
+#pragma unroll
+                for (int p = 0; p < BATCH; ++p)
+                    if (pb + BATCH + p < P1) tc_ld16_nowait(taddr + (pb + BATCH + p) * 16, rr[(bi + 1) & 1] + p * 16);
             }
-            if (ph == XB_POOL - 1 && win < nwin) {
-                // training keeps the 1-ulp deterministic exp of the table kernel: ReLU / max-pool kinks downstream turn
-                // a 1e-6 relative error into visibly different gradients; inference uses the 2-instruction MUFU exp
-                stage[row * sst + win] = TRAIN ? det_expf(m) : __expf(m + shift);
-                if (TRAIN) {
-                    stage[plane + row * sst + win] = xb;
-                    stage_i[row * sst + win] = (unsigned char)ib;
-                }
+#pragma unroll
+            for (int i = 0; i < BATCH * 16; ++i) {
+                const int col = pb * 16 + i;
+                if (col >= C0 && col < C1) column(col, r[i]);
             }
         }
     }
@@ -352,9 +382,9 @@ __global__ void __launch_bounds__(TC_THREADS + 64, 1) conv_tc_kernel(const TcArg
                 const float shift = u < a.U ? __ldg(a.shift + u) : 0.f;
                 float gam = 1.f, bet = 0.f;
                 if (TRAIN && u < a.U) { gam = __ldg(a.gamma + u); bet = __ldg(a.beta + u); }
-                // the previous tile of this group was staged in the same buffer: its bulk stores must be done
-                // reading before anybody overwrites it
                 XB_CLK(0);                                 // loop overhead, coefficient loads
+                // the previous tile of this group was staged in the same buffer: its bulk stores must be done
+                // reading before anybody overwrites it (a second staging buffer per group was tried: no gain)
                 if (gtid == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
                 XB_CLK(1);                                 // previous bulk store finished reading the staging buffer
                 asm volatile("bar.sync %0, 256;" ::"r"(1 + grp) : "memory");
@@ -380,7 +410,7 @@ __global__ void __launch_bounds__(TC_THREADS + 64, 1) conv_tc_kernel(const TcArg
                 const int nvalid = min(TC_M, a.U - u0);
                 const size_t o = ((size_t)t.b * a.U + u0) * a.P;
                 const uint32_t bytes = (uint32_t)nvalid * a.P * 4;
-                const bool bulk_f = sst == a.P && (bytes & 15u) == 0 && ((o * 4) & 15u) == 0;
+                const bool bulk_f = sst == a.P && (bytes & 15u) == 0 && ((o * 4) & 15u) == 0 && !(a.dbg & 16);
                 const bool bulk_i = TRAIN && sst == a.P && ((bytes / 4) & 15u) == 0 && (o & 15u) == 0;
                 if (gtid == 0 && (bulk_f || bulk_i)) {
                     if (bulk_f) {

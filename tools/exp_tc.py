@@ -18,6 +18,6 @@ def timeit(f, n=10):
     for _ in range(n): f()
     e.record(); torch.cuda.synchronize()
     return s.elapsed_time(e) / n
-for dbg in [0, 1, 2, 4, 8, 3, 5, 6, 7, 12, 15]:
+for dbg in [0, 16, 1, 2, 4, 8, 3, 5, 6, 7, 12, 15]:
     os.environ["XB_TC_DBG"] = str(dbg)
     print("dbg=%2d  %.1f us" % (dbg, timeit(lambda: Fn.conv_pool_fwd_tc(pk, tcp)) * 1e3))
