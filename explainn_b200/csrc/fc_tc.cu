@@ -782,6 +782,137 @@ __global__ void __launch_bounds__(FT_THREADS, 2) fc1_tc_eval_pipe_kernel(const F
 }
 
 // ------------------------------------------------------------------------------------------------
+// Software-pipelined training-mode FC1 (P <= 40: one K chunk): the schedule of fc1_tc_eval_pipe_kernel with the
+// epilogue of fc1_tc_kernel<false> (thread = hidden channel: + bias, h1 store, BatchNorm-2 partial sums).  Same
+// MMAs, operand order and summation order as the unpipelined kernel, so h1 and the partial sums are bit-identical.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(FT_THREADS, 2) fc1_tc_train_pipe_kernel(const FcTcArgs a)
+{
+    extern __shared__ __align__(128) unsigned char smem[];
+    __shared__ __align__(8) uint64_t bar;
+    __shared__ uint32_t tmem_base_s;
+    __shared__ float bias_s[2][128];                // per unit parity
+    __shared__ float red_s[2][128], red_q[2][128];
+
+    unsigned char *sWh = smem, *sWl = sWh + FT_TILE_BYTES, *sAh = sWl + FT_TILE_BYTES, *sAl = sAh + FT_TILE_BYTES;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    if (threadIdx.x == 0) {
+        mbar_init(&bar, 1);
+        mbar_fence_init();
+    }
+    if (warp == 0) tc_alloc(&tmem_base_s, 256u);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_base_s;
+    const uint32_t idesc = tc_idesc(2u, 128, 128);
+    uint32_t parity = 0;
+    const int warp_u = tc_warp_uniform();
+    const uint64_t dW_hi = make_smem_desc(smem_u32(sWh), 128, FT_KC * 128), dW_lo = make_smem_desc(smem_u32(sWl), 128, FT_KC * 128);
+    const uint64_t dA_hi = make_smem_desc(smem_u32(sAh), 128, FT_KC * 128), dA_lo = make_smem_desc(smem_u32(sAl), 128, FT_KC * 128);
+
+    const long long total = (long long)a.U * a.nchunk;
+    const long long t_begin = total * blockIdx.x / gridDim.x, t_end = total * (blockIdx.x + 1) / gridDim.x;
+    const size_t row_stride = (size_t)a.U * a.P;
+    float xv[FT_NIT];
+    int cur_u = -1, sel = 0;
+    int p_u = 0, p_rows = 0, p_sel = 0, p_chunk = 0;
+    long long p_b0 = 0;
+    if (t_begin < t_end) {
+        const int u = (int)(t_begin / a.nchunk), chunk = (int)(t_begin - (long long)u * a.nchunk);
+        const long long b0 = (long long)chunk * FT_ROWS;
+        tile_load(xv, a.pooled + ((size_t)b0 * a.U + u) * a.P, row_stride, (int)min((long long)FT_ROWS, a.B - b0), a.P);
+    }
+    int it = 0;
+    for (long long tile = t_begin; tile <= t_end && t_begin < t_end; ++tile, ++it) {
+        const bool have = tile < t_end;
+        if (it > 0) {        // the MMAs of the previous tile have retired: its accumulator is ready, the operand tiles are free
+            mbar_wait(&bar, parity);
+            parity ^= 1;
+            tc_fence_after();
+        }
+        int u = 0, rows = 0, chunk = 0;
+        long long b0 = 0;
+        if (have) {
+            u = (int)(tile / a.nchunk);
+            chunk = (int)(tile - (long long)u * a.nchunk);
+            b0 = (long long)chunk * FT_ROWS;
+            rows = (int)min((long long)FT_ROWS, a.B - b0);
+            if (u != cur_u) {
+                sel ^= 1;
+                if (threadIdx.x < 128) bias_s[sel][threadIdx.x] = threadIdx.x < H ? a.b1[u * H + threadIdx.x] : 0.f;
+                fill_tile(sWh, sWl, a.W1 + (size_t)u * H * a.P, (size_t)a.P, H, 0, a.P);
+                cur_u = u;
+            }
+            tile_store(xv, sAh, sAl);
+            fence_proxy_async();
+        }
+        tc_fence_before();
+        __syncthreads();
+        if (have && warp_u == 0 && tc_elect_one()) {
+            tc_fence_after();
+            const uint32_t acc = tmem_base + (uint32_t)(it & 1) * 128u;
+#pragma unroll
+            for (int ks = 0; ks < FT_KCH / 8; ++ks) {      // M = hidden channels (W1 is the A operand), N = sequences
+                const uint64_t dWh = dW_hi + ks * 16, dWl = dW_lo + ks * 16, dAh = dA_hi + ks * 16, dAl = dA_lo + ks * 16;
+                tc_mma_tf32(acc, dWh, dAh, idesc, ks > 0 ? 1u : 0u);
+                tc_mma_tf32(acc, dWl, dAh, idesc, 1u);
+                tc_mma_tf32(acc, dWh, dAl, idesc, 1u);
+            }
+            tc_commit(&bar);
+        }
+        if (tile + 1 < t_end) {      // global loads of the next tile fly during this tile's MMAs and the epilogue below
+            const int un = (int)((tile + 1) / a.nchunk), cn = (int)((tile + 1) - (long long)un * a.nchunk);
+            const long long bn = (long long)cn * FT_ROWS;
+            tile_load(xv, a.pooled + ((size_t)bn * a.U + un) * a.P, row_stride, (int)min((long long)FT_ROWS, a.B - bn), a.P);
+        }
+        if (it > 0) {
+            // ---------------- epilogue of the previous tile: row = hidden channel j, this warp's 64 sequences ----------------
+            const int q = warp & 3, half = warp >> 2;
+            const int j = 32 * q + lane;
+            const uint32_t taddr = tmem_base + (uint32_t)((it - 1) & 1) * 128u + ((uint32_t)(32 * q) << 16);
+            const float bias = bias_s[p_sel][j];
+            float sm = 0.f, sq = 0.f;
+            float *dst = a.h1 + ((size_t)p_u * a.B + p_b0) * H + j;
+#pragma unroll
+            for (int pb = 0; pb < 4; pb += 2) {
+                uint32_t r[32];
+                tc_ld16_nowait(taddr + 64 * half + pb * 16, r);
+                tc_ld16_nowait(taddr + 64 * half + pb * 16 + 16, r + 16);
+                tc_wait_ld();
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                    const int b = 64 * half + pb * 16 + i;
+                    const float h = __uint_as_float(r[i]) + bias;
+                    if (b < p_rows) {
+                        sm += h;
+                        sq = fmaf(h, h, sq);
+                        if (j < H) dst[(size_t)b * H] = h;
+                    }
+                }
+            }
+            red_s[half][j] = sm;
+            red_q[half][j] = sq;
+            tc_fence_before();
+            __syncthreads();
+            if (threadIdx.x < H) {
+                float *pp = a.part2 + ((size_t)p_u * a.nchunk + p_chunk) * 2 * H;
+                pp[threadIdx.x] = red_s[0][threadIdx.x] + red_s[1][threadIdx.x];
+                pp[H + threadIdx.x] = red_q[0][threadIdx.x] + red_q[1][threadIdx.x];
+            }
+        }
+        p_u = u; p_rows = rows; p_sel = sel; p_b0 = b0; p_chunk = chunk;
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) {
+        tc_fence_after();
+        tc_dealloc(tmem_base, 256u);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 // Final linear layer (networks.py:118,160-162: out = unit_out @ Wf^T + bias) on the tensor cores, 3-term tf32 split.
 //   D[b][c] = sum_u x[b][u] * Wf[c][u]      M = 128 sequences, N = classes padded to 16 (<= 128), K = U in chunks of 40
 // Both operands are K-major as they lie in memory.  One tile of 128 sequences per CTA; the global loads of K chunk
@@ -898,6 +1029,9 @@ int launch_fc1_tc(bool eval, const FcTcArgs &a, cudaStream_t stream)
     } else if (eval) {
         e = cudaFuncSetAttribute(fc1_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e == cudaSuccess) fc1_tc_kernel<true><<<grid, FT_THREADS, smem, stream>>>(a);
+    } else if (a.P <= FT_KCH && !no_pipe) {
+        e = cudaFuncSetAttribute(fc1_tc_train_pipe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e == cudaSuccess) fc1_tc_train_pipe_kernel<<<grid, FT_THREADS, smem, stream>>>(a);
     } else {
         e = cudaFuncSetAttribute(fc1_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e == cudaSuccess) fc1_tc_kernel<false><<<grid, FT_THREADS, smem, stream>>>(a);
