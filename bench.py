@@ -369,6 +369,29 @@ def extras(torch, dev, model, trainer, data, labels, batch, _cabi, Fn, interpret
                                          "achieved_GBps": ach, "frac_of_hbm_peak": ach / hbm_peak,
                                          "algorithmic_bytes_per_launch": bytes_inf}}
 
+    # ---- inference at the large-scale shape (BASELINE.json config 5: num_cnns=500, L=1000, 100 outputs) ----------
+    try:
+        from explainn_b200 import networks as xnet5
+        torch.manual_seed(0)
+        m5 = xnet5.ExplaiNN(500, 1000, 100, 19).to(dev).eval()
+        g5 = torch.Generator(device=dev).manual_seed(7)
+        c5 = torch.randint(0, 4, (2048, 1000), generator=g5, device=dev)
+        x5 = torch.zeros((2048, 4, 1000), device=dev)
+        x5.scatter_(1, c5.unsqueeze(1), 1.0)
+        with torch.no_grad():
+            m5(x5)
+            torch.cuda.synchronize()
+            s.record()
+            for i in range(5):
+                m5(x5)
+            e.record()
+            torch.cuda.synchronize()
+        out["infer_cfg5"] = {"sequences_per_sec": 2048 / (s.elapsed_time(e) / 5 * 1e-3), "batch": 2048,
+                             "workload": "num_cnns=500 L=1000 filter=19 classes=100, eval forward from fp32 one-hot on the device"}
+        del m5, x5, c5
+    except Exception as ex:       # pragma: no cover
+        out["infer_cfg5"] = {"error": str(ex)}
+
     # ---- interpretation: fused two-pass PWM extraction -------------------------------------------------
     NI = 4 * IB
     with torch.no_grad():
