@@ -64,6 +64,13 @@ SIGNATURES = {
     "explainn_loss_fwd_bwd": [_P, _P, _LL, _I, _I, _F, _P, _P, _P, _P],
     "explainn_adam_step": [_P, _P, _P, _P, _LL, _P, _F, _F, _F, _F, _F, _P],
     "explainn_reduce_partials": [_P, _P, _LL, _I, _P],
+    "explainn_p2p_flag_bytes": [],
+    "explainn_p2p_alloc": [_LL, _P],
+    "explainn_p2p_free": [_P],
+    "explainn_p2p_export": [_P, _P],
+    "explainn_p2p_open": [_P, _P],
+    "explainn_p2p_close": [_P],
+    "explainn_p2p_adam_step": [_P, _P, _P, _LL, _P, _P, _P, _I, _I, _ULL, _F, _F, _F, _F, _P],
 }
 _RESTYPES = {
     "explainn_last_error": C.c_char_p,
@@ -72,6 +79,7 @@ _RESTYPES = {
     "explainn_interp_unit_max_scratch_floats": _LL,
     "explainn_loss_scratch_bytes": _LL,
     "explainn_conv_tc_image_halfs": _LL,
+    "explainn_p2p_flag_bytes": _LL,
 }
 
 

@@ -267,6 +267,27 @@ int explainn_loss_fwd_bwd(const float *logits, const float *target, long long B,
 int explainn_adam_step(float *param, const float *grad, float *exp_avg, float *exp_avg_sq, long long n, float *step,
                        float lr, float beta1, float beta2, float eps, float grad_scale, cudaStream_t stream);
 
+/* Data-parallel optimizer step as ONE kernel over NVLink peer memory (no counterpart in the reference, which is
+ * single-device; it replaces "NCCL all-reduce of the gradients + Adam", the DDP form of train.py:65-67).
+ * grads[q] / flags[q], q < world: device pointers to rank q's flat gradient buffer and flag buffer
+ * (explainn_p2p_flag_bytes() bytes, zero-initialised once), valid in THIS process (the caller opens the peers' buffers
+ * through CUDA IPC and enables peer access); grads[rank] / flags[rank] are the local ones.  The arrays grads / flags
+ * themselves are host arrays.  Every rank sums the gradients in rank order, scales by 1/world and applies Adam to its
+ * own param / exp_avg / exp_avg_sq (n floats, 16-byte aligned, n % 4 == 0); *step (device) is incremented first.
+ * seq: the same strictly increasing positive number on every rank for every step.  All ranks must call it once per
+ * step; a peer that does not show up within ~2 s makes the kernel trap (the call never hangs the GPU). */
+/* Peer buffers: plain cudaMalloc allocations (zero-filled) that CUDA IPC can export -- the only memory this library
+ * allocates; export writes a 64-byte handle, open maps a peer's allocation for the current device. */
+int explainn_p2p_alloc(long long bytes, void **out);
+int explainn_p2p_free(void *p);
+int explainn_p2p_export(const void *p, unsigned char *handle);
+int explainn_p2p_open(const unsigned char *handle, void **out);
+int explainn_p2p_close(void *p);
+long long explainn_p2p_flag_bytes(void);
+int explainn_p2p_adam_step(float *param, float *exp_avg, float *exp_avg_sq, long long n, float *step,
+                           const float *const *grads, unsigned long long *const *flags, int world, int rank,
+                           unsigned long long seq, float lr, float beta1, float beta2, float eps, cudaStream_t stream);
+
 /* out[i] = sum_{c<k} partials[c*n + i] */
 int explainn_reduce_partials(float *out, const float *partials, long long n, int k, cudaStream_t stream);
 

@@ -44,9 +44,28 @@ for r in range(world):
     g = [p.grad.clone() for p in autograd_fn._params(ref)]
     mean_g = g if mean_g is None else [a + b for a, b in zip(mean_g, g)]
 mean_g = [g / world for g in mean_g]
+p2p = os.environ.get("XB_P2P_ADAM", "1") != "0"
+p0, m0, v0 = tr.flat_p.clone(), tr.flat_m.clone(), tr.flat_v.clone()
 tr.step(xs[rank], ys[rank])
 torch.cuda.synchronize()
-got = [v / world for v in tr.views_g]                # the flat buffer holds the SUM over ranks; Adam applies 1/world
+if p2p:
+    # the fused kernel sums the peers' buffers on the fly; every rank keeps its local gradients
+    assert tr.p2p is not None
+    allg = [torch.empty_like(tr.flat_g) for _ in range(world)]
+    dist.all_gather(allg, tr.flat_g)
+    flat = allg[0].clone()
+    for q in range(1, world):
+        flat += allg[q]
+    flat /= world
+    got = [flat[o:o + p.numel()].view_as(p) for p, o in zip(tr.params, tr.offsets)]
+    # and the update itself: Adam (lr 1e-2, default betas / eps) on the mean gradient
+    t = float(tr.step_t.item())
+    m1 = m0 + (flat - m0) * 0.1
+    v1 = v0 * 0.999 + flat * flat * 0.001
+    p1 = p0 - (1e-2 / (1 - 0.9 ** t)) * (m1 / (v1.sqrt() / (1 - 0.999 ** t) ** 0.5 + 1e-8))
+    assert float((tr.flat_p - p1).abs().max()) <= 1e-6 * max(float(p1.abs().max()), 1.0), "fused Adam update"
+else:
+    got = [v / world for v in tr.views_g]            # the flat buffer holds the SUM over ranks; Adam applies 1/world
 err = 0.0
 for i, (a, b) in enumerate(zip(got, mean_g)):
     # index 3 = BatchNorm-1 beta: its gradient is mathematically zero, both sides hold rounding noise (test_gpu_train.py)
@@ -66,7 +85,7 @@ dist.destroy_process_group()
 '''
 
 
-@pytest.mark.parametrize("overlap", ["0", "1"])
+@pytest.mark.parametrize("overlap", ["0", "1", "p2p"])
 @pytest.mark.parametrize("mode", ["eager", "graph"])
 def test_two_gpu_step_allreduce(tmp_path, mode, overlap):
     if torch.cuda.device_count() < 2:
@@ -76,7 +95,7 @@ def test_two_gpu_step_allreduce(tmp_path, mode, overlap):
     out = tmp_path / "out.txt"
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
            "--master-port", "29533", str(script), ROOT, str(out), mode]
-    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300, env=dict(os.environ, XB_DP_OVERLAP=overlap))
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300, env=dict(os.environ, XB_DP_OVERLAP="1" if overlap == "1" else "0", XB_P2P_ADAM="1" if overlap == "p2p" else "0"))      # "0" / "1": NCCL all-reduce (plain / overlapped)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     same, err, split = out.read_text().split()
     assert int(same) == 1, "ranks diverged"
