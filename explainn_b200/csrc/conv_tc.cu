@@ -13,9 +13,9 @@
 // thread owns one unit and pools 7 consecutive columns in registers.
 //
 // One CTA per SM, persistent.  A (one 128-unit tile, hi+lo, 40 KB) stays in shared memory; for every
-// (sequence, 34-window chunk) the producer warps expand the 2-bit codes into the X tile (240 rows x K fp16,
-// canonical no-swizzle K-major core-matrix layout), one thread issues 2*K/16 tcgen05.mma into one of two
-// TMEM accumulators (240 columns each) and the epilogue warps drain the other one.
+// (sequence, 34-window chunk) a builder warp expands the 2-bit codes into the one-hot operand (16 bytes per
+// position, read by the tensor core through overlapping K-major core matrices), an issue warp issues 2*K/16
+// tcgen05.mma into one of two TMEM accumulators (240 columns each) and the epilogue warps drain the other one.
 #include "tc_common.cuh"
 #include "../../include/explainn_b200.h"
 #include <stdlib.h>
@@ -191,9 +191,11 @@ struct TcIter {
 };
 
 // Warp-specialised persistent kernel.
-//   warp 16      producer: expands the packed codes of one (sequence, chunk) into the V operand ONCE, then issues
-//                the tcgen05.mma of every resident unit tile against it (the weights of up to `gsz` 128-unit
-//                tiles stay in shared memory), committing each accumulator to an mbarrier
+//   warp 17      builder: expands the packed codes of one (sequence, chunk) into the V operand ONCE (ring of four
+//                buffers, v_full / v_empty mbarriers)
+//   warp 16      issuer: one elected lane issues the tcgen05.mma of every resident unit tile against that operand (the
+//                weights of up to `gsz` 128-unit tiles stay in shared memory) and commits each accumulator to an
+//                mbarrier; the last commit of an item hands the operand buffer back to the builder
 //   warps 0..15  epilogue: drain the accumulator (lane quarter = warp & 3, window range = warp >> 2), pool, exp,
 //                stage, TMA bulk store
 // Two TMEM accumulators (tmem_full / tmem_empty mbarriers), four V buffers and two staging buffers keep the

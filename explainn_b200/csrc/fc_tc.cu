@@ -10,6 +10,9 @@
 //              (replaces networks.py:105-116 in eval mode; the hidden activations never leave the SM)
 // Both modes use the same two shared-memory tiles (W1[u] and the pooled tile, K-major, no-swizzle core-matrix
 // layout); only which one is the A operand changes.
+// fc1_tc_eval_pipe_kernel / fc1_tc_train_pipe_kernel are the software-pipelined forms used when P <= 40 (one K chunk);
+// linear_tc_kernel is the final Linear for inference; bwd_fc1_tc_kernel the FC1 backward.  All MMAs are issued from one
+// elected lane of a warp-uniform branch with precomputed descriptors (tc_common.cuh: tc_elect_one).
 #include "tc_common.cuh"
 #include "../../include/explainn_b200.h"
 #include <stdlib.h>
@@ -329,9 +332,9 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bwd_fc1_tc_kernel(const FcBwdAr
     // operand descriptors of K step 0, computed once in warp-uniform code (see tc_elect_one)
     const int warp_u = tc_warp_uniform();
     const uint64_t dG_hi = make_smem_desc(smem_u32(sR), 128, BT_G_SBO), dG_lo = make_smem_desc(smem_u32(sR) + BT_G_BYTES, 128, BT_G_SBO);
-    const uint64_t dW_hi = make_smem_desc(smem_u32(sWh), 128, BT_G_SBO), dW_lo = make_smem_desc(smem_u32(sWl), 128, BT_G_SBO);
+    const uint64_t dW_hi = make_smem_desc(smem_u32(sWh), 128, BT_G_SBO);       // [W1t hi ; W1t lo]: the lo tile follows the hi tile
     const uint64_t dT_hi = make_smem_desc(smem_u32(sR), 128, BT_B_SBO), dT_lo = make_smem_desc(smem_u32(sR) + BT_GT_BYTES, 128, BT_B_SBO);
-    const uint64_t dA_hi = make_smem_desc(smem_u32(sAh), 128, BT_B_SBO), dA_lo = make_smem_desc(smem_u32(sAl), 128, BT_B_SBO);
+    const uint64_t dA_hi = make_smem_desc(smem_u32(sAh), 128, BT_B_SBO);       // [pooled hi ; pooled lo]
 
     const long long total = (long long)a.U * a.nchunk;
     const long long t_begin = total * blockIdx.x / gridDim.x, t_end = total * (blockIdx.x + 1) / gridDim.x;
