@@ -168,8 +168,8 @@ __global__ void __launch_bounds__(BW_WARPS * 32) conv_bwd_sparse_kernel(
     const long long e0 = per * blockIdx.y, e1 = min(n, e0 + per);
     float dbeta = 0.f, dgamma = 0.f;
     float *mine = my + lane;
-    // Two-stage software pipeline over this lane's entries e = first, first + 128, ...:
-    //   stage A (entry i+2): gradient, pooled value, xhat, argmax offset      stage B (entry i+1): the code / N-mask words
+    // Software pipeline over this lane's entries e = first, first + 128, ...:
+    //   stage A (entry i+4): gradient, pooled value, xhat, argmax offset      stage B (entry i+2): the code / N-mask words
     //   at the argmax position (their address depends on stage A)             stage C (entry i): shared-memory updates
     // Entries past the end are clamped to the last one and weighted with zero, so every lane runs the same trip count.
     constexpr int STRIDE = BW_WARPS * 32;
@@ -217,19 +217,8 @@ __global__ void __launch_bounds__(BW_WARPS * 32) conv_bwd_sparse_kernel(
         r.m1 = mi + 1 < wm ? mw[mi + 1] : 0u;
         return r;
     };
-    StA sa{};
-    StB sb{};
-    if (niter > 0) {
-        sa = fetchA();
-        sb = fetchB(sa);
-        sa = fetchA();
-    }
-    for (int it = 0; it < niter; ++it) {
-        const StB c = sb;
-        if (it + 1 < niter) {
-            sb = fetchB(sa);
-            sa = fetchA();
-        }
+    // shared-memory updates of one entry
+    auto consume = [&](const StB &c) {
         const float gz = c.gz;
         dbeta += gz;
         dgamma = fmaf(gz, c.xh, dgamma);
@@ -262,6 +251,27 @@ __global__ void __launch_bounds__(BW_WARPS * 32) conv_bwd_sparse_kernel(
                 if (!((MW >> k) & 1u)) mine[k * 128 + cc * 32] += gz;
             }
         }
+    };
+    // Unrolled by two with two register sets (X, Y) and NO register rotation: a copy of a stage-B register would wait
+    // for its load (that copy was 46 % of the kernel's stall samples).  In the trip that consumes entries i and i+1 the
+    // code words of entries i+2 / i+3 and the gradients of entries i+4 / i+5 are requested.
+    StA saX{}, saY{};
+    StB sbX{}, sbY{};
+    if (niter > 0) {
+        saX = fetchA();
+        saY = fetchA();
+        sbX = fetchB(saX);
+        saX = fetchA();
+        sbY = fetchB(saY);
+        saY = fetchA();
+    }
+    for (int it = 0; it < niter; it += 2) {
+        consume(sbX);
+        sbX = fetchB(saX);
+        saX = fetchA();
+        if (it + 1 < niter) consume(sbY);
+        sbY = fetchB(saY);
+        saY = fetchA();
     }
     __syncwarp();
     // lane-transposed reduction: lane l sums cells l, l+32, ...  (cell r = k*4 + c  ->  output index c*F + k)
