@@ -603,25 +603,25 @@ __global__ void __launch_bounds__(FC_THREADS) bwd_fc2_kernel(const float *__rest
         bev[i] = act ? be[j0 + i] : 0.f; w2v[i] = act ? w2s[j0 + i] : 0.f;
     }
     float dW2[4] = {0, 0, 0, 0}, sg[4] = {0, 0, 0, 0}, sgx[4] = {0, 0, 0, 0};
-    float4 hn = make_float4(0.f, 0.f, 0.f, 0.f), hn2 = hn;
-    float gn = 0.f, gn2 = 0.f;
-    uint32_t wn = 0u, wn2 = 0u;
     const bool use_mask = pdrop > 0.f && dropmask;
-    auto fetch = [&](size_t rowi, float4 &hh, float &gg, uint32_t &ww) {
-        if (act) hh = *reinterpret_cast<const float4 *>(h1 + rowi * H + j0);
-        gg = gh2[rowi];
-        ww = use_mask ? dropmask[rowi * 4 + (lane >> 3)] : 0u;
+    // two register sets (X, Y), each written in place by its loads and never copied: a register copy of a load
+    // destination waits for the load (such a copy was 46 % of this kernel's stall samples)
+    float4 hX = make_float4(0.f, 0.f, 0.f, 0.f), hY = hX;
+    float gX = 0.f, gY = 0.f;
+    uint32_t wX = 0u, wY = 0u;
+    auto fetch = [&](int r, float4 &hh, float &gg, uint32_t &ww) {
+        if (r < rows) {
+            const size_t rowi = (size_t)u * B + b0 + r;
+            if (act) hh = *reinterpret_cast<const float4 *>(h1 + rowi * H + j0);
+            gg = gh2[rowi];
+            if (use_mask) ww = dropmask[rowi * 4 + (lane >> 3)];
+        }
     };
-    if (warp < rows) fetch((size_t)u * B + b0 + warp, hn, gn, wn);
-    if (warp + 8 < rows) fetch((size_t)u * B + b0 + warp + 8, hn2, gn2, wn2);
-    for (int r = warp; r < rows; r += 8) {
+    auto row = [&](int r, const float4 &hh, float g, uint32_t ww) {
         const size_t rowi = (size_t)u * B + b0 + r;
-        const float hc[4] = {hn.x, hn.y, hn.z, hn.w};
-        const float g = gn;
+        const float hc[4] = {hh.x, hh.y, hh.z, hh.w};
         uint32_t nib = 15u;
-        if (pdrop > 0.f) nib = use_mask ? (wn >> (4 * (lane & 7))) & 15u : drop_keep4(seed, rowi * (H / 4) + lane, thresh);
-        hn = hn2; gn = gn2; wn = wn2;
-        if (r + 16 < rows) fetch(rowi + 16, hn2, gn2, wn2);       // two rows in flight while this one is processed
+        if (pdrop > 0.f) nib = use_mask ? (ww >> (4 * (lane & 7))) & 15u : drop_keep4(seed, rowi * (H / 4) + lane, thresh);
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             const float xh = (hc[i] - muv[i]) * inv4[i];
@@ -633,6 +633,14 @@ __global__ void __launch_bounds__(FC_THREADS) bwd_fc2_kernel(const float *__rest
             sg[i] += gz2;
             sgx[i] = fmaf(gz2, xh, sgx[i]);
         }
+    };
+    fetch(warp, hX, gX, wX);
+    fetch(warp + 8, hY, gY, wY);
+    for (int r = warp; r < rows; r += 16) {      // rows r, r+8, ... of this warp; each is requested two rows ahead
+        row(r, hX, gX, wX);
+        fetch(r + 16, hX, gX, wX);
+        if (r + 8 < rows) row(r + 8, hY, gY, wY);
+        fetch(r + 24, hY, gY, wY);
     }
     if (act) {
 #pragma unroll
