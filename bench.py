@@ -327,7 +327,7 @@ def extras(torch, dev, model, trainer, data, labels, batch, _cabi, Fn, interpret
                            # dram__bytes_read.sum + dram__bytes_write.sum of one launch at this batch size, from the
                            # ncu --set full capture summarised in profiles/r1_ncu_full_summary_final.txt: the 45.7 MB the
                            # kernel writes are still resident in the 126 MB L2 when it ends
-                           "traffic": 524800 if conv_key.endswith("_tc") and B == 512 and U == 300 else None,
+                           "traffic": 425728 if conv_key.endswith("_tc") and B == 512 and U == 300 else None,
                            "traffic_source": "profiles/r1_ncu_full_summary_final.txt",
                            "peak_source": peak_src, "avg_launch_us": conv_ms * 1e3,
                            "algorithmic_bytes_per_launch": bytes_train,
