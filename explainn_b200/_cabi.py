@@ -44,6 +44,10 @@ SIGNATURES = {
     "explainn_interp_unit_max_noalloc": [_P, _P, _LL, _I, _I, _I, _P, _P, _P, _P, _I, _P],
     "explainn_interp_thresholds": [_P, _I, _P, _P, _P, _P, _P],
     "explainn_interp_pwm_count": [_P, _P, _LL, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P],
+    "explainn_interp_seq_argmax": [_P, _P, _LL, _I, _I, _I, _P, _P, _P, _P, _P, _P],
+    "explainn_act_unit_max": [_P, _I, _LL, _I, _I, _P, _P],
+    "explainn_act_thresholds": [_P, _I, _I, _P, _P, _P],
+    "explainn_act_pwm_count": [_P, _I, _P, _P, _LL, _I, _I, _I, _P, _P, _P, _P, _P],
     "explainn_revcomp_packed": [_P, _P, _LL, _I, _P, _P, _P],
     "explainn_encode_dna": [_P, _P, _LL, _I, _P, _P, _P],
     "explainn_unpack_onehot": [_P, _P, _LL, _I, _P, _I, _P],

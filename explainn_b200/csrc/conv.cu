@@ -385,6 +385,49 @@ struct ScoreSink {
     __device__ void end_tile(int, const ConvArgs &) {}
 };
 
+// (7) per (sequence, unit): the maximum activation and the FIRST position that attains it -- torch.max(act, dim=2)
+//     (explainn/models/networks.py:228,281), act = exp(z) in float32.  exp is monotone but not injective in float32,
+//     so "first maximum of z" is not enough: when a new z exceeds the running maximum by less than 2^-19 (or lies
+//     where the float32 exp saturates / goes subnormal) the two activations are compared themselves; beyond that
+//     margin the <= 2 ulp det_expf is strictly increasing and the comparison of z decides.
+struct ArgmaxSink {
+    struct Params { float *amax; int *apos; };
+    static __host__ __device__ int smem_bytes(int) { return 0; }
+    Params p;
+    int lane, pos;
+    float shift, m;
+    long long out_idx;
+    __device__ void init_cta(unsigned char *, const Params &pp, int, int lane_) { p = pp; lane = lane_; }
+    __device__ void begin_tile(int, int, float shift_, const ConvArgs &) { shift = shift_; }
+    __device__ void begin_seq(long long b, int u0, const ConvArgs &a)
+    {
+        m = -INFINITY;
+        pos = 0;
+        out_idx = u0 + lane < a.U ? b * a.U + u0 + lane : -1;
+    }
+    __device__ __forceinline__ void window(int win, int t, const float *acc, const ConvArgs &a)
+    {
+        if (win >= a.nwin) return;
+#pragma unroll
+        for (int j = 0; j < XB_POOL; ++j) {
+            const float z = __fadd_rn(acc[j], shift);
+            if (t + j < a.S && z > m) {
+                bool later = true;
+                if (__fsub_rn(z, m) < 1.9073486328125e-06f || z > 88.0f || z < -86.0f) later = det_expf(z) > det_expf(m);
+                if (later) pos = t + j;
+                m = z;
+            }
+        }
+    }
+    __device__ void end_seq(const ConvArgs &)
+    {
+        if (out_idx < 0) return;
+        p.amax[out_idx] = det_expf(m);
+        p.apos[out_idx] = pos;
+    }
+    __device__ void end_tile(int, const ConvArgs &) {}
+};
+
 template <class Sink> struct NeedsSeq { static constexpr bool value = false; };
 template <> struct NeedsSeq<CountSink> { static constexpr bool value = true; };
 
@@ -757,6 +800,20 @@ extern "C" int explainn_pwm_score(const uint32_t *codes, const uint32_t *nmask, 
     a.nwin = g.nwin_all;
     ScoreSink::Params sp{out, use_max, accumulate};
     return dispatch_scan<ScoreSink, ScoreSink>(g.G, a, sp, 0, stream);
+}
+
+extern "C" int explainn_interp_seq_argmax(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F,
+                                          const float *tables, const float *wq_t, const float *shift, float *amax,
+                                          int *apos, cudaStream_t stream)
+{
+    ConvArgs a; Geometry g;
+    int rc = fill_args(&a, &g, codes, nmask, B, L, U, F, tables, wq_t, shift);
+    if (rc != XB_OK) return rc;
+    XB_REQUIRE(amax && apos, "interp_seq_argmax: null output");
+    if (B == 0) return XB_OK;
+    a.nwin = g.nwin_all;
+    ArgmaxSink::Params sp{amax, apos};
+    return dispatch_scan<ArgmaxSink, ArgmaxSink>(g.G, a, sp, 0, stream);
 }
 
 extern "C" int explainn_interp_pwm_count(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F,

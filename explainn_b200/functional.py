@@ -173,6 +173,57 @@ def interp_thresholds(zmax):
     return thr, zlo, zhi, amax
 
 
+def interp_seq_argmax(pk, prep):
+    """Per (sequence, unit) maximum activation (float32) and the first position attaining it (int32), both (B,U)."""
+    dev = pk.codes.device
+    amax = torch.empty((pk.B, prep.U), dtype=torch.float32, device=dev)
+    apos = torch.empty((pk.B, prep.U), dtype=torch.int32, device=dev)
+    if pk.B:
+        call("explainn_interp_seq_argmax", ptr(pk.codes), ptr(pk.nmask), pk.B, pk.L, prep.U, prep.F, ptr(prep.tables),
+             ptr(prep.wq_t), ptr(prep.shift), ptr(amax), ptr(apos), stream())
+    return amax, apos
+
+
+def _act_dtype(act):
+    if act.dtype == torch.float16:
+        return _cabi.DTYPE_F16
+    if act.dtype == torch.float32:
+        return _cabi.DTYPE_F32
+    raise ValueError("activations must be float16 or float32, got %s" % act.dtype)
+
+
+def act_unit_max(act, state=None):
+    """Fold a chunk of (N,U,S) activations into the running per-unit maximum state (see explainn_act_unit_max)."""
+    N, U, S = act.shape
+    if state is None:
+        state = torch.zeros(2 * U, dtype=torch.int32, device=act.device)
+    if N:
+        call("explainn_act_unit_max", ptr(act), _act_dtype(act), N, U, S, ptr(state), stream())
+    return state
+
+
+def act_thresholds(state, U, dtype):
+    amax = torch.empty(U, dtype=dtype, device=state.device)
+    thr = torch.empty(U, dtype=dtype, device=state.device)
+    call("explainn_act_thresholds", ptr(state), U, _cabi.DTYPE_F16 if dtype == torch.float16 else _cabi.DTYPE_F32,
+         ptr(amax), ptr(thr), stream())
+    return amax, thr
+
+
+def act_pwm_count(act, pk, F, thr, counts=None, hits=None, seq_hit=None):
+    N, U, S = act.shape
+    if S != pk.L - F + 1 or pk.B != N:
+        raise ValueError("activations of shape %s do not match %d sequences of length %d and filter_size %d"
+                         % (tuple(act.shape), pk.B, pk.L, F))
+    if counts is None:
+        counts = torch.zeros((U, 4, F), dtype=torch.int64, device=act.device)
+        hits = torch.zeros(U, dtype=torch.int64, device=act.device)
+    if N:
+        call("explainn_act_pwm_count", ptr(act), _act_dtype(act), ptr(pk.codes), ptr(pk.nmask), N, pk.L, U, F, ptr(thr),
+             ptr(counts), ptr(hits), ptr(seq_hit), stream())
+    return counts, hits
+
+
 def revcomp_packed(pk):
     """Reverse complement of packed sequences (the other strand)."""
     codes = torch.empty_like(pk.codes)

@@ -69,6 +69,120 @@ def pwm_from_counts(counts, hits):
     return pwm
 
 
+def _chunks_on_device(array, device, budget_bytes=1 << 30):
+    """Yield (lo, hi, device tensor) chunks of a host (or device) array along axis 0, each at most budget_bytes."""
+    n = array.shape[0]
+    if n == 0:
+        return
+    per = max(1, int(np.prod(array.shape[1:])) * array.dtype.itemsize if isinstance(array, np.ndarray)
+              else array[0].numel() * array.element_size())
+    step = max(1, budget_bytes // per)
+    for lo in range(0, n, step):
+        hi = min(n, lo + step)
+        part = array[lo:hi]
+        if isinstance(part, np.ndarray):
+            part = torch.from_numpy(np.ascontiguousarray(part))
+        yield lo, hi, part.to(device, non_blocking=True).contiguous()
+
+
+def get_pwms_explainn(activations, sequences, filter_size, device=None, return_counts=False):
+    """Convert unit activations to PWMs -- drop-in for explainn/interpretation/interpretation.py:176-227.
+
+    activations: (N,U,S) array as returned by get_explainn_unit_activations (float16; float32 is accepted);
+    sequences: (N,4,L) one-hot (torch tensor or numpy array); returns float64 (U,4,filter_size).
+    The threshold 0.5 * max (in the activations' own dtype) and the window counts are computed on the GPU from the
+    caller's array -- nothing is recomputed from the model, so the counts are the reference's integers for that
+    array.  PWM values are float32 counts/total widened to float64 (the reference's result for float32 one-hot
+    input; its float16-input path saturates sums at 2048 and is deliberately not reproduced).  Prefer
+    get_pwms_explainn_fused when the activation array is not needed for anything else."""
+    if isinstance(activations, torch.Tensor):
+        act = activations
+        if act.dtype not in (torch.float16, torch.float32):
+            act = act.float()
+    else:
+        act = np.asarray(activations)
+        if act.dtype not in (np.float16, np.float32):
+            act = act.astype(np.float32)
+    if act.ndim != 3:
+        raise ValueError("activations must have shape (N, U, S), got %s" % (tuple(act.shape),))
+    N, U, S = act.shape
+    F = int(filter_size)
+    if sequences.shape[0] != N or sequences.shape[1] != 4 or sequences.shape[2] != S + F - 1:
+        raise ValueError("sequences of shape %s do not match activations %s and filter_size %d"
+                         % (tuple(sequences.shape), (N, U, S), F))
+    if device is None:
+        if isinstance(sequences, torch.Tensor) and sequences.is_cuda:
+            device = sequences.device
+        elif isinstance(act, torch.Tensor) and act.is_cuda:
+            device = act.device
+        else:
+            device = torch.device("cuda", torch.cuda.current_device())
+    device = torch.device(device)
+    if device.type != "cuda":
+        raise RuntimeError("explainn_b200 runs only on CUDA devices (there is no CPU fallback)")
+    tdtype = torch.float16 if (act.dtype in (np.float16, torch.float16)) else torch.float32
+    invalid = torch.zeros(1, dtype=torch.int32, device=device)
+    with torch.cuda.device(device):
+        parts = list(_chunks_on_device(act, device))
+        keep = len(parts) == 1                      # a single chunk stays on the device for the second pass
+        state = None
+        for lo, hi, a in parts:
+            state = Fn.act_unit_max(a, state)
+        if state is None:
+            state = torch.zeros(2 * U, dtype=torch.int32, device=device)
+        amax, thr = Fn.act_thresholds(state, U, tdtype)
+        counts = torch.zeros((U, 4, F), dtype=torch.int64, device=device)
+        hits = torch.zeros(U, dtype=torch.int64, device=device)
+        for lo, hi, a in (parts if keep else _chunks_on_device(act, device)):
+            x = sequences[lo:hi]
+            if not isinstance(x, torch.Tensor):
+                x = torch.from_numpy(np.ascontiguousarray(x))
+            x = x.to(device, non_blocking=True)
+            pk = Fn.pack_onehot(x, 1, invalid)
+            Fn.act_pwm_count(a, pk, F, thr, counts, hits)
+        Fn.check_invalid(invalid)
+        counts_h, hits_h = counts.cpu().numpy(), hits.cpu().numpy()
+    pwm = pwm_from_counts(counts_h, hits_h)
+    if return_counts:
+        return pwm, counts_h, hits_h
+    return pwm
+
+
+def get_explainn_unit_argmax(data_loader, model, device):
+    """Per (sequence, unit): the maximum activation and the first position that attains it, computed inside the
+    scan (no (N,U,S) tensor) -- `torch.max(activations, dim=2)` (networks.py:228,281) over `model.linears[:3]`.
+    Returns (max (N,U) float32, argmax (N,U) int32).  `data_loader` yields (seq, label) batches or is an (N,4,L)
+    tensor."""
+    if model.linears[1].training:
+        raise RuntimeError("the activation scan uses BatchNorm running statistics; call model.eval() first")
+    prep = model._conv_prep_eval()
+    vals, poss = [], []
+
+    def batches():
+        if isinstance(data_loader, torch.Tensor):
+            for i in range(0, data_loader.shape[0], 8192):
+                yield data_loader[i:i + 8192]
+        else:
+            for item in data_loader:
+                yield item[0] if isinstance(item, (tuple, list)) else item
+
+    with torch.no_grad():
+        for seq in batches():
+            a, p = Fn.interp_seq_argmax(model._pack(seq.to(device, non_blocking=True)), prep)
+            vals.append(a)
+            poss.append(p)
+    model.check_inputs()
+    return torch.cat(vals, 0).cpu().numpy(), torch.cat(poss, 0).cpu().numpy()
+
+
+def unit_argmax_global(amax, apos):
+    """From the per-sequence results of get_explainn_unit_argmax: for every unit the maximum activation over the whole
+    dataset, the first sequence that attains it and the position inside it -> (max (U,), seq (U,), pos (U,))."""
+    n_star = np.argmax(amax, axis=0)
+    u = np.arange(amax.shape[1])
+    return amax[n_star, u], n_star, apos[n_star, u]
+
+
 class PwmAccumulator:
     """Two-pass PWM extraction over a stream of batches without the activation tensor.
 
@@ -174,6 +288,33 @@ def get_specific_unit_importance(activations, model, unit_outputs, filt, target_
     for cl in range(len(target_labels)):
         res[target_labels[cl]] = np.multiply(unit_outputs, weights[cl])[:, filt][hit]
     return pd.Series(res)
+
+
+def _hit_sequences(activations, chunk=1024):
+    """(N,U) bool: does sequence n have any position above 0.5 * max for unit u (interpretation.py:269-279)."""
+    activations = np.asarray(activations)
+    thr = 0.5 * np.amax(activations, axis=(0, 2))
+    out = np.empty(activations.shape[:2], bool)
+    for i in range(0, activations.shape[0], chunk):
+        out[i:i + chunk] = (activations[i:i + chunk] > thr[None, :, None]).any(axis=2)
+    return out
+
+
+def get_median_unit_importance(activations, model, unit_outputs, target_labels):
+    """Median unit importance (unit output x class weight over the sequences that activate the unit) -- drop-in for
+    interpretation.py:261-300.  The reference hard-codes 100 units and 50 classes; this returns
+    (U, len(target_labels)), which is the same (100, 50) matrix for that case.  Units no sequence activates give NaN
+    (numpy's median of an empty array, as in the reference)."""
+    hit = _hit_sequences(activations)
+    weights = model.final.weight.detach().cpu().numpy()
+    unit_outputs = np.asarray(unit_outputs)
+    U, O = hit.shape[1], len(target_labels)
+    out = np.full((U, O), np.nan)
+    for u in range(U):
+        rows = hit[:, u]
+        if rows.any():
+            out[u] = np.median(unit_outputs[rows, u][:, None] * weights[None, :O, u], axis=0)
+    return out
 
 
 def unit_importance_fused(data_loader, model, device, target_labels=None):

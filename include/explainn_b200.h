@@ -160,6 +160,29 @@ int explainn_interp_pwm_count(const uint32_t *codes, const uint32_t *nmask, long
                               const float *zhi, const float *thr, unsigned long long *counts,
                               unsigned long long *hits, unsigned char *seq_hit, cudaStream_t stream);
 
+/* Per (sequence, unit): the maximum activation exp(z) (float32) and the FIRST position that attains it, the rule of
+ * `torch.max(activations, dim=2)` (explainn/models/networks.py:228,281; the reference computes it for its ConvNet
+ * baselines, BASELINE.json's north star asks for it from the ExplaiNN scan).  amax (B,U) fp32, apos (B,U) int32,
+ * bit-identical to oracle/explainn_oracle.c::orc_seq_argmax. */
+int explainn_interp_seq_argmax(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F,
+                               const float *tables, const float *wq_t, const float *shift, float *amax, int *apos,
+                               cudaStream_t stream);
+
+/* ---- threshold / count stage on activations the caller already holds ------------------------------------------
+ * `get_pwms_explainn(activations, sequences, filter_size)` (explainn/interpretation/interpretation.py:176-227) with
+ * the (N,U,S) activation array of get_explainn_unit_activations (:126-149) as input; act_dtype EXPLAINN_DTYPE_F16
+ * (the reference flow) or _F32.  Nothing is recomputed, so the counts are the reference's integers for that array.
+ *   explainn_act_unit_max:   folds one chunk of activations into `state` (2*U uint32, zero-initialised by the caller
+ *                            before the first chunk): np.amax(activations, axis=(0, 2)) incl. its NaN propagation (:187)
+ *   explainn_act_thresholds: amax (U) and thr (U) = 0.5 * amax, both in the activation dtype (:187)
+ *   explainn_act_pwm_count:  counts (U,4,F) u64 / hits (U) u64 += windows at positions with act > thr (:203-214);
+ *                            seq_hit (N,U) u8 optional (NULL to skip), as in explainn_interp_pwm_count. */
+int explainn_act_unit_max(const void *act, int act_dtype, long long N, int U, int S, uint32_t *state, cudaStream_t stream);
+int explainn_act_thresholds(const uint32_t *state, int U, int act_dtype, void *amax, void *thr, cudaStream_t stream);
+int explainn_act_pwm_count(const void *act, int act_dtype, const uint32_t *codes, const uint32_t *nmask, long long N, int L,
+                           int U, int F, const void *thr, unsigned long long *counts, unsigned long long *hits,
+                           unsigned char *seq_hit, cudaStream_t stream);
+
 /* ---- per-unit FC stack, eval mode -----------------------------------------------------------------------
  * Replaces linears[4..13] with BatchNorm in eval mode (explainn/models/networks.py:103-116): grouped 1x1
  * Conv1d(U*P->100U) -> BN -> ReLU -> (Dropout = identity) -> grouped 1x1 Conv1d(100U->U) -> BN -> ReLU.

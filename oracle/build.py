@@ -18,7 +18,7 @@ def build(force=False):
     if (not force and os.path.exists(LIB)
             and os.path.getmtime(LIB) >= os.path.getmtime(SRC)):
         return LIB
-    cmd = ["gcc", "-O2", "-ffp-contract=off", "-fno-fast-math", "-fPIC", "-shared",
+    cmd = ["gcc", "-O2", "-fopenmp", "-ffp-contract=off", "-fno-fast-math", "-fPIC", "-shared",
            "-o", LIB, SRC, "-lm"]
     subprocess.check_call(cmd)
     return LIB

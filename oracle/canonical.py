@@ -138,6 +138,50 @@ def pwm_counts(act16, onehot, filter_size, amax16=None):
     return counts, hits, thr
 
 
+def unit_max_fp16_c(act16):
+    """interpretation.py:187 in C (OpenMP over units) -- same result as unit_max_fp16, for the large test shapes."""
+    a = np.ascontiguousarray(act16, np.float16)
+    N, U, S = a.shape
+    out = np.empty(U, np.float16)
+    lib().orc_unit_max_f16(_p(a), C.c_long(N), C.c_int(U), C.c_int(S), _p(out))
+    return out
+
+
+def pwm_counts_c(act16, onehot, filter_size, amax16=None, counts=None, hits=None, want_seq_hit=False):
+    """interpretation.py:187-214 in C (OpenMP over units): same integers as pwm_counts (tests/test_oracle_golden.py
+    holds the two against each other and against the reference's PWMs), fast enough for >= 16k sequences at
+    U=300.  `counts`/`hits` may be passed in to accumulate over chunks; `amax16` carries the global maxima then."""
+    a = np.ascontiguousarray(act16, np.float16)
+    x = np.ascontiguousarray(onehot, np.float32)
+    N, U, S = a.shape
+    L = x.shape[2]
+    F = int(filter_size)
+    assert x.shape[0] == N and x.shape[1] == 4 and S + F - 1 <= L
+    if amax16 is None:
+        amax16 = unit_max_fp16_c(a)
+    thr = (np.float16(0.5) * np.asarray(amax16, np.float16)).astype(np.float16)
+    if counts is None:
+        counts = np.zeros((U, 4, F), np.int64)
+        hits = np.zeros(U, np.int64)
+    seq_hit = np.zeros((N, U), np.uint8) if want_seq_hit else None
+    lib().orc_pwm_counts_f16(_p(a), C.c_long(N), C.c_int(U), C.c_int(S), _p(thr), _p(x), C.c_int(L), C.c_int(F),
+                             _p(counts), _p(hits), _p(seq_hit) if want_seq_hit else None)
+    if want_seq_hit:
+        return counts, hits, thr, seq_hit
+    return counts, hits, thr
+
+
+def seq_argmax(z):
+    """Per (sequence, unit): max activation (float32 det_expf(z)) and its FIRST position -- torch.max(act, dim=2),
+    networks.py:228,281.  z (B,U,S) float32 -> (amax (B,U) float32, apos (B,U) int32)."""
+    z = np.ascontiguousarray(z, np.float32)
+    B, U, S = z.shape
+    amax = np.empty((B, U), np.float32)
+    apos = np.empty((B, U), np.int32)
+    lib().orc_seq_argmax(_p(z), C.c_long(B * U), C.c_int(S), _p(amax), _p(apos))
+    return amax, apos
+
+
 def pwm_from_counts_hits(counts, hits):
     """interpretation.py:196,217-224 -- float32 column normalisation widened to float64; units
     for which no window was collected (hits == 0) keep 0.25 everywhere."""

@@ -12,6 +12,7 @@
  *   - MaxPool1d(k, stride) floor mode ... explainn/models/networks.py:102
  *   - fp16 activation scan .............. explainn/interpretation/interpretation.py:126-149
  *   - threshold/count PWM extraction .... explainn/interpretation/interpretation.py:176-227
+ *   - per-sequence max / first argmax ... torch.max(act, dim=2) as in explainn/models/networks.py:228,281
  *
  * Parity pinning: the reference ships no known-answer tests.  This
  * restatement is pinned against outputs of the reference itself, generated in the build
@@ -64,6 +65,7 @@ ORC_API float orc_expf(float x)
 
 ORC_API void orc_expf_vec(const float *x, float *y, long n)
 {
+#pragma omp parallel for schedule(static)
     for (long i = 0; i < n; ++i) y[i] = orc_expf(x[i]);
 }
 
@@ -124,8 +126,13 @@ ORC_API void orc_conv_z(const uint32_t *codes, const uint32_t *nmask, long B, in
 {
     int wc = orc_words_codes(L), wm = orc_words_mask(L);
     int S = L - F + 1, G = (F + 3) / 4;
+    /* sequences are independent: the OpenMP split changes no arithmetic */
+#pragma omp parallel for schedule(static)
     for (long b = 0; b < B; ++b) {
         const uint32_t *cb = codes + b * wc, *mb = nmask + b * wm;
+        /* decode once per sequence: 0..3 = base, 4 = N column (same values get_code / get_mask return per tap) */
+        uint8_t cd[L + 4 * G + 4];
+        for (int i = 0; i < L + 4 * G + 4; ++i) cd[i] = (i >= L || get_mask(mb, i, L)) ? 4 : (uint8_t)get_code(cb, i);
         for (int u = 0; u < U; ++u) {
             const float *wu = wq + (long)u * 4 * F;
             float *zr = z + ((long)b * U + u) * S;
@@ -136,7 +143,7 @@ ORC_API void orc_conv_z(const uint32_t *codes, const uint32_t *nmask, long B, in
                     for (int j = 0; j < 4; ++j) {
                         int k = 4 * g + j;
                         float a = 0.0f;
-                        if (k < F && !get_mask(mb, s + k, L)) a = wu[get_code(cb, s + k) * F + k];
+                        if (k < F && cd[s + k] < 4) a = wu[cd[s + k] * F + k];
                         t = (j == 0) ? a : t + a;
                     }
                     acc = (g == 0) ? t : acc + t;
@@ -164,5 +171,87 @@ ORC_API void orc_pool_exp(const float *z, long BU, int S, int pk, int ps,
             pooled[r * P + p] = orc_expf(m);
             if (idx) idx[r * P + p] = (uint8_t)im;
         }
+    }
+}
+
+/* ---- float16 -> float32 (exact) ---- */
+static inline float half_to_float(uint16_t h)
+{
+    uint32_t sign = (uint32_t)(h & 0x8000u) << 16, e = (h >> 10) & 0x1Fu, m = h & 0x3FFu;
+    if (e == 0x1Fu) return u2f(sign | 0x7F800000u | (m << 13));
+    if (e == 0) {
+        if (m == 0) return u2f(sign);
+        float f = (float)m * 5.9604644775390625e-08f;        /* m * 2^-24, exact */
+        return sign ? -f : f;
+    }
+    return u2f(sign | ((e + 112u) << 23) | (m << 13));
+}
+
+/* ---- per-unit maximum of float16 activations, numpy semantics (np.amax propagates NaN):
+ *      interpretation.py:187  np.amax(activations, axis=(0, 2)).  act16 (N,U,S) raw float16 bits,
+ *      amax16 (U) raw float16 bits out. ---- */
+ORC_API void orc_unit_max_f16(const uint16_t *act16, long N, int U, int S, uint16_t *amax16)
+{
+#pragma omp parallel for schedule(static)
+    for (int u = 0; u < U; ++u) {
+        float m = -INFINITY;
+        uint16_t mb = 0xFC00u;
+        int nan = 0;
+        for (long n = 0; n < N && !nan; ++n) {
+            const uint16_t *row = act16 + ((long)n * U + u) * S;
+            for (int s = 0; s < S; ++s) {
+                float v = half_to_float(row[s]);
+                if (v != v) { nan = 1; mb = row[s]; break; }
+                if (v > m) { m = v; mb = row[s]; }
+            }
+        }
+        amax16[u] = mb;
+    }
+}
+
+/* ---- threshold / count stage of get_pwms_explainn (interpretation.py:203-214) on the caller's float16
+ *      activations.  thr16 (U) raw float16 bits (0.5 * max, computed by the caller in float16 as numpy does);
+ *      onehot (N,4,L) float32; a hit is act > thr in float16 (the conversion to float32 is exact, so the
+ *      comparison is the same).  counts (U,4,F) and hits (U) int64, accumulated into.  seq_hit (N,U) u8 or NULL. ---- */
+ORC_API void orc_pwm_counts_f16(const uint16_t *act16, long N, int U, int S, const uint16_t *thr16,
+                                const float *onehot, int L, int F, long long *counts, long long *hits,
+                                uint8_t *seq_hit)
+{
+#pragma omp parallel for schedule(dynamic, 1)
+    for (int u = 0; u < U; ++u) {
+        const float thr = half_to_float(thr16[u]);
+        long long *cu = counts + (long)u * 4 * F;
+        for (long n = 0; n < N; ++n) {
+            const uint16_t *row = act16 + ((long)n * U + u) * S;
+            const float *x = onehot + (long)n * 4 * L;
+            int any = 0;
+            for (int s = 0; s < S; ++s) {
+                if (!(half_to_float(row[s]) > thr)) continue;
+                any = 1;
+                hits[u] += 1;
+                for (int c = 0; c < 4; ++c)
+                    for (int k = 0; k < F; ++k)
+                        if (x[(long)c * L + s + k] != 0.0f) cu[c * F + k] += 1;
+            }
+            if (seq_hit) seq_hit[n * U + u] = (uint8_t)any;
+        }
+    }
+}
+
+/* ---- per (sequence, unit): maximum activation and the FIRST position that attains it, the rule of
+ *      torch.max(act, dim=2) (networks.py:228,281).  act = orc_expf(z) in float32.  z (BU,S). ---- */
+ORC_API void orc_seq_argmax(const float *z, long BU, int S, float *amax, int32_t *apos)
+{
+#pragma omp parallel for schedule(static)
+    for (long r = 0; r < BU; ++r) {
+        const float *zr = z + r * S;
+        float m = orc_expf(zr[0]);
+        int im = 0;
+        for (int s = 1; s < S; ++s) {
+            float v = orc_expf(zr[s]);
+            if (v > m) { m = v; im = s; }
+        }
+        amax[r] = m;
+        apos[r] = im;
     }
 }

@@ -120,3 +120,49 @@ def test_det_expf_accuracy_and_monotone_sample():
         assert np.all(e[1:] >= e[:-1]), a
         h = e.astype(np.float16)
         assert np.all(h[1:] >= h[:-1]), a
+
+
+@pytest.mark.parametrize("name", EVAL_GOLDENS)
+def test_c_count_stage_and_argmax_match_reference(name):
+    """The C (OpenMP) count stage used for the large shapes equals the numpy restatement and the reference's PWMs;
+    the per-sequence max / first-argmax restatement equals torch.max(act, dim=2) (networks.py:228,281) on the
+    activations of the reference's own graph wherever the canonical exp does not move the maximum."""
+    g = load_golden(name)
+    F = int(g["F"])
+    x = onehot_from_codes(g["codes"])
+    m = _port(g).eval()
+    a16_ref = tp.unit_activations_fp16(m, torch.from_numpy(x))
+    assert np.array_equal(cn.unit_max_fp16_c(a16_ref).view(np.uint16), cn.unit_max_fp16(a16_ref).view(np.uint16))
+    cnt, hits, thr = cn.pwm_counts(a16_ref, x, F)
+    cnt_c, hits_c, thr_c, seq_hit = cn.pwm_counts_c(a16_ref, x, F, want_seq_hit=True)
+    assert np.array_equal(cnt_c, cnt) and np.array_equal(hits_c, hits) and np.array_equal(thr_c, thr)
+    assert np.array_equal(cn.pwm_from_counts_hits(cnt_c, hits_c), g["pwm"])
+    assert np.array_equal(seq_hit.astype(bool), (a16_ref > thr[None, :, None]).any(axis=2))
+    # chunked accumulation with the global maxima gives the same integers
+    amax = cn.unit_max_fp16_c(a16_ref)
+    h = a16_ref.shape[0] // 2
+    c2, h2, _ = cn.pwm_counts_c(a16_ref[:h], x[:h], F, amax16=amax)
+    c2, h2, _ = cn.pwm_counts_c(a16_ref[h:], x[h:], F, amax16=amax, counts=c2, hits=h2)
+    assert np.array_equal(c2, cnt) and np.array_equal(h2, hits)
+    # NaN and inf handling of the maximum follows numpy
+    b = a16_ref[:4].copy()
+    b[1, 0, 3] = np.nan
+    b[2, 1, 5] = np.inf
+    assert np.array_equal(cn.unit_max_fp16_c(b).view(np.uint16)[1:], np.amax(b, axis=(0, 2)).view(np.uint16)[1:])
+    assert np.isnan(cn.unit_max_fp16_c(b)[0])
+    # per-sequence max and first argmax
+    sd = state_dict_from(g)
+    n = lambda k: sd[k].numpy()
+    codes, nmask, _ = cn.pack_onehot(x)
+    wq, shift, _ = cn.fold_bn(n("linears.0.weight"), n("linears.0.bias"), n("linears.1.weight"),
+                              n("linears.1.bias"), n("linears.1.running_mean"), n("linears.1.running_var"))
+    z = cn.conv_z(codes, nmask, int(g["L"]), wq, shift)
+    amax_c, apos_c = cn.seq_argmax(z)
+    with torch.no_grad():
+        act = m.activations(torch.from_numpy(x))
+    vmax, imax = torch.max(act, dim=2)
+    np.testing.assert_allclose(amax_c, vmax.numpy(), rtol=1e-5)
+    # positions agree except where the two fp32 evaluations order a near-tie differently
+    assert np.mean(apos_c != imax.numpy()) < 2e-3
+    e = cn.expf(z)
+    assert np.array_equal(apos_c, np.argmax(e, axis=2)) and np.array_equal(amax_c, e.max(axis=2))
