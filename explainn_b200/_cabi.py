@@ -74,7 +74,8 @@ SIGNATURES = {
     "explainn_p2p_export": [_P, _P],
     "explainn_p2p_open": [_P, _P],
     "explainn_p2p_close": [_P],
-    "explainn_p2p_adam_step": [_P, _P, _P, _LL, _P, _P, _P, _I, _I, _ULL, _F, _F, _F, _F, _P],
+    "explainn_p2p_error": [_P, _P],
+    "explainn_p2p_adam_step": [_P, _P, _P, _LL, _P, _P, _P, _I, _I, _ULL, _F, _F, _F, _F, C.c_double, _P],
 }
 _RESTYPES = {
     "explainn_last_error": C.c_char_p,
@@ -124,6 +125,24 @@ def ptr(t):
 
 def stream():
     return torch.cuda.current_stream().cuda_stream
+
+
+def on_device_of(argnum=1):
+    """Decorator: run the wrapped method with the device of its tensor argument current, so that the stream handed
+    to the kernels (torch's current stream of the CURRENT device) and per-device caches belong to the GPU that holds
+    the data -- a model on cuda:1 works while cuda:0 is current, as with the reference's plain `device` argument."""
+    import functools
+
+    def deco(fn):
+        @functools.wraps(fn)
+        def wrapper(*args, **kw):
+            t = args[argnum] if len(args) > argnum else None
+            if isinstance(t, torch.Tensor) and t.is_cuda and t.device.index != torch.cuda.current_device():
+                with torch.cuda.device(t.device):
+                    return fn(*args, **kw)
+            return fn(*args, **kw)
+        return wrapper
+    return deco
 
 
 LAUNCHES = 0   # kernels launched through this binding (bench.py reports it)

@@ -85,8 +85,15 @@ struct TcArgs {
     unsigned char *idx;     // train only
     const float *gamma, *beta;
     int gsz;                // unit tiles (of 128) whose weights stay resident in shared memory together
-    int dbg;                // XB_TC_DBG bitmask (profiling experiments only): 1 no stores, 2 no V build, 4 no drain, 8 no MMA
+#ifdef XB_EXPERIMENT
+    int dbg;                // XB_TC_DBG bitmask (experiment build only): 1 no stores, 2 no V build, 4 no drain, 8 no MMA
+#endif
 };
+#ifdef XB_EXPERIMENT
+#define XB_DBG(a, bit) ((a).dbg & (bit))
+#else
+#define XB_DBG(a, bit) 0
+#endif
 
 constexpr int TC_VROWS = TC_N + 64;     // dinucleotide entries per tile: positions n0 .. n0 + 240 + 2*KC
 constexpr int TC_VBUFS = 4;             // V tiles in flight: tile n may be built while the MMAs of n-1, n-2 run
@@ -290,7 +297,7 @@ __global__ void __launch_bounds__(TC_THREADS + 64, 1) conv_tc_kernel(const TcArg
                 const uint64_t dV = make_smem_desc(smem_u32(V), 32, 128);
                 if (tc_elect_one()) {
                     tc_fence_after();
-                    for (int ks = 0; ks < ((a.dbg & 8) ? 0 : KS); ++ks) {
+                    for (int ks = 0; ks < (XB_DBG(a, 8) ? 0 : KS); ++ks) {
                         tc_mma_f16(d, dA_hi + ks * 16, dV + ks * 4, idesc, ks > 0 ? 1u : 0u);
                         tc_mma_f16(d, dA_lo + ks * 16, dV + ks * 4, idesc, 1u);
                     }
@@ -349,7 +356,7 @@ __global__ void __launch_bounds__(TC_THREADS + 64, 1) conv_tc_kernel(const TcArg
                     ox[j] = (c & 2u) ? 0u : one;
                     oy[j] = (c & 2u) ? one : 0u;
                 }
-                if (lane < TC_VROWS / 16 && !((a.dbg & 2) && vi >= TC_VBUFS)) {
+                if (lane < TC_VROWS / 16 && !(XB_DBG(a, 2) && vi >= TC_VBUFS)) {
 #pragma unroll
                     for (int j = 0; j < 16; ++j) V[16 * lane + j] = make_uint4(ox[j], oy[j], ox[j + 1], oy[j + 1]);
                 }
@@ -394,7 +401,7 @@ __global__ void __launch_bounds__(TC_THREADS + 64, 1) conv_tc_kernel(const TcArg
                 mbar_wait(&tmem_full[grp], use & 1);
                 tc_fence_after();
                 XB_CLK(3);                                 // wait for the accumulator
-                if (u0 + 32 * (warp & 3) < a.U && !(a.dbg & 4)) {   // lane quarters without a valid unit are not read at all
+                if (u0 + 32 * (warp & 3) < a.U && !XB_DBG(a, 4)) {   // lane quarters without a valid unit are not read at all
                     if (((warp >> 2) & 1) == 0) tc_drain<TRAIN, 0, SPLIT>(taddr, row, nwin, sst, stage, stage_i, shift, gam, bet);
                     else tc_drain<TRAIN, SPLIT, TC_WIN * XB_POOL>(taddr, row, nwin, sst, stage, stage_i, shift, gam, bet);
                 }
@@ -403,7 +410,7 @@ __global__ void __launch_bounds__(TC_THREADS + 64, 1) conv_tc_kernel(const TcArg
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&tmem_empty[grp]);
                 XB_CLK(4);                                 // drain
-                if (a.dbg & 1) continue;
+                if (XB_DBG(a, 1)) continue;
 
                 // ---- store the staged tile ----
                 fence_proxy_async();
@@ -412,7 +419,7 @@ __global__ void __launch_bounds__(TC_THREADS + 64, 1) conv_tc_kernel(const TcArg
                 const int nvalid = min(TC_M, a.U - u0);
                 const size_t o = ((size_t)t.b * a.U + u0) * a.P;
                 const uint32_t bytes = (uint32_t)nvalid * a.P * 4;
-                const bool bulk_f = sst == a.P && (bytes & 15u) == 0 && ((o * 4) & 15u) == 0 && !(a.dbg & 16);
+                const bool bulk_f = sst == a.P && (bytes & 15u) == 0 && ((o * 4) & 15u) == 0 && !XB_DBG(a, 16);
                 const bool bulk_i = TRAIN && sst == a.P && ((bytes / 4) & 15u) == 0 && (o & 15u) == 0;
                 if (gtid == 0 && (bulk_f || bulk_i)) {
                     if (bulk_f) {
@@ -505,7 +512,9 @@ static int launch_tc(bool train, const uint32_t *codes, const uint32_t *nmask, l
     a.codes = codes; a.nmask = nmask; a.B = B; a.L = L; a.F = F; a.U = U; a.K = tc_K(F);
     a.P = ((L - F + 1) - XB_POOL) / XB_POOL + 1;
     a.wc = xb_words_codes(L); a.wm = xb_words_mask(L);
+#ifdef XB_EXPERIMENT
     { const char *e = getenv("XB_TC_DBG"); a.dbg = e ? atoi(e) : 0; }
+#endif
     a.images = (const __half *)images; a.shift = shift; a.pooled = pooled; a.xhat = xhat; a.idx = idx; a.gamma = gamma; a.beta = beta;
     const int n_mt = (U + TC_M - 1) / TC_M, nchunk = (a.P + TC_WIN - 1) / TC_WIN;
     const size_t tile_bytes = (size_t)2 * TC_M * a.K * 2;

@@ -1025,7 +1025,11 @@ int launch_fc1_tc(bool eval, const FcTcArgs &a, cudaStream_t stream)
     int grid = 2 * xb_num_sms();
     if (total < grid) grid = (int)total;
     cudaError_t e;
+#ifdef XB_EXPERIMENT     // ablation switch of the experiment build only (build_lib.py: XB_NVCC_EXTRA=-DXB_EXPERIMENT)
     static const bool no_pipe = [] { const char *v = getenv("XB_FC_PIPE"); return v && v[0] == '0'; }();
+#else
+    constexpr bool no_pipe = false;
+#endif
     if (eval && a.P <= FT_KCH && !no_pipe) {
         e = cudaFuncSetAttribute(fc1_tc_eval_pipe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e == cudaSuccess) fc1_tc_eval_pipe_kernel<<<grid, FT_THREADS, smem, stream>>>(a);
@@ -1091,8 +1095,12 @@ int xb_linear_tc(const float *x, long long B, int U, int C, const float *W, cons
 
 bool xb_fc_tc_enabled()
 {
+#ifdef XB_EXPERIMENT     // XB_FC_TC=0 selects the CUDA-core kernels (experiment build only)
     const char *e = getenv("XB_FC_TC");
     return !(e && e[0] == '0');
+#else
+    return true;
+#endif
 }
 
 // returns XB_ERR_UNSUPPORTED (without setting an error) when the shape does not fit the tensor-core tiles

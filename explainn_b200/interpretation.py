@@ -7,6 +7,7 @@ import torch
 import torch.nn as nn
 
 from . import functional as Fn
+from ._cabi import on_device_of as _on_device_of
 
 
 def get_explainn_predictions(data_loader, model, device, isSigmoid=False):
@@ -196,13 +197,15 @@ class PwmAccumulator:
         if model.linears[1].training:
             raise RuntimeError("PWM extraction uses BatchNorm running statistics; call model.eval() first")
         self.model = model
-        self.prep = model._conv_prep_eval()
+        with torch.cuda.device(model.linears[0].weight.device):
+            self.prep = model._conv_prep_eval()
         self.zmax = None
         self.thr = self.zlo = self.zhi = self.amax = None
         self.counts = self.hits = None
         self.keep_seq_hits = False      # set True to also collect, per batch, which sequences pass each unit's threshold
         self.seq_hits = []
 
+    @_on_device_of(1)
     def scan_max(self, x):
         pk = self.model._pack(x)
         self.zmax = Fn.interp_unit_max(pk, self.prep, self.zmax)
@@ -210,8 +213,10 @@ class PwmAccumulator:
     def finish_max(self):
         if self.zmax is None:
             raise RuntimeError("scan_max was never called")
-        self.thr, self.zlo, self.zhi, self.amax = Fn.interp_thresholds(self.zmax)
+        with torch.cuda.device(self.zmax.device):
+            self.thr, self.zlo, self.zhi, self.amax = Fn.interp_thresholds(self.zmax)
 
+    @_on_device_of(1)
     def scan_count(self, x):
         pk = self.model._pack(x)
         seq_hit = None

@@ -11,6 +11,7 @@ import torch
 import torch.nn as nn
 
 from . import functional as Fn
+from ._cabi import on_device_of
 
 HIDDEN = Fn.HIDDEN
 
@@ -81,16 +82,13 @@ class ExplaiNN(nn.Module):
 
     def __init__(self, num_cnns, input_length, num_classes, filter_size=19, num_fc=2, pool_size=7, pool_stride=7,
                  weight_path=None):
-        """
-        :param num_cnns: int, number of independent cnn units
-        :param input_length: int, input sequence length
-        :param num_classes: int, number of outputs
-        :param filter_size: int, size of the unit's filter, default=19
-        :param num_fc: int, number of FC layers in the unit, default=2
-        :param pool_size: int, size of the unit's maxpooling layer, default=7
-        :param pool_stride: int, stride of the unit's maxpooling layer, default=7
-        :param weight_path: string, path to the file with model weights
-        """
+        """Same positional / keyword arguments as the reference constructor (networks.py:48-49).
+
+        num_cnns independent units, each one filter of width filter_size over a length-input_length one-hot
+        sequence, max-pooling (pool_size, pool_stride), num_fc per-unit fully connected layers, and one Linear over
+        the unit outputs to num_classes logits.  weight_path, if given, is a state_dict file of the reference (or of
+        this class) and is loaded at the end of construction.  Limits of the kernels are checked here:
+        filter_size <= 24, input_length <= 2048 (see the NotImplementedError messages)."""
         super().__init__()
         self._options = {
             "num_cnns": num_cnns,
@@ -111,6 +109,9 @@ class ExplaiNN(nn.Module):
                                       % (pool_size, pool_stride))
         if filter_size > 24:
             raise NotImplementedError("explainn_b200: filter_size <= 24 (k-mer tables of the fused conv kernel)")
+        if input_length > 2048:
+            raise NotImplementedError("explainn_b200: input_length <= 2048 (a packed sequence is prefetched into the "
+                                      "registers of one warp by the scan kernels)")
         U = num_cnns
         S = input_length - (filter_size - 1)
         P = 1 if num_fc == 0 else Fn.pooled_len(input_length, filter_size, pool_size, pool_stride)
@@ -192,6 +193,7 @@ class ExplaiNN(nn.Module):
         return self.linears[1].training
 
     # ------------------------------------------------------------------ fused pieces (eval statistics)
+    @on_device_of(1)
     def _activations(self, x, dtype=torch.float16):
         """exp(BN(conv(x))) as (B,U,S) -- interpretation.py:143-145."""
         if self._bn_uses_batch_stats():
@@ -200,6 +202,7 @@ class ExplaiNN(nn.Module):
         pk = self._pack(x)
         return Fn.unit_activations(pk, self._conv_prep_eval(), dtype)
 
+    @on_device_of(1)
     def _pooled(self, x):
         """max-pooled activations (B,U,P)."""
         return self._pooled_packed(self._pack(x))
@@ -216,6 +219,7 @@ class ExplaiNN(nn.Module):
             return Fn.conv_pool_fwd_tc(pk, tcp)
         return Fn.conv_pool_fwd(pk, self._conv_prep_eval())
 
+    @on_device_of(1)
     def _unit_outputs_eval(self, x):
         return self._unit_outputs_eval_packed(self._pack(x))
 
@@ -241,6 +245,7 @@ class ExplaiNN(nn.Module):
             L[10].weight.detach(), L[10].bias.detach(),
             (bn3.weight.detach(), bn3.bias.detach(), bn3.running_mean, bn3.running_var), bn2.eps)
 
+    @on_device_of(1)
     def _unit_outputs(self, x):
         if self.training:
             from . import autograd_fn
@@ -248,6 +253,7 @@ class ExplaiNN(nn.Module):
         return self._unit_outputs_eval(x)
 
     # ------------------------------------------------------------------ forward
+    @on_device_of(1)
     def forward(self, x):
         """x: (B,4,L) one-hot float tensor on the GPU -> (B,C) logits (networks.py:152-162)."""
         if self.training:
@@ -299,6 +305,7 @@ class PWM(nn.Module):
         out = Fn.pwm_score(pk, prep, use_max)
         return Fn.pwm_score(Fn.revcomp_packed(pk), prep, use_max, out=out)
 
+    @on_device_of(1)
     def forward(self, x):
         """x: (B,4,L) one-hot float tensor on the GPU -> (B,G) scores."""
         _require_cuda(x)

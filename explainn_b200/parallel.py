@@ -49,13 +49,35 @@ def allreduce_counts(counts, hits):
 
 
 def allreduce_mean_gradients(flat_grad):
-    """The one collective of a training step: SUM the flat gradient buffer; returns the factor by which the
-    optimizer must scale it (1/world) so that the update uses the mean over ranks (DDP semantics)."""
+    """The one collective of a training step on the NCCL path (train.FusedTrainer._finish_allreduce): SUM the flat
+    gradient buffer; returns the factor by which the optimizer must scale it (1/world) so that the update uses the
+    mean over ranks (DDP semantics)."""
     d = _dist()
     if d is not None and d.get_world_size() > 1:
         d.all_reduce(flat_grad, op=d.ReduceOp.SUM)
         return 1.0 / d.get_world_size()
     return 1.0
+
+
+def broadcast_model_state(model, src=0):
+    """Make every replica start from rank `src`'s parameters and buffers (what DistributedDataParallel does at
+    construction): without it, ranks that built their models from different RNG states would stay different."""
+    d = _dist()
+    if d is None or d.get_world_size() == 1:
+        return
+    for t in list(model.parameters()) + list(model.buffers()):
+        d.broadcast(t.data, src=src)
+
+
+def allreduce_mean_scalar(value, device):
+    """Mean over ranks of a python float (epoch validation loss: every rank must take the same best-epoch and
+    early-stopping decisions, or the replicas and the collectives of the next epoch fall apart)."""
+    d = _dist()
+    if d is None or d.get_world_size() == 1:
+        return value
+    t = torch.tensor([value], dtype=torch.float64, device=device if d.get_backend() == "nccl" else "cpu")
+    d.all_reduce(t, op=d.ReduceOp.SUM)
+    return float(t.item()) / d.get_world_size()
 
 
 def gather_rows(local_rows, n_total):
@@ -119,10 +141,11 @@ class _DevBuffer:
 
 
 class PeerGradients:
-    """Peer-memory plumbing of the fused all-reduce + Adam kernel (csrc/p2p.cu).  Every rank allocates its flat gradient
-    buffer and a small flag buffer as plain cudaMalloc memory (CUDA IPC exports whole allocations), exchanges the IPC
-    handles over the process group and maps the peers' buffers for its own GPU, so that `explainn_p2p_adam_step` reads
-    all gradients over NVLink.  `self.flat_grad` is the torch view the backward kernels write.  One node only."""
+    """Peer-memory plumbing of the fused reduce-scatter + Adam + all-gather kernel (csrc/p2p.cu).  Every rank allocates
+    its flat gradient buffer, its flat parameter buffer and a small flag buffer as plain cudaMalloc memory (CUDA IPC
+    exports whole allocations), exchanges the IPC handles over the process group and maps the peers' buffers for its own
+    GPU, so that `explainn_p2p_adam_step` reads all gradients and writes all parameter replicas over NVLink.
+    `self.flat_grad` / `self.flat_param` are the torch views the kernels and the nn.Parameters use.  One node only."""
 
     def __init__(self, n_floats, device):
         import ctypes
@@ -141,14 +164,18 @@ class PeerGradients:
         payload = None
         try:
             self._gbuf = _DevBuffer(4 * n_floats, self.device)
+            self._pbuf = _DevBuffer(4 * n_floats, self.device)
             self._fbuf = _DevBuffer(_cabi.lib.explainn_p2p_flag_bytes(), self.device)
             self.flat_grad = torch.as_tensor(self._gbuf, device=self.device).view(torch.float32)
+            self.flat_param = torch.as_tensor(self._pbuf, device=self.device).view(torch.float32)
             self.flags = torch.as_tensor(self._fbuf, device=self.device).view(torch.int64)
-            hg, hf = (ctypes.c_ubyte * 64)(), (ctypes.c_ubyte * 64)()
+            handles = []
             with torch.cuda.device(self.device):
-                _cabi.call("explainn_p2p_export", self._gbuf.ptr, ctypes.cast(hg, ctypes.c_void_p))
-                _cabi.call("explainn_p2p_export", self._fbuf.ptr, ctypes.cast(hf, ctypes.c_void_p))
-            payload = (n_floats, bytes(hg), bytes(hf))
+                for buf in (self._gbuf, self._pbuf, self._fbuf):
+                    h = (ctypes.c_ubyte * 64)()
+                    _cabi.call("explainn_p2p_export", buf.ptr, ctypes.cast(h, ctypes.c_void_p))
+                    handles.append(bytes(h))
+            payload = (n_floats, handles)
         except Exception as ex:
             self.ok, self.error = False, "export: %s" % ex
         everyone = [None] * self.world
@@ -156,26 +183,26 @@ class PeerGradients:
         if any(e is None for e in everyone):
             self.ok = False
             self.error = self.error or "a peer could not export its buffers"
-        g_ptrs, f_ptrs = [], []
+        ptrs = [[], [], []]
         if self.ok:
             try:
-                for q, (qn, qg, qf) in enumerate(everyone):
+                for q, (qn, qh) in enumerate(everyone):
                     if qn != n_floats:
                         raise RuntimeError("rank %d holds %d gradient elements, this rank %d" % (q, qn, n_floats))
                     if q == self.rank:
-                        g_ptrs.append(self._gbuf.ptr)
-                        f_ptrs.append(self._fbuf.ptr)
+                        for lst, buf in zip(ptrs, (self._gbuf, self._pbuf, self._fbuf)):
+                            lst.append(buf.ptr)
                         continue
-                    pg, pf = ctypes.c_void_p(), ctypes.c_void_p()
                     with torch.cuda.device(self.device):
-                        _cabi.call("explainn_p2p_open", ctypes.cast((ctypes.c_ubyte * 64).from_buffer_copy(qg), ctypes.c_void_p), ctypes.byref(pg))
-                        self._opened.append(pg.value)
-                        _cabi.call("explainn_p2p_open", ctypes.cast((ctypes.c_ubyte * 64).from_buffer_copy(qf), ctypes.c_void_p), ctypes.byref(pf))
-                        self._opened.append(pf.value)
-                    g_ptrs.append(pg.value)
-                    f_ptrs.append(pf.value)
-                self.g_array = (ctypes.c_void_p * 8)(*g_ptrs)
-                self.f_array = (ctypes.c_void_p * 8)(*f_ptrs)
+                        for lst, hb in zip(ptrs, qh):
+                            pp = ctypes.c_void_p()
+                            _cabi.call("explainn_p2p_open", ctypes.cast((ctypes.c_ubyte * 64).from_buffer_copy(hb), ctypes.c_void_p),
+                                       ctypes.byref(pp))
+                            self._opened.append(pp.value)
+                            lst.append(pp.value)
+                self.g_array = (ctypes.c_void_p * 8)(*ptrs[0])
+                self.p_array = (ctypes.c_void_p * 8)(*ptrs[1])
+                self.f_array = (ctypes.c_void_p * 8)(*ptrs[2])
                 torch.cuda.synchronize(self.device)
             except Exception as ex:
                 self.ok, self.error = False, "open: %s" % ex
@@ -184,6 +211,21 @@ class PeerGradients:
         if int(agree.item()) == 0:
             self.ok = False
             self.error = self.error or "a peer could not map the buffers"
+
+    def slice_range(self, n_floats):
+        """[lo, hi) in floats of the parameter slice this rank owns (same split as csrc/p2p.cu)."""
+        n4 = n_floats // 4
+        return 4 * (n4 * self.rank // self.world), 4 * (n4 * (self.rank + 1) // self.world)
+
+    def check(self):
+        """Raise if a step of the peer-memory optimizer kernel gave up waiting for a rank (synchronises)."""
+        import ctypes
+        w = ctypes.c_int(0)
+        with torch.cuda.device(self.device):
+            self._cabi.call("explainn_p2p_error", self._fbuf.ptr, ctypes.byref(w))
+        if w.value:
+            raise RuntimeError("explainn_b200: the peer-memory optimizer step gave up waiting for rank %d "
+                               "(XB_P2P_TIMEOUT_S); the replicas are no longer consistent" % (w.value - 1))
 
     def __del__(self):
         try:

@@ -67,8 +67,9 @@ class FusedTrainer:
             self.offsets.append(off)
             off += (n + 3) // 4 * 4
         self.n = off
-        self.flat_p = torch.zeros(off, dtype=torch.float32, device=dev)
         d0 = _dist()
+        if d0 is not None and d0.get_world_size() > 1:
+            parallel.broadcast_model_state(model)       # all replicas start from rank 0's weights and BatchNorm buffers
         # world 2..8 on one node: all-reduce + Adam run as ONE kernel that reads the peers' gradients over NVLink
         # (csrc/p2p.cu; 2.37 M vs 2.22 M seq/s with NCCL at 2 GPUs); the flat gradient buffer is then a CUDA-IPC
         # exportable allocation of parallel.PeerGradients.  XB_P2P_ADAM=0, or any rank that cannot map its peers,
@@ -84,8 +85,11 @@ class FusedTrainer:
                 warnings.warn("explainn_b200: peer-memory optimizer step unavailable (%s); using the NCCL all-reduce" % pg.error)
         if self.p2p is not None:
             self.flat_g = self.p2p.flat_grad
+            self.flat_p = self.p2p.flat_param          # peers store their updated slices straight into it
         else:
             self.flat_g = torch.zeros(off, dtype=torch.float32, device=dev)
+            self.flat_p = torch.zeros(off, dtype=torch.float32, device=dev)
+        self.p2p_timeout_s = float(os.environ.get("XB_P2P_TIMEOUT_S", "1800"))
         self.flat_m = torch.zeros(off, dtype=torch.float32, device=dev)
         self.flat_v = torch.zeros(off, dtype=torch.float32, device=dev)
         self.step_t = torch.zeros(1, dtype=torch.float32, device=dev)
@@ -168,8 +172,7 @@ class FusedTrainer:
             return 1.0
         d = _dist()
         if not self.dp_overlap:             # one collective over the whole flat buffer after the backward
-            d.all_reduce(self.flat_g, op=d.ReduceOp.SUM)
-            return 1.0 / self.world
+            return parallel.allreduce_mean_gradients(self.flat_g)
         if self._pending is None:           # defensive: the first half was not started
             self._start_fc_allreduce()
         d.all_reduce(self.flat_g[:self.n_conv], op=d.ReduceOp.SUM)
@@ -210,6 +213,7 @@ class FusedTrainer:
         self._graph = g
         self._graph2 = g2
 
+    @_cabi.on_device_of(1)
     def step(self, x, y):
         """One optimisation step (train.py:59-67).  Returns the loss as a 1-element device tensor."""
         if not self._still_aliased():       # somebody re-assigned a parameter: re-adopt it
@@ -243,9 +247,10 @@ class FusedTrainer:
         b1, b2 = g["betas"]
         if self.p2p is not None:
             import ctypes
-            call("explainn_p2p_adam_step", ptr(self.flat_p), ptr(self.flat_m), ptr(self.flat_v), self.n, ptr(self.step_t),
-                 ctypes.cast(self.p2p.g_array, ctypes.c_void_p), ctypes.cast(self.p2p.f_array, ctypes.c_void_p), self.world,
-                 self.p2p.rank, self.steps_done + 1, float(g["lr"]), float(b1), float(b2), float(g["eps"]), stream())
+            call("explainn_p2p_adam_step", ctypes.cast(self.p2p.p_array, ctypes.c_void_p), ptr(self.flat_m), ptr(self.flat_v),
+                 self.n, ptr(self.step_t), ctypes.cast(self.p2p.g_array, ctypes.c_void_p),
+                 ctypes.cast(self.p2p.f_array, ctypes.c_void_p), self.world, self.p2p.rank, self.steps_done + 1, float(g["lr"]),
+                 float(b1), float(b2), float(g["eps"]), self.p2p_timeout_s, stream())
             self.steps_done += 1
             return loss
         scale = self._finish_allreduce()     # SUM over ranks (NCCL over NVLink); Adam divides by the world size
@@ -254,7 +259,22 @@ class FusedTrainer:
         self.steps_done += 1
         return loss
 
+    def check_health(self):
+        """Raise if the peer-memory optimizer step ever gave up waiting for a rank (one small synchronous read)."""
+        if self.p2p is not None:
+            self.p2p.check()
+
     def sync_optimizer_state(self):
+        if self.p2p is not None:
+            # the Adam moments of a slice live on its owner (csrc/p2p.cu): gather them so that optimizer.state_dict()
+            # is complete on every rank
+            self.check_health()
+            lo, hi = self.p2p.slice_range(self.n)
+            d = _dist()
+            for buf in (self.flat_m, self.flat_v):
+                buf[:lo].zero_()
+                buf[hi:].zero_()
+                d.all_reduce(buf, op=d.ReduceOp.SUM)
         for p in self.params:
             self.optimizer.state[p]["step"] = torch.tensor(float(self.steps_done))
         for p, gview in zip(self.params, self.views_g):
@@ -276,31 +296,36 @@ def train_explainn(train_loader, test_loader, model, device, criterion,
                    optimizer, num_epochs=100, weights_folder="./",
                    name_ind=None, verbose=False, trim_weights=False,
                    checkpoint=1, patience=0):
-    """
-    Function to train the ExplaiNN model (reference: explainn/train/train.py:13-142)
+    """Epoch loop of the reference (explainn/train/train.py:13-142) on the fused kernels; same arguments, files and
+    return value, so callers of the reference need no change.
 
-    :param train_loader: pytorch DataLoader, train data
-    :param test_loader: pytorch DataLoader, validation data
-    :param model: ExplaiNN model
-    :param device: current available device ("cuda:0")
-    :param criterion: objective (loss) function to use (e.g. MSELoss)
-    :param optimizer: pytorch Optimizer (e.g. SGD)
-    :param num_epochs: int, number of epochs to train the model
-    :param weights_folder: string, folder where to save checkpoints
-    :param name_ind: string, suffix name of the checkpoints
-    :param verbose: boolean, if False, does not print the progress
-    :param trim_weights: boolean, if True, makes output layer weights non-negative
-    :param checkpoint: int, how often to save checkpoints (e.g. 1 means that the model will be saved after each epoch;
-                       0 that only the best model will be saved)
-    :param patience: int, number of epochs to wait before stopping training if validation loss does not improve;
-                     if 0, this parameter is ignored
-    :return: tuple: trained ExplaiNN model, list of train losses, list of test losses
-    """
+    train_loader / test_loader yield (sequences (B,4,L) one-hot, labels (B,C)) batches; `criterion` and `optimizer`
+    are the caller's objects.  BCEWithLogitsLoss / MSELoss (mean) with a plain torch.optim.Adam over all model
+    parameters take the flat-buffer fast path (FusedTrainer); anything else runs forward and backward on the same
+    kernels through autograd and steps the caller's optimizer.  Per epoch: mean of the step losses, validation in
+    eval() mode, best-so-far weights by validation loss.  `checkpoint` = k > 0 writes the best-so-far weights as
+    model_epoch_{e}[_{name_ind}].pth every k epochs (and, like the reference, reloads them into the model at that
+    point); `patience` = n > 0 stops n epochs after the best one; `trim_weights` clamps final.weight at zero after
+    every step.  At the end the best weights are loaded, written as model_epoch_best_{e}[_{name_ind}].pth and
+    (model, train losses, validation losses) is returned; the model is left in eval() mode.
+
+    Under an initialised torch.distributed group (one process per GPU, each loader yielding that rank's shard) the
+    gradients are averaged over ranks every step, all ranks start from rank 0's weights, the validation loss is
+    averaged over ranks before the best-epoch / early-stopping decisions (so every rank takes the same ones) and
+    only rank 0 writes files."""
     train_error, test_error = [], []
+    d = _dist()
+    world = d.get_world_size() if d is not None else 1
+    rank = d.get_rank() if d is not None else 0
+    fused = FusedTrainer(model, criterion, optimizer) if FusedTrainer.supports(model, criterion, optimizer) else None
+    if world > 1 and fused is None:
+        import warnings
+        warnings.warn("explainn_b200: criterion / optimizer not recognised by the fused trainer; data-parallel training "
+                      "continues on the autograd path with one gradient all-reduce per parameter per step")
+        parallel.broadcast_model_state(model)
     best_model_wts = copy.deepcopy(model.state_dict())
     best_loss_valid = float('inf')
     best_epoch = 1
-    fused = FusedTrainer(model, criterion, optimizer) if FusedTrainer.supports(model, criterion, optimizer) else None
 
     for epoch in range(1, num_epochs + 1):
         step_losses = []
@@ -315,8 +340,13 @@ def train_explainn(train_loader, test_loader, model, device, criterion,
                 outputs = model(x)
                 loss = criterion(outputs, labels)
                 loss.backward()
+                if world > 1:
+                    for p in model.parameters():
+                        if p.grad is not None:
+                            d.all_reduce(p.grad, op=d.ReduceOp.SUM)
+                            p.grad.div_(world)
                 optimizer.step()
-            if trim_weights:        # constrain the output layer weights to be non-negative (train.py:70-71)
+            if trim_weights:        # non-negative output layer weights (train.py:70-71)
                 model.final.weight.data.clamp_(0)
             step_losses.append(loss)
         epoch_loss = _epoch_mean(step_losses)
@@ -333,13 +363,16 @@ def train_explainn(train_loader, test_loader, model, device, criterion,
         test_error.append(test_loss)
         if hasattr(model, "check_inputs"):
             model.check_inputs()
+        if fused is not None:
+            fused.check_health()
 
         if verbose:
             print('Epoch [{}], Current Train Loss: {:.5f}, Current Val Loss: {:.5f}'
                   .format(epoch, epoch_loss, test_loss))
 
-        if test_loss < best_loss_valid:
-            best_loss_valid = test_loss
+        decide_loss = parallel.allreduce_mean_scalar(test_loss, device) if world > 1 else test_loss
+        if decide_loss < best_loss_valid:
+            best_loss_valid = decide_loss
             best_epoch = epoch
             best_model_wts = copy.deepcopy(model.state_dict())
 
@@ -347,7 +380,8 @@ def train_explainn(train_loader, test_loader, model, device, criterion,
             if epoch % checkpoint == 0:
                 model.load_state_dict(best_model_wts)
                 f = f"model_epoch_{epoch}_{name_ind}.pth" if name_ind else f"model_epoch_{epoch}.pth"
-                torch.save(best_model_wts, os.path.join(weights_folder, f))
+                if rank == 0:
+                    torch.save(best_model_wts, os.path.join(weights_folder, f))
 
         if patience:
             if epoch >= best_epoch + patience:
@@ -360,5 +394,6 @@ def train_explainn(train_loader, test_loader, model, device, criterion,
         fused.sync_optimizer_state()
     model.load_state_dict(best_model_wts)
     f = f"model_epoch_best_{best_epoch}_{name_ind}.pth" if name_ind else f"model_epoch_best_{best_epoch}.pth"
-    torch.save(best_model_wts, os.path.join(weights_folder, f))
+    if rank == 0:
+        torch.save(best_model_wts, os.path.join(weights_folder, f))
     return model, train_error, test_error

@@ -9,6 +9,9 @@
  *   - All pointers are DEVICE pointers unless stated otherwise; the caller owns every buffer.  No entry
  *     point allocates or frees device memory or keeps a pointer after it returns.
  *   - Every call is asynchronous on `stream` and re-entrant (no global mutable state).
+ *   - Exceptions to the two rules above, each documented at its declaration: explainn_p2p_alloc / _free / _open /
+ *     _close (CUDA-IPC peer buffers are allocated and mapped here), explainn_p2p_error (synchronous 4-byte read) and
+ *     explainn_interp_unit_max_noalloc (scratch in a library-owned static device array shared by all calls on a GPU).
  *   - Return value 0 = success; otherwise an EXPLAINN_ERR_* code and explainn_last_error() (thread-local)
  *     describes the failure.  No C++ exception crosses this boundary.
  *   - Tensors are dense row-major with the shapes given, fp32 unless stated otherwise.
@@ -291,14 +294,17 @@ int explainn_adam_step(float *param, const float *grad, float *exp_avg, float *e
                        float lr, float beta1, float beta2, float eps, float grad_scale, cudaStream_t stream);
 
 /* Data-parallel optimizer step as ONE kernel over NVLink peer memory (no counterpart in the reference, which is
- * single-device; it replaces "NCCL all-reduce of the gradients + Adam", the DDP form of train.py:65-67).
- * grads[q] / flags[q], q < world: device pointers to rank q's flat gradient buffer and flag buffer
- * (explainn_p2p_flag_bytes() bytes, zero-initialised once), valid in THIS process (the caller opens the peers' buffers
- * through CUDA IPC and enables peer access); grads[rank] / flags[rank] are the local ones.  The arrays grads / flags
- * themselves are host arrays.  Every rank sums the gradients in rank order, scales by 1/world and applies Adam to its
- * own param / exp_avg / exp_avg_sq (n floats, 16-byte aligned, n % 4 == 0); *step (device) is incremented first.
- * seq: the same strictly increasing positive number on every rank for every step.  All ranks must call it once per
- * step; a peer that does not show up within ~2 s makes the kernel trap (the call never hangs the GPU). */
+ * single-device; it replaces "NCCL all-reduce of the gradients + Adam", the DDP form of train.py:65-67), in
+ * reduce-scatter / all-gather form: rank r sums slice r of all ranks' gradients (rank order), scales by 1/world,
+ * applies Adam to slice r of its own exp_avg / exp_avg_sq and stores the updated parameter slice into EVERY rank's
+ * parameter buffer.  params[q] / grads[q] / flags[q], q < world: device pointers to rank q's flat parameter buffer,
+ * flat gradient buffer and flag buffer (explainn_p2p_flag_bytes() bytes, zero-initialised once), valid in THIS process
+ * (the caller opens the peers' buffers through CUDA IPC); index `rank` holds the local ones.  The three arrays
+ * themselves are host arrays.  n floats per buffer, 16-byte aligned, n % 4 == 0; *step (device) is incremented first.
+ * The moments of slices other than `rank` are not touched.  seq: the same strictly increasing positive number on every
+ * rank for every step.  All ranks must call it once per step.  A late peer is waited for (never a trap); after
+ * timeout_s seconds (0 = wait for ever) the kernel gives up, sets the error word that explainn_p2p_error reads
+ * (0 = healthy, 1 + q = gave up waiting for rank q) and finishes with undefined parameters. */
 /* Peer buffers: plain cudaMalloc allocations (zero-filled) that CUDA IPC can export -- the only memory this library
  * allocates; export writes a 64-byte handle, open maps a peer's allocation for the current device. */
 int explainn_p2p_alloc(long long bytes, void **out);
@@ -307,9 +313,11 @@ int explainn_p2p_export(const void *p, unsigned char *handle);
 int explainn_p2p_open(const unsigned char *handle, void **out);
 int explainn_p2p_close(void *p);
 long long explainn_p2p_flag_bytes(void);
-int explainn_p2p_adam_step(float *param, float *exp_avg, float *exp_avg_sq, long long n, float *step,
+int explainn_p2p_error(const unsigned long long *flags, int *out);
+int explainn_p2p_adam_step(float *const *params, float *exp_avg, float *exp_avg_sq, long long n, float *step,
                            const float *const *grads, unsigned long long *const *flags, int world, int rank,
-                           unsigned long long seq, float lr, float beta1, float beta2, float eps, cudaStream_t stream);
+                           unsigned long long seq, float lr, float beta1, float beta2, float eps, double timeout_s,
+                           cudaStream_t stream);
 
 /* out[i] = sum_{c<k} partials[c*n + i] */
 int explainn_reduce_partials(float *out, const float *partials, long long n, int k, cudaStream_t stream);

@@ -1,7 +1,7 @@
 """Full-size parity against the ORACLE at the BASELINE.json shapes the CPU can still finish in seconds:
 configs[4] (num_cnns=500, L=1000, 100 outputs) eval forward on 2,048 sequences against the fp32 CPU port, and
 configs[3] (interpretation sweep, num_cnns=300, L=251) PWM counts on 16,384 sequences against the canonical C
-restatement -- bit for bit, in the sparse regime of default-initialised weights and in a dense-hit regime."""
+restatement -- bit for bit, in a dense-hit regime (default-initialised weights) and in a sparse one."""
 import numpy as np
 import pytest
 import torch

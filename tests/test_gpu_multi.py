@@ -101,3 +101,29 @@ def test_two_gpu_step_allreduce(tmp_path, mode, overlap):
     assert int(same) == 1, "ranks diverged"
     assert float(err) < 1e-4, (same, err, split)                    # same kernels on both paths; only summation order differs
     assert int(split) == (1 if mode == "graph" and overlap == "1" else 0)
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_model_on_non_current_device():
+    """A model on cuda:1 while cuda:0 is the current device: launches, streams and per-device caches follow the data."""
+    import numpy as np
+    from explainn_b200 import interpretation, networks
+    from util import onehot_from_codes, random_codes
+    torch.cuda.set_device(0)
+    torch.manual_seed(0)
+    m = networks.ExplaiNN(40, 120, 5, 19)
+    x = torch.from_numpy(onehot_from_codes(random_codes(64, 120, 3, n_frac=0.01)))
+    m0 = m.to("cuda:0").eval()
+    with torch.no_grad():
+        ref = m0(x.to("cuda:0")).cpu()
+        pwm0 = interpretation.get_pwms_explainn_fused(x, m0, "cuda:0")
+    m1 = m0.to("cuda:1")
+    with torch.no_grad():
+        out = m1(x.to("cuda:1")).cpu()
+        pwm1 = interpretation.get_pwms_explainn_fused(x, m1, "cuda:1")
+    assert torch.equal(out, ref) and np.array_equal(pwm0, pwm1)
+    m1.train()
+    y = torch.rand(64, 5, device="cuda:1")
+    torch.nn.functional.mse_loss(m1(x.to("cuda:1")), y).backward()
+    assert all(torch.isfinite(p.grad).all() for p in m1.parameters())
+    assert torch.cuda.current_device() == 0

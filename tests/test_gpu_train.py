@@ -142,11 +142,16 @@ def _close_per_unit(got, ref, rtol, name, max_outlier_frac=0.02, outlier_rtol=0.
     differ the same way).  So: every unit within `outlier_rtol`, and all but a few within `rtol`."""
     got = np.asarray(got, np.float64).reshape(got.shape[0], -1)
     ref = np.asarray(ref, np.float64).reshape(ref.shape[0], -1)
-    scale = np.maximum(np.abs(ref).max(axis=1), 1e-3 * np.abs(ref).max())
+    # a one-element row (BatchNorm-1 gamma: one number per unit) is a sum of B*P signed terms that cancel to ~1 % of
+    # their magnitude, so an element near a zero crossing carries the fp32 accumulation noise of the whole sum on BOTH
+    # sides; the floor below which an element is compared absolutely is 1 % of the tensor scale there, 0.1 % otherwise
+    floor = 1e-2 if got.shape[1] == 1 else 1e-3
+    scale = np.maximum(np.abs(ref).max(axis=1), floor * np.abs(ref).max())
     err = np.abs(got - ref).max(axis=1) / scale
     assert err.max() <= outlier_rtol, "%s: worst unit err %.3e" % (name, err.max())
     allowed = max(1, int(max_outlier_frac * err.size))
-    assert (err > rtol).sum() <= allowed, "%s: %d of %d units above %.1e" % (name, (err > rtol).sum(), err.size, rtol)
+    assert (err > rtol).sum() <= allowed, "%s: %d of %d units above %.1e (worst %.2e, tensor-scale err %.2e)" % (
+        name, (err > rtol).sum(), err.size, rtol, err.max(), np.abs(got - ref).max() / np.abs(ref).max())
 
 
 @pytest.mark.parametrize("backend", ["tc", "lut"])
