@@ -170,8 +170,15 @@ class ExplaiNN(nn.Module):
         return Fn.pooled_len(o["input_length"], o["filter_size"], o["pool_size"], o["pool_stride"])
 
     def _pack(self, x):
+        if isinstance(x, Fn.Packed):
+            return x
         _require_cuda(x)
         o = self._options
+        if x.dim() == 2 and x.dtype == torch.uint8:
+            # (B, L) ASCII bases ("ACGT", anything else = N): encoded on the device, 16x fewer bytes than fp32 one-hot
+            if x.shape[1] != o["input_length"]:
+                raise ValueError("expected text input of shape (B, %d), got %s" % (o["input_length"], tuple(x.shape)))
+            return Fn.encode_dna_array(x, o["input_length"], x.device)
         if x.dim() != 3 or x.shape[2] != o["input_length"]:
             raise ValueError("expected input of shape (B, 4, %d), got %s" % (o["input_length"], tuple(x.shape)))
         if self._invalid is None or self._invalid.device != x.device:

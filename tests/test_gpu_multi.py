@@ -12,7 +12,11 @@ pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 WORKER = r'''
-import os, sys
+import os, sys, traceback
+def _hook(t, v, tb):
+    open(sys.argv[2] + ".err%s" % os.environ.get("RANK", "0"), "w").write("".join(traceback.format_exception(t, v, tb)))
+    sys.__excepthook__(t, v, tb)
+sys.excepthook = _hook
 import torch, torch.distributed as dist
 sys.path.insert(0, sys.argv[1]); sys.path.insert(0, os.path.join(sys.argv[1], "tests"))
 from util import onehot_from_codes, random_codes
@@ -45,6 +49,8 @@ for r in range(world):
     mean_g = g if mean_g is None else [a + b for a, b in zip(mean_g, g)]
 mean_g = [g / world for g in mean_g]
 p2p = os.environ.get("XB_P2P_ADAM", "1") != "0"
+if p2p:
+    tr.sync_optimizer_state()                        # the moments of a slice live on its owner: gather them for the check
 p0, m0, v0 = tr.flat_p.clone(), tr.flat_m.clone(), tr.flat_v.clone()
 tr.step(xs[rank], ys[rank])
 torch.cuda.synchronize()
@@ -64,6 +70,9 @@ if p2p:
     v1 = v0 * 0.999 + flat * flat * 0.001
     p1 = p0 - (1e-2 / (1 - 0.9 ** t)) * (m1 / (v1.sqrt() / (1 - 0.999 ** t) ** 0.5 + 1e-8))
     assert float((tr.flat_p - p1).abs().max()) <= 1e-6 * max(float(p1.abs().max()), 1.0), "fused Adam update"
+    lo, hi = tr.p2p.slice_range(tr.n)                # ... and this rank's slice of the moments
+    assert float((tr.flat_m[lo:hi] - m1[lo:hi]).abs().max()) <= 1e-6 * max(float(m1.abs().max()), 1e-30), "exp_avg slice"
+    tr.check_health()
 else:
     got = [v / world for v in tr.views_g]            # the flat buffer holds the SUM over ranks; Adam applies 1/world
 err = 0.0
@@ -96,7 +105,8 @@ def test_two_gpu_step_allreduce(tmp_path, mode, overlap):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
            "--master-port", "29533", str(script), ROOT, str(out), mode]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=300, env=dict(os.environ, XB_DP_OVERLAP="1" if overlap == "1" else "0", XB_P2P_ADAM="1" if overlap == "p2p" else "0"))      # "0" / "1": NCCL all-reduce (plain / overlapped)
-    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    errs = "".join(p.read_text() for p in sorted(tmp_path.glob("out.txt.err*")))
+    assert r.returncode == 0, errs + r.stdout[-1000:] + r.stderr[-1000:]
     same, err, split = out.read_text().split()
     assert int(same) == 1, "ranks diverged"
     assert float(err) < 1e-4, (same, err, split)                    # same kernels on both paths; only summation order differs
