@@ -305,6 +305,7 @@ def dp_check(torch, dist, dev, trainer, model, rank, world):
     from explainn_b200 import interpretation, parallel
     out = {}
     trainer.check_health()
+    trainer.sync_buffers()                                           # every rank evaluates the same model below
     flat = trainer.flat_p.clone()
     ref = flat.clone()
     dist.broadcast(ref, src=0)
@@ -386,7 +387,7 @@ def leg_conv_roofline(torch, dev, model, batch, hbm_peak, peak_src, peaks):
     rm, rv, nbt = bn1.running_mean.clone(), bn1.running_var.clone(), bn1.num_batches_tracked.clone()
     mean1, var1, _ = Fn.bn1_batch_stats(M, cw, cb, B * S, bn1.momentum, rm, rv, nbt)
     ones, zeros = torch.ones(U, device=dev), torch.zeros(U, device=dev)
-    tcp = Fn.conv_tc_prepare(cw, cb, ones, zeros, mean1, var1, bn1.eps)
+    tcp = Fn.conv_tc_prepare(cw, cb, ones, zeros, mean1, var1, bn1.eps, sign_of=g1)
     for _ in range(5):
         Fn.conv_pool_fwd_train_tc(pk, tcp, g1, b1n)
     torch.cuda.synchronize()

@@ -35,8 +35,9 @@ SIGNATURES = {
     "explainn_conv_pool_fwd": [_P, _P, _LL, _I, _I, _I, _P, _P, _P, _P, _P],
     "explainn_conv_pool_fwd_train": [_P, _P, _LL, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P],
     "explainn_conv_tc_image_halfs": [_I, _I],
-    "explainn_conv_tc_prepare": [_P, _P, _P, _P, _P, _P, _F, _I, _I, _P, _P, _P],
+    "explainn_conv_tc_prepare": [_P, _P, _P, _P, _P, _P, _F, _P, _I, _I, _P, _P, _P],
     "explainn_conv_pool_fwd_tc": [_P, _P, _LL, _I, _I, _I, _P, _P, _P, _P],
+    "explainn_conv_pool_fwd_tc_fp16": [_P, _P, _LL, _I, _I, _I, _P, _P, _P, _P],
     "explainn_conv_pool_fwd_train_tc": [_P, _P, _LL, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P],
     "explainn_unit_activations": [_P, _P, _LL, _I, _I, _I, _P, _P, _P, _P, _I, _P],
     "explainn_interp_unit_max_scratch_floats": [_I],

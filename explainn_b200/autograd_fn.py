@@ -88,8 +88,8 @@ def train_forward(model, x, params=None, seed=None, seed_dev=None):
                                                   bn1.num_batches_tracked)
     ones, zeros = _const(dev, U)
     # the conv is prepared with gamma=1, beta=0 and the batch statistics, so the scan yields x_hat = (y - mu) / sigma
-    if getattr(model, "conv_backend", "tc") == "tc":
-        tcp = Fn.conv_tc_prepare(cw, cb, ones, zeros, ws.mean1, ws.var1, bn1.eps)
+    if getattr(model, "conv_backend", "tc") != "lut":      # training always uses the two-piece (fp32-accurate) weights
+        tcp = Fn.conv_tc_prepare(cw, cb, ones, zeros, ws.mean1, ws.var1, bn1.eps, sign_of=g1)
         ws.pooled, ws.xhat, ws.idx = Fn.conv_pool_fwd_train_tc(pk, tcp, g1, b1n)
     else:
         prep = Fn.conv_prepare(cw, cb, ones, zeros, ws.mean1, ws.var1, bn1.eps)
@@ -138,8 +138,8 @@ def _train_forward_conv(model, x, cw, cb, g1, b1n):
     ws.mean1, ws.var1, ws.Mw = Fn.bn1_batch_stats(ws.M, cw, cb, B * S, bn1.momentum, bn1.running_mean, bn1.running_var,
                                                   bn1.num_batches_tracked)
     ones, zeros = _const(dev, U)
-    if getattr(model, "conv_backend", "tc") == "tc":
-        tcp = Fn.conv_tc_prepare(cw, cb, ones, zeros, ws.mean1, ws.var1, bn1.eps)
+    if getattr(model, "conv_backend", "tc") != "lut":      # training always uses the two-piece (fp32-accurate) weights
+        tcp = Fn.conv_tc_prepare(cw, cb, ones, zeros, ws.mean1, ws.var1, bn1.eps, sign_of=g1)
         ws.pooled, ws.xhat, ws.idx = Fn.conv_pool_fwd_train_tc(pk, tcp, g1, b1n)
     else:
         prep = Fn.conv_prepare(cw, cb, ones, zeros, ws.mean1, ws.var1, bn1.eps)

@@ -44,34 +44,81 @@ __device__ long long g_conv_clk[16];
 // ------------------------------------------------------------------------------------------------
 // A-operand images: per 128-unit tile, [hi | lo] x canonical K-major layout
 //   byte offset of element (row r, k) inside one image = (r/8)*KC*128 + (k/8)*128 + (r%8)*16 + (k%8)*2
-// shift[u] (fp32) is added in the epilogue.
+// Row u holds  sgn_u * 2^e_u * w'[u][:]  with w' the BatchNorm-folded filter:
+//   2^e_u  brings the row's largest tap into [128, 256), so that neither piece of the fp16 split can overflow
+//          (|w'| > 65504) or lose its low piece to the fp16 subnormal range (|w'| < 2^-3 * row maximum at worst:
+//          absolute error 2^-25 against a row maximum of 2^7);
+//   sgn_u  = sign of the training-mode BatchNorm gain (sign_of == NULL: +1): max-pooling z = gamma * x_hat + beta is
+//          then a plain maximum of the accumulators for either sign of gamma.
+// shift_rs[u] = shift (fp32), shift_rs[U + u] = sgn_u * 2^-e_u: the epilogue evaluates fma(acc, rs, shift), which is
+// exact in the scale (a power of two) and so equal to the unscaled sum.
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) tc_prepare_kernel(const float *__restrict__ w, const float *__restrict__ bias,
                                                          const float *__restrict__ gamma, const float *__restrict__ beta,
                                                          const float *__restrict__ mean, const float *__restrict__ var, float eps,
-                                                         int U, int F, int K, __half *__restrict__ images, float *__restrict__ shift)
+                                                         const float *__restrict__ sign_of, int U, int F, int K,
+                                                         __half *__restrict__ images, float *__restrict__ shift_rs)
 {
     const int mt = blockIdx.x, KC = K / 8;
     __half *hi = images + (size_t)mt * 2 * TC_M * K, *lo = hi + (size_t)TC_M * K;
-    // grid (n_mt, 8): block y handles 16 rows of the tile
-    for (int i = blockIdx.y * 16 * K + threadIdx.x; i < (blockIdx.y + 1) * 16 * K; i += blockDim.x) {
-        const int r = i / K, k = i - r * K;
-        const int u = mt * TC_M + r;
-        float v = 0.0f;
-        if (u < U) {
-            const float sc = __fdiv_rn(gamma[u], __fsqrt_rn(__fadd_rn(var[u], eps)));
-            if (k < 4 * F) {
-                const int tap = k >> 2, c = k & 3;
-                v = __fmul_rn(w[((size_t)u * 4 + c) * F + tap], sc);
-            }
-            if (k == 0) shift[u] = __fadd_rn(__fmul_rn(__fsub_rn(bias[u], mean[u]), sc), beta[u]);
-        }
+    // grid (n_mt, 8): block y handles 16 rows of the tile, 16 threads per row
+    const int r = blockIdx.y * 16 + (threadIdx.x >> 4), l16 = threadIdx.x & 15;
+    const int u = mt * TC_M + r;
+    float sc = 0.f;
+    if (u < U) sc = __fdiv_rn(gamma[u], __fsqrt_rn(__fadd_rn(var[u], eps)));
+    auto tap = [&](int k) -> float {
+        if (u >= U || k >= 4 * F) return 0.0f;
+        return __fmul_rn(w[((size_t)u * 4 + (k & 3)) * F + (k >> 2)], sc);
+    };
+    float mx = 0.f;
+    for (int k = l16; k < K; k += 16) mx = fmaxf(mx, fabsf(tap(k)));
+#pragma unroll
+    for (int o = 8; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    int e = 0;
+    if (mx > 0.f && mx < INFINITY) {
+        e = 7 - ilogbf(mx);
+        e = max(-100, min(100, e));
+    }
+    const float sg = (sign_of && u < U && sign_of[u] < 0.f) ? -1.0f : 1.0f;
+    const float up = ldexpf(sg, e);
+    for (int k = l16; k < K; k += 16) {
+        const float v = __fmul_rn(tap(k), up);                      // exact: power of two
         const __half h = __float2half_rn(v);
         const __half l = __float2half_rn(v - __half2float(h));
         const size_t off = (size_t)(r >> 3) * KC * 64 + (size_t)(k >> 3) * 64 + (r & 7) * 8 + (k & 7);
         hi[off] = h;
         lo[off] = l;
     }
+    if (l16 == 0 && u < U) {
+        shift_rs[u] = __fadd_rn(__fmul_rn(__fsub_rn(bias[u], mean[u]), sc), beta[u]);
+        shift_rs[U + u] = ldexpf(sg, -e);
+    }
+}
+
+// 3-input maximum (one FMNMX3 instead of two FMNMX)
+__device__ __forceinline__ float fmax3(float a, float b, float c)
+{
+    float d;
+    asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+    return d;
+}
+
+// exp(z) to ~2 ulp in 10 instructions: z * log2(e) is split into an integer n (magic-number rounding) and a fraction
+// f = z*log2e - n evaluated with a two-term log2(e) (error ~3e-8 absolute), 2^f comes from MUFU.EX2 (2^-22 relative),
+// 2^n is added into the exponent field.  (__expf multiplies first and loses |z| * 2^-24 relative; the 25-instruction
+// det_expf of the table kernel exists for bit-equality with the CPU oracle, which this kernel does not claim.)
+__device__ __forceinline__ float tc_expf(float z)
+{
+    const float tm = __fmaf_rn(z, 1.44269502f, 12582912.0f);
+    const float n = __fsub_rn(tm, 12582912.0f);
+    float f = __fmaf_rn(z, 1.44269502f, -n);
+    f = __fmaf_rn(z, 1.92596303e-8f, f);
+    float p;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(p) : "f"(f));
+    float r = __int_as_float(__float_as_int(p) + (int)((unsigned)__float_as_int(tm) << 23));
+    r = z < -87.0f ? 0.0f : r;
+    r = z > 88.7228394f ? __int_as_float(0x7f800000) : r;
+    return z != z ? z : r;
 }
 
 struct TcArgs {
@@ -79,12 +126,13 @@ struct TcArgs {
     long long B;
     int L, F, U, K, P, wc, wm;
     const __half *images;
-    const float *shift;     // (U)
+    const float *shift;     // (2U): shift, then the signed power-of-two row scale (see tc_prepare_kernel)
     float *pooled;          // (B,U,P)
     float *xhat;            // train only
     unsigned char *idx;     // train only
     const float *gamma, *beta;
     int gsz;                // unit tiles (of 128) whose weights stay resident in shared memory together
+    int single;             // 1: only the high fp16 piece of the weights is multiplied (stated-tolerance mode)
 #ifdef XB_EXPERIMENT
     int dbg;                // XB_TC_DBG bitmask (experiment build only): 1 no stores, 2 no V build, 4 no drain, 8 no MMA
 #endif
@@ -99,77 +147,69 @@ constexpr int TC_VROWS = TC_N + 64;     // dinucleotide entries per tile: positi
 constexpr int TC_VBUFS = 4;             // V tiles in flight: tile n may be built while the MMAs of n-1, n-2 run
 
 // Epilogue of one accumulator for the columns [C0, C1) (whole pool windows), one unit per thread.
-// TMEM reads are the scarce resource of this kernel (~64 B/clk/SM), so only the 16-column pieces that
-// intersect the range are loaded, all of them are issued before a single wait, and warps whose lane
-// quarter holds no valid unit skip the drain altogether (caller).
+// The accumulators are  sgn * 2^e * (z - shift)  (tc_prepare_kernel), so the window maximum is taken on the RAW values
+// (three 3-input maxima per window), and the affine map and the exponential run once per window, not per position.
+// Training also needs the first position of the maximum (MaxPool1d backward routing): found by comparing the seven
+// values with the maximum afterwards.  Tie rule: first maximum of the normalised conv output x_hat (times sign(gamma));
+// gamma == 0 makes z constant, where the first position wins as in the reference.
+// Tensor-memory loads are double-buffered in batches of 32 columns (the loads of batch k+1 are in flight while batch k
+// is pooled); warps whose lane quarter holds no valid unit skip the drain altogether (caller).
 template <bool TRAIN, int C0, int C1>
 __device__ __forceinline__ void tc_drain(uint32_t taddr, int row, int nwin, int sst, float *stage, unsigned char *stage_i, float shift,
-                                         float gam, float bet)
+                                         float rs, float gam, float bet)
 {
     constexpr int plane = TC_M * (TC_WIN + 1);
     constexpr int P0 = C0 / 16, P1 = (C1 + 15) / 16;
-    float m = 0.f, xb = 0.f;
+    const bool gzero = TRAIN && gam == 0.0f;
+    float m = 0.f, pa = 0.f, pb_ = 0.f, w0 = 0.f;      // running maximum, the one or two values waiting for their partner
     int ib = 0;
-    // one pooled column: running max of the window, emit at its last position
     auto column = [&](int col, uint32_t bits) {
-        const float v = __uint_as_float(bits);
+        static_assert(XB_POOL == 7, "window maximum written for 7 positions: (0,1,2) (3,4) (5,6)");
         const int ph = col % XB_POOL, win = col / XB_POOL;
-        if (TRAIN) {
-            const float x = v + shift;
-            const float z = fmaf(gam, x, bet);
-            if (ph == 0 || z > m) { m = z; xb = x; ib = ph; }
-        } else {
-            m = ph == 0 ? v : fmaxf(m, v);
+        const float v = __uint_as_float(bits);
+        if (ph == 0) { pa = v; if (TRAIN) w0 = v; }
+        else if (ph == 1) pb_ = v;
+        else if (ph == 2) {
+            m = fmax3(pa, pb_, v);
+            if (TRAIN) ib = pa == m ? 0 : (pb_ == m ? 1 : 2);
+        } else if (ph == 3 || ph == 5) pa = v;
+        else {                                          // ph == 4 or 6: fold the pair (ph-1, ph) into the maximum
+            const float m2 = fmax3(m, pa, v);
+            if (TRAIN) ib = m2 == m ? ib : (pa == m2 ? ph - 1 : ph);       // an earlier maximum keeps its position
+            m = m2;
         }
         if (ph == XB_POOL - 1 && win < nwin) {
-            // training keeps the 1-ulp deterministic exp of the table kernel: ReLU / max-pool kinks downstream turn
-            // a 1e-6 relative error into visibly different gradients; inference uses the 2-instruction MUFU exp
-            stage[row * sst + win] = TRAIN ? det_expf(m) : __expf(m + shift);
             if (TRAIN) {
-                stage[plane + row * sst + win] = xb;
+                if (gzero) { ib = 0; m = w0; }
+                const float xh = __fmaf_rn(m, rs, shift);
+                stage[row * sst + win] = tc_expf(__fmaf_rn(gam, xh, bet));
+                stage[plane + row * sst + win] = xh;
                 stage_i[row * sst + win] = (unsigned char)ib;
+            } else {
+                stage[row * sst + win] = tc_expf(__fmaf_rn(m, rs, shift));
             }
         }
     };
-    if constexpr (TRAIN) {
-        // 64 columns in registers at a time (the training epilogue needs its registers for the three outputs)
-        constexpr int BATCH = 4;
+    constexpr int BATCH = TRAIN ? 1 : 2;        // the training epilogue keeps three outputs per window: fewer columns in flight
+    constexpr int NB = (P1 - P0 + BATCH - 1) / BATCH;
+    uint32_t rr[2][BATCH * 16] = {};
 #pragma unroll
-        for (int pb = P0; pb < P1; pb += BATCH) {
-            uint32_t r[BATCH * 16];
+    for (int p = 0; p < BATCH; ++p)
+        if (P0 + p < P1) tc_ld16_nowait(taddr + (P0 + p) * 16, rr[0] + p * 16);
+#pragma unroll
+    for (int bi = 0; bi < NB; ++bi) {
+        const int pb = P0 + bi * BATCH;
+        uint32_t *r = rr[bi & 1];
+        if constexpr (BATCH == 2) tc_wait_ld32(r); else tc_wait_ld16(r);
+        if (bi + 1 < NB) {
 #pragma unroll
             for (int p = 0; p < BATCH; ++p)
-                if (pb + p < P1) tc_ld16_nowait(taddr + (pb + p) * 16, r + p * 16);
-            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-#pragma unroll
-            for (int i = 0; i < BATCH * 16; ++i) {
-                const int col = pb * 16 + i;
-                if (col >= C0 && col < C1) column(col, r[i]);
-            }
+                if (pb + BATCH + p < P1) tc_ld16_nowait(taddr + (pb + BATCH + p) * 16, rr[(bi + 1) & 1] + p * 16);
         }
-    } else {
-        // double-buffered batches of 32 columns: the TMEM loads of batch k+1 are in flight while batch k is pooled
-        constexpr int BATCH = 2;
-        constexpr int NB = (P1 - P0 + BATCH - 1) / BATCH;
-        uint32_t rr[2][BATCH * 16] = {};
 #pragma unroll
-        for (int p = 0; p < BATCH; ++p)
-            if (P0 + p < P1) tc_ld16_nowait(taddr + (P0 + p) * 16, rr[0] + p * 16);
-#pragma unroll
-        for (int bi = 0; bi < NB; ++bi) {
-            const int pb = P0 + bi * BATCH;
-            uint32_t *r = rr[bi & 1];
-            tc_wait_ld32(r);
-            if (bi + 1 < NB) {
-#pragma unroll
-                for (int p = 0; p < BATCH; ++p)
-                    if (pb + BATCH + p < P1) tc_ld16_nowait(taddr + (pb + BATCH + p) * 16, rr[(bi + 1) & 1] + p * 16);
-            }
-#pragma unroll
-            for (int i = 0; i < BATCH * 16; ++i) {
-                const int col = pb * 16 + i;
-                if (col >= C0 && col < C1) column(col, r[i]);
-            }
+        for (int i = 0; i < BATCH * 16; ++i) {
+            const int col = pb * 16 + i;
+            if (col >= C0 && col < C1) column(col, r[i]);
         }
     }
 }
@@ -259,7 +299,6 @@ __global__ void __launch_bounds__(TC_THREADS + 64, 1) conv_tc_kernel(const TcArg
         // =========================== issue warp ===========================
         // waits for an operand buffer (built by the builder warp) and a free accumulator, issues the MMAs of every
         // resident unit tile and commits; the last commit of an item also hands its operand buffer back
-        const uint32_t idesc = (1u << 4) | ((uint32_t)(TC_N >> 3) << 17) | ((uint32_t)(TC_M >> 4) << 24);   // f16xf16->f32, M128 N240
         uint32_t a_parity = 0;
         int cur_grp = -1;
         long long n = 0;                                   // tiles issued by this CTA
@@ -283,6 +322,10 @@ __global__ void __launch_bounds__(TC_THREADS + 64, 1) conv_tc_kernel(const TcArg
             }
             const int slot = (int)(vi & (TC_VBUFS - 1));
             const uint4 *V = sV + slot * TC_VROWS;
+            // f16 x f16 -> f32, M = 128, N = the columns this chunk's pool windows need (multiple of 16, at most 240):
+            // a short last chunk (P = 140: 4 windows) or a short sequence (P = 32) does not pay for 240 columns
+            const int ncol = (min(TC_WIN, a.P - t.chunk * TC_WIN) * XB_POOL + 15) & ~15;
+            const uint32_t idesc = (1u << 4) | ((uint32_t)(ncol >> 3) << 17) | ((uint32_t)(TC_M >> 4) << 24);
             mbar_wait(&v_full[slot], (uint32_t)((vi / TC_VBUFS) & 1));
             XB_CLK(1);                                     // wait for the operand buffer
             for (int m = 0; m < mtn; ++m, ++n) {
@@ -299,7 +342,7 @@ __global__ void __launch_bounds__(TC_THREADS + 64, 1) conv_tc_kernel(const TcArg
                     tc_fence_after();
                     for (int ks = 0; ks < (XB_DBG(a, 8) ? 0 : KS); ++ks) {
                         tc_mma_f16(d, dA_hi + ks * 16, dV + ks * 4, idesc, ks > 0 ? 1u : 0u);
-                        tc_mma_f16(d, dA_lo + ks * 16, dV + ks * 4, idesc, 1u);
+                        if (!a.single) tc_mma_f16(d, dA_lo + ks * 16, dV + ks * 4, idesc, 1u);
                     }
                     tc_commit(&tmem_full[buf]);
                     if (m == mtn - 1) tc_commit(&v_empty[slot]);     // all MMAs reading this operand buffer have retired
@@ -389,6 +432,7 @@ __global__ void __launch_bounds__(TC_THREADS + 64, 1) conv_tc_kernel(const TcArg
                 const int u0 = (mt0 + m) * TC_M;
                 const int u = u0 + row;
                 const float shift = u < a.U ? __ldg(a.shift + u) : 0.f;
+                const float rs = u < a.U ? __ldg(a.shift + a.U + u) : 1.f;
                 float gam = 1.f, bet = 0.f;
                 if (TRAIN && u < a.U) { gam = __ldg(a.gamma + u); bet = __ldg(a.beta + u); }
                 XB_CLK(0);                                 // loop overhead, coefficient loads
@@ -402,8 +446,8 @@ __global__ void __launch_bounds__(TC_THREADS + 64, 1) conv_tc_kernel(const TcArg
                 tc_fence_after();
                 XB_CLK(3);                                 // wait for the accumulator
                 if (u0 + 32 * (warp & 3) < a.U && !XB_DBG(a, 4)) {   // lane quarters without a valid unit are not read at all
-                    if (((warp >> 2) & 1) == 0) tc_drain<TRAIN, 0, SPLIT>(taddr, row, nwin, sst, stage, stage_i, shift, gam, bet);
-                    else tc_drain<TRAIN, SPLIT, TC_WIN * XB_POOL>(taddr, row, nwin, sst, stage, stage_i, shift, gam, bet);
+                    if (((warp >> 2) & 1) == 0) tc_drain<TRAIN, 0, SPLIT>(taddr, row, nwin, sst, stage, stage_i, shift, rs, gam, bet);
+                    else tc_drain<TRAIN, SPLIT, TC_WIN * XB_POOL>(taddr, row, nwin, sst, stage, stage_i, shift, rs, gam, bet);
                 }
                 // accumulator free again for the producer
                 tc_fence_before();
@@ -485,8 +529,8 @@ extern "C" long long explainn_conv_tc_image_halfs(int U, int F)
 }
 
 extern "C" int explainn_conv_tc_prepare(const float *w, const float *bias, const float *gamma, const float *beta,
-                                        const float *mean, const float *var, float eps, int U, int F, void *images,
-                                        float *shift, cudaStream_t stream)
+                                        const float *mean, const float *var, float eps, const float *sign_of, int U, int F,
+                                        void *images, float *shift, cudaStream_t stream)
 {
     XB_REQUIRE(w && bias && gamma && beta && mean && var && images && shift && U >= 1 && F >= 1, "conv_tc_prepare: bad argument");
     if (F > 4 * XB_MAX_G) {
@@ -494,11 +538,11 @@ extern "C" int explainn_conv_tc_prepare(const float *w, const float *bias, const
         return XB_ERR_UNSUPPORTED;
     }
     const int n_mt = (U + TC_M - 1) / TC_M;
-    tc_prepare_kernel<<<dim3(n_mt, 8), 256, 0, stream>>>(w, bias, gamma, beta, mean, var, eps, U, F, tc_K(F), (__half *)images, shift);
+    tc_prepare_kernel<<<dim3(n_mt, 8), 256, 0, stream>>>(w, bias, gamma, beta, mean, var, eps, sign_of, U, F, tc_K(F), (__half *)images, shift);
     return xb_check_launch("conv_tc_prepare");
 }
 
-static int launch_tc(bool train, const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F, const void *images,
+static int launch_tc(bool train, bool single, const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F, const void *images,
                      const float *shift, const float *gamma, const float *beta, float *pooled, float *xhat, unsigned char *idx,
                      cudaStream_t stream)
 {
@@ -515,6 +559,7 @@ static int launch_tc(bool train, const uint32_t *codes, const uint32_t *nmask, l
 #ifdef XB_EXPERIMENT
     { const char *e = getenv("XB_TC_DBG"); a.dbg = e ? atoi(e) : 0; }
 #endif
+    a.single = single ? 1 : 0;
     a.images = (const __half *)images; a.shift = shift; a.pooled = pooled; a.xhat = xhat; a.idx = idx; a.gamma = gamma; a.beta = beta;
     const int n_mt = (U + TC_M - 1) / TC_M, nchunk = (a.P + TC_WIN - 1) / TC_WIN;
     const size_t tile_bytes = (size_t)2 * TC_M * a.K * 2;
@@ -548,7 +593,13 @@ static int launch_tc(bool train, const uint32_t *codes, const uint32_t *nmask, l
 extern "C" int explainn_conv_pool_fwd_tc(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F,
                                          const void *images, const float *shift, float *pooled, cudaStream_t stream)
 {
-    return launch_tc(false, codes, nmask, B, L, U, F, images, shift, nullptr, nullptr, pooled, nullptr, nullptr, stream);
+    return launch_tc(false, false, codes, nmask, B, L, U, F, images, shift, nullptr, nullptr, pooled, nullptr, nullptr, stream);
+}
+
+extern "C" int explainn_conv_pool_fwd_tc_fp16(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F,
+                                              const void *images, const float *shift, float *pooled, cudaStream_t stream)
+{
+    return launch_tc(false, true, codes, nmask, B, L, U, F, images, shift, nullptr, nullptr, pooled, nullptr, nullptr, stream);
 }
 
 extern "C" int explainn_conv_pool_fwd_train_tc(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F,
@@ -556,5 +607,5 @@ extern "C" int explainn_conv_pool_fwd_train_tc(const uint32_t *codes, const uint
                                                float *pooled, float *xhat, unsigned char *idx, cudaStream_t stream)
 {
     XB_REQUIRE(gamma && beta && xhat && idx, "conv_pool_fwd_train_tc: null pointer");
-    return launch_tc(true, codes, nmask, B, L, U, F, images, shift, gamma, beta, pooled, xhat, idx, stream);
+    return launch_tc(true, false, codes, nmask, B, L, U, F, images, shift, gamma, beta, pooled, xhat, idx, stream);
 }

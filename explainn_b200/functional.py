@@ -329,21 +329,24 @@ def fc_nchunk(B):
 
 
 # ------------------------------------------------------------------------------------------ tensor-core conv
-def conv_tc_prepare(w, bias, gamma, beta, mean, var, eps=1e-5):
+def conv_tc_prepare(w, bias, gamma, beta, mean, var, eps=1e-5, sign_of=None):
+    """Weight images of the tensor-core conv.  `sign_of` (U): training passes the BatchNorm gain whose sign is folded
+    into the rows (the prepare call itself then gets gamma = 1, beta = 0 and the batch statistics)."""
     U, four, F = w.shape
     images = torch.empty(_cabi.lib.explainn_conv_tc_image_halfs(U, F), dtype=torch.float16, device=w.device)
-    shift = torch.empty(U, dtype=torch.float32, device=w.device)
+    shift = torch.empty(2 * U, dtype=torch.float32, device=w.device)
     call("explainn_conv_tc_prepare", ptr(w.contiguous()), ptr(bias), ptr(gamma), ptr(beta), ptr(mean), ptr(var), float(eps),
-         U, F, ptr(images), ptr(shift), stream())
+         ptr(sign_of), U, F, ptr(images), ptr(shift), stream())
     return images, shift, U, F
 
 
-def conv_pool_fwd_tc(pk, tcprep):
+def conv_pool_fwd_tc(pk, tcprep, fp16_weights=False):
+    """fp16_weights: the stated-tolerance mode (one fp16 piece per weight, half the tensor-core work)."""
     images, shift, U, F = tcprep
     P = pooled_len(pk.L, F)
     pooled = torch.empty((pk.B, U, P), dtype=torch.float32, device=pk.codes.device)
     if pk.B:
-        call("explainn_conv_pool_fwd_tc", ptr(pk.codes), ptr(pk.nmask), pk.B, pk.L, U, F, ptr(images), ptr(shift), ptr(pooled),
+        call("explainn_conv_pool_fwd_tc_fp16" if fp16_weights else "explainn_conv_pool_fwd_tc", ptr(pk.codes), ptr(pk.nmask), pk.B, pk.L, U, F, ptr(images), ptr(shift), ptr(pooled),
              stream())
     return pooled
 

@@ -156,6 +156,7 @@ class ExplaiNN(nn.Module):
         self.final = nn.Linear(U, num_classes)
         self._invalid = None      # lazily read counter of non-one-hot input columns
         # "tc": tcgen05/TMEM implicit-GEMM conv for inference and the training forward (fp32-rounding accurate);
+        # "tc_fp16": inference only, one fp16 piece per weight (stated tolerance 2e-3, half the tensor-core work);
         # "lut": the k-mer table kernel (bit-identical to the CPU oracle).  The interpretation pass always uses "lut".
         self.conv_backend = "tc"
         if weight_path:
@@ -219,11 +220,11 @@ class ExplaiNN(nn.Module):
             raise RuntimeError("model.linears[:4] on the fused path needs eval() mode")
         if self._options["num_fc"] == 0:       # MaxPool1d(S): exp of the maximum over all positions, (B,U,1)
             return Fn.pwm_score(pk, self._conv_prep_eval(), 2).unsqueeze(-1)
-        if self.conv_backend == "tc":
+        if self.conv_backend in ("tc", "tc_fp16"):
             conv, bn = self.linears[0], self.linears[1]
             tcp = Fn.conv_tc_prepare(conv.weight.detach(), conv.bias.detach(), bn.weight.detach(), bn.bias.detach(),
                                      bn.running_mean, bn.running_var, bn.eps)
-            return Fn.conv_pool_fwd_tc(pk, tcp)
+            return Fn.conv_pool_fwd_tc(pk, tcp, fp16_weights=self.conv_backend == "tc_fp16")
         return Fn.conv_pool_fwd(pk, self._conv_prep_eval())
 
     @on_device_of(1)

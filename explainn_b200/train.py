@@ -26,6 +26,15 @@ def _dist():
     return dist if dist.is_available() and dist.is_initialized() else None
 
 
+class _Captured:
+    """One captured training step (CUDA graph, its static input / output tensors, launch counts)."""
+    __slots__ = ("graph", "graph2", "gx", "gy", "gloss", "launches", "launches2", "keep")
+
+    def __init__(self):
+        self.graph = self.graph2 = self.gx = self.gy = self.gloss = self.keep = None
+        self.launches = self.launches2 = 0
+
+
 class FusedTrainer:
     """Flat-buffer training step: forward, fused loss, backward, (all-reduce), fused Adam."""
 
@@ -115,9 +124,8 @@ class FusedTrainer:
         # CUDA-graph replay of forward+loss+backward (the step is launch-bound at batch 512, SURVEY 7.3 g)
         self.use_graph = use_graph
         self._graph = None
+        self._graphs = {}
         self._graph_failed = False
-        self._gx = self._gy = self._gloss = None
-        self._graph_launches = 0
         self._seed_ctr = torch.zeros(1, dtype=torch.int64, device=dev)
         self._loss_scratch = torch.zeros(_cabi.lib.explainn_loss_scratch_bytes(), dtype=torch.uint8, device=dev)
         self.world = 1
@@ -130,7 +138,6 @@ class FusedTrainer:
         # opt-in (XB_DP_OVERLAP=1): measured on 2 B200s the NCCL kernel competing with the conv backward for SMs costs more
         # (2.15 M seq/s) than the exposed 4.6 MB all-reduce of the default single collective (2.21 M seq/s)
         self.dp_overlap = os.environ.get("XB_DP_OVERLAP", "0") == "1"
-        self._graph2 = None
         self._pending = None
 
     def _still_aliased(self):
@@ -181,68 +188,77 @@ class FusedTrainer:
         return 1.0 / self.world
 
     def _capture(self, x, y, seed):
-        """Capture forward+loss+backward for this batch shape.  Capturing executes nothing, so the
-        BatchNorm running statistics are untouched until the first replay."""
-        self._gx = torch.empty_like(x)
-        self._gy = torch.empty_like(y)
+        """Capture forward+loss+backward for this batch shape / dtype.  Capturing executes nothing, so the BatchNorm
+        running statistics are untouched until the first replay.  One graph per input signature is kept (fp32 one-hot
+        and ASCII text batches, or a short last batch, each get their own), at most four."""
+        c = _Captured()
+        c.gx = torch.empty_like(x)
+        c.gy = torch.empty_like(y)
         if x.dtype == torch.uint8:
             self.model._pack(x)          # creates the cached offset vector of this shape outside the capture
         g = torch.cuda.CUDAGraph()
-        g2 = None
         l0 = _cabi.LAUNCHES
         try:
             self._split = None
             with torch.cuda.graph(g, capture_error_mode="thread_local"):
                 self._seed_ctr.add_(1)
-                self._gloss = self._fwd_bwd(self._gx, self._gy, seed, self._seed_ctr)
-            self._graph_launches = _cabi.LAUNCHES - l0
+                c.gloss = self._fwd_bwd(c.gx, c.gy, seed, self._seed_ctr)
+            c.launches = _cabi.LAUNCHES - l0
             if self._split is not None:      # world > 1: the conv backward is a second graph (see _between)
                 ws, gpool = self._split
-                g2 = torch.cuda.CUDAGraph()
-                with torch.cuda.graph(g2, pool=g.pool(), capture_error_mode="thread_local"):
+                c.graph2 = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(c.graph2, pool=g.pool(), capture_error_mode="thread_local"):
                     autograd_fn.train_backward_conv(self.model, ws, gpool, self.views_p, self.views_g)
-                self._graph2_launches = _cabi.LAUNCHES - l0 - self._graph_launches
-                self._split = (ws, gpool)    # keep the workspace of the captured graphs alive
+                c.launches2 = _cabi.LAUNCHES - l0 - c.launches
+                c.keep = (ws, gpool)         # keep the workspace of the captured graphs alive
             _cabi.LAUNCHES = l0              # captured, not executed
         except Exception as e:      # keep training eagerly rather than fail
             import warnings
             warnings.warn("explainn_b200: CUDA-graph capture failed (%s); continuing without graphs" % (e,))
             self._graph_failed = True
+            self._graphs.clear()
             self._graph = None
-            self._graph2 = None
             torch.cuda.synchronize()
-            return
-        self._graph = g
-        self._graph2 = g2
+            return None
+        c.graph = g
+        if len(self._graphs) >= 4:
+            self._graphs.pop(next(iter(self._graphs)))
+        return c
 
     @_cabi.on_device_of(1)
     def step(self, x, y):
-        """One optimisation step (train.py:59-67).  Returns the loss as a 1-element device tensor."""
+        """One optimisation step (train.py:59-67).  Returns the loss as a 1-element device tensor.  `x`: fp32 / fp16
+        one-hot (B,4,L) or uint8 ASCII text (B,L) on the device."""
         if not self._still_aliased():       # somebody re-assigned a parameter: re-adopt it
             for p, v in zip(self.params, self.views_p):
                 if p.data_ptr() != v.data_ptr():
                     v.copy_(p.data)
                     p.data = v
+            self._graphs.clear()
             self._graph = None
-            self._graph2 = None
         base = self.dropout_seed if self.dropout_seed is not None else (torch.initial_seed() & 0xFFFFFFFFFFFF)
         seed = (base + 0x9E3779B97F4A7C15 * (self.steps_done + 1)) & 0xFFFFFFFFFFFFFFFF
         y = y.to(x.device, dtype=torch.float32).contiguous()
         x = x.contiguous()
-        # the first step runs eagerly (it is the warm-up); the graph is captured once, for the shape of the
-        # second step; batches of any other shape (a short last batch) run eagerly
-        if self.use_graph and not self._graph_failed and self._graph is None and self.steps_done >= 1:
-            self._capture(x, y, base)
-        if self._graph is not None and self._gx.shape == x.shape and self._gx.dtype == x.dtype:
-            self._gx.copy_(x, non_blocking=True)
-            self._gy.copy_(y, non_blocking=True)
-            self._graph.replay()
-            _cabi.LAUNCHES += self._graph_launches
-            if self._graph2 is not None:
+        # the first step runs eagerly (it is the warm-up); a graph is captured the first time an input signature is
+        # seen after that
+        key = (tuple(x.shape), x.dtype, tuple(y.shape))
+        c = self._graphs.get(key)
+        if c is None and self.use_graph and not self._graph_failed and self.steps_done >= 1:
+            c = self._capture(x, y, base)
+            if c is not None:
+                self._graphs[key] = c
+        if c is not None and self.use_graph:
+            self._graph = c.graph            # (kept for callers that test "is a graph in use")
+            c.gx.copy_(x, non_blocking=True)
+            c.gy.copy_(y, non_blocking=True)
+            c.graph.replay()
+            _cabi.LAUNCHES += c.launches
+            if c.graph2 is not None:
                 self._start_fc_allreduce()          # NCCL works on the FC-stack gradients while the conv backward runs
-                self._graph2.replay()
-                _cabi.LAUNCHES += self._graph2_launches
-            loss = self._gloss.clone()
+                c.graph2.replay()
+                _cabi.LAUNCHES += c.launches2
+            loss = c.gloss.clone()
         else:
             loss = self._fwd_bwd(x, y, seed)
         g = self.optimizer.param_groups[0]
@@ -260,6 +276,18 @@ class FusedTrainer:
              ptr(self.step_t), float(g["lr"]), float(b1), float(b2), float(g["eps"]), scale, stream())
         self.steps_done += 1
         return loss
+
+    def sync_buffers(self):
+        """Data parallel: every rank normalises with its own batch statistics, so the BatchNorm running statistics drift
+        apart between replicas.  Average them over the ranks (call before validation / interpretation so that every
+        rank evaluates the same model; DistributedDataParallel broadcasts rank 0's buffers instead)."""
+        d = _dist()
+        if d is None or self.world == 1:
+            return
+        for name, buf in self.model.named_buffers():
+            if buf.dtype.is_floating_point:
+                d.all_reduce(buf, op=d.ReduceOp.SUM)
+                buf.div_(self.world)
 
     def check_health(self):
         """Raise if the peer-memory optimizer step ever gave up waiting for a rank (one small synchronous read)."""
@@ -392,6 +420,8 @@ def train_explainn(train_loader, test_loader, model, device, criterion,
         epoch_loss = _epoch_mean(step_losses)
         train_error.append(epoch_loss)
 
+        if fused is not None:
+            fused.sync_buffers()
         val_losses = []
         with torch.no_grad():
             model.eval()

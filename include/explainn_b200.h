@@ -104,13 +104,24 @@ int explainn_conv_pool_fwd_train(const uint32_t *codes, const uint32_t *nmask, l
  * evaluated as an fp16 GEMM (one-hot operand exact; fp32 weights split into two fp16 pieces, fp32 accumulation in
  * tensor memory), so results agree with the table kernel to fp32 rounding, not bit for bit; the interpretation
  * entry points keep the table kernel.  images: explainn_conv_tc_image_halfs(U,F) fp16 values written by
- * explainn_conv_tc_prepare (arguments as explainn_conv_prepare; shift (U) fp32 is added in the epilogue).  Outputs as in the table variants (B,U,P). */
+ * explainn_conv_tc_prepare (arguments as explainn_conv_prepare).  Every filter row is stored times a power of two that
+ * brings its largest tap into [128, 256) -- no folded weight can overflow fp16 or lose its low piece to the fp16
+ * subnormal range -- and times the sign of sign_of[u] (NULL: +1; training passes the BatchNorm gain so that pooling
+ * gamma * x_hat + beta is a maximum of the raw accumulators).  shift: (2U) fp32, the shift added in the epilogue
+ * followed by the signed inverse row scale the epilogue multiplies by.  Outputs as in the table variants (B,U,P).
+ * Training tie rule: the first maximum of sign(gamma) * x_hat inside the window (gamma == 0: position 0). */
 long long explainn_conv_tc_image_halfs(int U, int F);
 int explainn_conv_tc_prepare(const float *w, const float *bias, const float *gamma, const float *beta,
-                             const float *mean, const float *var, float eps, int U, int F, void *images,
-                             float *shift, cudaStream_t stream);
+                             const float *mean, const float *var, float eps, const float *sign_of, int U, int F,
+                             void *images, float *shift, cudaStream_t stream);
 int explainn_conv_pool_fwd_tc(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F,
                               const void *images, const float *shift, float *pooled, cudaStream_t stream);
+/* Stated-tolerance variant (inference only): the weights enter as ONE fp16 piece (the high half of the split), i.e.
+ * each tap carries a relative rounding error of at most 2^-11 (row-scaled, so no overflow / underflow); accumulation
+ * stays fp32.  Half the tensor-core work of explainn_conv_pool_fwd_tc.  Tolerance (tests/test_gpu_eval.py): pooled
+ * activations within 2e-3 relative of the fp32 path, logits within 2e-3 of the tensor scale. */
+int explainn_conv_pool_fwd_tc_fp16(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F,
+                                   const void *images, const float *shift, float *pooled, cudaStream_t stream);
 int explainn_conv_pool_fwd_train_tc(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F,
                                     const void *images, const float *shift, const float *gamma, const float *beta,
                                     float *pooled, float *xhat, unsigned char *idx, cudaStream_t stream);

@@ -223,3 +223,40 @@ def test_empty_batch_and_errors():
         networks.ExplaiNN(8, 60, 2, 19, num_fc=3)
     with pytest.raises(NotImplementedError):
         networks.ExplaiNN(8, 60, 2, 19, pool_size=5, pool_stride=5)
+
+
+def test_tc_fp16_weight_mode_stated_tolerance():
+    """conv_backend = "tc_fp16": one fp16 piece per folded weight (relative rounding 2^-11 per tap), fp32 accumulation.
+    Stated tolerance: pooled activations within 2e-3 relative of the fp32-accurate path, logits within 2e-3 of the
+    tensor scale; the two-piece default stays at 1e-5 / 1e-4.  Includes folded weights far outside the fp16 range
+    (row scaling in explainn_conv_tc_prepare)."""
+    from explainn_b200 import networks
+    torch.manual_seed(5)
+    m = networks.ExplaiNN(300, 251, 81, 19)
+    with torch.no_grad():
+        m.linears[1].weight.uniform_(0.5, 1.5)
+        m.linears[1].running_var.uniform_(0.5, 1.5)
+        m.linears[0].weight[:20].mul_(1e-6)            # folded taps ~1e-7: fp16 subnormal range without the row scale
+        m.linears[1].bias[:20] = -3.0
+        m.linears[0].weight[20:24].mul_(3e5)           # folded taps ~3e4 .. 1e5: fp16 overflow without the row scale
+        m.linears[1].bias[20:24] = -4e5
+    m = m.to(DEV).eval()
+    x = torch.from_numpy(onehot_from_codes(random_codes(512, 251, 9, n_frac=0.01))).to(DEV)
+    with torch.no_grad():
+        m.conv_backend = "lut"
+        p_ref, o_ref = m.linears[:4](x), m(x)
+        m.conv_backend = "tc"
+        p_tc, o_tc = m.linears[:4](x), m(x)
+        m.conv_backend = "tc_fp16"
+        p_16, o_16 = m.linears[:4](x), m(x)
+    assert torch.isfinite(p_ref).all()
+    rel = lambda a, b: float(((a - b).abs() / b.abs().clamp_min(1e-30)).max())
+    # units 20..23 have |z| of 1e5: relative error of exp(z) there is |z| * (relative error of z)
+    keep = torch.ones(300, dtype=torch.bool, device=DEV)
+    keep[20:24] = False
+    assert rel(p_tc[:, keep], p_ref[:, keep]) <= 1e-5
+    assert rel(p_16[:, keep], p_ref[:, keep]) <= 2e-3
+    assert float((p_tc[:, ~keep] - p_ref[:, ~keep]).abs().max()) <= 1e-2 * float(p_ref[:, ~keep].abs().max() + 1e-30)
+    assert float((o_tc - o_ref).abs().max()) <= 1e-4 * float(o_ref.abs().max())
+    assert float((o_16 - o_ref).abs().max()) <= 2e-3 * float(o_ref.abs().max())
+    assert not torch.equal(p_16, p_tc)
