@@ -263,40 +263,40 @@ struct MaxSink {
     }
 };
 
-// (5) interpretation pass B: count one-hot windows at positions whose float16 activation exceeds
-//     the float16 threshold (interpretation.py:187,209-214).
-//     hit  <=>  half(exp(z)) > thr  <=>  z > zhi, or z in (zlo, zhi] and the exact test holds;
-//     zlo/zhi bracket the cut-over by 64 ulps on each side (prep.cu: interp_thresholds).
-struct CountSink {
-    struct Params { const float *zlo; const float *zhi; const float *thr; unsigned long long *counts; unsigned long long *hits; unsigned char *seq_hit; };
-    static __host__ __device__ int smem_bytes(int F) { return (4 * F + 1) * XB_UT * 4; }
+// (5) interpretation pass B, first half: WHICH positions have a float16 activation above the float16 threshold
+//     (interpretation.py:187,209).  hit  <=>  half(exp(z)) > thr  <=>  z > zhi, or z in (zlo, zhi] and the exact test
+//     holds; zlo/zhi bracket the cut-over by 64 ulps on each side (prep.cu: interp_thresholds).
+//     The sink only records the hits: one bit per position, W = ceil(S/32) words per (sequence, unit), plus one flag
+//     byte per (sequence, unit).  The windows themselves are counted afterwards by hit_count_kernel with bit-parallel
+//     population counts, so the cost of pass B does not depend on how many positions hit (round 1 added F shared-memory
+//     atomics per hit inside the scan: 50x slower when 5 % of the positions hit).
+struct HitSink {
+    struct Params { const float *zlo; const float *zhi; const float *thr; uint32_t *hitbits; unsigned char *flags; int W; };
+    static __host__ __device__ int smem_bytes(int) { return 0; }
     Params p;
-    unsigned int *cnt;   // [4*F + 1][32]; last row = number of hit positions
-    int lane, warp;
+    int lane;
     float shift, zlo, zhi, thr;
-    const uint32_t *cw, *mw;
-    __device__ void init_cta(unsigned char *smem, const Params &pp, int warp_, int lane_)
-    {
-        p = pp;
-        lane = lane_;
-        warp = warp_;
-        cnt = reinterpret_cast<unsigned int *>(smem);
-    }
+    unsigned long long acc64;
+    int nb, wi;
+    bool seq_any, valid;
+    uint32_t *dst;
+    long long flag_idx;
+    __device__ void init_cta(unsigned char *, const Params &pp, int, int lane_) { p = pp; lane = lane_; }
     __device__ void begin_tile(int u0, int, float shift_, const ConvArgs &a)
     {
         shift = shift_;
         const int u = u0 + lane;
-        zlo = u < a.U ? p.zlo[u] : INFINITY;
-        zhi = u < a.U ? p.zhi[u] : INFINITY;
-        thr = u < a.U ? p.thr[u] : INFINITY;
-        for (int i = threadIdx.x; i < (4 * a.F + 1) * XB_UT; i += blockDim.x) cnt[i] = 0;
-        __syncthreads();
+        valid = u < a.U;
+        zlo = valid ? p.zlo[u] : INFINITY;
+        zhi = valid ? p.zhi[u] : INFINITY;
+        thr = valid ? p.thr[u] : INFINITY;
     }
-    long long seq_b;
-    int seq_u0;
-    bool seq_any;
-    __device__ void set_seq(const uint32_t *cw_, const uint32_t *mw_) { cw = cw_; mw = mw_; }
-    __device__ void begin_seq(long long b, int u0, const ConvArgs &) { seq_b = b; seq_u0 = u0; seq_any = false; }
+    __device__ void begin_seq(long long b, int u0, const ConvArgs &a)
+    {
+        acc64 = 0ull; nb = 0; wi = 0; seq_any = false;
+        flag_idx = b * a.U + u0 + lane;
+        dst = p.hitbits + flag_idx * p.W;
+    }
     __device__ __forceinline__ void window(int win, int t, const float *acc, const ConvArgs &a)
     {
         if (win >= a.nwin) return;
@@ -309,41 +309,25 @@ struct CountSink {
             if (h && t + j < a.S) hitmask |= 1u << j;
         }
         seq_any |= hitmask != 0;
-        if (__any_sync(0xffffffffu, hitmask != 0)) record(t, hitmask, a);
-    }
-    __device__ __noinline__ void record(int t, unsigned hitmask, const ConvArgs &a)
-    {
-        for (int j = 0; j < XB_POOL; ++j) {
-            const bool h = (hitmask >> j) & 1;
-            if (!__any_sync(0xffffffffu, h)) continue;
-            if (h) atomicAdd(&cnt[4 * a.F * XB_UT + lane], 1u);
-            for (int k = 0; k < a.F; ++k) {
-                const int pos = t + j + k;
-                if ((mw[pos >> 5] >> (pos & 31)) & 1) continue;
-                const int c = (cw[pos >> 4] >> (2 * (pos & 15))) & 3;
-                if (h) atomicAdd(&cnt[(c * a.F + k) * XB_UT + lane], 1u);
-            }
+        acc64 |= (unsigned long long)hitmask << nb;
+        nb += XB_POOL;
+        if (nb >= 32) {
+            if (valid) dst[wi] = (uint32_t)acc64;
+            acc64 >>= 32;
+            nb -= 32;
+            ++wi;
         }
     }
-    __device__ void end_seq(const ConvArgs &a)
+    __device__ void end_seq(const ConvArgs &)
     {
-        // "does sequence b have any position above threshold for unit u" -- the set interpretation.py:311-317 builds
-        if (p.seq_hit && seq_u0 + lane < a.U) p.seq_hit[seq_b * a.U + seq_u0 + lane] = seq_any ? 1 : 0;
-    }
-    __device__ void end_tile(int u0, const ConvArgs &a)
-    {
-        __syncthreads();
-        for (int i = threadIdx.x; i < (4 * a.F + 1) * XB_UT; i += blockDim.x) {
-            const unsigned v = cnt[i];
-            const int u = u0 + (i & 31);
-            if (v && u < a.U) {
-                const int row = i >> 5;
-                if (row < 4 * a.F) atomicAdd(&p.counts[(long long)u * 4 * a.F + row], (unsigned long long)v);
-                else atomicAdd(&p.hits[u], (unsigned long long)v);
-            }
+        if (!valid) return;
+        for (; wi < p.W; ++wi) {                 // the last, partly filled word and any word past the last window
+            dst[wi] = (uint32_t)acc64;
+            acc64 >>= 32;
         }
-        __syncthreads();
+        p.flags[flag_idx] = seq_any ? 1 : 0;
     }
+    __device__ void end_tile(int, const ConvArgs &) {}
 };
 
 // (6) PWM scoring (explainn/models/networks.py:393-441): per sequence and unit, the maximum or the sum of the conv
@@ -429,7 +413,6 @@ struct ArgmaxSink {
 };
 
 template <class Sink> struct NeedsSeq { static constexpr bool value = false; };
-template <> struct NeedsSeq<CountSink> { static constexpr bool value = true; };
 
 // ----------------------------------------------------------------------------------------------
 // The scan kernel.  grid = one CTA per SM; the flattened (tile, sequence) space is split evenly.
@@ -816,19 +799,133 @@ extern "C" int explainn_interp_seq_argmax(const uint32_t *codes, const uint32_t 
     return dispatch_scan<ArgmaxSink, ArgmaxSink>(g.G, a, sp, 0, stream);
 }
 
+// Base masks of a batch: bmask[n][c][i] bit p = 1 iff base(32 i + p) == c (N columns and positions >= L: no bit),
+// i <= W.  One warp per sequence.
+__global__ void __launch_bounds__(256) basemask_kernel(const uint32_t *__restrict__ codes, const uint32_t *__restrict__ nmask, long long B,
+                                                       int L, int W, uint32_t *__restrict__ bmask)
+{
+    const int lane = threadIdx.x & 31;
+    const long long n = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (n >= B) return;
+    const int wc = xb_words_codes(L), wm = xb_words_mask(L);
+    for (int i = 0; i <= W; ++i) {
+        const int pos = 32 * i + lane;
+        int c = 4;
+        if (pos < L && !((nmask[n * wm + (pos >> 5)] >> (pos & 31)) & 1u)) c = (codes[n * wc + (pos >> 4)] >> (2 * (pos & 15))) & 3;
+#pragma unroll
+        for (int cc = 0; cc < 4; ++cc) {
+            const unsigned m = __ballot_sync(0xffffffffu, c == cc);
+            if (lane == cc) bmask[(n * 4 + cc) * (W + 1) + i] = m;
+        }
+    }
+}
+
+// Pass B, second half: counts[u][c][k] += #{hit positions s of unit u : base(s + k) == c} = popc(H_u & (B_c >> k)).
+// A warp owns 8 units and a range of sequences; lane k < F owns tap k (its base masks shifted by k live in registers,
+// prepared once per sequence and 8-word chunk), lane 31 carries an all-ones mask and so counts the hits themselves.
+// The 32 counters per lane stay in registers over all the warp's sequences: no atomics until the very end.
+__global__ void __launch_bounds__(128) hit_count_kernel(const uint32_t *__restrict__ hitbits, const uint32_t *__restrict__ bmask,
+                                                        const unsigned char *__restrict__ flags, long long B, int U, int W, int F,
+                                                        unsigned long long *__restrict__ counts, unsigned long long *__restrict__ hits)
+{
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int u0 = blockIdx.x * 8;
+    const long long n0 = B * blockIdx.y / gridDim.y, n1 = B * (blockIdx.y + 1) / gridDim.y;
+    unsigned acc[8][4];
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+#pragma unroll
+        for (int c = 0; c < 4; ++c) acc[j][c] = 0u;
+    const bool tap = lane < F, ones = lane == 31;
+    for (long long n = n0 + warp; n < n1; n += 4) {
+        const unsigned f = (lane < 8 && u0 + lane < U) ? flags[n * U + u0 + lane] : 0;
+        const unsigned any = __ballot_sync(0xffffffffu, f != 0);
+        if (!any) continue;
+        const uint32_t *bm = bmask + n * 4 * (W + 1);
+        const uint32_t *hb = hitbits + (n * U + u0) * W;
+        for (int w0 = 0; w0 < W; w0 += 8) {
+            unsigned m[4][8];
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                unsigned prev = w0 < W ? bm[c * (W + 1) + w0] : 0u;
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const unsigned next = (w0 + i < W) ? bm[c * (W + 1) + w0 + i + 1] : 0u;
+                    m[c][i] = (w0 + i < W) ? (tap ? __funnelshift_r(prev, next, lane) : ((ones && c == 0) ? 0xFFFFFFFFu : 0u)) : 0u;
+                    prev = next;
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                if (!((any >> j) & 1u)) continue;
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const unsigned h = (w0 + i < W) ? hb[j * W + w0 + i] : 0u;
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) acc[j][c] += __popc(h & m[c][i]);
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const int u = u0 + j;
+        if (u >= U) continue;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            if (!acc[j][c]) continue;
+            if (tap) atomicAdd(&counts[((long long)u * 4 + c) * F + lane], (unsigned long long)acc[j][c]);
+            else if (ones && c == 0) atomicAdd(&hits[u], (unsigned long long)acc[j][c]);
+        }
+    }
+}
+
+static long long pwm_count_layout(long long B, int L, int U, int F, long long *off_bmask, long long *off_bits)
+{
+    const int S = L - F + 1, W = (S + 31) / 32;
+    long long o = (B * U + 255) / 256 * 256;            // flag bytes
+    *off_bmask = o;
+    o += (B * 4 * (W + 1) * 4 + 255) / 256 * 256;
+    *off_bits = o;
+    o += B * U * W * 4;
+    return o;
+}
+
+extern "C" long long explainn_interp_pwm_count_scratch_bytes(long long B, int L, int U, int F)
+{
+    if (B < 0 || U < 1 || F < 1 || L < F) return 0;
+    long long a, b;
+    return pwm_count_layout(B, L, U, F, &a, &b);
+}
+
 extern "C" int explainn_interp_pwm_count(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F,
                                          const float *tables, const float *wq_t, const float *shift, const float *zlo,
                                          const float *zhi, const float *thr, unsigned long long *counts,
-                                         unsigned long long *hits, unsigned char *seq_hit, cudaStream_t stream)
+                                         unsigned long long *hits, unsigned char *seq_hit, void *scratch, cudaStream_t stream)
 {
     ConvArgs a; Geometry g;
     int rc = fill_args(&a, &g, codes, nmask, B, L, U, F, tables, wq_t, shift);
     if (rc != XB_OK) return rc;
-    XB_REQUIRE(zlo && zhi && thr && counts && hits, "interp_pwm_count: null pointer");
+    XB_REQUIRE(zlo && zhi && thr && counts && hits && scratch, "interp_pwm_count: null pointer");
     if (B == 0) return XB_OK;
     a.nwin = g.nwin_all;
-    CountSink::Params sp{zlo, zhi, thr, counts, hits, seq_hit};
-    return dispatch_scan<CountSink, CountSink>(g.G, a, sp, F, stream);
+    const int W = (g.S + 31) / 32;
+    long long off_bmask, off_bits;
+    pwm_count_layout(B, L, U, F, &off_bmask, &off_bits);
+    unsigned char *base = static_cast<unsigned char *>(scratch);
+    unsigned char *flags = seq_hit ? seq_hit : base;
+    uint32_t *bmask = reinterpret_cast<uint32_t *>(base + off_bmask), *bits = reinterpret_cast<uint32_t *>(base + off_bits);
+    HitSink::Params sp{zlo, zhi, thr, bits, flags, W};
+    rc = dispatch_scan<HitSink, HitSink>(g.G, a, sp, 0, stream);
+    if (rc != XB_OK) return rc;
+    basemask_kernel<<<(unsigned)((B + 7) / 8), 256, 0, stream>>>(codes, nmask, B, L, W, bmask);
+    const int groups = (U + 7) / 8;
+    long long split = (8LL * xb_num_sms() + groups - 1) / groups;
+    if (split > (B + 3) / 4) split = (B + 3) / 4;
+    if (split > 65535) split = 65535;
+    if (split < 1) split = 1;
+    hit_count_kernel<<<dim3((unsigned)groups, (unsigned)split), 128, 0, stream>>>(bits, bmask, flags, B, U, W, F, counts, hits);
+    return xb_check_launch("interp_pwm_count");
 }
 
 // ----------------------------------------------------------------------------------------------

@@ -186,7 +186,9 @@ __device__ __forceinline__ void tc_drain(uint32_t taddr, int row, int nwin, int 
                 stage[plane + row * sst + win] = xh;
                 stage_i[row * sst + win] = (unsigned char)ib;
             } else {
-                stage[row * sst + win] = tc_expf(__fmaf_rn(m, rs, shift));
+                // inference: the 2-instruction exp (relative error |z| * 2^-24 from the multiplication by log2(e), within
+                // the 1e-5 the tests ask of this backend); the epilogue's instruction count sets the pace of this kernel
+                stage[row * sst + win] = __expf(__fmaf_rn(m, rs, shift));
             }
         }
     };
@@ -251,7 +253,7 @@ template <bool TRAIN>
 __global__ void __launch_bounds__(TC_THREADS + 64, 1) conv_tc_kernel(const TcArgs a)
 {
     extern __shared__ __align__(128) unsigned char smem[];
-    __shared__ __align__(8) uint64_t bar_a, tmem_full[2], tmem_empty[2], v_full[TC_VBUFS], v_empty[TC_VBUFS];
+    __shared__ __align__(8) uint64_t bar_a[4], tmem_full[2], tmem_empty[2], v_full[TC_VBUFS], v_empty[TC_VBUFS];
     __shared__ uint32_t tmem_base_s;
 
     const int K = a.K, KC = K / 8, KS = K / 16;
@@ -277,7 +279,7 @@ __global__ void __launch_bounds__(TC_THREADS + 64, 1) conv_tc_kernel(const TcArg
     const long long it0 = total * blockIdx.x / gridDim.x, it1 = total * (blockIdx.x + 1) / gridDim.x;
 
     if (threadIdx.x == 0) {
-        mbar_init(&bar_a, 1);
+        for (int i = 0; i < 4; ++i) mbar_init(&bar_a[i], 1);
         mbar_init(&tmem_full[0], 1);
         mbar_init(&tmem_full[1], 1);
         mbar_init(&tmem_empty[0], TC_THREADS / 64);      // the 8 warps of the epilogue group that owns the buffer
@@ -299,7 +301,7 @@ __global__ void __launch_bounds__(TC_THREADS + 64, 1) conv_tc_kernel(const TcArg
         // =========================== issue warp ===========================
         // waits for an operand buffer (built by the builder warp) and a free accumulator, issues the MMAs of every
         // resident unit tile and commits; the last commit of an item also hands its operand buffer back
-        uint32_t a_parity = 0;
+        uint32_t a_parity = 1;                             // toggled when a group's load is issued: first group waits on 0
         int cur_grp = -1;
         long long n = 0;                                   // tiles issued by this CTA
         long long vi = 0;                                  // items (V tiles) consumed by this CTA
@@ -310,13 +312,14 @@ __global__ void __launch_bounds__(TC_THREADS + 64, 1) conv_tc_kernel(const TcArg
             if (t.grp != cur_grp) {
                 // new group of unit tiles: every MMA that reads sA must have completed before TMA overwrites it
                 if (n > 0) mbar_wait(&tmem_full[(n - 1) & 1], (uint32_t)(((n - 1) >> 1) & 1));
+                // one barrier per image: the MMAs of the first tile start as soon as ITS weights have landed
                 if (lane == 0) {
-                    mbar_arrive_expect_tx(&bar_a, (uint32_t)mtn * 2 * a_bytes);
-                    for (int m = 0; m < mtn; ++m)
+                    for (int m = 0; m < mtn; ++m) {
+                        mbar_arrive_expect_tx(&bar_a[m], 2 * a_bytes);
                         tma_bulk_g2s(sA + (size_t)m * 2 * a_bytes, reinterpret_cast<const unsigned char *>(a.images) + (size_t)(mt0 + m) * 2 * a_bytes,
-                                     2 * a_bytes, &bar_a);
+                                     2 * a_bytes, &bar_a[m]);
+                    }
                 }
-                mbar_wait(&bar_a, a_parity);
                 a_parity ^= 1;
                 cur_grp = t.grp;
             }
@@ -331,6 +334,7 @@ __global__ void __launch_bounds__(TC_THREADS + 64, 1) conv_tc_kernel(const TcArg
             for (int m = 0; m < mtn; ++m, ++n) {
                 const int buf = (int)(n & 1);
                 const uint32_t use = (uint32_t)(n >> 1);   // how often this accumulator has been used before
+                mbar_wait(&bar_a[m], a_parity);                      // this tile's weights (immediate after the first item)
                 mbar_wait(&tmem_empty[buf], (use & 1) ^ 1);          // drained by the epilogue warps
                 XB_CLK(2);                                 // wait for a free accumulator
                 // descriptors of K step 0, computed by the whole warp; a K step advances A by 256 bytes and V by 64
@@ -569,7 +573,7 @@ static int launch_tc(bool train, bool single, const uint32_t *codes, const uint3
         xb_set_error("conv_pool_fwd_tc: %zu bytes of shared memory needed (L=%d, filter_size=%d)", fixed + tile_bytes, L, F);
         return XB_ERR_UNSUPPORTED;
     }
-    a.gsz = (int)std::min<size_t>((budget - fixed) / tile_bytes, (size_t)n_mt);
+    a.gsz = (int)std::min<size_t>(std::min<size_t>((budget - fixed) / tile_bytes, (size_t)n_mt), 4);      // four weight barriers
     const size_t smem = fixed + (size_t)a.gsz * tile_bytes;
     const int n_grp = (n_mt + a.gsz - 1) / a.gsz;
     long long total = (long long)n_grp * B * nchunk;

@@ -269,8 +269,11 @@ def interp_pwm_count(pk, prep, thr, zlo, zhi, counts=None, hits=None, seq_hit=No
         hits = torch.zeros(prep.U, dtype=torch.int64, device=dev)
     if pk.B == 0:
         return counts, hits
+    nbytes = _cabi.lib.explainn_interp_pwm_count_scratch_bytes(pk.B, pk.L, prep.U, prep.F)
+    scratch = torch.empty(nbytes, dtype=torch.uint8, device=dev)
     call("explainn_interp_pwm_count", ptr(pk.codes), ptr(pk.nmask), pk.B, pk.L, prep.U, prep.F, ptr(prep.tables),
-         ptr(prep.wq_t), ptr(prep.shift), ptr(zlo), ptr(zhi), ptr(thr), ptr(counts), ptr(hits), ptr(seq_hit), stream())
+         ptr(prep.wq_t), ptr(prep.shift), ptr(zlo), ptr(zhi), ptr(thr), ptr(counts), ptr(hits), ptr(seq_hit), ptr(scratch),
+         stream())
     return counts, hits
 
 

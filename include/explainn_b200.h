@@ -168,11 +168,14 @@ int explainn_pwm_score(const uint32_t *codes, const uint32_t *nmask, long long B
  * (interpretation.py:203-214); hits[u] += number of such positions.  counts (U,4,F) u64, hits (U) u64,
  * both accumulated into (zero them first).  seq_hit (B,U) u8, optional (NULL to skip): 1 if the sequence has any
  * position above threshold for the unit -- the per-unit sequence sets of get_specific_unit_importance
- * (interpretation.py:311-317). */
+ * (interpretation.py:311-317).  Three kernels: the scan records one hit bit per position, then the windows are counted
+ * with bit-parallel population counts (cost independent of the number of hits).  scratch:
+ * explainn_interp_pwm_count_scratch_bytes(B, L, U, F) bytes of caller-owned workspace (hit bits, base masks, flags). */
+long long explainn_interp_pwm_count_scratch_bytes(long long B, int L, int U, int F);
 int explainn_interp_pwm_count(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F,
                               const float *tables, const float *wq_t, const float *shift, const float *zlo,
                               const float *zhi, const float *thr, unsigned long long *counts,
-                              unsigned long long *hits, unsigned char *seq_hit, cudaStream_t stream);
+                              unsigned long long *hits, unsigned char *seq_hit, void *scratch, cudaStream_t stream);
 
 /* Per (sequence, unit): the maximum activation exp(z) (float32) and the FIRST position that attains it, the rule of
  * `torch.max(activations, dim=2)` (explainn/models/networks.py:228,281; the reference computes it for its ConvNet

@@ -239,7 +239,7 @@ def test_tc_fp16_weight_mode_stated_tolerance():
         m.linears[0].weight[:20].mul_(1e-6)            # folded taps ~1e-7: fp16 subnormal range without the row scale
         m.linears[1].bias[:20] = -3.0
         m.linears[0].weight[20:24].mul_(3e5)           # folded taps ~3e4 .. 1e5: fp16 overflow without the row scale
-        m.linears[1].bias[20:24] = -4e5
+        m.linears[1].bias[20:24] = -2e6                # keeps exp(z) finite (it underflows) for these units
     m = m.to(DEV).eval()
     x = torch.from_numpy(onehot_from_codes(random_codes(512, 251, 9, n_frac=0.01))).to(DEV)
     with torch.no_grad():
