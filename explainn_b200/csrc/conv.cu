@@ -531,47 +531,49 @@ __global__ void __launch_bounds__(NW * 32, 1) conv_scan_kernel(const ConvArgs a,
                         addr[SPAN + j] = lane_base + ((km & 0xFFu) << 7);
                     }
                 }
-                // any N column under this iteration's footprint?
-                bool has_n;
+                // N flags of the positions under this iteration's footprint (bit p = position t0 + p).  All lanes of the
+                // warp work on the same sequence, so every test on them is warp-uniform.
+                unsigned long long MM;
                 {
-                    constexpr int NB = ITER_POS - 1 + 4 * G;   // positions touched
                     const uint32_t wi = (uint32_t)t0 >> 5, sh = (uint32_t)t0 & 31u;
                     const uint32_t m0 = mw[wi], m1 = mw[wi + 1], m2 = mw[wi + 2];
-                    const uint32_t M0 = __funnelshift_r(m0, m1, sh), M1 = __funnelshift_r(m1, m2, sh);
-                    if (NB <= 32) has_n = (M0 & (NB == 32 ? 0xFFFFFFFFu : ((1u << (NB & 31)) - 1u))) != 0;
-                    else has_n = (M0 | (M1 & ((1u << ((NB - 32) & 31)) - 1u))) != 0;
+                    MM = (unsigned long long)__funnelshift_r(m0, m1, sh) | ((unsigned long long)__funnelshift_r(m1, m2, sh) << 32);
                 }
+                const uint32_t foot = a.F >= 32 ? 0xFFFFFFFFu : ((1u << a.F) - 1u);     // taps >= F are +0 in the tables
                 float acc[ITER_POS];
-                if (!has_n) {
 #pragma unroll
-                    for (int j = 0; j < ITER_POS; ++j) {
-                        float v = lds_f32(tbl, addr[j]);
+                for (int j = 0; j < ITER_POS; ++j) {
+                    const uint32_t nm = (uint32_t)(MM >> j) & foot;
+                    float v;
+                    if (nm == 0u) {
+                        v = lds_f32(tbl, addr[j]);
 #pragma unroll
                         for (int g = 1; g < G; ++g) v = __fadd_rn(v, lds_f32(tbl, addr[j + 4 * g] + g * TBL_GROUP_BYTES));
-                        acc[j] = v;
-                    }
-                } else {
+                    } else {
+                        // an N column under this window: only the 4-tap groups that contain it are summed tap by tap
+                        // (same expression as the table entry, with +0 for the N taps); the others keep their lookup
+                        v = 0.0f;
 #pragma unroll
-                    for (int j = 0; j < ITER_POS; ++j) {
-                        const int t = t0 + j;
-                        float v = 0.0f;
-#pragma unroll 1
                         for (int g = 0; g < G; ++g) {
-                            float tg = 0.0f;
+                            const uint32_t nib = (nm >> (4 * g)) & 15u;
+                            float tg;
+                            if (nib == 0u) {
+                                tg = lds_f32(tbl, addr[j + 4 * g] + g * TBL_GROUP_BYTES);
+                            } else {
+                                const uint32_t km = (addr[j + 4 * g] - lane_base) >> 7;
+                                tg = 0.0f;
 #pragma unroll
-                            for (int jj = 0; jj < 4; ++jj) {
-                                const int k = 4 * g + jj, pos = t + k;
-                                float w = 0.0f;
-                                if (k < a.F && !((mw[pos >> 5] >> (pos & 31)) & 1)) {
-                                    const int c = (cw[pos >> 4] >> (2 * (pos & 15))) & 3;
-                                    w = wq[(c * a.F + k) * XB_UT + lane];
+                                for (int jj = 0; jj < 4; ++jj) {
+                                    const int k = 4 * g + jj;
+                                    float w = 0.0f;
+                                    if (k < a.F && !((nib >> jj) & 1u)) w = wq[(((km >> (2 * jj)) & 3u) * a.F + k) * XB_UT + lane];
+                                    tg = jj == 0 ? w : __fadd_rn(tg, w);
                                 }
-                                tg = jj == 0 ? w : __fadd_rn(tg, w);
                             }
                             v = g == 0 ? tg : __fadd_rn(v, tg);
                         }
-                        acc[j] = v;
                     }
+                    acc[j] = v;
                 }
 #pragma unroll
                 for (int w = 0; w < ITER_WIN; ++w) sink.window(it * ITER_WIN + w, t0 + w * XB_POOL, acc + w * XB_POOL, a);

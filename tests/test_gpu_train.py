@@ -206,10 +206,11 @@ def test_train_step_vs_torch_port(U, L, C, F, B, loss, backend):
             # units may reach a percent of the BatchNorm-1 gain gradient (Adam normalises the magnitude away in any case)
             dg = float(port.linears[1].weight.grad.abs().max())
             assert float(q.grad.abs().median()) < 1e-5 * dg and float(q.grad.abs().max()) < 5e-2 * dg
-        elif k in ("linears.0.weight", "linears.1.weight", "linears.6.weight", "linears.7.weight", "linears.7.bias"):
-            # parameters upstream of a ReLU / max-pool kink, compared row by row (unit or hidden channel): a
-            # pre-activation within rounding of zero may fall on the other side of the kink, which moves that one
-            # row's gradient by ~1/B of its norm
+        elif k in ("linears.0.weight", "linears.1.weight", "linears.6.weight", "linears.7.weight", "linears.7.bias",
+                   "linears.10.weight", "linears.11.weight", "linears.11.bias"):
+            # parameters upstream of a ReLU / max-pool kink (the unit-output ReLU behind BatchNorm-3 for linears.10 / 11),
+            # compared row by row (unit or hidden channel): a pre-activation within rounding of zero may fall on the
+            # other side of the kink, which moves that one row's gradient by ~1/B of its norm
             _close_per_unit(q.grad.cpu().numpy(), p.grad.numpy(), 2e-4, "grad " + k, batch=B)
         else:
             _close(q.grad.cpu().numpy(), p.grad.numpy(), 2e-4, "grad " + k)
