@@ -18,7 +18,7 @@ if not os.path.exists(LIB_PATH):
 
 lib = C.CDLL(LIB_PATH)
 
-DTYPE_F32, DTYPE_F16 = 0, 1
+DTYPE_F32, DTYPE_F16, DTYPE_F32_PREACT = 0, 1, 2
 LOSS_BCE, LOSS_MSE = 0, 1
 
 _P, _LL, _I, _F, _ULL = C.c_void_p, C.c_longlong, C.c_int, C.c_float, C.c_ulonglong
@@ -66,6 +66,12 @@ SIGNATURES = {
     "explainn_fc_stack_bwd": [_P, _LL, _I, _I, _I] + [_P] * 14 + [_F, _ULL, _P, _P] + [_P] * 14 + [_P],
     "explainn_conv_bwd_nsplit": [_I],
     "explainn_conv_pool_bwd": [_P, _P, _LL, _I, _I, _I] + [_P] * 10 + [_F, _P, _I] + [_P] * 4 + [_P],
+    "explainn_pool_general": [_P, _LL, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P],
+    "explainn_conv_pool_bwd_general": [_P, _P, _LL, _I, _I, _I, _I, _I] + [_P] * 10 + [_F, _P, _I] + [_P] * 4 + [_P],
+    "explainn_linear_bwd": [_P, _P, _P, _LL, _I, _I, _P, _P, _P, _P],
+    "explainn_hidden_fwd_train": [_P, _LL, _I, _I] + [_P] * 6 + [_F, _F, _F, _ULL, _P] + [_P] * 4 + [_P],
+    "explainn_hidden_fwd_eval": [_P, _LL, _I, _I] + [_P] * 6 + [_F] + [_P] * 3 + [_P],
+    "explainn_hidden_bwd": [_P, _LL, _I, _I] + [_P] * 7 + [_F, _ULL, _P] + [_P] * 7 + [_P],
     "explainn_loss_scratch_bytes": [],
     "explainn_loss_fwd_bwd": [_P, _P, _LL, _I, _I, _F, _P, _P, _P, _P],
     "explainn_adam_step": [_P, _P, _P, _P, _LL, _P, _F, _F, _F, _F, _F, _P],

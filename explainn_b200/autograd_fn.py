@@ -29,8 +29,17 @@ def _num_fc(model):
     return model._options.get("num_fc", 2)
 
 
+def _is_variant(model):
+    """True for the units served by variants.py: num_fc = 0 or > 2, or a pool other than MaxPool1d(7, 7)."""
+    o = model._options
+    return o.get("num_fc", 2) not in (1, 2) or o.get("pool_size", 7) != Fn.POOL or o.get("pool_stride", 7) != Fn.POOL
+
+
 def _params(model):
     """Parameters in state_dict order; the conv / BatchNorm-1 tensors always come first."""
+    if _is_variant(model):
+        from . import variants
+        return variants.params(model)
     L = model.linears
     if _num_fc(model) == 0:        # networks.py:73-80 (eval only here: _check_modes refuses to train it)
         return (L[0].weight, L[0].bias, L[1].weight, L[1].bias, model.final.weight, model.final.bias)
@@ -63,6 +72,11 @@ class TrainWorkspace:
 
 def train_forward(model, x, params=None, seed=None, seed_dev=None):
     """Runs the training-mode forward kernels.  Returns a TrainWorkspace (logits in ws.logits)."""
+    if _is_variant(model):
+        from . import variants
+        if params is None:
+            params = [p.detach() for p in _params(model)]
+        return variants.train_forward(model, x, params, _next_dropout_seed() if seed is None else seed, seed_dev)
     _check_modes(model)
     L = model.linears
     if params is None:
@@ -207,6 +221,9 @@ def train_backward(model, ws, gout, params=None, grads=None, wrt_unit=False, bet
     L = model.linears
     if params is None:
         params = [p.detach() for p in _params(model)]
+    if _is_variant(model):
+        from . import variants
+        return variants.train_backward(model, ws, gout, params, grads, wrt_unit, between)
     if _num_fc(model) == 1:
         return _train_backward_fc1(model, ws, gout, params, grads, wrt_unit, between)
     (cw, cb, g1, b1n, W1, b1, g2, be2, W2, b2, g3, be3, Wf, bf) = params
@@ -233,6 +250,9 @@ def train_backward(model, ws, gout, params=None, grads=None, wrt_unit=False, bet
 
 def train_backward_conv(model, ws, gpool, params, grads, wrt_unit=False):
     """Second half of the backward: sparse conv / BatchNorm-1 gradients from d(pooled)."""
+    if _is_variant(model):
+        from . import variants
+        return variants.train_backward_conv(model, ws, gpool, params, grads, wrt_unit)
     L = model.linears
     (cw, cb, g1, b1n) = params[:4]
     (dcw, dcb, dg1, db1n) = grads[:4]

@@ -176,8 +176,8 @@ struct PoolTrainSinkT {
     __device__ void end_tile(int, const ConvArgs &) {}
 };
 
-// (3) activation map: act[b,u,s] = exp(z) for every s < S, float16 or float32
-template <typename OutT, int PCH_>
+// (3) activation map: act[b,u,s] = exp(z) for every s < S, float16 or float32 (RAW: z itself, float32)
+template <typename OutT, int PCH_, bool RAW = false>
 struct ActSink {
     struct Params { OutT *act; };
     static constexpr int PCH = PCH_;                     // windows per flush
@@ -214,7 +214,10 @@ struct ActSink {
         if (win - win_base == PCH) flush(win, a);
         const int c0 = (win - win_base) * XB_POOL;
 #pragma unroll
-        for (int j = 0; j < XB_POOL; ++j) stage[lane * ROW + c0 + j] = (OutT)det_expf(__fadd_rn(acc[j], shift));
+        for (int j = 0; j < XB_POOL; ++j) {
+            const float z = __fadd_rn(acc[j], shift);
+            stage[lane * ROW + c0 + j] = (OutT)(RAW ? z : det_expf(z));
+        }
     }
     __device__ void end_seq(const ConvArgs &a) { flush(a.nwin, a); }
     __device__ void end_tile(int, const ConvArgs &) {}
@@ -731,6 +734,9 @@ extern "C" int explainn_unit_activations(const uint32_t *codes, const uint32_t *
     } else if (act_dtype == EXPLAINN_DTYPE_F32) {
         ActSink<float, 6>::Params sp{(float *)act};
         return dispatch_scan<ActSink<float, 6>, ActSink<float, 1>>(g.G, a, sp, 0, stream);
+    } else if (act_dtype == EXPLAINN_DTYPE_F32_PREACT) {
+        ActSink<float, 6, true>::Params sp{(float *)act};
+        return dispatch_scan<ActSink<float, 6, true>, ActSink<float, 1, true>>(g.G, a, sp, 0, stream);
     }
     xb_set_error("unit_activations: unsupported dtype %d", act_dtype);
     return XB_ERR_UNSUPPORTED;

@@ -948,6 +948,29 @@ extern "C" int explainn_fc_stack_fwd_train(const float *pooled, long long B, int
     return xb_check_launch("fc_stack_fwd_train");
 }
 
+// Backward of the final Linear alone (networks.py:147,161), for the units without an FC stack (num_fc = 0):
+// dWf (C,U) = glogits^T unit, dbf (C) = column sums of glogits, gunit (B,U) = glogits Wf masked where unit <= 0
+// (unit outputs are post-ReLU or post-exp, so the mask only ever hides entries whose gradient is dead anyway).
+extern "C" int explainn_linear_bwd(const float *glogits, const float *unit, const float *Wf, long long B, int U, int C, float *gunit,
+                                   float *dWf, float *dbf, cudaStream_t stream)
+{
+    XB_REQUIRE(glogits && unit && Wf && gunit && B >= 1 && U >= 1 && C >= 1, "linear_bwd: bad argument");
+    if (dWf) cudaMemsetAsync(dWf, 0, (size_t)C * U * sizeof(float), stream);
+    if (dbf) cudaMemsetAsync(dbf, 0, (size_t)C * sizeof(float), stream);
+    if (dWf || dbf) {
+        const int nsb = (int)std::min<long long>(8, (B + 63) / 64);
+        bwd_final_linear2_kernel<<<dim3((U + 127) / 128, (C + 7) / 8, nsb), 128, 0, stream>>>(glogits, unit, B, U, C, dWf, dbf);
+    }
+    const size_t smem_gu = ((size_t)8 * C + (size_t)C * GU_UT) * 4;
+    if (smem_gu > 200 * 1024) {
+        xb_set_error("linear_bwd: %d classes need %zu bytes of shared memory", C, smem_gu);
+        return XB_ERR_LIMIT;
+    }
+    cudaFuncSetAttribute(bwd_gunit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_gu);
+    bwd_gunit_kernel<<<dim3((unsigned)((B + 7) / 8), (U + GU_UT - 1) / GU_UT), 256, smem_gu, stream>>>(glogits, Wf, unit, B, U, C, gunit);
+    return xb_check_launch("linear_bwd");
+}
+
 extern "C" int explainn_fc_stack_bwd(const float *glogits, long long B, int U, int P, int C, const float *pooled, const float *h1,
                                      const float *h2, const float *unit, const float *W1, const float *bn2_w, const float *bn2_b,
                                      const float *mean2, const float *invstd2, const float *W2, const float *bn3_w,

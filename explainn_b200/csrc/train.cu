@@ -155,7 +155,8 @@ template <int FT>
 __global__ void __launch_bounds__(BW_WARPS * 32) conv_bwd_sparse_kernel(
     const uint32_t *__restrict__ codes, const uint32_t *__restrict__ nmask, long long B, int L, int Frt, int P, int wc, int wm,
     const float *__restrict__ gpool, const float *__restrict__ pooled, const float *__restrict__ xhat,
-    const unsigned char *__restrict__ idx, float *__restrict__ partial /* (nsplit, U, 4F+2) */, int U)
+    const unsigned char *__restrict__ idx, const unsigned short *__restrict__ idx16, int pstride,
+    float *__restrict__ partial /* (nsplit, U, 4F+2) */, int U)
 {
     extern __shared__ float acc[];   // [BW_WARPS][F][4][32] then [BW_WARPS][4F+2] for the block reduce
     const int F = FT > 0 ? FT : Frt;
@@ -194,8 +195,8 @@ __global__ void __launch_bounds__(BW_WARPS * 32) conv_bwd_sparse_kernel(
         r.gp = gpool[o];
         r.po = pooled[o];
         r.xh = xhat[o];
-        r.ix = idx[o];
-        r.p7 = ap * XB_POOL;
+        r.ix = idx16 ? (int)idx16[o] : (int)idx[o];      // offset of the maximum inside its pool window
+        r.p7 = ap * pstride;
         r.b = ab;
         ea += STRIDE;
         ab += db; ap += dp;
@@ -458,23 +459,24 @@ extern "C" int explainn_conv_bwd_nsplit(int U)
     return ns < 1 ? 1 : ns;
 }
 
-extern "C" int explainn_conv_pool_bwd(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F,
-                                      const float *gpool, const float *pooled, const float *xhat, const unsigned char *idx,
-                                      const int *M, const float *Mw, const float *bias, const float *mean, const float *var,
-                                      const float *gamma, float eps, float *partial, int nsplit, float *dW, float *dbias,
-                                      float *dgamma, float *dbeta, cudaStream_t stream)
+static int conv_pool_bwd_impl(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F, int psize, int pstride,
+                              const float *gpool, const float *pooled, const float *xhat, const unsigned char *idx,
+                              const unsigned short *idx16, const int *M, const float *Mw, const float *bias, const float *mean,
+                              const float *var, const float *gamma, float eps, float *partial, int nsplit, float *dW, float *dbias,
+                              float *dgamma, float *dbeta, cudaStream_t stream)
 {
-    XB_REQUIRE(codes && nmask && gpool && pooled && xhat && idx && M && Mw && bias && mean && var && gamma && partial,
+    XB_REQUIRE(codes && nmask && gpool && pooled && xhat && (idx || idx16) && M && Mw && bias && mean && var && gamma && partial,
                "conv_pool_bwd: null pointer");
-    XB_REQUIRE(B >= 1 && U >= 1 && F >= 1 && F <= 4 * XB_MAX_G && L >= F + XB_POOL - 1 && nsplit >= 1, "conv_pool_bwd: bad sizes");
-    const int S = L - F + 1, P = (S - XB_POOL) / XB_POOL + 1, W = 4 * F;
+    XB_REQUIRE(B >= 1 && U >= 1 && F >= 1 && F <= 4 * XB_MAX_G && psize >= 1 && pstride >= 1 && L >= F + psize - 1 && nsplit >= 1,
+               "conv_pool_bwd: bad sizes");
+    const int S = L - F + 1, P = (S - psize) / pstride + 1, W = 4 * F;
     XB_REQUIRE(B * P < (1LL << 31), "conv_pool_bwd: B*P = %lld entries per unit exceed 2^31", B * P);
     const size_t smem = ((size_t)BW_WARPS * W * 32 + (size_t)BW_WARPS * (W + 2)) * sizeof(float);
 #define XB_LAUNCH_SPARSE(FTV)                                                                                                  \
     do {                                                                                                                      \
         cudaFuncSetAttribute(conv_bwd_sparse_kernel<FTV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);            \
         conv_bwd_sparse_kernel<FTV><<<dim3(U, nsplit), BW_WARPS * 32, smem, stream>>>(                                        \
-            codes, nmask, B, L, F, P, xb_words_codes(L), xb_words_mask(L), gpool, pooled, xhat, idx, partial, U);             \
+            codes, nmask, B, L, F, P, xb_words_codes(L), xb_words_mask(L), gpool, pooled, xhat, idx, idx16, pstride, partial, U); \
     } while (0)
     if (F == 19) XB_LAUNCH_SPARSE(19);
     else if (F == 20) XB_LAUNCH_SPARSE(20);
@@ -485,6 +487,28 @@ extern "C" int explainn_conv_pool_bwd(const uint32_t *codes, const uint32_t *nma
     conv_bwd_final_kernel<<<U, 128, 0, stream>>>(partial, nsplit, U, F, M, Mw, bias, mean, var, gamma, eps, (double)B * S, dW, dbias,
                                                 dgamma, dbeta);
     return xb_check_launch("conv_bwd_final");
+}
+
+extern "C" int explainn_conv_pool_bwd(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F,
+                                      const float *gpool, const float *pooled, const float *xhat, const unsigned char *idx,
+                                      const int *M, const float *Mw, const float *bias, const float *mean, const float *var,
+                                      const float *gamma, float eps, float *partial, int nsplit, float *dW, float *dbias,
+                                      float *dgamma, float *dbeta, cudaStream_t stream)
+{
+    return conv_pool_bwd_impl(codes, nmask, B, L, U, F, XB_POOL, XB_POOL, gpool, pooled, xhat, idx, nullptr, M, Mw, bias, mean, var, gamma,
+                              eps, partial, nsplit, dW, dbias, dgamma, dbeta, stream);
+}
+
+// any (pool_size, pool_stride); idx16 (B,U,P) u16 = offset of the window maximum (explainn_pool_general)
+extern "C" int explainn_conv_pool_bwd_general(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F,
+                                              int pool_size, int pool_stride, const float *gpool, const float *pooled,
+                                              const float *xhat, const unsigned short *idx16, const int *M, const float *Mw,
+                                              const float *bias, const float *mean, const float *var, const float *gamma, float eps,
+                                              float *partial, int nsplit, float *dW, float *dbias, float *dgamma, float *dbeta,
+                                              cudaStream_t stream)
+{
+    return conv_pool_bwd_impl(codes, nmask, B, L, U, F, pool_size, pool_stride, gpool, pooled, xhat, nullptr, idx16, M, Mw, bias, mean, var,
+                              gamma, eps, partial, nsplit, dW, dbias, dgamma, dbeta, stream);
 }
 
 extern "C" long long explainn_loss_scratch_bytes(void) { return (long long)LOSS_MAX_BLOCKS * sizeof(double) + 16; }

@@ -169,10 +169,13 @@ def conv_pool_fwd(pk, prep):
     return pooled
 
 
-def unit_activations(pk, prep, dtype=torch.float16):
+def unit_activations(pk, prep, dtype=torch.float16, preact=False):
+    """exp(z) as (B,U,S) in `dtype`; preact=True: z itself (float32), the input of pool_general."""
     S = pk.L - prep.F + 1
+    if preact:
+        dtype = torch.float32
     act = torch.empty((pk.B, prep.U, S), dtype=dtype, device=pk.codes.device)
-    dt = _cabi.DTYPE_F16 if dtype == torch.float16 else _cabi.DTYPE_F32
+    dt = _cabi.DTYPE_F32_PREACT if preact else (_cabi.DTYPE_F16 if dtype == torch.float16 else _cabi.DTYPE_F32)
     if pk.B == 0:
         return act
     call("explainn_unit_activations", ptr(pk.codes), ptr(pk.nmask), pk.B, pk.L, prep.U, prep.F, ptr(prep.tables),
@@ -364,3 +367,32 @@ def conv_pool_fwd_train_tc(pk, tcprep, gamma, beta):
     call("explainn_conv_pool_fwd_train_tc", ptr(pk.codes), ptr(pk.nmask), pk.B, pk.L, U, F, ptr(images), ptr(shift), ptr(gamma), ptr(beta),
          ptr(pooled), ptr(xhat), ptr(idx), stream())
     return pooled, xhat, idx
+
+
+# ------------------------------------------------------------------------------------------ model variants (generic.cu)
+def pool_general(z, pool_size, pool_stride, gamma=None, beta=None):
+    """General max-pool of the pre-activation map z (B,U,S).  Eval (gamma None): pooled.  Train: pooled, xhat, idx16."""
+    B, U, S = z.shape
+    P = (S - pool_size) // pool_stride + 1
+    dev = z.device
+    pooled = torch.empty((B, U, P), dtype=torch.float32, device=dev)
+    train = gamma is not None
+    xhat = torch.empty((B, U, P), dtype=torch.float32, device=dev) if train else None
+    idx = torch.empty((B, U, P), dtype=torch.int16, device=dev) if train else None
+    if B:
+        call("explainn_pool_general", ptr(z), B, U, S, int(pool_size), int(pool_stride), ptr(gamma), ptr(beta), ptr(pooled), ptr(xhat),
+             ptr(idx), stream())
+    return (pooled, xhat, idx) if train else pooled
+
+
+def hidden_fwd_eval(X, W, b, bn, eps):
+    """Hidden block in eval mode: X (B,U,Pin) -> (B,U,100).  bn = (weight, bias, running_mean, running_var)."""
+    B, U, Pin = X.shape
+    dev = X.device
+    out = torch.empty((B, U, HIDDEN), dtype=torch.float32, device=dev)
+    if B:
+        Y = torch.empty((U, B, HIDDEN), dtype=torch.float32, device=dev)
+        stat = torch.empty(2 * U * HIDDEN, dtype=torch.float32, device=dev)
+        call("explainn_hidden_fwd_eval", ptr(X), B, U, Pin, ptr(W.contiguous()), ptr(b), ptr(bn[0]), ptr(bn[1]), ptr(bn[2]), ptr(bn[3]),
+             float(eps), ptr(Y), ptr(stat), ptr(out), stream())
+    return out

@@ -100,13 +100,10 @@ class ExplaiNN(nn.Module):
             "pool_stride": pool_stride,
             "weight_path": weight_path,
         }
-        if num_fc not in (0, 1, 2):
-            raise NotImplementedError(
-                "explainn_b200 implements num_fc = 0, 1 (networks.py:73-95) and the default 2 (networks.py:96-116); "
-                "num_fc=%d (extra 100 -> 100 layers, networks.py:117-145) is not built yet" % num_fc)
-        if num_fc != 0 and (pool_size != Fn.POOL or pool_stride != Fn.POOL):
-            raise NotImplementedError("explainn_b200: pool 7/7 only (the reference default); pool=%d/%d is not built yet"
-                                      % (pool_size, pool_stride))
+        if num_fc < 0:
+            raise ValueError("num_fc must be >= 0")
+        if pool_size < 1 or pool_stride < 1:
+            raise ValueError("pool_size and pool_stride must be >= 1")
         if filter_size > 24:
             raise NotImplementedError("explainn_b200: filter_size <= 24 (k-mer tables of the fused conv kernel)")
         if input_length > 2048:
@@ -116,7 +113,7 @@ class ExplaiNN(nn.Module):
         S = input_length - (filter_size - 1)
         P = 1 if num_fc == 0 else Fn.pooled_len(input_length, filter_size, pool_size, pool_stride)
         if S < 1 or P < 1:
-            raise ValueError("input_length %d too short for filter_size %d and pool 7" % (input_length, filter_size))
+            raise ValueError("input_length %d too short for filter_size %d and pool size %d" % (input_length, filter_size, pool_size))
         if num_fc == 0:          # networks.py:73-80: global max-pool, no FC
             self.linears = _UnitStack(
                 nn.Conv1d(in_channels=4 * U, out_channels=U, kernel_size=filter_size, groups=U),   # 0
@@ -136,7 +133,7 @@ class ExplaiNN(nn.Module):
                 nn.BatchNorm1d(U, 1e-05, 0.1, True),                                                # 7
                 nn.ReLU(),                                                                          # 8
                 nn.Flatten())                                                                       # 9
-        else:
+        elif num_fc == 2:
             self.linears = _UnitStack(
                 nn.Conv1d(in_channels=4 * U, out_channels=U, kernel_size=filter_size, groups=U),   # 0
                 nn.BatchNorm1d(U),                                                                  # 1
@@ -152,6 +149,28 @@ class ExplaiNN(nn.Module):
                 nn.BatchNorm1d(U, 1e-05, 0.1, True),                                                # 11
                 nn.ReLU(),                                                                          # 12
                 nn.Flatten())                                                                       # 13
+        else:                    # networks.py:117-145: num_fc - 2 extra hidden layers between FC1 and the 100 -> 1 layer
+            self.linears = _UnitStack(
+                nn.Conv1d(in_channels=4 * U, out_channels=U, kernel_size=filter_size, groups=U),   # 0
+                nn.BatchNorm1d(U),                                                                  # 1
+                ExpActivation(),                                                                    # 2
+                nn.MaxPool1d(pool_size, pool_stride),                                               # 3
+                nn.Flatten(),                                                                       # 4
+                Unsqueeze(),                                                                        # 5
+                nn.Conv1d(in_channels=P * U, out_channels=HIDDEN * U, kernel_size=1, groups=U),     # 6
+                nn.BatchNorm1d(HIDDEN * U, 1e-05, 0.1, True),                                       # 7
+                nn.ReLU())                                                                          # 8
+            self.linears_bg = nn.ModuleList([nn.Sequential(
+                nn.Dropout(0.3),
+                nn.Conv1d(in_channels=HIDDEN * U, out_channels=HIDDEN * U, kernel_size=1, groups=U),
+                nn.BatchNorm1d(HIDDEN * U, 1e-05, 0.1, True),
+                nn.ReLU()) for _ in range(num_fc - 2)])
+            self.last_linear = nn.Sequential(
+                nn.Dropout(0.3),
+                nn.Conv1d(in_channels=HIDDEN * U, out_channels=U, kernel_size=1, groups=U),
+                nn.BatchNorm1d(U, 1e-05, 0.1, True),
+                nn.ReLU(),
+                nn.Flatten())
         self.linears._bind(self)
         self.final = nn.Linear(U, num_classes)
         self._invalid = None      # lazily read counter of non-one-hot input columns
@@ -218,8 +237,13 @@ class ExplaiNN(nn.Module):
     def _pooled_packed(self, pk):
         if self._bn_uses_batch_stats():
             raise RuntimeError("model.linears[:4] on the fused path needs eval() mode")
-        if self._options["num_fc"] == 0:       # MaxPool1d(S): exp of the maximum over all positions, (B,U,1)
+        o = self._options
+        if o["num_fc"] == 0:       # MaxPool1d(S): exp of the maximum over all positions, (B,U,1)
             return Fn.pwm_score(pk, self._conv_prep_eval(), 2).unsqueeze(-1)
+        if o["pool_size"] != Fn.POOL or o["pool_stride"] != Fn.POOL:
+            # any other MaxPool1d (networks.py:102): pre-activation map from the table kernel, then the general pool
+            z = Fn.unit_activations(pk, self._conv_prep_eval(), preact=True)
+            return Fn.pool_general(z, o["pool_size"], o["pool_stride"])
         if self.conv_backend in ("tc", "tc_fp16"):
             conv, bn = self.linears[0], self.linears[1]
             tcp = Fn.conv_tc_prepare(conv.weight.detach(), conv.bias.detach(), bn.weight.detach(), bn.bias.detach(),
@@ -246,6 +270,8 @@ class ExplaiNN(nn.Module):
             bn = L[7]
             return Fn.fc1_stack_fwd_eval(pooled, L[6].weight.detach(), L[6].bias.detach(),
                                          (bn.weight.detach(), bn.bias.detach(), bn.running_mean, bn.running_var), bn.eps)
+        if nfc > 2:
+            return self._unit_outputs_eval_deep(pooled)
         bn2, bn3 = L[7], L[11]
         return Fn.fc_stack_fwd_eval(
             pooled, L[6].weight.detach(), L[6].bias.detach(),
@@ -254,7 +280,29 @@ class ExplaiNN(nn.Module):
             (bn3.weight.detach(), bn3.bias.detach(), bn3.running_mean, bn3.running_var), bn2.eps)
 
     @on_device_of(1)
+    def _hidden_eval(self, X, fc, bn):
+        return Fn.hidden_fwd_eval(X, fc.weight.detach(), fc.bias.detach(),
+                                  (bn.weight.detach(), bn.bias.detach(), bn.running_mean, bn.running_var), bn.eps)
+
+    def _unit_outputs_eval_deep(self, pooled):
+        """num_fc > 2 in eval mode: hidden blocks, then the last hidden layer + last_linear in the FC-stack kernel."""
+        from . import variants
+        conv, bn1, fcs, bns, drops, last_fc, last_bn = variants.layout(self)
+        X = pooled
+        for fc, bn in zip(fcs[:-1], bns[:-1]):
+            X = self._hidden_eval(X, fc, bn)
+        fc, bn = fcs[-1], bns[-1]
+        return Fn.fc_stack_fwd_eval(
+            X, fc.weight.detach(), fc.bias.detach(), (bn.weight.detach(), bn.bias.detach(), bn.running_mean, bn.running_var),
+            last_fc.weight.detach(), last_fc.bias.detach(),
+            (last_bn.weight.detach(), last_bn.bias.detach(), last_bn.running_mean, last_bn.running_var), bn.eps)
+
     def _unit_outputs(self, x):
+        if self._options["num_fc"] > 2 and not self.training:
+            # the reference's `linears` ends behind the first hidden layer for num_fc > 2 (networks.py:117-129): calling it
+            # returns those activations, shape (B, 100 * num_cnns, 1)
+            X = self._hidden_eval(self._pooled(x), self.linears[6], self.linears[7])
+            return X.reshape(X.shape[0], -1, 1)
         if self.training:
             from . import autograd_fn
             return autograd_fn.unit_outputs_train(self, x)

@@ -45,8 +45,6 @@ class FusedTrainer:
         from .networks import ExplaiNN
         if not isinstance(model, ExplaiNN) or type(criterion) not in FusedTrainer.LOSSES:
             return False
-        if model._options.get("num_fc", 2) not in (1, 2):
-            return False
         if getattr(criterion, "reduction", "mean") != "mean":
             return False
         if getattr(criterion, "weight", None) is not None or getattr(criterion, "pos_weight", None) is not None:

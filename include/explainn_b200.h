@@ -40,6 +40,7 @@ typedef struct CUstream_st *cudaStream_t;
 
 #define EXPLAINN_DTYPE_F32 0
 #define EXPLAINN_DTYPE_F16 1
+#define EXPLAINN_DTYPE_F32_PREACT 2   /* explainn_unit_activations only: z = BN(conv) before the exponential, fp32 */
 
 #define EXPLAINN_LOSS_BCE_WITH_LOGITS 0
 #define EXPLAINN_LOSS_MSE 1
@@ -128,7 +129,8 @@ int explainn_conv_pool_fwd_train_tc(const uint32_t *codes, const uint32_t *nmask
 
 /* ---- activation scan ------------------------------------------------------------------------------------
  * Replaces `model.linears[:3](seq.repeat(...))` + `.astype(np.half)`
- * (explainn/interpretation/interpretation.py:143-147).  act: (B,U,S) in act_dtype. */
+ * (explainn/interpretation/interpretation.py:143-147).  act: (B,U,S) in act_dtype; EXPLAINN_DTYPE_F32_PREACT writes
+ * the pre-activation z instead (input of the general max-pool path below). */
 int explainn_unit_activations(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F,
                               const float *tables, const float *wq_t, const float *shift, void *act,
                               int act_dtype, cudaStream_t stream);
@@ -291,6 +293,43 @@ int explainn_conv_pool_bwd(const uint32_t *codes, const uint32_t *nmask, long lo
                            const int *M, const float *Mw, const float *bias, const float *mean, const float *var,
                            const float *gamma, float eps, float *partial, int nsplit, float *dW, float *dbias,
                            float *dgamma, float *dbeta, cudaStream_t stream);
+
+/* ==== model variants beside the default unit (explainn/models/networks.py:48-49,73-80,102,117-145) ====
+ * General MaxPool1d(pool_size, pool_stride) over the pre-activation map z (B,U,S) that explainn_unit_activations writes
+ * with EXPLAINN_DTYPE_F32_PREACT (networks.py:102; the global pool MaxPool1d(S) of the num_fc = 0 unit, networks.py:77,
+ * is pool_size = pool_stride = S).  gamma/beta NULL (eval: z carries the BatchNorm map): pooled (B,U,P) = exp(max z).
+ * gamma/beta given (train: the map holds x_hat): first maximum of gamma*x_hat+beta, pooled = exp of it, xhat (B,U,P) the
+ * x_hat there, idx (B,U,P) u16 its offset inside the window (xhat / idx may be NULL). */
+int explainn_pool_general(const float *z, long long B, int U, int S, int pool_size, int pool_stride, const float *gamma,
+                          const float *beta, float *pooled, float *xhat, unsigned short *idx, cudaStream_t stream);
+/* explainn_conv_pool_bwd for any (pool_size, pool_stride) with the 16-bit window offsets of explainn_pool_general. */
+int explainn_conv_pool_bwd_general(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F,
+                                   int pool_size, int pool_stride, const float *gpool, const float *pooled, const float *xhat,
+                                   const unsigned short *idx16, const int *M, const float *Mw, const float *bias,
+                                   const float *mean, const float *var, const float *gamma, float eps, float *partial,
+                                   int nsplit, float *dW, float *dbias, float *dgamma, float *dbeta, cudaStream_t stream);
+/* Backward of the final Linear alone (networks.py:147,161; the num_fc = 0 unit has nothing between pool and Linear):
+ * dWf (C,U), dbf (C), gunit (B,U) = glogits Wf, zeroed where unit <= 0.  dWf / dbf may be NULL. */
+int explainn_linear_bwd(const float *glogits, const float *unit, const float *Wf, long long B, int U, int C, float *gunit,
+                        float *dWf, float *dbf, cudaStream_t stream);
+/* Hidden block of the num_fc > 2 unit (networks.py:117-138): in X (B,U,Pin) -> grouped Conv1d(Pin*U -> 100U, k=1) ->
+ * BatchNorm1d(100U) -> ReLU -> Dropout -> out (B,U,100) (the Dropout is the one the reference places at the head of the
+ * NEXT layer).  W (100U,Pin), b (100U), bn_* (100U).  Train: batch statistics (running buffers updated when non-NULL),
+ * Y (U,B,100) pre-BatchNorm values and mean / invstd (100U) are kept for the backward; dropout mask from `seed`
+ * (+ *seed_dev) and the element index.  Eval: running statistics, no dropout; Y and stat (2*100U) are scratch.
+ * Backward: gout (B,U,100) -> gin (B,U,Pin) (NULL to skip), dW, db (exact zeros), dbn_w, dbn_b; sums (2*100U) and
+ * G (U,B,100) are scratch.  The last hidden layer and last_linear reuse explainn_fc_stack_* with P = 100. */
+int explainn_hidden_fwd_train(const float *X, long long B, int U, int Pin, const float *W, const float *b, const float *bn_w,
+                              const float *bn_b, float *bn_rm, float *bn_rv, float momentum, float eps, float pdrop,
+                              unsigned long long seed, const unsigned long long *seed_dev, float *Y, float *mean,
+                              float *invstd, float *out, cudaStream_t stream);
+int explainn_hidden_fwd_eval(const float *X, long long B, int U, int Pin, const float *W, const float *b, const float *bn_w,
+                             const float *bn_b, const float *bn_rm, const float *bn_rv, float eps, float *Y, float *stat,
+                             float *out, cudaStream_t stream);
+int explainn_hidden_bwd(const float *gout, long long B, int U, int Pin, const float *X, const float *Y, const float *W,
+                        const float *bn_w, const float *bn_b, const float *mean, const float *invstd, float pdrop,
+                        unsigned long long seed, const unsigned long long *seed_dev, float *sums, float *G, float *gin,
+                        float *dW, float *db, float *dbn_w, float *dbn_b, cudaStream_t stream);
 
 /* ---- fused criterion (mean reduction) and its gradient ---------------------------------------------------------
  * BCEWithLogitsLoss / MSELoss as scripts/train.py:210-219 constructs them (explainn/train/train.py:62).

@@ -5,8 +5,8 @@ for the floating-point kernels and the timed CPU baseline of bench.py (`cpu_base
 
 The reference is pure Python on top of torch.nn, so the arithmetic below is executed by the very
 same ATen CPU kernels the reference triggers; what is restated is the module graph:
-  explainn/models/networks.py:73-116   unit stack for num_fc == 0, 1, 2 (module indices kept identical,
-                                       so reference state_dicts load unchanged)
+  explainn/models/networks.py:73-145   unit stack for every num_fc and pool size / stride (module indices kept
+                                       identical, so reference state_dicts load unchanged)
   explainn/models/networks.py:147      final Linear(U, C)
   explainn/models/networks.py:152-162  forward: tile the 4 input rows U times, stack, final
   explainn/train/train.py:54-73        one optimisation step
@@ -61,8 +61,17 @@ class PortExplaiNN(nn.Module):
                     nn.BatchNorm1d(U, 1e-05, 0.1, True),              # 11
                     nn.ReLU(),                                        # 12
                     nn.Flatten()]                                     # 13
-        else:
-            raise NotImplementedError("port: num_fc in (0, 1, 2)")
+        else:                    # networks.py:117-145
+            tail = [nn.MaxPool1d(pool_size, pool_stride), nn.Flatten(), _AddTrailingDim(),
+                    nn.Conv1d(P * U, HIDDEN * U, 1, groups=U),        # 6
+                    nn.BatchNorm1d(HIDDEN * U, 1e-05, 0.1, True),     # 7
+                    nn.ReLU()]                                        # 8
+            self.linears_bg = nn.ModuleList([nn.Sequential(nn.Dropout(0.3), nn.Conv1d(HIDDEN * U, HIDDEN * U, 1, groups=U),
+                                                           nn.BatchNorm1d(HIDDEN * U, 1e-05, 0.1, True), nn.ReLU())
+                                             for _ in range(num_fc - 2)])
+            self.last_linear = nn.Sequential(nn.Dropout(0.3), nn.Conv1d(HIDDEN * U, U, 1, groups=U),
+                                             nn.BatchNorm1d(U, 1e-05, 0.1, True), nn.ReLU(), nn.Flatten())
+        self.num_fc = num_fc
         self.linears = nn.Sequential(*(head + tail))
         self.final = nn.Linear(U, num_classes)
 
@@ -70,7 +79,12 @@ class PortExplaiNN(nn.Module):
         return x.repeat(1, self.U, 1)
 
     def forward(self, x):
-        return self.final(self.linears(self.tile(x)))
+        outs = self.linears(self.tile(x))
+        if self.num_fc > 2:      # networks.py:152-162
+            for blk in self.linears_bg:
+                outs = blk(outs)
+            outs = self.last_linear(outs)
+        return self.final(outs)
 
     # pieces used by the parity tests
     def conv_bn(self, x):
