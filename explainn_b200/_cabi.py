@@ -46,6 +46,10 @@ SIGNATURES = {
     "explainn_interp_thresholds": [_P, _I, _P, _P, _P, _P, _P],
     "explainn_interp_pwm_count_scratch_bytes": [_LL, _I, _I, _I],
     "explainn_interp_pwm_count": [_P, _P, _LL, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P],
+    "explainn_interp_tc_bounds": [_P, _P, _P, _I, _I, _P, _P],
+    "explainn_interp_tc_list_bytes": [_I],
+    "explainn_interp_unit_max_tc": [_P, _P, _LL, _I, _I, _I] + [_P] * 7 + [_LL, _P, _P],
+    "explainn_interp_pwm_count_tc": [_P, _P, _LL, _I, _I, _I] + [_P] * 13 + [_LL, _P, _P],
     "explainn_interp_seq_argmax": [_P, _P, _LL, _I, _I, _I, _P, _P, _P, _P, _P, _P],
     "explainn_act_unit_max": [_P, _I, _LL, _I, _I, _P, _P],
     "explainn_act_thresholds": [_P, _I, _I, _P, _P, _P],
@@ -91,6 +95,7 @@ _RESTYPES = {
     "explainn_conv_wq_floats": _LL,
     "explainn_interp_unit_max_scratch_floats": _LL,
     "explainn_interp_pwm_count_scratch_bytes": _LL,
+    "explainn_interp_tc_list_bytes": _LL,
     "explainn_loss_scratch_bytes": _LL,
     "explainn_conv_tc_image_halfs": _LL,
     "explainn_p2p_flag_bytes": _LL,
@@ -155,7 +160,7 @@ def on_device_of(argnum=1):
 
 
 LAUNCHES = 0   # kernels launched through this binding (bench.py reports it)
-_LAUNCH_COST = {"explainn_interp_unit_max": 3, "explainn_interp_unit_max_noalloc": 3, "explainn_interp_pwm_count": 3, "explainn_input_cooc_stats": 1, "explainn_fc_stack_fwd_train": 3,
+_LAUNCH_COST = {"explainn_interp_unit_max": 3, "explainn_interp_unit_max_noalloc": 3, "explainn_interp_pwm_count": 3, "explainn_interp_unit_max_tc": 4, "explainn_interp_pwm_count_tc": 4, "explainn_input_cooc_stats": 1, "explainn_fc_stack_fwd_train": 3,
                 "explainn_fc_stack_bwd": 6, "explainn_conv_pool_bwd": 2, "explainn_adam_step": 2}
 
 

@@ -21,6 +21,11 @@ enum {
 void xb_set_error(const char *fmt, ...);
 int xb_check_launch(const char *what);
 int xb_num_sms();
+// conv.cu, shared with interp_tc.cu
+int xb_hit_count(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F, const uint32_t *bits, uint32_t *bmask,
+                 const unsigned char *flags, unsigned char *seq_hit_out, unsigned long long *counts, unsigned long long *hits,
+                 cudaStream_t stream);
+long long xb_pwm_count_layout(long long B, int L, int U, int F, long long *off_bmask, long long *off_bits);
 
 #define XB_REQUIRE(cond, ...)                         \
     do {                                              \

@@ -833,7 +833,8 @@ __global__ void __launch_bounds__(256) basemask_kernel(const uint32_t *__restric
 // prepared once per sequence and 8-word chunk), lane 31 carries an all-ones mask and so counts the hits themselves.
 // The 32 counters per lane stay in registers over all the warp's sequences: no atomics until the very end.
 __global__ void __launch_bounds__(128) hit_count_kernel(const uint32_t *__restrict__ hitbits, const uint32_t *__restrict__ bmask,
-                                                        const unsigned char *__restrict__ flags, long long B, int U, int W, int F,
+                                                        const unsigned char *__restrict__ flags, unsigned char *__restrict__ seq_hit_out,
+                                                        long long B, int U, int W, int F,
                                                         unsigned long long *__restrict__ counts, unsigned long long *__restrict__ hits)
 {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -846,11 +847,18 @@ __global__ void __launch_bounds__(128) hit_count_kernel(const uint32_t *__restri
         for (int c = 0; c < 4; ++c) acc[j][c] = 0u;
     const bool tap = lane < F, ones = lane == 31;
     for (long long n = n0 + warp; n < n1; n += 4) {
-        const unsigned f = (lane < 8 && u0 + lane < U) ? flags[n * U + u0 + lane] : 0;
+        const uint32_t *hb = hitbits + (n * U + u0) * W;
+        unsigned f = 0;
+        if (lane < 8 && u0 + lane < U) {
+            if (flags) f = flags[n * U + u0 + lane];
+            else {                                   // no flag bytes (tensor-core pass B): any bit of the row
+                for (int i = 0; i < W; ++i) f |= hb[lane * W + i];
+                if (seq_hit_out) seq_hit_out[n * U + u0 + lane] = f ? 1 : 0;
+            }
+        }
         const unsigned any = __ballot_sync(0xffffffffu, f != 0);
         if (!any) continue;
         const uint32_t *bm = bmask + n * 4 * (W + 1);
-        const uint32_t *hb = hitbits + (n * U + u0) * W;
         for (int w0 = 0; w0 < W; w0 += 8) {
             unsigned m[4][8];
 #pragma unroll
@@ -888,6 +896,25 @@ __global__ void __launch_bounds__(128) hit_count_kernel(const uint32_t *__restri
     }
 }
 
+// shared with interp_tc.cu: base masks of the batch + window counting from hit bits.  flags == NULL: the "any hit" test
+// reads the bit rows themselves and, when seq_hit_out is given, writes the per-(sequence, unit) flags there.
+int xb_hit_count(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F, const uint32_t *bits, uint32_t *bmask,
+                 const unsigned char *flags, unsigned char *seq_hit_out, unsigned long long *counts, unsigned long long *hits,
+                 cudaStream_t stream)
+{
+    const int W = (L - F + 1 + 31) / 32;
+    basemask_kernel<<<(unsigned)((B + 7) / 8), 256, 0, stream>>>(codes, nmask, B, L, W, bmask);
+    const int groups = (U + 7) / 8;
+    long long split = (8LL * xb_num_sms() + groups - 1) / groups;
+    if (split > (B + 3) / 4) split = (B + 3) / 4;
+    if (split > 65535) split = 65535;
+    if (split < 1) split = 1;
+    hit_count_kernel<<<dim3((unsigned)groups, (unsigned)split), 128, 0, stream>>>(bits, bmask, flags, seq_hit_out, B, U, W, F, counts, hits);
+    return xb_check_launch("interp_pwm_count");
+}
+
+long long xb_pwm_count_layout(long long B, int L, int U, int F, long long *off_bmask, long long *off_bits);
+
 static long long pwm_count_layout(long long B, int L, int U, int F, long long *off_bmask, long long *off_bits)
 {
     const int S = L - F + 1, W = (S + 31) / 32;
@@ -897,6 +924,11 @@ static long long pwm_count_layout(long long B, int L, int U, int F, long long *o
     *off_bits = o;
     o += B * U * W * 4;
     return o;
+}
+
+long long xb_pwm_count_layout(long long B, int L, int U, int F, long long *off_bmask, long long *off_bits)
+{
+    return pwm_count_layout(B, L, U, F, off_bmask, off_bits);
 }
 
 extern "C" long long explainn_interp_pwm_count_scratch_bytes(long long B, int L, int U, int F)
@@ -926,14 +958,7 @@ extern "C" int explainn_interp_pwm_count(const uint32_t *codes, const uint32_t *
     HitSink::Params sp{zlo, zhi, thr, bits, flags, W};
     rc = dispatch_scan<HitSink, HitSink>(g.G, a, sp, 0, stream);
     if (rc != XB_OK) return rc;
-    basemask_kernel<<<(unsigned)((B + 7) / 8), 256, 0, stream>>>(codes, nmask, B, L, W, bmask);
-    const int groups = (U + 7) / 8;
-    long long split = (8LL * xb_num_sms() + groups - 1) / groups;
-    if (split > (B + 3) / 4) split = (B + 3) / 4;
-    if (split > 65535) split = 65535;
-    if (split < 1) split = 1;
-    hit_count_kernel<<<dim3((unsigned)groups, (unsigned)split), 128, 0, stream>>>(bits, bmask, flags, B, U, W, F, counts, hits);
-    return xb_check_launch("interp_pwm_count");
+    return xb_hit_count(codes, nmask, B, L, U, F, bits, bmask, flags, nullptr, counts, hits, stream);
 }
 
 // ----------------------------------------------------------------------------------------------

@@ -396,3 +396,44 @@ def hidden_fwd_eval(X, W, b, bn, eps):
         call("explainn_hidden_fwd_eval", ptr(X), B, U, Pin, ptr(W.contiguous()), ptr(b), ptr(bn[0]), ptr(bn[1]), ptr(bn[2]), ptr(bn[3]),
              float(eps), ptr(Y), ptr(stat), ptr(out), stream())
     return out
+
+
+# ------------------------------------------------------------------------------------------ tensor-core interpretation
+class InterpTc:
+    """State of the tensor-core interpretation passes for one model: weight images, error bounds, the list workspace
+    and the device status word (see include/explainn_b200.h: explainn_interp_unit_max_tc / _pwm_count_tc)."""
+
+    def __init__(self, w, prep, tcprep):
+        self.prep, self.tcprep = prep, tcprep
+        dev = w.device
+        U, F = prep.U, prep.F
+        self.delta = torch.empty(U, dtype=torch.float32, device=dev)
+        call("explainn_interp_tc_bounds", ptr(w.contiguous()), ptr(prep.scale), ptr(prep.shift), U, F, ptr(self.delta), stream())
+        self.list_bytes = int(_cabi.lib.explainn_interp_tc_list_bytes(U))
+        self.list = torch.empty(self.list_bytes, dtype=torch.uint8, device=dev)
+        self.status = torch.zeros(1, dtype=torch.int32, device=dev)
+
+    def unit_max(self, pk, zmax):
+        images, shift_rs, U, F = self.tcprep
+        if pk.B:
+            call("explainn_interp_unit_max_tc", ptr(pk.codes), ptr(pk.nmask), pk.B, pk.L, U, F, ptr(images), ptr(shift_rs),
+                 ptr(self.delta), ptr(self.prep.wq_t), ptr(self.prep.shift), ptr(zmax), ptr(self.list), self.list_bytes,
+                 ptr(self.status), stream())
+        return zmax
+
+    def pwm_count(self, pk, thr, zlo, zhi, counts, hits, seq_hit=None):
+        images, shift_rs, U, F = self.tcprep
+        if pk.B:
+            nbytes = _cabi.lib.explainn_interp_pwm_count_scratch_bytes(pk.B, pk.L, U, F)
+            scratch = torch.empty(nbytes, dtype=torch.uint8, device=pk.codes.device)
+            call("explainn_interp_pwm_count_tc", ptr(pk.codes), ptr(pk.nmask), pk.B, pk.L, U, F, ptr(images), ptr(shift_rs),
+                 ptr(self.delta), ptr(self.prep.wq_t), ptr(self.prep.shift), ptr(zlo), ptr(zhi), ptr(thr), ptr(counts), ptr(hits),
+                 ptr(seq_hit), ptr(scratch), ptr(self.list), self.list_bytes, ptr(self.status), stream())
+        return counts, hits
+
+    def check(self):
+        """Raise if a pass had more positions to re-evaluate than the list workspace holds (one small D2H read)."""
+        st = int(self.status.item())
+        if st:
+            raise RuntimeError("explainn_b200: the tensor-core interpretation pass %s overflowed its resolve list; "
+                               "rerun with PwmAccumulator(model, backend='lut')" % ("A" if st & 1 else "B"))

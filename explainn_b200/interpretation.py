@@ -193,12 +193,23 @@ class PwmAccumulator:
     `counts`/`hits` with SUM after pass B (see parallel.py).
     """
 
-    def __init__(self, model):
+    def __init__(self, model, backend="tc"):
+        """backend "tc": both passes on the tensor cores (positions near a decision re-evaluated in the canonical order:
+        same integers as "lut"); "lut": the k-mer table kernel throughout."""
         if model.linears[1].training:
             raise RuntimeError("PWM extraction uses BatchNorm running statistics; call model.eval() first")
+        if backend not in ("tc", "lut"):
+            raise ValueError("backend must be 'tc' or 'lut'")
         self.model = model
-        with torch.cuda.device(model.linears[0].weight.device):
+        self.backend = backend
+        conv, bn = model.linears[0], model.linears[1]
+        with torch.cuda.device(conv.weight.device):
             self.prep = model._conv_prep_eval()
+            self.tc = None
+            if backend == "tc":
+                tcp = Fn.conv_tc_prepare(conv.weight.detach(), conv.bias.detach(), bn.weight.detach(), bn.bias.detach(),
+                                         bn.running_mean, bn.running_var, bn.eps)
+                self.tc = Fn.InterpTc(conv.weight.detach(), self.prep, tcp)
         self.zmax = None
         self.thr = self.zlo = self.zhi = self.amax = None
         self.counts = self.hits = None
@@ -208,7 +219,12 @@ class PwmAccumulator:
     @_on_device_of(1)
     def scan_max(self, x):
         pk = self.model._pack(x)
-        self.zmax = Fn.interp_unit_max(pk, self.prep, self.zmax)
+        if self.tc is not None:
+            if self.zmax is None:
+                self.zmax = torch.full((self.prep.U,), float("-inf"), dtype=torch.float32, device=pk.codes.device)
+            self.tc.unit_max(pk, self.zmax)
+        else:
+            self.zmax = Fn.interp_unit_max(pk, self.prep, self.zmax)
 
     def finish_max(self):
         if self.zmax is None:
@@ -223,22 +239,30 @@ class PwmAccumulator:
         if self.keep_seq_hits:
             seq_hit = torch.zeros((pk.B, self.prep.U), dtype=torch.uint8, device=pk.codes.device)
             self.seq_hits.append(seq_hit)
-        self.counts, self.hits = Fn.interp_pwm_count(pk, self.prep, self.thr, self.zlo, self.zhi, self.counts, self.hits,
-                                                     seq_hit)
+        if self.tc is not None:
+            if self.counts is None:
+                self.counts = torch.zeros((self.prep.U, 4, self.prep.F), dtype=torch.int64, device=pk.codes.device)
+                self.hits = torch.zeros(self.prep.U, dtype=torch.int64, device=pk.codes.device)
+            self.tc.pwm_count(pk, self.thr, self.zlo, self.zhi, self.counts, self.hits, seq_hit)
+        else:
+            self.counts, self.hits = Fn.interp_pwm_count(pk, self.prep, self.thr, self.zlo, self.zhi, self.counts, self.hits,
+                                                         seq_hit)
 
     def result(self):
         self.model.check_inputs()
+        if self.tc is not None:
+            self.tc.check()
         counts = self.counts.cpu().numpy()
         hits = self.hits.cpu().numpy()
         return pwm_from_counts(counts, hits), counts, hits
 
 
-def get_pwms_explainn_fused(data_loader, model, device, return_counts=False):
+def get_pwms_explainn_fused(data_loader, model, device, return_counts=False, backend="tc"):
     """PWMs straight from the sequences: same result as
     get_pwms_explainn(get_explainn_unit_activations(loader, model, device), sequences, filter_size)
     but the (N,U,S) float16 tensor never exists.  `data_loader` yields (seq, label) batches (or is a
-    single (N,4,L) tensor) and is iterated twice."""
-    acc = PwmAccumulator(model)
+    single (N,4,L) tensor) and is iterated twice.  `backend`: see PwmAccumulator."""
+    acc = PwmAccumulator(model, backend=backend)
 
     def batches():
         if isinstance(data_loader, torch.Tensor):

@@ -179,6 +179,31 @@ int explainn_interp_pwm_count(const uint32_t *codes, const uint32_t *nmask, long
                               const float *zhi, const float *thr, unsigned long long *counts,
                               unsigned long long *hits, unsigned char *seq_hit, void *scratch, cudaStream_t stream);
 
+/* ---- the two interpretation passes on the tensor cores, same results --------------------------------------------------
+ * Same reference lines and the SAME outputs, bit for bit, as explainn_interp_unit_max / explainn_interp_pwm_count
+ * (interpretation.py:187,203-214).  The tcgen05 GEMM of explainn_conv_pool_fwd_tc (images / shift from
+ * explainn_conv_tc_prepare with the model's eval BatchNorm, sign_of = NULL) gives every pre-activation to within delta[u]
+ * (explainn_interp_tc_bounds: w (U,4,F) raw filter, scale / shift (U) from explainn_conv_prepare); positions further than
+ * that from a decision (the running maximum in pass A, the float16 threshold bracket in pass B) are decided by the GEMM,
+ * the few others are re-evaluated in the canonical fp32 order (wq_t / shift of explainn_conv_prepare) by a resolve kernel.
+ *   zmax (U): in / out, the exact maximum so far (start at -inf); accumulates over chunks.
+ *   list_scratch: explainn_interp_tc_list_bytes(U) bytes (or more) of caller workspace for the positions to resolve;
+ *   *status (device int, zero it once): bit 0 / bit 1 set if pass A / pass B had more such positions than the list
+ *   holds -- the results of that call are then incomplete and the caller must redo it with the table entry points.
+ *   scratch (pass B): explainn_interp_pwm_count_scratch_bytes(B, L, U, F) bytes, as for explainn_interp_pwm_count. */
+int explainn_interp_tc_bounds(const float *w, const float *scale, const float *shift, int U, int F, float *delta,
+                              cudaStream_t stream);
+long long explainn_interp_tc_list_bytes(int U);
+int explainn_interp_unit_max_tc(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F,
+                                const void *images, const float *shift_rs, const float *delta, const float *wq_t,
+                                const float *shift, float *zmax, void *list_scratch, long long list_bytes, int *status,
+                                cudaStream_t stream);
+int explainn_interp_pwm_count_tc(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F,
+                                 const void *images, const float *shift_rs, const float *delta, const float *wq_t,
+                                 const float *shift, const float *zlo, const float *zhi, const float *thr,
+                                 unsigned long long *counts, unsigned long long *hits, unsigned char *seq_hit, void *scratch,
+                                 void *list_scratch, long long list_bytes, int *status, cudaStream_t stream);
+
 /* Per (sequence, unit): the maximum activation exp(z) (float32) and the FIRST position that attains it, the rule of
  * `torch.max(activations, dim=2)` (explainn/models/networks.py:228,281; the reference computes it for its ConvNet
  * baselines, BASELINE.json's north star asks for it from the ExplaiNN scan).  amax (B,U) fp32, apos (B,U) int32,

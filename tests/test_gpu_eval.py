@@ -127,8 +127,9 @@ def test_logits_and_unit_outputs_match_reference(name, backend):
     np.testing.assert_allclose(logits, g["logits"], rtol=1e-4, atol=1e-5 * np.abs(g["logits"]).max())
 
 
+@pytest.mark.parametrize("backend", ["tc", "lut"])
 @pytest.mark.parametrize("name", EVAL_GOLDENS)
-def test_pwm_counts_bit_exact(name):
+def test_pwm_counts_bit_exact(name, backend):
     from oracle import canonical as cn
     from explainn_b200 import interpretation
     g = load_golden(name)
@@ -138,7 +139,8 @@ def test_pwm_counts_bit_exact(name):
     xt = torch.from_numpy(x)
     # several uneven chunks so that the accumulate path is exercised
     chunks = [xt[:5], xt[5:6], xt[6:]]
-    pwm, counts, hits = interpretation.get_pwms_explainn_fused([(c, None) for c in chunks], m, DEV, return_counts=True)
+    pwm, counts, hits = interpretation.get_pwms_explainn_fused([(c, None) for c in chunks], m, DEV, return_counts=True,
+                                                               backend=backend)
     a16 = cn.activations_fp16(z)
     ref_counts, ref_hits, ref_thr = cn.pwm_counts(a16, x, F)
     assert np.array_equal(counts, ref_counts)
@@ -146,7 +148,7 @@ def test_pwm_counts_bit_exact(name):
     assert np.array_equal(pwm, cn.pwm_from_counts_hits(ref_counts, ref_hits))
     # the reference's own output
     assert np.array_equal(pwm, g["pwm"])
-    acc = interpretation.PwmAccumulator(m)
+    acc = interpretation.PwmAccumulator(m, backend=backend)
     acc.scan_max(xt.to(DEV))
     acc.finish_max()
     assert np.array_equal(acc.zmax.cpu().numpy(), z.max(axis=(0, 2)))

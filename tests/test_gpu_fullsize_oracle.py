@@ -52,6 +52,9 @@ def test_cfg5_forward_vs_port():
     m.check_inputs()
 
 
+_ORACLE_CACHE = {}
+
+
 def _oracle_counts(m, x, F, chunk=2048):
     """Canonical activations (C restatement, chunked) -> float16 -> global maxima -> integer counts."""
     from oracle import canonical as cn
@@ -74,10 +77,12 @@ def _oracle_counts(m, x, F, chunk=2048):
     return counts, hits, amax, np.concatenate(seq_hit, 0)
 
 
+@pytest.mark.parametrize("backend", ["tc", "lut"])
 @pytest.mark.parametrize("regime", ["sparse", "dense"])
-def test_cfg4_pwm_counts_bit_exact(regime):
+def test_cfg4_pwm_counts_bit_exact(regime, backend):
     """Interpretation sweep shape (num_cnns=300, L=251, filter 19), 16,384 sequences with 1 % N columns: counts, hit
-    counters, per-sequence hit flags and PWMs equal to oracle.canonical (interpretation.py:176-227) bit for bit.
+    counters, per-sequence hit flags and PWMs equal to oracle.canonical (interpretation.py:176-227) bit for bit, for the
+    tensor-core passes (backend "tc": GEMM decides, near-boundary positions re-evaluated canonically) and the table kernel.
     dense:  default-initialised weights -- 0.5 x max lies inside the bulk of the activation distribution: 99 % of the
             (sequence, unit) pairs and 4.8 % of all positions hit (54 M windows);
     sparse: the same filters behind a BatchNorm gain of 4, which stretches the distribution so that only the tail
@@ -92,11 +97,13 @@ def test_cfg4_pwm_counts_bit_exact(regime):
             m.linears[1].weight.fill_(4.0)
     m = m.to(DEV).eval()
     x = onehot_from_codes(random_codes(N, L, 1714, n_frac=0.01))
-    ref_counts, ref_hits, ref_amax, ref_seq_hit = _oracle_counts(m, x, F)
+    if regime not in _ORACLE_CACHE:          # ~40 s of host time per regime: shared by the two backends
+        _ORACLE_CACHE[regime] = _oracle_counts(m, x, F)
+    ref_counts, ref_hits, ref_amax, ref_seq_hit = _ORACLE_CACHE[regime]
     pair_rate = ref_seq_hit.mean()
     assert (pair_rate >= 0.05) if regime == "dense" else (0 < pair_rate < 0.05), pair_rate
     xt = torch.from_numpy(x)
-    acc = interpretation.PwmAccumulator(m)
+    acc = interpretation.PwmAccumulator(m, backend=backend)
     acc.keep_seq_hits = True
     with torch.no_grad():
         for i in range(0, N, 4096):
@@ -110,3 +117,7 @@ def test_cfg4_pwm_counts_bit_exact(regime):
     assert np.array_equal(counts, ref_counts)
     assert np.array_equal(torch.cat(acc.seq_hits, 0).cpu().numpy(), ref_seq_hit)
     assert np.array_equal(pwm, cn.pwm_from_counts_hits(ref_counts, ref_hits))
+    if backend == "tc":
+        # the tensor-core passes decide almost everything; what they hand to the canonical re-evaluation is a sliver
+        n_resolved = int(acc.tc.list[:4].view(torch.int32).item())          # entries of the last pass-B call
+        assert n_resolved < 1e-3 * 4096 * U * (L - F + 1), n_resolved
