@@ -417,6 +417,38 @@ struct ArgmaxSink {
 
 template <class Sink> struct NeedsSeq { static constexpr bool value = false; };
 
+// One position whose window contains an N column: only the 4-tap groups that contain the N are summed tap by tap (the
+// table entry's own expression with +0 for the N taps), the other groups keep their table lookup -- bit-identical to the
+// oracle.  Deliberately not inlined and not unrolled: the sequence of a warp is shared by its lanes, so the call is
+// warp-uniform, and the 21-position unrolled fast path of the caller stays small.
+template <int G>
+__device__ __noinline__ float scan_slow_position(const uint32_t *cw, const uint32_t *mw, int t, uint32_t nm, int F, const unsigned char *tbl,
+                                                 const float *wq, int lane)
+{
+    float v = 0.0f;
+#pragma unroll 1
+    for (int g = 0; g < G; ++g) {
+        const uint32_t o = 2u * (uint32_t)(t + 4 * g);
+        const uint32_t km = __funnelshift_r(cw[o >> 5], cw[(o >> 5) + 1], o & 31u) & 0xFFu;
+        const uint32_t nib = (nm >> (4 * g)) & 15u;
+        float tg;
+        if (nib == 0u) {
+            tg = lds_f32(tbl, (uint32_t)lane * 4u + (km << 7) + (uint32_t)g * TBL_GROUP_BYTES);
+        } else {
+            tg = 0.0f;
+#pragma unroll 1
+            for (int jj = 0; jj < 4; ++jj) {
+                const int k = 4 * g + jj;
+                float w = 0.0f;
+                if (k < F && !((nib >> jj) & 1u)) w = wq[(((km >> (2 * jj)) & 3u) * F + k) * XB_UT + lane];
+                tg = jj == 0 ? w : __fadd_rn(tg, w);
+            }
+        }
+        v = g == 0 ? tg : __fadd_rn(v, tg);
+    }
+    return v;
+}
+
 // ----------------------------------------------------------------------------------------------
 // The scan kernel.  grid = one CTA per SM; the flattened (tile, sequence) space is split evenly.
 // ----------------------------------------------------------------------------------------------
@@ -553,28 +585,9 @@ __global__ void __launch_bounds__(NW * 32, 1) conv_scan_kernel(const ConvArgs a,
 #pragma unroll
                         for (int g = 1; g < G; ++g) v = __fadd_rn(v, lds_f32(tbl, addr[j + 4 * g] + g * TBL_GROUP_BYTES));
                     } else {
-                        // an N column under this window: only the 4-tap groups that contain it are summed tap by tap
-                        // (same expression as the table entry, with +0 for the N taps); the others keep their lookup
-                        v = 0.0f;
-#pragma unroll
-                        for (int g = 0; g < G; ++g) {
-                            const uint32_t nib = (nm >> (4 * g)) & 15u;
-                            float tg;
-                            if (nib == 0u) {
-                                tg = lds_f32(tbl, addr[j + 4 * g] + g * TBL_GROUP_BYTES);
-                            } else {
-                                const uint32_t km = (addr[j + 4 * g] - lane_base) >> 7;
-                                tg = 0.0f;
-#pragma unroll
-                                for (int jj = 0; jj < 4; ++jj) {
-                                    const int k = 4 * g + jj;
-                                    float w = 0.0f;
-                                    if (k < a.F && !((nib >> jj) & 1u)) w = wq[(((km >> (2 * jj)) & 3u) * a.F + k) * XB_UT + lane];
-                                    tg = jj == 0 ? w : __fadd_rn(tg, w);
-                                }
-                            }
-                            v = g == 0 ? tg : __fadd_rn(v, tg);
-                        }
+                        // an N column under this window (rare): evaluated out of line, so that the unrolled fast path
+                        // stays small enough for the instruction cache
+                        v = scan_slow_position<G>(cw, mw, t0 + j, nm, a.F, tbl, wq, lane);
                     }
                     acc[j] = v;
                 }

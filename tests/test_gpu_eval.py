@@ -222,9 +222,11 @@ def test_empty_batch_and_errors():
     with pytest.raises(ValueError):
         m(torch.zeros(2, 4, 61, device=DEV))
     with pytest.raises(NotImplementedError):
-        networks.ExplaiNN(8, 60, 2, 19, num_fc=3)
+        networks.ExplaiNN(8, 60, 2, 25)                      # filter_size > 24: limit of the k-mer tables, named in the message
     with pytest.raises(NotImplementedError):
-        networks.ExplaiNN(8, 60, 2, 19, pool_size=5, pool_stride=5)
+        networks.ExplaiNN(8, 4096, 2, 19)                    # input_length > 2048
+    with pytest.raises(ValueError):
+        networks.ExplaiNN(8, 20, 2, 19, pool_size=7)         # too short for one pool window
 
 
 def test_tc_fp16_weight_mode_stated_tolerance():
