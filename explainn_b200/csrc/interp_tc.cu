@@ -39,6 +39,8 @@ struct ItArgs {
     const float *delta;                 // (U)
     // pass A
     const float *zmax_in;               // (U) exact maximum so far (-inf at the start)
+    uint32_t *vrun;                     // (U) running maximum of the raw accumulators, order-preserving encoding, shared by
+                                        //     all CTAs (seeded from zmax_in): keeps the candidate lists short
     // pass B
     const float *zlo, *zhi;             // (U) bracket of the float16 cut-over (interp_thresholds)
     uint32_t *hitbits;                  // (B,U,W)
@@ -76,6 +78,13 @@ __device__ __forceinline__ float fmax3i(float a, float b, float c)
     asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
     return d;
 }
+
+__device__ __forceinline__ uint32_t ord_enc(float f)
+{
+    const uint32_t b = __float_as_uint(f);
+    return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+__device__ __forceinline__ float ord_dec(uint32_t e) { return __uint_as_float((e & 0x80000000u) ? (e & 0x7FFFFFFFu) : ~e); }
 
 // append one entry; lanes of a warp that arrive together share one atomic
 __device__ __forceinline__ void it_append(const ItArgs &a, uint32_t n, uint32_t u, uint32_t s)
@@ -258,13 +267,16 @@ __global__ void __launch_bounds__(IT_THREADS + 64, 1) interp_tc_kernel(const ItA
                 const bool uvalid = u < a.U;
                 float sh = 0.f, rs = 1.f, dl = 0.f;
                 if (uvalid) { sh = __ldg(a.shift_rs + u); rs = __ldg(a.shift_rs + a.U + u); dl = __ldg(a.delta + u); }
+                float grun = -INFINITY;            // the unit's running maximum over ALL CTAs (may be stale: any lower bound works)
+                if (MODE == IT_MAX && uvalid) grun = ord_dec(__ldcg(a.vrun + u));
                 mbar_wait(&tmem_full[grp], use & 1);
                 tc_fence_after();
                 const bool active = (mt0 + m) * IT_M + 32 * (warp & 3) < a.U && cvalid > 0;      // warp-uniform
                 if (active) {
                     if (MODE == IT_MAX) {
                         // ---- pass A: running maximum of the raw accumulators; near-maximal positions are listed ----
-                        float run = run_s[m * IT_THREADS + threadIdx.x];
+                        float run = fmaxf(run_s[m * IT_THREADS + threadIdx.x], grun);
+                        const float run_in = run;
                         const float tol = __fdiv_rn(2.0f * dl, rs);            // 2 delta in accumulator units (rs > 0 in eval mode)
                         uint32_t rr[2][32];
                         tc_ld16_nowait(taddr, rr[0]);
@@ -298,6 +310,7 @@ __global__ void __launch_bounds__(IT_THREADS + 64, 1) interp_tc_kernel(const ItA
                             run = fmaxf(run, mx);
                         }
                         run_s[m * IT_THREADS + threadIdx.x] = run;
+                        if (uvalid && run > run_in) atomicMax(a.vrun + u, ord_enc(run));
                     } else {
                         // ---- pass B: sure / possible hit bits by comparing the raw accumulators with the scaled bracket ----
                         float hi_t = INFINITY, lo_t = INFINITY;
@@ -394,17 +407,15 @@ __device__ float canon_z(const uint32_t *__restrict__ cw, const uint32_t *__rest
     return __fadd_rn(v, shift);
 }
 
-__device__ __forceinline__ uint32_t ord_enc(float f)
-{
-    const uint32_t b = __float_as_uint(f);
-    return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
-}
-__device__ __forceinline__ float ord_dec(uint32_t e) { return __uint_as_float((e & 0x80000000u) ? (e & 0x7FFFFFFFu) : ~e); }
-
-__global__ void it_enc_kernel(const float *__restrict__ zmax, int U, uint32_t *__restrict__ zenc)
+__global__ void it_enc_kernel(const float *__restrict__ zmax, const float *__restrict__ shift_rs, int U, uint32_t *__restrict__ zenc,
+                              uint32_t *__restrict__ vrun)
 {
     const int u = blockIdx.x * blockDim.x + threadIdx.x;
-    if (u < U) zenc[u] = ord_enc(zmax[u]);
+    if (u >= U) return;
+    const float zi = zmax[u];
+    zenc[u] = ord_enc(zi);
+    // the same maximum in accumulator units (z = acc * rs + shift)
+    vrun[u] = ord_enc(zi > -INFINITY ? __fdiv_rn(__fsub_rn(zi, shift_rs[u]), shift_rs[U + u]) : -INFINITY);
 }
 
 struct ResolveArgs {
@@ -502,15 +513,16 @@ extern "C" int explainn_interp_tc_bounds(const float *w, const float *scale, con
     return xb_check_launch("interp_tc_bounds");
 }
 
-extern "C" long long explainn_interp_tc_list_bytes(int U) { return 256 + (long long)((U + 63) / 64 * 64) * 4 + (8LL << 20) * 8; }
+extern "C" long long explainn_interp_tc_list_bytes(int U) { return 256 + (long long)((U + 63) / 64 * 64) * 8 + (8LL << 20) * 8; }
 
-static void it_list_layout(void *list_scratch, long long list_bytes, int U, unsigned int **count, uint32_t **zenc, uint2 **list,
-                           unsigned int *cap)
+static void it_list_layout(void *list_scratch, long long list_bytes, int U, unsigned int **count, uint32_t **zenc, uint32_t **vrun,
+                           uint2 **list, unsigned int *cap)
 {
     unsigned char *base = static_cast<unsigned char *>(list_scratch);
     *count = reinterpret_cast<unsigned int *>(base);
     *zenc = reinterpret_cast<uint32_t *>(base + 256);
-    const long long off = 256 + (long long)((U + 63) / 64 * 64) * 4;
+    *vrun = *zenc + (U + 63) / 64 * 64;
+    const long long off = 256 + (long long)((U + 63) / 64 * 64) * 8;
     *list = reinterpret_cast<uint2 *>(base + off);
     const long long room = (list_bytes - off) / 8;
     *cap = room > 0 ? (unsigned int)std::min<long long>(room, 0x7FFFFFFFLL) : 0u;
@@ -523,7 +535,7 @@ extern "C" int explainn_interp_unit_max_tc(const uint32_t *codes, const uint32_t
 {
     XB_REQUIRE(codes && nmask && images && shift_rs && delta && wq_t && shift && zmax && list_scratch && status && B >= 0 && U >= 1,
                "interp_unit_max_tc: bad argument");
-    XB_REQUIRE(list_bytes >= 256 + (long long)((U + 63) / 64 * 64) * 4 + 8 * 1024, "interp_unit_max_tc: list scratch too small");
+    XB_REQUIRE(list_bytes >= 256 + (long long)((U + 63) / 64 * 64) * 8 + 8 * 1024, "interp_unit_max_tc: list scratch too small");
     XB_REQUIRE(U <= 65535, "interp_unit_max_tc: at most 65535 units");
     if (B == 0) return XB_OK;
     ItArgs a{};
@@ -531,10 +543,10 @@ extern "C" int explainn_interp_unit_max_tc(const uint32_t *codes, const uint32_t
     int rc = it_fill(&a, codes, nmask, B, L, U, F, images, shift_rs, delta, &smem, &grid);
     if (rc != XB_OK) return rc;
     uint32_t *zenc;
-    it_list_layout(list_scratch, list_bytes, U, &a.count, &zenc, &a.list, &a.cap);
+    it_list_layout(list_scratch, list_bytes, U, &a.count, &zenc, &a.vrun, &a.list, &a.cap);
     a.zmax_in = zmax;
     cudaMemsetAsync(a.count, 0, 4, stream);
-    it_enc_kernel<<<(U + 127) / 128, 128, 0, stream>>>(zmax, U, zenc);
+    it_enc_kernel<<<(U + 127) / 128, 128, 0, stream>>>(zmax, shift_rs, U, zenc, a.vrun);
     cudaError_t e = cudaFuncSetAttribute(interp_tc_kernel<IT_MAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) {
         xb_set_error("interp_unit_max_tc: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
@@ -556,7 +568,7 @@ extern "C" int explainn_interp_pwm_count_tc(const uint32_t *codes, const uint32_
     XB_REQUIRE(codes && nmask && images && shift_rs && delta && wq_t && shift && zlo && zhi && thr && counts && hits && scratch &&
                    list_scratch && status && B >= 0 && U >= 1,
                "interp_pwm_count_tc: bad argument");
-    XB_REQUIRE(list_bytes >= 256 + (long long)((U + 63) / 64 * 64) * 4 + 8 * 1024, "interp_pwm_count_tc: list scratch too small");
+    XB_REQUIRE(list_bytes >= 256 + (long long)((U + 63) / 64 * 64) * 8 + 8 * 1024, "interp_pwm_count_tc: list scratch too small");
     XB_REQUIRE(U <= 65535, "interp_pwm_count_tc: at most 65535 units");
     if (B == 0) return XB_OK;
     ItArgs a{};
@@ -564,7 +576,7 @@ extern "C" int explainn_interp_pwm_count_tc(const uint32_t *codes, const uint32_
     int rc = it_fill(&a, codes, nmask, B, L, U, F, images, shift_rs, delta, &smem, &grid);
     if (rc != XB_OK) return rc;
     uint32_t *zenc;
-    it_list_layout(list_scratch, list_bytes, U, &a.count, &zenc, &a.list, &a.cap);
+    it_list_layout(list_scratch, list_bytes, U, &a.count, &zenc, &a.vrun, &a.list, &a.cap);
     long long off_bmask, off_bits;
     xb_pwm_count_layout(B, L, U, F, &off_bmask, &off_bits);
     unsigned char *base = static_cast<unsigned char *>(scratch);
