@@ -669,6 +669,15 @@ def extras(torch, dev, model, trainer, data, labels, batch, _cabi, rank=0, world
         e.record()
         torch.cuda.synchronize()
         k_ms = s.elapsed_time(e) / 10
+        # the stated-tolerance mode: one fp16 piece per weight (half the tensor-core work; tests/test_gpu_eval.py: 2e-3)
+        Fn.conv_pool_fwd_tc(pk, tcp, fp16_weights=True)
+        torch.cuda.synchronize()
+        s.record()
+        for i in range(10):
+            Fn.conv_pool_fwd_tc(pk, tcp, fp16_weights=True)
+        e.record()
+        torch.cuda.synchronize()
+        k16_ms = s.elapsed_time(e) / 10
     bytes_inf = IB * ((L + 3) // 4 + (L + 7) // 8 + 4 * U * P)
     ach = bytes_inf / (k_ms * 1e-3) / 1e9
     n_mt, K16 = (U + 127) // 128, (4 * F + 15) // 16
@@ -680,7 +689,10 @@ def extras(torch, dev, model, trainer, data, labels, batch, _cabi, rank=0, world
                                          "algorithmic_bytes_per_launch": bytes_inf, "executed_flops": executed,
                                          "achieved_tflops": executed / (k_ms * 1e-3) / 1e12,
                                          "frac_of_tensor_peak": (executed / (k_ms * 1e-3) / 1e12 / tpeak) if tpeak else None,
-                                         "output": "325 MB of pooled activations per launch: larger than the 126 MB L2"}}
+                                         "output": "325 MB of pooled activations per launch: larger than the 126 MB L2",
+                                         "fp16_weight_mode": {"avg_launch_ms": k16_ms, "sequences_per_sec": IB / (k16_ms * 1e-3),
+                                                              "frac_of_hbm_peak": bytes_inf / (k16_ms * 1e-3) / 1e9 / hbm_peak,
+                                                              "tolerance": "2e-3 relative on pooled activations / logits (stated, tested)"}}}
     model.train()
 
     # ---- input encoding and PWM scoring ----------------------------------------------
