@@ -87,7 +87,7 @@ SIGNATURES = {
     "explainn_p2p_open": [_P, _P],
     "explainn_p2p_close": [_P],
     "explainn_p2p_error": [_P, _P],
-    "explainn_p2p_adam_step": [_P, _P, _P, _LL, _P, _P, _P, _I, _I, _ULL, _F, _F, _F, _F, C.c_double, _P],
+    "explainn_p2p_adam_step": [_P, _P, _P, _LL, _LL, _P, _I, _P, _P, _I, _I, _ULL, _F, _F, _F, _F, C.c_double, _P],
 }
 _RESTYPES = {
     "explainn_last_error": C.c_char_p,

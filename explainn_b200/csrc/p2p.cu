@@ -38,7 +38,8 @@ struct P2pArgs {
     unsigned int *ticket;                          // local block counter
     unsigned int *error;                           // local error word
     const float *step;                             // Adam step count (already incremented)
-    long long n;
+    long long n;                                   // floats of the range this call updates
+    long long off;                                 // its first float inside the flat buffers
     int world, rank;
     unsigned long long seq;                        // step sequence number, identical on all ranks, > 0, increasing
     unsigned long long timeout_ns;
@@ -99,8 +100,8 @@ __global__ void __launch_bounds__(256) p2p_adam_kernel(const P2pArgs a)
     const float bc2s = (float)sqrt(bc2);
     const float w1 = 1.0f - a.b1, w2 = 1.0f - a.b2;
     const float scale = 1.0f / (float)a.world;
-    const long long n4 = a.n >> 2;             // the flat buffers are 16-byte aligned and padded to multiples of 4
-    const long long lo = n4 * a.rank / a.world, hi = n4 * (a.rank + 1) / a.world;      // my slice, in float4 units
+    const long long n4 = a.n >> 2, o4 = a.off >> 2;      // the flat buffers are 16-byte aligned and padded to multiples of 4
+    const long long lo = o4 + n4 * a.rank / a.world, hi = o4 + n4 * (a.rank + 1) / a.world;      // my slice, in float4 units
     float4 *pl = reinterpret_cast<float4 *>(a.p[a.rank]);
     for (long long i = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += (long long)gridDim.x * blockDim.x) {
         float4 gs = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -230,18 +231,19 @@ extern "C" int explainn_p2p_error(const unsigned long long *flags, int *out)
     return XB_OK;
 }
 
-extern "C" int explainn_p2p_adam_step(float *const *params, float *exp_avg, float *exp_avg_sq, long long n, float *step,
-                                      const float *const *grads, unsigned long long *const *flags, int world, int rank,
-                                      unsigned long long seq, float lr, float beta1, float beta2, float eps,
+extern "C" int explainn_p2p_adam_step(float *const *params, float *exp_avg, float *exp_avg_sq, long long offset, long long n,
+                                      float *step, int tick, const float *const *grads, unsigned long long *const *flags,
+                                      int world, int rank, unsigned long long seq, float lr, float beta1, float beta2, float eps,
                                       double timeout_s, cudaStream_t stream)
 {
-    XB_REQUIRE(params && exp_avg && exp_avg_sq && step && grads && flags && n >= 0, "p2p_adam_step: null pointer");
+    XB_REQUIRE(params && exp_avg && exp_avg_sq && step && grads && flags && n >= 0 && offset >= 0, "p2p_adam_step: null pointer");
+    XB_REQUIRE((offset & 3) == 0, "p2p_adam_step: offset must be a multiple of 4 elements");
     XB_REQUIRE(world >= 1 && world <= P2P_MAX_WORLD && rank >= 0 && rank < world && seq > 0, "p2p_adam_step: world %d rank %d seq %llu",
                world, rank, seq);
     XB_REQUIRE((n & 3) == 0 && (((uintptr_t)exp_avg | (uintptr_t)exp_avg_sq) & 15) == 0,
                "p2p_adam_step: buffers must be 16-byte aligned and padded to a multiple of 4 elements");
     P2pArgs a{};
-    a.m = exp_avg; a.v = exp_avg_sq; a.n = n; a.step = step; a.world = world; a.rank = rank; a.seq = seq;
+    a.m = exp_avg; a.v = exp_avg_sq; a.n = n; a.off = offset; a.step = step; a.world = world; a.rank = rank; a.seq = seq;
     a.lr = lr; a.b1 = beta1; a.b2 = beta2; a.eps = eps;
     a.timeout_ns = timeout_s > 0 ? (unsigned long long)(timeout_s * 1e9) : 0ull;
     for (int q = 0; q < world; ++q) {
@@ -254,7 +256,7 @@ extern "C" int explainn_p2p_adam_step(float *const *params, float *exp_avg, floa
     // the ticket counter and the error word live behind the two flag rows of this rank's own flag buffer
     a.ticket = reinterpret_cast<unsigned int *>(flags[rank] + 2 * P2P_MAX_WORLD);
     a.error = a.ticket + 2;
-    p2p_tick_kernel<<<1, 1, 0, stream>>>(step);
+    if (tick) p2p_tick_kernel<<<1, 1, 0, stream>>>(step);
     long long blocks = (n / 4 / world + 255) / 256;
     const long long cap = 2LL * xb_num_sms();
     if (blocks > cap) blocks = cap;

@@ -212,10 +212,11 @@ class PeerGradients:
             self.ok = False
             self.error = self.error or "a peer could not map the buffers"
 
-    def slice_range(self, n_floats):
-        """[lo, hi) in floats of the parameter slice this rank owns (same split as csrc/p2p.cu)."""
+    def slice_range(self, n_floats, offset=0):
+        """[lo, hi) in floats of the slice this rank owns inside the range [offset, offset + n_floats) of the flat
+        buffers (same split as csrc/p2p.cu)."""
         n4 = n_floats // 4
-        return 4 * (n4 * self.rank // self.world), 4 * (n4 * (self.rank + 1) // self.world)
+        return offset + 4 * (n4 * self.rank // self.world), offset + 4 * (n4 * (self.rank + 1) // self.world)
 
     def check(self):
         """Raise if a step of the peer-memory optimizer kernel gave up waiting for a rank (synchronises)."""

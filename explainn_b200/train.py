@@ -97,6 +97,12 @@ class FusedTrainer:
             self.flat_g = torch.zeros(off, dtype=torch.float32, device=dev)
             self.flat_p = torch.zeros(off, dtype=torch.float32, device=dev)
         self.p2p_timeout_s = float(os.environ.get("XB_P2P_TIMEOUT_S", "1800"))
+        # the FC-stack part of the peer-memory step overlaps the conv backward (XB_P2P_OVERLAP=0: one call after it)
+        self.p2p_overlap = os.environ.get("XB_P2P_OVERLAP", "1") != "0"
+        self._p2p_fc_started = False
+        if self.p2p is not None:
+            self._p2p_stream = torch.cuda.Stream(dev)
+            self._p2p_ev, self._p2p_ev2 = torch.cuda.Event(), torch.cuda.Event()
         self.flat_m = torch.zeros(off, dtype=torch.float32, device=dev)
         self.flat_v = torch.zeros(off, dtype=torch.float32, device=dev)
         self.step_t = torch.zeros(1, dtype=torch.float32, device=dev)
@@ -159,13 +165,54 @@ class FusedTrainer:
     def _between(self, ws, gpool, params, grads, wrt_unit):
         """Runs after the FC-stack backward.  Eager: start the all-reduce of the FC-stack gradients.  During graph
         capture (world > 1): end the first graph here; the conv backward is captured as a second graph."""
-        if self.world == 1 or not self.dp_overlap or self.p2p is not None:
+        if self.world == 1:
+            return True
+        if self.p2p is not None:
+            if not self.p2p_overlap:
+                return True
+            if torch.cuda.is_current_stream_capturing():
+                self._split = (ws, gpool)
+                return False
+            self._p2p_fc_part()             # eager: the FC-stack update starts here, beside the conv backward
+            return True
+        if not self.dp_overlap:
             return True
         if torch.cuda.is_current_stream_capturing():
             self._split = (ws, gpool)
             return False
         self._start_fc_allreduce()
         return True
+
+    # ---- peer-memory optimizer step in two parts ------------------------------------------------------------
+    def _p2p_call(self, offset, count, tick, seq):
+        import ctypes
+        g = self.optimizer.param_groups[0]
+        b1, b2 = g["betas"]
+        call("explainn_p2p_adam_step", ctypes.cast(self.p2p.p_array, ctypes.c_void_p), ptr(self.flat_m), ptr(self.flat_v),
+             offset, count, ptr(self.step_t), tick, ctypes.cast(self.p2p.g_array, ctypes.c_void_p),
+             ctypes.cast(self.p2p.f_array, ctypes.c_void_p), self.world, self.p2p.rank, seq, float(g["lr"]), float(b1), float(b2),
+             float(g["eps"]), self.p2p_timeout_s, stream())
+
+    def _p2p_fc_part(self):
+        """Reduce-scatter + Adam + all-gather of everything behind the conv / BatchNorm-1 tensors (99 % of the
+        parameters; their gradients are final once the FC-stack backward is done) on a side stream, so that it runs
+        beside the conv backward of this rank and of its peers."""
+        main = torch.cuda.current_stream()
+        self._p2p_ev.record(main)
+        self._p2p_stream.wait_event(self._p2p_ev)
+        with torch.cuda.stream(self._p2p_stream):
+            self._p2p_call(self.n_conv, self.n - self.n_conv, 1, 2 * (self.steps_done + 1) - 1)
+            self._p2p_ev2.record(self._p2p_stream)
+        self._p2p_fc_started = True
+
+    def _p2p_finish(self):
+        """The conv / BatchNorm-1 part after the conv backward (and after the FC part: calls must not overlap)."""
+        if self._p2p_fc_started:
+            torch.cuda.current_stream().wait_event(self._p2p_ev2)
+            self._p2p_call(0, self.n_conv, 0, 2 * (self.steps_done + 1))
+        else:
+            self._p2p_call(0, self.n, 1, 2 * (self.steps_done + 1))
+        self._p2p_fc_started = False
 
     def _start_fc_allreduce(self):
         d = _dist()
@@ -253,7 +300,11 @@ class FusedTrainer:
             c.graph.replay()
             _cabi.LAUNCHES += c.launches
             if c.graph2 is not None:
-                self._start_fc_allreduce()          # NCCL works on the FC-stack gradients while the conv backward runs
+                # the FC-stack gradients are final: their reduction (peer-memory kernel or NCCL) runs beside the conv backward
+                if self.p2p is not None:
+                    self._p2p_fc_part()
+                else:
+                    self._start_fc_allreduce()
                 c.graph2.replay()
                 _cabi.LAUNCHES += c.launches2
             loss = c.gloss.clone()
@@ -262,11 +313,7 @@ class FusedTrainer:
         g = self.optimizer.param_groups[0]
         b1, b2 = g["betas"]
         if self.p2p is not None:
-            import ctypes
-            call("explainn_p2p_adam_step", ctypes.cast(self.p2p.p_array, ctypes.c_void_p), ptr(self.flat_m), ptr(self.flat_v),
-                 self.n, ptr(self.step_t), ctypes.cast(self.p2p.g_array, ctypes.c_void_p),
-                 ctypes.cast(self.p2p.f_array, ctypes.c_void_p), self.world, self.p2p.rank, self.steps_done + 1, float(g["lr"]),
-                 float(b1), float(b2), float(g["eps"]), self.p2p_timeout_s, stream())
+            self._p2p_finish()
             self.steps_done += 1
             return loss
         scale = self._finish_allreduce()     # SUM over ranks (NCCL over NVLink); Adam divides by the world size
@@ -297,11 +344,15 @@ class FusedTrainer:
             # the Adam moments of a slice live on its owner (csrc/p2p.cu): gather them so that optimizer.state_dict()
             # is complete on every rank
             self.check_health()
-            lo, hi = self.p2p.slice_range(self.n)
+            torch.cuda.current_stream().wait_stream(self._p2p_stream)
+            ranges = ([self.p2p.slice_range(self.n_conv), self.p2p.slice_range(self.n - self.n_conv, self.n_conv)]
+                      if self.p2p_overlap else [self.p2p.slice_range(self.n)])
+            own = torch.zeros(self.n, dtype=torch.bool, device=self.flat_m.device)
+            for lo, hi in ranges:
+                own[lo:hi] = True
             d = _dist()
             for buf in (self.flat_m, self.flat_v):
-                buf[:lo].zero_()
-                buf[hi:].zero_()
+                buf.mul_(own)
                 d.all_reduce(buf, op=d.ReduceOp.SUM)
         for p in self.params:
             self.optimizer.state[p]["step"] = torch.tensor(float(self.steps_done))

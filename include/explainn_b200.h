@@ -378,7 +378,10 @@ int explainn_adam_step(float *param, const float *grad, float *exp_avg, float *e
  * parameter buffer.  params[q] / grads[q] / flags[q], q < world: device pointers to rank q's flat parameter buffer,
  * flat gradient buffer and flag buffer (explainn_p2p_flag_bytes() bytes, zero-initialised once), valid in THIS process
  * (the caller opens the peers' buffers through CUDA IPC); index `rank` holds the local ones.  The three arrays
- * themselves are host arrays.  n floats per buffer, 16-byte aligned, n % 4 == 0; *step (device) is incremented first.
+ * themselves are host arrays.  The call updates the floats [offset, offset + n) of the flat buffers (16-byte aligned,
+ * offset % 4 == n % 4 == 0), split into `world` slices; *step (device) is incremented first when tick != 0 -- a step may
+ * be issued as several calls over disjoint ranges (the FC-stack gradients are final before the conv backward runs, so
+ * their update can overlap it), the first with tick = 1, each with its own seq.  Calls on one GPU must not overlap in time.
  * The moments of slices other than `rank` are not touched.  seq: the same strictly increasing positive number on every
  * rank for every step.  All ranks must call it once per step.  A late peer is waited for (never a trap); after
  * timeout_s seconds (0 = wait for ever) the kernel gives up, sets the error word that explainn_p2p_error reads
@@ -392,8 +395,8 @@ int explainn_p2p_open(const unsigned char *handle, void **out);
 int explainn_p2p_close(void *p);
 long long explainn_p2p_flag_bytes(void);
 int explainn_p2p_error(const unsigned long long *flags, int *out);
-int explainn_p2p_adam_step(float *const *params, float *exp_avg, float *exp_avg_sq, long long n, float *step,
-                           const float *const *grads, unsigned long long *const *flags, int world, int rank,
+int explainn_p2p_adam_step(float *const *params, float *exp_avg, float *exp_avg_sq, long long offset, long long n,
+                           float *step, int tick, const float *const *grads, unsigned long long *const *flags, int world, int rank,
                            unsigned long long seq, float lr, float beta1, float beta2, float eps, double timeout_s,
                            cudaStream_t stream);
 

@@ -70,8 +70,11 @@ if p2p:
     v1 = v0 * 0.999 + flat * flat * 0.001
     p1 = p0 - (1e-2 / (1 - 0.9 ** t)) * (m1 / (v1.sqrt() / (1 - 0.999 ** t) ** 0.5 + 1e-8))
     assert float((tr.flat_p - p1).abs().max()) <= 1e-6 * max(float(p1.abs().max()), 1.0), "fused Adam update"
-    lo, hi = tr.p2p.slice_range(tr.n)                # ... and this rank's slice of the moments
-    assert float((tr.flat_m[lo:hi] - m1[lo:hi]).abs().max()) <= 1e-6 * max(float(m1.abs().max()), 1e-30), "exp_avg slice"
+    # ... and this rank's slices of the moments (two ranges when the FC-stack part overlaps the conv backward)
+    rngs = ([tr.p2p.slice_range(tr.n_conv), tr.p2p.slice_range(tr.n - tr.n_conv, tr.n_conv)] if tr.p2p_overlap
+            else [tr.p2p.slice_range(tr.n)])
+    for lo, hi in rngs:
+        assert float((tr.flat_m[lo:hi] - m1[lo:hi]).abs().max()) <= 1e-6 * max(float(m1.abs().max()), 1e-30), "exp_avg slice"
     tr.check_health()
 else:
     got = [v / world for v in tr.views_g]            # the flat buffer holds the SUM over ranks; Adam applies 1/world
@@ -94,7 +97,7 @@ dist.destroy_process_group()
 '''
 
 
-@pytest.mark.parametrize("overlap", ["0", "1", "p2p"])
+@pytest.mark.parametrize("overlap", ["0", "1", "p2p", "p2p_serial"])
 @pytest.mark.parametrize("mode", ["eager", "graph"])
 def test_two_gpu_step_allreduce(tmp_path, mode, overlap):
     if torch.cuda.device_count() < 2:
@@ -104,13 +107,15 @@ def test_two_gpu_step_allreduce(tmp_path, mode, overlap):
     out = tmp_path / "out.txt"
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
            "--master-port", "29533", str(script), ROOT, str(out), mode]
-    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300, env=dict(os.environ, XB_DP_OVERLAP="1" if overlap == "1" else "0", XB_P2P_ADAM="1" if overlap == "p2p" else "0"))      # "0" / "1": NCCL all-reduce (plain / overlapped)
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300, env=dict(os.environ, XB_DP_OVERLAP="1" if overlap == "1" else "0", XB_P2P_ADAM="1" if overlap.startswith("p2p") else "0",
+                                XB_P2P_OVERLAP="0" if overlap == "p2p_serial" else "1"))
+    # "0" / "1": NCCL all-reduce (plain / overlapped); "p2p": peer-memory step, FC part beside the conv backward; "p2p_serial": one call
     errs = "".join(p.read_text() for p in sorted(tmp_path.glob("out.txt.err*")))
     assert r.returncode == 0, errs + r.stdout[-1000:] + r.stderr[-1000:]
     same, err, split = out.read_text().split()
     assert int(same) == 1, "ranks diverged"
     assert float(err) < 1e-4, (same, err, split)                    # same kernels on both paths; only summation order differs
-    assert int(split) == (1 if mode == "graph" and overlap == "1" else 0)
+    assert int(split) == (1 if mode == "graph" and overlap in ("1", "p2p") else 0)
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
