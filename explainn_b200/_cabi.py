@@ -68,6 +68,9 @@ SIGNATURES = {
     "explainn_fc_nchunk": [_LL],
     "explainn_fc_stack_fwd_train": [_P, _LL, _I, _I, _I] + [_P] * 12 + [_F, _F, _F, _ULL, _P, _P] + [_P] * 12 + [_P],
     "explainn_fc_stack_bwd": [_P, _LL, _I, _I, _I] + [_P] * 14 + [_F, _ULL, _P, _P] + [_P] * 14 + [_P],
+    "explainn_fc_stack_fwd_train_phase": [_I, _LL, _P, _LL, _I, _I, _I] + [_P] * 12 + [_F, _F, _F, _ULL, _P, _P] + [_P] * 12 + [_P],
+    "explainn_fc_stack_bwd_phase": [_I, _P, _LL, _I, _I, _I] + [_P] * 14 + [_F, _ULL, _P, _P] + [_P] * 14 + [_P],
+    "explainn_conv_pool_bwd_phase": [_I, _LL, _P, _P, _LL, _I, _I, _I] + [_P] * 10 + [_F, _P, _I] + [_P] * 4 + [_P],
     "explainn_conv_bwd_nsplit": [_I],
     "explainn_conv_pool_bwd": [_P, _P, _LL, _I, _I, _I] + [_P] * 10 + [_F, _P, _I] + [_P] * 4 + [_P],
     "explainn_pool_general": [_P, _LL, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P],

@@ -64,16 +64,35 @@ def _check_modes(model):
                                       "(momentum=0.1, affine, track_running_stats)")
 
 
+def _sync_group(model):
+    """(dist, world) when the model asks for synchronised BatchNorm statistics (model.sync_bn = True) inside an
+    initialised process group of more than one rank, else (None, 1)."""
+    if not getattr(model, "sync_bn", False):
+        return None, 1
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
+        return None, 1
+    return dist, dist.get_world_size()
+
+
+def _allreduce_avg(d, t, world):
+    d.all_reduce(t, op=d.ReduceOp.SUM)
+    t.mul_(1.0 / world)
+
+
 class TrainWorkspace:
     """Everything the backward needs, produced by one training forward."""
     __slots__ = ("pk", "B", "U", "P", "C", "F", "M", "mean1", "var1", "Mw", "pooled", "xhat", "idx", "h1", "mean2",
-                 "invstd2", "h2", "mean3", "invstd3", "unit", "logits", "pdrop", "seed", "seed_dev", "nchunk", "dropmask")
+                 "invstd2", "h2", "mean3", "invstd3", "unit", "logits", "pdrop", "seed", "seed_dev", "nchunk", "dropmask",
+                 "sync_world")
 
 
 def train_forward(model, x, params=None, seed=None, seed_dev=None):
     """Runs the training-mode forward kernels.  Returns a TrainWorkspace (logits in ws.logits)."""
     if _is_variant(model):
         from . import variants
+        if _sync_group(model)[0] is not None:
+            raise NotImplementedError("explainn_b200: sync_bn is built for the default unit (num_fc = 2, MaxPool1d(7, 7))")
         if params is None:
             params = [p.detach() for p in _params(model)]
         return variants.train_forward(model, x, params, _next_dropout_seed() if seed is None else seed, seed_dev)
@@ -97,8 +116,14 @@ def train_forward(model, x, params=None, seed=None, seed_dev=None):
     ws.pk, ws.B, ws.U, ws.C, ws.F = pk, B, U, C, F
     S = pk.L - F + 1
     P = ws.P = model.pooled_length
+    # synchronised BatchNorm (model.sync_bn under a process group): every additive statistic is all-reduced between the
+    # kernel that produces it and the one that consumes it, so the step equals the reference's on the concatenated batch
+    dsync, world = _sync_group(model)
+    ws.sync_world = world
     ws.M = Fn.input_cooc_stats(pk, F)
-    ws.mean1, ws.var1, ws.Mw = Fn.bn1_batch_stats(ws.M, cw, cb, B * S, bn1.momentum, bn1.running_mean, bn1.running_var,
+    if dsync is not None:
+        dsync.all_reduce(ws.M, op=dsync.ReduceOp.SUM)
+    ws.mean1, ws.var1, ws.Mw = Fn.bn1_batch_stats(ws.M, cw, cb, B * S * world, bn1.momentum, bn1.running_mean, bn1.running_var,
                                                   bn1.num_batches_tracked)
     ones, zeros = _const(dev, U)
     # the conv is prepared with gamma=1, beta=0 and the batch statistics, so the scan yields x_hat = (y - mu) / sigma
@@ -124,11 +149,19 @@ def train_forward(model, x, params=None, seed=None, seed_dev=None):
     ws.seed = _next_dropout_seed() if seed is None else seed
     ws.seed_dev = seed_dev
     ws.dropmask = torch.empty((U, B, 4), dtype=torch.int32, device=dev) if ws.pdrop > 0 else None
-    call("explainn_fc_stack_fwd_train", ptr(ws.pooled), B, U, P, C, ptr(W1), ptr(b1), ptr(g2), ptr(be2),
-         ptr(bn2.running_mean), ptr(bn2.running_var), ptr(W2), ptr(b2), ptr(g3), ptr(be3), ptr(bn3.running_mean),
-         ptr(bn3.running_var), float(bn2.momentum), float(bn2.eps), ws.pdrop, ws.seed, ptr(seed_dev), ptr(ws.dropmask), ptr(Wf), ptr(bf), ptr(ws.h1),
-         ptr(part2), ptr(ws.mean2), ptr(ws.invstd2), ptr(ws.h2), ptr(part3), ptr(ws.mean3), ptr(ws.invstd3), ptr(ws.unit),
-         ptr(ws.logits), stream())
+    fargs = (ptr(ws.pooled), B, U, P, C, ptr(W1), ptr(b1), ptr(g2), ptr(be2),
+             ptr(bn2.running_mean), ptr(bn2.running_var), ptr(W2), ptr(b2), ptr(g3), ptr(be3), ptr(bn3.running_mean),
+             ptr(bn3.running_var), float(bn2.momentum), float(bn2.eps), ws.pdrop, ws.seed, ptr(seed_dev), ptr(ws.dropmask), ptr(Wf), ptr(bf), ptr(ws.h1),
+             ptr(part2), ptr(ws.mean2), ptr(ws.invstd2), ptr(ws.h2), ptr(part3), ptr(ws.mean3), ptr(ws.invstd3), ptr(ws.unit),
+             ptr(ws.logits), stream())
+    if dsync is None:
+        call("explainn_fc_stack_fwd_train", *fargs)
+    else:
+        call("explainn_fc_stack_fwd_train_phase", 1, B * world, *fargs)
+        dsync.all_reduce(part2, op=dsync.ReduceOp.SUM)
+        call("explainn_fc_stack_fwd_train_phase", 2, B * world, *fargs)
+        dsync.all_reduce(part3, op=dsync.ReduceOp.SUM)
+        call("explainn_fc_stack_fwd_train_phase", 4, B * world, *fargs)
     bn2.num_batches_tracked.add_(1)
     bn3.num_batches_tracked.add_(1)
     return ws
@@ -165,6 +198,8 @@ def _train_forward_conv(model, x, cw, cb, g1, b1n):
 
 def _train_forward_fc1(model, x, params):
     """num_fc = 1 (networks.py:82-95): pooled -> FC (P -> 1) -> BatchNorm -> ReLU -> final Linear."""
+    if _sync_group(model)[0] is not None:
+        raise NotImplementedError("explainn_b200: sync_bn is built for the default unit (num_fc = 2, MaxPool1d(7, 7))")
     (cw, cb, g1, b1n, W1, b1, g3, be3, Wf, bf) = params
     ws = _train_forward_conv(model, x, cw, cb, g1, b1n)
     bn3 = model.linears[7]
@@ -238,11 +273,22 @@ def train_backward(model, ws, gout, params=None, grads=None, wrt_unit=False, bet
     pb2 = torch.empty((U, ws.nchunk, 3, H), **f32)
     dW1p = torch.empty((ws.nchunk, U, H, P), **f32)
     gpool = torch.empty((B, U, P), **f32)
-    call("explainn_fc_stack_bwd", ptr(gout), B, U, P, C, ptr(ws.pooled), ptr(ws.h1), ptr(ws.h2), ptr(ws.unit), ptr(W1),
-         ptr(g2), ptr(be2), ptr(ws.mean2), ptr(ws.invstd2), ptr(W2), ptr(g3), ptr(ws.mean3), ptr(ws.invstd3),
-         None if wrt_unit else ptr(Wf), ws.pdrop, ws.seed, ptr(ws.seed_dev), ptr(ws.dropmask), ptr(gh2), ptr(pb2), ptr(dW1p), ptr(gpool), ptr(dW1), ptr(db1),
-         ptr(dg2), ptr(dbe2), ptr(dW2), ptr(db2), ptr(dg3), ptr(dbe3), None if wrt_unit else ptr(dWf),
-         None if wrt_unit else ptr(dbf), stream())
+    bargs = (ptr(gout), B, U, P, C, ptr(ws.pooled), ptr(ws.h1), ptr(ws.h2), ptr(ws.unit), ptr(W1),
+             ptr(g2), ptr(be2), ptr(ws.mean2), ptr(ws.invstd2), ptr(W2), ptr(g3), ptr(ws.mean3), ptr(ws.invstd3),
+             None if wrt_unit else ptr(Wf), ws.pdrop, ws.seed, ptr(ws.seed_dev), ptr(ws.dropmask), ptr(gh2), ptr(pb2), ptr(dW1p), ptr(gpool), ptr(dW1), ptr(db1),
+             ptr(dg2), ptr(dbe2), ptr(dW2), ptr(db2), ptr(dg3), ptr(dbe3), None if wrt_unit else ptr(dWf),
+             None if wrt_unit else ptr(dbf), stream())
+    dsync, world = _sync_group(model) if getattr(ws, "sync_world", 1) > 1 else (None, 1)
+    if dsync is None:
+        call("explainn_fc_stack_bwd", *bargs)
+    else:
+        # sums of the BatchNorm backward passes, averaged over the ranks between producer and consumer (the kernels divide
+        # by the local batch: mean of local sums / local batch = global sum / global batch)
+        call("explainn_fc_stack_bwd_phase", 1, *bargs)
+        _allreduce_avg(dsync, pb2.view(-1)[:2 * U], world)
+        call("explainn_fc_stack_bwd_phase", 2, *bargs)
+        _allreduce_avg(dsync, pb2, world)
+        call("explainn_fc_stack_bwd_phase", 4, *bargs)
     if between is not None and between(ws, gpool, params, grads, wrt_unit) is False:
         return grads
     return train_backward_conv(model, ws, gpool, params, grads, wrt_unit)
@@ -261,9 +307,17 @@ def train_backward_conv(model, ws, gpool, params, grads, wrt_unit=False):
     f32 = dict(dtype=torch.float32, device=gpool.device)
     nsplit = Fn._cabi.lib.explainn_conv_bwd_nsplit(U)
     partial = torch.empty((nsplit, U, 4 * F + 2), **f32)
-    call("explainn_conv_pool_bwd", ptr(ws.pk.codes), ptr(ws.pk.nmask), B, ws.pk.L, U, F, ptr(gpool), ptr(ws.pooled),
-         ptr(ws.xhat), ptr(ws.idx), ptr(ws.M), ptr(ws.Mw), ptr(cb), ptr(ws.mean1), ptr(ws.var1), ptr(g1),
-         float(L[1].eps), ptr(partial), nsplit, ptr(dcw), ptr(dcb), ptr(dg1), ptr(db1n), stream())
+    cargs = (ptr(ws.pk.codes), ptr(ws.pk.nmask), B, ws.pk.L, U, F, ptr(gpool), ptr(ws.pooled),
+             ptr(ws.xhat), ptr(ws.idx), ptr(ws.M), ptr(ws.Mw), ptr(cb), ptr(ws.mean1), ptr(ws.var1), ptr(g1),
+             float(L[1].eps), ptr(partial), nsplit, ptr(dcw), ptr(dcb), ptr(dg1), ptr(db1n), stream())
+    dsync, world = _sync_group(model) if getattr(ws, "sync_world", 1) > 1 else (None, 1)
+    if dsync is None:
+        call("explainn_conv_pool_bwd", *cargs)
+    else:
+        n_pos = B * world * (ws.pk.L - F + 1)
+        call("explainn_conv_pool_bwd_phase", 1, n_pos, *cargs)
+        _allreduce_avg(dsync, partial, world)
+        call("explainn_conv_pool_bwd_phase", 2, n_pos, *cargs)
     if wrt_unit:
         dWf.zero_()
         dbf.zero_()

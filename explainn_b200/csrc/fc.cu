@@ -267,7 +267,10 @@ __global__ void __launch_bounds__(FC_THREADS) fc2_train_kernel(
         if (j < H) {
             double sm = 0.0, sq = 0.0;
             const double inv_B = (double)inv_batch;
-            const float unbias = (float)B / (float)(B > 1 ? B - 1 : 1);
+            // statistics count = 1 / inv_batch: the local batch, or the whole data-parallel batch when the partial sums were
+            // all-reduced (synchronised BatchNorm)
+            const double nstat = 1.0 / inv_B;
+            const float unbias = (float)(nstat / (nstat > 1.5 ? nstat - 1.0 : 1.0));
             for (int k = 0; k < nchunk; ++k) {
                 const float *pp = part2 + ((size_t)u * nchunk + k) * 2 * H;
                 sm += (double)pp[j];
@@ -387,7 +390,8 @@ __global__ void __launch_bounds__(256) out_train_kernel(const float *__restrict_
             mean3[u] = (float)mean;
             invstd3[u] = inv;
             if (rm3) {
-                const float unb = B > 1 ? varf * ((float)B / (float)(B - 1)) : varf;
+                const double nstat = 1.0 / inv_batch;
+                const float unb = nstat > 1.5 ? varf * (float)(nstat / (nstat - 1.0)) : varf;
                 rm3[u] = (1.0f - momentum) * rm3[u] + momentum * (float)mean;
                 rv3[u] = (1.0f - momentum) * rv3[u] + momentum * unb;
             }
@@ -539,10 +543,13 @@ __global__ void __launch_bounds__(128) bwd_final_linear2_kernel(const float *__r
 }
 
 // BatchNorm-3 backward per unit: sums over the batch, then gh2 (U,B), dgamma3, dbeta3.  One warp per unit.
+// mode 0: both halves; mode 1: only the sums, written to sums[2u], sums[2u+1]; mode 2: only the second half, with the
+// sums read back from there (synchronised BatchNorm: the caller averages them over the ranks in between).
 __global__ void __launch_bounds__(256) bwd_bn3_kernel(const float *__restrict__ gz, const float *__restrict__ h2, long long B,
                                                       int U, const float *__restrict__ g3, const float *__restrict__ mean3,
                                                       const float *__restrict__ invstd3, float *__restrict__ gh2,
-                                                      float *__restrict__ dg3, float *__restrict__ db3)
+                                                      float *__restrict__ dg3, float *__restrict__ db3, float *__restrict__ sums,
+                                                      int mode)
 {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int u = blockIdx.x * 8 + warp;
@@ -550,13 +557,22 @@ __global__ void __launch_bounds__(256) bwd_bn3_kernel(const float *__restrict__ 
     const float mean = mean3[u], inv = invstd3[u];
     const float *h2u = h2 + (size_t)u * B;
     float s1 = 0.f, s2 = 0.f;
-    for (long long b = lane; b < B; b += 32) {
-        const float g = gz[b * U + u], xh = (h2u[b] - mean) * inv;
-        s1 += g;
-        s2 = fmaf(g, xh, s2);
+    if (mode != 2) {
+        for (long long b = lane; b < B; b += 32) {
+            const float g = gz[b * U + u], xh = (h2u[b] - mean) * inv;
+            s1 += g;
+            s2 = fmaf(g, xh, s2);
+        }
+        s1 = warp_sum(s1);
+        s2 = warp_sum(s2);
+        if (mode == 1) {
+            if (lane == 0) { sums[2 * u] = s1; sums[2 * u + 1] = s2; }
+            return;
+        }
+    } else {
+        s1 = sums[2 * u];
+        s2 = sums[2 * u + 1];
     }
-    s1 = warp_sum(s1);
-    s2 = warp_sum(s2);
     if (lane == 0) {
         if (db3) db3[u] = s1;
         if (dg3) dg3[u] = s2;
@@ -908,13 +924,15 @@ extern "C" int explainn_linear_fwd(const float *x, long long B, int U, int C, co
 
 extern "C" int explainn_fc_nchunk(long long B) { return (int)((B + BM - 1) / BM); }
 
-extern "C" int explainn_fc_stack_fwd_train(const float *pooled, long long B, int U, int P, int C, const float *W1, const float *b1,
-                                           const float *bn2_w, const float *bn2_b, float *bn2_rm, float *bn2_rv, const float *W2,
-                                           const float *b2, const float *bn3_w, const float *bn3_b, float *bn3_rm, float *bn3_rv,
-                                           float momentum, float eps, float pdrop, unsigned long long seed,
-                                           const unsigned long long *seed_dev, uint32_t *dropmask, const float *Wf, const float *bf, float *h1, float *part2, float *mean2, float *invstd2, float *h2,
-                                           float *part3, float *mean3, float *invstd3, float *unit, float *logits,
-                                           cudaStream_t stream)
+// phases: 1 = FC1 (h1, part2), 2 = BatchNorm-2 .. FC2 (h2, part3), 4 = BatchNorm-3 .. logits; batch_total = number of
+// samples behind the partial sums (B, or the whole data-parallel batch once the caller has all-reduced part2 / part3)
+static int fc_stack_fwd_train_impl(int phases, long long batch_total, const float *pooled, long long B, int U, int P, int C,
+                                   const float *W1, const float *b1, const float *bn2_w, const float *bn2_b, float *bn2_rm,
+                                   float *bn2_rv, const float *W2, const float *b2, const float *bn3_w, const float *bn3_b,
+                                   float *bn3_rm, float *bn3_rv, float momentum, float eps, float pdrop, unsigned long long seed,
+                                   const unsigned long long *seed_dev, uint32_t *dropmask, const float *Wf, const float *bf,
+                                   float *h1, float *part2, float *mean2, float *invstd2, float *h2, float *part3, float *mean3,
+                                   float *invstd3, float *unit, float *logits, cudaStream_t stream)
 {
     XB_REQUIRE(pooled && W1 && b1 && bn2_w && bn2_b && W2 && b2 && bn3_w && bn3_b && Wf && bf && h1 && part2 && mean2 && invstd2 &&
                    h2 && part3 && mean3 && invstd3 && unit && logits,
@@ -933,19 +951,56 @@ extern "C" int explainn_fc_stack_fwd_train(const float *pooled, long long B, int
         xb_set_error("fc_stack_fwd_train: shared memory need (%zu / %zu bytes) exceeds the SM", smem1, smem3);
         return XB_ERR_UNSUPPORTED;
     }
-    if (xb_fc_tc_enabled()) {    // tcgen05 path (XB_FC_TC=0 selects the CUDA-core kernel)
-        int rc = xb_fc1_fwd_train_tc(pooled, B, U, P, W1, b1, h1, part2, stream);
-        if (rc != XB_OK) return rc;
-    } else {
-        cudaFuncSetAttribute(fc1_train_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1);
-        fc1_train_kernel<<<dim3(U, nchunk), FC_THREADS, smem1, stream>>>(pooled, B, U, P, W1, b1, h1, part2);
+    XB_REQUIRE(batch_total >= B && phases >= 1 && phases <= 7, "fc_stack_fwd_train: bad phase arguments");
+    const double inv_batch = 1.0 / (double)batch_total;
+    if (phases & 1) {
+        if (xb_fc_tc_enabled()) {    // tcgen05 path (XB_FC_TC=0 selects the CUDA-core kernel)
+            int rc = xb_fc1_fwd_train_tc(pooled, B, U, P, W1, b1, h1, part2, stream);
+            if (rc != XB_OK) return rc;
+        } else {
+            cudaFuncSetAttribute(fc1_train_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1);
+            fc1_train_kernel<<<dim3(U, nchunk), FC_THREADS, smem1, stream>>>(pooled, B, U, P, W1, b1, h1, part2);
+        }
     }
-    fc2_train_kernel<<<dim3(U, nchunk), FC_THREADS, 0, stream>>>(h1, B, U, part2, nchunk, bn2_w, bn2_b, bn2_rm, bn2_rv, momentum, eps,
-                                                                 W2, b2, mean2, invstd2, pdrop, seed, seed_dev, dropmask, h2, part3, 1.0 / (double)B);
-    cudaFuncSetAttribute(out_train_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem3);
-    out_train_kernel<<<dim3((unsigned)((B + OT_ROWS - 1) / OT_ROWS), ot_ny), 256, smem3, stream>>>(h2, B, U, C, part3, nchunk, bn3_w, bn3_b, bn3_rm, bn3_rv,
-                                                                        momentum, eps, mean3, invstd3, Wf, bf, unit, logits, wf_in_smem, 1.0 / (double)B);
+    if (phases & 2)
+        fc2_train_kernel<<<dim3(U, nchunk), FC_THREADS, 0, stream>>>(h1, B, U, part2, nchunk, bn2_w, bn2_b, bn2_rm, bn2_rv, momentum, eps,
+                                                                     W2, b2, mean2, invstd2, pdrop, seed, seed_dev, dropmask, h2, part3, inv_batch);
+    if (phases & 4) {
+        cudaFuncSetAttribute(out_train_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem3);
+        out_train_kernel<<<dim3((unsigned)((B + OT_ROWS - 1) / OT_ROWS), ot_ny), 256, smem3, stream>>>(h2, B, U, C, part3, nchunk, bn3_w, bn3_b, bn3_rm, bn3_rv,
+                                                                            momentum, eps, mean3, invstd3, Wf, bf, unit, logits, wf_in_smem, inv_batch);
+    }
     return xb_check_launch("fc_stack_fwd_train");
+}
+
+extern "C" int explainn_fc_stack_fwd_train(const float *pooled, long long B, int U, int P, int C, const float *W1, const float *b1,
+                                           const float *bn2_w, const float *bn2_b, float *bn2_rm, float *bn2_rv, const float *W2,
+                                           const float *b2, const float *bn3_w, const float *bn3_b, float *bn3_rm, float *bn3_rv,
+                                           float momentum, float eps, float pdrop, unsigned long long seed,
+                                           const unsigned long long *seed_dev, uint32_t *dropmask, const float *Wf, const float *bf, float *h1, float *part2, float *mean2, float *invstd2, float *h2,
+                                           float *part3, float *mean3, float *invstd3, float *unit, float *logits,
+                                           cudaStream_t stream)
+{
+    return fc_stack_fwd_train_impl(7, B, pooled, B, U, P, C, W1, b1, bn2_w, bn2_b, bn2_rm, bn2_rv, W2, b2, bn3_w, bn3_b, bn3_rm, bn3_rv,
+                                   momentum, eps, pdrop, seed, seed_dev, dropmask, Wf, bf, h1, part2, mean2, invstd2, h2, part3, mean3,
+                                   invstd3, unit, logits, stream);
+}
+
+// The same forward in separately callable phases (bitmask: 1 FC1, 2 BatchNorm-2 .. FC2, 4 BatchNorm-3 .. logits), for
+// data-parallel training with synchronised BatchNorm statistics: the caller all-reduces (SUM) part2 between phases 1
+// and 2 and part3 between 2 and 4 and passes batch_total = the number of samples of ALL ranks.
+extern "C" int explainn_fc_stack_fwd_train_phase(int phases, long long batch_total, const float *pooled, long long B, int U, int P,
+                                                 int C, const float *W1, const float *b1, const float *bn2_w, const float *bn2_b,
+                                                 float *bn2_rm, float *bn2_rv, const float *W2, const float *b2, const float *bn3_w,
+                                                 const float *bn3_b, float *bn3_rm, float *bn3_rv, float momentum, float eps,
+                                                 float pdrop, unsigned long long seed, const unsigned long long *seed_dev,
+                                                 uint32_t *dropmask, const float *Wf, const float *bf, float *h1, float *part2,
+                                                 float *mean2, float *invstd2, float *h2, float *part3, float *mean3, float *invstd3,
+                                                 float *unit, float *logits, cudaStream_t stream)
+{
+    return fc_stack_fwd_train_impl(phases, batch_total, pooled, B, U, P, C, W1, b1, bn2_w, bn2_b, bn2_rm, bn2_rv, W2, b2, bn3_w, bn3_b,
+                                   bn3_rm, bn3_rv, momentum, eps, pdrop, seed, seed_dev, dropmask, Wf, bf, h1, part2, mean2, invstd2, h2,
+                                   part3, mean3, invstd3, unit, logits, stream);
 }
 
 // Backward of the final Linear alone (networks.py:147,161), for the units without an FC stack (num_fc = 0):
@@ -971,39 +1026,49 @@ extern "C" int explainn_linear_bwd(const float *glogits, const float *unit, cons
     return xb_check_launch("linear_bwd");
 }
 
-extern "C" int explainn_fc_stack_bwd(const float *glogits, long long B, int U, int P, int C, const float *pooled, const float *h1,
-                                     const float *h2, const float *unit, const float *W1, const float *bn2_w, const float *bn2_b,
-                                     const float *mean2, const float *invstd2, const float *W2, const float *bn3_w,
-                                     const float *mean3, const float *invstd3, const float *Wf, float pdrop,
-                                     unsigned long long seed, const unsigned long long *seed_dev, const uint32_t *dropmask, float *gh2, float *pb2, float *dW1_partials, float *gpool,
-                                     float *dW1, float *db1, float *dbn2_w, float *dbn2_b, float *dW2, float *db2, float *dbn3_w,
-                                     float *dbn3_b, float *dWf, float *dbf, cudaStream_t stream)
+// phases: 1 = final-Linear gradients, d/d unit, BatchNorm-3 sums; 2 = BatchNorm-3 backward, FC2 backward + BatchNorm-2 sums
+// (pb2); 4 = FC1 backward + dW1 reduction.  phases == 7 runs the fused BatchNorm-3 kernel; otherwise the BatchNorm-3 sums
+// travel through the first 2U floats of pb2 between phases 1 and 2 (the caller may average them over ranks there).
+static int fc_stack_bwd_impl(int phases, const float *glogits, long long B, int U, int P, int C, const float *pooled, const float *h1,
+                             const float *h2, const float *unit, const float *W1, const float *bn2_w, const float *bn2_b,
+                             const float *mean2, const float *invstd2, const float *W2, const float *bn3_w, const float *mean3,
+                             const float *invstd3, const float *Wf, float pdrop, unsigned long long seed,
+                             const unsigned long long *seed_dev, const uint32_t *dropmask, float *gh2, float *pb2,
+                             float *dW1_partials, float *gpool, float *dW1, float *db1, float *dbn2_w, float *dbn2_b, float *dW2,
+                             float *db2, float *dbn3_w, float *dbn3_b, float *dWf, float *dbf, cudaStream_t stream)
 {
+    XB_REQUIRE(phases >= 1 && phases <= 7, "fc_stack_bwd: bad phase mask");
     XB_REQUIRE(glogits && pooled && h1 && h2 && unit && W1 && bn2_w && bn2_b && mean2 && invstd2 && W2 && bn3_w && mean3 && invstd3 &&
                    gh2 && pb2 && dW1_partials && gpool && dW1,
                "fc_stack_bwd: null pointer");
     XB_REQUIRE(B >= 2 && U >= 1 && P >= 1 && C >= 1, "fc_stack_bwd: bad sizes");
     XB_REQUIRE(((uintptr_t)h1 & 15) == 0, "fc_stack_bwd: h1 must be 16-byte aligned");
     const int nchunk = (int)((B + BM - 1) / BM);
-    // Wf == NULL: glogits is the gradient w.r.t. the unit outputs (B,U) and the final layer is skipped
-    if (Wf) {
-        if (dWf) cudaMemsetAsync(dWf, 0, (size_t)C * U * sizeof(float), stream);
-        if (dbf) cudaMemsetAsync(dbf, 0, (size_t)C * sizeof(float), stream);
-        const int nsb = (int)std::min<long long>(8, (B + 63) / 64);
-        bwd_final_linear2_kernel<<<dim3((U + 127) / 128, (C + 7) / 8, nsb), 128, 0, stream>>>(glogits, unit, B, U, C, dWf, dbf);
-    }
     // gz3 (B,U) lives in the head of the gpool buffer (U*B*P floats >= B*U); it is consumed by bwd_bn3_kernel
     // before bwd_fc1_kernel overwrites gpool
     float *gz3 = gpool;
-    const size_t smem_gu = ((size_t)8 * C + (size_t)C * GU_UT) * 4;
-    if (smem_gu > 200 * 1024) {
-        xb_set_error("fc_stack_bwd: %d classes need %zu bytes of shared memory", C, smem_gu);
-        return XB_ERR_LIMIT;
+    if (phases & 1) {
+        // Wf == NULL: glogits is the gradient w.r.t. the unit outputs (B,U) and the final layer is skipped
+        if (Wf) {
+            if (dWf) cudaMemsetAsync(dWf, 0, (size_t)C * U * sizeof(float), stream);
+            if (dbf) cudaMemsetAsync(dbf, 0, (size_t)C * sizeof(float), stream);
+            const int nsb = (int)std::min<long long>(8, (B + 63) / 64);
+            bwd_final_linear2_kernel<<<dim3((U + 127) / 128, (C + 7) / 8, nsb), 128, 0, stream>>>(glogits, unit, B, U, C, dWf, dbf);
+        }
+        const size_t smem_gu = ((size_t)8 * C + (size_t)C * GU_UT) * 4;
+        if (smem_gu > 200 * 1024) {
+            xb_set_error("fc_stack_bwd: %d classes need %zu bytes of shared memory", C, smem_gu);
+            return XB_ERR_LIMIT;
+        }
+        cudaFuncSetAttribute(bwd_gunit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_gu);
+        bwd_gunit_kernel<<<dim3((unsigned)((B + 7) / 8), (U + GU_UT - 1) / GU_UT), 256, smem_gu, stream>>>(glogits, Wf, unit, B, U, C, gz3);
+        if (phases != 7) bwd_bn3_kernel<<<(U + 7) / 8, 256, 0, stream>>>(gz3, h2, B, U, bn3_w, mean3, invstd3, gh2, dbn3_w, dbn3_b, pb2, 1);
     }
-    cudaFuncSetAttribute(bwd_gunit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_gu);
-    bwd_gunit_kernel<<<dim3((unsigned)((B + 7) / 8), (U + GU_UT - 1) / GU_UT), 256, smem_gu, stream>>>(glogits, Wf, unit, B, U, C, gz3);
-    bwd_bn3_kernel<<<(U + 7) / 8, 256, 0, stream>>>(gz3, h2, B, U, bn3_w, mean3, invstd3, gh2, dbn3_w, dbn3_b);
-    bwd_fc2_kernel<<<dim3(U, nchunk), FC_THREADS, 0, stream>>>(h1, gh2, B, U, bn2_w, bn2_b, mean2, invstd2, W2, pdrop, seed, seed_dev, dropmask, pb2);
+    if (phases & 2) {
+        bwd_bn3_kernel<<<(U + 7) / 8, 256, 0, stream>>>(gz3, h2, B, U, bn3_w, mean3, invstd3, gh2, dbn3_w, dbn3_b, pb2, phases == 7 ? 0 : 2);
+        bwd_fc2_kernel<<<dim3(U, nchunk), FC_THREADS, 0, stream>>>(h1, gh2, B, U, bn2_w, bn2_b, mean2, invstd2, W2, pdrop, seed, seed_dev, dropmask, pb2);
+    }
+    if (!(phases & 4)) return xb_check_launch("fc_stack_bwd");
 #define XB_LAUNCH_BWD_FC1(PHV)                                                                                                      \
     do {                                                                                                                            \
         const size_t sm = bwd_fc1_smem<PHV>();                                                                                      \
@@ -1031,6 +1096,36 @@ extern "C" int explainn_fc_stack_bwd(const float *glogits, long long B, int U, i
     if (rc != XB_OK) return rc;
     // dW1 = sum over batch chunks of the per-tile partials
     return explainn_reduce_partials(dW1, dW1_partials, (long long)U * H * P, nchunk, stream);
+}
+
+extern "C" int explainn_fc_stack_bwd(const float *glogits, long long B, int U, int P, int C, const float *pooled, const float *h1,
+                                     const float *h2, const float *unit, const float *W1, const float *bn2_w, const float *bn2_b,
+                                     const float *mean2, const float *invstd2, const float *W2, const float *bn3_w,
+                                     const float *mean3, const float *invstd3, const float *Wf, float pdrop,
+                                     unsigned long long seed, const unsigned long long *seed_dev, const uint32_t *dropmask, float *gh2, float *pb2, float *dW1_partials, float *gpool,
+                                     float *dW1, float *db1, float *dbn2_w, float *dbn2_b, float *dW2, float *db2, float *dbn3_w,
+                                     float *dbn3_b, float *dWf, float *dbf, cudaStream_t stream)
+{
+    return fc_stack_bwd_impl(7, glogits, B, U, P, C, pooled, h1, h2, unit, W1, bn2_w, bn2_b, mean2, invstd2, W2, bn3_w, mean3, invstd3, Wf,
+                             pdrop, seed, seed_dev, dropmask, gh2, pb2, dW1_partials, gpool, dW1, db1, dbn2_w, dbn2_b, dW2, db2, dbn3_w,
+                             dbn3_b, dWf, dbf, stream);
+}
+
+// The same backward in separately callable phases (bitmask 1 / 2 / 4, see fc_stack_bwd_impl), for synchronised BatchNorm
+// under data parallel: between phases 1 and 2 the caller averages the first 2U floats of pb2 (BatchNorm-3 sums) over the
+// ranks, between 2 and 4 all of pb2 (BatchNorm-2 sums).
+extern "C" int explainn_fc_stack_bwd_phase(int phases, const float *glogits, long long B, int U, int P, int C, const float *pooled,
+                                           const float *h1, const float *h2, const float *unit, const float *W1, const float *bn2_w,
+                                           const float *bn2_b, const float *mean2, const float *invstd2, const float *W2,
+                                           const float *bn3_w, const float *mean3, const float *invstd3, const float *Wf, float pdrop,
+                                           unsigned long long seed, const unsigned long long *seed_dev, const uint32_t *dropmask,
+                                           float *gh2, float *pb2, float *dW1_partials, float *gpool, float *dW1, float *db1,
+                                           float *dbn2_w, float *dbn2_b, float *dW2, float *db2, float *dbn3_w, float *dbn3_b,
+                                           float *dWf, float *dbf, cudaStream_t stream)
+{
+    return fc_stack_bwd_impl(phases, glogits, B, U, P, C, pooled, h1, h2, unit, W1, bn2_w, bn2_b, mean2, invstd2, W2, bn3_w, mean3, invstd3,
+                             Wf, pdrop, seed, seed_dev, dropmask, gh2, pb2, dW1_partials, gpool, dW1, db1, dbn2_w, dbn2_b, dW2, db2,
+                             dbn3_w, dbn3_b, dWf, dbf, stream);
 }
 
 
@@ -1097,7 +1192,7 @@ extern "C" int explainn_fc1_stack_bwd(const float *glogits, long long B, int U, 
     }
     cudaFuncSetAttribute(bwd_gunit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_gu);
     bwd_gunit_kernel<<<dim3((unsigned)((B + 7) / 8), (U + GU_UT - 1) / GU_UT), 256, smem_gu, stream>>>(glogits, Wf, unit, B, U, C, gz3);
-    bwd_bn3_kernel<<<(U + 7) / 8, 256, 0, stream>>>(gz3, h2, B, U, bn_w, mean3, invstd3, gh2, dbn_w, dbn_b);
+    bwd_bn3_kernel<<<(U + 7) / 8, 256, 0, stream>>>(gz3, h2, B, U, bn_w, mean3, invstd3, gh2, dbn_w, dbn_b, nullptr, 0);
     const size_t smem = ((size_t)P + BM + (size_t)BM * (P + 1)) * 4;
     if (smem > 200 * 1024) {
         xb_set_error("fc1_stack_bwd: pooled length %d needs %zu bytes of shared memory", P, smem);

@@ -459,7 +459,9 @@ extern "C" int explainn_conv_bwd_nsplit(int U)
     return ns < 1 ? 1 : ns;
 }
 
-static int conv_pool_bwd_impl(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F, int psize, int pstride,
+// phases: 1 = sparse scatter into `partial`, 2 = dense correction + assembly; n_pos_total = B*S of the batch the
+// statistics (M, Mw, mean, var) describe (the whole data-parallel batch under synchronised BatchNorm)
+static int conv_pool_bwd_impl(int phases, long long n_pos_total, const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F, int psize, int pstride,
                               const float *gpool, const float *pooled, const float *xhat, const unsigned char *idx,
                               const unsigned short *idx16, const int *M, const float *Mw, const float *bias, const float *mean,
                               const float *var, const float *gamma, float eps, float *partial, int nsplit, float *dW, float *dbias,
@@ -478,14 +480,18 @@ static int conv_pool_bwd_impl(const uint32_t *codes, const uint32_t *nmask, long
         conv_bwd_sparse_kernel<FTV><<<dim3(U, nsplit), BW_WARPS * 32, smem, stream>>>(                                        \
             codes, nmask, B, L, F, P, xb_words_codes(L), xb_words_mask(L), gpool, pooled, xhat, idx, idx16, pstride, partial, U); \
     } while (0)
-    if (F == 19) XB_LAUNCH_SPARSE(19);
-    else if (F == 20) XB_LAUNCH_SPARSE(20);
-    else XB_LAUNCH_SPARSE(0);
+    if (phases & 1) {
+        if (F == 19) XB_LAUNCH_SPARSE(19);
+        else if (F == 20) XB_LAUNCH_SPARSE(20);
+        else XB_LAUNCH_SPARSE(0);
+        int rc = xb_check_launch("conv_bwd_sparse");
+        if (rc != XB_OK) return rc;
+    }
 #undef XB_LAUNCH_SPARSE
-    int rc = xb_check_launch("conv_bwd_sparse");
-    if (rc != XB_OK) return rc;
-    conv_bwd_final_kernel<<<U, 128, 0, stream>>>(partial, nsplit, U, F, M, Mw, bias, mean, var, gamma, eps, (double)B * S, dW, dbias,
-                                                dgamma, dbeta);
+    if (phases & 2) {
+        const double N = n_pos_total > 0 ? (double)n_pos_total : (double)B * S;
+        conv_bwd_final_kernel<<<U, 128, 0, stream>>>(partial, nsplit, U, F, M, Mw, bias, mean, var, gamma, eps, N, dW, dbias, dgamma, dbeta);
+    }
     return xb_check_launch("conv_bwd_final");
 }
 
@@ -495,7 +501,7 @@ extern "C" int explainn_conv_pool_bwd(const uint32_t *codes, const uint32_t *nma
                                       const float *gamma, float eps, float *partial, int nsplit, float *dW, float *dbias,
                                       float *dgamma, float *dbeta, cudaStream_t stream)
 {
-    return conv_pool_bwd_impl(codes, nmask, B, L, U, F, XB_POOL, XB_POOL, gpool, pooled, xhat, idx, nullptr, M, Mw, bias, mean, var, gamma,
+    return conv_pool_bwd_impl(3, 0, codes, nmask, B, L, U, F, XB_POOL, XB_POOL, gpool, pooled, xhat, idx, nullptr, M, Mw, bias, mean, var, gamma,
                               eps, partial, nsplit, dW, dbias, dgamma, dbeta, stream);
 }
 
@@ -507,8 +513,23 @@ extern "C" int explainn_conv_pool_bwd_general(const uint32_t *codes, const uint3
                                               float *partial, int nsplit, float *dW, float *dbias, float *dgamma, float *dbeta,
                                               cudaStream_t stream)
 {
-    return conv_pool_bwd_impl(codes, nmask, B, L, U, F, pool_size, pool_stride, gpool, pooled, xhat, nullptr, idx16, M, Mw, bias, mean, var,
+    return conv_pool_bwd_impl(3, 0, codes, nmask, B, L, U, F, pool_size, pool_stride, gpool, pooled, xhat, nullptr, idx16, M, Mw, bias, mean, var,
                               gamma, eps, partial, nsplit, dW, dbias, dgamma, dbeta, stream);
+}
+
+// explainn_conv_pool_bwd in two separately callable phases (1 sparse scatter, 2 dense correction) for synchronised
+// BatchNorm: between them the caller averages `partial` over the ranks; M / Mw / mean / var then describe the whole
+// data-parallel batch and n_pos_total is its B*S.
+extern "C" int explainn_conv_pool_bwd_phase(int phases, long long n_pos_total, const uint32_t *codes, const uint32_t *nmask,
+                                            long long B, int L, int U, int F, const float *gpool, const float *pooled,
+                                            const float *xhat, const unsigned char *idx, const int *M, const float *Mw,
+                                            const float *bias, const float *mean, const float *var, const float *gamma, float eps,
+                                            float *partial, int nsplit, float *dW, float *dbias, float *dgamma, float *dbeta,
+                                            cudaStream_t stream)
+{
+    XB_REQUIRE(phases >= 1 && phases <= 3, "conv_pool_bwd_phase: bad phase mask");
+    return conv_pool_bwd_impl(phases, n_pos_total, codes, nmask, B, L, U, F, XB_POOL, XB_POOL, gpool, pooled, xhat, idx, nullptr, M, Mw,
+                              bias, mean, var, gamma, eps, partial, nsplit, dW, dbias, dgamma, dbeta, stream);
 }
 
 extern "C" long long explainn_loss_scratch_bytes(void) { return (long long)LOSS_MAX_BLOCKS * sizeof(double) + 16; }

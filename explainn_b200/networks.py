@@ -178,6 +178,9 @@ class ExplaiNN(nn.Module):
         # "tc_fp16": inference only, one fp16 piece per weight (stated tolerance 2e-3, half the tensor-core work);
         # "lut": the k-mer table kernel (bit-identical to the CPU oracle).  The interpretation pass always uses "lut".
         self.conv_backend = "tc"
+        # data parallel only: True = BatchNorm batch statistics over the batches of ALL ranks (the reference's single-device
+        # maths on the concatenated batch; default unit only, eager execution); False = each rank's own batch (DDP default)
+        self.sync_bn = False
         if weight_path:
             self.load_state_dict(torch.load(weight_path))
 

@@ -127,6 +127,8 @@ class FusedTrainer:
         self.dropout_seed = dropout_seed
         # CUDA-graph replay of forward+loss+backward (the step is launch-bound at batch 512, SURVEY 7.3 g)
         self.use_graph = use_graph
+        if getattr(model, "sync_bn", False) and d0 is not None and d0.get_world_size() > 1:
+            self.use_graph = False      # the synchronised-BatchNorm step has NCCL all-reduces between its kernels: eager
         self._graph = None
         self._graphs = {}
         self._graph_failed = False

@@ -308,6 +308,39 @@ int explainn_fc_stack_bwd(const float *glogits, long long B, int U, int P, int C
                           float *dW1, float *db1, float *dbn2_w, float *dbn2_b, float *dW2, float *db2, float *dbn3_w,
                           float *dbn3_b, float *dWf, float *dbf, cudaStream_t stream);
 
+/* ---- the same training entry points in separately callable phases (synchronised BatchNorm under data parallel) ------
+ * The reference is single-device: its BatchNorm statistics cover the whole batch (networks.py:100,108,114).  To reproduce
+ * that with the batch split over ranks, the additive statistics are all-reduced BETWEEN the kernels that produce and
+ * consume them; these entry points expose those seams (arguments as in the unphased calls, plus a phase bitmask):
+ *   forward   1: FC1 -> part2 | all-reduce SUM part2 | 2: BatchNorm-2 .. FC2 -> part3 | all-reduce SUM part3 | 4: BatchNorm-3 ..
+ *             logits; batch_total = samples of all ranks (statistics and the unbiased running variance use it)
+ *   backward  1: final-Linear gradients, d/d unit, BatchNorm-3 sums (first 2U floats of pb2) | average them over ranks |
+ *             2: BatchNorm-3 backward, FC2 backward -> pb2 | average pb2 | 4: FC1 backward
+ *   conv bwd  1: sparse scatter -> partial | average partial | 2: dense correction with M, Mw, mean, var of the whole batch
+ *             and n_pos_total = its B*S
+ * (means of local sums over ranks divided by the local batch equal global sums divided by the global batch, so the
+ * backward kernels keep B = the local batch; the input co-occurrence table M is all-reduced with SUM before
+ * explainn_bn1_batch_stats, whose n_pos is then the global B*S.) */
+int explainn_fc_stack_fwd_train_phase(int phases, long long batch_total, const float *pooled, long long B, int U, int P, int C,
+                                      const float *W1, const float *b1, const float *bn2_w, const float *bn2_b, float *bn2_rm,
+                                      float *bn2_rv, const float *W2, const float *b2, const float *bn3_w, const float *bn3_b,
+                                      float *bn3_rm, float *bn3_rv, float momentum, float eps, float pdrop, unsigned long long seed,
+                                      const unsigned long long *seed_dev, uint32_t *dropmask, const float *Wf, const float *bf,
+                                      float *h1, float *part2, float *mean2, float *invstd2, float *h2, float *part3, float *mean3,
+                                      float *invstd3, float *unit, float *logits, cudaStream_t stream);
+int explainn_fc_stack_bwd_phase(int phases, const float *glogits, long long B, int U, int P, int C, const float *pooled,
+                                const float *h1, const float *h2, const float *unit, const float *W1, const float *bn2_w,
+                                const float *bn2_b, const float *mean2, const float *invstd2, const float *W2, const float *bn3_w,
+                                const float *mean3, const float *invstd3, const float *Wf, float pdrop, unsigned long long seed,
+                                const unsigned long long *seed_dev, const uint32_t *dropmask, float *gh2, float *pb2,
+                                float *dW1_partials, float *gpool, float *dW1, float *db1, float *dbn2_w, float *dbn2_b, float *dW2,
+                                float *db2, float *dbn3_w, float *dbn3_b, float *dWf, float *dbf, cudaStream_t stream);
+int explainn_conv_pool_bwd_phase(int phases, long long n_pos_total, const uint32_t *codes, const uint32_t *nmask, long long B, int L,
+                                 int U, int F, const float *gpool, const float *pooled, const float *xhat, const unsigned char *idx,
+                                 const int *M, const float *Mw, const float *bias, const float *mean, const float *var,
+                                 const float *gamma, float eps, float *partial, int nsplit, float *dW, float *dbias, float *dgamma,
+                                 float *dbeta, cudaStream_t stream);
+
 /* ---- backward of conv + BN + exp + maxpool (autograd of networks.py:98-102) ----------------------------------
  * Only the pool-argmax positions carry gradient (sparse scatter); the dense BatchNorm correction comes from
  * M / Mw.  partial: (nsplit, U, 4F+2) floats of scratch with nsplit = explainn_conv_bwd_nsplit(U).

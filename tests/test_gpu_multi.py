@@ -142,3 +142,104 @@ def test_model_on_non_current_device():
     torch.nn.functional.mse_loss(m1(x.to("cuda:1")), y).backward()
     assert all(torch.isfinite(p.grad).all() for p in m1.parameters())
     assert torch.cuda.current_device() == 0
+
+
+SYNC_WORKER = r'''
+import os, sys, traceback
+def _hook(t, v, tb):
+    open(sys.argv[2] + ".err%s" % os.environ.get("RANK", "0"), "w").write("".join(traceback.format_exception(t, v, tb)))
+    sys.__excepthook__(t, v, tb)
+sys.excepthook = _hook
+import numpy as np
+import torch, torch.distributed as dist
+sys.path.insert(0, sys.argv[1]); sys.path.insert(0, os.path.join(sys.argv[1], "tests"))
+from util import onehot_from_codes, random_codes
+from explainn_b200 import networks, train as xtrain
+from oracle import torch_port as tp
+rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+torch.cuda.set_device(rank)
+dev = "cuda:%d" % rank
+dist.init_process_group("nccl", device_id=torch.device(dev))
+U, L, C, F, Bl = 20, 80, 3, 19, 48
+torch.manual_seed(0)
+port = tp.PortExplaiNN(U, L, C, F)
+gen = torch.Generator().manual_seed(8)
+for mod in port.modules():
+    if isinstance(mod, torch.nn.BatchNorm1d):
+        mod.weight.data.uniform_(0.5, 1.5, generator=gen)
+        mod.bias.data.normal_(0, 0.1, generator=gen)
+m = networks.ExplaiNN(U, L, C, F)
+m.load_state_dict(port.state_dict())
+m = m.to(dev).train()
+m.sync_bn = True
+m.linears[9].eval()
+port.train(); port.linears[9].eval()
+x = torch.from_numpy(onehot_from_codes(random_codes(Bl * world, L, 10, n_frac=0.01)))
+y = (torch.rand(Bl * world, C, generator=gen) < 0.5).float()
+crit = torch.nn.BCEWithLogitsLoss()
+# the reference step on the CONCATENATED batch (single device)
+out_p = port(x)
+lp = crit(out_p, y)
+lp.backward()
+xs, ys = x[rank * Bl:(rank + 1) * Bl].to(dev), y[rank * Bl:(rank + 1) * Bl].to(dev)
+out = m(xs)
+lm = crit(out, ys)
+lm.backward()
+def close(a, b, tol, what):
+    a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
+    err = np.abs(a - b).max() / max(np.abs(b).max(), 1e-30)
+    assert err <= tol, "%s: %.3e of scale (tol %.1e)" % (what, err, tol)
+close(out.detach().cpu().numpy(), out_p.detach().numpy()[rank * Bl:(rank + 1) * Bl], 1e-4, "logits")
+lsum = lm.detach().clone(); dist.all_reduce(lsum); lsum /= world
+assert abs(float(lsum) - float(lp)) <= 1e-5 * abs(float(lp)), "loss"
+zero = ("linears.0.bias", "linears.6.bias", "linears.10.bias")
+dgam = float(port.linears[1].weight.grad.abs().max())
+for (k, p), (_, q) in zip(port.named_parameters(), m.named_parameters()):
+    g = q.grad.detach().clone(); dist.all_reduce(g); g /= world           # what the data-parallel step applies
+    g, ref = g.cpu().numpy(), p.grad.numpy()
+    if k in zero:
+        assert np.abs(g).max() == 0.0, k
+    elif k == "linears.1.bias":
+        assert np.abs(g).max() < 1e-3 * dgam, k
+    else:
+        d = np.abs(g - ref); scale = np.abs(ref).max()
+        assert np.quantile(d, 0.98) <= 1e-4 * scale and d.max() <= 2e-2 * scale, (k, float(np.quantile(d, 0.98) / scale), float(d.max() / scale))
+for (k, a), (_, b) in zip(port.state_dict().items(), m.state_dict().items()):
+    if "running" in k:
+        close(b.cpu().numpy(), a.numpy(), 1e-5, k)
+# without sync_bn the local statistics give different logits (the test would be vacuous otherwise)
+m.sync_bn = False
+with torch.no_grad():
+    out_local = m(xs)
+assert float((out_local - out.detach()).abs().max()) > 1e-3 * float(out.detach().abs().max())
+# the fused trainer takes the same path (eager): replicas stay identical, loss equals the reference's
+m2 = networks.ExplaiNN(U, L, C, F); m2.load_state_dict(port.state_dict()); m2 = m2.to(dev).train(); m2.sync_bn = True; m2.linears[9].eval()
+opt = torch.optim.Adam(m2.parameters(), lr=1e-3)
+tr = xtrain.FusedTrainer(m2, crit, opt)
+l1 = tr.step(xs, ys).clone(); dist.all_reduce(l1); l1 /= world
+l2 = tr.step(xs, ys)
+assert tr._graph is None and abs(float(l1) - float(lp)) <= 1e-5 * abs(float(lp)), "fused loss"
+torch.cuda.synchronize()
+flat = tr.flat_p.clone(); others = [torch.empty_like(flat) for _ in range(world)]; dist.all_gather(others, flat)
+assert all(torch.equal(o, others[0]) for o in others), "replicas diverged"
+if rank == 0:
+    open(sys.argv[2], "w").write("ok\n")
+dist.barrier()
+dist.destroy_process_group()
+'''
+
+
+def test_sync_bn_equals_reference_on_concatenated_batch(tmp_path):
+    """model.sync_bn = True under two ranks: logits, loss, rank-averaged gradients and BatchNorm running statistics equal
+    the reference step on the CONCATENATED batch on one device (the port), which local statistics do not."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    script = tmp_path / "worker.py"
+    script.write_text(SYNC_WORKER)
+    out = tmp_path / "out.txt"
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+           "--master-port", "29537", str(script), ROOT, str(out)]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
+    errs = "".join(p.read_text() for p in sorted(tmp_path.glob("out.txt.err*")))
+    assert r.returncode == 0, errs + r.stdout[-1000:] + r.stderr[-1000:]
+    assert out.read_text().strip() == "ok"
