@@ -1026,6 +1026,26 @@ extern "C" int explainn_linear_bwd(const float *glogits, const float *unit, cons
     return xb_check_launch("linear_bwd");
 }
 
+// One side stream per device for kernels that are independent of the main chain of a call (created on first use, kept
+// until the process ends: the library's only long-lived CUDA objects besides the static scratch of the no-alloc entry).
+struct SideStream { cudaStream_t stream; cudaEvent_t fork, join; };
+static SideStream *side_stream_for_current_device()
+{
+    static SideStream table[64];
+    static bool ready[64];
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+    if (!__atomic_load_n(&ready[dev], __ATOMIC_ACQUIRE)) {
+        SideStream t;
+        if (cudaStreamCreateWithFlags(&t.stream, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
+        if (cudaEventCreateWithFlags(&t.fork, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+        if (cudaEventCreateWithFlags(&t.join, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+        table[dev] = t;          // two racing threads would each create a set; the later store wins, the other set leaks once
+        __atomic_store_n(&ready[dev], true, __ATOMIC_RELEASE);
+    }
+    return &table[dev];
+}
+
 // phases: 1 = final-Linear gradients, d/d unit, BatchNorm-3 sums; 2 = BatchNorm-3 backward, FC2 backward + BatchNorm-2 sums
 // (pb2); 4 = FC1 backward + dW1 reduction.  phases == 7 runs the fused BatchNorm-3 kernel; otherwise the BatchNorm-3 sums
 // travel through the first 2U floats of pb2 between phases 1 and 2 (the caller may average them over ranks there).
@@ -1047,13 +1067,23 @@ static int fc_stack_bwd_impl(int phases, const float *glogits, long long B, int 
     // gz3 (B,U) lives in the head of the gpool buffer (U*B*P floats >= B*U); it is consumed by bwd_bn3_kernel
     // before bwd_fc1_kernel overwrites gpool
     float *gz3 = gpool;
+    // The final-Linear weight gradient depends on nothing the rest of this backward produces: in the unphased call it runs
+    // on a side stream (fork here, join at the end; the same pattern is legal inside a CUDA-graph capture).
+    SideStream *side = (phases == 7 && Wf && (dWf || dbf)) ? side_stream_for_current_device() : nullptr;
     if (phases & 1) {
         // Wf == NULL: glogits is the gradient w.r.t. the unit outputs (B,U) and the final layer is skipped
-        if (Wf) {
-            if (dWf) cudaMemsetAsync(dWf, 0, (size_t)C * U * sizeof(float), stream);
-            if (dbf) cudaMemsetAsync(dbf, 0, (size_t)C * sizeof(float), stream);
+        if (Wf && (dWf || dbf)) {
+            cudaStream_t s2 = stream;
+            if (side) {
+                cudaEventRecord(side->fork, stream);
+                cudaStreamWaitEvent(side->stream, side->fork, 0);
+                s2 = side->stream;
+            }
+            if (dWf) cudaMemsetAsync(dWf, 0, (size_t)C * U * sizeof(float), s2);
+            if (dbf) cudaMemsetAsync(dbf, 0, (size_t)C * sizeof(float), s2);
             const int nsb = (int)std::min<long long>(8, (B + 63) / 64);
-            bwd_final_linear2_kernel<<<dim3((U + 127) / 128, (C + 7) / 8, nsb), 128, 0, stream>>>(glogits, unit, B, U, C, dWf, dbf);
+            bwd_final_linear2_kernel<<<dim3((U + 127) / 128, (C + 7) / 8, nsb), 128, 0, s2>>>(glogits, unit, B, U, C, dWf, dbf);
+            if (side) cudaEventRecord(side->join, side->stream);
         }
         const size_t smem_gu = ((size_t)8 * C + (size_t)C * GU_UT) * 4;
         if (smem_gu > 200 * 1024) {
@@ -1092,6 +1122,7 @@ static int fc_stack_bwd_impl(int phases, const float *glogits, long long B, int 
         return XB_ERR_UNSUPPORTED;
     }
 #undef XB_LAUNCH_BWD_FC1
+    if (side) cudaStreamWaitEvent(stream, side->join, 0);
     int rc = xb_check_launch("fc_stack_bwd");
     if (rc != XB_OK) return rc;
     // dW1 = sum over batch chunks of the per-tile partials

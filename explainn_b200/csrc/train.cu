@@ -26,6 +26,17 @@ namespace {
 //   M[(c,k),(c',k')] += popcount( (I_c >> k) & (I_c' >> k') & [s < S] )
 // 32 positions per AND+POPC, counters in registers, one atomicAdd per counter and CTA at the end.
 // ------------------------------------------------------------------------------------------------
+// the 16 even-position bits of x packed into the low half (Morton decode)
+__device__ __forceinline__ uint32_t even_bits(uint32_t x)
+{
+    x &= 0x55555555u;
+    x = (x | (x >> 1)) & 0x33333333u;
+    x = (x | (x >> 2)) & 0x0F0F0F0Fu;
+    x = (x | (x >> 4)) & 0x00FF00FFu;
+    x = (x | (x >> 8)) & 0x0000FFFFu;
+    return x;
+}
+
 __global__ void __launch_bounds__(320) cooc_kernel(const uint32_t *__restrict__ codes, const uint32_t *__restrict__ nmask,
                                                    long long B, int L, int F, int wc, int wm, int *__restrict__ M)
 {
@@ -57,11 +68,7 @@ __global__ void __launch_bounds__(320) cooc_kernel(const uint32_t *__restrict__ 
                 const uint32_t pat = 0x55555555u * (uint32_t)c;
                 const uint32_t x0 = c0 ^ pat, x1 = c1 ^ pat;
                 const uint32_t z0 = ~(x0 | (x0 >> 1)) & 0x55555555u, z1 = ~(x1 | (x1 >> 1)) & 0x55555555u;   // bit 2j set iff code j == c
-#pragma unroll
-                for (int j = 0; j < 16; ++j) {
-                    bits |= ((z0 >> (2 * j)) & 1u) << j;
-                    bits |= ((z1 >> (2 * j)) & 1u) << (16 + j);
-                }
+                bits = even_bits(z0) | (even_bits(z1) << 16);
                 bits &= ~nmask[b * wm + w];
                 if (32 * w + 32 > L) bits &= (L - 32 * w >= 32) ? 0xFFFFFFFFu : ((1u << (L - 32 * w)) - 1u);
             }
@@ -434,7 +441,7 @@ extern "C" int explainn_input_cooc_stats(const uint32_t *codes, const uint32_t *
     const int npairs = F * (F + 1) / 2;
     const int NT = ((npairs + 31) / 32) * 32;
     const size_t smem = (size_t)4 * (xb_words_mask(L) + 1) * 4;
-    int grid = xb_num_sms();
+    int grid = 2 * xb_num_sms();         // the kernel is latency-bound (6 warps per CTA): two CTAs per SM
     if (grid > B) grid = (int)B;
     cudaFuncSetAttribute(cooc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     cooc_kernel<<<grid, NT, smem, stream>>>(codes, nmask, B, L, F, xb_words_codes(L), xb_words_mask(L), M);

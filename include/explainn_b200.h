@@ -11,7 +11,10 @@
  *   - Every call is asynchronous on `stream` and re-entrant (no global mutable state).
  *   - Exceptions to the two rules above, each documented at its declaration: explainn_p2p_alloc / _free / _open /
  *     _close (CUDA-IPC peer buffers are allocated and mapped here), explainn_p2p_error (synchronous 4-byte read) and
- *     explainn_interp_unit_max_noalloc (scratch in a library-owned static device array shared by all calls on a GPU).
+ *     explainn_interp_unit_max_noalloc (scratch in a library-owned static device array shared by all calls on a GPU),
+ *     and explainn_fc_stack_bwd, which runs its final-Linear weight gradient on a library-owned side stream per device
+ *     (forked from and joined back into `stream` inside the call; created on the first call on a device, so make that
+ *     first call outside stream capture; do not run the call from two host threads on one device at the same time).
  *   - Return value 0 = success; otherwise an EXPLAINN_ERR_* code and explainn_last_error() (thread-local)
  *     describes the failure.  No C++ exception crosses this boundary.
  *   - Tensors are dense row-major with the shapes given, fp32 unless stated otherwise.
