@@ -305,12 +305,16 @@ def train_backward_conv(model, ws, gpool, params, grads, wrt_unit=False):
     dWf, dbf = grads[-2], grads[-1]
     B, U, F = ws.B, ws.U, ws.F
     f32 = dict(dtype=torch.float32, device=gpool.device)
-    nsplit = Fn._cabi.lib.explainn_conv_bwd_nsplit(U)
+    dsync, world = _sync_group(model) if getattr(ws, "sync_world", 1) > 1 else (None, 1)
+    nsplit = Fn._cabi.lib.explainn_conv_bwd_nsplit(U)          # one slice per SM: the tensor-core scatter
+    if dsync is not None:
+        # `partial` is all-reduced between the two phases: few slices (the shared-memory scatter kernel)
+        sms = torch.cuda.get_device_properties(gpool.device).multi_processor_count
+        nsplit = min(nsplit, max(1, -(-5 * sms // U)))
     partial = torch.empty((nsplit, U, 4 * F + 2), **f32)
     cargs = (ptr(ws.pk.codes), ptr(ws.pk.nmask), B, ws.pk.L, U, F, ptr(gpool), ptr(ws.pooled),
              ptr(ws.xhat), ptr(ws.idx), ptr(ws.M), ptr(ws.Mw), ptr(cb), ptr(ws.mean1), ptr(ws.var1), ptr(g1),
              float(L[1].eps), ptr(partial), nsplit, ptr(dcw), ptr(dcb), ptr(dg1), ptr(db1n), stream())
-    dsync, world = _sync_group(model) if getattr(ws, "sync_world", 1) > 1 else (None, 1)
     if dsync is None:
         call("explainn_conv_pool_bwd", *cargs)
     else:

@@ -26,6 +26,10 @@ int xb_hit_count(const uint32_t *codes, const uint32_t *nmask, long long B, int 
                  const unsigned char *flags, unsigned char *seq_hit_out, unsigned long long *counts, unsigned long long *hits,
                  cudaStream_t stream);
 long long xb_pwm_count_layout(long long B, int L, int U, int F, long long *off_bmask, long long *off_bits);
+// conv_bwd_tc.cu, used by train.cu: slices of `partial` the tensor-core scatter writes (0 = shape not handled); launch
+int xb_conv_bwd_tc_slices(long long B, int L, int U, int F, int nsplit, const void *gpool, const void *pooled, const void *xhat);
+int xb_conv_bwd_tc(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F, const float *gpool, const float *pooled,
+                   const float *xhat, const unsigned char *idx, float *partial, int nsplit, cudaStream_t stream);
 
 #define XB_REQUIRE(cond, ...)                         \
     do {                                              \

@@ -301,41 +301,46 @@ __global__ void __launch_bounds__(BW_WARPS * 32) conv_bwd_sparse_kernel(
     }
 }
 
-// dense correction + assembly of the conv/BN-1 parameter gradients (one block per unit)
-__global__ void __launch_bounds__(128) conv_bwd_final_kernel(const float *__restrict__ partial, int nsplit, int U, int F,
-                                                             const int *__restrict__ M, const float *__restrict__ Mw,
-                                                             const float *__restrict__ bias, const float *__restrict__ mean,
-                                                             const float *__restrict__ var, const float *__restrict__ gamma,
-                                                             float eps, double N, float *__restrict__ dW,
-                                                             float *__restrict__ dbias, float *__restrict__ dgamma,
-                                                             float *__restrict__ dbeta)
+// dense correction + assembly of the conv/BN-1 parameter gradients (one block per unit).  The `nsplit` slices of
+// `partial` (one per CTA of the scatter kernel: up to one per SM) are summed by four thread rows, slices c = r, r + 4, ...
+// each, then across the rows in a fixed order.
+constexpr int BF_COLS = 128;        // >= 4F + 2 (filter_size <= 24)
+__global__ void __launch_bounds__(4 * BF_COLS) conv_bwd_final_kernel(const float *__restrict__ partial, int nsplit, int U, int F,
+                                                                     const int *__restrict__ M, const float *__restrict__ Mw,
+                                                                     const float *__restrict__ bias, const float *__restrict__ mean,
+                                                                     const float *__restrict__ var, const float *__restrict__ gamma,
+                                                                     float eps, double N, float *__restrict__ dW,
+                                                                     float *__restrict__ dbias, float *__restrict__ dgamma,
+                                                                     float *__restrict__ dbeta)
 {
     const int u = blockIdx.x, W = 4 * F;
-    __shared__ double s_dg, s_db;
-    if (threadIdx.x == 0) {
-        double dg = 0.0, db = 0.0;
-        for (int c = 0; c < nsplit; ++c) {
-            dg += (double)partial[((size_t)c * U + u) * (W + 2) + W];
-            db += (double)partial[((size_t)c * U + u) * (W + 2) + W + 1];
-        }
-        s_dg = dg; s_db = db;
+    const int i = threadIdx.x & (BF_COLS - 1), r = threadIdx.x / BF_COLS;
+    __shared__ double part[4][BF_COLS];
+    double acc = 0.0;
+    if (i < W + 2) {
+        const float *src = partial + (size_t)u * (W + 2) + i;
+#pragma unroll 4
+        for (int c = r; c < nsplit; c += 4) acc += (double)src[(size_t)c * U * (W + 2)];
+    }
+    part[r][i] = acc;
+    __syncthreads();
+    if (r != 0 || i >= W + 2) return;
+    const double A = ((part[0][i] + part[1][i]) + part[2][i]) + part[3][i];
+    const double dg = ((part[0][W] + part[1][W]) + part[2][W]) + part[3][W];
+    const double db = ((part[0][W + 1] + part[1][W + 1]) + part[2][W + 1]) + part[3][W + 1];
+    if (i == W) {
         if (dgamma) dgamma[u] = (float)dg;
-        if (dbeta) dbeta[u] = (float)db;
         if (dbias) dbias[u] = 0.0f;      // exactly zero: the bias is followed by a train-mode BatchNorm
     }
-    __syncthreads();
-    if (!dW) return;
+    if (i == W + 1 && dbeta) dbeta[u] = (float)db;
+    if (!dW || i >= W) return;
     const double inv = 1.0 / sqrt((double)var[u] + (double)eps);
     const double mc = (double)mean[u] - (double)bias[u];
-    const double m1 = s_db / N, m2 = s_dg / N;
+    const double m1 = db / N, m2 = dg / N;
     const double g = (double)gamma[u] * inv;
-    for (int i = threadIdx.x; i < W; i += blockDim.x) {
-        double A = 0.0;
-        for (int c = 0; c < nsplit; ++c) A += (double)partial[((size_t)c * U + u) * (W + 2) + i];
-        const double cnt = (double)M[(size_t)i * W + i];
-        const double R = inv * ((double)Mw[(size_t)u * W + i] - mc * cnt);
-        dW[(size_t)u * W + i] = (float)(g * (A - m1 * cnt - m2 * R));
-    }
+    const double cnt = (double)M[(size_t)i * W + i];
+    const double R = inv * ((double)Mw[(size_t)u * W + i] - mc * cnt);
+    dW[(size_t)u * W + i] = (float)(g * (A - m1 * cnt - m2 * R));
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -459,11 +464,20 @@ extern "C" int explainn_bn1_batch_stats(const int *M, const float *w, const floa
     return xb_check_launch("bn1_batch_stats");
 }
 
-extern "C" int explainn_conv_bwd_nsplit(int U)
+// slices of `partial` for conv_bwd_sparse_kernel
+static int sparse_nsplit(int U)
 {
     const int target = 5 * xb_num_sms();     // 5 CTAs of 4 warps fit on an SM (39 KB of accumulators each)
     int ns = (target + U - 1) / U;
     return ns < 1 ? 1 : ns;
+}
+
+// slices to allocate: one per SM selects the tensor-core scatter (conv_bwd_tc.cu) where the shape allows it; a caller
+// may pass any smaller nsplit >= 1 (synchronised BatchNorm does, to keep the all-reduced buffer small) and gets the
+// shared-memory scatter kernel
+extern "C" int explainn_conv_bwd_nsplit(int U)
+{
+    return std::max(sparse_nsplit(U), xb_num_sms());
 }
 
 // phases: 1 = sparse scatter into `partial`, 2 = dense correction + assembly; n_pos_total = B*S of the batch the
@@ -487,7 +501,14 @@ static int conv_pool_bwd_impl(int phases, long long n_pos_total, const uint32_t 
         conv_bwd_sparse_kernel<FTV><<<dim3(U, nsplit), BW_WARPS * 32, smem, stream>>>(                                        \
             codes, nmask, B, L, F, P, xb_words_codes(L), xb_words_mask(L), gpool, pooled, xhat, idx, idx16, pstride, partial, U); \
     } while (0)
-    if (phases & 1) {
+    // both phases derive the slice count from the same arguments: the tensor-core scatter (default pool, one slice per
+    // CTA) when the caller's `partial` has room for it, else the shared-memory scatter
+    const int tc_slices = (idx && psize == XB_POOL && pstride == XB_POOL) ? xb_conv_bwd_tc_slices(B, L, U, F, nsplit, gpool, pooled, xhat) : 0;
+    nsplit = tc_slices > 0 ? tc_slices : std::min(nsplit, sparse_nsplit(U));
+    if ((phases & 1) && tc_slices > 0) {
+        int rc = xb_conv_bwd_tc(codes, nmask, B, L, U, F, gpool, pooled, xhat, idx, partial, nsplit, stream);
+        if (rc != XB_OK) return rc;
+    } else if (phases & 1) {
         if (F == 19) XB_LAUNCH_SPARSE(19);
         else if (F == 20) XB_LAUNCH_SPARSE(20);
         else XB_LAUNCH_SPARSE(0);
@@ -497,7 +518,7 @@ static int conv_pool_bwd_impl(int phases, long long n_pos_total, const uint32_t 
 #undef XB_LAUNCH_SPARSE
     if (phases & 2) {
         const double N = n_pos_total > 0 ? (double)n_pos_total : (double)B * S;
-        conv_bwd_final_kernel<<<U, 128, 0, stream>>>(partial, nsplit, U, F, M, Mw, bias, mean, var, gamma, eps, N, dW, dbias, dgamma, dbeta);
+        conv_bwd_final_kernel<<<U, 4 * BF_COLS, 0, stream>>>(partial, nsplit, U, F, M, Mw, bias, mean, var, gamma, eps, N, dW, dbias, dgamma, dbeta);
     }
     return xb_check_launch("conv_bwd_final");
 }

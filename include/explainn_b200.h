@@ -346,7 +346,11 @@ int explainn_conv_pool_bwd_phase(int phases, long long n_pos_total, const uint32
 
 /* ---- backward of conv + BN + exp + maxpool (autograd of networks.py:98-102) ----------------------------------
  * Only the pool-argmax positions carry gradient (sparse scatter); the dense BatchNorm correction comes from
- * M / Mw.  partial: (nsplit, U, 4F+2) floats of scratch with nsplit = explainn_conv_bwd_nsplit(U).
+ * M / Mw.  partial: (nsplit, U, 4F+2) floats of scratch.  nsplit = explainn_conv_bwd_nsplit(U) (one slice per SM)
+ * selects the tensor-core scatter (csrc/conv_bwd_tc.cu: the sum over the argmax positions as a per-sequence GEMM, gz
+ * in three bfloat16 pieces written straight into tensor memory) for the default pool when (U*P) % 4 == 0 and
+ * gpool / pooled / xhat are 16-byte aligned; any smaller nsplit >= 1, or any other shape, runs the shared-memory
+ * scatter kernel (csrc/train.cu).  Both are deterministic; they differ in summation order only.
  * Outputs dW (U,4,F), dbias (U, exact zeros), dgamma (U), dbeta (U); each may be NULL. */
 int explainn_conv_bwd_nsplit(int U);
 int explainn_conv_pool_bwd(const uint32_t *codes, const uint32_t *nmask, long long B, int L, int U, int F,
