@@ -293,7 +293,7 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bwd_fc1_tc_kernel(const FcBwdAr
     __shared__ uint32_t tmem_base_s;
     // per hidden channel: zb = h*c1 + c0 ;  G = h*cB + cC + (zb > 0 && kept ? gh2[row] * cA : 0)
     __shared__ float c1s[128], c0s[128], cAs[128], cBs[128], cCs[128];
-    __shared__ __align__(16) uint32_t msk[FT_ROWS][4];
+    __shared__ __align__(16) uint32_t msk[2][FT_ROWS][4];       // dropout keep bits of the tile's rows: this tile / the next one
 
     unsigned char *sR = smem;                                   // phase 1: G hi | G lo ; phase 2: Gt hi | Gt lo
     unsigned char *sAh = sR + 2 * BT_GT_BYTES, *sAl = sAh + BT_A_BYTES;
@@ -305,7 +305,7 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bwd_fc1_tc_kernel(const FcBwdAr
     unsigned char *sWh = sAh + BT_H_BYTES + BT_S_BYTES, *sWl = sWh + BT_W_BYTES;
     static_assert(BT_H_BYTES >= 2 * BT_A_BYTES && BT_GT_BYTES == BT_G_BYTES, "shared-memory plan");
     __shared__ __align__(8) uint64_t bar_h;
-    __shared__ float gh2s[FT_ROWS];
+    __shared__ float gh2s[2][FT_ROWS];                          // upstream gradient of the tile's rows: this tile / the next one
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const bool worker = warp < FT_THREADS / 32;
     const unsigned long long seed = a.seed0 + (a.seed_dev ? *a.seed_dev * 0xD1B54A32D192ED03ull : 0ull);
@@ -339,6 +339,34 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bwd_fc1_tc_kernel(const FcBwdAr
     const long long total = (long long)a.U * a.nchunk;
     const long long t_begin = total * blockIdx.x / gridDim.x, t_end = total * (blockIdx.x + 1) / gridDim.x;
     int cur_u = -1;
+    // upstream gradient and dropout keep bits of the rows of tile `t` into buffer `buf` (threads 0..127, one row each)
+    auto row_data = [&](long long t, int buf) {
+        if (threadIdx.x >= FT_ROWS) return;
+        const int r = threadIdx.x;
+        const int tu = (int)(t / a.nchunk);
+        const long long tb0 = (t - (long long)tu * a.nchunk) * FT_ROWS;
+        const int trows = (int)min((long long)FT_ROWS, a.B - tb0);
+        const size_t e = (size_t)tu * a.B + tb0 + r;
+        if (r < trows) {
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(&gh2s[buf][r])), "l"(a.gh2 + e) : "memory");
+        } else {
+            gh2s[buf][r] = 0.f;
+        }
+        if (a.pdrop > 0.f && r < trows && a.dropmask) {
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(&msk[buf][r][0])), "l"(a.dropmask + e * 4) : "memory");
+        } else {
+            uint4 mw = make_uint4(~0u, ~0u, ~0u, ~0u);
+            if (a.pdrop > 0.f && r < trows) {     // no saved keep bits: regenerate them from the counter hash (slow path)
+                uint32_t w[4] = {0u, 0u, 0u, 0u};
+                for (int qd = 0; qd < H / 4; ++qd) w[qd >> 3] |= drop_keep4(seed, e * (H / 4) + qd, thresh) << (4 * (qd & 7));
+                mw = make_uint4(w[0], w[1], w[2], w[3]);
+            }
+            *reinterpret_cast<uint4 *>(&msk[buf][r][0]) = mw;
+        }
+    };
+    if (t_begin < t_end) row_data(t_begin, 0);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
     for (long long tile = t_begin; tile < t_end; ++tile) {
         const int u = (int)(tile / a.nchunk), chunk = (int)(tile - (long long)u * a.nchunk);
         const long long b0 = (long long)chunk * FT_ROWS;
@@ -348,22 +376,23 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bwd_fc1_tc_kernel(const FcBwdAr
             mbar_arrive_expect_tx(&bar_h, (uint32_t)rows * H * 4);
             tma_bulk_g2s(sH, a.h1 + ((size_t)u * a.B + b0) * H, (uint32_t)rows * H * 4, &bar_h);
         }
-        if (threadIdx.x < FT_ROWS) {
-            const int r = threadIdx.x;
-            gh2s[r] = r < rows ? a.gh2[(size_t)u * a.B + b0 + r] : 0.f;
-            uint4 mw = make_uint4(~0u, ~0u, ~0u, ~0u);
-            if (a.pdrop > 0.f && r < rows) {
-                if (a.dropmask) {
-                    mw = *reinterpret_cast<const uint4 *>(a.dropmask + ((size_t)u * a.B + b0 + r) * 4);
-                } else {          // no saved keep bits: regenerate them from the counter hash (slow path)
-                    uint32_t w[4] = {0u, 0u, 0u, 0u};
-                    for (int qd = 0; qd < H / 4; ++qd)
-                        w[qd >> 3] |= drop_keep4(seed, ((size_t)u * a.B + b0 + r) * (H / 4) + qd, thresh) << (4 * (qd & 7));
-                    mw = make_uint4(w[0], w[1], w[2], w[3]);
-                }
+        // per-row data of the NEXT tile (asynchronous copies, consumed after the barrier at the top of that tile) and the
+        // pooled tile of THIS one, raw (row, p) layout, into the output staging buffer: both fly during the G build
+        const int rb = (int)((tile - t_begin) & 1);
+        if (tile + 1 < t_end) row_data(tile + 1, rb ^ 1);
+        if (worker) {
+            const float *psrc = a.pooled + ((size_t)b0 * a.U + u) * a.P;
+            const size_t rstride = (size_t)a.U * a.P;
+            const int n = rows * a.P, dr = FT_THREADS / a.P, dp = FT_THREADS - dr * a.P;
+            int rr = threadIdx.x / a.P, pp = threadIdx.x - rr * a.P;
+            const uint32_t d0 = smem_u32(sS);
+            for (int i = threadIdx.x; i < n; i += FT_THREADS) {
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d0 + 4u * i), "l"(psrc + rr * rstride + pp) : "memory");
+                rr += dr; pp += dp;
+                if (pp >= a.P) { pp -= a.P; ++rr; }
             }
-            *reinterpret_cast<uint4 *>(&msk[r][0]) = mw;
         }
+        asm volatile("cp.async.commit_group;" ::: "memory");
         if (u != cur_u) {
             if (threadIdx.x < 128) {
                 const int j = threadIdx.x, ch = u * H + j;
@@ -443,8 +472,8 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bwd_fc1_tc_kernel(const FcBwdAr
 #pragma unroll
             for (int g = 0; g < BT_RG; ++g) {
                 const int rg = rg0 + g, r = rg * 8 + rl;
-                const float gh = gh2s[r];
-                const uint4 mw = *reinterpret_cast<const uint4 *>(&msk[r][0]);
+                const float gh = gh2s[rb][r];
+                const uint4 mw = *reinterpret_cast<const uint4 *>(&msk[rb][r][0]);
                 const uint32_t mws[4] = {mw.x, mw.y, mw.z, mw.w};
 #pragma unroll
                 for (int t = 0; t < BT_KT; ++t) {
@@ -463,6 +492,7 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bwd_fc1_tc_kernel(const FcBwdAr
                 }
             }
         }
+        asm volatile("cp.async.wait_group 0;" ::: "memory");      // pooled tile and the next tile's row data have landed
         fence_proxy_async();
         tc_fence_before();
         __syncthreads();
@@ -483,14 +513,12 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bwd_fc1_tc_kernel(const FcBwdAr
         if (worker) {
             constexpr int NIT = (BT_P / 8) * (FT_ROWS / 4) / (FT_THREADS / 32);     // 24 core matrices per warp
             float xv[NIT];
-            const float *psrc = a.pooled + ((size_t)b0 * a.U + u) * a.P;
-            const int rstride = a.U * a.P;
 #pragma unroll
             for (int i = 0; i < NIT; ++i) {
                 const int cm = warp + (FT_THREADS / 32) * i;
                 const int pg = cm / (FT_ROWS / 4), bc = cm - pg * (FT_ROWS / 4);
                 const int p = pg * 8 + (lane >> 2), r = bc * 4 + (lane & 3);
-                xv[i] = (r < rows && p < a.P) ? __ldg(psrc + (size_t)r * rstride + p) : 0.f;
+                xv[i] = (r < rows && p < a.P) ? sS[r * a.P + p] : 0.f;       // staged by the copies issued at the top of the tile
             }
 #pragma unroll
             for (int i = 0; i < NIT; ++i) st_split(sAh, sAl, (uint32_t)(warp + (FT_THREADS / 32) * i) * 128 + lane * 4, xv[i]);
