@@ -273,364 +273,411 @@ __device__ __forceinline__ void st_split(unsigned char *hi, unsigned char *lo, u
     *reinterpret_cast<float *>(lo + off) = x - xh;
 }
 
-// Phase clocks (experiments only, compiled in with -DXB_PHASE_CLOCKS): thread 0 of CTA 0 records clock64() at the
-// phase boundaries of its first tiles; tools/phase_clocks.py prints the per-phase cycle counts.
-#ifdef XB_PHASE_CLOCKS
-__device__ long long g_phase_clk[32 * 16];
-#define XB_PHASE(i) do { if (blockIdx.x == 0 && threadIdx.x == 0 && tile - t_begin < 32) g_phase_clk[(tile - t_begin) * 16 + (i)] = clock64(); } while (0)
-#else
-#define XB_PHASE(i) do { } while (0)
-#endif
+// Three kinds of warps, so that the phases of consecutive tiles overlap:
+//   warps 0..7   workers: the h1 tile from its staging buffer into registers, G arithmetic, G stored j-contiguous (D1), then, once D1 has retired, the same
+//                values b-contiguous (D2) over the same region
+//   warp  12     issues the tcgen05.mma of D1 and D2 into one of two accumulator pairs, commits them to mbarriers and, once
+//                a D2 has retired, the TMA bulk copy of the next tile's h1 rows
+//   warps 8..11  helpers: pooled tile (global -> registers at the top of the tile, transposed hi/lo operand once the
+//                previous D2 has retired), then both drains (tensor memory -> staging -> coalesced global stores) while
+//                the workers are already on the next tile
+// Registers: the kernel starts with 128 per thread (16 warps); each group of four warps then re-sizes its share
+// (setmaxnreg): workers 192 (their 56 G values and 35 coefficients stay in registers), helpers 96, the issue warp's
+// group (three of its warps only wait at the final barrier) 24.
+constexpr int BT_HW = 4;
+constexpr int BT_THREADS = 512;
+constexpr int BT_ISSUE = FT_THREADS / 32 + BT_HW;             // warp 12
+constexpr int BT_WI = FT_THREADS + 32;                        // workers + issue warp: named barrier 1
 
-// 8 worker warps (builds, fills, drains) + 1 issue warp: the tcgen05.mma issue of one product takes about as long as the
-// product itself (the issuing thread blocks on the MMA queue), so it runs beside the workers' next fill / drain.
-constexpr int BT_THREADS = FT_THREADS + 32;
+__device__ __forceinline__ void bt_bar(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
+
+#ifdef XB_PHASE_CLOCKS
+__device__ long long g_bt_clk[3 * 16];
+#define BT_CLK_DECL long long ck_acc[12] = {0}; long long ck_t = clock64()
+#define BT_CLK(i) do { const long long n_ = clock64(); ck_acc[i] += n_ - ck_t; ck_t = n_; } while (0)
+#define BT_CLK_FLUSH(role_, cond) do { if (blockIdx.x == 0 && (cond)) for (int q_ = 0; q_ < 12; ++q_) g_bt_clk[(role_) * 16 + q_] = ck_acc[q_]; } while (0)
+#else
+#define BT_CLK_DECL
+#define BT_CLK(i) do { } while (0)
+#define BT_CLK_FLUSH(role_, cond) do { } while (0)
+#endif
 
 __global__ void __launch_bounds__(BT_THREADS, 1) bwd_fc1_tc_kernel(const FcBwdArgs a)
 {
     extern __shared__ __align__(128) unsigned char smem[];
-    __shared__ __align__(8) uint64_t bar;
+    __shared__ __align__(8) uint64_t d1_full[2], d2_full[2], acc_free[2], at_full, bar_h, h_free;
     __shared__ uint32_t tmem_base_s;
     // per hidden channel: zb = h*c1 + c0 ;  G = h*cB + cC + (zb > 0 && kept ? gh2[row] * cA : 0)
     __shared__ float c1s[128], c0s[128], cAs[128], cBs[128], cCs[128];
     __shared__ __align__(16) uint32_t msk[2][FT_ROWS][4];       // dropout keep bits of the tile's rows: this tile / the next one
-
-    unsigned char *sR = smem;                                   // phase 1: G hi | G lo ; phase 2: Gt hi | Gt lo
-    unsigned char *sAh = sR + 2 * BT_GT_BYTES, *sAl = sAh + BT_A_BYTES;
-    // the h1 tile (128 x 100 floats, contiguous in global memory) is staged by ONE TMA bulk copy into the pooled-tile
-    // buffers (filled only after the G build) plus a 2 KB pad; it is issued as soon as the previous tile's D2 MMAs
-    // have retired, so it flies during that tile's output drain
-    float *sH = reinterpret_cast<float *>(sAh);
-    float *sS = reinterpret_cast<float *>(sAh + BT_H_BYTES);           // staging of D1 / D2 for coalesced stores
-    unsigned char *sWh = sAh + BT_H_BYTES + BT_S_BYTES, *sWl = sWh + BT_W_BYTES;
-    static_assert(BT_H_BYTES >= 2 * BT_A_BYTES && BT_GT_BYTES == BT_G_BYTES, "shared-memory plan");
-    __shared__ __align__(8) uint64_t bar_h;
     __shared__ float gh2s[2][FT_ROWS];                          // upstream gradient of the tile's rows: this tile / the next one
+
+    unsigned char *sR = smem;                                   // G hi | G lo, then Gt hi | Gt lo
+    unsigned char *sAh = sR + 2 * BT_GT_BYTES, *sAl = sAh + BT_A_BYTES;        // pooled tile transposed, hi | lo
+    // the h1 tile (128 x 100 floats, contiguous in global memory) is staged by ONE TMA bulk copy into the pooled-tile
+    // buffers plus a 2 KB pad: issued as soon as the previous tile's D2 (their last reader) has retired, read into
+    // registers by the workers, and only then do the helpers store the pooled operand of this tile over it
+    float *sH = reinterpret_cast<float *>(sAh);
+    float *sS = reinterpret_cast<float *>(sAh + BT_H_BYTES);                   // staging of D1 / D2 for coalesced stores
+    static_assert(BT_H_BYTES >= 2 * BT_A_BYTES, "shared-memory plan");
+    unsigned char *sWh = reinterpret_cast<unsigned char *>(sS) + BT_S_BYTES, *sWl = sWh + BT_W_BYTES;
+    static_assert(BT_GT_BYTES == BT_G_BYTES, "shared-memory plan");
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const bool worker = warp < FT_THREADS / 32;
     const unsigned long long seed = a.seed0 + (a.seed_dev ? *a.seed_dev * 0xD1B54A32D192ED03ull : 0ull);
     const unsigned thresh = a.pdrop > 0.f ? (unsigned)min(4294967295.0, (double)a.pdrop * 4294967296.0) : 0u;
     const float keep_scale = a.pdrop > 0.f ? 1.0f / (1.0f - a.pdrop) : 1.0f;
 
     if (threadIdx.x == 0) {
-        mbar_init(&bar, 1);
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(&d1_full[i], 1);
+            mbar_init(&d2_full[i], 1);
+            mbar_init(&acc_free[i], BT_HW);
+        }
+        mbar_init(&at_full, BT_HW);
         mbar_init(&bar_h, 1);
+        mbar_init(&h_free, 1);
         mbar_fence_init();
     }
-    if (warp == 0) tc_alloc(&tmem_base_s, 256u);
+    if (warp == 0) tc_alloc(&tmem_base_s, 512u);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    const uint32_t tmem_base = tmem_base_s;
+    const uint32_t tmem_base = tmem_base_s;       // accumulator pair b: D1 at columns 256 b, D2 at 256 b + 128
     // The hi and lo tiles of W1t (and of the pooled tile) are adjacent in shared memory, so one MMA with N = 2*BT_P
     // multiplies by [hi ; lo] at once: per K step  X_hi.[Y_hi ; Y_lo] -> columns 0..95  and  X_lo.Y_hi -> columns 0..47.
     // The drain adds column p and column BT_P + p.  (Two MMAs instead of three: a third less operand traffic from
     // shared memory, which is what bounds these products.)
     const uint32_t idesc = tc_idesc(2u, 128, BT_P), idesc2 = tc_idesc(2u, 128, 2 * BT_P);
     static_assert(BT_W_BYTES == (BT_P / 8) * BT_G_SBO && BT_A_BYTES == (BT_P / 8) * BT_B_SBO, "hi/lo tiles must be adjacent row groups");
-    uint32_t parity = 0, h_parity = 0;
-    // operand descriptors of K step 0, computed once in warp-uniform code (see tc_elect_one)
-    const int warp_u = tc_warp_uniform();
-    const uint64_t dG_hi = make_smem_desc(smem_u32(sR), 128, BT_G_SBO), dG_lo = make_smem_desc(smem_u32(sR) + BT_G_BYTES, 128, BT_G_SBO);
-    const uint64_t dW_hi = make_smem_desc(smem_u32(sWh), 128, BT_G_SBO);       // [W1t hi ; W1t lo]: the lo tile follows the hi tile
-    const uint64_t dT_hi = make_smem_desc(smem_u32(sR), 128, BT_B_SBO), dT_lo = make_smem_desc(smem_u32(sR) + BT_GT_BYTES, 128, BT_B_SBO);
-    const uint64_t dA_hi = make_smem_desc(smem_u32(sAh), 128, BT_B_SBO);       // [pooled hi ; pooled lo]
-
+    const int role = tc_warp_uniform();
     const long long total = (long long)a.U * a.nchunk;
     const long long t_begin = total * blockIdx.x / gridDim.x, t_end = total * (blockIdx.x + 1) / gridDim.x;
-    int cur_u = -1;
-    // upstream gradient and dropout keep bits of the rows of tile `t` into buffer `buf` (threads 0..127, one row each)
-    auto row_data = [&](long long t, int buf) {
-        if (threadIdx.x >= FT_ROWS) return;
-        const int r = threadIdx.x;
-        const int tu = (int)(t / a.nchunk);
-        const long long tb0 = (t - (long long)tu * a.nchunk) * FT_ROWS;
-        const int trows = (int)min((long long)FT_ROWS, a.B - tb0);
-        const size_t e = (size_t)tu * a.B + tb0 + r;
-        if (r < trows) {
-            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(&gh2s[buf][r])), "l"(a.gh2 + e) : "memory");
-        } else {
-            gh2s[buf][r] = 0.f;
-        }
-        if (a.pdrop > 0.f && r < trows && a.dropmask) {
-            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(&msk[buf][r][0])), "l"(a.dropmask + e * 4) : "memory");
-        } else {
-            uint4 mw = make_uint4(~0u, ~0u, ~0u, ~0u);
-            if (a.pdrop > 0.f && r < trows) {     // no saved keep bits: regenerate them from the counter hash (slow path)
-                uint32_t w[4] = {0u, 0u, 0u, 0u};
-                for (int qd = 0; qd < H / 4; ++qd) w[qd >> 3] |= drop_keep4(seed, e * (H / 4) + qd, thresh) << (4 * (qd & 7));
-                mw = make_uint4(w[0], w[1], w[2], w[3]);
+
+    if (role >= BT_ISSUE) {
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 24;");
+    }
+    if (role == BT_ISSUE) {
+        // =========================== issue warp ===========================
+        const uint64_t dG_hi = make_smem_desc(smem_u32(sR), 128, BT_G_SBO), dG_lo = make_smem_desc(smem_u32(sR) + BT_G_BYTES, 128, BT_G_SBO);
+        const uint64_t dW_hi = make_smem_desc(smem_u32(sWh), 128, BT_G_SBO);       // [W1t hi ; W1t lo]: the lo tile follows the hi tile
+        const uint64_t dT_hi = make_smem_desc(smem_u32(sR), 128, BT_B_SBO), dT_lo = make_smem_desc(smem_u32(sR) + BT_GT_BYTES, 128, BT_B_SBO);
+        const uint64_t dA_hi = make_smem_desc(smem_u32(sAh), 128, BT_B_SBO);       // [pooled hi ; pooled lo]
+        BT_CLK_DECL;
+        auto load_h1 = [&](long long t) {                        // one lane: h1 rows of tile t -> staging
+            const int tu = (int)(t / a.nchunk);
+            const long long tb0 = (t - (long long)tu * a.nchunk) * FT_ROWS;
+            const uint32_t bytes = (uint32_t)min((long long)FT_ROWS, a.B - tb0) * H * 4;
+            mbar_arrive_expect_tx(&bar_h, bytes);
+            tma_bulk_g2s(sH, a.h1 + ((size_t)tu * a.B + tb0) * H, bytes, &bar_h);
+        };
+        if (lane == 0 && t_begin < t_end) load_h1(t_begin);
+        for (long long tile = t_begin; tile < t_end; ++tile) {
+            const uint32_t i = (uint32_t)(tile - t_begin), buf = i & 1u, use = i >> 1;
+            const uint32_t acc = tmem_base + 256u * buf;
+            bt_bar(1, BT_WI);                                    // coefficients ready (workers only need it)
+            bt_bar(1, BT_WI);                                    // G stored
+            BT_CLK(0);
+            mbar_wait(&acc_free[buf], (use & 1u) ^ 1u);          // the helpers have drained this pair (two tiles ago)
+            BT_CLK(1);
+            if (tc_elect_one()) {
+                tc_fence_after();
+#pragma unroll
+                for (int ks = 0; ks < BT_J / 8; ++ks) {          // + 16 per K step: 256 bytes in the descriptor's address field
+                    tc_mma_tf32(acc, dG_hi + ks * 16, dW_hi + ks * 16, idesc2, ks > 0 ? 1u : 0u);
+                    tc_mma_tf32(acc, dG_lo + ks * 16, dW_hi + ks * 16, idesc, 1u);
+                }
+                tc_commit(&d1_full[buf]);
             }
-            *reinterpret_cast<uint4 *>(&msk[buf][r][0]) = mw;
+            __syncwarp();
+            BT_CLK(2);
+            bt_bar(1, BT_WI);                                    // Gt stored
+            BT_CLK(3);
+            mbar_wait(&at_full, i & 1u);                         // pooled operand of this tile stored by the helpers
+            BT_CLK(4);
+            if (tc_elect_one()) {
+                tc_fence_after();
+#pragma unroll
+                for (int ks = 0; ks < FT_ROWS / 8; ++ks) {
+                    tc_mma_tf32(acc + 128, dT_hi + ks * 16, dA_hi + ks * 16, idesc2, ks > 0 ? 1u : 0u);
+                    tc_mma_tf32(acc + 128, dT_lo + ks * 16, dA_hi + ks * 16, idesc, 1u);
+                }
+                tc_commit(&d2_full[buf]);
+            }
+            __syncwarp();
+            BT_CLK(5);
+            if (tile + 1 < t_end) {
+                // D2 was the last reader of the pooled-tile buffers: the next tile's h1 rows go there
+                mbar_wait(&d2_full[buf], use & 1u);
+                if (lane == 0) load_h1(tile + 1);
+                __syncwarp();
+            }
+            BT_CLK(6);
         }
-    };
-    if (t_begin < t_end) row_data(t_begin, 0);
-    asm volatile("cp.async.commit_group;" ::: "memory");
-    asm volatile("cp.async.wait_group 0;" ::: "memory");
-    for (long long tile = t_begin; tile < t_end; ++tile) {
-        const int u = (int)(tile / a.nchunk), chunk = (int)(tile - (long long)u * a.nchunk);
-        const long long b0 = (long long)chunk * FT_ROWS;
-        const int rows = (int)min((long long)FT_ROWS, a.B - b0);
-        XB_PHASE(0);
-        if (threadIdx.x == 0 && tile == t_begin) {      // later tiles: issued by the previous iteration (see below)
-            mbar_arrive_expect_tx(&bar_h, (uint32_t)rows * H * 4);
-            tma_bulk_g2s(sH, a.h1 + ((size_t)u * a.B + b0) * H, (uint32_t)rows * H * 4, &bar_h);
-        }
-        // per-row data of the NEXT tile (asynchronous copies, consumed after the barrier at the top of that tile) and the
-        // pooled tile of THIS one, raw (row, p) layout, into the output staging buffer: both fly during the G build
-        const int rb = (int)((tile - t_begin) & 1);
-        if (tile + 1 < t_end) row_data(tile + 1, rb ^ 1);
-        if (worker) {
+        BT_CLK_FLUSH(0, lane == 0);
+    } else if (role >= FT_THREADS / 32 && role < BT_ISSUE) {
+        // =========================== helper warps ===========================
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 96;");
+        const int hw = warp - FT_THREADS / 32;                   // 0..3: core matrices hw, hw + 4, ... of the pooled operand
+        const int q = warp & 3, row = 32 * q + lane;             // tensor-memory lane quarter this warp may read
+        const int htid = hw * 32 + lane;
+        const uint32_t lane_base = (uint32_t)(32 * q) << 16;
+        // one accumulator (rows x P, hi and lo halves added) -> staging
+        auto tmem_to_staging = [&](uint32_t taddr, bool row_ok) {
+            float *st = sS + row * a.P;
+#pragma unroll
+            for (int c = 0; c < BT_P / 16; ++c) {
+                if (16 * c < a.P) {
+                    uint32_t r[16], r2[16];
+                    tc_ld16_nowait(taddr + 16 * c, r);
+                    tc_ld16_nowait(taddr + BT_P + 16 * c, r2);
+                    tc_wait_ld();
+                    if (row_ok) {
+#pragma unroll
+                        for (int p = 0; p < 16; ++p)
+                            if (16 * c + p < a.P) st[16 * c + p] = __uint_as_float(r[p]) + __uint_as_float(r2[p]);
+                    }
+                }
+            }
+        };
+        BT_CLK_DECL;
+        for (long long tile = t_begin; tile < t_end; ++tile) {
+            const uint32_t i = (uint32_t)(tile - t_begin), buf = i & 1u, use = i >> 1;
+            const int u = (int)(tile / a.nchunk), chunk = (int)(tile - (long long)u * a.nchunk);
+            const long long b0 = (long long)chunk * FT_ROWS;
+            const int rows = (int)min((long long)FT_ROWS, a.B - b0);
+            const uint32_t acc = tmem_base + 256u * buf + lane_base;
+            BT_CLK(0);
+            // pooled tile transposed: rows p, K = b contiguous (B operand of D2); one warp store = one core matrix.
+            // All loads are issued now; they are consumed once the previous tile's D2 no longer reads the buffers.
+            constexpr int NIT = (BT_P / 8) * (FT_ROWS / 4) / BT_HW;      // 48 core matrices per warp
+            float xv[NIT];
             const float *psrc = a.pooled + ((size_t)b0 * a.U + u) * a.P;
             const size_t rstride = (size_t)a.U * a.P;
-            const int n = rows * a.P, dr = FT_THREADS / a.P, dp = FT_THREADS - dr * a.P;
-            int rr = threadIdx.x / a.P, pp = threadIdx.x - rr * a.P;
-            const uint32_t d0 = smem_u32(sS);
-            for (int i = threadIdx.x; i < n; i += FT_THREADS) {
-                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d0 + 4u * i), "l"(psrc + rr * rstride + pp) : "memory");
-                rr += dr; pp += dp;
-                if (pp >= a.P) { pp -= a.P; ++rr; }
+#pragma unroll
+            for (int k = 0; k < NIT; ++k) {
+                const int cm = hw + BT_HW * k;
+                const int pg = cm / (FT_ROWS / 4), bc = cm - pg * (FT_ROWS / 4);
+                const int p = pg * 8 + (lane >> 2), r = bc * 4 + (lane & 3);
+                xv[k] = (r < rows && p < a.P) ? __ldg(psrc + r * rstride + p) : 0.f;
             }
+            BT_CLK(1);
+            mbar_wait(&h_free, i & 1u);                          // the workers have read the h1 rows staged in these buffers
+            BT_CLK(2);
+#pragma unroll
+            for (int k = 0; k < NIT; ++k) st_split(sAh, sAl, (uint32_t)(hw + BT_HW * k) * 128 + lane * 4, xv[k]);
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&at_full);
+            // ---- D1 (row = sequence): staged, then written with consecutive threads on consecutive addresses ----
+            BT_CLK(3);
+            mbar_wait(&d1_full[buf], use & 1u);
+            BT_CLK(4);
+            tc_fence_after();
+            tmem_to_staging(acc, true);
+            bt_bar(2, BT_HW * 32);
+            {
+                float *dst = a.gpool + ((size_t)b0 * a.U + u) * a.P;
+                const int n = rows * a.P, dr = (BT_HW * 32) / a.P, dp = BT_HW * 32 - dr * a.P;
+                int rr = htid / a.P, pp = htid - rr * a.P;
+                for (int k = htid; k < n; k += BT_HW * 32) {
+                    dst[rr * rstride + pp] = sS[k];
+                    rr += dr; pp += dp;
+                    if (pp >= a.P) { pp -= a.P; ++rr; }
+                }
+            }
+            bt_bar(2, BT_HW * 32);                               // the copy-out has finished reading the staging buffer
+            BT_CLK(5);
+            // ---- D2 (row = hidden channel): the 100 x P tile is contiguous in global memory ----
+            mbar_wait(&d2_full[buf], use & 1u);
+            BT_CLK(6);
+            tc_fence_after();
+            tmem_to_staging(acc + 128, row < H);
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&acc_free[buf]);          // both accumulators of the pair have been read
+            bt_bar(2, BT_HW * 32);
+            {
+                float *dst = a.dW1p + ((size_t)chunk * a.U + u) * H * a.P;
+                const int n = H * a.P;
+                for (int k = htid; k < n; k += BT_HW * 32) dst[k] = sS[k];
+            }
+            bt_bar(2, BT_HW * 32);
+            BT_CLK(7);
         }
+        BT_CLK_FLUSH(1, htid == 0);
+    } else if (role < FT_THREADS / 32) {
+        // =========================== worker warps ===========================
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 192;");
+        // upstream gradient and dropout keep bits of the rows of tile `t` into buffer `rbuf` (threads 0..127, one row each)
+        auto row_data = [&](long long t, int rbuf) {
+            if (threadIdx.x >= FT_ROWS) return;
+            const int r = threadIdx.x;
+            const int tu = (int)(t / a.nchunk);
+            const long long tb0 = (t - (long long)tu * a.nchunk) * FT_ROWS;
+            const int trows = (int)min((long long)FT_ROWS, a.B - tb0);
+            const size_t e = (size_t)tu * a.B + tb0 + r;
+            if (r < trows) {
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(&gh2s[rbuf][r])), "l"(a.gh2 + e) : "memory");
+            } else {
+                gh2s[rbuf][r] = 0.f;
+            }
+            if (a.pdrop > 0.f && r < trows && a.dropmask) {
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(&msk[rbuf][r][0])), "l"(a.dropmask + e * 4) : "memory");
+            } else {
+                uint4 mw = make_uint4(~0u, ~0u, ~0u, ~0u);
+                if (a.pdrop > 0.f && r < trows) {     // no saved keep bits: regenerate them from the counter hash (slow path)
+                    uint32_t w[4] = {0u, 0u, 0u, 0u};
+                    for (int qd = 0; qd < H / 4; ++qd) w[qd >> 3] |= drop_keep4(seed, e * (H / 4) + qd, thresh) << (4 * (qd & 7));
+                    mw = make_uint4(w[0], w[1], w[2], w[3]);
+                }
+                *reinterpret_cast<uint4 *>(&msk[rbuf][r][0]) = mw;
+            }
+        };
+        if (t_begin < t_end) row_data(t_begin, 0);
         asm volatile("cp.async.commit_group;" ::: "memory");
-        if (u != cur_u) {
-            if (threadIdx.x < 128) {
-                const int j = threadIdx.x, ch = u * H + j;
-                const bool v = j < H;
-                float acc = 0.f, s1 = 0.f, s2 = 0.f;
-                if (v) {
-                    for (int k = 0; k < a.nchunk; ++k) {
-                        const float *pp = a.pb2 + ((size_t)u * a.nchunk + k) * 3 * H;
-                        acc += pp[j]; s1 += pp[H + j]; s2 += pp[2 * H + j];
-                    }
-                    if (chunk == 0) {
-                        if (a.dW2) a.dW2[ch] = acc;
-                        if (a.dbe2) a.dbe2[ch] = s1;
-                        if (a.dg2) a.dg2[ch] = s2;
-                        if (a.db1) a.db1[ch] = 0.f;          // bias followed by train-mode BatchNorm: gradient is exactly zero
-                        if (a.db2 && j == 0) a.db2[u] = 0.f;
-                    }
-                }
-                const float mu = v ? a.mean2[ch] : 0.f, inv = v ? a.invstd2[ch] : 0.f, gam = v ? a.g2[ch] : 0.f;
-                const float bet = v ? a.be2[ch] : 0.f, w2 = v ? a.W2[ch] : 0.f;
-                const float m1 = s1 / (float)a.B, m2 = s2 / (float)a.B;
-                const float c1 = gam * inv;
-                c1s[j] = c1;
-                c0s[j] = bet - mu * c1;
-                cAs[j] = w2 * c1 * keep_scale;
-                cBs[j] = -c1 * m2 * inv;
-                cCs[j] = c1 * (m2 * inv * mu - m1);
-            }
-            // W1[u] transposed: rows p, K = j contiguous (B operand of D1); one warp store = one core matrix.
-            // All loads are issued before the first store so that only one global latency is exposed.
-            if (worker) {
-                constexpr int NCM = (BT_P / 8) * (BT_J / 4), NIT = (NCM + FT_THREADS / 32 - 1) / (FT_THREADS / 32);
-                float xv[NIT];
-                const float *wsrc = a.W1 + (size_t)u * H * a.P;
-#pragma unroll
-                for (int i = 0; i < NIT; ++i) {
-                    const int cm = warp + (FT_THREADS / 32) * i;
-                    const int pg = cm / (BT_J / 4), kc = cm - pg * (BT_J / 4);
-                    const int p = pg * 8 + (lane >> 2), j = kc * 4 + (lane & 3);
-                    xv[i] = (cm < NCM && j < H && p < a.P) ? __ldg(wsrc + j * a.P + p) : 0.f;
-                }
-#pragma unroll
-                for (int i = 0; i < NIT; ++i) {
-                    const int cm = warp + (FT_THREADS / 32) * i;
-                    if (cm < NCM) st_split(sWh, sWl, (uint32_t)cm * 128 + lane * 4, xv[i]);
-                }
-            }
-            cur_u = u;
-        }
-        __syncthreads();          // coefficient arrays and gh2 tile ready for the G build
-        XB_PHASE(1);
-        mbar_wait(&bar_h, h_parity);
-        h_parity ^= 1;
-        XB_PHASE(2);
-        // G values of this thread.  Warp w owns the core matrices (row group rg = 8*(w/4) + g, column group kc = w%4 + 4t),
-        // g < 8, t < 7: thread (rl = lane/4, jl = lane%4) sees rows r = 8*rg + rl and only seven channels j = 4*kc + jl,
-        // whose BatchNorm coefficients are read once.  Pass 1 issues every shared-memory read of the h1 tile back to
-        // back; pass 2 does the arithmetic and the operand-tile stores.
-        float gv[BT_KT * BT_RG];
+        int cur_u = -1;
+        // Warp w owns the core matrices (row group rg = 8*(w/4) + g, column group kc = w%4 + 4t), g < 8, t < 7: thread
+        // (rl = lane/4, jl = lane%4) sees rows r = 8*rg + rl and only seven channels j = 4*kc + jl.
         const int kq = warp & 3, rg0 = BT_RG * (warp >> 2), rl = lane >> 2, jl = lane & 3;
-        if (worker) {
+        BT_CLK_DECL;
+        for (long long tile = t_begin; tile < t_end; ++tile) {
+            BT_CLK(0);
+            const uint32_t i = (uint32_t)(tile - t_begin), buf = i & 1u, use = i >> 1;
+            const int rb = (int)buf;
+            const int u = (int)(tile / a.nchunk), chunk = (int)(tile - (long long)u * a.nchunk);
+            const long long b0 = (long long)chunk * FT_ROWS;
+            const int rows = (int)min((long long)FT_ROWS, a.B - b0);
+            if (tile + 1 < t_end) row_data(tile + 1, rb ^ 1);
+            asm volatile("cp.async.commit_group;" ::: "memory");
+            if (u != cur_u) {
+                if (threadIdx.x < 128) {
+                    const int j = threadIdx.x, ch = u * H + j;
+                    const bool v = j < H;
+                    float acc = 0.f, s1 = 0.f, s2 = 0.f;
+                    if (v) {
+                        for (int k = 0; k < a.nchunk; ++k) {
+                            const float *pp = a.pb2 + ((size_t)u * a.nchunk + k) * 3 * H;
+                            acc += pp[j]; s1 += pp[H + j]; s2 += pp[2 * H + j];
+                        }
+                        if (chunk == 0) {
+                            if (a.dW2) a.dW2[ch] = acc;
+                            if (a.dbe2) a.dbe2[ch] = s1;
+                            if (a.dg2) a.dg2[ch] = s2;
+                            if (a.db1) a.db1[ch] = 0.f;          // bias followed by train-mode BatchNorm: gradient is exactly zero
+                            if (a.db2 && j == 0) a.db2[u] = 0.f;
+                        }
+                    }
+                    const float mu = v ? a.mean2[ch] : 0.f, inv = v ? a.invstd2[ch] : 0.f, gam = v ? a.g2[ch] : 0.f;
+                    const float bet = v ? a.be2[ch] : 0.f, w2 = v ? a.W2[ch] : 0.f;
+                    const float m1 = s1 / (float)a.B, m2 = s2 / (float)a.B;
+                    const float c1 = gam * inv;
+                    c1s[j] = c1;
+                    c0s[j] = bet - mu * c1;
+                    cAs[j] = w2 * c1 * keep_scale;
+                    cBs[j] = -c1 * m2 * inv;
+                    cCs[j] = c1 * (m2 * inv * mu - m1);
+                }
+                // W1[u] transposed: rows p, K = j contiguous (B operand of D1); one warp store = one core matrix.  The
+                // previous tile's D1 (its last reader) retired before that tile's second store pass.
+                {
+                    constexpr int NCM = (BT_P / 8) * (BT_J / 4), NIT = (NCM + FT_THREADS / 32 - 1) / (FT_THREADS / 32);
+                    float xv[NIT];
+                    const float *wsrc = a.W1 + (size_t)u * H * a.P;
+#pragma unroll
+                    for (int k = 0; k < NIT; ++k) {
+                        const int cm = warp + (FT_THREADS / 32) * k;
+                        const int pg = cm / (BT_J / 4), kc = cm - pg * (BT_J / 4);
+                        const int p = pg * 8 + (lane >> 2), j = kc * 4 + (lane & 3);
+                        xv[k] = (cm < NCM && j < H && p < a.P) ? __ldg(wsrc + j * a.P + p) : 0.f;
+                    }
+#pragma unroll
+                    for (int k = 0; k < NIT; ++k) {
+                        const int cm = warp + (FT_THREADS / 32) * k;
+                        if (cm < NCM) st_split(sWh, sWl, (uint32_t)cm * 128 + lane * 4, xv[k]);
+                    }
+                }
+                cur_u = u;
+            }
+            BT_CLK(1);
+            asm volatile("cp.async.wait_group 1;" ::: "memory");      // this tile's row data (copied during the previous tile)
+            bt_bar(1, BT_WI);                                          // coefficient arrays and row data visible
+            BT_CLK(2);
+            // the h1 values of this thread from the staged tile (its copy was issued when the previous D2, the last reader
+            // of the G region as well, had retired); once every worker holds its values the buffers go to the helpers
+            mbar_wait(&bar_h, i & 1u);
+            float gv[BT_KT * BT_RG];
 #pragma unroll
             for (int t = 0; t < BT_KT; ++t) {
-                const int kc = kq + 4 * t, j = 4 * kc + jl;
+                const int j = 4 * (kq + 4 * t) + jl;
 #pragma unroll
                 for (int g = 0; g < BT_RG; ++g) {
                     const int r = (rg0 + g) * 8 + rl;
                     gv[t * BT_RG + g] = (j < H && r < rows) ? sH[r * H + j] : 0.f;
                 }
             }
-            float k1[BT_KT], k0[BT_KT], kA[BT_KT], kB[BT_KT], kC[BT_KT];
-#pragma unroll
-            for (int t = 0; t < BT_KT; ++t) {
-                const int j = 4 * (kq + 4 * t) + jl;      // <= 111: inside the 128-entry arrays, zero beyond channel 99
-                k1[t] = c1s[j]; k0[t] = c0s[j]; kA[t] = cAs[j]; kB[t] = cBs[j]; kC[t] = cCs[j];
-            }
-#pragma unroll
-            for (int g = 0; g < BT_RG; ++g) {
-                const int rg = rg0 + g, r = rg * 8 + rl;
-                const float gh = gh2s[rb][r];
-                const uint4 mw = *reinterpret_cast<const uint4 *>(&msk[rb][r][0]);
-                const uint32_t mws[4] = {mw.x, mw.y, mw.z, mw.w};
+            bt_bar(3, FT_THREADS);
+            if (threadIdx.x == 0) mbar_arrive(&h_free);
+            BT_CLK(3);
+            // ---- G values and the j-contiguous operand of D1 ----
+            {
+                float k1[BT_KT], k0[BT_KT], kA[BT_KT], kB[BT_KT], kC[BT_KT];
 #pragma unroll
                 for (int t = 0; t < BT_KT; ++t) {
-                    const int kc = kq + 4 * t;
-                    if (kc < BT_J / 4) {                       // warp-uniform (t = 6 exists only for w%4 < 2)
-                        const int j = 4 * kc + jl;
-                        const float h = gv[t * BT_RG + g];
-                        const float zb = fmaf(h, k1[t], k0[t]);
-                        const bool kept = (mws[t >> 1] >> (j & 31)) & 1u;    // word j/32 == t/2
-                        float v = fmaf(h, kB[t], kC[t]);
-                        if (zb > 0.f && kept) v = fmaf(gh, kA[t], v);
-                        if (r >= rows) v = 0.f;
-                        gv[t * BT_RG + g] = v;
-                        st_split(sR, sR + BT_G_BYTES, (uint32_t)(rg * (BT_J / 4) + kc) * 128 + lane * 4, v);      // G, j-contiguous
+                    const int j = 4 * (kq + 4 * t) + jl;      // <= 111: inside the 128-entry arrays, zero beyond channel 99
+                    k1[t] = c1s[j]; k0[t] = c0s[j]; kA[t] = cAs[j]; kB[t] = cBs[j]; kC[t] = cCs[j];
+                }
+#pragma unroll
+                for (int g = 0; g < BT_RG; ++g) {
+                    const int rg = rg0 + g, r = rg * 8 + rl;
+                    const float gh = gh2s[rb][r];
+                    const uint4 mw = *reinterpret_cast<const uint4 *>(&msk[rb][r][0]);
+                    const uint32_t mws[4] = {mw.x, mw.y, mw.z, mw.w};
+#pragma unroll
+                    for (int t = 0; t < BT_KT; ++t) {
+                        const int kc = kq + 4 * t;
+                        if (kc < BT_J / 4) {                       // warp-uniform (t = 6 exists only for w%4 < 2)
+                            const int j = 4 * kc + jl;
+                            const float h = gv[t * BT_RG + g];
+                            const float zb = fmaf(h, k1[t], k0[t]);
+                            const bool kept = (mws[t >> 1] >> (j & 31)) & 1u;    // word j/32 == t/2
+                            float v = fmaf(h, kB[t], kC[t]);
+                            if (zb > 0.f && kept) v = fmaf(gh, kA[t], v);
+                            if (r >= rows) v = 0.f;
+                            gv[t * BT_RG + g] = v;
+                            st_split(sR, sR + BT_G_BYTES, (uint32_t)(rg * (BT_J / 4) + kc) * 128 + lane * 4, v);      // G, j-contiguous
+                        }
                     }
                 }
             }
-        }
-        asm volatile("cp.async.wait_group 0;" ::: "memory");      // pooled tile and the next tile's row data have landed
-        fence_proxy_async();
-        tc_fence_before();
-        __syncthreads();
-        XB_PHASE(3);
-        // ---- D1 = G . W1   (TMEM columns 0..95) ----
-        if (warp_u == FT_THREADS / 32 && tc_elect_one()) {
-            tc_fence_after();
+            BT_CLK(4);
+            fence_proxy_async();
+            bt_bar(1, BT_WI);                                          // -> the issue warp starts D1
+            BT_CLK(5);
+            // ---- once D1 has retired: the same values b-contiguous (Gt[j][b]) over the region it no longer reads ----
+            mbar_wait(&d1_full[buf], use & 1u);
+            BT_CLK(6);
 #pragma unroll
-            for (int ks = 0; ks < BT_J / 8; ++ks) {      // + 16 per K step: 256 bytes in the descriptor's address field
-                tc_mma_tf32(tmem_base, dG_hi + ks * 16, dW_hi + ks * 16, idesc2, ks > 0 ? 1u : 0u);
-                tc_mma_tf32(tmem_base, dG_lo + ks * 16, dW_hi + ks * 16, idesc, 1u);
-            }
-            tc_commit(&bar);
-        }
-        XB_PHASE(4);
-        // while D1 runs: pooled tile transposed, rows p, K = b contiguous (B operand of D2).  It overwrites the h1
-        // staging, which every thread has finished reading (barrier above).
-        if (worker) {
-            constexpr int NIT = (BT_P / 8) * (FT_ROWS / 4) / (FT_THREADS / 32);     // 24 core matrices per warp
-            float xv[NIT];
+            for (int t = 0; t < BT_KT; ++t) {
+                const int kc = kq + 4 * t;
+                if (kc < BT_J / 4) {
 #pragma unroll
-            for (int i = 0; i < NIT; ++i) {
-                const int cm = warp + (FT_THREADS / 32) * i;
-                const int pg = cm / (FT_ROWS / 4), bc = cm - pg * (FT_ROWS / 4);
-                const int p = pg * 8 + (lane >> 2), r = bc * 4 + (lane & 3);
-                xv[i] = (r < rows && p < a.P) ? sS[r * a.P + p] : 0.f;       // staged by the copies issued at the top of the tile
-            }
-#pragma unroll
-            for (int i = 0; i < NIT; ++i) st_split(sAh, sAl, (uint32_t)(warp + (FT_THREADS / 32) * i) * 128 + lane * 4, xv[i]);
-        }
-        XB_PHASE(5);
-        mbar_wait(&bar, parity);
-        parity ^= 1;
-        tc_fence_after();
-        XB_PHASE(6);
-        // ---- phase 2: the same values b-contiguous (Gt[j][b]) over the region the finished MMAs no longer read ----
-#pragma unroll
-        for (int t = 0; t < BT_KT; ++t) {
-            const int kc = kq + 4 * t;
-            if (worker && kc < BT_J / 4) {
-#pragma unroll
-                for (int g = 0; g < BT_RG; ++g)
-                    st_split(sR, sR + BT_GT_BYTES, core_off(4 * kc + jl, (rg0 + g) * 8 + rl, BT_B_SBO), gv[t * BT_RG + g]);
-            }
-        }
-        // rows 104..127 of Gt are never written: they only feed accumulator rows that are not read back
-        fence_proxy_async();
-        tc_fence_before();
-        __syncthreads();
-        XB_PHASE(7);
-        // ---- D2 = G^T . pooled   (TMEM columns 128..223) ----
-        if (warp_u == FT_THREADS / 32 && tc_elect_one()) {
-            tc_fence_after();
-#pragma unroll
-            for (int ks = 0; ks < FT_ROWS / 8; ++ks) {
-                tc_mma_tf32(tmem_base + 128, dT_hi + ks * 16, dA_hi + ks * 16, idesc2, ks > 0 ? 1u : 0u);
-                tc_mma_tf32(tmem_base + 128, dT_lo + ks * 16, dA_hi + ks * 16, idesc, 1u);
-            }
-            tc_commit(&bar);
-        }
-        XB_PHASE(8);
-        // ---- while D2 runs, all warps drain D1 (row = sequence): warps 0-3 take columns 0-15 and 32-47, warps 4-7
-        //      columns 16-31; the tile is staged in shared memory and written with consecutive threads on consecutive
-        //      addresses (rows of P floats) ----
-        const int q = warp & 3, which = warp >> 2;
-        const int row = 32 * q + lane;
-        auto tmem_to_staging = [&](uint32_t taddr, bool row_ok) {
-            float *st = sS + row * a.P;
-            if (which == 0) {
-                uint32_t r[32], r2[32];
-                tc_ld16_nowait(taddr, r);
-                tc_ld16_nowait(taddr + 32, r + 16);
-                tc_ld16_nowait(taddr + BT_P, r2);
-                tc_ld16_nowait(taddr + BT_P + 32, r2 + 16);
-                tc_wait_ld();
-                if (row_ok) {
-#pragma unroll
-                    for (int p = 0; p < 16; ++p) {
-                        if (p < a.P) st[p] = __uint_as_float(r[p]) + __uint_as_float(r2[p]);
-                        if (32 + p < a.P) st[32 + p] = __uint_as_float(r[16 + p]) + __uint_as_float(r2[16 + p]);
-                    }
-                }
-            } else {
-                uint32_t r[16], r2[16];
-                tc_ld16_nowait(taddr + 16, r);
-                tc_ld16_nowait(taddr + BT_P + 16, r2);
-                tc_wait_ld();
-                if (row_ok) {
-#pragma unroll
-                    for (int p = 0; p < 16; ++p)
-                        if (16 + p < a.P) st[16 + p] = __uint_as_float(r[p]) + __uint_as_float(r2[p]);
+                    for (int g = 0; g < BT_RG; ++g)
+                        st_split(sR, sR + BT_GT_BYTES, core_off(4 * kc + jl, (rg0 + g) * 8 + rl, BT_B_SBO), gv[t * BT_RG + g]);
                 }
             }
-        };
-        if (worker) tmem_to_staging(tmem_base + ((uint32_t)(32 * q) << 16), true);
-        __syncthreads();
-        if (worker) {
-            float *dst = a.gpool + ((size_t)b0 * a.U + u) * a.P;
-            const size_t rstride = (size_t)a.U * a.P;
-            const int n = rows * a.P, dr = FT_THREADS / a.P, dp = FT_THREADS - dr * a.P;
-            int rr = threadIdx.x / a.P, pp = threadIdx.x - rr * a.P;
-            for (int i = threadIdx.x; i < n; i += FT_THREADS) {
-                dst[rr * rstride + pp] = sS[i];
-                rr += dr; pp += dp;
-                if (pp >= a.P) { pp -= a.P; ++rr; }
-            }
+            // rows 104..127 of Gt are never written: they only feed accumulator rows that are not read back
+            BT_CLK(7);
+            fence_proxy_async();
+            bt_bar(1, BT_WI);                                          // -> the issue warp starts D2
+            BT_CLK(8);
         }
-        XB_PHASE(9);
-        mbar_wait(&bar, parity);
-        parity ^= 1;
-        tc_fence_after();
-        if (threadIdx.x == 0 && tile + 1 < t_end) {
-            // D2 has retired: the pooled-tile buffers are free, prefetch the next tile's h1 rows into them
-            const long long tn = tile + 1;
-            const int un = (int)(tn / a.nchunk);
-            const long long bn = (tn - (long long)un * a.nchunk) * FT_ROWS;
-            const uint32_t bytes = (uint32_t)min((long long)FT_ROWS, a.B - bn) * H * 4;
-            mbar_arrive_expect_tx(&bar_h, bytes);
-            tma_bulk_g2s(sH, a.h1 + ((size_t)un * a.B + bn) * H, bytes, &bar_h);
-        }
-        __syncthreads();      // the D1 copy-out has finished reading the staging buffer
-        XB_PHASE(10);
-        // ---- D2 drain (row = hidden channel): the 100 x P tile is contiguous in global memory ----
-        if (worker) tmem_to_staging(tmem_base + ((uint32_t)(32 * q) << 16) + 128, row < H);
-        __syncthreads();
-        if (worker) {
-            float *dst = a.dW1p + ((size_t)chunk * a.U + u) * H * a.P;
-            const int n = H * a.P;
-            for (int i = threadIdx.x; i < n; i += FT_THREADS) dst[i] = sS[i];
-        }
-        XB_PHASE(11);
-        tc_fence_before();
-        __syncthreads();
-        XB_PHASE(12);
+        BT_CLK_FLUSH(2, threadIdx.x == 0);
     }
+    tc_fence_before();
+    __syncthreads();
     if (warp == 0) {
         tc_fence_after();
-        tc_dealloc(tmem_base, 256u);
+        tc_dealloc(tmem_base, 512u);
     }
 }
 
@@ -1101,9 +1148,6 @@ int xb_fc_stack_fwd_eval_tc(const float *pooled, long long B, int U, int P, cons
     return launch_fc1_tc(true, a, stream);
 }
 
-#ifdef XB_PHASE_CLOCKS
-extern "C" int xb_dbg_phase_clocks(long long *host) { return (int)cudaMemcpyFromSymbol(host, g_phase_clk, sizeof(g_phase_clk)); }
-#endif
 
 // returns XB_ERR_UNSUPPORTED (without setting an error) when the class count does not fit one N tile
 int xb_linear_tc(const float *x, long long B, int U, int C, const float *W, const float *bias, float *out, cudaStream_t stream)
@@ -1120,6 +1164,10 @@ int xb_linear_tc(const float *x, long long B, int U, int C, const float *W, cons
     linear_tc_kernel<<<(unsigned)((B + FT_ROWS - 1) / FT_ROWS), FT_THREADS, smem, stream>>>(a);
     return xb_check_launch("linear_tc");
 }
+
+#ifdef XB_PHASE_CLOCKS
+extern "C" int xb_dbg_phase_clocks(long long *host) { return (int)cudaMemcpyFromSymbol(host, g_bt_clk, sizeof(g_bt_clk)); }
+#endif
 
 bool xb_fc_tc_enabled()
 {

@@ -1,4 +1,5 @@
-"""Per-phase cycle counts of bwd_fc1_tc_kernel (library built with XB_NVCC_EXTRA=-DXB_PHASE_CLOCKS)."""
+"""Where the three warp roles of bwd_fc1_tc_kernel spend their cycles (CTA 0, summed over its tiles).
+Library built with XB_NVCC_EXTRA=-DXB_PHASE_CLOCKS."""
 import ctypes, sys, torch
 sys.path.insert(0, ".")
 from explainn_b200 import networks, train as xtrain, _cabi
@@ -15,16 +16,13 @@ tr = xtrain.FusedTrainer(m, torch.nn.BCEWithLogitsLoss(), opt, dropout_seed=1, u
 for i in range(4):
     tr.step(data[i * B:(i + 1) * B], labels[i * B:(i + 1) * B])
 torch.cuda.synchronize()
-buf = (ctypes.c_longlong * (32 * 16))()
+buf = (ctypes.c_longlong * (3 * 16))()
 fn = _cabi.lib.xb_dbg_phase_clocks
 fn.argtypes = [ctypes.c_void_p]
 assert fn(buf) == 0
-names = ["top", "coef+W1t", "h1 wait", "G build", "sync+D1 issue", "pooled fill", "D1 wait", "Gt stores", "sync+D2 issue",
-         "D1 drain", "D2 wait", "D1/D2 sync", "D2 drain", "end sync"]
-for t in range(9):
-    c = [buf[t * 16 + i] for i in range(13)]
-    if c[0] == 0:
-        break
-    d = [c[i + 1] - c[i] for i in range(12)]
-    print("tile %d total %6d :" % (t, c[12] - c[0]), " ".join("%s=%d" % (n, v) for n, v in zip(
-        ["coef", "h1wait", "Gbuild", "syncD1", "poolfill", "D1wait", "Gt", "syncD2", "D1drain", "D2wait+sync", "D2drain", "endsync"], d)))
+names = [["barriers", "wait acc_free", "D1 issue", "bar Gt", "wait at_full", "D2 issue"],
+         ["top", "pooled loads", "wait D2 prev", "At stores", "wait D1", "D1 drain", "wait D2", "D2 drain"],
+         ["loop", "h1 loads+coef", "bar", "wait D2 prev", "G build", "bar", "wait D1", "Gt stores", "bar"]]
+for r, role in enumerate(["issue", "helper", "worker"]):
+    v = [buf[r * 16 + i] for i in range(len(names[r]))]
+    print("%-7s total %7d :" % (role, sum(v)), " ".join("%s=%d" % (n, x) for n, x in zip(names[r], v)))
