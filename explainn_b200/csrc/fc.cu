@@ -545,23 +545,35 @@ __global__ void __launch_bounds__(128) bwd_final_linear2_kernel(const float *__r
 // BatchNorm-3 backward per unit: sums over the batch, then gh2 (U,B), dgamma3, dbeta3.  One warp per unit.
 // mode 0: both halves; mode 1: only the sums, written to sums[2u], sums[2u+1]; mode 2: only the second half, with the
 // sums read back from there (synchronised BatchNorm: the caller averages them over the ranks in between).
-__global__ void __launch_bounds__(256) bwd_bn3_kernel(const float *__restrict__ gz, const float *__restrict__ h2, long long B,
+__global__ void __launch_bounds__(128) bwd_bn3_kernel(const float *__restrict__ gz, const float *__restrict__ h2, long long B,
                                                       int U, const float *__restrict__ g3, const float *__restrict__ mean3,
                                                       const float *__restrict__ invstd3, float *__restrict__ gh2,
                                                       float *__restrict__ dg3, float *__restrict__ db3, float *__restrict__ sums,
                                                       int mode)
 {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int u = blockIdx.x * 8 + warp;
+    const int u = blockIdx.x * 4 + warp;
     if (u >= U) return;
     const float mean = mean3[u], inv = invstd3[u];
     const float *h2u = h2 + (size_t)u * B;
     float s1 = 0.f, s2 = 0.f;
     if (mode != 2) {
-        for (long long b = lane; b < B; b += 32) {
-            const float g = gz[b * U + u], xh = (h2u[b] - mean) * inv;
-            s1 += g;
-            s2 = fmaf(g, xh, s2);
+        // eight rows per trip, all loads of a trip issued before the arithmetic (the warp is alone on its unit: without
+        // this the loop is one memory latency per 32 rows)
+        for (long long b0 = 0; b0 < B; b0 += 256) {
+            float g[8], x[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                const long long b = b0 + 32 * k + lane;
+                g[k] = b < B ? gz[b * U + u] : 0.f;
+                x[k] = b < B ? h2u[b] : mean;
+            }
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                const float xh = (x[k] - mean) * inv;
+                s1 += g[k];
+                s2 = fmaf(g[k], xh, s2);
+            }
         }
         s1 = warp_sum(s1);
         s2 = warp_sum(s2);
@@ -578,9 +590,20 @@ __global__ void __launch_bounds__(256) bwd_bn3_kernel(const float *__restrict__ 
         if (dg3) dg3[u] = s2;
     }
     const float m1 = s1 / (float)B, m2 = s2 / (float)B, k = g3[u] * inv;
-    for (long long b = lane; b < B; b += 32) {
-        const float xh = (h2u[b] - mean) * inv;
-        gh2[(size_t)u * B + b] = k * (gz[b * U + u] - m1 - xh * m2);
+    for (long long b0 = 0; b0 < B; b0 += 256) {
+        float g[8], x[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const long long b = b0 + 32 * i + lane;
+            g[i] = b < B ? gz[b * U + u] : 0.f;
+            x[i] = b < B ? h2u[b] : mean;
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const long long b = b0 + 32 * i + lane;
+            const float xh = (x[i] - mean) * inv;
+            if (b < B) gh2[(size_t)u * B + b] = k * (g[i] - m1 - xh * m2);
+        }
     }
 }
 
@@ -1092,10 +1115,10 @@ static int fc_stack_bwd_impl(int phases, const float *glogits, long long B, int 
         }
         cudaFuncSetAttribute(bwd_gunit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_gu);
         bwd_gunit_kernel<<<dim3((unsigned)((B + 7) / 8), (U + GU_UT - 1) / GU_UT), 256, smem_gu, stream>>>(glogits, Wf, unit, B, U, C, gz3);
-        if (phases != 7) bwd_bn3_kernel<<<(U + 7) / 8, 256, 0, stream>>>(gz3, h2, B, U, bn3_w, mean3, invstd3, gh2, dbn3_w, dbn3_b, pb2, 1);
+        if (phases != 7) bwd_bn3_kernel<<<(U + 3) / 4, 128, 0, stream>>>(gz3, h2, B, U, bn3_w, mean3, invstd3, gh2, dbn3_w, dbn3_b, pb2, 1);
     }
     if (phases & 2) {
-        bwd_bn3_kernel<<<(U + 7) / 8, 256, 0, stream>>>(gz3, h2, B, U, bn3_w, mean3, invstd3, gh2, dbn3_w, dbn3_b, pb2, phases == 7 ? 0 : 2);
+        bwd_bn3_kernel<<<(U + 3) / 4, 128, 0, stream>>>(gz3, h2, B, U, bn3_w, mean3, invstd3, gh2, dbn3_w, dbn3_b, pb2, phases == 7 ? 0 : 2);
         bwd_fc2_kernel<<<dim3(U, nchunk), FC_THREADS, 0, stream>>>(h1, gh2, B, U, bn2_w, bn2_b, mean2, invstd2, W2, pdrop, seed, seed_dev, dropmask, pb2);
     }
     if (!(phases & 4)) return xb_check_launch("fc_stack_bwd");
@@ -1223,7 +1246,7 @@ extern "C" int explainn_fc1_stack_bwd(const float *glogits, long long B, int U, 
     }
     cudaFuncSetAttribute(bwd_gunit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_gu);
     bwd_gunit_kernel<<<dim3((unsigned)((B + 7) / 8), (U + GU_UT - 1) / GU_UT), 256, smem_gu, stream>>>(glogits, Wf, unit, B, U, C, gz3);
-    bwd_bn3_kernel<<<(U + 7) / 8, 256, 0, stream>>>(gz3, h2, B, U, bn_w, mean3, invstd3, gh2, dbn_w, dbn_b, nullptr, 0);
+    bwd_bn3_kernel<<<(U + 3) / 4, 128, 0, stream>>>(gz3, h2, B, U, bn_w, mean3, invstd3, gh2, dbn_w, dbn_b, nullptr, 0);
     const size_t smem = ((size_t)P + BM + (size_t)BM * (P + 1)) * 4;
     if (smem > 200 * 1024) {
         xb_set_error("fc1_stack_bwd: pooled length %d needs %zu bytes of shared memory", P, smem);

@@ -94,10 +94,16 @@ __global__ void __launch_bounds__(256) p2p_adam_kernel(const P2pArgs a)
     }
     __syncthreads();
 
-    const double t = (double)*a.step;
-    const double bc1 = 1.0 - pow((double)a.b1, t), bc2 = 1.0 - pow((double)a.b2, t);
-    const float step_size = (float)((double)a.lr / bc1);
-    const float bc2s = (float)sqrt(bc2);
+    // bias corrections: double-precision pow, once per CTA (thread 0 computes them while it waits for the flags anyway)
+    __shared__ float s_step_size, s_bc2s;
+    if (threadIdx.x == 0) {
+        const double t = (double)*a.step;
+        const double bc1 = 1.0 - pow((double)a.b1, t), bc2 = 1.0 - pow((double)a.b2, t);
+        s_step_size = (float)((double)a.lr / bc1);
+        s_bc2s = (float)sqrt(bc2);
+    }
+    __syncthreads();
+    const float step_size = s_step_size, bc2s = s_bc2s;
     const float w1 = 1.0f - a.b1, w2 = 1.0f - a.b2;
     const float scale = 1.0f / (float)a.world;
     const long long n4 = a.n >> 2, o4 = a.off >> 2;      // the flat buffers are 16-byte aligned and padded to multiples of 4

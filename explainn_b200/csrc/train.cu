@@ -387,12 +387,18 @@ __global__ void __launch_bounds__(256) loss_kernel(const float *__restrict__ log
         last = atomicAdd(ticket, 1u) == gridDim.x - 1;
     }
     __syncthreads();
-    if (last && threadIdx.x == 0) {
+    if (last && threadIdx.x < 64) {
+        // the last block adds the partial sums: one per thread, then a fixed shuffle tree (deterministic)
+        static_assert(LOSS_MAX_BLOCKS == 64, "two warps");
         __threadfence();
-        double v = 0.0;
-        for (unsigned k = 0; k < gridDim.x; ++k) v += ((volatile double *)partial)[k];
-        *loss = (float)(v / (double)n);
-        *ticket = 0u;
+        double v = threadIdx.x < gridDim.x ? ((volatile double *)partial)[threadIdx.x] : 0.0;
+        v = warp_sum_d(v);
+        if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+        asm volatile("bar.sync 1, 64;" ::: "memory");
+        if (threadIdx.x == 0) {
+            *loss = (float)((red[0] + red[1]) / (double)n);
+            *ticket = 0u;
+        }
     }
 }
 
@@ -408,19 +414,45 @@ __global__ void __launch_bounds__(256) adam_kernel(float *__restrict__ p, const 
                                                    float *__restrict__ v, long long n, const float *__restrict__ step,
                                                    float lr, float b1, float b2, float eps, float grad_scale)
 {
-    const double t = (double)*step;
-    const double bc1 = 1.0 - pow((double)b1, t), bc2 = 1.0 - pow((double)b2, t);
-    const float step_size = (float)((double)lr / bc1);
-    const float bc2s = (float)sqrt(bc2);
+    // bias corrections: double-precision pow, once per CTA (every thread doing it cost more than the update itself)
+    __shared__ float s_step_size, s_bc2s;
+    if (threadIdx.x == 0) {
+        const double t = (double)*step;
+        const double bc1 = 1.0 - pow((double)b1, t), bc2 = 1.0 - pow((double)b2, t);
+        s_step_size = (float)((double)lr / bc1);
+        s_bc2s = (float)sqrt(bc2);
+    }
+    __syncthreads();
+    const float step_size = s_step_size, bc2s = s_bc2s;
     const float w1 = 1.0f - b1, w2 = 1.0f - b2;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
-        const float gi = g[i] * grad_scale;
-        const float mi = fmaf(gi - m[i], w1, m[i]);
-        const float vi = fmaf(gi * gi, w2, v[i] * b2);
+    auto upd = [&](float &pi, float gi_raw, float &mi, float &vi) {
+        const float gi = gi_raw * grad_scale;
+        mi = fmaf(gi - mi, w1, mi);
+        vi = fmaf(gi * gi, w2, vi * b2);
+        const float denom = sqrtf(vi) / bc2s + eps;
+        pi = pi - step_size * (mi / denom);
+    };
+    const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x, nthr = (long long)gridDim.x * blockDim.x;
+    const bool vec = ((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(g) | reinterpret_cast<uintptr_t>(m) |
+                       reinterpret_cast<uintptr_t>(v)) & 15u) == 0;
+    const long long n4 = vec ? n >> 2 : 0;
+    for (long long i = tid; i < n4; i += nthr) {
+        float4 pi = reinterpret_cast<float4 *>(p)[i], mi = reinterpret_cast<float4 *>(m)[i], vi = reinterpret_cast<float4 *>(v)[i];
+        const float4 gi = reinterpret_cast<const float4 *>(g)[i];
+        upd(pi.x, gi.x, mi.x, vi.x);
+        upd(pi.y, gi.y, mi.y, vi.y);
+        upd(pi.z, gi.z, mi.z, vi.z);
+        upd(pi.w, gi.w, mi.w, vi.w);
+        reinterpret_cast<float4 *>(m)[i] = mi;
+        reinterpret_cast<float4 *>(v)[i] = vi;
+        reinterpret_cast<float4 *>(p)[i] = pi;
+    }
+    for (long long i = 4 * n4 + tid; i < n; i += nthr) {
+        float pi = p[i], mi = m[i], vi = v[i];
+        upd(pi, g[i], mi, vi);
         m[i] = mi;
         v[i] = vi;
-        const float denom = sqrtf(vi) / bc2s + eps;
-        p[i] = p[i] - step_size * (mi / denom);
+        p[i] = pi;
     }
 }
 
@@ -430,6 +462,20 @@ __global__ void reduce_partials_kernel(float *__restrict__ out, const float *__r
     if (i >= n) return;
     float v = 0.f;
     for (int c = 0; c < k; ++c) v += part[(size_t)c * n + i];
+    out[i] = v;
+}
+
+// the same four elements at a time (n a multiple of 4, 16-byte aligned buffers); same summation order per element
+__global__ void reduce_partials4_kernel(float4 *__restrict__ out, const float4 *__restrict__ part, long long n4, int k)
+{
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n4) return;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 4
+    for (int c = 0; c < k; ++c) {
+        const float4 x = part[(size_t)c * n4 + i];
+        v.x += x.x; v.y += x.y; v.z += x.z; v.w += x.w;
+    }
     out[i] = v;
 }
 
@@ -582,8 +628,8 @@ extern "C" int explainn_adam_step(float *param, const float *grad, float *exp_av
     XB_REQUIRE(param && grad && exp_avg && exp_avg_sq && step && n >= 0, "adam_step: bad argument");
     adam_tick_kernel<<<1, 1, 0, stream>>>(step);
     if (n > 0) {
-        long long blocks = (n + 255) / 256;
-        const long long cap = 8LL * xb_num_sms();
+        long long blocks = (n / 4 + 255) / 256 + 1;
+        const long long cap = 4LL * xb_num_sms();
         if (blocks > cap) blocks = cap;
         adam_kernel<<<(unsigned)blocks, 256, 0, stream>>>(param, grad, exp_avg, exp_avg_sq, n, step, lr, beta1, beta2, eps, grad_scale);
     }
@@ -594,6 +640,10 @@ extern "C" int explainn_reduce_partials(float *out, const float *partials, long 
 {
     XB_REQUIRE(out && partials && n >= 0 && k >= 1, "reduce_partials: bad argument");
     if (n == 0) return XB_OK;
-    reduce_partials_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(out, partials, n, k);
+    if (n % 4 == 0 && ((reinterpret_cast<uintptr_t>(out) | reinterpret_cast<uintptr_t>(partials)) & 15u) == 0)
+        reduce_partials4_kernel<<<(unsigned)((n / 4 + 255) / 256), 256, 0, stream>>>(reinterpret_cast<float4 *>(out),
+                                                                                  reinterpret_cast<const float4 *>(partials), n / 4, k);
+    else
+        reduce_partials_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(out, partials, n, k);
     return xb_check_launch("reduce_partials");
 }
