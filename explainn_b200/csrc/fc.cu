@@ -364,18 +364,37 @@ __global__ void __launch_bounds__(256) out_train_kernel(const float *__restrict_
                                                         const float *__restrict__ Wf, const float *__restrict__ bf,
                                                         float *__restrict__ unit, float *__restrict__ logits, int wf_in_smem, double inv_batch)
 {
-    extern __shared__ float xs[];   // [8][U] then sc3[U], sh3[U], then (when it fits) Wf as [C][U+1]
-    float *sc3 = xs + OT_ROWS * U, *sh3 = sc3 + U;
-    float *wfs = sh3 + U;
+    extern __shared__ float xs[];   // [8][U] then sc3[U], sh3[U] (unused: kept for the layout), then (when it fits) Wf as [C][U+1]
+    float *wfs = xs + OT_ROWS * U + 2 * U;
     // blockIdx.y selects a slice of the classes, so that more SMs share the work and each CTA stages less of Wf
     const int cper = (C + gridDim.y - 1) / gridDim.y;
     const int c_lo = blockIdx.y * cper, c_hi = min(C, c_lo + cper);
-    if (wf_in_smem)
-        for (int c = c_lo + (threadIdx.x >> 5); c < c_hi; c += blockDim.x >> 5)
-            for (int k = threadIdx.x & 31; k < U; k += 32) wfs[(c - c_lo) * (U + 1) + k] = Wf[(size_t)c * U + k];
     const long long b0 = (long long)blockIdx.x * OT_ROWS;
     const int rows = (int)min((long long)OT_ROWS, B - b0);
+    // Every loop below issues its global loads in batches before it uses them: the CTA is alone with its latencies
+    // (a sequential version spent most of its time waiting for one load after the other).
+    if (wf_in_smem) {
+        const int nel = (c_hi - c_lo) * U;                   // rows c_lo .. c_hi-1 of Wf are one contiguous block
+        const float *src = Wf + (size_t)c_lo * U;
+        for (int i0 = threadIdx.x; i0 < nel; i0 += 8 * 256) {
+            float v[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = i0 + 256 * j < nel ? src[i0 + 256 * j] : 0.f;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const int i = i0 + 256 * j;
+                if (i < nel) {
+                    const int c = i / U;
+                    wfs[c * (U + 1) + (i - c * U)] = v[j];
+                }
+            }
+        }
+    }
+    // thread = unit: BatchNorm-3 statistics, then the unit's OT_ROWS values of h2 (contiguous in its (U,B) layout)
     for (int u = threadIdx.x; u < U; u += blockDim.x) {
+        float hv[OT_ROWS];
+#pragma unroll
+        for (int r = 0; r < OT_ROWS; ++r) hv[r] = r < rows ? h2[(size_t)u * B + b0 + r] : 0.f;
         double sm = 0.0, sq = 0.0;
         for (int k = 0; k < nchunk; ++k) {
             sm += (double)part3[((size_t)u * nchunk + k) * 2];
@@ -397,19 +416,18 @@ __global__ void __launch_bounds__(256) out_train_kernel(const float *__restrict_
             }
         }
         const float a = g3[u] * inv;
-        sc3[u] = a;
-        sh3[u] = be3[u] - (float)mean * a;
-    }
-    __syncthreads();
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    if (warp < rows) {
-        for (int u = lane; u < U; u += 32) {
-            const float v = fmaxf(fmaf(h2[(size_t)u * B + b0 + warp], sc3[u], sh3[u]), 0.f);
-            if (blockIdx.y == 0) unit[(b0 + warp) * U + u] = v;
-            xs[warp * U + u] = v;
+        const float sh = be3[u] - (float)mean * a;
+#pragma unroll
+        for (int r = 0; r < OT_ROWS; ++r) {
+            if (r < rows) {
+                const float v = fmaxf(fmaf(hv[r], a, sh), 0.f);
+                if (blockIdx.y == 0) unit[(b0 + r) * U + u] = v;
+                xs[r * U + u] = v;
+            }
         }
     }
     __syncthreads();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (warp < rows) {
         const float *xr = xs + warp * U;
         for (int c = c_lo + lane; c < c_hi; c += 32) {
@@ -449,9 +467,17 @@ __global__ void __launch_bounds__(256) bwd_gunit_kernel(const float *__restrict_
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (Wf != nullptr) {
         for (int i = threadIdx.x; i < rows * C; i += blockDim.x) gls[i] = gl[b0 * C + i];
-        for (int i = threadIdx.x; i < C * GU_UT; i += blockDim.x) {
-            const int c = i / GU_UT, uu = i - c * GU_UT;
-            wfs[i] = u0 + uu < U ? Wf[(size_t)c * U + u0 + uu] : 0.f;
+        // eight loads in flight per thread (issued before the stores: one exposed latency per batch, not per element)
+        for (int i0 = threadIdx.x; i0 < C * GU_UT; i0 += 8 * 256) {
+            float v[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const int i = i0 + 256 * j, c = i / GU_UT, uu = i - c * GU_UT;
+                v[j] = (i < C * GU_UT && u0 + uu < U) ? Wf[(size_t)c * U + u0 + uu] : 0.f;
+            }
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+                if (i0 + 256 * j < C * GU_UT) wfs[i0 + 256 * j] = v[j];
         }
         __syncthreads();
     }
