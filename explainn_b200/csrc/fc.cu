@@ -248,20 +248,21 @@ __global__ void __launch_bounds__(FC_THREADS) fc1_train_kernel(const float *__re
 }
 
 // BatchNorm-2 (batch stats) -> ReLU -> dropout -> FC2 (+b2) ; per-tile sums for BatchNorm-3
-__global__ void __launch_bounds__(FC_THREADS) fc2_train_kernel(
+constexpr int F2_THREADS = 128;        // fc2_train_kernel: one thread per sequence of a 128-row tile
+__global__ void __launch_bounds__(F2_THREADS) fc2_train_kernel(
     const float *__restrict__ h1, long long B, int U, const float *__restrict__ part2, int nchunk,
     const float *__restrict__ g2, const float *__restrict__ be2, float *__restrict__ rm2, float *__restrict__ rv2,
     float momentum, float eps, const float *__restrict__ W2, const float *__restrict__ b2, float *__restrict__ mean2,
     float *__restrict__ invstd2, float pdrop, unsigned long long seed0, const unsigned long long *__restrict__ seed_dev,
     uint32_t *__restrict__ dropmask, float *__restrict__ h2, float *__restrict__ part3, double inv_batch)
 {
-    __shared__ float sc[128], sh[128], w2s[128];
-    __shared__ float red[8][2];
+    __shared__ __align__(16) float sc[128], sh[128], w2s[128];
+    __shared__ float red[F2_THREADS / 32][2];
     const unsigned long long seed = seed0 + (seed_dev ? *seed_dev * 0xD1B54A32D192ED03ull : 0ull);
     const int u = blockIdx.x, chunk = blockIdx.y;
     const long long b0 = (long long)chunk * BM;
     const int rows = (int)min((long long)BM, B - b0);
-    if (threadIdx.x < 128) {
+    {
         const int j = threadIdx.x;
         float a = 0.f, c = 0.f, w = 0.f;
         if (j < H) {
@@ -300,55 +301,62 @@ __global__ void __launch_bounds__(FC_THREADS) fc2_train_kernel(
         sc[j] = a; sh[j] = c; w2s[j] = w;
     }
     __syncthreads();
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    // thread = one sequence of the tile: its 100 hidden values are read as 25 quads (pairs of quads = whole 32-byte
+    // sectors), BatchNorm-2 -> ReLU -> dropout -> dot with W2 accumulated in a register.  No shuffles, no idle lanes; the
+    // per-channel coefficients come from shared memory as broadcasts.
+    static_assert(H % 4 == 0 && F2_THREADS == BM, "one thread per row, quads of channels");
     const unsigned thresh = pdrop > 0.f ? (unsigned)min(4294967295.0, (double)pdrop * 4294967296.0) : 0u;
     const float keep_scale = pdrop > 0.f ? 1.0f / (1.0f - pdrop) : 1.0f;
-    float s3 = 0.f, q3 = 0.f;
-    // lane l < 25 owns hidden channels 4l .. 4l+3 (one 16-byte load per row); its BN-2 / FC2 coefficients stay in registers
-    static_assert(H % 4 == 0 && H / 4 <= 32, "quad layout");
-    const bool act = lane < H / 4;
-    const int j0 = act ? 4 * lane : 0;
-    const float4 scv = act ? make_float4(sc[j0], sc[j0 + 1], sc[j0 + 2], sc[j0 + 3]) : make_float4(0.f, 0.f, 0.f, 0.f);
-    const float4 shv = act ? make_float4(sh[j0], sh[j0 + 1], sh[j0 + 2], sh[j0 + 3]) : make_float4(0.f, 0.f, 0.f, 0.f);
-    const float4 w2v = act ? make_float4(w2s[j0], w2s[j0 + 1], w2s[j0 + 2], w2s[j0 + 3]) : make_float4(0.f, 0.f, 0.f, 0.f);
-    const float bias2 = b2[u];
-    // software pipeline: the next two rows of this warp are in flight while this row is reduced
-    float4 hn = make_float4(0.f, 0.f, 0.f, 0.f), hn2 = hn;
-    if (warp < rows && act) hn = *reinterpret_cast<const float4 *>(h1 + ((size_t)u * B + b0 + warp) * H + j0);
-    if (warp + 8 < rows && act) hn2 = *reinterpret_cast<const float4 *>(h1 + ((size_t)u * B + b0 + warp + 8) * H + j0);
-    for (int r = warp; r < rows; r += 8) {
-        const size_t rowi = (size_t)u * B + b0 + r;
-        const float4 hc = hn;
-        hn = hn2;
-        if (r + 16 < rows && act) hn2 = *reinterpret_cast<const float4 *>(h1 + (rowi + 16) * H + j0);
+    const int r = threadIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const bool valid = r < rows;
+    const size_t rowi = (size_t)u * B + b0 + (valid ? r : 0);
+    const float4 *hp = reinterpret_cast<const float4 *>(h1 + rowi * H);
+    float dot = 0.f;
+    uint32_t mw[4] = {0u, 0u, 0u, 0u};
+    auto quad = [&](int q, const float4 hc) {
+        const float4 a = *reinterpret_cast<const float4 *>(&sc[4 * q]), c = *reinterpret_cast<const float4 *>(&sh[4 * q]);
+        const float4 w = *reinterpret_cast<const float4 *>(&w2s[4 * q]);
         uint32_t nib = 15u;
-        if (pdrop > 0.f) nib = drop_keep4(seed, rowi * (H / 4) + lane, thresh);
-        const float v0 = (nib & 1u) ? fmaxf(fmaf(hc.x, scv.x, shv.x), 0.f) * keep_scale : 0.f;
-        const float v1 = (nib & 2u) ? fmaxf(fmaf(hc.y, scv.y, shv.y), 0.f) * keep_scale : 0.f;
-        const float v2 = (nib & 4u) ? fmaxf(fmaf(hc.z, scv.z, shv.z), 0.f) * keep_scale : 0.f;
-        const float v3 = (nib & 8u) ? fmaxf(fmaf(hc.w, scv.w, shv.w), 0.f) * keep_scale : 0.f;
-        float dot = fmaf(v3, w2v.w, fmaf(v2, w2v.z, fmaf(v1, w2v.y, v0 * w2v.x)));
-        if (pdrop > 0.f && dropmask) {
-            // the keep bits are saved for the backward: word w of the row holds channels 32w .. 32w+31 (8 lanes' nibbles)
-            uint32_t m = act ? nib << (4 * (lane & 7)) : 0u;
-            m |= __shfl_xor_sync(0xffffffffu, m, 1);
-            m |= __shfl_xor_sync(0xffffffffu, m, 2);
-            m |= __shfl_xor_sync(0xffffffffu, m, 4);
-            if ((lane & 7) == 0) dropmask[rowi * 4 + (lane >> 3)] = m;
+        if (pdrop > 0.f) nib = drop_keep4(seed, rowi * (H / 4) + q, thresh);
+        const float v0 = (nib & 1u) ? fmaxf(fmaf(hc.x, a.x, c.x), 0.f) * keep_scale : 0.f;
+        const float v1 = (nib & 2u) ? fmaxf(fmaf(hc.y, a.y, c.y), 0.f) * keep_scale : 0.f;
+        const float v2 = (nib & 4u) ? fmaxf(fmaf(hc.z, a.z, c.z), 0.f) * keep_scale : 0.f;
+        const float v3 = (nib & 8u) ? fmaxf(fmaf(hc.w, a.w, c.w), 0.f) * keep_scale : 0.f;
+        dot += fmaf(v3, w.w, fmaf(v2, w.z, fmaf(v1, w.y, v0 * w.x)));
+        mw[q >> 3] |= nib << (4 * (q & 7));
+    };
+    if (valid) {
+        // three pairs of quads in flight ahead of the arithmetic
+        constexpr int NQ = H / 4, NP = NQ / 2;
+        float4 buf[6];
+#pragma unroll
+        for (int i = 0; i < 6; ++i) buf[i] = hp[i];
+#pragma unroll
+        for (int pq = 0; pq < NP; ++pq) {
+            const float4 x0 = buf[(2 * pq) % 6], x1 = buf[(2 * pq + 1) % 6];
+            if (2 * pq + 6 < NQ) buf[(2 * pq) % 6] = hp[2 * pq + 6];
+            if (2 * pq + 7 < NQ) buf[(2 * pq + 1) % 6] = hp[2 * pq + 7];
+            quad(2 * pq, x0);
+            quad(2 * pq + 1, x1);
         }
-        dot = warp_sum(dot);
-        const float o = dot + bias2;
-        if (lane == 0) {
-            h2[rowi] = o;
-            s3 += o;
-            q3 = fmaf(o, o, q3);
-        }
+        if (NQ & 1) quad(NQ - 1, buf[(NQ - 1) % 6]);
     }
+    float s3 = 0.f, q3 = 0.f;
+    if (valid) {
+        const float o = dot + b2[u];
+        h2[rowi] = o;
+        s3 = o;
+        q3 = o * o;
+        // the keep bits are saved for the backward: word w of the row holds channels 32w .. 32w+31 (8 quads' nibbles)
+        if (pdrop > 0.f && dropmask) *reinterpret_cast<uint4 *>(dropmask + rowi * 4) = make_uint4(mw[0], mw[1], mw[2], mw[3]);
+    }
+    s3 = warp_sum(s3);
+    q3 = warp_sum(q3);
     if (lane == 0) { red[warp][0] = s3; red[warp][1] = q3; }
     __syncthreads();
     if (threadIdx.x < 2) {
         float v = 0.f;
-        for (int w = 0; w < 8; ++w) v += red[w][threadIdx.x];
+        for (int w = 0; w < F2_THREADS / 32; ++w) v += red[w][threadIdx.x];
         part3[((size_t)u * nchunk + chunk) * 2 + threadIdx.x] = v;
     }
 }
@@ -364,37 +372,18 @@ __global__ void __launch_bounds__(256) out_train_kernel(const float *__restrict_
                                                         const float *__restrict__ Wf, const float *__restrict__ bf,
                                                         float *__restrict__ unit, float *__restrict__ logits, int wf_in_smem, double inv_batch)
 {
-    extern __shared__ float xs[];   // [8][U] then sc3[U], sh3[U] (unused: kept for the layout), then (when it fits) Wf as [C][U+1]
-    float *wfs = xs + OT_ROWS * U + 2 * U;
+    extern __shared__ float xs[];   // [8][U] then sc3[U], sh3[U], then (when it fits) Wf as [C][U+1]
+    float *sc3 = xs + OT_ROWS * U, *sh3 = sc3 + U;
+    float *wfs = sh3 + U;
     // blockIdx.y selects a slice of the classes, so that more SMs share the work and each CTA stages less of Wf
     const int cper = (C + gridDim.y - 1) / gridDim.y;
     const int c_lo = blockIdx.y * cper, c_hi = min(C, c_lo + cper);
+    if (wf_in_smem)
+        for (int c = c_lo + (threadIdx.x >> 5); c < c_hi; c += blockDim.x >> 5)
+            for (int k = threadIdx.x & 31; k < U; k += 32) wfs[(c - c_lo) * (U + 1) + k] = Wf[(size_t)c * U + k];
     const long long b0 = (long long)blockIdx.x * OT_ROWS;
     const int rows = (int)min((long long)OT_ROWS, B - b0);
-    // Every loop below issues its global loads in batches before it uses them: the CTA is alone with its latencies
-    // (a sequential version spent most of its time waiting for one load after the other).
-    if (wf_in_smem) {
-        const int nel = (c_hi - c_lo) * U;                   // rows c_lo .. c_hi-1 of Wf are one contiguous block
-        const float *src = Wf + (size_t)c_lo * U;
-        for (int i0 = threadIdx.x; i0 < nel; i0 += 8 * 256) {
-            float v[8];
-#pragma unroll
-            for (int j = 0; j < 8; ++j) v[j] = i0 + 256 * j < nel ? src[i0 + 256 * j] : 0.f;
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                const int i = i0 + 256 * j;
-                if (i < nel) {
-                    const int c = i / U;
-                    wfs[c * (U + 1) + (i - c * U)] = v[j];
-                }
-            }
-        }
-    }
-    // thread = unit: BatchNorm-3 statistics, then the unit's OT_ROWS values of h2 (contiguous in its (U,B) layout)
     for (int u = threadIdx.x; u < U; u += blockDim.x) {
-        float hv[OT_ROWS];
-#pragma unroll
-        for (int r = 0; r < OT_ROWS; ++r) hv[r] = r < rows ? h2[(size_t)u * B + b0 + r] : 0.f;
         double sm = 0.0, sq = 0.0;
         for (int k = 0; k < nchunk; ++k) {
             sm += (double)part3[((size_t)u * nchunk + k) * 2];
@@ -416,18 +405,19 @@ __global__ void __launch_bounds__(256) out_train_kernel(const float *__restrict_
             }
         }
         const float a = g3[u] * inv;
-        const float sh = be3[u] - (float)mean * a;
-#pragma unroll
-        for (int r = 0; r < OT_ROWS; ++r) {
-            if (r < rows) {
-                const float v = fmaxf(fmaf(hv[r], a, sh), 0.f);
-                if (blockIdx.y == 0) unit[(b0 + r) * U + u] = v;
-                xs[r * U + u] = v;
-            }
-        }
+        sc3[u] = a;
+        sh3[u] = be3[u] - (float)mean * a;
     }
     __syncthreads();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (warp < rows) {
+        for (int u = lane; u < U; u += 32) {
+            const float v = fmaxf(fmaf(h2[(size_t)u * B + b0 + warp], sc3[u], sh3[u]), 0.f);
+            if (blockIdx.y == 0) unit[(b0 + warp) * U + u] = v;
+            xs[warp * U + u] = v;
+        }
+    }
+    __syncthreads();
     if (warp < rows) {
         const float *xr = xs + warp * U;
         for (int c = c_lo + lane; c < c_hi; c += 32) {
@@ -1012,7 +1002,7 @@ static int fc_stack_fwd_train_impl(int phases, long long batch_total, const floa
         }
     }
     if (phases & 2)
-        fc2_train_kernel<<<dim3(U, nchunk), FC_THREADS, 0, stream>>>(h1, B, U, part2, nchunk, bn2_w, bn2_b, bn2_rm, bn2_rv, momentum, eps,
+        fc2_train_kernel<<<dim3(U, nchunk), F2_THREADS, 0, stream>>>(h1, B, U, part2, nchunk, bn2_w, bn2_b, bn2_rm, bn2_rv, momentum, eps,
                                                                      W2, b2, mean2, invstd2, pdrop, seed, seed_dev, dropmask, h2, part3, inv_batch);
     if (phases & 4) {
         cudaFuncSetAttribute(out_train_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem3);

@@ -121,14 +121,12 @@ __global__ void __launch_bounds__(128) bn1_stats_kernel(const int *__restrict__ 
     __syncthreads();
     double a = 0.0, q = 0.0;
     for (int i = threadIdx.x; i < W; i += blockDim.x) {
-        // M is symmetric: column i read down the rows, so that consecutive threads read consecutive addresses and the
-        // loads of a trip are independent (same summation order as along row i)
+        const int *row = M + (size_t)i * W;
         double d = 0.0;
-#pragma unroll 8
-        for (int j = 0; j < W; ++j) d += wsm[j] * (double)M[(size_t)j * W + i];
+        for (int j = 0; j < W; ++j) d += wsm[j] * (double)row[j];
         Mw_out[(size_t)u * W + i] = (float)d;
         q += wsm[i] * d;
-        a += wsm[i] * (double)M[(size_t)i * W + i];
+        a += wsm[i] * (double)row[i];
     }
     a = warp_sum_d(a);
     q = warp_sum_d(q);
