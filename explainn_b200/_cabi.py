@@ -83,6 +83,7 @@ SIGNATURES = {
     "explainn_loss_fwd_bwd": [_P, _P, _LL, _I, _I, _F, _P, _P, _P, _P],
     "explainn_adam_step": [_P, _P, _P, _P, _LL, _P, _F, _F, _F, _F, _F, _P],
     "explainn_reduce_partials": [_P, _P, _LL, _I, _P],
+    "explainn_counters_inc": [_P, _P, _P, _P, _P],
     "explainn_p2p_flag_bytes": [],
     "explainn_p2p_alloc": [_LL, _P],
     "explainn_p2p_free": [_P],

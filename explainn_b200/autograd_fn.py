@@ -87,7 +87,14 @@ class TrainWorkspace:
                  "sync_world")
 
 
-def train_forward(model, x, params=None, seed=None, seed_dev=None):
+def _bump_counters(bn2, bn3, seed_dev, bump_seed):
+    """num_batches_tracked of BatchNorm-2 / -3 (BatchNorm-1's is incremented by its statistics kernel) and, for a captured
+    step, the per-replay dropout counter: one launch."""
+    call("explainn_counters_inc", ptr(bn2.num_batches_tracked), ptr(bn3.num_batches_tracked) if bn3 is not None else None,
+         ptr(seed_dev) if bump_seed else None, None, stream())
+
+
+def train_forward(model, x, params=None, seed=None, seed_dev=None, bump_seed=False):
     """Runs the training-mode forward kernels.  Returns a TrainWorkspace (logits in ws.logits)."""
     if _is_variant(model):
         from . import variants
@@ -95,12 +102,16 @@ def train_forward(model, x, params=None, seed=None, seed_dev=None):
             raise NotImplementedError("explainn_b200: sync_bn is built for the default unit (num_fc = 2, MaxPool1d(7, 7))")
         if params is None:
             params = [p.detach() for p in _params(model)]
+        if bump_seed:
+            seed_dev.add_(1)
         return variants.train_forward(model, x, params, _next_dropout_seed() if seed is None else seed, seed_dev)
     _check_modes(model)
     L = model.linears
     if params is None:
         params = [p.detach() for p in _params(model)]
     if _num_fc(model) == 1:
+        if bump_seed:
+            seed_dev.add_(1)
         return _train_forward_fc1(model, x, params)
     (cw, cb, g1, b1n, W1, b1, g2, be2, W2, b2, g3, be3, Wf, bf) = params
     o = model._options
@@ -112,6 +123,7 @@ def train_forward(model, x, params=None, seed=None, seed_dev=None):
         raise ValueError("Expected more than 1 value per channel when training, got input size %s" % (tuple(x.shape),))
     dev = pk.codes.device
     bn1, bn2, bn3, drop = L[1], L[7], L[11], L[9]
+    _bump_counters(bn2, bn3, seed_dev, bump_seed)          # before the first kernel that reads the dropout counter
     ws = TrainWorkspace()
     ws.pk, ws.B, ws.U, ws.C, ws.F = pk, B, U, C, F
     S = pk.L - F + 1
@@ -162,8 +174,6 @@ def train_forward(model, x, params=None, seed=None, seed_dev=None):
         call("explainn_fc_stack_fwd_train_phase", 2, B * world, *fargs)
         dsync.all_reduce(part3, op=dsync.ReduceOp.SUM)
         call("explainn_fc_stack_fwd_train_phase", 4, B * world, *fargs)
-    bn2.num_batches_tracked.add_(1)
-    bn3.num_batches_tracked.add_(1)
     return ws
 
 
@@ -241,10 +251,15 @@ _CONST = {}
 
 
 def _const(dev, U):
+    """(ones, zeros) of length U, cached per device.  Under CUDA-graph capture nothing is cached: tensors made there live
+    in the graph's private pool and are filled by captured kernels, so they must not outlive the graph."""
     key = (str(dev), U)
-    if key not in _CONST:
-        _CONST[key] = (torch.ones(U, dtype=torch.float32, device=dev), torch.zeros(U, dtype=torch.float32, device=dev))
-    return _CONST[key]
+    if key in _CONST:
+        return _CONST[key]
+    pair = (torch.ones(U, dtype=torch.float32, device=dev), torch.zeros(U, dtype=torch.float32, device=dev))
+    if not torch.cuda.is_current_stream_capturing():
+        _CONST[key] = pair
+    return pair
 
 
 def train_backward(model, ws, gout, params=None, grads=None, wrt_unit=False, between=None):

@@ -636,6 +636,19 @@ extern "C" int explainn_adam_step(float *param, const float *grad, float *exp_av
     return xb_check_launch("adam_step");
 }
 
+// ---- up to four int64 device counters += 1 in one launch (BatchNorm num_batches_tracked, the dropout step counter) ----
+__global__ void counters_inc_kernel(long long *c0, long long *c1, long long *c2, long long *c3)
+{
+    long long *c[4] = {c0, c1, c2, c3};
+    if (threadIdx.x < 4 && c[threadIdx.x]) *c[threadIdx.x] += 1;
+}
+
+extern "C" int explainn_counters_inc(long long *c0, long long *c1, long long *c2, long long *c3, cudaStream_t stream)
+{
+    counters_inc_kernel<<<1, 32, 0, stream>>>(c0, c1, c2, c3);
+    return xb_check_launch("counters_inc");
+}
+
 extern "C" int explainn_reduce_partials(float *out, const float *partials, long long n, int k, cudaStream_t stream)
 {
     XB_REQUIRE(out && partials && n >= 0 && k >= 1, "reduce_partials: bad argument");

@@ -91,9 +91,12 @@ def encode_dna_array(text, seq_len=None, device=None):
     key = (str(dev), B, Lt)
     offs_d = _OFFSETS.get(key)
     if offs_d is None:
-        if len(_OFFSETS) > 64:
-            _OFFSETS.clear()
-        offs_d = _OFFSETS[key] = torch.arange(B + 1, dtype=torch.int64, device=dev) * Lt
+        offs_d = torch.arange(B + 1, dtype=torch.int64, device=dev) * Lt
+        # under CUDA-graph capture the tensor lives in the graph's private pool (filled by captured kernels): not cached
+        if not torch.cuda.is_current_stream_capturing():
+            if len(_OFFSETS) > 64:
+                _OFFSETS.clear()
+            _OFFSETS[key] = offs_d
     codes = torch.empty((B, (L + 15) // 16), dtype=torch.int32, device=dev)
     nmask = torch.empty((B, (L + 31) // 32), dtype=torch.int32, device=dev)
     if B:

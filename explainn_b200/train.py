@@ -150,9 +150,10 @@ class FusedTrainer:
         return all(p.data_ptr() == v.data_ptr() for p, v in zip(self.params, self.views_p))
 
     def _fwd_bwd(self, x, y, seed, seed_dev=None):
-        """forward + fused loss + backward into the flat gradient buffer; returns the loss tensor."""
+        """forward + fused loss + backward into the flat gradient buffer; returns the loss tensor.  With `seed_dev` (a
+        captured step) the forward first increments that counter, so every replay draws a new dropout mask."""
         ps = self.views_p
-        ws = autograd_fn.train_forward(self.model, x, ps, seed=seed, seed_dev=seed_dev)
+        ws = autograd_fn.train_forward(self.model, x, ps, seed=seed, seed_dev=seed_dev, bump_seed=seed_dev is not None)
         B, C = ws.logits.shape
         if tuple(y.shape) != (B, C):
             raise ValueError("labels of shape %s do not match logits %s" % (tuple(y.shape), (B, C)))
@@ -248,7 +249,6 @@ class FusedTrainer:
         try:
             self._split = None
             with torch.cuda.graph(g, capture_error_mode="thread_local"):
-                self._seed_ctr.add_(1)
                 c.gloss = self._fwd_bwd(c.gx, c.gy, seed, self._seed_ctr)
             c.launches = _cabi.LAUNCHES - l0
             if self._split is not None:      # world > 1: the conv backward is a second graph (see _between)

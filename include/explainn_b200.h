@@ -404,6 +404,11 @@ long long explainn_loss_scratch_bytes(void);
 int explainn_loss_fwd_bwd(const float *logits, const float *target, long long B, int C, int kind, float grad_scale,
                           float *loss, float *dlogits, void *scratch, cudaStream_t stream);
 
+/* Adds 1 to each non-NULL int64 device counter in one launch: `num_batches_tracked` of the train-mode BatchNorm1d
+ * layers (torch.nn.BatchNorm1d increments it per forward; networks.py:107,112) and the per-replay dropout counter of a
+ * captured training step.  The four pointers must be distinct. */
+int explainn_counters_inc(long long *c0, long long *c1, long long *c2, long long *c3, cudaStream_t stream);
+
 /* ---- fused Adam over one flat buffer ------------------------------------------------------------------------------
  * torch.optim.Adam with its defaults-compatible options (amsgrad=False, weight_decay=0, maximize=False), the
  * optimizer scripts/train.py:246-247 builds (explainn/train/train.py:67).  *step (device float) is incremented
