@@ -84,19 +84,16 @@ __device__ void wait_flags(const unsigned long long *mine, int phase, int world,
 
 __global__ void __launch_bounds__(256) p2p_adam_kernel(const P2pArgs a)
 {
-    // ---- barrier A ----
+    // ---- barrier A; meanwhile a thread of another warp computes the bias corrections (double-precision pow, once per
+    //      CTA: the step counter is local, it does not depend on the peers) ----
+    __shared__ float s_step_size, s_bc2s;
     if (threadIdx.x == 0) {
         if (blockIdx.x == 0) {
             __threadfence_system();
             for (int q = 0; q < a.world; ++q) st_sys(a.flags[q] + 0 * P2P_MAX_WORLD + a.rank, a.seq);
         }
         wait_flags(a.flags[a.rank], 0, a.world, a.seq, a.timeout_ns, a.error);
-    }
-    __syncthreads();
-
-    // bias corrections: double-precision pow, once per CTA (thread 0 computes them while it waits for the flags anyway)
-    __shared__ float s_step_size, s_bc2s;
-    if (threadIdx.x == 0) {
+    } else if (threadIdx.x == 32) {
         const double t = (double)*a.step;
         const double bc1 = 1.0 - pow((double)a.b1, t), bc2 = 1.0 - pow((double)a.b2, t);
         s_step_size = (float)((double)a.lr / bc1);
