@@ -1,5 +1,5 @@
-"""explainn_conv_pool_bwd: the tensor-core scatter (csrc/conv_bwd_tc.cu, one `partial` slice per SM) against the
-shared-memory scatter kernel (csrc/train.cu, few slices) and against a float64 restatement of the sum they compute:
+"""explainn_conv_pool_bwd: the tensor-core scatter (csrc/conv_bwd_tc.cu; CTA = (128-unit tile, slice of the batch), one
+`partial` slice per CTA of a tile) against the shared-memory scatter kernel (csrc/train.cu, few slices) and against a float64 restatement of the sum they compute:
     A[u, c*F + k] = sum_{b,p} gpool[b,u,p] * pooled[b,u,p] * X[b, c, 7p + idx[b,u,p] + k]
 (backward of MaxPool1d -> exp -> BatchNorm1d -> grouped Conv1d, explainn/models/networks.py:98-102)."""
 import numpy as np
